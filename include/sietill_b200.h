@@ -1,0 +1,131 @@
+/* sietill_b200.h — C-ABI of the B200-native GMM acoustic-model hot path.
+ *
+ * Drop-in boundary for the hot path of kkromberg/SpeechRecognition's src/sietill:
+ *   GMM max-approx scoring  ->  Viterbi alignment over linear HMMs with TDPs  ->  EM accumulation.
+ * Plain pointers and sizes only; every buffer passed in is HOST memory owned by the caller, every
+ * device buffer is owned by the context.  All functions return 0 on success, non-zero on failure
+ * (the text is available from sgmm_last_error); no C++ exception crosses this boundary.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the reference
+ * repository, src/sietill/).  The C++ classes of speechrecognition_b200/csrc/host/ (MixtureModel,
+ * Aligner, TdpModel, Trainer — same public signatures as the reference's) are the callers;
+ * INTEGRATION.md shows the binding a maintainer of the reference would add.
+ */
+#ifndef SIETILL_B200_H
+#define SIETILL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sgmm_ctx sgmm_ctx;
+
+/* AlignmentItem, Types.hpp:29-38 (8 bytes; only slot [0] of each frame is used, num-max-aligns = 1). */
+typedef struct {
+  uint16_t count;
+  uint16_t state;
+  float    weight;
+} sgmm_alignment_item;
+
+/* TDP lookup convention.  SOURCE: Aligner::align_sequence_full looks the penalty up with the state
+ * of the position the transition LEAVES (Alignment.cpp:95,100,108).  DESTINATION: the pruned aligner
+ * and the recogniser use the state it ENTERS (Alignment.cpp:191, Recognizer.cpp:141,170). */
+enum { SGMM_TDP_SOURCE = 0, SGMM_TDP_DESTINATION = 1 };
+
+/* ---- context -------------------------------------------------------------------------------- */
+/* One context per GPU (not thread-safe; replaces the single shared MixtureModel/Aligner pair that
+ * main() builds, SieTill.cpp:107-113). */
+int         sgmm_create(int device, sgmm_ctx** out);
+void        sgmm_destroy(sgmm_ctx* ctx);
+const char* sgmm_last_error(const sgmm_ctx* ctx); /* ctx may be NULL: error of a failed sgmm_create */
+const char* sgmm_version(void);
+
+/* ---- model tables (K5) ---------------------------------------------------------------------- */
+/* Uploads the parameter tables that MixtureModel::finalize/calculate_variance produce
+ * (Mixtures.cpp:251-275,374-461), already resolved through mixtures_[s][k] into state-major order:
+ * density j = state_off[s] + k is the k-th entry of mixtures_[s].  mean / inv_var are [D*dim] f64
+ * (means_ / vars_inv_ rows), norm[D] = norm_[var_idx], log_weight[D] = mean_weights_log_[mean_idx].
+ * The device keeps them in f64 and evaluates density_score_sse's exact operation order
+ * (Mixtures.cpp:645-690). */
+int sgmm_set_model(sgmm_ctx* ctx, uint32_t dim, uint32_t n_states, const uint32_t* state_off,
+                   const double* mean, const double* inv_var, const double* norm,
+                   const double* log_weight);
+
+/* ---- corpus --------------------------------------------------------------------------------- */
+/* Corpus::features_ (Corpus.hpp:75-81): one contiguous row-major float[n_frames * dim]; one H2D copy,
+ * resident until replaced. */
+int sgmm_set_features(sgmm_ctx* ctx, const float* x, uint64_t n_frames, uint32_t dim);
+
+/* Per-utterance frame ranges (segment_offsets, Training.cpp:67-76) and utterance automata
+ * (Trainer::build_segment_automaton, Training.cpp:239-253) concatenated: utterance u owns frames
+ * [frame_off[u], frame_off[u+1]) and positions automata[aut_off[u] .. aut_off[u+1]). */
+int sgmm_set_corpus(sgmm_ctx* ctx, uint32_t n_utts, const uint64_t* frame_off,
+                    const uint32_t* automata, const uint32_t* aut_off);
+
+/* TdpModel (TdpModel.cpp:19-29): silence_state always pays `forward`. */
+int sgmm_set_tdp(sgmm_ctx* ctx, double loop, double forward, double skip, uint32_t silence_state);
+
+/* ---- scoring (K1) --------------------------------------------------------------------------- */
+/* MixtureModel::min_score (Mixtures.cpp:696-713) for every frame in [f0, f1) and every state:
+ * scores[(f-f0)*n_states + s] (f64, bit-identical to the reference), argmin likewise = position k
+ * within mixtures_[s].  Either output may be NULL.  Replaces the per-cell score() calls of
+ * Alignment.cpp:90 / Recognizer.cpp:149,179 by one batched pass (the prepare_sequence idiom of
+ * FeatureScorer.hpp:12-16). */
+int sgmm_score_all(sgmm_ctx* ctx, uint64_t f0, uint64_t f1, double* scores, uint32_t* argmin);
+
+/* ---- alignment (K1 gathered + K2) ----------------------------------------------------------- */
+/* Aligner::align_sequence_full (Alignment.cpp:50-144) for every utterance of the corpus in one call
+ * (the loop of Training.cpp:168-183).  The alignment stays resident on the device for
+ * sgmm_accumulate; `alignment` (n_frames items, may be NULL) and `costs` (n_utts, may be NULL)
+ * receive host copies.  An utterance whose end state is unreachable (S > 2T-1) gets cost +inf. */
+int sgmm_align(sgmm_ctx* ctx, int tdp_convention, sgmm_alignment_item* alignment, double* costs);
+
+/* Upload an alignment produced elsewhere (e.g. the linear segmentation of Training.cpp:85-99). */
+int sgmm_set_alignment(sgmm_ctx* ctx, const sgmm_alignment_item* alignment, uint64_t n_frames);
+
+/* ---- EM accumulation (K3 + K4) -------------------------------------------------------------- */
+/* MixtureModel::accumulate with max_approx (Mixtures.cpp:278-372) over the resident alignment:
+ * for frame f with aligned state m the density is k = 0 (first_pass) or min_score(x_f, m).second with
+ * the CURRENT model; then count[j] += 1, sum_x[j*dim..] += x, sum_xx[j*dim..] += x*x for
+ * j = state_off[m] + k.  Outputs are per density in state-major order (count[D], sum_x[D*dim],
+ * sum_xx[D*dim], all f64, starting from 0 — the caller adds the reference's 1e-4 variance seed,
+ * Mixtures.cpp:243, and folds pooled variances).  score_sum receives sum_f min_score(x_f, m).first,
+ * i.e. Trainer::calc_am_score's numerator (Training.cpp:585-612) for the model the E-step used
+ * (0 when first_pass).  If a communicator is attached the four outputs are summed over all ranks
+ * with ONE ncclAllReduce before they are copied out.  Any output may be NULL. */
+int sgmm_accumulate(sgmm_ctx* ctx, int first_pass, double* count, double* sum_x, double* sum_xx,
+                    double* score_sum);
+
+/* Trainer::calc_am_score's numerator alone (Training.cpp:585-612): sum over the resident alignment of
+ * min_score(x_f, state_f).first with the current model (all-reduced if a communicator is attached). */
+int sgmm_am_score_sum(sgmm_ctx* ctx, double* score_sum);
+
+/* Per-frame results of the last sgmm_accumulate / sgmm_am_score_sum (tests, diagnostics):
+ * density[f] = k chosen for frame f, score[f] = its min score.  Either may be NULL. */
+int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
+
+/* ---- multi-GPU ------------------------------------------------------------------------------ */
+/* One process per GPU.  Rank 0 calls sgmm_comm_unique_id (ncclGetUniqueId), ships the 128 bytes to
+ * the other ranks by any side channel (torch.distributed store, MPI, a file), then every rank calls
+ * sgmm_comm_init.  The reference has no counterpart (it is single-process). */
+int sgmm_comm_unique_id(void* id_out, size_t id_bytes);
+int sgmm_comm_init(sgmm_ctx* ctx, int rank, int world_size, const void* id, size_t id_bytes);
+
+/* ---- instrumentation ------------------------------------------------------------------------ */
+/* CUDA-event times (ms) of the stages of the most recent call, mirroring the Timer buckets of
+ * Trainer::train (Training.cpp:45-49,230-234).  Index with the SGMM_T_* constants. */
+enum {
+  SGMM_T_H2D = 0, SGMM_T_SCORE = 1, SGMM_T_VITERBI = 2, SGMM_T_RESCORE = 3, SGMM_T_SORT = 4,
+  SGMM_T_REDUCE = 5, SGMM_T_ALLREDUCE = 6, SGMM_T_D2H = 7, SGMM_T_COUNT = 8
+};
+int sgmm_stage_ms(sgmm_ctx* ctx, float* ms /* [SGMM_T_COUNT] */);
+/* Number of kernel launches issued by this context since creation. */
+uint64_t sgmm_launch_count(const sgmm_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SIETILL_B200_H */

@@ -1,0 +1,185 @@
+"""ctypes binding of the C-ABI in include/sietill_b200.h (libsietill_b200.so).
+
+This is plumbing for tests and bench.py; the product is the shared library.  There is no CPU fallback:
+if the library is missing, or no B200 is present, calls fail loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsietill_b200.so")
+
+T_NAMES = ["h2d", "score", "viterbi", "rescore", "sort", "reduce", "allreduce", "d2h"]
+TDP_SOURCE, TDP_DESTINATION = 0, 1
+
+ALI_DTYPE = np.dtype([("count", np.uint16), ("state", np.uint16), ("weight", np.float32)])  # Types.hpp:29-38
+
+# every symbol include/sietill_b200.h declares (checked by tests/test_capi_symbols.py)
+SYMBOLS = [
+    "sgmm_create", "sgmm_destroy", "sgmm_last_error", "sgmm_version", "sgmm_set_model", "sgmm_set_features",
+    "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
+    "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
+    "sgmm_launch_count",
+]
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(make -C speechrecognition_b200/csrc).  There is no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        L.sgmm_last_error.restype = C.c_char_p
+        L.sgmm_version.restype = C.c_char_p
+        L.sgmm_launch_count.restype = C.c_uint64
+        L.sgmm_last_error.argtypes = [C.c_void_p]
+        L.sgmm_destroy.argtypes = [C.c_void_p]
+        L.sgmm_launch_count.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _ptr(a, ctype):
+    return None if a is None else a.ctypes.data_as(C.POINTER(ctype))
+
+
+class SgmmError(RuntimeError):
+    pass
+
+
+class Context:
+    """One sgmm_ctx (one GPU).  All arrays are numpy host arrays, as the C-ABI takes host buffers."""
+
+    def __init__(self, device=0):
+        self.L = load()
+        h = C.c_void_p()
+        if self.L.sgmm_create(int(device), C.byref(h)):
+            raise SgmmError(self.L.sgmm_last_error(None).decode())
+        self.h = h
+        self.dim = self.n_states = self.D = 0
+        self.n_frames = self.n_utts = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sgmm_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc:
+            raise SgmmError(self.L.sgmm_last_error(self.h).decode())
+
+    # ---- setup
+    def set_model(self, dim, state_off, mean, inv_var, norm, log_weight):
+        state_off = np.ascontiguousarray(state_off, np.uint32)
+        mean = np.ascontiguousarray(mean, np.float64).reshape(-1)
+        inv_var = np.ascontiguousarray(inv_var, np.float64).reshape(-1)
+        norm = np.ascontiguousarray(norm, np.float64)
+        log_weight = np.ascontiguousarray(log_weight, np.float64)
+        n = len(state_off) - 1
+        D = int(state_off[-1])
+        assert mean.size == D * dim and inv_var.size == D * dim and norm.size == D and log_weight.size == D
+        self._ck(self.L.sgmm_set_model(self.h, C.c_uint32(dim), C.c_uint32(n), _ptr(state_off, C.c_uint32),
+                                       _ptr(mean, C.c_double), _ptr(inv_var, C.c_double), _ptr(norm, C.c_double),
+                                       _ptr(log_weight, C.c_double)))
+        self.dim, self.n_states, self.D = dim, n, D
+
+    def set_model_tables(self, dim, t):
+        """From a reference-layout table dict (see oracle.binding / host MixtureModel): resolves
+        mixtures_[s][k] -> (mean_idx, var_idx) into the state-major packed tables of sgmm_set_model."""
+        mi, vi = t["mean_idx"].astype(np.int64), t["var_idx"].astype(np.int64)
+        self.set_model(dim, t["mix_offsets"], t["means"].reshape(-1, dim)[mi], t["vars_inv"].reshape(-1, dim)[vi],
+                       t["norm"][vi], t["mean_wlog"][mi])
+
+    def set_features(self, x):
+        x = np.ascontiguousarray(x, np.float32)
+        assert x.ndim == 2
+        self._ck(self.L.sgmm_set_features(self.h, _ptr(x, C.c_float), C.c_uint64(x.shape[0]), C.c_uint32(x.shape[1])))
+        self.n_frames = x.shape[0]
+
+    def set_corpus(self, frame_off, automata, aut_off):
+        frame_off = np.ascontiguousarray(frame_off, np.uint64)
+        automata = np.ascontiguousarray(automata, np.uint32)
+        aut_off = np.ascontiguousarray(aut_off, np.uint32)
+        self._ck(self.L.sgmm_set_corpus(self.h, C.c_uint32(len(frame_off) - 1), _ptr(frame_off, C.c_uint64),
+                                        _ptr(automata, C.c_uint32), _ptr(aut_off, C.c_uint32)))
+        self.n_utts = len(frame_off) - 1
+
+    def set_tdp(self, loop, forward, skip, silence_state=0):
+        self._ck(self.L.sgmm_set_tdp(self.h, C.c_double(loop), C.c_double(forward), C.c_double(skip),
+                                     C.c_uint32(silence_state)))
+
+    # ---- compute
+    def score_all(self, f0=0, f1=None, want_argmin=True):
+        f1 = self.n_frames if f1 is None else f1
+        scores = np.empty((f1 - f0, self.n_states), np.float64)
+        argmin = np.empty((f1 - f0, self.n_states), np.uint32) if want_argmin else None
+        self._ck(self.L.sgmm_score_all(self.h, C.c_uint64(f0), C.c_uint64(f1), _ptr(scores, C.c_double),
+                                       _ptr(argmin, C.c_uint32)))
+        return scores, argmin
+
+    def align(self, convention=TDP_SOURCE, want_alignment=True, want_costs=True, out=None):
+        ali = out if out is not None else (np.empty(self.n_frames, ALI_DTYPE) if want_alignment else None)
+        costs = np.empty(self.n_utts, np.float64) if want_costs else None
+        self._ck(self.L.sgmm_align(self.h, int(convention), _ptr(ali, C.c_uint8) if ali is not None else None,
+                                   _ptr(costs, C.c_double)))
+        return ali, costs
+
+    def set_alignment(self, states):
+        if states.dtype != ALI_DTYPE:
+            a = np.zeros(len(states), ALI_DTYPE)
+            a["state"] = states
+            a["count"] = 1
+            a["weight"] = 1.0
+            states = a
+        states = np.ascontiguousarray(states)
+        self._ck(self.L.sgmm_set_alignment(self.h, _ptr(states, C.c_uint8), C.c_uint64(len(states))))
+
+    def accumulate(self, first_pass=False, want=True):
+        D, d = self.D, self.dim
+        cnt = np.empty(D, np.float64) if want else None
+        sx = np.empty((D, d), np.float64) if want else None
+        sxx = np.empty((D, d), np.float64) if want else None
+        ssum = np.zeros(1, np.float64)
+        self._ck(self.L.sgmm_accumulate(self.h, int(first_pass), _ptr(cnt, C.c_double), _ptr(sx, C.c_double),
+                                        _ptr(sxx, C.c_double), _ptr(ssum, C.c_double)))
+        return cnt, sx, sxx, float(ssum[0])
+
+    def am_score_sum(self):
+        ssum = np.zeros(1, np.float64)
+        self._ck(self.L.sgmm_am_score_sum(self.h, _ptr(ssum, C.c_double)))
+        return float(ssum[0])
+
+    def last_frame_results(self):
+        dens = np.empty(self.n_frames, np.uint32)
+        score = np.empty(self.n_frames, np.float64)
+        self._ck(self.L.sgmm_last_frame_results(self.h, _ptr(dens, C.c_uint32), _ptr(score, C.c_double)))
+        return dens, score
+
+    # ---- multi-GPU
+    @staticmethod
+    def comm_unique_id():
+        buf = np.zeros(128, np.uint8)
+        if load().sgmm_comm_unique_id(_ptr(buf, C.c_uint8), C.c_size_t(128)):
+            raise SgmmError(load().sgmm_last_error(None).decode())
+        return buf
+
+    def comm_init(self, rank, world, uid):
+        uid = np.ascontiguousarray(uid, np.uint8)
+        self._ck(self.L.sgmm_comm_init(self.h, int(rank), int(world), _ptr(uid, C.c_uint8), C.c_size_t(128)))
+
+    # ---- instrumentation
+    def stage_ms(self):
+        ms = np.zeros(len(T_NAMES), np.float32)
+        self._ck(self.L.sgmm_stage_ms(self.h, _ptr(ms, C.c_float)))
+        return dict(zip(T_NAMES, (float(v) for v in ms)))
+
+    def launch_count(self):
+        return int(self.L.sgmm_launch_count(self.h))

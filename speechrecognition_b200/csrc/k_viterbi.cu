@@ -1,0 +1,285 @@
+// K2: batched Viterbi alignment over linear 0-1-2 HMMs with time-distortion penalties and a device
+// backtrace — Aligner::align_sequence_full (reference src/sietill/Alignment.cpp:50-144), one warp per
+// utterance.
+//
+//  * The trellis column lives in registers: lane l owns the C contiguous positions [l*C, (l+1)*C); only
+//    three f64 values cross lanes per frame (warp shuffles).  Path costs are f64 and every add/compare is
+//    the reference's, in its order (current = local + best; loop, then forward, then skip with strict
+//    '<'), so costs and backpointers are bit-identical.  The reference's 0-1-2 band (:73-74,82,87) is an
+//    optimisation only: cells outside it are +inf or cannot reach (T-1,S-1), so the un-banded DP below
+//    visits a superset of cells with identical values on the band.
+//  * Emission scores (f64, one row of the utterance's distinct states per frame) are streamed from HBM
+//    by TMA bulk copies (cp.async.bulk -> shared, mbarrier completion) SGMM_STAGES tiles ahead of the DP.
+//  * Backpointers are 2-bit jumps packed 16 frames per 32-bit word per position; they stay in shared
+//    memory, so the backtrace never touches HBM.  The backtrace writes AlignmentItem{1, state, 1.0f}
+//    (Alignment.cpp:131-133).
+#include <math_constants.h>
+
+#include "sgmm_internal.cuh"
+
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// 1-D TMA bulk copy global -> shared (SASS: UBLKCP); completion is signalled on the mbarrier.
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+struct VitParams {
+  const uint32_t* utts;        // utterances of this launch class
+  uint32_t n_utts;
+  const uint64_t* frame_off;
+  const uint32_t* aut;
+  const uint32_t* aut_off;
+  const uint16_t* pos2uniq;    // per automaton position: column in the utterance's emission row
+  const uint32_t* nuniq_pad;
+  const uint64_t* E_off;
+  const double* E;
+  double tdp_loop, tdp_forward, tdp_skip;
+  uint32_t silence_state;
+  sgmm_alignment_item* ali;
+  double* costs;
+};
+
+template <int C>
+__device__ __forceinline__ double pick(const double (&v)[C], int c) {
+  double r = v[0];
+#pragma unroll
+  for (int i = 1; i < C; i++) r = (c == i) ? v[i] : r;
+  return r;
+}
+
+// DEST = false: align_sequence_full semantics (source-state TDP, tie order loop > forward > skip, end at S-1).
+// DEST = true : align_sequence_pruned with an infinite threshold (destination-state TDP, Alignment.cpp:191;
+//               candidates arrive skip, forward, loop and replace on strictly smaller cost, :199-204; the
+//               backtrace starts from the highest position alive in the last frame, :245-256).
+template <int C, bool DEST>
+__global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int lane = threadIdx.x;
+  if (blockIdx.x >= p.n_utts) return;
+  const uint32_t u = p.utts[blockIdx.x];
+  const uint64_t f0 = p.frame_off[u];
+  const uint32_t T = (uint32_t)(p.frame_off[u + 1] - f0);
+  const uint32_t a0 = p.aut_off[u];
+  const uint32_t S = p.aut_off[u + 1] - a0;
+  const uint32_t ncol = p.nuniq_pad[u];
+  const double* Eu = p.E + p.E_off[u];
+  const double INF = CUDART_INF;
+
+  // shared memory carve-up
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                          // SGMM_STAGES mbarriers
+  double* tiles = reinterpret_cast<double*>(smem + 64);                        // STAGES x TILE_T x ncol
+  const size_t tile_elems = (size_t)SGMM_TILE_T * ncol;
+  uint32_t* bpw = reinterpret_cast<uint32_t*>(tiles + SGMM_STAGES * tile_elems);  // ceil(T/16) x 32C words
+  uint16_t* sref = reinterpret_cast<uint16_t*>(bpw + (size_t)((T + 15) / 16) * 32 * C);  // automaton states
+
+  const uint32_t n_tiles = (T + SGMM_TILE_T - 1) / SGMM_TILE_T;
+  if (lane == 0) {
+    for (int i = 0; i < SGMM_STAGES; i++) mbar_init(&bars[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (uint32_t s = lane; s < S; s += 32) sref[s] = (uint16_t)p.aut[a0 + s];
+  __syncwarp();
+  if (lane == 0) {
+    for (uint32_t i = 0; i < SGMM_STAGES && i < n_tiles; i++) {
+      const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - i * SGMM_TILE_T);
+      const uint32_t bytes = rows * ncol * sizeof(double);
+      mbar_expect_tx(&bars[i], bytes);
+      tma_load_1d(tiles + i * tile_elems, Eu + (size_t)i * tile_elems, bytes, &bars[i]);
+    }
+  }
+
+  // per-position constants (registers)
+  double q[C];
+  uint32_t col[C], w[C];
+  uint32_t silmask = 0, validmask = 0;
+#pragma unroll
+  for (int c = 0; c < C; c++) {
+    const uint32_t s = lane * C + c;
+    q[c] = INF;
+    w[c] = 0;
+    col[c] = 0;
+    if (s < S) {
+      validmask |= 1u << c;
+      col[c] = p.pos2uniq[a0 + s];
+      if (sref[s] == p.silence_state) silmask |= 1u << c;
+    }
+  }
+
+  for (uint32_t ti = 0; ti < n_tiles; ti++) {
+    const uint32_t slot = ti % SGMM_STAGES;
+    mbar_wait(&bars[slot], (ti / SGMM_STAGES) & 1);
+    const double* tile = tiles + slot * tile_elems;
+    const uint32_t t0 = ti * SGMM_TILE_T;
+    const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - t0);
+    for (uint32_t tt = 0; tt < rows; tt++) {
+      const uint32_t t = t0 + tt;
+      const double* row = tile + tt * ncol;
+      double e[C];
+#pragma unroll
+      for (int c = 0; c < C; c++) e[c] = ((validmask >> c) & 1) ? row[col[c]] : INF;
+      if (t == 0) {
+        // Q(0,0) = emission(0, ref[0]); every other position starts at +inf (Alignment.cpp:62-63,77)
+#pragma unroll
+        for (int c = 0; c < C; c++) q[c] = (lane == 0 && c == 0) ? e[0] : INF;
+        continue;
+      }
+      double nq[C];
+      if (!DEST) {
+        double lv[C], fv[C], kv[C];
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+          const bool sil = (silmask >> c) & 1;   // TdpModel::score: silence always pays tdp_forward
+          lv[c] = __dadd_rn(q[c], sil ? p.tdp_forward : p.tdp_loop);
+          fv[c] = __dadd_rn(q[c], p.tdp_forward);
+          kv[c] = __dadd_rn(q[c], sil ? p.tdp_forward : p.tdp_skip);
+        }
+        double F = __shfl_up_sync(0xffffffffu, fv[C - 1], 1);
+        double K1 = __shfl_up_sync(0xffffffffu, kv[C - 2], 1);
+        double K2 = __shfl_up_sync(0xffffffffu, kv[C - 1], 1);
+        if (lane == 0) { F = INF; K1 = INF; K2 = INF; }
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+          double best = lv[c];
+          uint32_t j = 0;
+          const double fwd = c > 0 ? fv[c > 0 ? c - 1 : 0] : F;
+          if (fwd < best) { best = fwd; j = 1; }
+          const double skp = c > 1 ? kv[c > 1 ? c - 2 : 0] : (c == 1 ? K2 : K1);
+          if (skp < best) { best = skp; j = 2; }
+          nq[c] = __dadd_rn(e[c], best);
+          w[c] |= j << (2 * (t & 15));
+        }
+      } else {
+        double Q1 = __shfl_up_sync(0xffffffffu, q[C - 1], 1);   // position s-1 of c = 0
+        double Q2 = __shfl_up_sync(0xffffffffu, q[C - 2], 1);   // position s-2 of c = 0
+        if (lane == 0) { Q1 = INF; Q2 = INF; }
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+          const bool sil = (silmask >> c) & 1;
+          const double p1 = c > 0 ? q[c > 0 ? c - 1 : 0] : Q1;
+          const double p2 = c > 1 ? q[c > 1 ? c - 2 : 0] : (c == 1 ? Q1 : Q2);
+          // (prev + tdp) + emission, Alignment.cpp:190-197
+          const double ck = __dadd_rn(__dadd_rn(p2, sil ? p.tdp_forward : p.tdp_skip), e[c]);
+          const double cf = __dadd_rn(__dadd_rn(p1, p.tdp_forward), e[c]);
+          const double cl = __dadd_rn(__dadd_rn(q[c], sil ? p.tdp_forward : p.tdp_loop), e[c]);
+          // dead predecessors are +inf: they never win a strict comparison, exactly as hypotheses that
+          // were never created are never expanded in the reference
+          double best = ck;
+          uint32_t j = 2;
+          if (best > cf) { best = cf; j = 1; }
+          if (best > cl) { best = cl; j = 0; }
+          nq[c] = best;
+          w[c] |= j << (2 * (t & 15));
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < C; c++) q[c] = nq[c];
+      if ((t & 15) == 15 || t == T - 1) {
+#pragma unroll
+        for (int c = 0; c < C; c++) { bpw[(size_t)(t >> 4) * 32 * C + c * 32 + lane] = w[c]; w[c] = 0; }
+      }
+    }
+    __syncwarp();
+    const uint32_t nxt = ti + SGMM_STAGES;
+    if (lane == 0 && nxt < n_tiles) {
+      const uint32_t nrows = min((uint32_t)SGMM_TILE_T, T - nxt * SGMM_TILE_T);
+      const uint32_t bytes = nrows * ncol * sizeof(double);
+      mbar_expect_tx(&bars[slot], bytes);
+      tma_load_1d(tiles + slot * tile_elems, Eu + (size_t)nxt * tile_elems, bytes, &bars[slot]);
+    }
+  }
+  __syncwarp();
+
+  // end position and path cost
+  uint32_t end_s = S - 1;
+  if (DEST) {
+    uint32_t hi = 0;
+#pragma unroll
+    for (int c = 0; c < C; c++)
+      if (((validmask >> c) & 1) && q[c] < INF) hi = lane * C + c + 1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    end_s = hi ? hi - 1 : 0;
+  }
+  const double mine = pick<C>(q, (int)(end_s % C));
+  const double cost = __shfl_sync(0xffffffffu, mine, (int)(end_s / C));
+
+  if (lane == 0) {
+    if (p.costs) p.costs[u] = cost;
+    uint2* out = reinterpret_cast<uint2*>(p.ali + f0);
+    const uint32_t one = __float_as_uint(1.0f);
+    uint32_t s = end_s;
+    for (uint32_t t = T - 1; t >= 1; t--) {
+      out[t] = make_uint2(1u | ((uint32_t)sref[s] << 16), one);
+      const uint32_t word = bpw[(size_t)(t >> 4) * 32 * C + (s % C) * 32 + s / C];
+      const uint32_t j = (word >> (2 * (t & 15))) & 3u;
+      s = s >= j ? s - j : 0;
+    }
+    // frame 0: the full aligner writes reference[state reached] (= position 0 on any valid path); the
+    // pruned one writes reference[0] explicitly (Alignment.cpp:272-275)
+    out[0] = make_uint2(1u | ((uint32_t)sref[DEST ? 0 : s] << 16), one);
+  }
+}
+
+template <int C>
+int launch_c(sgmm_ctx* c, const VitParams& p, size_t smem, int conv) {
+  if (conv == SGMM_TDP_SOURCE) {
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_viterbi<C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_viterbi<C, false><<<p.n_utts, 32, smem, c->stream>>>(p);
+  } else {
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_viterbi<C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_viterbi<C, true><<<p.n_utts, 32, smem, c->stream>>>(p);
+  }
+  SGMM_LAUNCH_CHECK(c);
+  return 0;
+}
+
+}  // namespace
+
+int sgmm_launch_viterbi(sgmm_ctx* c, int conv) {
+  for (ViterbiClass& vc : c->vclasses) {
+    if (vc.utts.empty()) continue;
+    VitParams p{};
+    p.utts = vc.d_utts.p; p.n_utts = (uint32_t)vc.utts.size();
+    p.frame_off = c->d_frame_off.p; p.aut = c->d_aut.p; p.aut_off = c->d_aut_off.p;
+    p.pos2uniq = c->d_pos2uniq.p; p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p;
+    p.tdp_loop = c->tdp_loop; p.tdp_forward = c->tdp_forward; p.tdp_skip = c->tdp_skip;
+    p.silence_state = c->silence_state;
+    p.ali = c->d_ali.p; p.costs = c->d_costs.p;
+    int rc = 1;
+    switch (vc.C) {
+      case 2: rc = launch_c<2>(c, p, vc.smem, conv); break;
+      case 3: rc = launch_c<3>(c, p, vc.smem, conv); break;
+      case 4: rc = launch_c<4>(c, p, vc.smem, conv); break;
+      case 5: rc = launch_c<5>(c, p, vc.smem, conv); break;
+      case 6: rc = launch_c<6>(c, p, vc.smem, conv); break;
+      case 8: rc = launch_c<8>(c, p, vc.smem, conv); break;
+      case 10: rc = launch_c<10>(c, p, vc.smem, conv); break;
+      case 12: rc = launch_c<12>(c, p, vc.smem, conv); break;
+      case 16: rc = launch_c<16>(c, p, vc.smem, conv); break;
+      default: SGMM_FAIL(c, "viterbi: unsupported positions-per-lane class");
+    }
+    if (rc) return rc;
+  }
+  return 0;
+}

@@ -1,0 +1,304 @@
+// extern "C" entry points of libsietill_b200.so (declared in include/sietill_b200.h).
+// Host-side glue only: buffer management, table packing (K5), launch ordering, copies, NCCL.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+
+#include "sgmm_internal.cuh"
+
+namespace {
+std::string g_create_error;
+
+template <typename T>
+int upload(sgmm_ctx* c, DevBuf<T>& buf, const T* src, size_t n) {
+  SGMM_CHECK(c, buf.reserve(n ? n : 1));
+  if (n) SGMM_CHECK(c, cudaMemcpyAsync(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+
+void begin_call(sgmm_ctx* c) {
+  for (int i = 0; i < SGMM_T_COUNT; i++) c->stage_ms[i] = 0.f;
+}
+
+constexpr int kViterbiC[] = {2, 3, 4, 5, 6, 8, 10, 12, 16};
+
+size_t viterbi_smem(uint32_t T, uint32_t S, uint32_t ncol, int C) {
+  size_t b = 64;
+  b += (size_t)SGMM_STAGES * SGMM_TILE_T * ncol * sizeof(double);
+  b += (size_t)((T + 15) / 16) * 32 * C * sizeof(uint32_t);
+  b += (size_t)S * sizeof(uint16_t);
+  return (b + 15) & ~(size_t)15;
+}
+}  // namespace
+
+extern "C" {
+
+const char* sgmm_version(void) { return "sietill-b200 0.1 (sm_100a)"; }
+
+const char* sgmm_last_error(const sgmm_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int sgmm_create(int device, sgmm_ctx** out) {
+  if (!out) return 1;
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                     " (this library has no CPU fallback)";
+    return 1;
+  }
+  if (device < 0 || device >= n) { g_create_error = "device index out of range"; return 1; }
+  e = cudaSetDevice(device);
+  if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); return 1; }
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  if (prop.major != 10) {
+    g_create_error = "device is sm_" + std::to_string(prop.major * 10 + prop.minor) +
+                     "; this library is built for sm_100a (B200) only";
+    return 1;
+  }
+  sgmm_ctx* c = new sgmm_ctx();
+  c->device = device;
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    g_create_error = "cudaStreamCreate failed";
+    delete c;
+    return 1;
+  }
+  for (auto& ev : c->ev) cudaEventCreate(&ev);
+  *out = c;
+  return 0;
+}
+
+void sgmm_destroy(sgmm_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  c->d_meanT.release(); c->d_invT.release(); c->d_mean_tail.release(); c->d_inv_tail.release();
+  c->d_norm.release(); c->d_logw.release(); c->d_state_off.release(); c->d_x.release();
+  c->d_frame_off.release(); c->d_E_off.release(); c->d_aut.release(); c->d_aut_off.release();
+  c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
+  c->d_tasks.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
+  c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
+  for (int i = 0; i < 2; i++) { c->d_keys[i].release(); c->d_vals[i].release(); }
+  c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release();
+  c->d_partial.release(); c->d_acc.release(); c->d_score_part.release();
+  c->d_dense_scores.release(); c->d_dense_argmin.release();
+  for (auto& vc : c->vclasses) vc.d_utts.release();
+  for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+// K5: pack the f64 parameter tables dim-pair-major (see k_score.cu).
+int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t* state_off,
+                   const double* mean, const double* inv_var, const double* norm, const double* log_weight) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  if (dim < 2 || dim > 128) SGMM_FAIL(c, "set_model: dim must be in [2, 128]");
+  if (n_states == 0 || n_states > 65535) SGMM_FAIL(c, "set_model: n_states must be in [1, 65535] (StateIdx is 16 bit)");
+  const uint32_t D = state_off[n_states];
+  if (state_off[0] != 0 || D == 0) SGMM_FAIL(c, "set_model: bad state_off");
+  uint32_t max_d = 0;
+  for (uint32_t s = 0; s < n_states; s++) {
+    if (state_off[s + 1] < state_off[s]) SGMM_FAIL(c, "set_model: state_off not monotone");
+    max_d = std::max(max_d, state_off[s + 1] - state_off[s]);
+  }
+  const uint32_t npair = dim / 2;
+  std::vector<double2> mT((size_t)npair * D), vT((size_t)npair * D);
+  std::vector<double> mt(D, 0.0), vt(D, 0.0);
+  for (uint32_t j = 0; j < D; j++) {
+    const double* mu = mean + (size_t)j * dim;
+    const double* iv = inv_var + (size_t)j * dim;
+    for (uint32_t ip = 0; ip < npair; ip++) {
+      mT[(size_t)ip * D + j] = make_double2(mu[2 * ip], mu[2 * ip + 1]);
+      vT[(size_t)ip * D + j] = make_double2(iv[2 * ip], iv[2 * ip + 1]);
+    }
+    if (dim & 1) { mt[j] = mu[dim - 1]; vt[j] = iv[dim - 1]; }
+  }
+  if (upload(c, c->d_meanT, mT.data(), mT.size()) || upload(c, c->d_invT, vT.data(), vT.size()) ||
+      upload(c, c->d_mean_tail, mt.data(), mt.size()) || upload(c, c->d_inv_tail, vt.data(), vt.size()) ||
+      upload(c, c->d_norm, norm, (size_t)D) || upload(c, c->d_logw, log_weight, (size_t)D) ||
+      upload(c, c->d_state_off, state_off, (size_t)n_states + 1))
+    return 1;
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));  // the staging vectors die here
+  c->dim = dim; c->npair = npair; c->n_states = n_states; c->Dtot = D; c->max_dens = max_d;
+  c->h_state_off.assign(state_off, state_off + n_states + 1);
+  return 0;
+}
+
+int sgmm_set_features(sgmm_ctx* c, const float* x, uint64_t n_frames, uint32_t dim) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  begin_call(c);
+  SGMM_CHECK(c, c->d_x.reserve((size_t)n_frames * dim + 8));
+  {
+    StageTimer st(c, SGMM_T_H2D);
+    SGMM_CHECK(c, cudaMemcpyAsync(c->d_x.p, x, (size_t)n_frames * dim * sizeof(float), cudaMemcpyHostToDevice,
+                                  c->stream));
+  }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  c->n_frames = n_frames; c->feat_dim = dim;
+  c->have_alignment = false;
+  return 0;
+}
+
+int sgmm_set_tdp(sgmm_ctx* c, double loop, double forward, double skip, uint32_t silence_state) {
+  if (!c) return 1;
+  c->tdp_loop = loop; c->tdp_forward = forward; c->tdp_skip = skip; c->silence_state = silence_state;
+  return 0;
+}
+
+int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const uint32_t* automata,
+                    const uint32_t* aut_off) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  if (frame_off[0] != 0 || aut_off[0] != 0) SGMM_FAIL(c, "set_corpus: offsets must start at 0");
+  std::vector<uint32_t> uniq, uniq_off(U + 1, 0), ncol(U);
+  std::vector<uint16_t> p2u(aut_off[U]);
+  std::vector<uint64_t> E_off(U + 1, 0);
+  std::vector<uint4> tasks;
+  std::map<std::pair<int, size_t>, ViterbiClass> classes;
+  uint32_t max_state = 0;
+  for (uint32_t u = 0; u < U; u++) {
+    if (frame_off[u + 1] <= frame_off[u]) SGMM_FAIL(c, "set_corpus: empty utterance");
+    const uint64_t T64 = frame_off[u + 1] - frame_off[u];
+    if (T64 > 65535) SGMM_FAIL(c, "set_corpus: utterance longer than 65535 frames");
+    const uint32_t T = (uint32_t)T64;
+    const uint32_t S = aut_off[u + 1] - aut_off[u];
+    if (S == 0) SGMM_FAIL(c, "set_corpus: empty automaton");
+    if (S > 512) SGMM_FAIL(c, "set_corpus: automaton longer than 512 positions");
+    const uint32_t* a = automata + aut_off[u];
+    for (uint32_t s = 0; s < S; s++) max_state = std::max(max_state, a[s]);
+    std::vector<uint32_t> us(a, a + S);
+    std::sort(us.begin(), us.end());
+    us.erase(std::unique(us.begin(), us.end()), us.end());
+    for (uint32_t s = 0; s < S; s++)
+      p2u[aut_off[u] + s] = (uint16_t)(std::lower_bound(us.begin(), us.end(), a[s]) - us.begin());
+    uniq.insert(uniq.end(), us.begin(), us.end());
+    uniq_off[u + 1] = (uint32_t)uniq.size();
+    ncol[u] = ((uint32_t)us.size() + 1u) & ~1u;
+    E_off[u + 1] = E_off[u] + (uint64_t)T * ncol[u];
+    for (uint32_t t0 = 0; t0 < T; t0 += 32) tasks.push_back(make_uint4(u, t0, 0, 0));
+    int C = 0;
+    for (int cc : kViterbiC) if ((uint32_t)cc * 32 >= S) { C = cc; break; }
+    size_t sm = viterbi_smem(T, S, ncol[u], C);
+    if (sm > 227 * 1024) SGMM_FAIL(c, "set_corpus: utterance trellis exceeds shared memory (T*S too large)");
+    size_t bucket = 8 * 1024;  // classes by shared-memory bucket so short utterances keep high occupancy
+    while (bucket < sm) bucket += bucket < 64 * 1024 ? 8 * 1024 : 32 * 1024;
+    bucket = std::min(bucket, (size_t)227 * 1024);
+    ViterbiClass& vc = classes[{C, bucket}];
+    vc.C = C; vc.smem = bucket;
+    vc.utts.push_back(u);
+  }
+  for (auto& vc : c->vclasses) vc.d_utts.release();
+  c->vclasses.clear();
+  for (auto& kv : classes) {
+    // longest utterances first inside a class: the tail of the launch is then made of short ones
+    std::stable_sort(kv.second.utts.begin(), kv.second.utts.end(), [&](uint32_t a, uint32_t b) {
+      return frame_off[a + 1] - frame_off[a] > frame_off[b + 1] - frame_off[b];
+    });
+    c->vclasses.push_back(std::move(kv.second));
+  }
+  for (auto& vc : c->vclasses)
+    if (upload(c, vc.d_utts, vc.utts.data(), vc.utts.size())) return 1;
+  if (upload(c, c->d_frame_off, frame_off, (size_t)U + 1) || upload(c, c->d_aut, automata, (size_t)aut_off[U]) ||
+      upload(c, c->d_aut_off, aut_off, (size_t)U + 1) || upload(c, c->d_uniq, uniq.data(), uniq.size()) ||
+      upload(c, c->d_uniq_off, uniq_off.data(), uniq_off.size()) || upload(c, c->d_nuniq_pad, ncol.data(), ncol.size()) ||
+      upload(c, c->d_pos2uniq, p2u.data(), p2u.size()) || upload(c, c->d_E_off, E_off.data(), E_off.size()) ||
+      upload(c, c->d_tasks, tasks.data(), tasks.size()))
+    return 1;
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  c->max_aut_state = max_state;
+  c->n_utts = U; c->n_tasks = tasks.size(); c->E_elems = E_off[U];
+  c->h_frame_off.assign(frame_off, frame_off + U + 1);
+  c->h_aut_off.assign(aut_off, aut_off + U + 1);
+  return 0;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// NCCL, loaded lazily so that single-GPU users (and the CPU-only build check) never need libnccl.
+// ---------------------------------------------------------------------------------------------------
+namespace {
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, /*ncclUniqueId by value*/ struct Id128, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+struct Id128 { char internal[128]; };
+NcclApi g_nccl;
+
+bool load_nccl(std::string& err) {
+  if (g_nccl.lib) return true;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (g_nccl.lib) break;
+  }
+  if (!g_nccl.lib) { err = std::string("cannot load libnccl: ") + dlerror(); return false; }
+  g_nccl.GetUniqueId = (int (*)(void*))dlsym(g_nccl.lib, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(void**, int, Id128, int))dlsym(g_nccl.lib, "ncclCommInitRank");
+  g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(g_nccl.lib, "ncclAllReduce");
+  g_nccl.CommDestroy = (int (*)(void*))dlsym(g_nccl.lib, "ncclCommDestroy");
+  g_nccl.GetErrorString = (const char* (*)(int))dlsym(g_nccl.lib, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce) { err = "libnccl lacks required symbols"; return false; }
+  return true;
+}
+}  // namespace
+
+int sgmm_nccl_allreduce(sgmm_ctx* c, double* d_buf, size_t n) {
+  if (!c->nccl_comm || c->world <= 1) return 0;
+  StageTimer st(c, SGMM_T_ALLREDUCE);
+  const int ncclFloat64 = 8, ncclSum = 0;
+  int rc = g_nccl.AllReduce(d_buf, d_buf, n, ncclFloat64, ncclSum, c->nccl_comm, c->stream);
+  if (rc != 0) SGMM_FAIL(c, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
+  return 0;
+}
+
+extern "C" {
+
+int sgmm_comm_unique_id(void* id_out, size_t id_bytes) {
+  if (id_bytes < 128) return 1;
+  if (!load_nccl(g_create_error)) return 1;
+  return g_nccl.GetUniqueId(id_out) == 0 ? 0 : 1;
+}
+
+int sgmm_comm_init(sgmm_ctx* c, int rank, int world, const void* id, size_t id_bytes) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  if (world <= 1) { c->rank = 0; c->world = 1; return 0; }
+  if (id_bytes < 128) SGMM_FAIL(c, "comm_init: unique id must be 128 bytes");
+  if (!load_nccl(c->err)) return 1;
+  Id128 uid;
+  memcpy(uid.internal, id, 128);
+  int rc = g_nccl.CommInitRank(&c->nccl_comm, world, uid, rank);
+  if (rc != 0) SGMM_FAIL(c, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
+  c->rank = rank; c->world = world;
+  return 0;
+}
+
+int sgmm_stage_ms(sgmm_ctx* c, float* ms) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  for (int i = 0; i < SGMM_T_COUNT; i++) {
+    if (c->stage_ms[i] < 0.f) {
+      float v = 0.f;
+      cudaEventElapsedTime(&v, c->ev[2 * i], c->ev[2 * i + 1]);
+      c->stage_ms[i] = v;
+    }
+    ms[i] = c->stage_ms[i];
+  }
+  return 0;
+}
+
+uint64_t sgmm_launch_count(const sgmm_ctx* c) { return c ? c->launches : 0; }
+
+}  // extern "C"

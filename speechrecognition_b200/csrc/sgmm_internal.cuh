@@ -1,0 +1,126 @@
+// Internal declarations shared by the .cu files of libsietill_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "sietill_b200.h"
+
+#define SGMM_WARP 32
+#define SGMM_TILE_T 16      // Viterbi: time steps per emission tile
+#define SGMM_STAGES 3       // Viterbi: emission tiles in flight (cp.async.bulk ring)
+#define SGMM_SORT_CHUNK 2048  // radix sort: keys per warp-chunk
+#define SGMM_RED_BLOCK 256    // segmented reduce: frames per partial
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t cap = 0;  // elements
+  cudaError_t reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = n + n / 8 + 64;
+    cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct ViterbiClass {  // utterances that share one launch (same lanes-per-position shape + smem size)
+  int C = 0;                 // positions per lane
+  size_t smem = 0;           // dynamic shared memory per CTA
+  std::vector<uint32_t> utts;
+  DevBuf<uint32_t> d_utts;
+};
+
+struct sgmm_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  uint64_t launches = 0;
+  float stage_ms[SGMM_T_COUNT] = {0};
+  cudaEvent_t ev[2 * SGMM_T_COUNT] = {nullptr};
+
+  // ---- model (exact f64 tables, dim-pair-major: tabT[ip * Dtot + j] = {mean.x, mean.y} etc.)
+  uint32_t dim = 0, npair = 0, n_states = 0, Dtot = 0, max_dens = 0;
+  std::vector<uint32_t> h_state_off;
+  DevBuf<double2> d_meanT, d_invT;
+  DevBuf<double> d_mean_tail, d_inv_tail, d_norm, d_logw;
+  DevBuf<uint32_t> d_state_off;
+
+  // ---- features
+  uint64_t n_frames = 0;
+  uint32_t feat_dim = 0;
+  DevBuf<float> d_x;
+
+  // ---- corpus
+  uint32_t n_utts = 0, max_aut_state = 0;
+  std::vector<uint64_t> h_frame_off;
+  std::vector<uint32_t> h_aut_off;
+  DevBuf<uint64_t> d_frame_off, d_E_off;
+  DevBuf<uint32_t> d_aut, d_aut_off, d_uniq, d_uniq_off, d_nuniq_pad;
+  DevBuf<uint16_t> d_pos2uniq;
+  DevBuf<uint4> d_tasks;          // emission warp-tasks: {utt, t0, 0, 0}
+  uint64_t n_tasks = 0, E_elems = 0;
+  DevBuf<double> d_E;             // ragged emission matrix, utterance u: [T_u][nuniq_pad_u]
+  std::vector<ViterbiClass> vclasses;
+  DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)
+
+  // ---- tdp
+  double tdp_loop = 0, tdp_forward = 0, tdp_skip = 0;
+  uint32_t silence_state = 0;
+
+  // ---- alignment + per-frame E-step results
+  bool have_alignment = false;
+  DevBuf<sgmm_alignment_item> d_ali;
+  DevBuf<double> d_costs;
+  DevBuf<uint32_t> d_fdens;       // global density id per frame
+  DevBuf<double> d_fscore;
+
+  // ---- accumulation
+  DevBuf<uint32_t> d_keys[2], d_vals[2], d_hist, d_cnt_u32, d_seg_off, d_item_off;
+  DevBuf<double> d_partial, d_acc;   // d_acc = [count D | sum_x D*d | sum_xx D*d | score_sum 1]
+  DevBuf<double> d_score_part;
+  DevBuf<double> d_dense_scores;
+  DevBuf<uint32_t> d_dense_argmin;
+
+  // ---- NCCL (dlopen'ed lazily)
+  void* nccl_comm = nullptr;
+  int rank = 0, world = 1;
+};
+
+#define SGMM_CHECK(ctx, call)                                                             \
+  do {                                                                                    \
+    cudaError_t _e = (call);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(_e) + " (" + __FILE__ + \
+                   ":" + std::to_string(__LINE__) + ")";                                  \
+      return 1;                                                                           \
+    }                                                                                     \
+  } while (0)
+
+#define SGMM_FAIL(ctx, msg) do { (ctx)->err = (msg); return 1; } while (0)
+
+#define SGMM_LAUNCH_CHECK(ctx)                     \
+  do {                                             \
+    (ctx)->launches++;                             \
+    SGMM_CHECK(ctx, cudaGetLastError());           \
+  } while (0)
+
+struct StageTimer {  // CUDA-event bracket on the context's stream, accumulated into stage_ms at read time
+  sgmm_ctx* c; int idx;
+  StageTimer(sgmm_ctx* c, int idx) : c(c), idx(idx) { cudaEventRecord(c->ev[2 * idx], c->stream); }
+  ~StageTimer() { cudaEventRecord(c->ev[2 * idx + 1], c->stream); c->stage_ms[idx] = -1.f; }
+};
+
+// kernels / launchers (defined in k_*.cu)
+int sgmm_launch_emission(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
+                         uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin);
+int sgmm_launch_viterbi(sgmm_ctx* c, int tdp_convention);
+int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass);
+int sgmm_launch_accumulate(sgmm_ctx* c);
+int sgmm_launch_score_sum(sgmm_ctx* c);
+int sgmm_nccl_allreduce(sgmm_ctx* c, double* d_buf, size_t n);

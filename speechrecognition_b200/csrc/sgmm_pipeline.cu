@@ -1,0 +1,180 @@
+// The compute entry points: score_all (K1), align (K1 gathered + K2), accumulate (K3 + K4 [+ NCCL]).
+#include <algorithm>
+#include <cstring>
+
+#include "sgmm_internal.cuh"
+
+namespace {
+
+int require(sgmm_ctx* c, bool model, bool feats, bool corpus) {
+  if (model && c->Dtot == 0) SGMM_FAIL(c, "no model: call sgmm_set_model first");
+  if (feats && c->n_frames == 0) SGMM_FAIL(c, "no features: call sgmm_set_features first");
+  if (model && feats && c->feat_dim != c->dim) SGMM_FAIL(c, "feature dimension differs from the model's");
+  if (corpus) {
+    if (c->n_utts == 0) SGMM_FAIL(c, "no corpus: call sgmm_set_corpus first");
+    if (c->h_frame_off.back() != c->n_frames) SGMM_FAIL(c, "corpus frame offsets do not cover the resident features");
+    if (model && c->max_aut_state >= c->n_states) SGMM_FAIL(c, "automaton names a state the model does not have");
+  }
+  return 0;
+}
+
+inline size_t acc_len(const sgmm_ctx* c) { return (size_t)c->Dtot * (1 + 2 * (size_t)c->dim) + 1; }
+
+void reset_stage(sgmm_ctx* c) {
+  for (int i = 0; i < SGMM_T_COUNT; i++) c->stage_ms[i] = 0.f;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sgmm_score_all(sgmm_ctx* c, uint64_t f0, uint64_t f1, double* scores, uint32_t* argmin) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  reset_stage(c);
+  if (require(c, true, true, false)) return 1;
+  if (f1 > c->n_frames || f0 > f1) SGMM_FAIL(c, "score_all: frame range out of bounds");
+  const uint32_t N = c->n_states;
+  // chunked so that the device staging buffers stay bounded (<= ~256 MB of scores)
+  const uint64_t chunk = std::max<uint64_t>(32, ((256ull << 20) / (N * sizeof(double))) & ~31ull);
+  SGMM_CHECK(c, c->d_dense_scores.reserve((size_t)std::min<uint64_t>(chunk, f1 - f0 + 1) * N));
+  SGMM_CHECK(c, c->d_dense_argmin.reserve((size_t)std::min<uint64_t>(chunk, f1 - f0 + 1) * N));
+  for (uint64_t b = f0; b < f1; b += chunk) {
+    const uint64_t nf = std::min(chunk, f1 - b);
+    {
+      StageTimer st(c, SGMM_T_SCORE);
+      if (sgmm_launch_emission(c, nullptr, (nf + 31) / 32, true, b, nf, c->d_dense_scores.p,
+                               argmin ? c->d_dense_argmin.p : nullptr))
+        return 1;
+    }
+    StageTimer st(c, SGMM_T_D2H);
+    if (scores)
+      SGMM_CHECK(c, cudaMemcpyAsync(scores + (b - f0) * N, c->d_dense_scores.p, nf * N * sizeof(double),
+                                    cudaMemcpyDeviceToHost, c->stream));
+    if (argmin)
+      SGMM_CHECK(c, cudaMemcpyAsync(argmin + (b - f0) * N, c->d_dense_argmin.p, nf * N * sizeof(uint32_t),
+                                    cudaMemcpyDeviceToHost, c->stream));
+    SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  }
+  return 0;
+}
+
+int sgmm_align(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* costs) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  reset_stage(c);
+  if (require(c, true, true, true)) return 1;
+  if (conv != SGMM_TDP_SOURCE && conv != SGMM_TDP_DESTINATION) SGMM_FAIL(c, "align: bad tdp_convention");
+  SGMM_CHECK(c, c->d_E.reserve(c->E_elems + 2));
+  SGMM_CHECK(c, c->d_ali.reserve(c->n_frames));
+  SGMM_CHECK(c, c->d_costs.reserve(c->n_utts));
+  {
+    StageTimer st(c, SGMM_T_SCORE);
+    if (sgmm_launch_emission(c, c->d_tasks.p, c->n_tasks, false, 0, 0, nullptr, nullptr)) return 1;
+  }
+  {
+    StageTimer st(c, SGMM_T_VITERBI);
+    if (sgmm_launch_viterbi(c, conv)) return 1;
+  }
+  {
+    StageTimer st(c, SGMM_T_D2H);
+    if (alignment)
+      SGMM_CHECK(c, cudaMemcpyAsync(alignment, c->d_ali.p, c->n_frames * sizeof(sgmm_alignment_item),
+                                    cudaMemcpyDeviceToHost, c->stream));
+    if (costs)
+      SGMM_CHECK(c, cudaMemcpyAsync(costs, c->d_costs.p, c->n_utts * sizeof(double), cudaMemcpyDeviceToHost,
+                                    c->stream));
+  }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  c->have_alignment = true;
+  return 0;
+}
+
+int sgmm_set_alignment(sgmm_ctx* c, const sgmm_alignment_item* alignment, uint64_t n_frames) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  reset_stage(c);
+  if (n_frames != c->n_frames) SGMM_FAIL(c, "set_alignment: length differs from the resident features");
+  if (c->n_states)
+    for (uint64_t f = 0; f < n_frames; f++)
+      if (alignment[f].state >= c->n_states) SGMM_FAIL(c, "set_alignment: state index out of range");
+  SGMM_CHECK(c, c->d_ali.reserve(n_frames));
+  {
+    StageTimer st(c, SGMM_T_H2D);
+    SGMM_CHECK(c, cudaMemcpyAsync(c->d_ali.p, alignment, n_frames * sizeof(sgmm_alignment_item),
+                                  cudaMemcpyHostToDevice, c->stream));
+  }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  c->have_alignment = true;
+  return 0;
+}
+
+static int rescore_common(sgmm_ctx* c, bool first_pass) {
+  if (require(c, true, true, false)) return 1;
+  if (!c->have_alignment) SGMM_FAIL(c, "no alignment resident: call sgmm_align or sgmm_set_alignment first");
+  SGMM_CHECK(c, c->d_fdens.reserve(c->n_frames));
+  SGMM_CHECK(c, c->d_fscore.reserve(c->n_frames));
+  SGMM_CHECK(c, c->d_cnt_u32.reserve(c->Dtot + 1));
+  SGMM_CHECK(c, c->d_acc.reserve(acc_len(c)));
+  SGMM_CHECK(c, cudaMemsetAsync(c->d_cnt_u32.p, 0, (c->Dtot + 1) * sizeof(uint32_t), c->stream));
+  StageTimer st(c, SGMM_T_RESCORE);
+  if (sgmm_launch_rescore(c, first_pass)) return 1;
+  if (sgmm_launch_score_sum(c)) return 1;
+  return 0;
+}
+
+int sgmm_accumulate(sgmm_ctx* c, int first_pass, double* count, double* sum_x, double* sum_xx,
+                    double* score_sum) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  reset_stage(c);
+  if (rescore_common(c, first_pass != 0)) return 1;
+  if (sgmm_launch_accumulate(c)) return 1;
+  if (sgmm_nccl_allreduce(c, c->d_acc.p, acc_len(c))) return 1;
+  const size_t D = c->Dtot, d = c->dim;
+  {
+    StageTimer st(c, SGMM_T_D2H);
+    if (count) SGMM_CHECK(c, cudaMemcpyAsync(count, c->d_acc.p, D * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (sum_x) SGMM_CHECK(c, cudaMemcpyAsync(sum_x, c->d_acc.p + D, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (sum_xx) SGMM_CHECK(c, cudaMemcpyAsync(sum_xx, c->d_acc.p + D + D * d, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (score_sum) SGMM_CHECK(c, cudaMemcpyAsync(score_sum, c->d_acc.p + D + 2 * D * d, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int sgmm_am_score_sum(sgmm_ctx* c, double* score_sum) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  reset_stage(c);
+  if (rescore_common(c, false)) return 1;
+  double* slot = c->d_acc.p + (size_t)c->Dtot * (1 + 2 * (size_t)c->dim);
+  if (sgmm_nccl_allreduce(c, slot, 1)) return 1;
+  if (score_sum) SGMM_CHECK(c, cudaMemcpyAsync(score_sum, slot, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int sgmm_last_frame_results(sgmm_ctx* c, uint32_t* density, double* score) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  if (c->d_fdens.cap < c->n_frames || c->n_frames == 0) SGMM_FAIL(c, "no per-frame results yet");
+  if (score) SGMM_CHECK(c, cudaMemcpyAsync(score, c->d_fscore.p, c->n_frames * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  std::vector<uint32_t> glob;
+  if (density) {
+    glob.resize(c->n_frames);
+    SGMM_CHECK(c, cudaMemcpyAsync(glob.data(), c->d_fdens.p, c->n_frames * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  if (density) {
+    // global density id -> position k within its state (state_off is sorted)
+    for (uint64_t f = 0; f < c->n_frames; f++) {
+      const uint32_t g = glob[f];
+      const uint32_t s = (uint32_t)(std::upper_bound(c->h_state_off.begin(), c->h_state_off.end(), g) - c->h_state_off.begin()) - 1;
+      density[f] = g - c->h_state_off[s];
+    }
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,150 @@
+"""-m gpu: the CUDA path (through the C-ABI) against the oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): alignments, density argmins, counts bit-exact; scores, sum_x, sum_xx within
+1e-5 relative.  This implementation evaluates the reference's f64 operation order on the device, so the
+tests below demand MORE: scores and path costs bit-identical, statistics to 1e-12 relative.
+"""
+import numpy as np
+import pytest
+
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+
+STAT_RTOL = 1e-12   # north_star allows 1e-5
+
+
+@pytest.fixture(scope="module")
+def small25():
+    O, corp, ali = helpers.trained_oracle(dim=25, n_utts=24, splits=2)
+    ctx = helpers.gpu_context(O, corp, 25)
+    yield O, corp, ali, ctx
+    ctx.close()
+
+
+@pytest.fixture(scope="module")
+def small33():
+    O, corp, ali = helpers.trained_oracle(dim=33, n_utts=16, splits=3, seed=11, min_obs=10, dens_gen=4)
+    ctx = helpers.gpu_context(O, corp, 33)
+    yield O, corp, ali, ctx
+    ctx.close()
+
+
+@pytest.mark.parametrize("fx", ["small25", "small33"])
+def test_score_all_bit_exact(fx, request):
+    O, corp, ali, ctx = request.getfixturevalue(fx)
+    n = 700
+    want_s, want_a = O.min_score(corp["x"][:n])
+    got_s, got_a = ctx.score_all(0, n)
+    assert np.array_equal(got_a, want_a)
+    assert np.array_equal(got_s, want_s)          # bit-identical f64
+    # ragged range that is not a multiple of the 32-frame warp tile
+    got_s2, got_a2 = ctx.score_all(37, 37 + 45)
+    assert np.array_equal(got_s2, want_s[37:82]) and np.array_equal(got_a2, want_a[37:82])
+
+
+@pytest.mark.parametrize("fx", ["small25", "small33"])
+def test_align_full_bit_exact(fx, request):
+    O, corp, ali, ctx = request.getfixturevalue(fx)
+    want_states, want_costs = O.align_batch(corp["x"], corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
+    got, costs = ctx.align()
+    assert np.array_equal(got["state"].astype(np.uint32), want_states)
+    assert np.all(got["count"] == 1) and np.all(got["weight"] == 1.0)   # Alignment.cpp:131-133
+    assert np.array_equal(costs, want_costs)      # f64 path costs, bit-identical
+
+
+def test_align_destination_convention(small25):
+    O, corp, ali, ctx = small25
+    from speechrecognition_b200 import capi
+    got, costs = ctx.align(capi.TDP_DESTINATION)
+    for u in range(len(corp["frame_off"]) - 1):
+        f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
+        aut = corp["automata"][corp["aut_off"][u]:corp["aut_off"][u + 1]]
+        c, st, _ = O.align_pruned(corp["x"][f0:f1], aut, 1e300)
+        assert c == costs[u]
+        assert np.array_equal(got["state"][f0:f1].astype(np.uint32), st)
+    ctx.align()  # leave the source-convention alignment resident for the following tests
+
+
+@pytest.mark.parametrize("fx", ["small25", "small33"])
+def test_accumulate_matches_oracle(fx, request):
+    O, corp, ali, ctx = request.getfixturevalue(fx)
+    dim = O.dim
+    ctx.set_alignment(ali)
+    cnt, sx, sxx, ssum = ctx.accumulate(first_pass=False)
+    dens, fscore = ctx.last_frame_results()
+    # oracle: same E-step on a copy of the model
+    from oracle.binding import Oracle
+    P = Oracle(dim, O.n_mix, "none", True, O.tdp, O.silence)
+    P.load_tables(O.tables())
+    want_dens = P.accumulate(ali, corp["x"])
+    t = P.tables()
+    want_cnt, want_sx = helpers.packed_stats(t, dim)
+    assert np.array_equal(dens, want_dens)                       # density argmin per frame: bit-exact
+    assert np.array_equal(cnt, want_cnt)                         # counts: exact
+    np.testing.assert_allclose(sx, want_sx, rtol=STAT_RTOL, atol=1e-9)
+    vi = t["var_idx"].astype(np.int64)
+    want_sxx = t["var_acc"].reshape(-1, dim)[vi] - 1e-4          # reference seeds 1e-4 (Mixtures.cpp:243)
+    np.testing.assert_allclose(sxx, want_sxx, rtol=1e-9, atol=1e-7)
+    want_scores, _ = O.min_score(corp["x"][:300])
+    assert np.array_equal(fscore[:300], want_scores[np.arange(300), ali[:300]])
+    am = O.am_score(ali, corp["x"])
+    assert abs(ssum / len(ali) - am) <= 1e-12 * abs(am)
+    assert abs(ctx.am_score_sum() - ssum) == 0.0                 # deterministic reduction
+
+
+def test_accumulate_first_pass_and_determinism(small25):
+    O, corp, ali, ctx = small25
+    ctx.set_alignment(ali)
+    c1 = ctx.accumulate(first_pass=True)
+    c2 = ctx.accumulate(first_pass=True)
+    for a, b in zip(c1[:3], c2[:3]):
+        assert np.array_equal(a, b)                              # bit-reproducible
+    off = O.tables()["mix_offsets"]
+    first = off[:-1]
+    want = np.bincount(ali, minlength=O.n_mix).astype(np.float64)
+    assert np.array_equal(c1[0][first], want)                    # everything lands in density 0 of its state
+    assert c1[0].sum() == len(ali)
+    a3 = ctx.accumulate(first_pass=False)
+    a4 = ctx.accumulate(first_pass=False)
+    for a, b in zip(a3[:3], a4[:3]):
+        assert np.array_equal(a, b)
+
+
+def test_edge_shapes():
+    """Tiny and ragged utterances: S < 32 (two positions per lane), T not a multiple of the 16-frame tile,
+    T == S (only the diagonal path), long automaton (S > 256), single-frame tail tiles."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(3)
+    dim, n_states = 6, 40
+    t = synth.random_model(rng, dim, n_states, 3, "none")
+    O = Oracle(dim, n_states, "none", True, (2.0, 0.5, 7.0), 0)
+    O.load_tables(t)
+    shapes = [(5, 3), (17, 17), (33, 9), (16, 2), (100, 70), (640, 300), (31, 1), (2, 2), (48, 33)]
+    xs, auts, f_off, a_off = [], [], [0], [0]
+    for T, S in shapes:
+        aut = rng.integers(0, n_states, size=S).astype(np.uint32)
+        aut[rng.integers(0, S)] = 0   # make sure the silence state shows up
+        st = aut[synth.sample_path(rng, T, S)]
+        xs.append(synth.emit_frames(rng, t, dim, st)); auts.append(aut)
+        f_off.append(f_off[-1] + T); a_off.append(a_off[-1] + S)
+    x = np.concatenate(xs); automata = np.concatenate(auts)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, t); ctx.set_features(x); ctx.set_corpus(f_off, automata, a_off)
+    ctx.set_tdp(2.0, 0.5, 7.0, 0)
+    got, costs = ctx.align()
+    want_states, want_costs = O.align_batch(x, f_off, automata, a_off)
+    assert np.array_equal(costs, want_costs)
+    assert np.array_equal(got["state"].astype(np.uint32), want_states)
+    ctx.close()
+
+
+def test_errors_are_loud():
+    from speechrecognition_b200 import capi
+    ctx = capi.Context(0)
+    with pytest.raises(capi.SgmmError):
+        ctx.align()
+    with pytest.raises(capi.SgmmError):
+        capi.Context(99)
+    ctx.close()
