@@ -220,12 +220,12 @@ int sgmm_launch_accumulate(sgmm_ctx* c) {
   SGMM_CHECK(c, c->d_keys[0].reserve(n)); SGMM_CHECK(c, c->d_keys[1].reserve(n));
   SGMM_CHECK(c, c->d_vals[0].reserve(n)); SGMM_CHECK(c, c->d_vals[1].reserve(n));
   SGMM_CHECK(c, c->d_hist.reserve((size_t)256 * n_chunks + 1));
-  SGMM_CHECK(c, c->d_seg_off.reserve(D + 1)); SGMM_CHECK(c, c->d_item_off.reserve(D + 1));
+  SGMM_CHECK(c, c->d_seg_off.reserve(D + 2)); SGMM_CHECK(c, c->d_item_off.reserve(D + 1));
   const size_t max_items = n / SGMM_RED_BLOCK + D + 1;
   SGMM_CHECK(c, c->d_partial.reserve(max_items * 2 * dim));
 
   int bits = 1;
-  while ((1ull << bits) < D) bits++;
+  while ((1ull << bits) < (uint64_t)D + 1) bits++;   // keys are 0..D (D = dummy slot of empty mixtures)
   const int passes = (bits + 7) / 8;
   const uint32_t sort_grid = (n_chunks + kSortWarps - 1) / kSortWarps;
   const uint32_t* keys_in = c->d_fdens.p;
@@ -250,7 +250,7 @@ int sgmm_launch_accumulate(sgmm_ctx* c) {
   }
   {
     StageTimer st(c, SGMM_T_REDUCE);
-    k_excl_scan<<<1, 1024, 0, c->stream>>>(c->d_cnt_u32.p, c->d_seg_off.p, D, 0);
+    k_excl_scan<<<1, 1024, 0, c->stream>>>(c->d_cnt_u32.p, c->d_seg_off.p, D + 1, 0);
     SGMM_LAUNCH_CHECK(c);
     k_excl_scan<<<1, 1024, 0, c->stream>>>(c->d_cnt_u32.p, c->d_item_off.p, D, 1);
     SGMM_LAUNCH_CHECK(c);

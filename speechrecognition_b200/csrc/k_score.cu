@@ -215,9 +215,13 @@ __global__ void __launch_bounds__(kRescoreWarps * 32) k_rescore_f64(RescoreParam
     if (valid) min_over_state(p.m, k0, k1, xs + lane, 32, xt[lane], best, bk);
   }
   if (valid) {
-    p.fdens[f] = k0 + bk;
+    // A state whose mixture is empty (every density eliminated) contributes nothing: the reference's loop
+    // over mixtures_[m] (Mixtures.cpp:333) runs zero times.  Such frames go to the dummy slot Dtot.
+    const uint32_t gid = (k1 > k0) ? k0 + bk : p.m.Dtot;
+    if (k1 == k0 && !p.first_pass) best = 1e10;   // min_score of an empty mixture, Mixtures.cpp:699
+    p.fdens[f] = gid;
     p.fscore[f] = best;
-    atomicAdd(p.cnt + k0 + bk, 1u);
+    atomicAdd(p.cnt + gid, 1u);
   }
 }
 

@@ -114,7 +114,7 @@ static int rescore_common(sgmm_ctx* c, bool first_pass) {
   if (!c->have_alignment) SGMM_FAIL(c, "no alignment resident: call sgmm_align or sgmm_set_alignment first");
   SGMM_CHECK(c, c->d_fdens.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_fscore.reserve(c->n_frames));
-  SGMM_CHECK(c, c->d_cnt_u32.reserve(c->Dtot + 1));
+  SGMM_CHECK(c, c->d_cnt_u32.reserve(c->Dtot + 2));
   SGMM_CHECK(c, c->d_acc.reserve(acc_len(c)));
   SGMM_CHECK(c, cudaMemsetAsync(c->d_cnt_u32.p, 0, (c->Dtot + 1) * sizeof(uint32_t), c->stream));
   StageTimer st(c, SGMM_T_RESCORE);
@@ -170,6 +170,7 @@ int sgmm_last_frame_results(sgmm_ctx* c, uint32_t* density, double* score) {
     // global density id -> position k within its state (state_off is sorted)
     for (uint64_t f = 0; f < c->n_frames; f++) {
       const uint32_t g = glob[f];
+      if (g >= c->Dtot) { density[f] = 0; continue; }   // empty mixture: min_score returns index 0
       const uint32_t s = (uint32_t)(std::upper_bound(c->h_state_off.begin(), c->h_state_off.end(), g) - c->h_state_off.begin()) - 1;
       density[f] = g - c->h_state_off[s];
     }
