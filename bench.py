@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py — frames/sec scored + aligned (+ accumulated) on the BASELINE.json workload.
+
+A "step" is one pass of the hot path — GMM max-approx scoring, Viterbi alignment, EM accumulation
+(score + align + accumulate, BASELINE.json configs[1]/[2]) — over one synthetic sietill-shaped corpus
+shard: 106 states x 256 densities/state, 33-dim features, pooled (per-state) diagonal covariance.
+One process per GPU; every rank owns its own shard (weak scaling); the accumulators are all-reduced
+with one ncclAllReduce per step.  See the module docstring of the printed JSON keys in DESIGN.md §5.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from speechrecognition_b200 import synth  # noqa: E402
+
+FFMA_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # nominal FP32 FFMA peak of a B200 at max clock
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--utts", type=int, default=4096, help="utterances per GPU")
+    ap.add_argument("--dens", type=int, default=256, help="densities per state")
+    ap.add_argument("--dim", type=int, default=33)
+    ap.add_argument("--ref-utts", type=int, default=96, help="utterances of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def make_workload(args, rank):
+    lex = synth.Lexicon()
+    model_rng = np.random.default_rng(synth.SEED)
+    tables = synth.random_model(model_rng, args.dim, lex.num_states, args.dens, "mixture")
+    rng = np.random.default_rng(synth.SEED + 1 + rank)
+    corp = synth.make_corpus(rng, lex, tables, args.dim, args.utts)
+    return lex, tables, corp
+
+
+def densities_scored(tables, corp):
+    """sum over frames of the number of densities the alignment pass scores for that frame."""
+    per_state = np.diff(tables["mix_offsets"]).astype(np.int64)
+    total = 0
+    fo, ao, aut = corp["frame_off"], corp["aut_off"], corp["automata"]
+    for u in range(len(fo) - 1):
+        us = np.unique(aut[int(ao[u]):int(ao[u + 1])])
+        total += int(fo[u + 1] - fo[u]) * int(per_state[us].sum())
+    return total
+
+
+class ClockSampler(threading.Thread):
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        super().__init__(daemon=True)
+        self.gpu, self.rows, self.stop_flag = gpu, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                for line in out.strip().splitlines():
+                    self.rows.append([c.strip() for c in line.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 8:
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_rate(args, tables, corp, lex, n_utts, threads):
+    """frames/s of the reference's own CPU path (align_sequence_full per utterance + accumulate) on the
+    first n_utts utterances, `threads` utterance shards in parallel (the reference itself is single-threaded,
+    Training.cpp:168-183; independent shards are how it would use more cores)."""
+    from oracle import binding
+    n_utts = min(n_utts, len(corp["frame_off"]) - 1)
+    fo = corp["frame_off"][:n_utts + 1].astype(np.uint64)
+    ao = corp["aut_off"][:n_utts + 1].astype(np.uint32)
+    F = int(fo[-1])
+    x = corp["x"][:F]
+    tdp = (3.0, 0.0, 30.0)
+    kind = "reference" if binding.have_ref() else "port"
+    if kind == "reference":
+        import tempfile
+        from speechrecognition_b200 import mixio
+        with tempfile.NamedTemporaryFile(suffix=".mix", delete=False) as f:
+            path = f.name
+        mixio.write_mix(path, args.dim, tables)
+        M = binding.Reference(args.dim, lex.num_states, "mixture", True, tdp, lex.silence_state, mix_path=path)
+        os.unlink(path)
+    else:
+        M = binding.Oracle(args.dim, lex.num_states, "mixture", True, tdp, lex.silence_state)
+        M.load_tables(tables)
+    shards = np.array_split(np.arange(n_utts), threads)
+    states = np.zeros(F, np.uint32)
+
+    def work(idx):
+        if len(idx) == 0:
+            return
+        u0, u1 = int(idx[0]), int(idx[-1]) + 1
+        f0, f1 = int(fo[u0]), int(fo[u1])
+        a0, a1 = int(ao[u0]), int(ao[u1])
+        if kind == "reference":
+            st, _ = M.align_batch(x[f0:f1], fo[u0:u1 + 1] - fo[u0], corp["automata"][a0:a1], ao[u0:u1 + 1] - ao[u0])
+        else:
+            st, _ = M.align_batch(x[f0:f1], fo[u0:u1 + 1] - fo[u0], corp["automata"][a0:a1], ao[u0:u1 + 1] - ao[u0], 1)
+        states[f0:f1] = st
+
+    t0 = time.perf_counter()
+    ths = [threading.Thread(target=work, args=(s,)) for s in shards]
+    [t.start() for t in ths]
+    [t.join() for t in ths]
+    t_align = time.perf_counter() - t0
+    t1 = time.perf_counter()
+    M.accumulate(states, x)     # single-threaded, as in the reference
+    t_acc = time.perf_counter() - t1
+    return {"frames": F, "seconds": t_align + t_acc, "align_s": t_align, "accumulate_s": t_acc, "kind": kind,
+            "value": F / (t_align + t_acc)}
+
+
+def config_dict(args, frames_per_gpu, extra=None):
+    c = {"workload": "BASELINE configs[1] shape (106 states x %d densities, d=%d, per-state pooled diag cov) "
+                     "run as configs[2]'s full EM pass: score + Viterbi-align + accumulate" % (args.dens, args.dim),
+         "utterances_per_gpu": args.utts, "frames_per_gpu": int(frames_per_gpu), "tdp": [3.0, 0.0, 30.0],
+         "l2": "inputs exceed L2 (features + emission matrix > 126 MB per step)", "seed": synth.SEED}
+    c.update(extra or {})
+    return c
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    lex, tables, corp = make_workload(args, 0)
+    cores = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        cpu_reference_rate(args, tables, corp, lex, min(8, args.ref_utts), cores)
+    vals, secs, frames = [], 0.0, 0
+    for _ in range(args.steps):
+        r = cpu_reference_rate(args, tables, corp, lex, args.ref_utts, cores)
+        vals.append(r["value"]); secs += r["seconds"]; frames = r["frames"]
+    value = frames * args.steps / secs
+    line = {"impl": "reference", "metric": "frames/sec scored+aligned+accumulated (GMM+Viterbi+EM)", "value": value,
+            "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_dict(args, corp["frame_off"][-1]),
+            "cpu_baseline": {"value": value, "unit": "frames/s", "cores": cores, "kind": r["kind"],
+                             "sample": "first %d utterances (%d frames) of the rank-0 shard per step; alignment in %d "
+                                       "parallel utterance shards, accumulate single-threaded" % (args.ref_utts, frames, cores)},
+            "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from speechrecognition_b200 import capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    lex, tables, corp = make_workload(args, rank)
+    F, U = int(corp["frame_off"][-1]), args.utts
+    ctx = capi.Context(local)
+    if world > 1:
+        uid = torch.from_numpy(capi.Context.comm_unique_id() if rank == 0 else np.zeros(128, np.uint8)).cuda()
+        dist.broadcast(uid, 0)
+        ctx.comm_init(rank, world, uid.cpu().numpy())
+    ctx.set_model_tables(args.dim, tables)
+    ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"])
+    ctx.set_tdp(3.0, 0.0, 30.0, lex.silence_state)
+    x_pin = capi.pinned_empty(corp["x"].shape, np.float32)
+    x_pin[...] = corp["x"]
+    ali_pin = capi.pinned_empty((F,), capi.ALI_DTYPE)
+    ctx.set_features(x_pin)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        ctx.align(want_alignment=False, want_costs=False)
+        st = ctx.stage_ms()
+        ctx.accumulate(first_pass=False, want=False)
+        st2 = ctx.stage_ms()
+        for k in ("rescore", "sort", "reduce", "allreduce"):
+            st[k] = st2[k]
+        return st
+
+    def step_e2e():
+        ctx.set_features(x_pin)
+        ctx.align(out=ali_pin)
+        return ctx.accumulate(first_pass=False, want=True)
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    l0 = ctx.launch_count()
+    ctx.timer_start()
+    stages = []
+    for _ in range(args.steps):
+        stages.append(step_resident())
+    ms = ctx.timer_stop()
+    launches = ctx.launch_count() - l0
+    barrier()
+    ms = max_over_ranks(ms)
+    sampler.stop_flag = True
+    clocks = sampler.summary()
+
+    # end to end through the C-ABI with host buffers: H2D of the features, D2H of alignment + statistics
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        out = step_e2e()
+    ms_e2e = max_over_ranks(ctx.timer_stop())
+    barrier()
+    h2d = x_pin.nbytes
+    d2h = ali_pin.nbytes + U * 8 + sum(a.nbytes for a in out[:3]) + 8
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    frames_total = F * world
+    stage = {k: float(np.mean([s[k] for s in stages])) for k in stages[0]}
+    dens_scored = densities_scored(tables, corp)
+    K = 2 * args.dim + 1
+    score_s = stage["score"] / 1e3
+    achieved = 2.0 * K * dens_scored / score_s / 1e12
+    # Viterbi: algorithmic bytes = emission row read (f64) + AlignmentItem write per frame
+    ncols = []
+    for u in range(U):
+        n = len(np.unique(corp["automata"][int(corp["aut_off"][u]):int(corp["aut_off"][u + 1])]))
+        ncols.append(((n + 1) // 2 * 2) * int(corp["frame_off"][u + 1] - corp["frame_off"][u]))
+    vit_bytes = 8.0 * sum(ncols) + 8.0 * F
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    line = {
+        "metric": "frames/sec scored+aligned+accumulated (GMM+Viterbi+EM)", "value": frames_total * args.steps / (ms / 1e3),
+        "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": config_dict(args, F, {"parallelism": "dp%d (utterance shards)" % world}),
+        "clocks": clocks,
+        "e2e": {"value": frames_total * args.steps / (ms_e2e / 1e3), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
+        "stage_ms_per_step": stage,
+        "roofline": {"bound": "tensor", "kernel": "k_emission_f64 (exact-f64 GMM scoring, FP64 pipe)",
+                     "achieved": achieved, "peak": FFMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": achieved / FFMA_PEAK_TFLOPS,
+                     "traffic": None,
+                     "note": "algorithmic flops 2*(2d+1) per (frame, density scored); peak = nominal FP32 FFMA "
+                             "(148 SM x 128 lanes x 2 x 1.965 GHz); this kernel runs on the FP64 pipe"},
+        "roofline_viterbi": {"bound": "hbm", "kernel": "k_viterbi", "achieved": vit_bytes / (stage["viterbi"] / 1e3) / 1e9,
+                             "peak": hbm_peak, "unit": "GB/s",
+                             "frac": vit_bytes / (stage["viterbi"] / 1e3) / 1e9 / hbm_peak,
+                             "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        r = cpu_reference_rate(args, tables, corp, lex, args.ref_utts, cores)
+        line["cpu_baseline"] = {"value": r["value"], "unit": "frames/s", "cores": cores, "kind": r["kind"],
+                                "sample": "first %d utterances (%d frames) of the shard, one pass; alignment in %d parallel "
+                                          "utterance shards (%.1f s), accumulate single-threaded (%.1f s)"
+                                          % (args.ref_utts, r["frames"], cores, r["align_s"], r["accumulate_s"])}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -122,6 +122,13 @@ enum {
   SGMM_T_REDUCE = 5, SGMM_T_ALLREDUCE = 6, SGMM_T_D2H = 7, SGMM_T_COUNT = 8
 };
 int sgmm_stage_ms(sgmm_ctx* ctx, float* ms /* [SGMM_T_COUNT] */);
+/* Device-side stopwatch on the context's stream (CUDA events): start, then stop returns the elapsed ms
+ * of everything enqueued in between (copies included). */
+int sgmm_timer_start(sgmm_ctx* ctx);
+int sgmm_timer_stop(sgmm_ctx* ctx, float* ms);
+/* Pinned (page-locked) host memory for callers that want asynchronous-speed H2D/D2H copies. */
+void* sgmm_host_alloc(size_t bytes);
+void  sgmm_host_free(void* p);
 /* Number of kernel launches issued by this context since creation. */
 uint64_t sgmm_launch_count(const sgmm_ctx* ctx);
 

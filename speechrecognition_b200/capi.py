@@ -21,7 +21,7 @@ SYMBOLS = [
     "sgmm_create", "sgmm_destroy", "sgmm_last_error", "sgmm_version", "sgmm_set_model", "sgmm_set_features",
     "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
     "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
-    "sgmm_launch_count",
+    "sgmm_launch_count", "sgmm_timer_start", "sgmm_timer_stop", "sgmm_host_alloc", "sgmm_host_free",
 ]
 
 _lib = None
@@ -41,6 +41,9 @@ def load():
         L.sgmm_last_error.argtypes = [C.c_void_p]
         L.sgmm_destroy.argtypes = [C.c_void_p]
         L.sgmm_launch_count.argtypes = [C.c_void_p]
+        L.sgmm_host_alloc.restype = C.c_void_p
+        L.sgmm_host_alloc.argtypes = [C.c_size_t]
+        L.sgmm_host_free.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -181,5 +184,28 @@ class Context:
         self._ck(self.L.sgmm_stage_ms(self.h, _ptr(ms, C.c_float)))
         return dict(zip(T_NAMES, (float(v) for v in ms)))
 
+    def timer_start(self):
+        self._ck(self.L.sgmm_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        self._ck(self.L.sgmm_timer_stop(self.h, C.byref(ms)))
+        return float(ms.value)
+
     def launch_count(self):
         return int(self.L.sgmm_launch_count(self.h))
+
+
+_pinned_keepalive = []
+
+
+def pinned_empty(shape, dtype):
+    """numpy array over cudaHostAlloc'ed (page-locked) memory; lives until the process exits."""
+    dtype = np.dtype(dtype)
+    n = max(int(np.prod(shape)) * dtype.itemsize, 1)
+    p = load().sgmm_host_alloc(C.c_size_t(n))
+    if not p:
+        raise SgmmError("cudaHostAlloc failed")
+    buf = (C.c_uint8 * n).from_address(p)
+    _pinned_keepalive.append(buf)
+    return np.frombuffer(buf, dtype=np.uint8, count=int(np.prod(shape)) * dtype.itemsize).view(dtype).reshape(shape)

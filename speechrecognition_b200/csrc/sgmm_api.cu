@@ -68,6 +68,7 @@ int sgmm_create(int device, sgmm_ctx** out) {
     return 1;
   }
   for (auto& ev : c->ev) cudaEventCreate(&ev);
+  for (auto& ev : c->tev) cudaEventCreate(&ev);
   *out = c;
   return 0;
 }
@@ -88,6 +89,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_dense_scores.release(); c->d_dense_argmin.release();
   for (auto& vc : c->vclasses) vc.d_utts.release();
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  for (auto& ev : c->tev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -298,6 +300,30 @@ int sgmm_stage_ms(sgmm_ctx* c, float* ms) {
   }
   return 0;
 }
+
+int sgmm_timer_start(sgmm_ctx* c) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  SGMM_CHECK(c, cudaEventRecord(c->tev[0], c->stream));
+  return 0;
+}
+
+int sgmm_timer_stop(sgmm_ctx* c, float* ms) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  SGMM_CHECK(c, cudaEventRecord(c->tev[1], c->stream));
+  SGMM_CHECK(c, cudaEventSynchronize(c->tev[1]));
+  SGMM_CHECK(c, cudaEventElapsedTime(ms, c->tev[0], c->tev[1]));
+  return 0;
+}
+
+void* sgmm_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+  return p;
+}
+
+void sgmm_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 uint64_t sgmm_launch_count(const sgmm_ctx* c) { return c ? c->launches : 0; }
 

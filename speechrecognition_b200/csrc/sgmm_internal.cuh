@@ -43,6 +43,7 @@ struct sgmm_ctx {
   uint64_t launches = 0;
   float stage_ms[SGMM_T_COUNT] = {0};
   cudaEvent_t ev[2 * SGMM_T_COUNT] = {nullptr};
+  cudaEvent_t tev[2] = {nullptr, nullptr};
 
   // ---- model (exact f64 tables, dim-pair-major: tabT[ip * Dtot + j] = {mean.x, mean.y} etc.)
   uint32_t dim = 0, npair = 0, n_states = 0, Dtot = 0, max_dens = 0;

@@ -64,12 +64,25 @@ def random_model(rng, dim, n_states, dens_per_state, pooling="none"):
         var_idx = np.repeat(np.arange(n_states, dtype=np.uint32), dens_per_state)
     else:
         var_idx = np.zeros(D, np.uint32)
-    cnt = np.full(D, 100.0)
+    # sufficient statistics that finalize() (Mixtures.cpp:374-461) turns back into these parameters, so the
+    # model can also travel as a .mix file: counts follow the weights, sum_x = mean * count,
+    # sum_xx = (var + mean_ref^2) * count_v with mean_ref the own / mixture / global mean.
+    cnt = w * 100.0 * dens_per_state
+    macc = means * cnt[:, None]
+    if pooling == "none":
+        vcnt, mref = cnt.copy(), means
+    elif pooling == "mixture":
+        vcnt = cnt.reshape(n_states, dens_per_state).sum(1)
+        mref = macc.reshape(n_states, dens_per_state, dim).sum(1) / vcnt[:, None]
+    else:
+        vcnt = np.array([cnt.sum()])
+        mref = macc.sum(0, keepdims=True) / vcnt[:, None]
+    vacc = (var + mref * mref) * vcnt[:, None]
     return {
-        "means": means.reshape(-1).copy(), "mean_acc": (means * 100.0).reshape(-1).copy(), "mean_w": w,
+        "means": means.reshape(-1).copy(), "mean_acc": macc.reshape(-1).copy(), "mean_w": w,
         "mean_wlog": np.log(w), "mean_wacc": cnt, "mean_refs": np.ones(D, np.uint64),
         "vars": var.reshape(-1).copy(), "vars_inv": (1.0 / var).reshape(-1).copy(),
-        "var_acc": np.zeros(V * dim), "var_wacc": np.full(V, 100.0 * D / V), "var_refs": np.ones(V, np.uint64),
+        "var_acc": vacc.reshape(-1).copy(), "var_wacc": vcnt, "var_refs": np.ones(V, np.uint64),
         "norm": norm, "mix_offsets": (np.arange(n_states + 1) * dens_per_state).astype(np.uint32),
         "mean_idx": mean_idx, "var_idx": var_idx,
     }
