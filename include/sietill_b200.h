@@ -107,6 +107,14 @@ int sgmm_am_score_sum(sgmm_ctx* ctx, double* score_sum);
  * density[f] = k chosen for frame f, score[f] = its min score.  Either may be NULL. */
 int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
 
+/* ---- options / counters -------------------------------------------------------------------- */
+/* "scorer": 0 = automatic choice by model shape, 1 = exact-f64 kernel, 2 = FP32-FFMA kernel with certified
+ * f64 refinement.  Every scorer returns results bit-identical to the reference; the choice only moves time. */
+int sgmm_set_option(sgmm_ctx* ctx, const char* key, int64_t value);
+/* "fallbacks": (frame, state) cells whose f32 top-2 gap was inside the error bound and were re-scanned in
+ * f64 since the counter was last read; "scorer": the scorer the automatic choice resolves to. */
+int sgmm_get_counter(sgmm_ctx* ctx, const char* key, int64_t* value);
+
 /* ---- multi-GPU ------------------------------------------------------------------------------ */
 /* One process per GPU.  Rank 0 calls sgmm_comm_unique_id (ncclGetUniqueId), ships the 128 bytes to
  * the other ranks by any side channel (torch.distributed store, MPI, a file), then every rank calls

@@ -22,6 +22,7 @@ SYMBOLS = [
     "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
     "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
     "sgmm_launch_count", "sgmm_timer_start", "sgmm_timer_stop", "sgmm_host_alloc", "sgmm_host_free",
+    "sgmm_set_option", "sgmm_get_counter",
 ]
 
 _lib = None
@@ -191,6 +192,14 @@ class Context:
         ms = C.c_float(0)
         self._ck(self.L.sgmm_timer_stop(self.h, C.byref(ms)))
         return float(ms.value)
+
+    def set_option(self, key, value):
+        self._ck(self.L.sgmm_set_option(self.h, key.encode(), C.c_int64(int(value))))
+
+    def get_counter(self, key):
+        v = C.c_int64(0)
+        self._ck(self.L.sgmm_get_counter(self.h, key.encode(), C.byref(v)))
+        return int(v.value)
 
     def launch_count(self):
         return int(self.L.sgmm_launch_count(self.h))

@@ -81,7 +81,8 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_norm.release(); c->d_logw.release(); c->d_state_off.release(); c->d_x.release();
   c->d_frame_off.release(); c->d_E_off.release(); c->d_aut.release(); c->d_aut_off.release();
   c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
-  c->d_tasks.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
+  c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_h32.release(); c->d_c32.release();
+  c->d_sguard.release(); c->d_fallbacks.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
   for (int i = 0; i < 2; i++) { c->d_keys[i].release(); c->d_vals[i].release(); }
   c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release();
@@ -125,7 +126,42 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
       upload(c, c->d_norm, norm, (size_t)D) || upload(c, c->d_logw, log_weight, (size_t)D) ||
       upload(c, c->d_state_off, state_off, (size_t)n_states + 1))
     return 1;
+  // f32 tables for the FFMA scorer (k_score_ffma.cu): mean, h = inv_var / 2, c = norm - log w, and the
+  // per-state constants of the certified error bound.
+  const uint32_t dv4 = dim <= 28 ? 7 : dim <= 36 ? 9 : dim <= 48 ? 12 : dim <= 64 ? 16 : 0;
+  std::vector<float> mu32, h32, c32;
+  std::vector<float4> sg(n_states, make_float4(0.f, 0.f, 0.f, 0.f));
+  if (dv4) {
+    const size_t row = 4 * (size_t)dv4;
+    mu32.assign((size_t)D * row, 0.f); h32.assign((size_t)D * row, 0.f); c32.assign(D, 0.f);
+    for (uint32_t s = 0; s < n_states; s++) {
+      double cmin = INFINITY, cabs = 0.0, Mmax = 0.0;
+      for (uint32_t j = state_off[s]; j < state_off[s + 1]; j++) {
+        double M = 0.0;
+        for (uint32_t i = 0; i < dim; i++) {
+          const double mu = mean[(size_t)j * dim + i], h = 0.5 * inv_var[(size_t)j * dim + i];
+          mu32[j * row + i] = (float)mu; h32[j * row + i] = (float)h;
+          M += h * mu * mu;
+        }
+        const double cc = norm[j] - log_weight[j];
+        c32[j] = (float)cc;
+        cmin = std::min(cmin, cc); cabs = std::max(cabs, std::fabs(cc)); Mmax = std::max(Mmax, M);
+      }
+      // round the guard constants conservatively (cmin down, the others up)
+      sg[s] = make_float4(nextafterf((float)cmin, -INFINITY), nextafterf((float)cabs, INFINITY),
+                          nextafterf((float)Mmax, INFINITY), 0.f);
+    }
+    if (upload(c, c->d_mu32, reinterpret_cast<const float4*>(mu32.data()), (size_t)D * dv4) ||
+        upload(c, c->d_h32, reinterpret_cast<const float4*>(h32.data()), (size_t)D * dv4) ||
+        upload(c, c->d_c32, c32.data(), (size_t)D) || upload(c, c->d_sguard, sg.data(), sg.size()))
+      return 1;
+  }
+  if (!c->d_fallbacks.p) {
+    SGMM_CHECK(c, c->d_fallbacks.reserve(1));
+    SGMM_CHECK(c, cudaMemsetAsync(c->d_fallbacks.p, 0, sizeof(unsigned long long), c->stream));
+  }
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));  // the staging vectors die here
+  c->dv4 = dv4;
   c->dim = dim; c->npair = npair; c->n_states = n_states; c->Dtot = D; c->max_dens = max_d;
   c->h_state_off.assign(state_off, state_off + n_states + 1);
   return 0;
@@ -161,7 +197,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   std::vector<uint32_t> uniq, uniq_off(U + 1, 0), ncol(U);
   std::vector<uint16_t> p2u(aut_off[U]);
   std::vector<uint64_t> E_off(U + 1, 0);
-  std::vector<uint4> tasks;
+  std::vector<uint4> tasks, tasks64;
   std::map<std::pair<int, size_t>, ViterbiClass> classes;
   uint32_t max_state = 0;
   for (uint32_t u = 0; u < U; u++) {
@@ -184,6 +220,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     ncol[u] = ((uint32_t)us.size() + 1u) & ~1u;
     E_off[u + 1] = E_off[u] + (uint64_t)T * ncol[u];
     for (uint32_t t0 = 0; t0 < T; t0 += 32) tasks.push_back(make_uint4(u, t0, 0, 0));
+    for (uint32_t t0 = 0; t0 < T; t0 += 64) tasks64.push_back(make_uint4(u, t0, 0, 0));
     int C = 0;
     for (int cc : kViterbiC) if ((uint32_t)cc * 32 >= S) { C = cc; break; }
     size_t sm = viterbi_smem(T, S, ncol[u], C);
@@ -210,11 +247,11 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       upload(c, c->d_aut_off, aut_off, (size_t)U + 1) || upload(c, c->d_uniq, uniq.data(), uniq.size()) ||
       upload(c, c->d_uniq_off, uniq_off.data(), uniq_off.size()) || upload(c, c->d_nuniq_pad, ncol.data(), ncol.size()) ||
       upload(c, c->d_pos2uniq, p2u.data(), p2u.size()) || upload(c, c->d_E_off, E_off.data(), E_off.size()) ||
-      upload(c, c->d_tasks, tasks.data(), tasks.size()))
+      upload(c, c->d_tasks, tasks.data(), tasks.size()) || upload(c, c->d_tasks64, tasks64.data(), tasks64.size()))
     return 1;
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->max_aut_state = max_state;
-  c->n_utts = U; c->n_tasks = tasks.size(); c->E_elems = E_off[U];
+  c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->E_elems = E_off[U];
   c->h_frame_off.assign(frame_off, frame_off + U + 1);
   c->h_aut_off.assign(aut_off, aut_off + U + 1);
   return 0;
@@ -299,6 +336,33 @@ int sgmm_stage_ms(sgmm_ctx* c, float* ms) {
     ms[i] = c->stage_ms[i];
   }
   return 0;
+}
+
+int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
+  if (!c || !key) return 1;
+  if (!strcmp(key, "scorer")) {
+    if (value < 0 || value > 2) SGMM_FAIL(c, "set_option: scorer must be 0 (auto), 1 (f64) or 2 (ffma)");
+    c->scorer = (int)value;
+    return 0;
+  }
+  SGMM_FAIL(c, std::string("set_option: unknown key ") + key);
+}
+
+int sgmm_get_counter(sgmm_ctx* c, const char* key, int64_t* value) {
+  if (!c || !key || !value) return 1;
+  cudaSetDevice(c->device);
+  if (!strcmp(key, "fallbacks")) {
+    unsigned long long v = 0;
+    if (c->d_fallbacks.p) {
+      SGMM_CHECK(c, cudaMemcpyAsync(&v, c->d_fallbacks.p, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+      SGMM_CHECK(c, cudaMemsetAsync(c->d_fallbacks.p, 0, sizeof(v), c->stream));
+      SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+    }
+    *value = (int64_t)v;
+    return 0;
+  }
+  if (!strcmp(key, "scorer")) { *value = sgmm_effective_scorer(c); return 0; }
+  SGMM_FAIL(c, std::string("get_counter: unknown key ") + key);
 }
 
 int sgmm_timer_start(sgmm_ctx* c) {

@@ -51,6 +51,12 @@ struct sgmm_ctx {
   DevBuf<double2> d_meanT, d_invT;
   DevBuf<double> d_mean_tail, d_inv_tail, d_norm, d_logw;
   DevBuf<uint32_t> d_state_off;
+  // f32 tables of the FFMA / tensor scorers: [D][4*dv4] mean and h = 1/(2 var), c = norm - log w, per-state guard constants
+  uint32_t dv4 = 0;
+  int scorer = 0;   // 0 auto, 1 exact f64, 2 f32 FFMA + certified refinement
+  DevBuf<float4> d_mu32, d_h32, d_sguard;
+  DevBuf<float> d_c32;
+  DevBuf<unsigned long long> d_fallbacks;
 
   // ---- features
   uint64_t n_frames = 0;
@@ -64,8 +70,8 @@ struct sgmm_ctx {
   DevBuf<uint64_t> d_frame_off, d_E_off;
   DevBuf<uint32_t> d_aut, d_aut_off, d_uniq, d_uniq_off, d_nuniq_pad;
   DevBuf<uint16_t> d_pos2uniq;
-  DevBuf<uint4> d_tasks;          // emission warp-tasks: {utt, t0, 0, 0}
-  uint64_t n_tasks = 0, E_elems = 0;
+  DevBuf<uint4> d_tasks, d_tasks64;   // emission warp-tasks {utt, t0, 0, 0}: 32-frame and 64-frame granules
+  uint64_t n_tasks = 0, n_tasks64 = 0, E_elems = 0;
   DevBuf<double> d_E;             // ragged emission matrix, utterance u: [T_u][nuniq_pad_u]
   std::vector<ViterbiClass> vclasses;
   DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)
@@ -120,6 +126,9 @@ struct StageTimer {  // CUDA-event bracket on the context's stream, accumulated 
 // kernels / launchers (defined in k_*.cu)
 int sgmm_launch_emission(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
                          uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin);
+int sgmm_launch_emission_ffma(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
+                              uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin);
+int sgmm_effective_scorer(const sgmm_ctx* c);
 int sgmm_launch_viterbi(sgmm_ctx* c, int tdp_convention);
 int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass);
 int sgmm_launch_accumulate(sgmm_ctx* c);

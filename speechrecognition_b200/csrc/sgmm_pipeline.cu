@@ -24,7 +24,26 @@ void reset_stage(sgmm_ctx* c) {
   for (int i = 0; i < SGMM_T_COUNT; i++) c->stage_ms[i] = 0.f;
 }
 
+// emission scoring through whichever scorer is selected
+int launch_emission_any(sgmm_ctx* c, bool dense, uint64_t f0, uint64_t nf, double* scores, uint32_t* argmin) {
+  if (sgmm_effective_scorer(c) == 2) {
+    if (dense) return sgmm_launch_emission_ffma(c, nullptr, (nf + 63) / 64, true, f0, nf, scores, argmin);
+    return sgmm_launch_emission_ffma(c, c->d_tasks64.p, c->n_tasks64, false, 0, 0, nullptr, nullptr);
+  }
+  if (dense) return sgmm_launch_emission(c, nullptr, (nf + 31) / 32, true, f0, nf, scores, argmin);
+  return sgmm_launch_emission(c, c->d_tasks.p, c->n_tasks, false, 0, 0, nullptr, nullptr);
+}
+
 }  // namespace
+
+// 1 = exact f64, 2 = FFMA + refinement.  Automatic: the f32 filter pays off once a state has enough
+// densities to amortise the mandatory f64 evaluation of the winner.
+int sgmm_effective_scorer(const sgmm_ctx* c) {
+  if (c->scorer == 1 || c->dv4 == 0) return 1;
+  if (c->scorer == 2) return 2;
+  const double avg = c->n_states ? (double)c->Dtot / c->n_states : 0.0;
+  return avg >= 6.0 ? 2 : 1;
+}
 
 extern "C" {
 
@@ -36,15 +55,14 @@ int sgmm_score_all(sgmm_ctx* c, uint64_t f0, uint64_t f1, double* scores, uint32
   if (f1 > c->n_frames || f0 > f1) SGMM_FAIL(c, "score_all: frame range out of bounds");
   const uint32_t N = c->n_states;
   // chunked so that the device staging buffers stay bounded (<= ~256 MB of scores)
-  const uint64_t chunk = std::max<uint64_t>(32, ((256ull << 20) / (N * sizeof(double))) & ~31ull);
+  const uint64_t chunk = std::max<uint64_t>(64, ((256ull << 20) / (N * sizeof(double))) & ~63ull);
   SGMM_CHECK(c, c->d_dense_scores.reserve((size_t)std::min<uint64_t>(chunk, f1 - f0 + 1) * N));
   SGMM_CHECK(c, c->d_dense_argmin.reserve((size_t)std::min<uint64_t>(chunk, f1 - f0 + 1) * N));
   for (uint64_t b = f0; b < f1; b += chunk) {
     const uint64_t nf = std::min(chunk, f1 - b);
     {
       StageTimer st(c, SGMM_T_SCORE);
-      if (sgmm_launch_emission(c, nullptr, (nf + 31) / 32, true, b, nf, c->d_dense_scores.p,
-                               argmin ? c->d_dense_argmin.p : nullptr))
+      if (launch_emission_any(c, true, b, nf, c->d_dense_scores.p, argmin ? c->d_dense_argmin.p : nullptr))
         return 1;
     }
     StageTimer st(c, SGMM_T_D2H);
@@ -70,7 +88,7 @@ int sgmm_align(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* co
   SGMM_CHECK(c, c->d_costs.reserve(c->n_utts));
   {
     StageTimer st(c, SGMM_T_SCORE);
-    if (sgmm_launch_emission(c, c->d_tasks.p, c->n_tasks, false, 0, 0, nullptr, nullptr)) return 1;
+    if (launch_emission_any(c, false, 0, 0, nullptr, nullptr)) return 1;
   }
   {
     StageTimer st(c, SGMM_T_VITERBI);

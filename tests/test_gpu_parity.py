@@ -30,9 +30,14 @@ def small33():
     ctx.close()
 
 
+SCORERS = {"f64": 1, "ffma": 2}
+
+
+@pytest.mark.parametrize("scorer", ["f64", "ffma"])
 @pytest.mark.parametrize("fx", ["small25", "small33"])
-def test_score_all_bit_exact(fx, request):
+def test_score_all_bit_exact(fx, scorer, request):
     O, corp, ali, ctx = request.getfixturevalue(fx)
+    ctx.set_option("scorer", SCORERS[scorer])
     n = 700
     want_s, want_a = O.min_score(corp["x"][:n])
     got_s, got_a = ctx.score_all(0, n)
@@ -43,9 +48,11 @@ def test_score_all_bit_exact(fx, request):
     assert np.array_equal(got_s2, want_s[37:82]) and np.array_equal(got_a2, want_a[37:82])
 
 
+@pytest.mark.parametrize("scorer", ["f64", "ffma"])
 @pytest.mark.parametrize("fx", ["small25", "small33"])
-def test_align_full_bit_exact(fx, request):
+def test_align_full_bit_exact(fx, scorer, request):
     O, corp, ali, ctx = request.getfixturevalue(fx)
+    ctx.set_option("scorer", SCORERS[scorer])
     want_states, want_costs = O.align_batch(corp["x"], corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
     got, costs = ctx.align()
     assert np.array_equal(got["state"].astype(np.uint32), want_states)
@@ -149,4 +156,42 @@ def test_errors_are_loud():
         ctx.align()
     with pytest.raises(capi.SgmmError):
         capi.Context(99)
+    ctx.close()
+
+
+def test_ffma_scorer_ties_and_near_ties():
+    """The f32 filter must never decide a near-tie: duplicated densities (exact f64 ties -> the reference keeps
+    the FIRST, Mixtures.cpp:705), densities 1e-9 apart, and far-apart ones, all in one model."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(17)
+    dim, n_states, nd = 33, 12, 16
+    t = synth.random_model(rng, dim, n_states, nd, "none")
+    means = t["means"].reshape(-1, dim); vinv = t["vars_inv"].reshape(-1, dim)
+    vars_ = t["vars"].reshape(-1, dim)
+    for s in range(n_states):
+        b = s * nd
+        means[b + 5] = means[b + 2]; vinv[b + 5] = vinv[b + 2]; vars_[b + 5] = vars_[b + 2]      # exact duplicate
+        t["norm"][b + 5] = t["norm"][b + 2]; t["mean_wlog"][b + 5] = t["mean_wlog"][b + 2]
+        means[b + 9] = means[b + 3] * (1 + 1e-9); vinv[b + 9] = vinv[b + 3]; vars_[b + 9] = vars_[b + 3]
+        t["norm"][b + 9] = t["norm"][b + 3]; t["mean_wlog"][b + 9] = t["mean_wlog"][b + 3]
+    O = Oracle(dim, n_states, "none", True, (3.0, 0.0, 30.0), 0)
+    O.load_tables(t)
+    # frames drawn AT the duplicated / near-duplicated densities so that they are the winners
+    st = np.repeat(np.arange(n_states), 40)
+    x = synth.emit_frames(rng, t, dim, st)
+    x[::4] = means[st[::4] * nd + 2] + 0.01 * rng.standard_normal((len(st[::4]), dim))
+    x[1::4] = means[st[1::4] * nd + 3] + 0.01 * rng.standard_normal((len(st[1::4]), dim))
+    x = x.astype(np.float32)
+    want_s, want_a = O.min_score(x)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, t); ctx.set_features(x)
+    ctx.set_option("scorer", 2)
+    assert ctx.get_counter("scorer") == 2
+    ctx.get_counter("fallbacks")
+    got_s, got_a = ctx.score_all()
+    assert np.array_equal(got_a, want_a) and np.array_equal(got_s, want_s)
+    fb = ctx.get_counter("fallbacks")
+    assert fb >= len(st) // 2                      # the planted ties did take the f64 rescan path
+    assert fb < 0.2 * got_s.size                   # ... and only they did
     ctx.close()
