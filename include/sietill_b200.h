@@ -109,7 +109,8 @@ int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
 
 /* ---- options / counters -------------------------------------------------------------------- */
 /* "scorer": 0 = automatic choice by model shape, 1 = exact-f64 kernel, 2 = FP32-FFMA kernel with certified
- * f64 refinement.  Every scorer returns results bit-identical to the reference; the choice only moves time. */
+ * f64 refinement, 3 = tcgen05 3xTF32 tensor-core GEMM with certified f64 refinement.  Every scorer returns
+ * results bit-identical to the reference; the choice only moves time. */
 int sgmm_set_option(sgmm_ctx* ctx, const char* key, int64_t value);
 /* "fallbacks": (frame, state) cells whose f32 top-2 gap was inside the error bound and were re-scanned in
  * f64 since the counter was last read; "scorer": the scorer the automatic choice resolves to. */

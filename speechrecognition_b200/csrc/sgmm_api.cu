@@ -82,7 +82,9 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_frame_off.release(); c->d_E_off.release(); c->d_aut.release(); c->d_aut_off.release();
   c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
   c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_h32.release(); c->d_c32.release();
-  c->d_sguard.release(); c->d_fallbacks.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
+  c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release();
+  c->d_Bhi.release(); c->d_Blo.release(); c->d_Ahi.release(); c->d_Alo.release(); c->d_cb1.release(); c->d_cb2.release();
+  c->d_xnorm.release(); c->d_sguard_tc.release(); c->d_col_off.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
   for (int i = 0; i < 2; i++) { c->d_keys[i].release(); c->d_vals[i].release(); }
   c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release();
@@ -156,6 +158,70 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
         upload(c, c->d_c32, c32.data(), (size_t)D) || upload(c, c->d_sguard, sg.data(), sg.size()))
       return 1;
   }
+  // Tensor-core scorer operands (k_score_tc.cu).  Columns = densities, state-major, every state padded to a
+  // multiple of 16 columns with never-winning dummies.  B row of density j:
+  //   full  : [ h_0..h_{d-1} | g_0..g_{d-1} | c | 0.. ]   h = inv_var/2, g = -inv_var*mu, c = norm - logw + sum h mu^2
+  //   pooled: [ g_0..g_{d-1} | c | 0.. ]  when all densities of every state share one variance vector (the
+  //           x^2 block is then the same for all candidates of a state and drops out of the argmin).
+  {
+    bool pooled = true;
+    for (uint32_t s = 0; s < n_states && pooled; s++)
+      for (uint32_t j = state_off[s] + 1; j < state_off[s + 1] && pooled; j++)
+        pooled = memcmp(inv_var + (size_t)j * dim, inv_var + (size_t)state_off[s] * dim, dim * sizeof(double)) == 0;
+    const uint32_t Kused = pooled ? dim + 1 : 2 * dim + 1;
+    const uint32_t KP = (Kused + 31) / 32 * 32;
+    c->tc_ok = KP <= 64;
+    if (c->tc_ok) {
+      const uint32_t nsq = pooled ? 0 : dim;
+      std::vector<uint32_t> col_off(n_states + 1, 0);
+      for (uint32_t s = 0; s < n_states; s++)
+        col_off[s + 1] = col_off[s] + (state_off[s + 1] - state_off[s] + 15) / 16 * 16;
+      const uint32_t Dpad = col_off[n_states];
+      std::vector<float> Bhi((size_t)Dpad * KP, 0.f), Blo((size_t)Dpad * KP, 0.f);
+      std::vector<float4> sgt(n_states, make_float4(0.f, 0.f, 0.f, 0.f));
+      auto tf32 = [](float v) {   // round to nearest, ties away (cvt.rna.tf32.f32)
+        uint32_t u; memcpy(&u, &v, 4);
+        if ((u & 0x7f800000u) == 0x7f800000u) return v;
+        u += 0x1000u; u &= 0xffffe000u;
+        float r; memcpy(&r, &u, 4); return r;
+      };
+      auto put = [&](size_t row, uint32_t k, double v) {
+        const float hi = tf32((float)v);
+        Bhi[row * KP + k] = hi;
+        Blo[row * KP + k] = tf32((float)(v - (double)hi));
+      };
+      for (uint32_t s = 0; s < n_states; s++) {
+        double Gmax = 0.0, Hmax = 0.0, cabs = 0.0;
+        const uint32_t nreal = state_off[s + 1] - state_off[s];
+        for (uint32_t q = 0; q < col_off[s + 1] - col_off[s]; q++) {
+          const size_t row = col_off[s] + q;
+          if (q >= nreal) { put(row, nsq + dim, 1e30); continue; }
+          const uint32_t j = state_off[s] + q;
+          double cc = norm[j] - log_weight[j], G = 0.0, H = 0.0;
+          for (uint32_t i = 0; i < dim; i++) {
+            const double mu = mean[(size_t)j * dim + i], iv = inv_var[(size_t)j * dim + i];
+            const double h = 0.5 * iv, g = -iv * mu;
+            if (!pooled) { put(row, i, h); H += h * h; }
+            put(row, nsq + i, g); G += g * g;
+            cc += h * mu * mu;
+          }
+          put(row, nsq + dim, cc);
+          Gmax = std::max(Gmax, std::sqrt(G)); Hmax = std::max(Hmax, std::sqrt(H)); cabs = std::max(cabs, std::fabs(cc));
+        }
+        sgt[s] = make_float4((float)(Gmax * 1.0001), (float)(Hmax * 1.0001), (float)(cabs * 1.0001), 0.f);
+      }
+      if (upload(c, c->d_Bhi, Bhi.data(), Bhi.size()) || upload(c, c->d_Blo, Blo.data(), Blo.size()) ||
+          upload(c, c->d_col_off, col_off.data(), col_off.size()) || upload(c, c->d_sguard_tc, sgt.data(), sgt.size()))
+        return 1;
+      SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+      c->tc_KP = KP; c->tc_ksteps = (Kused + 7) / 8; c->tc_Dpad = Dpad; c->tc_full = pooled ? 0 : 1;
+      // error model of one 3xTF32 dot product against |a|.|b|: hi/lo split leaves 2^-22 per operand and the
+      // dropped lo.lo term another 2^-22; fp32 accumulation of 3 * 8 * ksteps terms, assumed to truncate
+      // (2^-23 each).  The guard doubles this (two candidates).
+      c->tc_eps = 3.f * 2.384185791015625e-07f + 3.f * 8.f * (float)c->tc_ksteps * 1.1920928955078125e-07f;
+    }
+    c->tc_A_valid = false;
+  }
   if (!c->d_fallbacks.p) {
     SGMM_CHECK(c, c->d_fallbacks.reserve(1));
     SGMM_CHECK(c, cudaMemsetAsync(c->d_fallbacks.p, 0, sizeof(unsigned long long), c->stream));
@@ -180,6 +246,7 @@ int sgmm_set_features(sgmm_ctx* c, const float* x, uint64_t n_frames, uint32_t d
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->n_frames = n_frames; c->feat_dim = dim;
   c->have_alignment = false;
+  c->tc_A_valid = false;
   return 0;
 }
 
@@ -197,7 +264,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   std::vector<uint32_t> uniq, uniq_off(U + 1, 0), ncol(U);
   std::vector<uint16_t> p2u(aut_off[U]);
   std::vector<uint64_t> E_off(U + 1, 0);
-  std::vector<uint4> tasks, tasks64;
+  std::vector<uint4> tasks, tasks64, tasks128;
   std::map<std::pair<int, size_t>, ViterbiClass> classes;
   uint32_t max_state = 0;
   for (uint32_t u = 0; u < U; u++) {
@@ -221,6 +288,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     E_off[u + 1] = E_off[u] + (uint64_t)T * ncol[u];
     for (uint32_t t0 = 0; t0 < T; t0 += 32) tasks.push_back(make_uint4(u, t0, 0, 0));
     for (uint32_t t0 = 0; t0 < T; t0 += 64) tasks64.push_back(make_uint4(u, t0, 0, 0));
+    for (uint32_t t0 = 0; t0 < T; t0 += 128) tasks128.push_back(make_uint4(u, t0, 0, 0));
     int C = 0;
     for (int cc : kViterbiC) if ((uint32_t)cc * 32 >= S) { C = cc; break; }
     size_t sm = viterbi_smem(T, S, ncol[u], C);
@@ -247,11 +315,12 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       upload(c, c->d_aut_off, aut_off, (size_t)U + 1) || upload(c, c->d_uniq, uniq.data(), uniq.size()) ||
       upload(c, c->d_uniq_off, uniq_off.data(), uniq_off.size()) || upload(c, c->d_nuniq_pad, ncol.data(), ncol.size()) ||
       upload(c, c->d_pos2uniq, p2u.data(), p2u.size()) || upload(c, c->d_E_off, E_off.data(), E_off.size()) ||
-      upload(c, c->d_tasks, tasks.data(), tasks.size()) || upload(c, c->d_tasks64, tasks64.data(), tasks64.size()))
+      upload(c, c->d_tasks, tasks.data(), tasks.size()) || upload(c, c->d_tasks64, tasks64.data(), tasks64.size()) ||
+      upload(c, c->d_tasks128, tasks128.data(), tasks128.size()))
     return 1;
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->max_aut_state = max_state;
-  c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->E_elems = E_off[U];
+  c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->n_tasks128 = tasks128.size(); c->E_elems = E_off[U];
   c->h_frame_off.assign(frame_off, frame_off + U + 1);
   c->h_aut_off.assign(aut_off, aut_off + U + 1);
   return 0;
@@ -341,7 +410,7 @@ int sgmm_stage_ms(sgmm_ctx* c, float* ms) {
 int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!c || !key) return 1;
   if (!strcmp(key, "scorer")) {
-    if (value < 0 || value > 2) SGMM_FAIL(c, "set_option: scorer must be 0 (auto), 1 (f64) or 2 (ffma)");
+    if (value < 0 || value > 3) SGMM_FAIL(c, "set_option: scorer must be 0 (auto), 1 (f64), 2 (ffma) or 3 (tensor)");
     c->scorer = (int)value;
     return 0;
   }

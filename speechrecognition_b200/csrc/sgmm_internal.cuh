@@ -57,6 +57,17 @@ struct sgmm_ctx {
   DevBuf<float4> d_mu32, d_h32, d_sguard;
   DevBuf<float> d_c32;
   DevBuf<unsigned long long> d_fallbacks;
+  // tensor-core scorer (k_score_tc.cu): 3xTF32 operands, K-major, KP = padded K
+  uint32_t tc_KP = 0, tc_ksteps = 0, tc_Dpad = 0;
+  int tc_full = 0;                 // 1: K = x^2 | x | 1;  0: variances pooled per state, K = x | 1
+  bool tc_ok = false, tc_A_valid = false;
+  DevBuf<float> d_Bhi, d_Blo, d_Ahi, d_Alo, d_cb1, d_cb2;
+  DevBuf<float2> d_xnorm;
+  DevBuf<float4> d_sguard_tc;      // per state {max ||g||, max ||h||, max |c|, -}
+  DevBuf<uint32_t> d_col_off, d_ci1;
+  DevBuf<unsigned long long> d_rescan;   // [0] = count, [1..] = cell ids
+  size_t rescan_cap = 0;
+  float tc_eps = 0.f;
 
   // ---- features
   uint64_t n_frames = 0;
@@ -70,6 +81,8 @@ struct sgmm_ctx {
   DevBuf<uint64_t> d_frame_off, d_E_off;
   DevBuf<uint32_t> d_aut, d_aut_off, d_uniq, d_uniq_off, d_nuniq_pad;
   DevBuf<uint16_t> d_pos2uniq;
+  DevBuf<uint4> d_tasks128;
+  uint64_t n_tasks128 = 0;
   DevBuf<uint4> d_tasks, d_tasks64;   // emission warp-tasks {utt, t0, 0, 0}: 32-frame and 64-frame granules
   uint64_t n_tasks = 0, n_tasks64 = 0, E_elems = 0;
   DevBuf<double> d_E;             // ragged emission matrix, utterance u: [T_u][nuniq_pad_u]
@@ -128,9 +141,46 @@ int sgmm_launch_emission(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bo
                          uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin);
 int sgmm_launch_emission_ffma(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
                               uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin);
+int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t dense_nframes, double* d_scores,
+                           uint32_t* d_argmin);
 int sgmm_effective_scorer(const sgmm_ctx* c);
 int sgmm_launch_viterbi(sgmm_ctx* c, int tdp_convention);
 int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass);
 int sgmm_launch_accumulate(sgmm_ctx* c);
 int sgmm_launch_score_sum(sgmm_ctx* c);
 int sgmm_nccl_allreduce(sgmm_ctx* c, double* d_buf, size_t n);
+
+// Exact f64 density score in the reference's operation order (Mixtures.cpp:645-690) with the frame's
+// features read from global memory (f32 -> f64 is exact).  Shared by the refinement kernels.
+struct ExactTables {
+  const double2* meanT;
+  const double2* invT;
+  const double* mean_tail;
+  const double* inv_tail;
+  const double* norm;
+  const double* logw;
+  uint32_t dim, npair, Dtot;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ double sgmm_exact_score(const ExactTables& m, const float* __restrict__ xf, uint32_t k) {
+  double l0 = 0.0, l1 = 0.0;
+  const double2* mp = m.meanT + k;
+  const double2* vp = m.invT + k;
+  for (uint32_t ip = 0; ip < m.npair; ip++) {
+    const double2 mu = __ldg(mp), iv = __ldg(vp);
+    double a = __dsub_rn((double)__ldg(xf + 2 * ip), mu.x);
+    double b = __dsub_rn((double)__ldg(xf + 2 * ip + 1), mu.y);
+    a = __dmul_rn(a, a); b = __dmul_rn(b, b);
+    a = __dmul_rn(a, iv.x); b = __dmul_rn(b, iv.y);
+    l0 = __dadd_rn(l0, a); l1 = __dadd_rn(l1, b);
+    mp += m.Dtot; vp += m.Dtot;
+  }
+  double dist = __dadd_rn(l0, l1);
+  if (m.dim & 1) {
+    const double c = __dsub_rn((double)__ldg(xf + m.dim - 1), __ldg(m.mean_tail + k));
+    dist = __dadd_rn(dist, __dmul_rn(__dmul_rn(c, c), __ldg(m.inv_tail + k)));
+  }
+  const double s = __dadd_rn(__ldg(m.norm + k), __dmul_rn(dist, 0.5));
+  return __dsub_rn(s, __ldg(m.logw + k));
+}
+#endif

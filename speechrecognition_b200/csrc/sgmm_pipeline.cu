@@ -26,7 +26,9 @@ void reset_stage(sgmm_ctx* c) {
 
 // emission scoring through whichever scorer is selected
 int launch_emission_any(sgmm_ctx* c, bool dense, uint64_t f0, uint64_t nf, double* scores, uint32_t* argmin) {
-  if (sgmm_effective_scorer(c) == 2) {
+  const int sc = sgmm_effective_scorer(c);
+  if (sc == 3) return sgmm_launch_emission_tc(c, dense, f0, nf, scores, argmin);
+  if (sc == 2) {
     if (dense) return sgmm_launch_emission_ffma(c, nullptr, (nf + 63) / 64, true, f0, nf, scores, argmin);
     return sgmm_launch_emission_ffma(c, c->d_tasks64.p, c->n_tasks64, false, 0, 0, nullptr, nullptr);
   }
@@ -36,13 +38,16 @@ int launch_emission_any(sgmm_ctx* c, bool dense, uint64_t f0, uint64_t nf, doubl
 
 }  // namespace
 
-// 1 = exact f64, 2 = FFMA + refinement.  Automatic: the f32 filter pays off once a state has enough
-// densities to amortise the mandatory f64 evaluation of the winner.
+// 1 = exact f64, 2 = FP32 FFMA + in-kernel refinement, 3 = tcgen05 3xTF32 GEMM + refinement kernels.
+// Automatic: an f32 filter pays off once a state has enough densities to amortise the mandatory f64
+// evaluation of the winner; the tensor-core form needs enough columns per state to fill MMA tiles.
 int sgmm_effective_scorer(const sgmm_ctx* c) {
-  if (c->scorer == 1 || c->dv4 == 0) return 1;
-  if (c->scorer == 2) return 2;
+  if (c->scorer == 1) return 1;
+  if (c->scorer == 3) return c->tc_ok ? 3 : (c->dv4 ? 2 : 1);
+  if (c->scorer == 2) return c->dv4 ? 2 : 1;
   const double avg = c->n_states ? (double)c->Dtot / c->n_states : 0.0;
-  return avg >= 6.0 ? 2 : 1;
+  if (avg >= 48.0 && c->tc_ok) return 3;
+  return (avg >= 6.0 && c->dv4) ? 2 : 1;
 }
 
 extern "C" {

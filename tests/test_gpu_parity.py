@@ -30,10 +30,10 @@ def small33():
     ctx.close()
 
 
-SCORERS = {"f64": 1, "ffma": 2}
+SCORERS = {"f64": 1, "ffma": 2, "tc": 3}
 
 
-@pytest.mark.parametrize("scorer", ["f64", "ffma"])
+@pytest.mark.parametrize("scorer", ["f64", "ffma", "tc"])
 @pytest.mark.parametrize("fx", ["small25", "small33"])
 def test_score_all_bit_exact(fx, scorer, request):
     O, corp, ali, ctx = request.getfixturevalue(fx)
@@ -48,7 +48,7 @@ def test_score_all_bit_exact(fx, scorer, request):
     assert np.array_equal(got_s2, want_s[37:82]) and np.array_equal(got_a2, want_a[37:82])
 
 
-@pytest.mark.parametrize("scorer", ["f64", "ffma"])
+@pytest.mark.parametrize("scorer", ["f64", "ffma", "tc"])
 @pytest.mark.parametrize("fx", ["small25", "small33"])
 def test_align_full_bit_exact(fx, scorer, request):
     O, corp, ali, ctx = request.getfixturevalue(fx)
@@ -194,4 +194,45 @@ def test_ffma_scorer_ties_and_near_ties():
     fb = ctx.get_counter("fallbacks")
     assert fb >= len(st) // 2                      # the planted ties did take the f64 rescan path
     assert fb < 0.2 * got_s.size                   # ... and only they did
+    ctx.close()
+
+
+@pytest.mark.parametrize("dim,nd,pooling", [(33, 200, "mixture"), (25, 40, "none"), (33, 256, "global"), (12, 17, "none")])
+def test_tensor_core_scorer_exact(dim, nd, pooling):
+    """tcgen05 3xTF32 GEMM + certified refinement: dense scores/argmins and batched alignments bit-identical to
+    the oracle, in the pooled (K = d+1) and the full (K = 2d+1) operand forms, with ragged state sizes."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(23)
+    lex = synth.Lexicon()
+    t = synth.random_model(rng, dim, lex.num_states, nd, pooling)
+    # make the state sizes ragged: drop a few densities of every third state
+    if nd > 20:
+        keep = np.ones(len(t["mean_idx"]), bool)
+        for s in range(0, lex.num_states, 3):
+            keep[s * nd + nd - 7: s * nd + nd] = False
+        sizes = np.array([keep[s * nd:(s + 1) * nd].sum() for s in range(lex.num_states)])
+        t["mean_idx"], t["var_idx"] = t["mean_idx"][keep], t["var_idx"][keep]
+        t["mix_offsets"] = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint32)
+    corp = synth.make_corpus(rng, lex, t, dim, 5)
+    tdp = (3.0, 0.0, 30.0)
+    O = Oracle(dim, lex.num_states, pooling, True, tdp, lex.silence_state)
+    O.load_tables(t)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, t); ctx.set_features(corp["x"])
+    ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"]); ctx.set_tdp(*tdp, lex.silence_state)
+    ctx.set_option("scorer", 3)
+    assert ctx.get_counter("scorer") == 3
+    n = 300
+    want_s, want_a = O.min_score(corp["x"][:n])
+    ctx.get_counter("fallbacks")
+    got_s, got_a = ctx.score_all(0, n)
+    fb = ctx.get_counter("fallbacks")
+    assert np.array_equal(got_a, want_a)
+    assert np.array_equal(got_s, want_s)
+    assert fb < 0.25 * got_s.size, f"{fb} of {got_s.size} cells fell back to the f64 rescan"
+    want_states, want_costs = O.align_batch(corp["x"], corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
+    got, costs = ctx.align()
+    assert np.array_equal(costs, want_costs)
+    assert np.array_equal(got["state"].astype(np.uint32), want_states)
     ctx.close()
