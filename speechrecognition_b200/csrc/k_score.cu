@@ -34,6 +34,7 @@ struct EmisParams {
   const uint32_t* nuniq_pad;
   const uint64_t* E_off;
   double* E;
+  uint16_t* Amin;
   // dense mode
   int dense;
   uint64_t f0, nframes;
@@ -138,6 +139,7 @@ __global__ void __launch_bounds__(kEmisWarps * 32) k_emission_f64(EmisParams p) 
   const uint32_t* ulist = nullptr;
   double* out;
   uint32_t* amin = nullptr;
+  uint16_t* amin16 = nullptr;
   if (p.dense) {
     const uint64_t r0 = task * 32;
     fbase = p.f0 + r0;
@@ -156,6 +158,7 @@ __global__ void __launch_bounds__(kEmisWarps * 32) k_emission_f64(EmisParams p) 
     nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
     out_stride = p.nuniq_pad[t.x];
     out = p.E + p.E_off[t.x] + (uint64_t)t.y * out_stride;
+    amin16 = p.Amin + p.E_off[t.x] + (uint64_t)t.y * out_stride;
   }
   load_frames(p.x, fbase, nvalid, p.m.dim, p.m.npair, xs, xt, lane);
   const double xtail = xt[lane];
@@ -170,6 +173,7 @@ __global__ void __launch_bounds__(kEmisWarps * 32) k_emission_f64(EmisParams p) 
       min_over_state(p.m, p.m.state_off[s], p.m.state_off[s + 1], my_xs, 32, xtail, best, bk);
       stage[lane * 33 + jj] = best;
       if (amin && lane < (int)nvalid) amin[(uint64_t)lane * out_stride + j0 + jj] = bk;
+      if (amin16 && lane < (int)nvalid) amin16[(uint64_t)lane * out_stride + j0 + jj] = (uint16_t)bk;
     }
     __syncwarp();
     if (out && lane < (int)jn)
@@ -225,6 +229,41 @@ __global__ void __launch_bounds__(kRescoreWarps * 32) k_rescore_f64(RescoreParam
   }
 }
 
+// K3 when the model is the one the resident alignment was computed with: the alignment pass has already
+// scored every (frame, state-of-its-utterance) cell, so the frame's min score and argmin density are a lookup.
+struct CachedParams {
+  const sgmm_alignment_item* ali;
+  const uint16_t* fcol;
+  const double* E;
+  const uint16_t* Amin;
+  const uint64_t* frame_off;
+  const uint64_t* E_off;
+  const uint32_t* nuniq_pad;
+  const uint32_t* state_off;
+  uint32_t n_utts, Dtot;
+  uint64_t n_frames;
+  uint32_t* fdens;
+  double* fscore;
+  uint32_t* cnt;
+};
+
+__global__ void __launch_bounds__(256) k_rescore_cached(CachedParams p) {
+  const uint64_t f = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= p.n_frames) return;
+  uint32_t lo = 0, hi = p.n_utts;            // utterance of frame f: largest u with frame_off[u] <= f
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (p.frame_off[mid] <= f) lo = mid; else hi = mid;
+  }
+  const uint64_t e = p.E_off[lo] + (f - p.frame_off[lo]) * p.nuniq_pad[lo] + p.fcol[f];
+  const uint32_t s = p.ali[f].state;
+  const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
+  const uint32_t gid = (k1 > k0) ? k0 + p.Amin[e] : p.Dtot;
+  p.fdens[f] = gid;
+  p.fscore[f] = p.E[e];
+  atomicAdd(p.cnt + gid, 1u);
+}
+
 ModelView model_view(const sgmm_ctx* c) {
   ModelView m;
   m.meanT = c->d_meanT.p; m.invT = c->d_invT.p; m.mean_tail = c->d_mean_tail.p; m.inv_tail = c->d_inv_tail.p;
@@ -244,7 +283,7 @@ int sgmm_launch_emission(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bo
   p.n_tasks = n_tasks;
   p.tasks = d_tasks;
   p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
-  p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p;
+  p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p; p.Amin = c->d_Amin.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.scores = d_scores; p.argmin = d_argmin;
   const size_t smem = kEmisWarps * emis_smem_per_warp(c->npair);
@@ -267,6 +306,18 @@ int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass) {
   const uint64_t warps = (c->n_frames + 31) / 32;
   const uint64_t grid = (warps + kRescoreWarps - 1) / kRescoreWarps;
   k_rescore_f64<<<(unsigned)grid, kRescoreWarps * 32, smem, c->stream>>>(p);
+  SGMM_LAUNCH_CHECK(c);
+  return 0;
+}
+
+int sgmm_launch_rescore_cached(sgmm_ctx* c) {
+  if (c->n_frames == 0) return 0;
+  CachedParams p{};
+  p.ali = c->d_ali.p; p.fcol = c->d_fcol.p; p.E = c->d_E.p; p.Amin = c->d_Amin.p;
+  p.frame_off = c->d_frame_off.p; p.E_off = c->d_E_off.p; p.nuniq_pad = c->d_nuniq_pad.p;
+  p.state_off = c->d_state_off.p; p.n_utts = c->n_utts; p.Dtot = c->Dtot; p.n_frames = c->n_frames;
+  p.fdens = c->d_fdens.p; p.fscore = c->d_fscore.p; p.cnt = c->d_cnt_u32.p;
+  k_rescore_cached<<<(unsigned)((c->n_frames + 255) / 256), 256, 0, c->stream>>>(p);
   SGMM_LAUNCH_CHECK(c);
   return 0;
 }

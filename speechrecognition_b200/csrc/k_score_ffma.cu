@@ -53,6 +53,7 @@ struct Params {
   const uint32_t* nuniq_pad;
   const uint64_t* E_off;
   double* E;
+  uint16_t* Amin;
   // dense mode
   int dense;
   uint64_t f0, nframes;
@@ -99,6 +100,7 @@ __global__ void __launch_bounds__(kWarps * 32) k_emission_ffma(Params p) {
   const uint32_t* ulist = nullptr;
   double* out;
   uint32_t* amin = nullptr;
+  uint16_t* amin16 = nullptr;
   if (p.dense) {
     const uint64_t r0 = task * (32 * R);
     fbase = p.f0 + r0;
@@ -117,6 +119,7 @@ __global__ void __launch_bounds__(kWarps * 32) k_emission_ffma(Params p) {
     nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
     out_stride = p.nuniq_pad[t.x];
     out = p.E + p.E_off[t.x] + (uint64_t)t.y * out_stride;
+    amin16 = p.Amin + p.E_off[t.x] + (uint64_t)t.y * out_stride;
   }
 
   // features of this lane's R frames in registers (zero padded to 4*DV4)
@@ -205,6 +208,7 @@ __global__ void __launch_bounds__(kWarps * 32) k_emission_ffma(Params p) {
       }
       if (out) out[(uint64_t)row * out_stride + j] = best;
       if (amin) amin[(uint64_t)row * out_stride + j] = bk;
+      if (amin16) amin16[(uint64_t)row * out_stride + j] = (uint16_t)bk;
     }
   }
   if (p.fallback_count && n_fallback) atomicAdd(p.fallback_count, n_fallback);
@@ -223,7 +227,7 @@ int sgmm_launch_emission_ffma(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_task
   p.dim = c->dim; p.npair = c->npair; p.Dtot = c->Dtot; p.n_states = c->n_states;
   p.x = c->d_x.p; p.n_tasks = n_tasks; p.tasks = d_tasks;
   p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
-  p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p;
+  p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p; p.Amin = c->d_Amin.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes;
   p.scores = d_scores; p.argmin = d_argmin;
   p.fallback_count = c->d_fallbacks.p;

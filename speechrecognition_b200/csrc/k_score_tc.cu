@@ -343,6 +343,7 @@ struct RefineParams {
   const uint32_t* nuniq_pad;
   double* out;                 // emission matrix / dense scores
   uint32_t* argmin;            // dense only (may be NULL)
+  uint16_t* amin16;            // gathered only (may be NULL)
   unsigned long long* rescan;  // [0] count, [1..cap] cell ids
   unsigned long long cap;
   unsigned long long* fallback_count;
@@ -402,6 +403,7 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
   }
   p.out[e] = best;
   if (p.argmin) p.argmin[e] = bk;
+  if (p.amin16) p.amin16[e] = (uint16_t)bk;
 }
 
 // one warp per queued near-tie cell: exact f64 rescan of the whole state, first minimum wins
@@ -431,6 +433,7 @@ __global__ void __launch_bounds__(256) k_tc_rescan(RefineParams p) {
     if (lane == 0) {
       p.out[e] = best;
       if (p.argmin) p.argmin[e] = bk == 0xffffffffu ? 0 : bk;
+      if (p.amin16) p.amin16[e] = bk == 0xffffffffu ? 0 : (uint16_t)bk;
       if (p.fallback_count) atomicAdd(p.fallback_count, 1ull);
     }
   }
@@ -535,6 +538,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   r.frame_off = c->d_frame_off.p; r.E_off = c->d_E_off.p; r.uniq = c->d_uniq.p; r.uniq_off = c->d_uniq_off.p;
   r.nuniq_pad = c->d_nuniq_pad.p;
   r.out = dense ? d_scores : c->d_E.p; r.argmin = dense ? d_argmin : nullptr;
+  r.amin16 = dense ? nullptr : c->d_Amin.p;
   r.rescan = c->d_rescan.p; r.cap = cap; r.fallback_count = c->d_fallbacks.p;
   k_tc_refine<<<(unsigned)((n_cells + 255) / 256), 256, 0, c->stream>>>(r);
   SGMM_LAUNCH_CHECK(c);

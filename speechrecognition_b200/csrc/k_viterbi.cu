@@ -57,6 +57,7 @@ struct VitParams {
   double tdp_loop, tdp_forward, tdp_skip;
   uint32_t silence_state;
   sgmm_alignment_item* ali;
+  uint16_t* fcol;              // per frame: emission column of the aligned position
   double* costs;
 };
 
@@ -92,13 +93,14 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
   const size_t tile_elems = (size_t)SGMM_TILE_T * ncol;
   uint32_t* bpw = reinterpret_cast<uint32_t*>(tiles + SGMM_STAGES * tile_elems);  // ceil(T/16) x 32C words
   uint16_t* sref = reinterpret_cast<uint16_t*>(bpw + (size_t)((T + 15) / 16) * 32 * C);  // automaton states
+  uint16_t* scol = sref + S;                                                          // emission column per position
 
   const uint32_t n_tiles = (T + SGMM_TILE_T - 1) / SGMM_TILE_T;
   if (lane == 0) {
     for (int i = 0; i < SGMM_STAGES; i++) mbar_init(&bars[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (uint32_t s = lane; s < S; s += 32) sref[s] = (uint16_t)p.aut[a0 + s];
+  for (uint32_t s = lane; s < S; s += 32) { sref[s] = (uint16_t)p.aut[a0 + s]; scol[s] = p.pos2uniq[a0 + s]; }
   __syncwarp();
   if (lane == 0) {
     for (uint32_t i = 0; i < SGMM_STAGES && i < n_tiles; i++) {
@@ -231,6 +233,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     uint32_t s = end_s;
     for (uint32_t t = T - 1; t >= 1; t--) {
       out[t] = make_uint2(1u | ((uint32_t)sref[s] << 16), one);
+      p.fcol[f0 + t] = scol[s];
       const uint32_t word = bpw[(size_t)(t >> 4) * 32 * C + (s % C) * 32 + s / C];
       const uint32_t j = (word >> (2 * (t & 15))) & 3u;
       s = s >= j ? s - j : 0;
@@ -238,17 +241,18 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     // frame 0: the full aligner writes reference[state reached] (= position 0 on any valid path); the
     // pruned one writes reference[0] explicitly (Alignment.cpp:272-275)
     out[0] = make_uint2(1u | ((uint32_t)sref[DEST ? 0 : s] << 16), one);
+    p.fcol[f0] = scol[DEST ? 0 : s];
   }
 }
 
 template <int C>
-int launch_c(sgmm_ctx* c, const VitParams& p, size_t smem, int conv) {
+int launch_c(sgmm_ctx* c, const VitParams& p, size_t smem, int conv, cudaStream_t stream) {
   if (conv == SGMM_TDP_SOURCE) {
     SGMM_CHECK(c, cudaFuncSetAttribute(k_viterbi<C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_viterbi<C, false><<<p.n_utts, 32, smem, c->stream>>>(p);
+    k_viterbi<C, false><<<p.n_utts, 32, smem, stream>>>(p);
   } else {
     SGMM_CHECK(c, cudaFuncSetAttribute(k_viterbi<C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_viterbi<C, true><<<p.n_utts, 32, smem, c->stream>>>(p);
+    k_viterbi<C, true><<<p.n_utts, 32, smem, stream>>>(p);
   }
   SGMM_LAUNCH_CHECK(c);
   return 0;
@@ -257,29 +261,39 @@ int launch_c(sgmm_ctx* c, const VitParams& p, size_t smem, int conv) {
 }  // namespace
 
 int sgmm_launch_viterbi(sgmm_ctx* c, int conv) {
+  // the shape classes are independent: fork them over the side streams, join on the main stream
+  SGMM_CHECK(c, cudaEventRecord(c->ev_fork, c->stream));
+  int n_launched = 0;
   for (ViterbiClass& vc : c->vclasses) {
     if (vc.utts.empty()) continue;
+    cudaStream_t stream = c->aux[n_launched % sgmm_ctx::kAux];
+    if (n_launched < sgmm_ctx::kAux) SGMM_CHECK(c, cudaStreamWaitEvent(stream, c->ev_fork, 0));
+    n_launched++;
     VitParams p{};
     p.utts = vc.d_utts.p; p.n_utts = (uint32_t)vc.utts.size();
     p.frame_off = c->d_frame_off.p; p.aut = c->d_aut.p; p.aut_off = c->d_aut_off.p;
     p.pos2uniq = c->d_pos2uniq.p; p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p;
     p.tdp_loop = c->tdp_loop; p.tdp_forward = c->tdp_forward; p.tdp_skip = c->tdp_skip;
     p.silence_state = c->silence_state;
-    p.ali = c->d_ali.p; p.costs = c->d_costs.p;
+    p.ali = c->d_ali.p; p.fcol = c->d_fcol.p; p.costs = c->d_costs.p;
     int rc = 1;
     switch (vc.C) {
-      case 2: rc = launch_c<2>(c, p, vc.smem, conv); break;
-      case 3: rc = launch_c<3>(c, p, vc.smem, conv); break;
-      case 4: rc = launch_c<4>(c, p, vc.smem, conv); break;
-      case 5: rc = launch_c<5>(c, p, vc.smem, conv); break;
-      case 6: rc = launch_c<6>(c, p, vc.smem, conv); break;
-      case 8: rc = launch_c<8>(c, p, vc.smem, conv); break;
-      case 10: rc = launch_c<10>(c, p, vc.smem, conv); break;
-      case 12: rc = launch_c<12>(c, p, vc.smem, conv); break;
-      case 16: rc = launch_c<16>(c, p, vc.smem, conv); break;
+      case 2: rc = launch_c<2>(c, p, vc.smem, conv, stream); break;
+      case 3: rc = launch_c<3>(c, p, vc.smem, conv, stream); break;
+      case 4: rc = launch_c<4>(c, p, vc.smem, conv, stream); break;
+      case 5: rc = launch_c<5>(c, p, vc.smem, conv, stream); break;
+      case 6: rc = launch_c<6>(c, p, vc.smem, conv, stream); break;
+      case 8: rc = launch_c<8>(c, p, vc.smem, conv, stream); break;
+      case 10: rc = launch_c<10>(c, p, vc.smem, conv, stream); break;
+      case 12: rc = launch_c<12>(c, p, vc.smem, conv, stream); break;
+      case 16: rc = launch_c<16>(c, p, vc.smem, conv, stream); break;
       default: SGMM_FAIL(c, "viterbi: unsupported positions-per-lane class");
     }
     if (rc) return rc;
+  }
+  for (int i = 0; i < n_launched && i < sgmm_ctx::kAux; i++) {
+    SGMM_CHECK(c, cudaEventRecord(c->ev_join[i], c->aux[i]));
+    SGMM_CHECK(c, cudaStreamWaitEvent(c->stream, c->ev_join[i], 0));
   }
   return 0;
 }

@@ -29,7 +29,7 @@ size_t viterbi_smem(uint32_t T, uint32_t S, uint32_t ncol, int C) {
   size_t b = 64;
   b += (size_t)SGMM_STAGES * SGMM_TILE_T * ncol * sizeof(double);
   b += (size_t)((T + 15) / 16) * 32 * C * sizeof(uint32_t);
-  b += (size_t)S * sizeof(uint16_t);
+  b += 2 * (size_t)S * sizeof(uint16_t);
   return (b + 15) & ~(size_t)15;
 }
 }  // namespace
@@ -69,6 +69,9 @@ int sgmm_create(int device, sgmm_ctx** out) {
   }
   for (auto& ev : c->ev) cudaEventCreate(&ev);
   for (auto& ev : c->tev) cudaEventCreate(&ev);
+  for (auto& st : c->aux) cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+  cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+  for (auto& ev : c->ev_join) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
   *out = c;
   return 0;
 }
@@ -82,7 +85,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_frame_off.release(); c->d_E_off.release(); c->d_aut.release(); c->d_aut_off.release();
   c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
   c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_h32.release(); c->d_c32.release();
-  c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release();
+  c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release(); c->d_Amin.release(); c->d_fcol.release();
   c->d_Bhi.release(); c->d_Blo.release(); c->d_Ahi.release(); c->d_Alo.release(); c->d_cb1.release(); c->d_cb2.release();
   c->d_xnorm.release(); c->d_sguard_tc.release(); c->d_col_off.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
@@ -93,6 +96,9 @@ void sgmm_destroy(sgmm_ctx* c) {
   for (auto& vc : c->vclasses) vc.d_utts.release();
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
   for (auto& ev : c->tev) if (ev) cudaEventDestroy(ev);
+  for (auto& st : c->aux) if (st) cudaStreamDestroy(st);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  for (auto& ev : c->ev_join) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -230,6 +236,7 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
   c->dv4 = dv4;
   c->dim = dim; c->npair = npair; c->n_states = n_states; c->Dtot = D; c->max_dens = max_d;
   c->h_state_off.assign(state_off, state_off + n_states + 1);
+  c->model_version++;
   return 0;
 }
 
@@ -246,6 +253,7 @@ int sgmm_set_features(sgmm_ctx* c, const float* x, uint64_t n_frames, uint32_t d
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->n_frames = n_frames; c->feat_dim = dim;
   c->have_alignment = false;
+  c->ali_has_cols = false;
   c->tc_A_valid = false;
   return 0;
 }
@@ -414,6 +422,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
     c->scorer = (int)value;
     return 0;
   }
+  if (!strcmp(key, "rescore_cache")) { c->use_cache = value != 0; return 0; }
   SGMM_FAIL(c, std::string("set_option: unknown key ") + key);
 }
 

@@ -44,6 +44,10 @@ struct sgmm_ctx {
   float stage_ms[SGMM_T_COUNT] = {0};
   cudaEvent_t ev[2 * SGMM_T_COUNT] = {nullptr};
   cudaEvent_t tev[2] = {nullptr, nullptr};
+  // side streams so that independent launches (the Viterbi shape classes) overlap
+  static constexpr int kAux = 8;
+  cudaStream_t aux[kAux] = {nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join[kAux] = {nullptr};
 
   // ---- model (exact f64 tables, dim-pair-major: tabT[ip * Dtot + j] = {mean.x, mean.y} etc.)
   uint32_t dim = 0, npair = 0, n_states = 0, Dtot = 0, max_dens = 0;
@@ -86,6 +90,11 @@ struct sgmm_ctx {
   DevBuf<uint4> d_tasks, d_tasks64;   // emission warp-tasks {utt, t0, 0, 0}: 32-frame and 64-frame granules
   uint64_t n_tasks = 0, n_tasks64 = 0, E_elems = 0;
   DevBuf<double> d_E;             // ragged emission matrix, utterance u: [T_u][nuniq_pad_u]
+  DevBuf<uint16_t> d_Amin;        // argmin density of every emission cell (same indexing as d_E)
+  DevBuf<uint16_t> d_fcol;        // per frame: emission column of the aligned position (written by the backtrace)
+  uint64_t model_version = 1, E_model_version = 0;
+  bool use_cache = true;          // option "rescore_cache"
+  bool ali_has_cols = false;      // resident alignment came from sgmm_align (d_fcol valid)
   std::vector<ViterbiClass> vclasses;
   DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)
 
@@ -146,6 +155,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
 int sgmm_effective_scorer(const sgmm_ctx* c);
 int sgmm_launch_viterbi(sgmm_ctx* c, int tdp_convention);
 int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass);
+int sgmm_launch_rescore_cached(sgmm_ctx* c);
 int sgmm_launch_accumulate(sgmm_ctx* c);
 int sgmm_launch_score_sum(sgmm_ctx* c);
 int sgmm_nccl_allreduce(sgmm_ctx* c, double* d_buf, size_t n);

@@ -89,6 +89,8 @@ int sgmm_align(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* co
   if (require(c, true, true, true)) return 1;
   if (conv != SGMM_TDP_SOURCE && conv != SGMM_TDP_DESTINATION) SGMM_FAIL(c, "align: bad tdp_convention");
   SGMM_CHECK(c, c->d_E.reserve(c->E_elems + 2));
+  SGMM_CHECK(c, c->d_Amin.reserve(c->E_elems + 2));
+  SGMM_CHECK(c, c->d_fcol.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_ali.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_costs.reserve(c->n_utts));
   {
@@ -110,6 +112,8 @@ int sgmm_align(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* co
   }
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->have_alignment = true;
+  c->ali_has_cols = true;
+  c->E_model_version = c->model_version;
   return 0;
 }
 
@@ -129,6 +133,7 @@ int sgmm_set_alignment(sgmm_ctx* c, const sgmm_alignment_item* alignment, uint64
   }
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->have_alignment = true;
+  c->ali_has_cols = false;
   return 0;
 }
 
@@ -141,7 +146,9 @@ static int rescore_common(sgmm_ctx* c, bool first_pass) {
   SGMM_CHECK(c, c->d_acc.reserve(acc_len(c)));
   SGMM_CHECK(c, cudaMemsetAsync(c->d_cnt_u32.p, 0, (c->Dtot + 1) * sizeof(uint32_t), c->stream));
   StageTimer st(c, SGMM_T_RESCORE);
-  if (sgmm_launch_rescore(c, first_pass)) return 1;
+  // the alignment pass already scored these cells with this very model: look the results up
+  const bool cached = !first_pass && c->ali_has_cols && c->E_model_version == c->model_version && c->use_cache;
+  if (cached ? sgmm_launch_rescore_cached(c) : sgmm_launch_rescore(c, first_pass)) return 1;
   if (sgmm_launch_score_sum(c)) return 1;
   return 0;
 }

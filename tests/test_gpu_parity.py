@@ -236,3 +236,34 @@ def test_tensor_core_scorer_exact(dim, nd, pooling):
     assert np.array_equal(costs, want_costs)
     assert np.array_equal(got["state"].astype(np.uint32), want_states)
     ctx.close()
+
+
+@pytest.mark.parametrize("scorer", ["f64", "ffma", "tc"])
+def test_accumulate_after_align_uses_cached_scores(small25, scorer):
+    """align -> accumulate with an unchanged model takes the lookup path (the alignment pass already scored the
+    aligned cells); it must agree bit for bit with the recomputing path and with the oracle."""
+    O, corp, ali, ctx = small25
+    ctx.set_option("scorer", SCORERS[scorer])
+    got, _ = ctx.align()
+    states = got["state"].astype(np.uint32)
+    ctx.set_option("rescore_cache", 1)
+    a = ctx.accumulate(first_pass=False)
+    da, sa = ctx.last_frame_results()
+    ctx.set_option("rescore_cache", 0)
+    b = ctx.accumulate(first_pass=False)
+    db, sb = ctx.last_frame_results()
+    ctx.set_option("rescore_cache", 1)
+    assert np.array_equal(da, db) and np.array_equal(sa, sb)
+    for u, v in zip(a[:3], b[:3]):
+        assert np.array_equal(u, v)
+    assert a[3] == b[3]
+    from oracle.binding import Oracle
+    P = Oracle(O.dim, O.n_mix, "none", True, O.tdp, O.silence)
+    P.load_tables(O.tables())
+    want_dens = P.accumulate(states, corp["x"])
+    assert np.array_equal(da, want_dens)
+    # a new model invalidates the cache: the recomputing path must be taken (and still be right)
+    ctx.set_model_tables(O.dim, O.tables())
+    c = ctx.accumulate(first_pass=False)
+    for u, v in zip(a[:3], c[:3]):
+        assert np.array_equal(u, v)
