@@ -235,6 +235,7 @@ def run_ours(args):
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
+    ctx.get_counter("fallbacks")      # reset
     l0 = ctx.launch_count()
     ctx.timer_start()
     stages = []
@@ -242,6 +243,7 @@ def run_ours(args):
         stages.append(step_resident())
     ms = ctx.timer_stop()
     launches = ctx.launch_count() - l0
+    fallbacks = ctx.get_counter("fallbacks")
     barrier()
     ms = max_over_ranks(ms)
     sampler.stop_flag = True
@@ -267,19 +269,41 @@ def run_ours(args):
     stage = {k: float(np.mean([s[k] for s in stages])) for k in stages[0]}
     dens_scored = densities_scored(tables, corp)
     K = 2 * args.dim + 1
-    score_s = stage["score"] / 1e3
-    achieved = 2.0 * K * dens_scored / score_s / 1e12
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    scorer = ctx.get_counter("scorer")
+    alg_flops = 2.0 * K * dens_scored          # 2*(2d+1) per (frame, density scored)
+    if scorer == 3:
+        t_kernel = stage["score_filter"] / 1e3
+        bf16 = float(peaks.get("bf16_tflops", 1590.0))
+        peak = bf16 / 2.0 / 3.0                # tf32 dense = bf16/2; 3xTF32 executes 3 MMAs per algorithmic one
+        roof = {"bound": "tensor", "kernel": "k_tc_gemm (tcgen05 kind::tf32, 3xTF32, top-2 epilogue)",
+                "achieved": alg_flops / t_kernel / 1e12, "peak": peak, "unit": "TFLOP/s",
+                "peak_source": ("MEASURED_PEAKS.json bf16_tflops" if peaks else "fallback 1590") + " / 2 (tf32) / 3 (3xTF32)",
+                "kernel_ms": stage["score_filter"], "refine_ms": stage["score_refine"], "traffic": None}
+    elif scorer == 2:
+        t_kernel = stage["score"] / 1e3
+        roof = {"bound": "tensor", "kernel": "k_emission_ffma (FP32 FFMA + in-kernel f64 refinement)",
+                "achieved": alg_flops / t_kernel / 1e12, "peak": FFMA_PEAK_TFLOPS, "unit": "TFLOP/s",
+                "peak_source": "nominal FP32 FFMA: 148 SM x 128 lanes x 2 x 1.965 GHz", "kernel_ms": stage["score"],
+                "traffic": None}
+    else:
+        t_kernel = stage["score"] / 1e3
+        roof = {"bound": "tensor", "kernel": "k_emission_f64 (exact f64, FP64 pipe)",
+                "achieved": alg_flops / t_kernel / 1e12, "peak": FFMA_PEAK_TFLOPS, "unit": "TFLOP/s",
+                "peak_source": "nominal FP32 FFMA: 148 SM x 128 lanes x 2 x 1.965 GHz", "kernel_ms": stage["score"],
+                "traffic": None}
+    roof["frac"] = roof["achieved"] / roof["peak"]
+    roof["algorithmic_flops_per_step"] = alg_flops
     # Viterbi: algorithmic bytes = emission row read (f64) + AlignmentItem write per frame
     ncols = []
     for u in range(U):
         n = len(np.unique(corp["automata"][int(corp["aut_off"][u]):int(corp["aut_off"][u + 1])]))
         ncols.append(((n + 1) // 2 * 2) * int(corp["frame_off"][u + 1] - corp["frame_off"][u]))
     vit_bytes = 8.0 * sum(ncols) + 8.0 * F
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     line = {
         "metric": "frames/sec scored+aligned+accumulated (GMM+Viterbi+EM)", "value": frames_total * args.steps / (ms / 1e3),
@@ -291,11 +315,9 @@ def run_ours(args):
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
         "stage_ms_per_step": stage,
-        "roofline": {"bound": "tensor", "kernel": "k_emission_f64 (exact-f64 GMM scoring, FP64 pipe)",
-                     "achieved": achieved, "peak": FFMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": achieved / FFMA_PEAK_TFLOPS,
-                     "traffic": None,
-                     "note": "algorithmic flops 2*(2d+1) per (frame, density scored); peak = nominal FP32 FFMA "
-                             "(148 SM x 128 lanes x 2 x 1.965 GHz); this kernel runs on the FP64 pipe"},
+        "roofline": roof,
+        "scorer": {1: "f64", 2: "ffma", 3: "tcgen05"}[scorer],
+        "f64_rescan_cells_per_step": fallbacks / max(1, args.steps),
         "roofline_viterbi": {"bound": "hbm", "kernel": "k_viterbi", "achieved": vit_bytes / (stage["viterbi"] / 1e3) / 1e9,
                              "peak": hbm_peak, "unit": "GB/s",
                              "frac": vit_bytes / (stage["viterbi"] / 1e3) / 1e9 / hbm_peak,

@@ -128,7 +128,10 @@ int sgmm_comm_init(sgmm_ctx* ctx, int rank, int world_size, const void* id, size
  * Trainer::train (Training.cpp:45-49,230-234).  Index with the SGMM_T_* constants. */
 enum {
   SGMM_T_H2D = 0, SGMM_T_SCORE = 1, SGMM_T_VITERBI = 2, SGMM_T_RESCORE = 3, SGMM_T_SORT = 4,
-  SGMM_T_REDUCE = 5, SGMM_T_ALLREDUCE = 6, SGMM_T_D2H = 7, SGMM_T_COUNT = 8
+  SGMM_T_REDUCE = 5, SGMM_T_ALLREDUCE = 6, SGMM_T_D2H = 7,
+  SGMM_T_SCORE_FILTER = 8,   /* part of SCORE: the f32 / tensor-core candidate kernel (k_tc_gemm) */
+  SGMM_T_SCORE_REFINE = 9,   /* part of SCORE: f64 certification + rescan kernels */
+  SGMM_T_COUNT = 10
 };
 int sgmm_stage_ms(sgmm_ctx* ctx, float* ms /* [SGMM_T_COUNT] */);
 /* Device-side stopwatch on the context's stream (CUDA events): start, then stop returns the elapsed ms

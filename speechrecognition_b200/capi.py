@@ -11,7 +11,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsietill_b200.so")
 
-T_NAMES = ["h2d", "score", "viterbi", "rescore", "sort", "reduce", "allreduce", "d2h"]
+T_NAMES = ["h2d", "score", "viterbi", "rescore", "sort", "reduce", "allreduce", "d2h", "score_filter", "score_refine"]
 TDP_SOURCE, TDP_DESTINATION = 0, 1
 
 ALI_DTYPE = np.dtype([("count", np.uint16), ("state", np.uint16), ("weight", np.float32)])  # Types.hpp:29-38

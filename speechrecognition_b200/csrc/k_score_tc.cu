@@ -518,6 +518,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cb1 = c->d_cb1.p; p.cb2 = c->d_cb2.p; p.ci1 = c->d_ci1.p;
   const size_t smem = 1024 + (size_t)(2 + 2 * NSTAGE) * kblk * 16384 + 256;
+  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER], c->stream);
   if (kblk == 1) {
     SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_tc_gemm<1><<<(unsigned)n_tasks, 192, smem, c->stream>>>(mAhi, mAlo, mBhi, mBlo, p);
@@ -528,6 +529,8 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     SGMM_FAIL(c, "tensor-core scorer: K too large for the shared-memory plan");
   }
   SGMM_LAUNCH_CHECK(c);
+  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER + 1], c->stream);
+  c->stage_ms[SGMM_T_SCORE_FILTER] = -1.f;
 
   RefineParams r{};
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
@@ -540,9 +543,12 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   r.out = dense ? d_scores : c->d_E.p; r.argmin = dense ? d_argmin : nullptr;
   r.amin16 = dense ? nullptr : c->d_Amin.p;
   r.rescan = c->d_rescan.p; r.cap = cap; r.fallback_count = c->d_fallbacks.p;
+  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE], c->stream);
   k_tc_refine<<<(unsigned)((n_cells + 255) / 256), 256, 0, c->stream>>>(r);
   SGMM_LAUNCH_CHECK(c);
   k_tc_rescan<<<148 * 4, 256, 0, c->stream>>>(r);
   SGMM_LAUNCH_CHECK(c);
+  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE + 1], c->stream);
+  c->stage_ms[SGMM_T_SCORE_REFINE] = -1.f;
   return 0;
 }
