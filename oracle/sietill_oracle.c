@@ -334,7 +334,10 @@ void orc_finalize(orc_model *m) {
       for (uint32_t k = 0; k < m->mix_n[s]; k++)
         for (size_t i = 0; i < d; i++) pooled[i] = pooled[i] + m->mean_acc[(size_t)m->mix_mean[s][k] * d + i];
       for (size_t i = 0; i < d; i++) pooled[i] = pooled[i] / total_mix;
-      if (m->mix_n[s]) calculate_variance(m, m->mix_var[s][0], pooled);
+      /* The reference reads mixtures_[m][0] even when eliminate() emptied the mixture (:425) — the vector's
+       * storage still holds the last erased entry, so the stale variance slot is recomputed from a 0/0 mean and
+       * becomes NaN.  Reproduced here: mix_var[s][0] keeps the erased entry exactly like the vector's storage. */
+      if (m->mix_cap[s]) calculate_variance(m, m->mix_var[s][0], pooled);
     }
     total_observations += total_mix;
   }

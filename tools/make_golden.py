@@ -1,0 +1,70 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED reference (oracle/_ref, built from /root/reference).
+
+Run in the build container only:  python tools/make_golden.py
+The reference has no golden vectors of its own for this path, so these fixtures are its
+outputs on seeded synthetic inputs: a miniature Trainer::train trajectory per variance-pooling mode.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle.binding import Reference, TABLES  # noqa: E402
+from speechrecognition_b200 import synth  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+TDP = (3.0, 0.0, 30.0)
+DIM = 9
+MIN_OBS = 6
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    rng = np.random.default_rng(20161107)
+    lex = synth.Lexicon()
+    gen = synth.random_model(rng, DIM, lex.num_states, 2, "none")
+    corp = synth.make_corpus(rng, lex, gen, DIM, 10, t_choices=([70, 95, 130], [0.5, 0.3, 0.2]), words_per_utt=(1, 2))
+    x = corp["x"]
+    np.savez_compressed(os.path.join(OUT, "corpus.npz"), x=x, frame_off=corp["frame_off"], automata=corp["automata"],
+                        aut_off=corp["aut_off"], tdp=np.array(TDP), dim=DIM, min_obs=MIN_OBS)
+    for pooling in ("none", "mixture", "global"):
+        R = Reference(DIM, lex.num_states, pooling, True, TDP, lex.silence_state)
+        rec = {}
+        ali = synth.linear_alignment(corp["frame_off"], corp["automata"], corp["aut_off"])
+        rec["ali_linear"] = ali
+        R.accumulate(ali, x, first_pass=True); R.finalize()
+        for k, v in R.tables().items():
+            rec["t0_" + k] = v
+        rec["am0"] = R.am_score(ali, x)
+        R.split(2 * MIN_OBS)
+        for k, v in R.tables().items():
+            rec["tsplit_" + k] = v
+        R.accumulate(ali, x); R.finalize()
+        R.eliminate(MIN_OBS)
+        R.accumulate(ali, x); R.finalize()
+        for k, v in R.tables().items():
+            rec["t1_" + k] = v
+        st, costs = R.align_batch(x, corp["frame_off"], corp["automata"], corp["aut_off"])
+        rec["ali_full"], rec["costs_full"] = st, costs
+        f0, f1 = int(corp["frame_off"][2]), int(corp["frame_off"][3])
+        aut = corp["automata"][corp["aut_off"][2]:corp["aut_off"][3]]
+        for thr, tag in ((40.0, "p40"), (1e300, "pinf")):
+            c, s = R.align_pruned(x[f0:f1], aut, thr)
+            rec["ali_" + tag], rec["cost_" + tag] = s, c
+        sc, am = R.min_score(x[:64])
+        rec["scores64"], rec["argmin64"] = sc, am
+        R.accumulate(st, x)
+        for k, v in R.tables().items():
+            rec["t2_" + k] = v          # accumulators after the E-step on the Viterbi alignment (not finalized)
+        R.finalize()
+        rec["am2"] = R.am_score(st, x)
+        path = os.path.join(OUT, "mix_%s.mix" % pooling)
+        R.write(path)
+        np.savez_compressed(os.path.join(OUT, "trajectory_%s.npz" % pooling), **rec)
+        print(pooling, "densities", R.num_densities(), "am", rec["am0"], rec["am2"])
+
+
+if __name__ == "__main__":
+    main()
