@@ -1,0 +1,364 @@
+// Host-side mirror of the reference's C++ interfaces for the GMM acoustic-model hot path
+// (kkromberg/SpeechRecognition, src/sietill).  Class names, method names, argument meaning and error
+// behaviour follow the reference's headers (cited per class); every compute method forwards to the CUDA
+// path through the C-ABI of include/sietill_b200.h.  There is no CPU implementation of scoring, alignment
+// or accumulation in here: without a B200 those methods fail loudly (std::runtime_error carrying
+// sgmm_last_error).  What stays on the host is what the reference also keeps outside its hot loop: the
+// M-step (finalize / split / eliminate, O(D*d) per iteration) and the byte-compatible file formats.
+//
+// Differences from the reference, all deliberate:
+//   * DensityIdx is 32 bit (reference: 16, Types.hpp:17) so that BASELINE config 5 (288 064 densities) fits;
+//   * Aligner / Trainer gain BATCHED entry points (align_corpus) — one utterance at a time cannot fill a GPU;
+//     the per-utterance methods keep their reference signatures and run as a one-utterance batch;
+//   * Configuration is a plain key/value map (the JSON loader is outside the hot path).
+#pragma once
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include <iosfwd>
+#include <iterator>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "sietill_b200.h"
+
+namespace sietill_b200 {
+
+// ---- Types.hpp:14-40 ------------------------------------------------------------------------------
+typedef size_t SegmentIdx;
+typedef size_t WordIdx;
+typedef uint16_t StateIdx;
+typedef uint32_t DensityIdx;
+
+struct MixtureDensity {
+  DensityIdx mean_idx;
+  DensityIdx var_idx;
+  MixtureDensity(DensityIdx mean_idx, DensityIdx var_idx) : mean_idx(mean_idx), var_idx(var_idx) {}
+};
+typedef std::vector<MixtureDensity> Mixture;
+
+struct AlignmentItem {  // same 8 bytes as sgmm_alignment_item
+  uint16_t count;
+  StateIdx state;
+  float weight;
+  AlignmentItem() : count(0u), state(0u), weight(0.0f) {}
+  AlignmentItem(uint16_t count, StateIdx state, float weight) : count(count), state(state), weight(weight) {}
+};
+static_assert(sizeof(AlignmentItem) == sizeof(sgmm_alignment_item), "AlignmentItem must stay 8 bytes");
+typedef std::vector<AlignmentItem> Alignment;
+typedef std::vector<WordIdx>::const_iterator WordIter;
+
+// ---- Iter.hpp:12-104: a pointer that advances `size` elements per step ----------------------------
+template <typename T>
+class Iter2D {
+ public:
+  typedef std::random_access_iterator_tag iterator_category;
+  typedef T* value_type;
+  typedef ptrdiff_t difference_type;
+  typedef T** pointer;
+  typedef T*& reference;
+
+  size_t size;
+  Iter2D(T* pos, size_t size) : size(size), pos_(pos) {}
+  T* operator*() const { return pos_; }
+  T* operator[](difference_type i) const { return pos_ + i * (difference_type)size; }
+  Iter2D& operator++() { pos_ += size; return *this; }
+  Iter2D operator++(int) { Iter2D r(*this); pos_ += size; return r; }
+  Iter2D& operator--() { pos_ -= size; return *this; }
+  Iter2D& operator+=(difference_type d) { pos_ += d * (difference_type)size; return *this; }
+  Iter2D& operator-=(difference_type d) { pos_ -= d * (difference_type)size; return *this; }
+  Iter2D operator+(difference_type d) const { return Iter2D(pos_ + d * (difference_type)size, size); }
+  Iter2D operator-(difference_type d) const { return Iter2D(pos_ - d * (difference_type)size, size); }
+  difference_type operator-(Iter2D const& o) const { return (pos_ - o.pos_) / (difference_type)size; }
+  bool operator==(Iter2D const& o) const { return pos_ == o.pos_ && size == o.size; }
+  bool operator!=(Iter2D const& o) const { return !(*this == o); }
+  bool operator<(Iter2D const& o) const { return pos_ < o.pos_; }
+
+ private:
+  T* pos_;
+};
+typedef Iter2D<const float> FeatureIter;
+typedef Iter2D<AlignmentItem> AlignmentIter;
+typedef Iter2D<const AlignmentItem> ConstAlignmentIter;
+
+// ---- Config.hpp: key/value lookups with defaults (the reference's Parameter<T>(config) idiom) ------
+class Configuration {
+ public:
+  Configuration() {}
+  Configuration& set(std::string const& key, std::string const& value) { values_[key] = value; return *this; }
+  Configuration& set(std::string const& key, double value);
+  Configuration& set(std::string const& key, unsigned value) { return set(key, std::to_string(value)); }
+  Configuration& set(std::string const& key, bool value) { return set(key, std::string(value ? "true" : "false")); }
+  bool has(std::string const& key) const { return values_.count(key) != 0; }
+  std::string get_string(std::string const& key, std::string const& dflt) const;
+  double get_double(std::string const& key, double dflt) const;     // throws std::runtime_error on a non-number
+  unsigned get_uint(std::string const& key, unsigned dflt) const;
+  bool get_bool(std::string const& key, bool dflt) const;
+
+ private:
+  std::map<std::string, std::string> values_;
+};
+
+// ---- MarkovAutomaton.hpp:17-67 ---------------------------------------------------------------------
+struct MarkovAutomaton {
+  std::vector<StateIdx> states;
+  MarkovAutomaton() {}
+  MarkovAutomaton(StateIdx start, uint16_t num, uint16_t repetitions);
+  StateIdx first_state() const { return states.front(); }
+  StateIdx last_state() const { return states.back(); }
+  size_t num_states() const { return states.size(); }
+  StateIdx max_state() const;
+  StateIdx& operator[](size_t i) { return states[i]; }
+  StateIdx operator[](size_t i) const { return states[i]; }
+  static MarkovAutomaton concat(std::vector<MarkovAutomaton const*> automata);
+};
+
+// ---- Lexicon.hpp:16-33 ------------------------------------------------------------------------------
+class Lexicon {
+ public:
+  WordIdx add_word(std::string const& orth, uint16_t num_states, uint16_t state_repetitions, bool silence = false);
+  MarkovAutomaton const& get_silence_automaton() const { return automata_.at(silence_); }
+  MarkovAutomaton const& get_automaton_for_word(WordIdx w) const { return automata_.at(w); }
+  StateIdx num_states() const { return next_state_; }
+  WordIdx num_words() const { return automata_.size(); }
+  WordIdx silence_idx() const { return silence_; }
+  WordIdx operator[](std::string const& orth) const;
+
+ private:
+  std::vector<std::string> orth_;
+  std::vector<MarkovAutomaton> automata_;
+  WordIdx silence_ = 0;
+  StateIdx next_state_ = 0;
+};
+Lexicon build_sietill_lexicon();   // Lexicon.cpp:70-85: silence (1 state) + 11 German digit words, 106 states
+
+// ---- Corpus.hpp:53-81: the accessors Trainer / Recognizer use, over caller-owned arrays -------------
+class Corpus {
+ public:
+  // features: row-major float[n_frames * dim]; frame_off[U + 1] in FRAMES; words: concatenated word ids,
+  // word_off[U + 1].  Nothing is copied except the two offset tables.
+  Corpus(const float* features, size_t dim, std::vector<size_t> frame_off, std::vector<WordIdx> words,
+         std::vector<size_t> word_off);
+  size_t get_corpus_size() const { return frame_off_.size() - 1; }
+  size_t get_total_frame_count() const { return frame_off_.back(); }
+  size_t get_max_seq_length() const;
+  size_t get_features_per_timeframe() const { return dim_; }
+  std::pair<WordIter, WordIter> get_word_sequence(SegmentIdx s) const;
+  std::pair<FeatureIter, FeatureIter> get_feature_sequence(SegmentIdx s) const;
+  std::pair<FeatureIter, FeatureIter> get_all_features() const;
+  std::pair<size_t, size_t> get_feature_offsets(SegmentIdx s) const;   // in floats, as the reference's
+  std::vector<size_t> const& frame_offsets() const { return frame_off_; }
+
+ private:
+  const float* features_;
+  size_t dim_;
+  std::vector<size_t> frame_off_;
+  std::vector<WordIdx> words_;
+  std::vector<size_t> word_off_;
+};
+
+// ---- TdpModel.hpp:12-30 -----------------------------------------------------------------------------
+class TdpModel {
+ public:
+  const StateIdx silence_state;
+  TdpModel(Configuration const& config, StateIdx silence_state);   // "tdp-loop" / "tdp-forward" / "tdp-skip"
+  double score(StateIdx to, size_t jump) const;                     // TdpModel.cpp:19-29
+  double loop() const { return tdp_loop_; }
+  double forward() const { return tdp_forward_; }
+  double skip() const { return tdp_skip_; }
+
+ private:
+  const double tdp_loop_, tdp_forward_, tdp_skip_;
+};
+
+// ---- FeatureScorer.hpp:12-16 ------------------------------------------------------------------------
+class FeatureScorer {
+ public:
+  virtual ~FeatureScorer() {}
+  virtual void prepare_sequence(FeatureIter const& start, FeatureIter const& end) = 0;
+  virtual double score(FeatureIter const& iter, StateIdx state_idx) const = 0;
+};
+
+// One GPU context (sgmm_ctx) with RAII and exceptions; shared by MixtureModel and Aligner.
+class Device {
+ public:
+  explicit Device(int device_index = 0);
+  ~Device();
+  Device(Device const&) = delete;
+  Device& operator=(Device const&) = delete;
+  sgmm_ctx* ctx() const { return ctx_; }
+  void check(int rc, const char* what) const;   // throws std::runtime_error(what + sgmm_last_error)
+
+ private:
+  sgmm_ctx* ctx_ = nullptr;
+};
+
+// ---- Mixtures.hpp:16-93 -----------------------------------------------------------------------------
+class MixtureModel : public FeatureScorer {
+ public:
+  enum VarianceModel { GLOBAL_POOLING, MIXTURE_POOLING, NO_POOLING };
+
+  const size_t dimension;
+  const VarianceModel var_model;
+
+  // config keys: "load-mixtures-from" (+ "action" == "recognize"), as Mixtures.cpp:158-193; "device" (GPU index).
+  MixtureModel(Configuration const& config, size_t dimension, size_t num_mixtures, VarianceModel var_model,
+               bool max_approx);
+  ~MixtureModel();
+
+  void reset_accumulators();                                             // Mixtures.cpp:237-245
+  // E-step on the GPU (K3 + K4); max_approx == false is not on this path and throws.
+  void accumulate(ConstAlignmentIter alignment_begin, ConstAlignmentIter alignment_end, FeatureIter feature_begin,
+                  FeatureIter feature_end, bool first_pass, bool max_approx = true);
+  void finalize();                                                       // Mixtures.cpp:374-461 (host, f64)
+  void split(size_t min_obs);                                            // Mixtures.cpp:465-543
+  void eliminate(double min_obs);                                        // Mixtures.cpp:547-576
+  size_t num_densities() const;                                          // Mixtures.cpp:580-582
+
+  std::pair<double, DensityIdx> min_score(FeatureIter const& iter, StateIdx mixture_idx) const;  // :696-713
+  void prepare_sequence(FeatureIter const& start, FeatureIter const& end) override;  // scores the whole sequence (K1)
+  double score(FeatureIter const& iter, StateIdx mixture_idx) const override;        // lookup, or a 1-frame K1 call
+
+  void read(std::istream& in);                                           // .mix v2, Mixtures.cpp:748-843
+  void write(std::ostream& out) const;                                   // Mixtures.cpp:845-878
+
+  // ---- additions for the batched path
+  Device& device() const { return *device_; }
+  size_t num_mixtures() const { return mixtures_.size(); }
+  // uploads the parameter tables if they changed since the last upload (sgmm_set_model)
+  void sync_device() const;
+  // sum over the corpus of min_score(x_f, aligned state).first — Trainer::calc_am_score's numerator
+  // (Training.cpp:585-612) as a by-product of the last accumulate() with first_pass == false.
+  double last_score_sum() const { return last_score_sum_; }
+  // the GPU keeps the corpus features resident between calls; identified by (pointer, frame count)
+  void set_corpus_features(FeatureIter begin, FeatureIter end) const;
+  // attach one rank of a multi-GPU job: accumulate() then all-reduces with ONE ncclAllReduce
+  void comm_init(int rank, int world_size, const void* nccl_unique_id, size_t id_bytes);
+
+  // raw tables (tests; reference layout, Mixtures.hpp:72-87)
+  struct Tables {
+    std::vector<double> means, mean_acc, mean_w, mean_wlog, mean_wacc, vars, vars_inv, var_acc, var_wacc, norm;
+    std::vector<uint64_t> mean_refs, var_refs;
+    std::vector<uint32_t> mix_offsets, mean_idx, var_idx;   // mixtures_ flattened, state-major
+  };
+  Tables export_tables() const;
+  void import_tables(Tables const& t);
+
+ private:
+  friend class Aligner;
+  friend class Trainer;
+  void calculate_variance(DensityIdx var_idx, const double* mean);
+  MixtureDensity create_mixture_density(DensityIdx var_index);
+  void mark_dirty() { ++version_; }
+
+  bool max_approx_;
+  std::vector<double> means_, mean_accumulators_, mean_weights_, mean_weights_log_, mean_weight_accumulators_;
+  std::vector<size_t> mean_refs_;
+  std::vector<double> vars_, vars_inv_, var_accumulators_, var_weight_accumulators_;
+  std::vector<size_t> var_refs_;
+  std::vector<double> norm_;
+  std::vector<Mixture> mixtures_;
+  std::vector<MixtureDensity> stale_first_;   // last erased entry of an emptied mixture (see finalize)
+  double minimal_variance_value_;
+
+  std::unique_ptr<Device> device_;
+  uint64_t version_ = 1;
+  mutable uint64_t uploaded_version_ = 0;
+  mutable const float* resident_feat_ = nullptr;
+  mutable size_t resident_frames_ = 0;
+  mutable const AlignmentItem* resident_ali_ = nullptr;   // host range whose content is resident on the GPU
+  mutable size_t resident_ali_frames_ = 0;
+  mutable uint64_t resident_ali_sum_ = 0;                 // checksum of that range when it was made resident
+  double last_score_sum_ = 0.0;
+  // prepare_sequence cache
+  mutable const float* seq_begin_ = nullptr;
+  mutable size_t seq_frames_ = 0;
+  mutable uint64_t seq_version_ = 0;
+  mutable std::vector<double> seq_scores_;
+  mutable std::vector<uint32_t> seq_argmin_;
+  mutable std::unique_ptr<Device> scratch_;          // one-off sequences (per-utterance API)
+  mutable uint64_t scratch_version_ = 0;
+  Device& scratch() const;
+};
+
+// ---- Alignment.hpp:17-66 ----------------------------------------------------------------------------
+class Aligner {
+ public:
+  Aligner(MixtureModel const& mixtures, TdpModel const& tdp_model, size_t max_aligns);
+
+  // Alignment.cpp:50-144; runs as a one-utterance batch on the GPU (K1 gathered + K2).
+  double align_sequence_full(FeatureIter feature_begin, FeatureIter feature_end, MarkovAutomaton const& reference,
+                             AlignmentIter align_begin, AlignmentIter align_end);
+  // Alignment.cpp:149-288.  The GPU path is the exact DP, so only an infinite beam is supported:
+  // pruning_threshold must be >= 1e30 (destination-state TDP convention, "highest state reached" end);
+  // anything smaller throws.
+  double align_sequence_pruned(FeatureIter feature_begin, FeatureIter feature_end, MarkovAutomaton const& reference,
+                               AlignmentIter align_begin, AlignmentIter align_end, double pruning_threshold);
+
+  // Batched: every utterance of the corpus in one call (the loop of Training.cpp:168-183).  `alignment`
+  // covers all frames (num_max_aligns == 1); costs (optional) receives the per-utterance path costs.
+  void align_corpus(Corpus const& corpus, std::vector<MarkovAutomaton> const& automata, Alignment& alignment,
+                    bool destination_tdp = false, std::vector<double>* costs = nullptr);
+
+ private:
+  double align_one(FeatureIter fb, FeatureIter fe, MarkovAutomaton const& ref, AlignmentIter ab, AlignmentIter ae,
+                   int convention);
+  MixtureModel const& mixtures_;
+  TdpModel const& tdp_model_;
+  size_t max_aligns_;
+  const void* corpus_key_ = nullptr;   // corpus whose automata are resident
+};
+
+void write_alignment(std::ostream& out, Alignment const& alignment, size_t max_aligns);   // Alignment.cpp:303-308
+void read_alignment(std::istream& in, Alignment& alignment, size_t& max_aligns);          // Alignment.cpp:310-317
+
+// ---- Training.hpp:17-110 ----------------------------------------------------------------------------
+class Trainer {
+ public:
+  // config keys and defaults as Training.cpp:24-39: "min-obs", "num-splits", "num-aligns", "num-estimates",
+  // "num-max-aligns" (must be 1), "pruning-threshold", "mixture-path", "alignment-path",
+  // "training-stats-path", "realign", "alignment-pruning".
+  Trainer(Configuration const& config, Lexicon const& lexicon, MixtureModel& mixtures, TdpModel const& tdp_model,
+          bool max_approx);
+
+  // Training.cpp:51-235.  `initial` (optional) replaces the reference's energy-based linear segmentation
+  // (Training.cpp:85-99, outside this path — SURVEY.md §8 f3): all frames, one item each.  Without it an
+  // equal-length segmentation over the automaton positions is used.
+  void train(Corpus const& corpus, const Alignment* initial = nullptr);
+  MarkovAutomaton build_segment_automaton(WordIter segment_begin, WordIter segment_end) const;   // :239-253
+  MixtureModel const& get_mixtures() const { return mixtures_; }
+
+  struct StatLine { int split, align, estimate; double am_score; };   // one line of the training-stats file
+  std::vector<StatLine> const& stats() const { return stats_; }
+  Alignment const& alignment() const { return alignment_; }
+  // Timer buckets of Training.cpp:45-49,230-234 (seconds, host wall clock)
+  double align_seconds = 0, estimate_seconds = 0, score_seconds = 0, io_seconds = 0;
+
+ private:
+  double calc_am_score(Corpus const& corpus, Alignment const& alignment);   // Training.cpp:585-612
+  const unsigned min_obs_, num_splits_, num_aligns_, num_estimates_, num_max_aligns_;
+  const double pruning_threshold_;
+  const std::string mixture_path_, alignment_path_, training_stats_path_;
+  const bool max_approx_, realign_, alignment_pruning_;
+  Lexicon const& lexicon_;
+  MixtureModel& mixtures_;
+  TdpModel const& tdp_model_;
+  Aligner aligner_;
+  std::vector<StatLine> stats_;
+  Alignment alignment_;
+};
+
+// 64-bit checksum of an alignment range (guards the "already resident on the GPU" shortcut against the
+// caller editing the host copy in place).
+uint64_t alignment_checksum(const AlignmentItem* items, size_t n);
+
+// Contiguous utterance ranges balanced by frame count: rank r owns utterances
+// [bounds[r], bounds[r + 1]).  Deterministic; every rank computes the same table.
+std::vector<size_t> shard_utterances(std::vector<size_t> const& frame_off, int world_size);
+
+}  // namespace sietill_b200
