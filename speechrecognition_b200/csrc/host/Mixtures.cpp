@@ -186,10 +186,19 @@ void MixtureModel::set_corpus_features(FeatureIter begin, FeatureIter end) const
   if (!device_) fail("built host-only: no GPU context");
   if (begin.size != dimension) fail("feature dimension differs from the model's");
   const size_t n = (size_t)(end - begin);
-  if (*begin == resident_feat_ && n == resident_frames_) return;
+  // identity = (pointer, length, fingerprint of ~2048 sampled words): guards against a recycled address
+  uint64_t print = 0xCBF29CE484222325ull ^ n;
+  {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(*begin);
+    const size_t words = n * dimension, step = words / 2048 + 1;
+    for (size_t i = 0; i < words; i += step) print = (print ^ w[i]) * 0x100000001B3ull;
+    if (words) print = (print ^ w[words - 1]) * 0x100000001B3ull;
+  }
+  if (*begin == resident_feat_ && n == resident_frames_ && print == resident_feat_print_) return;
   device_->check(sgmm_set_features(device_->ctx(), *begin, n, (uint32_t)dimension), "sgmm_set_features");
   resident_feat_ = *begin;
   resident_frames_ = n;
+  resident_feat_print_ = print;
   resident_ali_ = nullptr;   // sgmm_set_features drops the resident alignment
 }
 

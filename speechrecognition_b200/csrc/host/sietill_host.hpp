@@ -271,6 +271,7 @@ class MixtureModel : public FeatureScorer {
   mutable uint64_t uploaded_version_ = 0;
   mutable const float* resident_feat_ = nullptr;
   mutable size_t resident_frames_ = 0;
+  mutable uint64_t resident_feat_print_ = 0;             // sampled fingerprint of the resident feature block
   mutable const AlignmentItem* resident_ali_ = nullptr;   // host range whose content is resident on the GPU
   mutable size_t resident_ali_frames_ = 0;
   mutable uint64_t resident_ali_sum_ = 0;                 // checksum of that range when it was made resident
