@@ -23,9 +23,7 @@ namespace sgmm_tc {
 
 constexpr int BM = 128;        // frames per CTA (TMEM lanes)
 constexpr int BN = 128;        // densities per B stage / MMA N
-constexpr int NSTAGE = 2;
-constexpr int NSLOT = 4;       // TMEM accumulator slots of BN columns
-constexpr int KB = 32;         // K elements per 128-byte swizzle atom
+constexpr int kMaxStage = 4;   // B stages in the TMA ring (the launcher picks what shared memory allows)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -46,11 +44,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+// 3-D tile {8 floats, 128 rows, ksteps} -> shared [kstep][row][8 floats] (one 4 KB SWIZZLE_32B block per k-step)
+__device__ __forceinline__ void tma_load_rows(void* dst, const CUtensorMap* map, int row0, uint64_t* bar) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
           smem_u32(dst)),
-      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      "l"(map), "r"(smem_u32(bar)), "r"(0), "r"(row0), "r"(0)
       : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -80,14 +79,17 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, float (&v)[16]) {
   for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
 
-// Shared-memory matrix descriptor, K-major, SWIZZLE_128B: 8-row groups are 1024 B apart (SBO), LBO unused.
-__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+// Shared-memory matrix descriptor, K-major, SWIZZLE_32B.  One k-step (8 tf32 = 32 bytes) of a 128-row operand
+// is its own 4 KB block [128 rows][32 B]: 8-row groups are 256 B apart (SBO), LBO unused.  K = 2d+1 or d+1 is
+// short and odd-sized here (34 -> 5 k-steps at d = 33), so 32-byte atoms waste no shared memory or L2
+// bandwidth on K padding, which 128-byte atoms (K padded to 64) did.
+__device__ __forceinline__ uint64_t make_desc_sw32(uint32_t saddr) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr & 0x3FFFF) >> 4);          // start address
   d |= (uint64_t)1 << 16;                           // leading byte offset (ignored for swizzled K-major)
-  d |= (uint64_t)(1024 >> 4) << 32;                 // stride byte offset
+  d |= (uint64_t)(256 >> 4) << 32;                  // stride byte offset
   d |= (uint64_t)1 << 46;                           // descriptor version (sm_100)
-  d |= (uint64_t)2 << 61;                           // layout type: SWIZZLE_128B
+  d |= (uint64_t)6 << 61;                           // layout type: SWIZZLE_32B
   return d;
 }
 // Instruction descriptor: D = f32, A = B = tf32, both K-major, M x N.
@@ -128,7 +130,8 @@ __global__ void k_tc_prep(const float* __restrict__ x, uint64_t n_frames, uint32
 
 
 struct TcParams {
-  uint32_t ksteps;             // K steps of 8 actually issued (K used = 8 * ksteps <= KP)
+  uint32_t ksteps;             // K steps of 8 (KP = 8 * ksteps)
+  uint32_t nstage;             // B stages in flight (<= kMaxStage)
   const uint32_t* col_off;     // [n_states + 1] first B row (padded density layout) of every state
   uint64_t n_tasks;
   // gathered mode: task = {utt, t0 (multiple of 128)}
@@ -148,30 +151,37 @@ struct TcParams {
   uint32_t* ci1;
 };
 
-template <int KBLK>
-__global__ void __launch_bounds__(192, 1) k_tc_gemm(const __grid_constant__ CUtensorMap mapAhi,
-                                                    const __grid_constant__ CUtensorMap mapAlo,
-                                                    const __grid_constant__ CUtensorMap mapBhi,
-                                                    const __grid_constant__ CUtensorMap mapBlo, TcParams p) {
+// NHALF frame halves of 128 rows (TMEM lanes) per CTA share every B tile: NHALF = 2 halves the L2 -> shared
+// traffic per flop and gives the tensor pipe two accumulators per B stage.  Warps: 0 = TMA producer, 1 = TMEM
+// allocator + MMA issuer (one lane), 2 .. 2 + 4*NHALF - 1 = epilogue (TMEM lane quarter = warp_id % 4, frame
+// half = (warp_id - 2) / 4).  TMEM: NSLOT accumulator slots x NHALF halves x BN columns = 512 columns.
+template <int NHALF>
+__global__ void __launch_bounds__(64 + 128 * NHALF, 1) k_tc_gemm(const __grid_constant__ CUtensorMap mapAhi,
+                                                                  const __grid_constant__ CUtensorMap mapAlo,
+                                                                  const __grid_constant__ CUtensorMap mapBhi,
+                                                                  const __grid_constant__ CUtensorMap mapBlo, TcParams p) {
   extern __shared__ unsigned char smem_raw[];
-  constexpr uint32_t ATOM = 128 * 128;                 // one 128-row x 128-byte swizzled block
-  constexpr uint32_t A_BYTES = KBLK * ATOM;            // per hi / lo
-  constexpr uint32_t B_STAGE = 2 * KBLK * ATOM;        // hi + lo
+  constexpr uint32_t NSLOT = 4 / NHALF;                // accumulator slots (of NHALF x BN columns)
+  constexpr uint32_t KSTEP_BYTES = 128 * 32;           // one k-step of a 128-row operand
+  const uint32_t op_bytes = p.ksteps * KSTEP_BYTES;    // one 128-row operand (hi or lo)
+  const uint32_t a_bytes = 2 * NHALF * op_bytes;       // hi + lo of every half
+  const uint32_t b_stage = 2 * op_bytes;               // hi + lo
+  const uint32_t nstage = p.nstage;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* smem = smem_raw + (base - smem_u32(smem_raw));
-  unsigned char* sAhi = smem;
-  unsigned char* sAlo = smem + A_BYTES;
-  unsigned char* sB = smem + 2 * A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + NSTAGE * B_STAGE);
+  unsigned char* sA = smem;                            // [half][hi, lo][kstep][128 rows][32 B]
+  unsigned char* sB = smem + a_bytes;                  // [stage][hi, lo][kstep][128 rows][32 B]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + nstage * b_stage);
   uint64_t* a_full = bars;
   uint64_t* full = bars + 1;
-  uint64_t* empty = full + NSTAGE;
-  uint64_t* tfull = empty + NSTAGE;
+  uint64_t* empty = full + kMaxStage;
+  uint64_t* tfull = empty + kMaxStage;
   uint64_t* tempty = tfull + NSLOT;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + NSLOT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint64_t task = blockIdx.x;
+  constexpr uint32_t ROWS = BM * NHALF;
 
   // ---- task decode (uniform over the CTA)
   uint64_t row0;        // first A row (absolute frame index)
@@ -179,9 +189,9 @@ __global__ void __launch_bounds__(192, 1) k_tc_gemm(const __grid_constant__ CUte
   const uint32_t* ulist = nullptr;
   uint64_t out_base;
   if (p.dense) {
-    const uint64_t r0 = task * BM;
+    const uint64_t r0 = task * ROWS;
     row0 = p.f0 + r0;
-    nvalid = (uint32_t)min((uint64_t)BM, p.nframes - r0);
+    nvalid = (uint32_t)min((uint64_t)ROWS, p.nframes - r0);
     nu = p.n_states;
     out_stride = p.n_states;
     out_base = r0 * p.n_states;
@@ -190,20 +200,21 @@ __global__ void __launch_bounds__(192, 1) k_tc_gemm(const __grid_constant__ CUte
     const uint64_t uf0 = p.frame_off[t.x];
     const uint32_t T = (uint32_t)(p.frame_off[t.x + 1] - uf0);
     row0 = uf0 + t.y;
-    nvalid = min((uint32_t)BM, T - t.y);
+    nvalid = min(ROWS, T - t.y);
     ulist = p.uniq + p.uniq_off[t.x];
     nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
     out_stride = p.nuniq_pad[t.x];
     out_base = p.E_off[t.x] + (uint64_t)t.y * out_stride;
   }
+  const uint32_t nh = (NHALF == 2 && nvalid > (uint32_t)BM) ? 2u : 1u;   // halves that hold valid frames
 
   // ---- one-time setup
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAhi));
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBhi));
     mbar_init(a_full, 1);
-    for (int i = 0; i < NSTAGE; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < NSLOT; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    for (uint32_t i = 0; i < nstage; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (uint32_t i = 0; i < NSLOT; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4 * nh); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -218,24 +229,22 @@ __global__ void __launch_bounds__(192, 1) k_tc_gemm(const __grid_constant__ CUte
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      mbar_expect_tx(a_full, 2 * A_BYTES);
-      for (int kb = 0; kb < KBLK; kb++) {
-        tma_load_2d(sAhi + kb * ATOM, &mapAhi, kb * KB, (int)row0, a_full);
-        tma_load_2d(sAlo + kb * ATOM, &mapAlo, kb * KB, (int)row0, a_full);
+      mbar_expect_tx(a_full, 2 * nh * op_bytes);
+      for (uint32_t h = 0; h < nh; h++) {
+        tma_load_rows(sA + (2 * h) * op_bytes, &mapAhi, (int)(row0 + h * BM), a_full);
+        tma_load_rows(sA + (2 * h + 1) * op_bytes, &mapAlo, (int)(row0 + h * BM), a_full);
       }
       uint32_t it = 0;
       for (uint32_t j = 0; j < nu; j++) {
         const uint32_t s = ulist ? ulist[j] : j;
         const uint32_t c0 = p.col_off[s], nc = p.col_off[s + 1] - c0;
         for (uint32_t n0 = 0; n0 < nc; n0 += BN, it++) {
-          const uint32_t stage = it % NSTAGE;
-          mbar_wait(&empty[stage], ((it / NSTAGE) & 1) ^ 1);
-          mbar_expect_tx(&full[stage], B_STAGE);
-          unsigned char* dst = sB + stage * B_STAGE;
-          for (int kb = 0; kb < KBLK; kb++) {
-            tma_load_2d(dst + kb * ATOM, &mapBhi, kb * KB, (int)(c0 + n0), &full[stage]);
-            tma_load_2d(dst + (KBLK + kb) * ATOM, &mapBlo, kb * KB, (int)(c0 + n0), &full[stage]);
-          }
+          const uint32_t stage = it % nstage;
+          mbar_wait(&empty[stage], ((it / nstage) & 1) ^ 1);
+          mbar_expect_tx(&full[stage], b_stage);
+          unsigned char* dst = sB + stage * b_stage;
+          tma_load_rows(dst, &mapBhi, (int)(c0 + n0), &full[stage]);
+          tma_load_rows(dst + op_bytes, &mapBlo, (int)(c0 + n0), &full[stage]);
         }
       }
     }
@@ -249,64 +258,69 @@ __global__ void __launch_bounds__(192, 1) k_tc_gemm(const __grid_constant__ CUte
         const uint32_t nc = p.col_off[s + 1] - p.col_off[s];
         for (uint32_t n0 = 0; n0 < nc; n0 += BN, it++) {
           const uint32_t N = min((uint32_t)BN, nc - n0);
-          const uint32_t stage = it % NSTAGE, slot = it % NSLOT;
+          const uint32_t stage = it % nstage, slot = it % NSLOT;
           mbar_wait(&tempty[slot], ((it / NSLOT) & 1) ^ 1);
-          mbar_wait(&full[stage], (it / NSTAGE) & 1);
+          mbar_wait(&full[stage], (it / nstage) & 1);
           tc_fence_after();
-          const uint32_t d = tmem_base + slot * BN;
           const uint32_t idesc = make_idesc_tf32(BM, N);
-          const uint32_t bhi = smem_u32(sB + stage * B_STAGE), blo = bhi + KBLK * ATOM;
-          const uint32_t ahi = smem_u32(sAhi), alo = smem_u32(sAlo);
-          uint32_t acc = 0;
+          const uint32_t bhi = smem_u32(sB + stage * b_stage), blo = bhi + op_bytes;
+          for (uint32_t h = 0; h < nh; h++) {
+            const uint32_t d = tmem_base + (slot * NHALF + h) * BN;
+            const uint32_t ahi = smem_u32(sA + (2 * h) * op_bytes), alo = ahi + op_bytes;
+            uint32_t acc = 0;
 #pragma unroll 1
-          for (int pass = 0; pass < 3; pass++) {
-            const uint32_t a0 = pass == 1 ? alo : ahi;
-            const uint32_t b0 = pass == 2 ? blo : bhi;
-            for (uint32_t kk = 0; kk < p.ksteps; kk++) {
-              const uint32_t off = (kk >> 2) * ATOM + (kk & 3) * 32;
-              tc_mma_tf32(d, make_desc_sw128(a0 + off), make_desc_sw128(b0 + off), idesc, acc);
-              acc = 1;
+            for (int pass = 0; pass < 3; pass++) {
+              const uint32_t a0 = pass == 1 ? alo : ahi;
+              const uint32_t b0 = pass == 2 ? blo : bhi;
+              for (uint32_t kk = 0; kk < p.ksteps; kk++) {
+                tc_mma_tf32(d, make_desc_sw32(a0 + kk * KSTEP_BYTES), make_desc_sw32(b0 + kk * KSTEP_BYTES), idesc, acc);
+                acc = 1;
+              }
             }
           }
           tc_commit(&empty[stage]);   // smem stage reusable once these MMAs have read it
-          tc_commit(&tfull[slot]);    // accumulator slot complete
+          tc_commit(&tfull[slot]);    // accumulator slot complete (all halves)
         }
       }
     }
   } else {
     // ===== epilogue: per-state top-2 over the accumulator columns =====
     const uint32_t quarter = warp & 3;
-    const uint32_t row = quarter * 32 + lane;
-    const uint32_t tlane = tmem_base + ((quarter * 32) << 16);
-    uint32_t it = 0;
-    for (uint32_t j = 0; j < nu; j++) {
-      const uint32_t s = ulist ? ulist[j] : j;
-      const uint32_t nc = p.col_off[s + 1] - p.col_off[s];
-      float b1 = INFINITY, b2 = INFINITY;
-      uint32_t i1 = 0;
-      for (uint32_t n0 = 0; n0 < nc; n0 += BN, it++) {
-        const uint32_t N = min((uint32_t)BN, nc - n0);
-        const uint32_t slot = it % NSLOT;
-        mbar_wait(&tfull[slot], (it / NSLOT) & 1);
-        tc_fence_after();
-        for (uint32_t cc = 0; cc < N; cc += 16) {
-          float v[16];
-          tc_ld16(tlane + slot * BN + cc, v);
+    const uint32_t half = (uint32_t)(warp - 2) >> 2;
+    if (half < nh) {
+      const uint32_t row = half * BM + quarter * 32 + lane;
+      const uint32_t tlane = tmem_base + ((quarter * 32) << 16);
+      uint32_t it = 0;
+      for (uint32_t j = 0; j < nu; j++) {
+        const uint32_t s = ulist ? ulist[j] : j;
+        const uint32_t nc = p.col_off[s + 1] - p.col_off[s];
+        float b1 = INFINITY, b2 = INFINITY;
+        uint32_t i1 = 0;
+        for (uint32_t n0 = 0; n0 < nc; n0 += BN, it++) {
+          const uint32_t N = min((uint32_t)BN, nc - n0);
+          const uint32_t slot = it % NSLOT;
+          mbar_wait(&tfull[slot], (it / NSLOT) & 1);
+          tc_fence_after();
+          const uint32_t tcol = tlane + (slot * NHALF + half) * BN;
+          for (uint32_t cc = 0; cc < N; cc += 16) {
+            float v[16];
+            tc_ld16(tcol + cc, v);
 #pragma unroll
-          for (int e = 0; e < 16; e++) {
-            b2 = fminf(b2, fmaxf(b1, v[e]));
-            if (v[e] < b1) { b1 = v[e]; i1 = n0 + cc + e; }
+            for (int e = 0; e < 16; e++) {
+              b2 = fminf(b2, fmaxf(b1, v[e]));
+              if (v[e] < b1) { b1 = v[e]; i1 = n0 + cc + e; }
+            }
           }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[slot]);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[slot]);
-      }
-      if (row < nvalid) {
-        const uint64_t o = out_base + (uint64_t)row * out_stride + j;
-        p.cb1[o] = b1;
-        p.cb2[o] = b2;
-        p.ci1[o] = i1;
+        if (row < nvalid) {
+          const uint64_t o = out_base + (uint64_t)row * out_stride + j;
+          p.cb1[o] = b1;
+          p.cb2[o] = b2;
+          p.ci1[o] = i1;
+        }
       }
     }
   }
@@ -397,7 +411,7 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
         if (sc < best) { best = sc; bk = k - k0; }
       }
     } else {
-      const double sc = sgmm_exact_score(p.m, p.x + frame * p.m.dim, k0 + i1);
+      const double sc = sgmm_exact_score_rm(p.m, p.x + frame * p.m.dim, k0 + i1);
       if (sc < best) { best = sc; bk = i1; }
     }
   }
@@ -462,19 +476,27 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// 2-D f32 tensor [rows][KP] (KP innermost), box = 128 rows x 32 columns, 128-byte swizzle
-int make_map(sgmm_ctx* c, CUtensorMap* map, const float* base, uint64_t rows, uint32_t KP) {
+// f32 matrix [rows][KP] (KP = 8 * ksteps innermost) seen as the 3-D tensor {8, rows, ksteps}: one box =
+// 128 rows x all k-steps, delivered as [kstep][row][8 floats] with the 32-byte swizzle the MMA descriptors name.
+int make_map(sgmm_ctx* c, CUtensorMap* map, const float* base, uint64_t rows, uint32_t ksteps) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) SGMM_FAIL(c, "cuTensorMapEncodeTiled is not available from the driver");
-  cuuint64_t dims[2] = {KP, rows};
-  cuuint64_t strides[1] = {(cuuint64_t)KP * sizeof(float)};
-  cuuint32_t box[2] = {32, 128};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+  const uint32_t KP = 8 * ksteps;
+  cuuint64_t dims[3] = {8, rows, ksteps};
+  cuuint64_t strides[2] = {(cuuint64_t)KP * sizeof(float), 8 * sizeof(float)};
+  cuuint32_t box[3] = {8, 128, ksteps};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) SGMM_FAIL(c, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
   return 0;
+}
+
+// shared-memory plan: A = 2 * NHALF operands, each B stage = 2 operands of ksteps * 4 KB
+constexpr size_t kSmemLimit = 227 * 1024;
+size_t tc_smem(uint32_t ksteps, int nhalf, int nstage) {
+  return 1024 + (size_t)(2 * nhalf + 2 * nstage) * ksteps * 4096 + 256;
 }
 
 }  // namespace
@@ -483,8 +505,12 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
                             uint32_t* d_argmin) {
   using namespace sgmm_tc;
   if (!c->tc_ok) SGMM_FAIL(c, "tensor-core scorer not available for this model shape");
-  const uint32_t KP = c->tc_KP;
-  const int kblk = KP / 32;
+  const uint32_t KP = c->tc_KP, ks = c->tc_ksteps;
+  // two frame halves per CTA when at least two B stages still fit next to them
+  int nhalf = (c->tc_halves == 1 || tc_smem(ks, 2, 2) > kSmemLimit) ? 1 : 2;
+  int nstage = 1;
+  while (nstage < sgmm_tc::kMaxStage && tc_smem(ks, nhalf, nstage + 1) <= kSmemLimit) nstage++;
+  const uint32_t rows_per_task = 128u * nhalf;
   // A operand (once per feature upload / model shape)
   if (!c->tc_A_valid) {
     SGMM_CHECK(c, c->d_Ahi.reserve((size_t)c->n_frames * KP));
@@ -497,7 +523,8 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     c->tc_A_valid = true;
   }
   const uint64_t n_cells = dense ? dense_nframes * c->n_states : c->E_elems;
-  const uint64_t n_tasks = dense ? (dense_nframes + BM - 1) / BM : c->n_tasks128;
+  const uint64_t n_tasks = dense ? (dense_nframes + rows_per_task - 1) / rows_per_task
+                                 : (nhalf == 2 ? c->n_tasks256 : c->n_tasks128);
   if (n_tasks == 0) return 0;
   SGMM_CHECK(c, c->d_cb1.reserve(n_cells)); SGMM_CHECK(c, c->d_cb2.reserve(n_cells));
   SGMM_CHECK(c, c->d_ci1.reserve(n_cells));
@@ -507,26 +534,24 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   SGMM_CHECK(c, cudaMemsetAsync(c->d_rescan.p, 0, sizeof(unsigned long long), c->stream));
 
   CUtensorMap mAhi, mAlo, mBhi, mBlo;
-  if (make_map(c, &mAhi, c->d_Ahi.p, c->n_frames, KP) || make_map(c, &mAlo, c->d_Alo.p, c->n_frames, KP) ||
-      make_map(c, &mBhi, c->d_Bhi.p, c->tc_Dpad, KP) || make_map(c, &mBlo, c->d_Blo.p, c->tc_Dpad, KP))
+  if (make_map(c, &mAhi, c->d_Ahi.p, c->n_frames, ks) || make_map(c, &mAlo, c->d_Alo.p, c->n_frames, ks) ||
+      make_map(c, &mBhi, c->d_Bhi.p, c->tc_Dpad, ks) || make_map(c, &mBlo, c->d_Blo.p, c->tc_Dpad, ks))
     return 1;
 
   TcParams p{};
-  p.ksteps = c->tc_ksteps; p.col_off = c->d_col_off.p; p.n_tasks = n_tasks;
-  p.tasks = c->d_tasks128.p; p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
+  p.ksteps = ks; p.nstage = (uint32_t)nstage; p.col_off = c->d_col_off.p; p.n_tasks = n_tasks;
+  p.tasks = nhalf == 2 ? c->d_tasks256.p : c->d_tasks128.p; p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
   p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cb1 = c->d_cb1.p; p.cb2 = c->d_cb2.p; p.ci1 = c->d_ci1.p;
-  const size_t smem = 1024 + (size_t)(2 + 2 * NSTAGE) * kblk * 16384 + 256;
+  const size_t smem = tc_smem(ks, nhalf, nstage);
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER], c->stream);
-  if (kblk == 1) {
+  if (nhalf == 2) {
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_tc_gemm<2><<<(unsigned)n_tasks, 320, smem, c->stream>>>(mAhi, mAlo, mBhi, mBlo, p);
+  } else {
     SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_tc_gemm<1><<<(unsigned)n_tasks, 192, smem, c->stream>>>(mAhi, mAlo, mBhi, mBlo, p);
-  } else if (kblk == 2) {
-    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_tc_gemm<2><<<(unsigned)n_tasks, 192, smem, c->stream>>>(mAhi, mAlo, mBhi, mBlo, p);
-  } else {
-    SGMM_FAIL(c, "tensor-core scorer: K too large for the shared-memory plan");
   }
   SGMM_LAUNCH_CHECK(c);
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER + 1], c->stream);
@@ -535,6 +560,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   RefineParams r{};
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
   r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;
+  r.m.meanR = c->d_meanR.p; r.m.invU = c->d_invU.p; r.m.var_of = c->d_var_of.p; r.m.dimP = c->dimP;
   r.state_off = c->d_state_off.p; r.x = c->d_x.p; r.cb1 = c->d_cb1.p; r.cb2 = c->d_cb2.p; r.ci1 = c->d_ci1.p;
   r.xnorm = c->d_xnorm.p; r.sguard = c->d_sguard_tc.p; r.eps = c->tc_eps; r.n_cells = n_cells;
   r.dense = dense ? 1 : 0; r.f0 = dense_f0; r.n_states = c->n_states; r.n_utts = c->n_utts;

@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstring>
 #include <map>
+#include <string>
 
 #include "sgmm_internal.cuh"
 
@@ -81,11 +82,12 @@ void sgmm_destroy(sgmm_ctx* c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   c->d_meanT.release(); c->d_invT.release(); c->d_mean_tail.release(); c->d_inv_tail.release();
+  c->d_meanR.release(); c->d_invU.release(); c->d_var_of.release();
   c->d_norm.release(); c->d_logw.release(); c->d_state_off.release(); c->d_x.release();
   c->d_frame_off.release(); c->d_E_off.release(); c->d_aut.release(); c->d_aut_off.release();
   c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
   c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_h32.release(); c->d_c32.release();
-  c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release(); c->d_Amin.release(); c->d_fcol.release();
+  c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release(); c->d_tasks256.release(); c->d_Amin.release(); c->d_fcol.release();
   c->d_Bhi.release(); c->d_Blo.release(); c->d_Ahi.release(); c->d_Alo.release(); c->d_cb1.release(); c->d_cb2.release();
   c->d_xnorm.release(); c->d_sguard_tc.release(); c->d_col_off.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
@@ -134,6 +136,32 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
       upload(c, c->d_norm, norm, (size_t)D) || upload(c, c->d_logw, log_weight, (size_t)D) ||
       upload(c, c->d_state_off, state_off, (size_t)n_states + 1))
     return 1;
+  // row-major twins for the refinement kernels: padded mean rows, distinct variance rows
+  {
+    const uint32_t dimP = (dim + 1) & ~1u;
+    std::vector<double> mR((size_t)D * dimP, 0.0), vU;
+    std::vector<uint32_t> var_of(D);
+    std::map<std::string, uint32_t> seen;
+    for (uint32_t j = 0; j < D; j++) {
+      memcpy(&mR[(size_t)j * dimP], mean + (size_t)j * dim, dim * sizeof(double));
+      const double* iv = inv_var + (size_t)j * dim;
+      // consecutive densities of a pooled state share the row: test the previous one before hashing
+      if (j > 0 && memcmp(iv, inv_var + (size_t)(j - 1) * dim, dim * sizeof(double)) == 0) { var_of[j] = var_of[j - 1]; continue; }
+      std::string key(reinterpret_cast<const char*>(iv), dim * sizeof(double));
+      auto it = seen.find(key);
+      if (it == seen.end()) {
+        it = seen.emplace(std::move(key), (uint32_t)(vU.size() / dimP)).first;
+        vU.resize(vU.size() + dimP, 0.0);
+        memcpy(&vU[(size_t)it->second * dimP], iv, dim * sizeof(double));
+      }
+      var_of[j] = it->second;
+    }
+    if (upload(c, c->d_meanR, mR.data(), mR.size()) || upload(c, c->d_invU, vU.data(), vU.size()) ||
+        upload(c, c->d_var_of, var_of.data(), var_of.size()))
+      return 1;
+    SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+    c->dimP = dimP; c->n_var_rows = (uint32_t)(vU.size() / dimP);
+  }
   // f32 tables for the FFMA scorer (k_score_ffma.cu): mean, h = inv_var / 2, c = norm - log w, and the
   // per-state constants of the certified error bound.
   const uint32_t dv4 = dim <= 28 ? 7 : dim <= 36 ? 9 : dim <= 48 ? 12 : dim <= 64 ? 16 : 0;
@@ -175,8 +203,8 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
       for (uint32_t j = state_off[s] + 1; j < state_off[s + 1] && pooled; j++)
         pooled = memcmp(inv_var + (size_t)j * dim, inv_var + (size_t)state_off[s] * dim, dim * sizeof(double)) == 0;
     const uint32_t Kused = pooled ? dim + 1 : 2 * dim + 1;
-    const uint32_t KP = (Kused + 31) / 32 * 32;
-    c->tc_ok = KP <= 64;
+    const uint32_t KP = (Kused + 7) / 8 * 8;     // whole k-steps of 8 (32-byte swizzle atoms: no further padding)
+    c->tc_ok = KP / 8 <= 13;                     // A (2 operands) + 2 B stages of ksteps * 4 KB fit 227 KB
     if (c->tc_ok) {
       const uint32_t nsq = pooled ? 0 : dim;
       std::vector<uint32_t> col_off(n_states + 1, 0);
@@ -272,7 +300,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   std::vector<uint32_t> uniq, uniq_off(U + 1, 0), ncol(U);
   std::vector<uint16_t> p2u(aut_off[U]);
   std::vector<uint64_t> E_off(U + 1, 0);
-  std::vector<uint4> tasks, tasks64, tasks128;
+  std::vector<uint4> tasks, tasks64, tasks128, tasks256;
   std::map<std::pair<int, size_t>, ViterbiClass> classes;
   uint32_t max_state = 0;
   for (uint32_t u = 0; u < U; u++) {
@@ -297,6 +325,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     for (uint32_t t0 = 0; t0 < T; t0 += 32) tasks.push_back(make_uint4(u, t0, 0, 0));
     for (uint32_t t0 = 0; t0 < T; t0 += 64) tasks64.push_back(make_uint4(u, t0, 0, 0));
     for (uint32_t t0 = 0; t0 < T; t0 += 128) tasks128.push_back(make_uint4(u, t0, 0, 0));
+    for (uint32_t t0 = 0; t0 < T; t0 += 256) tasks256.push_back(make_uint4(u, t0, 0, 0));
     int C = 0;
     for (int cc : kViterbiC) if ((uint32_t)cc * 32 >= S) { C = cc; break; }
     size_t sm = viterbi_smem(T, S, ncol[u], C);
@@ -324,11 +353,12 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       upload(c, c->d_uniq_off, uniq_off.data(), uniq_off.size()) || upload(c, c->d_nuniq_pad, ncol.data(), ncol.size()) ||
       upload(c, c->d_pos2uniq, p2u.data(), p2u.size()) || upload(c, c->d_E_off, E_off.data(), E_off.size()) ||
       upload(c, c->d_tasks, tasks.data(), tasks.size()) || upload(c, c->d_tasks64, tasks64.data(), tasks64.size()) ||
-      upload(c, c->d_tasks128, tasks128.data(), tasks128.size()))
+      upload(c, c->d_tasks128, tasks128.data(), tasks128.size()) ||
+      upload(c, c->d_tasks256, tasks256.data(), tasks256.size()))
     return 1;
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->max_aut_state = max_state;
-  c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->n_tasks128 = tasks128.size(); c->E_elems = E_off[U];
+  c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->n_tasks128 = tasks128.size(); c->n_tasks256 = tasks256.size(); c->E_elems = E_off[U];
   c->h_frame_off.assign(frame_off, frame_off + U + 1);
   c->h_aut_off.assign(aut_off, aut_off + U + 1);
   return 0;
@@ -423,6 +453,11 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
     return 0;
   }
   if (!strcmp(key, "rescore_cache")) { c->use_cache = value != 0; return 0; }
+  if (!strcmp(key, "tc_halves")) {
+    if (value < 0 || value > 2) SGMM_FAIL(c, "set_option: tc_halves must be 0 (auto), 1 or 2");
+    c->tc_halves = (int)value;
+    return 0;
+  }
   SGMM_FAIL(c, std::string("set_option: unknown key ") + key);
 }
 

@@ -54,6 +54,11 @@ struct sgmm_ctx {
   std::vector<uint32_t> h_state_off;
   DevBuf<double2> d_meanT, d_invT;
   DevBuf<double> d_mean_tail, d_inv_tail, d_norm, d_logw;
+  // row-major copies for one-thread-per-cell refinement: meanR[D][dimP] (dimP = dim rounded up to 2, rows 16-byte
+  // aligned), the DISTINCT variance rows invU[V][dimP] and var_of[D] (pooled models: V = n_states or 1)
+  uint32_t dimP = 0, n_var_rows = 0;
+  DevBuf<double> d_meanR, d_invU;
+  DevBuf<uint32_t> d_var_of;
   DevBuf<uint32_t> d_state_off;
   // f32 tables of the FFMA / tensor scorers: [D][4*dv4] mean and h = 1/(2 var), c = norm - log w, per-state guard constants
   uint32_t dv4 = 0;
@@ -85,8 +90,9 @@ struct sgmm_ctx {
   DevBuf<uint64_t> d_frame_off, d_E_off;
   DevBuf<uint32_t> d_aut, d_aut_off, d_uniq, d_uniq_off, d_nuniq_pad;
   DevBuf<uint16_t> d_pos2uniq;
-  DevBuf<uint4> d_tasks128;
-  uint64_t n_tasks128 = 0;
+  DevBuf<uint4> d_tasks128, d_tasks256;
+  uint64_t n_tasks128 = 0, n_tasks256 = 0;
+  int tc_halves = 0;               // option "tc_halves": 0 auto, 1 / 2 = frame halves (128 rows each) per GEMM CTA
   DevBuf<uint4> d_tasks, d_tasks64;   // emission warp-tasks {utt, t0, 0, 0}: 32-frame and 64-frame granules
   uint64_t n_tasks = 0, n_tasks64 = 0, E_elems = 0;
   DevBuf<double> d_E;             // ragged emission matrix, utterance u: [T_u][nuniq_pad_u]
@@ -170,6 +176,10 @@ struct ExactTables {
   const double* norm;
   const double* logw;
   uint32_t dim, npair, Dtot;
+  const double* meanR;     // row-major twins (see sgmm_ctx)
+  const double* invU;
+  const uint32_t* var_of;
+  uint32_t dimP;
 };
 #ifdef __CUDACC__
 __device__ __forceinline__ double sgmm_exact_score(const ExactTables& m, const float* __restrict__ xf, uint32_t k) {
@@ -189,6 +199,31 @@ __device__ __forceinline__ double sgmm_exact_score(const ExactTables& m, const f
   if (m.dim & 1) {
     const double c = __dsub_rn((double)__ldg(xf + m.dim - 1), __ldg(m.mean_tail + k));
     dist = __dadd_rn(dist, __dmul_rn(__dmul_rn(c, c), __ldg(m.inv_tail + k)));
+  }
+  const double s = __dadd_rn(__ldg(m.norm + k), __dmul_rn(dist, 0.5));
+  return __dsub_rn(s, __ldg(m.logw + k));
+}
+// Same value, same operation order, from the row-major tables: one thread walks ONE density row (contiguous
+// 16-byte loads; the variance row is shared by every density of a pooled state and stays in L1).
+__device__ __forceinline__ double sgmm_exact_score_rm(const ExactTables& m, const float* __restrict__ xf, uint32_t k) {
+  const uint32_t v = __ldg(m.var_of + k);
+  const double2* mp = reinterpret_cast<const double2*>(m.meanR + (size_t)k * m.dimP);
+  const double2* vp = reinterpret_cast<const double2*>(m.invU + (size_t)v * m.dimP);
+  double l0 = 0.0, l1 = 0.0;
+  for (uint32_t ip = 0; ip < m.npair; ip++) {
+    const double2 mu = __ldg(mp + ip), iv = __ldg(vp + ip);
+    double a = __dsub_rn((double)__ldg(xf + 2 * ip), mu.x);
+    double b = __dsub_rn((double)__ldg(xf + 2 * ip + 1), mu.y);
+    a = __dmul_rn(a, a); b = __dmul_rn(b, b);
+    a = __dmul_rn(a, iv.x); b = __dmul_rn(b, iv.y);
+    l0 = __dadd_rn(l0, a); l1 = __dadd_rn(l1, b);
+  }
+  double dist = __dadd_rn(l0, l1);
+  if (m.dim & 1) {
+    const double mu = __ldg(m.meanR + (size_t)k * m.dimP + m.dim - 1);
+    const double iv = __ldg(m.invU + (size_t)v * m.dimP + m.dim - 1);
+    const double c = __dsub_rn((double)__ldg(xf + m.dim - 1), mu);
+    dist = __dadd_rn(dist, __dmul_rn(__dmul_rn(c, c), iv));
   }
   const double s = __dadd_rn(__ldg(m.norm + k), __dmul_rn(dist, 0.5));
   return __dsub_rn(s, __ldg(m.logw + k));

@@ -197,8 +197,10 @@ def test_ffma_scorer_ties_and_near_ties():
     ctx.close()
 
 
-@pytest.mark.parametrize("dim,nd,pooling", [(33, 200, "mixture"), (25, 40, "none"), (33, 256, "global"), (12, 17, "none")])
-def test_tensor_core_scorer_exact(dim, nd, pooling):
+@pytest.mark.parametrize("halves", [1, 2])
+@pytest.mark.parametrize("dim,nd,pooling", [(33, 200, "mixture"), (25, 40, "none"), (33, 256, "global"), (12, 17, "none"),
+                                            (48, 64, "mixture"), (48, 30, "none")])
+def test_tensor_core_scorer_exact(dim, nd, pooling, halves):
     """tcgen05 3xTF32 GEMM + certified refinement: dense scores/argmins and batched alignments bit-identical to
     the oracle, in the pooled (K = d+1) and the full (K = 2d+1) operand forms, with ragged state sizes."""
     from oracle.binding import Oracle
@@ -222,6 +224,7 @@ def test_tensor_core_scorer_exact(dim, nd, pooling):
     ctx.set_model_tables(dim, t); ctx.set_features(corp["x"])
     ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"]); ctx.set_tdp(*tdp, lex.silence_state)
     ctx.set_option("scorer", 3)
+    ctx.set_option("tc_halves", halves)           # 128 or 256 frames per GEMM CTA
     assert ctx.get_counter("scorer") == 3
     n = 300
     want_s, want_a = O.min_score(corp["x"][:n])
