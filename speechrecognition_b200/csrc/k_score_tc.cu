@@ -2,19 +2,27 @@
 //     [frames x K] . [K x densities],   K = 2d+1  (x^2 | x | 1)  or  d+1 (x | 1) when variances are pooled
 // per state (the x^2 block is then common to all densities of a state and cannot change the argmin),
 // on the 5th-generation tensor cores: tcgen05.mma kind::tf32 with error-compensated 3xTF32 operands
-// (A = Ahi + Alo, B = Bhi + Blo; D = Ahi.Bhi + Alo.Bhi + Ahi.Blo accumulated in fp32 in TMEM), operands staged in
-// shared memory by TMA (SWIZZLE_128B, K-major), accumulators in TMEM, per-state top-2 (min, argmin,
-// second min) fused into the tcgen05.ld epilogue.
+// (A = Ahi + Alo, B = Bhi + Blo; D = Ahi.Bhi + Alo.Bhi + Ahi.Blo accumulated in fp32 in TMEM).
 //
-// Like the FFMA scorer this kernel is a FILTER: its f32 top-2 go to k_refine (below), which certifies the
-// argmin against a rigorous error bound and evaluates the winner's score in f64 in the reference's exact
-// operation order (Mixtures.cpp:645-713) — or rescans the state in f64 when the gap is inside the bound.
-// Results are therefore bit-identical to the reference; the tensor cores only decide where f64 work goes.
+// What shapes the kernel is that K is SHORT (5 k-steps of 8 at d = 33 pooled): an MMA of 128 x 128 x 8 runs 64
+// cycles and, with both operands in shared memory, reads 8 KB for it = the whole 128 B/cycle of the SM's shared
+// memory, leaving nothing for the TMA writes that refill the B ring (measured: loads and MMAs serialised).  So
+//   * A (the CTA's frames, reused by every tile) lives in TENSOR MEMORY: written once with tcgen05.st, read by
+//     tcgen05.mma in its A-from-TMEM form; shared memory only carries B (64 B/cycle of reads);
+//   * one CTA owns 256 frames = two halves of 128 TMEM lanes that share every B tile (halves the L2 -> shared
+//     traffic per flop); the two halves' accumulators are each other's double buffer: while the tensor pipe
+//     works on one half, the epilogue warps of the other half reduce theirs;
+//   * B tiles are pre-tiled and pre-swizzled on the host (sgmm_set_model) so a ring stage is one contiguous
+//     cp.async.bulk;
+//   * the epilogue is two passes over the accumulator tile kept in TMEM: pass 1 the plain minimum (FMNMX, ALU
+//     pipe), pass 2 counts and locates every column within the certified error bound of it with saturating FMAs
+//     (FMA pipe): c = sat((min + G - v) * 2/G), acc += c, idx += c * column.  acc == 1 exactly <=> the minimum is
+//     the only candidate, and idx is then its column.  FSETP/FSEL-based top-2 tracking measured 2x slower.
 //
-// Roles per CTA (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected
-// lane), warps 2..5 = epilogue (TMEM lane quarter = warp_id % 4).  One CTA owns 128 frames (TMEM lanes) and
-// walks the density blocks of its task's states; B tiles of 128 densities stream through a 2-stage
-// full/empty mbarrier ring, accumulators rotate through 4 TMEM slots of 128 columns.
+// Like the FFMA scorer this kernel is a FILTER: k_tc_refine evaluates the certified winner's score in f64 in
+// the reference's exact operation order (Mixtures.cpp:645-713) and queues uncertified cells for a full f64
+// rescan of the state (k_tc_rescan).  Results are therefore bit-identical to the reference; the tensor cores
+// only decide where f64 work goes.
 #include <cuda.h>
 
 #include "sgmm_internal.cuh"
@@ -23,7 +31,7 @@ namespace sgmm_tc {
 
 constexpr int BM = 128;        // frames per CTA (TMEM lanes)
 constexpr int BN = 128;        // densities per B stage / MMA N
-constexpr int kMaxStage = 4;   // B stages in the TMA ring (the launcher picks what shared memory allows)
+constexpr int kMaxStage = 6;   // B stages in the TMA ring (the launcher picks what shared memory allows)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -44,39 +52,80 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
-// 3-D tile {8 floats, 128 rows, ksteps} -> shared [kstep][row][8 floats] (one 4 KB SWIZZLE_32B block per k-step)
-__device__ __forceinline__ void tma_load_rows(void* dst, const CUtensorMap* map, int row0, uint64_t* bar) {
+// busy poll (no suspend): lower wake-up latency for the MMA <-> epilogue hand-offs on the critical path
+__device__ __forceinline__ void mbar_spin(uint64_t* bar, uint32_t parity) {
   asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
-          smem_u32(dst)),
-      "l"(map), "r"(smem_u32(bar)), "r"(0), "r"(row0), "r"(0)
-      : "memory");
+      "{\n\t.reg .pred p;\n\t"
+      "SPIN_%=:\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra SDONE_%=;\n\t"
+      "bra SPIN_%=;\n\t"
+      "SDONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// 1-D bulk copy global -> shared (UBLKCP), completion on the mbarrier
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-// D[tmem] (+)= A[smem desc] . B[smem desc]   (kind::tf32, fp32 accumulate)
-__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+// D[tmem] (+)= A[tmem] . B[smem desc]   (kind::tf32, fp32 accumulate; A: lane = row, one 32-bit column per k)
+// Called by the WHOLE (converged) MMA warp with warp-uniform operands; one elected lane issues.  Issuing from
+// inside an `if (lane == 0)` region instead makes the compiler wrap every MMA in a uniform-register "waterfall"
+// loop (ELECT / R2UR / BRA.U.ANY, ~15 dependent instructions): measured 158 cycles per 64-cycle MMA.
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "{\n\t.reg .pred pe, pa;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
+      "setp.ne.b32 pa, %4, 0;\n\t"
+      "@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, pa;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// same, both operands from shared memory (used for the Alo pass only)
+__device__ __forceinline__ void tc_mma_tf32_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred pe, pa;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
+      "setp.ne.b32 pa, %4, 0;\n\t"
+      "@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, pa;\n\t}" ::"r"(d_tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
       : "memory");
 }
-// 16 consecutive accumulator columns of this thread's TMEM lane
-__device__ __forceinline__ void tc_ld16(uint32_t taddr, float (&v)[16]) {
-  uint32_t r[16];
+__device__ __forceinline__ void tc_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred pe;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
+      "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
+      : "memory");
+}
+// 8 consecutive columns of this thread's TMEM lane <- registers
+__device__ __forceinline__ void tc_st8(uint32_t taddr, const float4& a, const float4& b) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(__float_as_uint(a.x)),
+               "r"(__float_as_uint(a.y)), "r"(__float_as_uint(a.z)), "r"(__float_as_uint(a.w)), "r"(__float_as_uint(b.x)),
+               "r"(__float_as_uint(b.y)), "r"(__float_as_uint(b.z)), "r"(__float_as_uint(b.w))
+               : "memory");
+}
+// 16 consecutive accumulator columns of this thread's TMEM lane (no wait: the caller overlaps the latency)
+__device__ __forceinline__ void tc_ld16_nowait(uint32_t taddr, uint32_t (&r)[16]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
         "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
+}
+// wait for the outstanding tcgen05.ld's; the registers about to be consumed are operands so that the compiler
+// cannot move their uses above the wait
+__device__ __forceinline__ void tc_ld_wait(uint32_t (&r)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                 "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+               :
+               : "memory");
 }
 
 // Shared-memory matrix descriptor, K-major, SWIZZLE_32B.  One k-step (8 tf32 = 32 bytes) of a 128-row operand
@@ -131,10 +180,21 @@ __global__ void k_tc_prep(const float* __restrict__ x, uint64_t n_frames, uint32
 
 struct TcParams {
   uint32_t ksteps;             // K steps of 8 (KP = 8 * ksteps)
-  uint32_t nstage;             // B stages in flight (<= kMaxStage)
-  const uint32_t* col_off;     // [n_states + 1] first B row (padded density layout) of every state
+  uint32_t nstage;             // B stages in the ring (<= kMaxStage)
+  uint32_t stage_bytes;        // bytes of one ring stage (a full 128-density tile: 2 * ksteps * 128 * 32)
+  uint32_t nhalf;              // frame halves (of 128) per task: 2 when 32 * ksteps <= 256 TMEM columns, else 1
+  uint32_t debug;              // timing experiments only (results invalid): 1 = no epilogue math, 2 = no MMAs
+  const float* Ahi;            // [n_frames][8 * ksteps] tf32 hi / lo of the A rows (k_tc_prep)
+  const float* Alo;
+  uint64_t n_frames;
+  const float* Bimg;           // pre-tiled, pre-swizzled B (sgmm_set_model)
+  const uint32_t* tile_first;  // [n_states + 1]
+  const uint2* tile_info;      // {offset / 16 bytes, N}
+  const float2* xnorm;         // per frame {||x||, ||x^2||}, rounded up
+  const float4* sguard;        // per state {max ||g||, max ||h||, max |c|, -}
+  float eps;                   // relative error of one 3xTF32 dot-product term + fp32 accumulation (see host)
   uint64_t n_tasks;
-  // gathered mode: task = {utt, t0 (multiple of 128)}
+  // gathered mode: task = {utt, t0}
   const uint4* tasks;
   const uint64_t* frame_off;
   const uint32_t* uniq;
@@ -145,43 +205,38 @@ struct TcParams {
   int dense;
   uint64_t f0, nframes;
   uint32_t n_states;
-  // candidates, indexed like the emission matrix (gathered) / [frame - f0][state] (dense)
-  float* cb1;
-  float* cb2;
-  uint32_t* ci1;
+  // per cell, indexed like the emission matrix (gathered) / [frame - f0][state] (dense):
+  // column of the certified minimum within the state's (padded) density list, or kUncertain
+  uint32_t* cand;
 };
+constexpr uint32_t kUncertain = 0x80000000u;
+constexpr uint32_t kAccCol = 128;    // TMEM: columns [0, 128) hold Ahi of both halves, then three 128-column accumulators
+constexpr uint32_t kNumAcc = 3;
 
-// NHALF frame halves of 128 rows (TMEM lanes) per CTA share every B tile: NHALF = 2 halves the L2 -> shared
-// traffic per flop and gives the tensor pipe two accumulators per B stage.  Warps: 0 = TMA producer, 1 = TMEM
-// allocator + MMA issuer (one lane), 2 .. 2 + 4*NHALF - 1 = epilogue (TMEM lane quarter = warp_id % 4, frame
-// half = (warp_id - 2) / 4).  TMEM: NSLOT accumulator slots x NHALF halves x BN columns = 512 columns.
-template <int NHALF>
-__global__ void __launch_bounds__(64 + 128 * NHALF, 1) k_tc_gemm(const __grid_constant__ CUtensorMap mapAhi,
-                                                                  const __grid_constant__ CUtensorMap mapAlo,
-                                                                  const __grid_constant__ CUtensorMap mapBhi,
-                                                                  const __grid_constant__ CUtensorMap mapBlo, TcParams p) {
+// Warps: 0 = bulk-copy producer, 1 = TMEM allocator + MMA issuer, 2..17 = epilogue: warp 2 + 8 * part + 4 * half + i
+// reduces columns [64 * part, +64) of frame half `half` (TMEM lane quarter = warp_id % 4).  With two valid halves, group g owns frame half g and accumulator g on
+// every tile.  With one valid half (short tail of an utterance, or large K) group 0 works alone and the two
+// accumulators alternate by tile.
+template <int KS>   // KS > 0: k-steps known at compile time (fully unrolled MMA issue); 0: p.ksteps
+__global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
   extern __shared__ unsigned char smem_raw[];
-  constexpr uint32_t NSLOT = 4 / NHALF;                // accumulator slots (of NHALF x BN columns)
-  constexpr uint32_t KSTEP_BYTES = 128 * 32;           // one k-step of a 128-row operand
-  const uint32_t op_bytes = p.ksteps * KSTEP_BYTES;    // one 128-row operand (hi or lo)
-  const uint32_t a_bytes = 2 * NHALF * op_bytes;       // hi + lo of every half
-  const uint32_t b_stage = 2 * op_bytes;               // hi + lo
-  const uint32_t nstage = p.nstage;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  unsigned char* smem = smem_raw + (base - smem_u32(smem_raw));
-  unsigned char* sA = smem;                            // [half][hi, lo][kstep][128 rows][32 B]
-  unsigned char* sB = smem + a_bytes;                  // [stage][hi, lo][kstep][128 rows][32 B]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + nstage * b_stage);
-  uint64_t* a_full = bars;
+  unsigned char* sAlo = smem_raw + (base - smem_u32(smem_raw));    // [half][kstep][128 rows][32 B], 32-byte swizzle
+  unsigned char* sB = sAlo + p.nhalf * (p.stage_bytes / 2);        // [stage][hi, lo][kstep][128 rows][32 B]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + p.nstage * p.stage_bytes);
+  uint64_t* a_full = bars;                 // A rows are in TMEM (8 epilogue warps arrive)
   uint64_t* full = bars + 1;
   uint64_t* empty = full + kMaxStage;
-  uint64_t* tfull = empty + kMaxStage;
-  uint64_t* tempty = tfull + NSLOT;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + NSLOT);
+  uint64_t* tfull = empty + kMaxStage;     // [3] accumulator complete
+  uint64_t* tempty = tfull + kNumAcc;      // [3] accumulator drained
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + kNumAcc);
+  float* xchg = reinterpret_cast<float*>(tmem_ptr + 4);   // [2 slots][2 halves][128 rows][5]: column-part merge
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint64_t task = blockIdx.x;
-  constexpr uint32_t ROWS = BM * NHALF;
+  const uint32_t ROWS = BM * p.nhalf;
+  const uint32_t nstage = p.nstage, ks = KS > 0 ? (uint32_t)KS : p.ksteps, KP = 8 * ks;
+  constexpr uint32_t kstride = 4096 >> 4;   // descriptor units between the 128-row k-step blocks of a B operand
 
   // ---- task decode (uniform over the CTA)
   uint64_t row0;        // first A row (absolute frame index)
@@ -206,15 +261,13 @@ __global__ void __launch_bounds__(64 + 128 * NHALF, 1) k_tc_gemm(const __grid_co
     out_stride = p.nuniq_pad[t.x];
     out_base = p.E_off[t.x] + (uint64_t)t.y * out_stride;
   }
-  const uint32_t nh = (NHALF == 2 && nvalid > (uint32_t)BM) ? 2u : 1u;   // halves that hold valid frames
+  const uint32_t nh = nvalid > (uint32_t)BM ? 2u : 1u;   // halves that hold valid frames
 
   // ---- one-time setup
   if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAhi));
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBhi));
-    mbar_init(a_full, 1);
+    mbar_init(a_full, 4 * nh);
     for (uint32_t i = 0; i < nstage; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (uint32_t i = 0; i < NSLOT; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4 * nh); }
+    for (uint32_t i = 0; i < kNumAcc; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -227,99 +280,186 @@ __global__ void __launch_bounds__(64 + 128 * NHALF, 1) k_tc_gemm(const __grid_co
   const uint32_t tmem_base = *tmem_ptr;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== producer: one bulk copy per B tile =====
     if (lane == 0) {
-      mbar_expect_tx(a_full, 2 * nh * op_bytes);
-      for (uint32_t h = 0; h < nh; h++) {
-        tma_load_rows(sA + (2 * h) * op_bytes, &mapAhi, (int)(row0 + h * BM), a_full);
-        tma_load_rows(sA + (2 * h + 1) * op_bytes, &mapAlo, (int)(row0 + h * BM), a_full);
-      }
       uint32_t it = 0;
       for (uint32_t j = 0; j < nu; j++) {
         const uint32_t s = ulist ? ulist[j] : j;
-        const uint32_t c0 = p.col_off[s], nc = p.col_off[s + 1] - c0;
-        for (uint32_t n0 = 0; n0 < nc; n0 += BN, it++) {
-          const uint32_t stage = it % nstage;
+        for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, it++) {
+          const uint32_t stage = it % nstage, bytes = p.stage_bytes;
+          if (p.debug & 16) continue;
           mbar_wait(&empty[stage], ((it / nstage) & 1) ^ 1);
-          mbar_expect_tx(&full[stage], b_stage);
-          unsigned char* dst = sB + stage * b_stage;
-          tma_load_rows(dst, &mapBhi, (int)(c0 + n0), &full[stage]);
-          tma_load_rows(dst + op_bytes, &mapBlo, (int)(c0 + n0), &full[stage]);
+          mbar_expect_tx(&full[stage], bytes);
+          bulk_load(sB + stage * p.stage_bytes, p.Bimg + (size_t)t * (p.stage_bytes / 4), bytes, &full[stage]);
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer (single thread) =====
-    if (lane == 0) {
-      mbar_wait(a_full, 0);
-      uint32_t it = 0;
-      for (uint32_t j = 0; j < nu; j++) {
-        const uint32_t s = ulist ? ulist[j] : j;
-        const uint32_t nc = p.col_off[s + 1] - p.col_off[s];
-        for (uint32_t n0 = 0; n0 < nc; n0 += BN, it++) {
-          const uint32_t N = min((uint32_t)BN, nc - n0);
-          const uint32_t stage = it % nstage, slot = it % NSLOT;
-          mbar_wait(&tempty[slot], ((it / NSLOT) & 1) ^ 1);
-          mbar_wait(&full[stage], (it / nstage) & 1);
+    // ===== MMA issuer: the whole warp walks the loop, one elected lane issues =====
+    mbar_wait(a_full, 0);
+    tc_fence_after();
+    uint32_t it = 0;
+    for (uint32_t j = 0; j < nu; j++) {
+      const uint32_t s = ulist ? ulist[j] : j;
+      for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, it++) {
+        const uint32_t N = p.tile_info[t].y;
+        const uint32_t stage = it % nstage;
+        if (!(p.debug & 16)) mbar_wait(&full[stage], (it / nstage) & 1);
+        const uint32_t idesc = make_idesc_tf32(BM, N);
+        const uint64_t bhi = make_desc_sw32(smem_u32(sB + stage * p.stage_bytes));
+        const uint64_t blo = bhi + (uint64_t)ks * kstride;   // every k-step block is 128 rows (4 KB) whatever N
+        for (uint32_t h = 0; h < nh; h++) {
+          // (tile, half) units rotate through the three accumulators: the tensor pipe may run a unit ahead of the
+          // epilogue that drains the previous unit of the same half
+          const uint32_t unit = it * nh + h, buf = unit % kNumAcc, use = unit / kNumAcc;
+          if (!(p.debug & 8)) mbar_wait(&tempty[buf], (use & 1) ^ 1);
           tc_fence_after();
-          const uint32_t idesc = make_idesc_tf32(BM, N);
-          const uint32_t bhi = smem_u32(sB + stage * b_stage), blo = bhi + op_bytes;
-          for (uint32_t h = 0; h < nh; h++) {
-            const uint32_t d = tmem_base + (slot * NHALF + h) * BN;
-            const uint32_t ahi = smem_u32(sA + (2 * h) * op_bytes), alo = ahi + op_bytes;
-            uint32_t acc = 0;
-#pragma unroll 1
-            for (int pass = 0; pass < 3; pass++) {
-              const uint32_t a0 = pass == 1 ? alo : ahi;
-              const uint32_t b0 = pass == 2 ? blo : bhi;
-              for (uint32_t kk = 0; kk < p.ksteps; kk++) {
-                tc_mma_tf32(d, make_desc_sw32(a0 + kk * KSTEP_BYTES), make_desc_sw32(b0 + kk * KSTEP_BYTES), idesc, acc);
-                acc = 1;
-              }
+          const uint32_t d = tmem_base + kAccCol + buf * BN;
+          const uint32_t ahi = tmem_base + h * KP;
+          const uint64_t alo = make_desc_sw32(smem_u32(sAlo + h * (p.stage_bytes / 2)));
+          if (!(p.debug & 2)) {
+            if (KS > 0) {
+#pragma unroll
+              for (uint32_t kk = 0; kk < (uint32_t)KS; kk++) tc_mma_tf32_ts(d, ahi + kk * 8, bhi + kk * kstride, idesc, kk);
+#pragma unroll
+              for (uint32_t kk = 0; kk < (uint32_t)KS; kk++) tc_mma_tf32_ts(d, ahi + kk * 8, blo + kk * kstride, idesc, 1);
+#pragma unroll
+              for (uint32_t kk = 0; kk < (uint32_t)KS; kk++) tc_mma_tf32_ss(d, alo + kk * kstride, bhi + kk * kstride, idesc, 1);
+            } else {
+              for (uint32_t kk = 0; kk < ks; kk++) tc_mma_tf32_ts(d, ahi + kk * 8, bhi + kk * kstride, idesc, kk);
+              for (uint32_t kk = 0; kk < ks; kk++) tc_mma_tf32_ts(d, ahi + kk * 8, blo + kk * kstride, idesc, 1);
+              for (uint32_t kk = 0; kk < ks; kk++) tc_mma_tf32_ss(d, alo + kk * kstride, bhi + kk * kstride, idesc, 1);
             }
           }
-          tc_commit(&empty[stage]);   // smem stage reusable once these MMAs have read it
-          tc_commit(&tfull[slot]);    // accumulator slot complete (all halves)
+          if (h + 1 == nh) tc_commit_elect(&empty[stage]);   // stage reusable once every MMA that reads it is done
+          tc_commit_elect(&tfull[buf]);
         }
       }
     }
   } else {
-    // ===== epilogue: per-state top-2 over the accumulator columns =====
+    // ===== epilogue warps: (half, lane quarter, column part) =====
     const uint32_t quarter = warp & 3;
-    const uint32_t half = (uint32_t)(warp - 2) >> 2;
-    if (half < nh) {
-      const uint32_t row = half * BM + quarter * 32 + lane;
+    const uint32_t group = ((uint32_t)(warp - 2) >> 2) & 1u;      // frame half
+    const uint32_t part = (uint32_t)(warp - 2) >> 3;              // columns [64 * part, 64 * part + 64) of every tile
+    if (group < nh) {
+      const uint32_t lrow = quarter * 32 + lane;
+      const uint32_t row = group * BM + lrow;
       const uint32_t tlane = tmem_base + ((quarter * 32) << 16);
+      // A rows of this thread's frame: hi -> TMEM, lo -> shared memory (part 0 only)
+      if (part == 0) {
+        const uint64_t fr = min(row0 + row, p.n_frames - 1);     // rows past the end are never read back
+        const float4* ah = reinterpret_cast<const float4*>(p.Ahi + fr * KP);
+        const float4* al = reinterpret_cast<const float4*>(p.Alo + fr * KP);
+        const uint32_t acol = tlane + group * KP;
+        // lo part: [kstep][row][32 B] with byte-address bit 7 (= row bit 2) XORed into bit 4
+        unsigned char* lo_row = sAlo + group * (p.stage_bytes / 2) + lrow * 32;
+        const uint32_t sw = ((lrow >> 2) & 1u) << 4;
+        for (uint32_t kk = 0; kk < ks; kk++) {
+          tc_st8(acol + kk * 8, __ldg(ah + 2 * kk), __ldg(ah + 2 * kk + 1));
+          *reinterpret_cast<float4*>(lo_row + kk * 4096 + (0 ^ sw)) = __ldg(al + 2 * kk);
+          *reinterpret_cast<float4*>(lo_row + kk * 4096 + (16 ^ sw)) = __ldg(al + 2 * kk + 1);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the MMA
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(a_full);
+      }
+      const float2 xn = p.xnorm[min(row0 + row, p.n_frames - 1)];
+      float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
       uint32_t it = 0;
       for (uint32_t j = 0; j < nu; j++) {
         const uint32_t s = ulist ? ulist[j] : j;
-        const uint32_t nc = p.col_off[s + 1] - p.col_off[s];
-        float b1 = INFINITY, b2 = INFINITY;
-        uint32_t i1 = 0;
-        for (uint32_t n0 = 0; n0 < nc; n0 += BN, it++) {
-          const uint32_t N = min((uint32_t)BN, nc - n0);
-          const uint32_t slot = it % NSLOT;
-          mbar_wait(&tfull[slot], (it / NSLOT) & 1);
+        const float4 g = __ldg(p.sguard + s);
+        // certified bound on |f32 score - exact score| differences between two candidates (+0.1 %)
+        const float Gs = 2.002f * p.eps * (xn.x * g.x + xn.y * g.y + g.z);
+        float Bbest = INFINITY, Bsecond = INFINITY, Bacc = 0.f, Bidx = 0.f, BG = 0.f;
+        uint32_t n0 = 0;
+        for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, it++) {
+          const uint32_t N = p.tile_info[t].y;
+          const uint32_t unit = it * nh + group, buf = unit % kNumAcc, use = unit / kNumAcc;
+          mbar_wait(&tfull[buf], use & 1);
           tc_fence_after();
-          const uint32_t tcol = tlane + (slot * NHALF + half) * BN;
-          for (uint32_t cc = 0; cc < N; cc += 16) {
-            float v[16];
-            tc_ld16(tcol + cc, v);
+          const uint32_t tcol = tlane + kAccCol + buf * BN;
+          const uint32_t c_lo = part * 64, c_hi = min(N, c_lo + 64);
+          float m = INFINITY, acc = 0.f, idx = 0.f, G = 0.f;
+          if (!(p.debug & 1) && c_lo < c_hi) {
+            uint32_t ra[16], rb[16];
 #pragma unroll
-            for (int e = 0; e < 16; e++) {
-              b2 = fminf(b2, fmaxf(b1, v[e]));
-              if (v[e] < b1) { b1 = v[e]; i1 = n0 + cc + e; }
+            for (int e = 0; e < 16; e++) rb[e] = 0;
+            // pass 1: minimum of this part's columns (loads run one block ahead; four independent chains)
+            float mm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+            tc_ld16_nowait(tcol + c_lo, ra);
+            tc_ld_wait(ra);
+            for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
+              if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
+#pragma unroll
+              for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(ra[e]));
+              tc_ld_wait(rb);
+              if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
+              if (cc + 16 < c_hi) {
+#pragma unroll
+                for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(rb[e]));
+              }
+              tc_ld_wait(ra);
+            }
+            m = fminf(fminf(mm[0], mm[1]), fminf(mm[2], mm[3]));
+            // pass 2: every column within G of the minimum contributes c in (0, 1]; the minimum itself exactly 1
+            G = Gs + 4e-6f * fabsf(m);
+            const float invg = __fdividef(2.f, G), t0 = (m + G) * invg, ninvg = -invg;
+            tc_ld16_nowait(tcol + c_lo, ra);
+            tc_ld_wait(ra);
+            for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
+              if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
+              {
+                float a4[4] = {0.f, 0.f, 0.f, 0.f}, i4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int e = 0; e < 16; e++) {
+                  const float c = __saturatef(fmaf(__uint_as_float(ra[e]), ninvg, t0));
+                  a4[e & 3] += c;
+                  i4[e & 3] = fmaf(c, (float)e, i4[e & 3]);
+                }
+                const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]), ib = (i4[0] + i4[1]) + (i4[2] + i4[3]);
+                acc += ab;
+                idx += fmaf(ab, (float)cc, ib);
+              }
+              tc_ld_wait(rb);
+              if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
+              if (cc + 16 < c_hi) {
+                float a4[4] = {0.f, 0.f, 0.f, 0.f}, i4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int e = 0; e < 16; e++) {
+                  const float c = __saturatef(fmaf(__uint_as_float(rb[e]), ninvg, t0));
+                  a4[e & 3] += c;
+                  i4[e & 3] = fmaf(c, (float)e, i4[e & 3]);
+                }
+                const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]), ib = (i4[0] + i4[1]) + (i4[2] + i4[3]);
+                acc += ab;
+                idx += fmaf(ab, (float)(cc + 16), ib);
+              }
+              tc_ld_wait(ra);
             }
           }
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[slot]);
+          if (lane == 0) mbar_arrive(&tempty[buf]);
+          // merge with the state's earlier tiles
+          if (m < Bbest) { Bsecond = Bbest; Bbest = m; Bacc = acc; Bidx = (float)n0 + idx; BG = G; }
+          else Bsecond = fminf(Bsecond, m);
+          n0 += N;
         }
-        if (row < nvalid) {
-          const uint64_t o = out_base + (uint64_t)row * out_stride + j;
-          p.cb1[o] = b1;
-          p.cb2[o] = b2;
-          p.ci1[o] = i1;
+        // the two column parts of a (half, quarter) meet through shared memory once per state
+        float* slot = my_x + (j & 1) * (2 * BM * 5);
+        if (part == 1) { slot[0] = Bbest; slot[1] = Bsecond; slot[2] = Bacc; slot[3] = Bidx; slot[4] = BG; }
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + group * 4 + quarter) : "memory");
+        if (part == 0) {
+          const float ob = slot[0], os = slot[1];
+          if (ob < Bbest) { Bsecond = fminf(Bbest, os); Bbest = ob; Bacc = slot[2]; Bidx = slot[3]; BG = slot[4]; }
+          else Bsecond = fminf(Bsecond, ob);
+          if (row < nvalid) {
+            const bool certain = Bacc == 1.0f && Bsecond > Bbest + BG;
+            p.cand[out_base + (uint64_t)row * out_stride + j] = certain ? (uint32_t)Bidx : kUncertain;
+          }
         }
       }
     }
@@ -339,12 +479,7 @@ struct RefineParams {
   ExactTables m;
   const uint32_t* state_off;
   const float* x;
-  const float* cb1;
-  const float* cb2;
-  const uint32_t* ci1;
-  const float2* xnorm;
-  const float4* sguard;        // per state {Gmax, Hmax, cabs, -}
-  float eps;                   // relative error of one 3xTF32 dot product term + fp32 accumulation (see host)
+  const uint32_t* cand;        // GEMM verdict per cell: certified argmin column, or kUncertain
   uint64_t n_cells;
   int dense;
   uint64_t f0;
@@ -395,12 +530,8 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
   double best = 1e10;
   uint32_t bk = 0;
   if (k1 > k0) {
-    const float b1 = p.cb1[e], b2 = p.cb2[e];
-    const uint32_t i1 = p.ci1[e];
-    const float2 xn = p.xnorm[frame];
-    const float4 g = p.sguard[s];
-    const float guard = 2.f * p.eps * (xn.x * g.x + xn.y * g.y + g.z);
-    const bool certain = (b2 - b1) > guard && i1 < k1 - k0;
+    const uint32_t i1 = p.cand[e];
+    const bool certain = i1 < k1 - k0;          // kUncertain and padding columns fail this
     if (!certain) {
       const unsigned long long slot = atomicAdd(p.rescan, 1ull);
       if (slot < p.cap) { p.rescan[1 + slot] = e; return; }
@@ -460,43 +591,10 @@ __global__ void __launch_bounds__(256) k_tc_rescan(RefineParams p) {
 // ---------------------------------------------------------------------------------------------------
 namespace {
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  }
-  return fn;
-}
-
-// f32 matrix [rows][KP] (KP = 8 * ksteps innermost) seen as the 3-D tensor {8, rows, ksteps}: one box =
-// 128 rows x all k-steps, delivered as [kstep][row][8 floats] with the 32-byte swizzle the MMA descriptors name.
-int make_map(sgmm_ctx* c, CUtensorMap* map, const float* base, uint64_t rows, uint32_t ksteps) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) SGMM_FAIL(c, "cuTensorMapEncodeTiled is not available from the driver");
-  const uint32_t KP = 8 * ksteps;
-  cuuint64_t dims[3] = {8, rows, ksteps};
-  cuuint64_t strides[2] = {(cuuint64_t)KP * sizeof(float), 8 * sizeof(float)};
-  cuuint32_t box[3] = {8, 128, ksteps};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) SGMM_FAIL(c, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
-  return 0;
-}
-
-// shared-memory plan: A = 2 * NHALF operands, each B stage = 2 operands of ksteps * 4 KB
+// shared memory: Alo + the B ring (Ahi lives in tensor memory)
 constexpr size_t kSmemLimit = 227 * 1024;
-size_t tc_smem(uint32_t ksteps, int nhalf, int nstage) {
-  return 1024 + (size_t)(2 * nhalf + 2 * nstage) * ksteps * 4096 + 256;
+size_t tc_smem(uint32_t stage_bytes, int nhalf, int nstage) {   // Alo of every half + the B ring + barriers
+  return 1024 + (size_t)nhalf * (stage_bytes / 2) + (size_t)nstage * stage_bytes + 256 + 2 * 2 * 128 * 5 * sizeof(float);
 }
 
 }  // namespace
@@ -506,10 +604,11 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   using namespace sgmm_tc;
   if (!c->tc_ok) SGMM_FAIL(c, "tensor-core scorer not available for this model shape");
   const uint32_t KP = c->tc_KP, ks = c->tc_ksteps;
-  // two frame halves per CTA when at least two B stages still fit next to them
-  int nhalf = (c->tc_halves == 1 || tc_smem(ks, 2, 2) > kSmemLimit) ? 1 : 2;
+  // two frame halves per CTA when their Ahi operands (KP columns each) fit the 128 TMEM columns set aside
+  const int nhalf = (c->tc_halves == 1 || 2 * KP > 128) ? 1 : 2;
+  const uint32_t stage_bytes = 2 * ks * 128 * 32;
   int nstage = 1;
-  while (nstage < sgmm_tc::kMaxStage && tc_smem(ks, nhalf, nstage + 1) <= kSmemLimit) nstage++;
+  while (nstage < sgmm_tc::kMaxStage && tc_smem(stage_bytes, nhalf, nstage + 1) <= kSmemLimit) nstage++;
   const uint32_t rows_per_task = 128u * nhalf;
   // A operand (once per feature upload / model shape)
   if (!c->tc_A_valid) {
@@ -526,32 +625,35 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   const uint64_t n_tasks = dense ? (dense_nframes + rows_per_task - 1) / rows_per_task
                                  : (nhalf == 2 ? c->n_tasks256 : c->n_tasks128);
   if (n_tasks == 0) return 0;
-  SGMM_CHECK(c, c->d_cb1.reserve(n_cells)); SGMM_CHECK(c, c->d_cb2.reserve(n_cells));
   SGMM_CHECK(c, c->d_ci1.reserve(n_cells));
   const size_t cap = (size_t)std::max<uint64_t>(1024, n_cells / 8);
   SGMM_CHECK(c, c->d_rescan.reserve(cap + 1));
   c->rescan_cap = cap;
   SGMM_CHECK(c, cudaMemsetAsync(c->d_rescan.p, 0, sizeof(unsigned long long), c->stream));
 
-  CUtensorMap mAhi, mAlo, mBhi, mBlo;
-  if (make_map(c, &mAhi, c->d_Ahi.p, c->n_frames, ks) || make_map(c, &mAlo, c->d_Alo.p, c->n_frames, ks) ||
-      make_map(c, &mBhi, c->d_Bhi.p, c->tc_Dpad, ks) || make_map(c, &mBlo, c->d_Blo.p, c->tc_Dpad, ks))
-    return 1;
-
   TcParams p{};
-  p.ksteps = ks; p.nstage = (uint32_t)nstage; p.col_off = c->d_col_off.p; p.n_tasks = n_tasks;
-  p.tasks = nhalf == 2 ? c->d_tasks256.p : c->d_tasks128.p; p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
+  p.ksteps = ks; p.nstage = (uint32_t)nstage; p.stage_bytes = stage_bytes; p.nhalf = (uint32_t)nhalf;
+  p.debug = (uint32_t)c->tc_debug;
+  p.Ahi = c->d_Ahi.p; p.Alo = c->d_Alo.p; p.n_frames = c->n_frames;
+  p.Bimg = c->d_Bimg.p; p.tile_first = c->d_tile_first.p; p.tile_info = c->d_tile_info.p;
+  p.xnorm = c->d_xnorm.p; p.sguard = c->d_sguard_tc.p; p.eps = c->tc_eps;
+  p.n_tasks = n_tasks;
+  p.tasks = nhalf == 2 ? c->d_tasks256.p : c->d_tasks128.p;
+  p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
   p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
-  p.cb1 = c->d_cb1.p; p.cb2 = c->d_cb2.p; p.ci1 = c->d_ci1.p;
-  const size_t smem = tc_smem(ks, nhalf, nstage);
+  p.cand = c->d_ci1.p;
+  const size_t smem = tc_smem(stage_bytes, nhalf, nstage);
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER], c->stream);
-  if (nhalf == 2) {
-    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_tc_gemm<2><<<(unsigned)n_tasks, 320, smem, c->stream>>>(mAhi, mAlo, mBhi, mBlo, p);
+  if (ks == 5) {          // d = 33 pooled (BASELINE configs 2-4)
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_tc_gemm<5><<<(unsigned)n_tasks, 576, smem, c->stream>>>(p);
+  } else if (ks == 7) {   // d = 48 pooled (config 5), d = 25 unpooled
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_tc_gemm<7><<<(unsigned)n_tasks, 576, smem, c->stream>>>(p);
   } else {
-    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_tc_gemm<1><<<(unsigned)n_tasks, 192, smem, c->stream>>>(mAhi, mAlo, mBhi, mBlo, p);
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_tc_gemm<0><<<(unsigned)n_tasks, 576, smem, c->stream>>>(p);
   }
   SGMM_LAUNCH_CHECK(c);
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER + 1], c->stream);
@@ -561,8 +663,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
   r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;
   r.m.meanR = c->d_meanR.p; r.m.invU = c->d_invU.p; r.m.var_of = c->d_var_of.p; r.m.dimP = c->dimP;
-  r.state_off = c->d_state_off.p; r.x = c->d_x.p; r.cb1 = c->d_cb1.p; r.cb2 = c->d_cb2.p; r.ci1 = c->d_ci1.p;
-  r.xnorm = c->d_xnorm.p; r.sguard = c->d_sguard_tc.p; r.eps = c->tc_eps; r.n_cells = n_cells;
+  r.state_off = c->d_state_off.p; r.x = c->d_x.p; r.cand = c->d_ci1.p; r.n_cells = n_cells;
   r.dense = dense ? 1 : 0; r.f0 = dense_f0; r.n_states = c->n_states; r.n_utts = c->n_utts;
   r.frame_off = c->d_frame_off.p; r.E_off = c->d_E_off.p; r.uniq = c->d_uniq.p; r.uniq_off = c->d_uniq_off.p;
   r.nuniq_pad = c->d_nuniq_pad.p;
@@ -572,7 +673,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE], c->stream);
   k_tc_refine<<<(unsigned)((n_cells + 255) / 256), 256, 0, c->stream>>>(r);
   SGMM_LAUNCH_CHECK(c);
-  k_tc_rescan<<<148 * 4, 256, 0, c->stream>>>(r);
+  k_tc_rescan<<<148 * 16, 256, 0, c->stream>>>(r);
   SGMM_LAUNCH_CHECK(c);
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE + 1], c->stream);
   c->stage_ms[SGMM_T_SCORE_REFINE] = -1.f;

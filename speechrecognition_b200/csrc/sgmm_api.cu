@@ -88,7 +88,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
   c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_h32.release(); c->d_c32.release();
   c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release(); c->d_tasks256.release(); c->d_Amin.release(); c->d_fcol.release();
-  c->d_Bhi.release(); c->d_Blo.release(); c->d_Ahi.release(); c->d_Alo.release(); c->d_cb1.release(); c->d_cb2.release();
+  c->d_Bimg.release(); c->d_tile_first.release(); c->d_tile_info.release(); c->d_Ahi.release(); c->d_Alo.release();
   c->d_xnorm.release(); c->d_sguard_tc.release(); c->d_col_off.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
   for (int i = 0; i < 2; i++) { c->d_keys[i].release(); c->d_vals[i].release(); }
@@ -204,7 +204,7 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
         pooled = memcmp(inv_var + (size_t)j * dim, inv_var + (size_t)state_off[s] * dim, dim * sizeof(double)) == 0;
     const uint32_t Kused = pooled ? dim + 1 : 2 * dim + 1;
     const uint32_t KP = (Kused + 7) / 8 * 8;     // whole k-steps of 8 (32-byte swizzle atoms: no further padding)
-    c->tc_ok = KP / 8 <= 13;                     // A (2 operands) + 2 B stages of ksteps * 4 KB fit 227 KB
+    c->tc_ok = KP / 8 <= 13;                     // A (hi, lo) = 16 * ksteps TMEM columns per 128 frames, <= 256
     if (c->tc_ok) {
       const uint32_t nsq = pooled ? 0 : dim;
       std::vector<uint32_t> col_off(n_states + 1, 0);
@@ -244,7 +244,39 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
         }
         sgt[s] = make_float4((float)(Gmax * 1.0001), (float)(Hmax * 1.0001), (float)(cabs * 1.0001), 0.f);
       }
-      if (upload(c, c->d_Bhi, Bhi.data(), Bhi.size()) || upload(c, c->d_Blo, Blo.data(), Blo.size()) ||
+      // B as the GEMM kernel consumes it: per state, tiles of up to 128 densities; every tile is ONE contiguous
+      // block [hi, lo][k-step][N rows][8 floats] already in the 32-byte-swizzled shared-memory image the MMA
+      // descriptors name (Swizzle<1,4,3>: byte-address bit 7 XORed into bit 4), so a stage is filled by a single
+      // bulk copy at full L2 line rate instead of 32-byte tensor-map rows.
+      const uint32_t ks = KP / 8;
+      std::vector<uint32_t> tile_first(n_states + 1, 0);
+      std::vector<uint2> tile_info;           // {offset in 16-byte units, N}
+      std::vector<float> img;
+      for (uint32_t s = 0; s < n_states; s++) {
+        const uint32_t nc = col_off[s + 1] - col_off[s];
+        for (uint32_t n0 = 0; n0 < nc; n0 += 128) {
+          // every tile occupies a full ring stage: k-step blocks of 128 rows (rows >= N stay zero and are never
+          // multiplied: the MMA's N says so), so tile t starts at t * stage bytes and descriptors step by 4 KB
+          const uint32_t N = std::min(128u, nc - n0);
+          const size_t off = img.size();
+          tile_info.push_back(make_uint2((uint32_t)(off / 4), N));
+          img.resize(off + (size_t)2 * ks * 128 * 8, 0.f);
+          for (int op = 0; op < 2; op++) {
+            const std::vector<float>& B = op ? Blo : Bhi;
+            float* base = img.data() + off + (size_t)op * ks * 128 * 8;
+            for (uint32_t kk = 0; kk < ks; kk++)
+              for (uint32_t r = 0; r < N; r++)
+                for (uint32_t e = 0; e < 8; e++) {
+                  const uint32_t lin = kk * 128 * 32 + r * 32 + e * 4;
+                  const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
+                  base[phys / 4] = B[(size_t)(col_off[s] + n0 + r) * KP + kk * 8 + e];
+                }
+          }
+        }
+        tile_first[s + 1] = (uint32_t)tile_info.size();
+      }
+      if (upload(c, c->d_Bimg, img.data(), img.size()) || upload(c, c->d_tile_first, tile_first.data(), tile_first.size()) ||
+          upload(c, c->d_tile_info, tile_info.data(), tile_info.size()) ||
           upload(c, c->d_col_off, col_off.data(), col_off.size()) || upload(c, c->d_sguard_tc, sgt.data(), sgt.size()))
         return 1;
       SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
@@ -453,6 +485,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
     return 0;
   }
   if (!strcmp(key, "rescore_cache")) { c->use_cache = value != 0; return 0; }
+  if (!strcmp(key, "tc_debug")) { c->tc_debug = (int)value; return 0; }
   if (!strcmp(key, "tc_halves")) {
     if (value < 0 || value > 2) SGMM_FAIL(c, "set_option: tc_halves must be 0 (auto), 1 or 2");
     c->tc_halves = (int)value;

@@ -70,7 +70,9 @@ struct sgmm_ctx {
   uint32_t tc_KP = 0, tc_ksteps = 0, tc_Dpad = 0;
   int tc_full = 0;                 // 1: K = x^2 | x | 1;  0: variances pooled per state, K = x | 1
   bool tc_ok = false, tc_A_valid = false;
-  DevBuf<float> d_Bhi, d_Blo, d_Ahi, d_Alo, d_cb1, d_cb2;
+  DevBuf<float> d_Bimg, d_Ahi, d_Alo;
+  DevBuf<uint32_t> d_tile_first;    // [n_states + 1] first B tile of every state
+  DevBuf<uint2> d_tile_info;        // per tile {offset into d_Bimg in 16-byte units, densities N (multiple of 16)}
   DevBuf<float2> d_xnorm;
   DevBuf<float4> d_sguard_tc;      // per state {max ||g||, max ||h||, max |c|, -}
   DevBuf<uint32_t> d_col_off, d_ci1;
@@ -92,6 +94,7 @@ struct sgmm_ctx {
   DevBuf<uint16_t> d_pos2uniq;
   DevBuf<uint4> d_tasks128, d_tasks256;
   uint64_t n_tasks128 = 0, n_tasks256 = 0;
+  int tc_debug = 0;                // option "tc_debug": timing experiments (k_score_tc.cu), never set in production
   int tc_halves = 0;               // option "tc_halves": 0 auto, 1 / 2 = frame halves (128 rows each) per GEMM CTA
   DevBuf<uint4> d_tasks, d_tasks64;   // emission warp-tasks {utt, t0, 0, 0}: 32-frame and 64-frame granules
   uint64_t n_tasks = 0, n_tasks64 = 0, E_elems = 0;
