@@ -485,6 +485,8 @@ struct RefineParams {
   uint64_t f0;
   uint32_t n_states;
   uint32_t n_utts;
+  const uint4* tasks;          // gathered: {utt, t0} granules of 128 frames
+  int pooled;                  // every state's densities share one inverse-variance row
   const uint64_t* frame_off;
   const uint64_t* E_off;
   const uint32_t* uniq;
@@ -520,35 +522,120 @@ __device__ __forceinline__ bool decode_cell(const RefineParams& p, uint64_t e, u
   return true;
 }
 
-__global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
-  const uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= p.n_cells) return;
-  uint64_t frame;
-  uint32_t s;
-  if (!decode_cell(p, e, frame, s)) return;
-  const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
-  double best = 1e10;
-  uint32_t bk = 0;
-  if (k1 > k0) {
-    const uint32_t i1 = p.cand[e];
-    const bool certain = i1 < k1 - k0;          // kUncertain and padding columns fail this
-    if (!certain) {
-      const unsigned long long slot = atomicAdd(p.rescan, 1ull);
-      if (slot < p.cap) { p.rescan[1 + slot] = e; return; }
-      // list full: rescan here
-      const float* xf = p.x + frame * p.m.dim;
-      for (uint32_t k = k0; k < k1; k++) {
-        const double sc = sgmm_exact_score(p.m, xf, k);
-        if (sc < best) { best = sc; bk = k - k0; }
-      }
-    } else {
-      const double sc = sgmm_exact_score_rm(p.m, p.x + frame * p.m.dim, k0 + i1);
-      if (sc < best) { best = sc; bk = i1; }
-    }
+// exact score from the row-major tables with NP dimension pairs known at compile time: every load of the mean
+// row is in flight before the (sequential, reference-ordered) f64 chain starts; the frame's features (xs, f32
+// pairs) and — for pooled models — the state's inverse variances (ivs) come from shared memory so that the
+// global load queue only carries the mean row.  NP == 0: generic (everything from global memory).
+template <int NP>
+__device__ __forceinline__ double exact_score_unrolled(const ExactTables& m, const float* __restrict__ xf, uint32_t k,
+                                                       const float* xs, const double* ivs) {
+  if (NP == 0) return sgmm_exact_score_rm(m, xf, k);
+  // 256-bit loads (LDG.256): one L1 tag lookup per 32-byte sector instead of two — this kernel is bound by the
+  // 32-distinct-rows-per-instruction gather of the mean rows, not by bytes
+  const double* mrow = m.meanR + (size_t)k * m.dimP;       // rows are 32-byte aligned (dimP % 4 == 0)
+  double2 mu[NP > 0 ? NP : 1];
+#pragma unroll
+  for (int q = 0; q < NP / 2; q++)
+    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+                 : "=d"(mu[2 * q].x), "=d"(mu[2 * q].y), "=d"(mu[2 * q + 1].x), "=d"(mu[2 * q + 1].y)
+                 : "l"(mrow + 4 * q));
+  static_assert(NP % 2 == 0, "unrolled refinement expects an even number of dimension pairs");
+  const double mt = (m.dim & 1) ? __ldg(mrow + m.dim - 1) : 0.0;
+  const double* vg = m.invU + (size_t)__ldg(m.var_of + k) * m.dimP;
+  double l0 = 0.0, l1 = 0.0;
+#pragma unroll
+  for (int ip = 0; ip < NP; ip++) {
+    const double2 iv = ivs ? *reinterpret_cast<const double2*>(ivs + 2 * ip) : __ldg(reinterpret_cast<const double2*>(vg) + ip);
+    const float2 xx = *reinterpret_cast<const float2*>(xs + 2 * ip);
+    double a = __dsub_rn((double)xx.x, mu[ip].x);
+    double b = __dsub_rn((double)xx.y, mu[ip].y);
+    a = __dmul_rn(a, a); b = __dmul_rn(b, b);
+    a = __dmul_rn(a, iv.x); b = __dmul_rn(b, iv.y);
+    l0 = __dadd_rn(l0, a); l1 = __dadd_rn(l1, b);
   }
-  p.out[e] = best;
-  if (p.argmin) p.argmin[e] = bk;
-  if (p.amin16) p.amin16[e] = (uint16_t)bk;
+  double dist = __dadd_rn(l0, l1);
+  if (m.dim & 1) {
+    const double iv = ivs ? ivs[m.dim - 1] : __ldg(vg + m.dim - 1);
+    const double c = __dsub_rn((double)xs[m.dim - 1], mt);
+    dist = __dadd_rn(dist, __dmul_rn(__dmul_rn(c, c), iv));
+  }
+  const double s = __dadd_rn(__ldg(m.norm + k), __dmul_rn(dist, 0.5));
+  return __dsub_rn(s, __ldg(m.logw + k));
+}
+
+// One CTA per GEMM task granule (128 frames of one utterance, or 128 dense frames): cell -> (frame, state) is
+// plain arithmetic, consecutive threads own consecutive cells of the emission matrix.
+template <int NP>
+__global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
+  uint64_t cell0, frame0;
+  uint32_t nrows, ncol, nu;
+  const uint32_t* ulist = nullptr;
+  if (p.dense) {
+    const uint64_t r0 = (uint64_t)blockIdx.x * 128;
+    nrows = (uint32_t)min((uint64_t)128, p.n_cells / p.n_states - r0);
+    ncol = nu = p.n_states;
+    cell0 = r0 * p.n_states;
+    frame0 = p.f0 + r0;
+  } else {
+    const uint4 t = p.tasks[blockIdx.x];
+    const uint64_t uf0 = p.frame_off[t.x];
+    nrows = min(128u, (uint32_t)(p.frame_off[t.x + 1] - uf0) - t.y);
+    ncol = p.nuniq_pad[t.x];
+    nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
+    ulist = p.uniq + p.uniq_off[t.x];
+    cell0 = p.E_off[t.x] + (uint64_t)t.y * ncol;
+    frame0 = uf0 + t.y;
+  }
+  // stage the granule's feature rows (and, pooled models, the inverse-variance row of each of its states)
+  extern __shared__ __align__(16) unsigned char refine_smem[];
+  constexpr uint32_t XS = 2 * NP + 2;                        // floats per staged feature row
+  float* xs_all = reinterpret_cast<float*>(refine_smem);
+  double* iv_all = reinterpret_cast<double*>(refine_smem + 128 * XS * sizeof(float));
+  if (NP > 0) {
+    const uint32_t dim = p.m.dim;
+    for (uint32_t i = threadIdx.x; i < nrows * dim; i += 256) {
+      const uint32_t r = i / dim, q = i - r * dim;
+      xs_all[r * XS + q] = __ldg(p.x + (frame0 + r) * dim + q);
+    }
+    if (p.pooled) {
+      for (uint32_t i = threadIdx.x; i < nu * p.m.dimP; i += 256) {
+        const uint32_t j = i / p.m.dimP, q = i - j * p.m.dimP;
+        const uint32_t s = ulist ? ulist[j] : j;
+        const uint32_t k0 = p.state_off[s];
+        iv_all[i] = k0 < p.state_off[s + 1] ? __ldg(p.m.invU + (size_t)__ldg(p.m.var_of + k0) * p.m.dimP + q) : 0.0;
+      }
+    }
+    __syncthreads();
+  }
+  const uint32_t ncell = nrows * ncol;
+  for (uint32_t i = threadIdx.x; i < ncell; i += 256) {
+    const uint32_t r = i / ncol, j = i - r * ncol;
+    if (j >= nu) continue;                       // padding column of a gathered row
+    const uint64_t e = cell0 + i, frame = frame0 + r;
+    const uint32_t s = ulist ? ulist[j] : j;
+    const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
+    double best = 1e10;
+    uint32_t bk = 0;
+    if (k1 > k0) {
+      const uint32_t i1 = p.cand[e];
+      if (i1 < k1 - k0) {                        // certified (kUncertain and padding columns fail this)
+        const double sc = exact_score_unrolled<NP>(p.m, p.x + frame * p.m.dim, k0 + i1, xs_all + r * XS,
+                                                   p.pooled ? iv_all + j * p.m.dimP : nullptr);
+        if (sc < best) { best = sc; bk = i1; }
+      } else {
+        const unsigned long long slot = atomicAdd(p.rescan, 1ull);
+        if (slot < p.cap) { p.rescan[1 + slot] = e; continue; }
+        const float* xf = p.x + frame * p.m.dim;   // list full: rescan here
+        for (uint32_t k = k0; k < k1; k++) {
+          const double sc = sgmm_exact_score(p.m, xf, k);
+          if (sc < best) { best = sc; bk = k - k0; }
+        }
+      }
+    }
+    p.out[e] = best;
+    if (p.argmin) p.argmin[e] = bk;
+    if (p.amin16) p.amin16[e] = (uint16_t)bk;
+  }
 }
 
 // one warp per queued near-tie cell: exact f64 rescan of the whole state, first minimum wins
@@ -671,7 +758,26 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   r.amin16 = dense ? nullptr : c->d_Amin.p;
   r.rescan = c->d_rescan.p; r.cap = cap; r.fallback_count = c->d_fallbacks.p;
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE], c->stream);
-  k_tc_refine<<<(unsigned)((n_cells + 255) / 256), 256, 0, c->stream>>>(r);
+  r.tasks = c->d_tasks128.p;
+  const unsigned rgrid = dense ? (unsigned)((dense_nframes + 127) / 128) : (unsigned)c->n_tasks128;
+  r.pooled = c->tc_full ? 0 : 1;
+  // shared memory: 128 feature rows + (pooled) one inverse-variance row per state of the granule
+  const size_t rsm = 128 * (2 * (size_t)c->npair + 2) * sizeof(float) +
+                     (r.pooled ? (size_t)(dense ? c->n_states : c->max_uniq) * c->dimP * sizeof(double) : 0);
+  if (rsm > 200 * 1024) r.pooled = 0;
+  const size_t rsm_used = r.pooled ? rsm : 128 * (2 * (size_t)c->npair + 2) * sizeof(float);
+  switch (c->npair) {   // common feature dimensions get a fully unrolled row walk
+    case 16:   // d = 32, 33
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
+      k_tc_refine<16><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
+    case 24:   // d = 48, 49
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
+      k_tc_refine<24><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
+    case 12:   // d = 24, 25
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
+      k_tc_refine<12><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
+    default: k_tc_refine<0><<<rgrid, 256, 0, c->stream>>>(r); break;
+  }
   SGMM_LAUNCH_CHECK(c);
   k_tc_rescan<<<148 * 16, 256, 0, c->stream>>>(r);
   SGMM_LAUNCH_CHECK(c);

@@ -138,7 +138,7 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
     return 1;
   // row-major twins for the refinement kernels: padded mean rows, distinct variance rows
   {
-    const uint32_t dimP = (dim + 1) & ~1u;
+    const uint32_t dimP = (dim + 3) & ~3u;       // rows 32-byte aligned for 256-bit loads
     std::vector<double> mR((size_t)D * dimP, 0.0), vU;
     std::vector<uint32_t> var_of(D);
     std::map<std::string, uint32_t> seen;
@@ -334,7 +334,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   std::vector<uint64_t> E_off(U + 1, 0);
   std::vector<uint4> tasks, tasks64, tasks128, tasks256;
   std::map<std::pair<int, size_t>, ViterbiClass> classes;
-  uint32_t max_state = 0;
+  uint32_t max_state = 0, max_uniq = 0;
   for (uint32_t u = 0; u < U; u++) {
     if (frame_off[u + 1] <= frame_off[u]) SGMM_FAIL(c, "set_corpus: empty utterance");
     const uint64_t T64 = frame_off[u + 1] - frame_off[u];
@@ -353,6 +353,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     uniq.insert(uniq.end(), us.begin(), us.end());
     uniq_off[u + 1] = (uint32_t)uniq.size();
     ncol[u] = ((uint32_t)us.size() + 1u) & ~1u;
+    max_uniq = std::max(max_uniq, (uint32_t)us.size());
     E_off[u + 1] = E_off[u] + (uint64_t)T * ncol[u];
     for (uint32_t t0 = 0; t0 < T; t0 += 32) tasks.push_back(make_uint4(u, t0, 0, 0));
     for (uint32_t t0 = 0; t0 < T; t0 += 64) tasks64.push_back(make_uint4(u, t0, 0, 0));
@@ -389,7 +390,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       upload(c, c->d_tasks256, tasks256.data(), tasks256.size()))
     return 1;
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
-  c->max_aut_state = max_state;
+  c->max_aut_state = max_state; c->max_uniq = max_uniq;
   c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->n_tasks128 = tasks128.size(); c->n_tasks256 = tasks256.size(); c->E_elems = E_off[U];
   c->h_frame_off.assign(frame_off, frame_off + U + 1);
   c->h_aut_off.assign(aut_off, aut_off + U + 1);

@@ -54,7 +54,7 @@ struct sgmm_ctx {
   std::vector<uint32_t> h_state_off;
   DevBuf<double2> d_meanT, d_invT;
   DevBuf<double> d_mean_tail, d_inv_tail, d_norm, d_logw;
-  // row-major copies for one-thread-per-cell refinement: meanR[D][dimP] (dimP = dim rounded up to 2, rows 16-byte
+  // row-major copies for one-thread-per-cell refinement: meanR[D][dimP] (dimP = dim rounded up to 4, rows 32-byte
   // aligned), the DISTINCT variance rows invU[V][dimP] and var_of[D] (pooled models: V = n_states or 1)
   uint32_t dimP = 0, n_var_rows = 0;
   DevBuf<double> d_meanR, d_invU;
@@ -86,7 +86,7 @@ struct sgmm_ctx {
   DevBuf<float> d_x;
 
   // ---- corpus
-  uint32_t n_utts = 0, max_aut_state = 0;
+  uint32_t n_utts = 0, max_aut_state = 0, max_uniq = 0;   // max_uniq: most distinct states in one automaton
   std::vector<uint64_t> h_frame_off;
   std::vector<uint32_t> h_aut_off;
   DevBuf<uint64_t> d_frame_off, d_E_off;
