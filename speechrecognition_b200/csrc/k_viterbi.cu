@@ -111,22 +111,30 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     }
   }
 
-  // per-position constants (registers)
-  double q[C];
+  // per-position constants (registers).  TdpModel::score: the silence state pays tdp_forward for every jump.
+  //   SOURCE convention: the penalty belongs to the position the transition LEAVES: loop from s, forward from
+  //   s-1, skip from s-2.  DESTINATION: to the position it ENTERS (s for all three).
+  double q[C], pl[C], pk[C];
   uint32_t col[C], w[C];
-  uint32_t silmask = 0, validmask = 0;
+  uint32_t validmask = 0;
+  const double INFd = INF;
 #pragma unroll
   for (int c = 0; c < C; c++) {
     const uint32_t s = lane * C + c;
-    q[c] = INF;
+    q[c] = INFd;
     w[c] = 0;
     col[c] = 0;
+    pl[c] = p.tdp_loop;
+    pk[c] = p.tdp_skip;
     if (s < S) {
       validmask |= 1u << c;
       col[c] = p.pos2uniq[a0 + s];
-      if (sref[s] == p.silence_state) silmask |= 1u << c;
+      if (sref[s] == p.silence_state) pl[c] = p.tdp_forward;
+      const uint32_t src = DEST ? s : (s >= 2 ? s - 2 : 0);
+      if (sref[src] == p.silence_state) pk[c] = p.tdp_forward;
     }
   }
+  const double pf = p.tdp_forward;
 
   for (uint32_t ti = 0; ti < n_tiles; ti++) {
     const uint32_t slot = ti % SGMM_STAGES;
@@ -134,65 +142,55 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     const double* tile = tiles + slot * tile_elems;
     const uint32_t t0 = ti * SGMM_TILE_T;
     const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - t0);
+#pragma unroll 4
     for (uint32_t tt = 0; tt < rows; tt++) {
       const uint32_t t = t0 + tt;
       const double* row = tile + tt * ncol;
+      // positions past the automaton read column 0: their costs never reach a valid position (jumps only go forward)
       double e[C];
 #pragma unroll
-      for (int c = 0; c < C; c++) e[c] = ((validmask >> c) & 1) ? row[col[c]] : INF;
+      for (int c = 0; c < C; c++) e[c] = row[col[c]];
       if (t == 0) {
         // Q(0,0) = emission(0, ref[0]); every other position starts at +inf (Alignment.cpp:62-63,77)
 #pragma unroll
-        for (int c = 0; c < C; c++) q[c] = (lane == 0 && c == 0) ? e[0] : INF;
+        for (int c = 0; c < C; c++) q[c] = (lane == 0 && c == 0) ? e[0] : INFd;
         continue;
       }
+      // the two costs that cross the lane boundary (positions s-1 and s-2 of this lane's first position)
+      double Q1 = __shfl_up_sync(0xffffffffu, q[C - 1], 1);
+      double Q2 = __shfl_up_sync(0xffffffffu, q[C - 2], 1);
+      if (lane == 0) { Q1 = INFd; Q2 = INFd; }
       double nq[C];
-      if (!DEST) {
-        double lv[C], fv[C], kv[C];
+      const uint32_t sh = 2 * (t & 15);
 #pragma unroll
-        for (int c = 0; c < C; c++) {
-          const bool sil = (silmask >> c) & 1;   // TdpModel::score: silence always pays tdp_forward
-          lv[c] = __dadd_rn(q[c], sil ? p.tdp_forward : p.tdp_loop);
-          fv[c] = __dadd_rn(q[c], p.tdp_forward);
-          kv[c] = __dadd_rn(q[c], sil ? p.tdp_forward : p.tdp_skip);
-        }
-        double F = __shfl_up_sync(0xffffffffu, fv[C - 1], 1);
-        double K1 = __shfl_up_sync(0xffffffffu, kv[C - 2], 1);
-        double K2 = __shfl_up_sync(0xffffffffu, kv[C - 1], 1);
-        if (lane == 0) { F = INF; K1 = INF; K2 = INF; }
-#pragma unroll
-        for (int c = 0; c < C; c++) {
-          double best = lv[c];
-          uint32_t j = 0;
-          const double fwd = c > 0 ? fv[c > 0 ? c - 1 : 0] : F;
-          if (fwd < best) { best = fwd; j = 1; }
-          const double skp = c > 1 ? kv[c > 1 ? c - 2 : 0] : (c == 1 ? K2 : K1);
-          if (skp < best) { best = skp; j = 2; }
+      for (int c = 0; c < C; c++) {
+        const double p1 = c > 0 ? q[c > 0 ? c - 1 : 0] : Q1;
+        const double p2 = c > 1 ? q[c > 1 ? c - 2 : 0] : (c == 1 ? Q1 : Q2);
+        uint32_t j;
+        if (!DEST) {
+          // current = local + min{loop, forward, skip}, ties loop > forward > skip (Alignment.cpp:96-113)
+          const double lv = __dadd_rn(q[c], pl[c]);
+          const double fv = __dadd_rn(p1, pf);
+          const double kv = __dadd_rn(p2, pk[c]);
+          const bool f1 = fv < lv;
+          const double m1 = f1 ? fv : lv;
+          const bool f2 = kv < m1;
+          const double best = f2 ? kv : m1;
+          j = f2 ? 2u : (f1 ? 1u : 0u);
           nq[c] = __dadd_rn(e[c], best);
-          w[c] |= j << (2 * (t & 15));
+        } else {
+          // (prev + tdp) + emission; candidates arrive skip, forward, loop and replace on strictly smaller cost
+          // (Alignment.cpp:190-204).  Dead predecessors are +inf and never win a strict comparison.
+          const double ck = __dadd_rn(__dadd_rn(p2, pk[c]), e[c]);
+          const double cf = __dadd_rn(__dadd_rn(p1, pf), e[c]);
+          const double cl = __dadd_rn(__dadd_rn(q[c], pl[c]), e[c]);
+          const bool f1 = cf < ck;
+          const double m1 = f1 ? cf : ck;
+          const bool f2 = cl < m1;
+          nq[c] = f2 ? cl : m1;
+          j = f2 ? 0u : (f1 ? 1u : 2u);
         }
-      } else {
-        double Q1 = __shfl_up_sync(0xffffffffu, q[C - 1], 1);   // position s-1 of c = 0
-        double Q2 = __shfl_up_sync(0xffffffffu, q[C - 2], 1);   // position s-2 of c = 0
-        if (lane == 0) { Q1 = INF; Q2 = INF; }
-#pragma unroll
-        for (int c = 0; c < C; c++) {
-          const bool sil = (silmask >> c) & 1;
-          const double p1 = c > 0 ? q[c > 0 ? c - 1 : 0] : Q1;
-          const double p2 = c > 1 ? q[c > 1 ? c - 2 : 0] : (c == 1 ? Q1 : Q2);
-          // (prev + tdp) + emission, Alignment.cpp:190-197
-          const double ck = __dadd_rn(__dadd_rn(p2, sil ? p.tdp_forward : p.tdp_skip), e[c]);
-          const double cf = __dadd_rn(__dadd_rn(p1, p.tdp_forward), e[c]);
-          const double cl = __dadd_rn(__dadd_rn(q[c], sil ? p.tdp_forward : p.tdp_loop), e[c]);
-          // dead predecessors are +inf: they never win a strict comparison, exactly as hypotheses that
-          // were never created are never expanded in the reference
-          double best = ck;
-          uint32_t j = 2;
-          if (best > cf) { best = cf; j = 1; }
-          if (best > cl) { best = cl; j = 0; }
-          nq[c] = best;
-          w[c] |= j << (2 * (t & 15));
-        }
+        w[c] |= j << sh;
       }
 #pragma unroll
       for (int c = 0; c < C; c++) q[c] = nq[c];
