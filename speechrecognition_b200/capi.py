@@ -129,9 +129,9 @@ class Context:
                                        _ptr(argmin, C.c_uint32)))
         return scores, argmin
 
-    def align(self, convention=TDP_SOURCE, want_alignment=True, want_costs=True, out=None):
+    def align(self, convention=TDP_SOURCE, want_alignment=True, want_costs=True, out=None, out_costs=None):
         ali = out if out is not None else (np.empty(self.n_frames, ALI_DTYPE) if want_alignment else None)
-        costs = np.empty(self.n_utts, np.float64) if want_costs else None
+        costs = out_costs if out_costs is not None else (np.empty(self.n_utts, np.float64) if want_costs else None)
         self._ck(self.L.sgmm_align(self.h, int(convention), _ptr(ali, C.c_uint8) if ali is not None else None,
                                    _ptr(costs, C.c_double)))
         return ali, costs
@@ -146,11 +146,17 @@ class Context:
         states = np.ascontiguousarray(states)
         self._ck(self.L.sgmm_set_alignment(self.h, _ptr(states, C.c_uint8), C.c_uint64(len(states))))
 
-    def accumulate(self, first_pass=False, want=True):
+    def accumulate(self, first_pass=False, want=True, out=None):
+        """out = (count[D], sum_x[D, d], sum_xx[D, d]) f64 arrays to fill (e.g. pinned_empty buffers)."""
         D, d = self.D, self.dim
-        cnt = np.empty(D, np.float64) if want else None
-        sx = np.empty((D, d), np.float64) if want else None
-        sxx = np.empty((D, d), np.float64) if want else None
+        if out is not None:
+            cnt, sx, sxx = out
+            assert cnt.shape == (D,) and sx.shape == (D, d) and sxx.shape == (D, d)
+            assert all(a.dtype == np.float64 and a.flags.c_contiguous for a in out)
+        else:
+            cnt = np.empty(D, np.float64) if want else None
+            sx = np.empty((D, d), np.float64) if want else None
+            sxx = np.empty((D, d), np.float64) if want else None
         ssum = np.zeros(1, np.float64)
         self._ck(self.L.sgmm_accumulate(self.h, int(first_pass), _ptr(cnt, C.c_double), _ptr(sx, C.c_double),
                                         _ptr(sxx, C.c_double), _ptr(ssum, C.c_double)))

@@ -24,6 +24,8 @@
 // rescan of the state (k_tc_rescan).  Results are therefore bit-identical to the reference; the tensor cores
 // only decide where f64 work goes.
 #include <cuda.h>
+#include <algorithm>
+#include <vector>
 
 #include "sgmm_internal.cuh"
 
@@ -208,6 +210,7 @@ struct TcParams {
   // per cell, indexed like the emission matrix (gathered) / [frame - f0][state] (dense):
   // column of the certified minimum within the state's (padded) density list, or kUncertain
   uint32_t* cand;
+  unsigned long long* prof;   // cycle profile (debug & 32), else NULL
 };
 constexpr uint32_t kUncertain = 0x80000000u;
 constexpr uint32_t kAccCol = 128;    // TMEM: columns [0, 128) hold Ahi of both halves, then three 128-column accumulators
@@ -296,7 +299,12 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
     }
   } else if (warp == 1) {
     // ===== MMA issuer: the whole warp walks the loop, one elected lane issues =====
+    const bool prof = p.prof != nullptr;
+    long long w_a = 0, w_full = 0, w_tempty = 0, c0 = 0, c1 = 0;
+    unsigned long long g0 = 0;
+    if (prof) { c0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0)); }
     mbar_wait(a_full, 0);
+    if (prof) { c1 = clock64(); w_a = c1 - c0; }
     tc_fence_after();
     uint32_t it = 0;
     for (uint32_t j = 0; j < nu; j++) {
@@ -304,7 +312,9 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
       for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, it++) {
         const uint32_t N = p.tile_info[t].y;
         const uint32_t stage = it % nstage;
+        if (prof) c1 = clock64();
         if (!(p.debug & 16)) mbar_wait(&full[stage], (it / nstage) & 1);
+        if (prof) w_full += clock64() - c1;
         const uint32_t idesc = make_idesc_tf32(BM, N);
         const uint64_t bhi = make_desc_sw32(smem_u32(sB + stage * p.stage_bytes));
         const uint64_t blo = bhi + (uint64_t)ks * kstride;   // every k-step block is 128 rows (4 KB) whatever N
@@ -312,7 +322,9 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           // (tile, half) units rotate through the three accumulators: the tensor pipe may run a unit ahead of the
           // epilogue that drains the previous unit of the same half
           const uint32_t unit = it * nh + h, buf = unit % kNumAcc, use = unit / kNumAcc;
+          if (prof) c1 = clock64();
           if (!(p.debug & 8)) mbar_wait(&tempty[buf], (use & 1) ^ 1);
+          if (prof) w_tempty += clock64() - c1;
           tc_fence_after();
           const uint32_t d = tmem_base + kAccCol + buf * BN;
           const uint32_t ahi = tmem_base + h * KP;
@@ -335,6 +347,21 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           tc_commit_elect(&tfull[buf]);
         }
       }
+    }
+    if (prof && lane == 0) {
+      // the last accumulator's completion marks the end of the tensor work of this CTA
+      const uint32_t last = it * nh - 1;
+      mbar_wait(&tfull[last % kNumAcc], (last / kNumAcc) & 1);
+      const long long c2 = clock64();
+      unsigned long long g1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
+      atomicAdd(p.prof + 1, (unsigned long long)(c2 - c0));      // issue-warp lifetime, cycles
+      atomicAdd(p.prof + 2, g1 - g0);                            // the same in ns
+      atomicAdd(p.prof + 3, (unsigned long long)w_a);            // waiting for the A rows
+      atomicAdd(p.prof + 4, (unsigned long long)w_full);         // waiting for B stages
+      atomicAdd(p.prof + 5, (unsigned long long)w_tempty);       // waiting for the epilogue to drain an accumulator
+      atomicAdd(p.prof + 6, (unsigned long long)it * nh * 3 * ks);   // MMAs issued
+      atomicAdd(p.prof + 7, 1ull);                               // CTAs
     }
   } else {
     // ===== epilogue warps: (half, lane quarter, column part) =====
@@ -368,6 +395,8 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
       const float2 xn = p.xnorm[min(row0 + row, p.n_frames - 1)];
       float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
       uint32_t it = 0;
+      long long e_wait = 0;
+      const long long e_start = p.prof ? clock64() : 0;
       for (uint32_t j = 0; j < nu; j++) {
         const uint32_t s = ulist ? ulist[j] : j;
         const float4 g = __ldg(p.sguard + s);
@@ -378,7 +407,10 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
         for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, it++) {
           const uint32_t N = p.tile_info[t].y;
           const uint32_t unit = it * nh + group, buf = unit % kNumAcc, use = unit / kNumAcc;
+          long long e0 = 0;
+          if (p.prof) e0 = clock64();
           mbar_wait(&tfull[buf], use & 1);
+          if (p.prof) e_wait += clock64() - e0;
           tc_fence_after();
           const uint32_t tcol = tlane + kAccCol + buf * BN;
           const uint32_t c_lo = part * 64, c_hi = min(N, c_lo + 64);
@@ -461,6 +493,11 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
             p.cand[out_base + (uint64_t)row * out_stride + j] = certain ? (uint32_t)Bidx : kUncertain;
           }
         }
+      }
+      if (p.prof && lane == 0 && quarter == 0) {   // one lane per (half, part) warp group
+        atomicAdd(p.prof + 8 + part, (unsigned long long)e_wait);                  // epilogue waiting for the tensor pipe
+        atomicAdd(p.prof + 10 + part, (unsigned long long)(clock64() - e_start));  // epilogue loop lifetime
+        atomicAdd(p.prof + 12, 1ull);
       }
     }
   }
@@ -697,15 +734,23 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   int nstage = 1;
   while (nstage < sgmm_tc::kMaxStage && tc_smem(stage_bytes, nhalf, nstage + 1) <= kSmemLimit) nstage++;
   const uint32_t rows_per_task = 128u * nhalf;
-  // A operand (once per feature upload / model shape)
-  if (!c->tc_A_valid) {
+  // Work is cut into frame ranges.  Normally there is one; while a chunked feature upload is in flight
+  // (option "async_upload") there is one per chunk, each launched behind that chunk's copy event, so that the
+  // GEMM of the first chunks runs under the copies of the later ones.
+  struct Range { uint64_t f_end; int ev; };
+  std::vector<Range> ranges;
+  if (!dense && c->feat_pending && !c->tc_A_valid) {
+    for (int i = 0; i < c->feat_pending; i++) ranges.push_back({c->feat_chunk_end[i], i});
+  } else {
+    if (sgmm_wait_features(c)) return 1;
+    ranges.push_back({c->n_frames, -1});
+  }
+  c->feat_pending = 0;
+  const bool need_prep = !c->tc_A_valid;
+  if (need_prep) {
     SGMM_CHECK(c, c->d_Ahi.reserve((size_t)c->n_frames * KP));
     SGMM_CHECK(c, c->d_Alo.reserve((size_t)c->n_frames * KP));
     SGMM_CHECK(c, c->d_xnorm.reserve(c->n_frames));
-    const unsigned grid = (unsigned)((c->n_frames + 7) / 8);
-    k_tc_prep<<<grid, 256, 0, c->stream>>>(c->d_x.p, c->n_frames, c->dim, c->tc_full, KP, c->d_Ahi.p, c->d_Alo.p,
-                                           c->d_xnorm.p);
-    SGMM_LAUNCH_CHECK(c);
     c->tc_A_valid = true;
   }
   const uint64_t n_cells = dense ? dense_nframes * c->n_states : c->E_elems;
@@ -721,6 +766,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   TcParams p{};
   p.ksteps = ks; p.nstage = (uint32_t)nstage; p.stage_bytes = stage_bytes; p.nhalf = (uint32_t)nhalf;
   p.debug = (uint32_t)c->tc_debug;
+  p.prof = (c->tc_debug & 32) ? c->d_fallbacks.p : nullptr;
   p.Ahi = c->d_Ahi.p; p.Alo = c->d_Alo.p; p.n_frames = c->n_frames;
   p.Bimg = c->d_Bimg.p; p.tile_first = c->d_tile_first.p; p.tile_info = c->d_tile_info.p;
   p.xnorm = c->d_xnorm.p; p.sguard = c->d_sguard_tc.p; p.eps = c->tc_eps;
@@ -731,21 +777,6 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
   const size_t smem = tc_smem(stage_bytes, nhalf, nstage);
-  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER], c->stream);
-  if (ks == 5) {          // d = 33 pooled (BASELINE configs 2-4)
-    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_tc_gemm<5><<<(unsigned)n_tasks, 576, smem, c->stream>>>(p);
-  } else if (ks == 7) {   // d = 48 pooled (config 5), d = 25 unpooled
-    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_tc_gemm<7><<<(unsigned)n_tasks, 576, smem, c->stream>>>(p);
-  } else {
-    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_tc_gemm<0><<<(unsigned)n_tasks, 576, smem, c->stream>>>(p);
-  }
-  SGMM_LAUNCH_CHECK(c);
-  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER + 1], c->stream);
-  c->stage_ms[SGMM_T_SCORE_FILTER] = -1.f;
-
   RefineParams r{};
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
   r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;
@@ -757,28 +788,78 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   r.out = dense ? d_scores : c->d_E.p; r.argmin = dense ? d_argmin : nullptr;
   r.amin16 = dense ? nullptr : c->d_Amin.p;
   r.rescan = c->d_rescan.p; r.cap = cap; r.fallback_count = c->d_fallbacks.p;
-  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE], c->stream);
-  r.tasks = c->d_tasks128.p;
-  const unsigned rgrid = dense ? (unsigned)((dense_nframes + 127) / 128) : (unsigned)c->n_tasks128;
+  const uint4* gemm_tasks = nhalf == 2 ? c->d_tasks256.p : c->d_tasks128.p;
+  const std::vector<uint64_t>& gemm_end = nhalf == 2 ? c->h_t256_end : c->h_t128_end;
   r.pooled = c->tc_full ? 0 : 1;
-  // shared memory: 128 feature rows + (pooled) one inverse-variance row per state of the granule
+  // refinement shared memory: 128 feature rows + (pooled) one inverse-variance row per state of the granule
   const size_t rsm = 128 * (2 * (size_t)c->npair + 2) * sizeof(float) +
                      (r.pooled ? (size_t)(dense ? c->n_states : c->max_uniq) * c->dimP * sizeof(double) : 0);
   if (rsm > 200 * 1024) r.pooled = 0;
   const size_t rsm_used = r.pooled ? rsm : 128 * (2 * (size_t)c->npair + 2) * sizeof(float);
-  switch (c->npair) {   // common feature dimensions get a fully unrolled row walk
-    case 16:   // d = 32, 33
-      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
-      k_tc_refine<16><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
-    case 24:   // d = 48, 49
-      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
-      k_tc_refine<24><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
-    case 12:   // d = 24, 25
-      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
-      k_tc_refine<12><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
-    default: k_tc_refine<0><<<rgrid, 256, 0, c->stream>>>(r); break;
+  const bool one = ranges.size() == 1;
+  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER], c->stream);
+  uint64_t f_prev = 0, g_prev = 0;
+  // several ranges: each on its own side stream, so that the next range's CTAs fill the SMs that the tail of the
+  // previous one leaves idle; all of them rejoin the main stream before the rescan
+  if (!one) SGMM_CHECK(c, cudaEventRecord(c->ev_fork, c->stream));
+  static_assert(sgmm_ctx::kFeatChunks <= sgmm_ctx::kAux, "one side stream per upload chunk");
+  for (size_t ri = 0; ri < ranges.size(); ri++) {
+    const Range& rg = ranges[ri];
+    cudaStream_t st = one ? c->stream : c->aux[ri];
+    if (!one) SGMM_CHECK(c, cudaStreamWaitEvent(st, c->ev_fork, 0));
+    if (rg.ev >= 0) SGMM_CHECK(c, cudaStreamWaitEvent(st, c->feat_ev[rg.ev], 0));
+    if (need_prep && rg.f_end > f_prev) {
+      const uint64_t nf = rg.f_end - f_prev;
+      k_tc_prep<<<(unsigned)((nf + 7) / 8), 256, 0, st>>>(c->d_x.p + f_prev * c->dim, nf, c->dim, c->tc_full, KP,
+                                                                c->d_Ahi.p + f_prev * KP, c->d_Alo.p + f_prev * KP,
+                                                                c->d_xnorm.p + f_prev);
+      SGMM_LAUNCH_CHECK(c);
+    }
+    f_prev = rg.f_end;
+    // tasks whose frames have all arrived
+    const uint64_t g_end = dense ? n_tasks : std::upper_bound(gemm_end.begin(), gemm_end.end(), rg.f_end) - gemm_end.begin();
+    if (g_end > g_prev) {
+      const unsigned grid = (unsigned)(g_end - g_prev);
+      p.tasks = dense ? nullptr : gemm_tasks + g_prev;
+      if (ks == 5) {          // d = 33 pooled (BASELINE configs 2-4)
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm<5><<<grid, 576, smem, st>>>(p);
+      } else if (ks == 7) {   // d = 48 pooled (config 5), d = 25 unpooled
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm<7><<<grid, 576, smem, st>>>(p);
+      } else {
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm<0><<<grid, 576, smem, st>>>(p);
+      }
+      SGMM_LAUNCH_CHECK(c);
+      g_prev = g_end;
+    }
+    if (!one) SGMM_CHECK(c, cudaEventRecord(c->ev_join[ri], st));
   }
-  SGMM_LAUNCH_CHECK(c);
+  if (!one)
+    for (size_t ri = 0; ri < ranges.size(); ri++) SGMM_CHECK(c, cudaStreamWaitEvent(c->stream, c->ev_join[ri], 0));
+  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER + 1], c->stream);
+  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE], c->stream);
+  // refinement of every cell in one launch (alternating GEMM and refinement launches per range wastes the SMs at
+  // every switch: a GEMM CTA needs the whole shared memory of an SM, so it waits for all refinement CTAs there)
+  {
+    const unsigned rgrid = dense ? (unsigned)((dense_nframes + 127) / 128) : (unsigned)c->n_tasks128;
+    r.tasks = dense ? nullptr : c->d_tasks128.p;
+    switch (c->npair) {   // common feature dimensions get a fully unrolled row walk
+      case 16:   // d = 32, 33
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
+        k_tc_refine<16><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
+      case 24:   // d = 48, 49
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
+        k_tc_refine<24><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
+      case 12:   // d = 24, 25
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsm_used));
+        k_tc_refine<12><<<rgrid, 256, rsm_used, c->stream>>>(r); break;
+      default: k_tc_refine<0><<<rgrid, 256, 0, c->stream>>>(r); break;
+    }
+    SGMM_LAUNCH_CHECK(c);
+  }
+  c->stage_ms[SGMM_T_SCORE_FILTER] = -1.f;
   k_tc_rescan<<<148 * 16, 256, 0, c->stream>>>(r);
   SGMM_LAUNCH_CHECK(c);
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE + 1], c->stream);

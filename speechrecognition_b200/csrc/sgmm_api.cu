@@ -73,6 +73,8 @@ int sgmm_create(int device, sgmm_ctx** out) {
   for (auto& st : c->aux) cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
   cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
   for (auto& ev : c->ev_join) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+  cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+  for (auto& ev : c->feat_ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
   *out = c;
   return 0;
 }
@@ -101,6 +103,8 @@ void sgmm_destroy(sgmm_ctx* c) {
   for (auto& st : c->aux) if (st) cudaStreamDestroy(st);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   for (auto& ev : c->ev_join) if (ev) cudaEventDestroy(ev);
+  if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+  for (auto& ev : c->feat_ev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -289,8 +293,8 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
     c->tc_A_valid = false;
   }
   if (!c->d_fallbacks.p) {
-    SGMM_CHECK(c, c->d_fallbacks.reserve(1));
-    SGMM_CHECK(c, cudaMemsetAsync(c->d_fallbacks.p, 0, sizeof(unsigned long long), c->stream));
+    SGMM_CHECK(c, c->d_fallbacks.reserve(16));   // [0] rescanned cells, [1..15] k_tc_gemm cycle profile (tc_debug & 32)
+    SGMM_CHECK(c, cudaMemsetAsync(c->d_fallbacks.p, 0, 16 * sizeof(unsigned long long), c->stream));
   }
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));  // the staging vectors die here
   c->dv4 = dv4;
@@ -304,13 +308,33 @@ int sgmm_set_features(sgmm_ctx* c, const float* x, uint64_t n_frames, uint32_t d
   if (!c) return 1;
   cudaSetDevice(c->device);
   begin_call(c);
-  SGMM_CHECK(c, c->d_x.reserve((size_t)n_frames * dim + 8));
-  {
-    StageTimer st(c, SGMM_T_H2D);
-    SGMM_CHECK(c, cudaMemcpyAsync(c->d_x.p, x, (size_t)n_frames * dim * sizeof(float), cudaMemcpyHostToDevice,
-                                  c->stream));
+  if (c->feat_pending) {   // a queued upload nobody consumed: let it finish before its target is reused
+    SGMM_CHECK(c, cudaStreamSynchronize(c->copy_stream));
+    c->feat_pending = 0;
   }
-  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  SGMM_CHECK(c, c->d_x.reserve((size_t)n_frames * dim + 8));
+  if (c->async_upload && n_frames >= 64 * (uint64_t)sgmm_ctx::kFeatChunks) {
+    // every compute entry point ends with a stream synchronize, so nothing is reading d_x now.  The first chunk
+    // is the smallest (the pipeline starts early), the others are equal.
+    const int n = c->feat_chunks;
+    uint64_t f0 = 0;
+    for (int i = 0; i < n; i++) {
+      const uint64_t f1 = (i + 1 == n) ? n_frames : (n_frames * (2 * (uint64_t)i + 1)) / (2 * (uint64_t)n - 1);
+      SGMM_CHECK(c, cudaMemcpyAsync(c->d_x.p + f0 * dim, x + f0 * dim, (f1 - f0) * dim * sizeof(float),
+                                    cudaMemcpyHostToDevice, c->copy_stream));
+      SGMM_CHECK(c, cudaEventRecord(c->feat_ev[i], c->copy_stream));
+      c->feat_chunk_end[i] = f1;
+      f0 = f1;
+    }
+    c->feat_pending = n;
+  } else {
+    {
+      StageTimer st(c, SGMM_T_H2D);
+      SGMM_CHECK(c, cudaMemcpyAsync(c->d_x.p, x, (size_t)n_frames * dim * sizeof(float), cudaMemcpyHostToDevice,
+                                    c->stream));
+    }
+    SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  }
   c->n_frames = n_frames; c->feat_dim = dim;
   c->have_alignment = false;
   c->ali_has_cols = false;
@@ -333,6 +357,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   std::vector<uint16_t> p2u(aut_off[U]);
   std::vector<uint64_t> E_off(U + 1, 0);
   std::vector<uint4> tasks, tasks64, tasks128, tasks256;
+  std::vector<uint64_t> t128_end, t256_end;
   std::map<std::pair<int, size_t>, ViterbiClass> classes;
   uint32_t max_state = 0, max_uniq = 0;
   for (uint32_t u = 0; u < U; u++) {
@@ -357,8 +382,14 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     E_off[u + 1] = E_off[u] + (uint64_t)T * ncol[u];
     for (uint32_t t0 = 0; t0 < T; t0 += 32) tasks.push_back(make_uint4(u, t0, 0, 0));
     for (uint32_t t0 = 0; t0 < T; t0 += 64) tasks64.push_back(make_uint4(u, t0, 0, 0));
-    for (uint32_t t0 = 0; t0 < T; t0 += 128) tasks128.push_back(make_uint4(u, t0, 0, 0));
-    for (uint32_t t0 = 0; t0 < T; t0 += 256) tasks256.push_back(make_uint4(u, t0, 0, 0));
+    for (uint32_t t0 = 0; t0 < T; t0 += 128) {
+      tasks128.push_back(make_uint4(u, t0, 0, 0));
+      t128_end.push_back(frame_off[u] + std::min(T, t0 + 128));
+    }
+    for (uint32_t t0 = 0; t0 < T; t0 += 256) {
+      tasks256.push_back(make_uint4(u, t0, 0, 0));
+      t256_end.push_back(frame_off[u] + std::min(T, t0 + 256));
+    }
     int C = 0;
     for (int cc : kViterbiC) if ((uint32_t)cc * 32 >= S) { C = cc; break; }
     size_t sm = viterbi_smem(T, S, ncol[u], C);
@@ -392,6 +423,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->max_aut_state = max_state; c->max_uniq = max_uniq;
   c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->n_tasks128 = tasks128.size(); c->n_tasks256 = tasks256.size(); c->E_elems = E_off[U];
+  c->h_t128_end.swap(t128_end); c->h_t256_end.swap(t256_end);
   c->h_frame_off.assign(frame_off, frame_off + U + 1);
   c->h_aut_off.assign(aut_off, aut_off + U + 1);
   return 0;
@@ -487,6 +519,12 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   }
   if (!strcmp(key, "rescore_cache")) { c->use_cache = value != 0; return 0; }
   if (!strcmp(key, "tc_debug")) { c->tc_debug = (int)value; return 0; }
+  if (!strcmp(key, "async_upload")) { c->async_upload = value != 0; return 0; }
+  if (!strcmp(key, "upload_chunks")) {
+    if (value < 1 || value > sgmm_ctx::kFeatChunks) SGMM_FAIL(c, "set_option: upload_chunks out of range");
+    c->feat_chunks = (int)value;
+    return 0;
+  }
   if (!strcmp(key, "tc_halves")) {
     if (value < 0 || value > 2) SGMM_FAIL(c, "set_option: tc_halves must be 0 (auto), 1 or 2");
     c->tc_halves = (int)value;
@@ -509,6 +547,16 @@ int sgmm_get_counter(sgmm_ctx* c, const char* key, int64_t* value) {
     return 0;
   }
   if (!strcmp(key, "scorer")) { *value = sgmm_effective_scorer(c); return 0; }
+  if (!strncmp(key, "tc_prof", 7)) {   // cycle counters of the instrumented GEMM (option tc_debug & 32); read-and-clear
+    const int i = atoi(key + 7);
+    if (i < 1 || i > 15 || !c->d_fallbacks.p) SGMM_FAIL(c, "get_counter: tc_prof index out of range");
+    unsigned long long v = 0;
+    SGMM_CHECK(c, cudaMemcpyAsync(&v, c->d_fallbacks.p + i, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+    SGMM_CHECK(c, cudaMemsetAsync(c->d_fallbacks.p + i, 0, sizeof(v), c->stream));
+    SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+    *value = (int64_t)v;
+    return 0;
+  }
   SGMM_FAIL(c, std::string("get_counter: unknown key ") + key);
 }
 

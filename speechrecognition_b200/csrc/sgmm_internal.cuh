@@ -84,6 +84,15 @@ struct sgmm_ctx {
   uint64_t n_frames = 0;
   uint32_t feat_dim = 0;
   DevBuf<float> d_x;
+  // option "async_upload": sgmm_set_features returns once the chunked copies are queued on copy_stream; the GEMM
+  // scorer consumes the chunks as they land (k_score_tc.cu), every other consumer waits for the last one
+  static constexpr int kFeatChunks = 8;
+  bool async_upload = false;
+  int feat_chunks = 8;                        // option "upload_chunks" (1..kFeatChunks)
+  int feat_pending = 0;                       // chunks of the upload in flight (0: features resident)
+  uint64_t feat_chunk_end[kFeatChunks] = {0};   // exclusive end frame of every chunk
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t feat_ev[kFeatChunks] = {nullptr};
 
   // ---- corpus
   uint32_t n_utts = 0, max_aut_state = 0, max_uniq = 0;   // max_uniq: most distinct states in one automaton
@@ -94,6 +103,7 @@ struct sgmm_ctx {
   DevBuf<uint16_t> d_pos2uniq;
   DevBuf<uint4> d_tasks128, d_tasks256;
   uint64_t n_tasks128 = 0, n_tasks256 = 0;
+  std::vector<uint64_t> h_t128_end, h_t256_end;   // exclusive end frame of every task (ascending)
   int tc_debug = 0;                // option "tc_debug": timing experiments (k_score_tc.cu), never set in production
   int tc_halves = 0;               // option "tc_halves": 0 auto, 1 / 2 = frame halves (128 rows each) per GEMM CTA
   DevBuf<uint4> d_tasks, d_tasks64;   // emission warp-tasks {utt, t0, 0, 0}: 32-frame and 64-frame granules
@@ -163,6 +173,14 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
                            uint32_t* d_argmin);
 int sgmm_effective_scorer(const sgmm_ctx* c);
 int sgmm_launch_viterbi(sgmm_ctx* c, int tdp_convention);
+// make the compute stream wait for a queued feature upload (option "async_upload"); no-op when resident
+inline int sgmm_wait_features(sgmm_ctx* c) {
+  if (c->feat_pending) {
+    SGMM_CHECK(c, cudaStreamWaitEvent(c->stream, c->feat_ev[c->feat_pending - 1], 0));
+    c->feat_pending = 0;
+  }
+  return 0;
+}
 int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass);
 int sgmm_launch_rescore_cached(sgmm_ctx* c);
 int sgmm_launch_accumulate(sgmm_ctx* c);

@@ -27,7 +27,8 @@ void reset_stage(sgmm_ctx* c) {
 // emission scoring through whichever scorer is selected
 int launch_emission_any(sgmm_ctx* c, bool dense, uint64_t f0, uint64_t nf, double* scores, uint32_t* argmin) {
   const int sc = sgmm_effective_scorer(c);
-  if (sc == 3) return sgmm_launch_emission_tc(c, dense, f0, nf, scores, argmin);
+  if (sc == 3) return sgmm_launch_emission_tc(c, dense, f0, nf, scores, argmin);   // consumes upload chunks itself
+  if (sgmm_wait_features(c)) return 1;
   if (sc == 2) {
     if (dense) return sgmm_launch_emission_ffma(c, nullptr, (nf + 63) / 64, true, f0, nf, scores, argmin);
     return sgmm_launch_emission_ffma(c, c->d_tasks64.p, c->n_tasks64, false, 0, 0, nullptr, nullptr);
@@ -140,6 +141,7 @@ int sgmm_set_alignment(sgmm_ctx* c, const sgmm_alignment_item* alignment, uint64
 static int rescore_common(sgmm_ctx* c, bool first_pass) {
   if (require(c, true, true, false)) return 1;
   if (!c->have_alignment) SGMM_FAIL(c, "no alignment resident: call sgmm_align or sgmm_set_alignment first");
+  if (sgmm_wait_features(c)) return 1;
   SGMM_CHECK(c, c->d_fdens.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_fscore.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_cnt_u32.reserve(c->Dtot + 2));

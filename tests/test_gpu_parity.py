@@ -270,3 +270,40 @@ def test_accumulate_after_align_uses_cached_scores(small25, scorer):
     c = ctx.accumulate(first_pass=False)
     for u, v in zip(a[:3], c[:3]):
         assert np.array_equal(u, v)
+
+
+@pytest.mark.parametrize("scorer", ["f64", "ffma", "tc"])
+def test_async_upload_same_results(scorer):
+    """Option async_upload: sgmm_set_features queues chunked copies from pinned memory and returns; the GEMM scorer
+    consumes chunk by chunk, every other consumer waits for the last chunk.  Alignment, costs and statistics
+    must be bit-identical to the synchronous upload."""
+    from speechrecognition_b200 import capi
+    O, corp, ali = helpers.trained_oracle(dim=33, n_utts=40, splits=3, seed=5, min_obs=10, dens_gen=4)
+    ctx = helpers.gpu_context(O, corp, 33)
+    ctx.set_option("scorer", SCORERS[scorer])
+    want_ali, want_costs = ctx.align()
+    want = ctx.accumulate(first_pass=False)
+    x_pin = capi.pinned_empty(corp["x"].shape, np.float32)
+    x_pin[...] = corp["x"]
+    ctx.set_option("async_upload", 1)
+    for _ in range(2):                       # second round: the chunks overwrite a buffer that is already resident
+        ctx.set_features(x_pin)
+        got_ali, got_costs = ctx.align()
+        got = ctx.accumulate(first_pass=False)
+        assert np.array_equal(got_ali, want_ali) and np.array_equal(got_costs, want_costs)
+        for u, v in zip(got[:3], want[:3]):
+            assert np.array_equal(u, v)
+        assert got[3] == want[3]
+    # upload followed directly by a consumer that is not the scorer
+    ctx.set_features(x_pin)
+    ctx.set_alignment(want_ali)
+    again = ctx.accumulate(first_pass=False)
+    for u, v in zip(again[:3], want[:3]):
+        assert np.array_equal(u, v)
+    ctx.set_features(x_pin)
+    s_async, a_async = ctx.score_all(0, 64)
+    ctx.set_option("async_upload", 0)
+    ctx.set_features(x_pin)
+    s_sync, a_sync = ctx.score_all(0, 64)
+    assert np.array_equal(s_async, s_sync) and np.array_equal(a_async, a_sync)
+    ctx.close()

@@ -142,6 +142,65 @@ __global__ void k_mma(int n, uint32_t N, long long* cycles) {
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_ptr), "r"(512));
 }
 
+// ---- the GEMM kernel's issue pattern on every SM: units of `ks` k-steps x 3 passes into rotating accumulators.
+// MODE 0: all three passes A-from-shared (SS); 1: all A-from-TMEM (TS); 2: two TS passes + one SS pass (the kernel's mix)
+template <int MODE>
+__global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, unsigned long long* ns) {
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t tmem_ptr;
+  __shared__ uint64_t bar;
+  uint32_t x = seed + threadIdx.x * 2654435761u + blockIdx.x;
+  for (int i = threadIdx.x; i < 3 * 8 * 4096 / 4; i += blockDim.x) {
+    x = x * 1664525u + 1013904223u;
+    reinterpret_cast<float*>(sm)[i] = seed ? (float)(int)(x >> 20) * 1e-3f : 0.f;
+  }
+  const int warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&bar)), "r"(1));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_ptr)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  if (warp == 0) {   // converged warp, one elected lane issues (the kernel's pattern)
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+    const uint64_t alo = desc_sw32(smem_u32(sm)), bhi = desc_sw32(smem_u32(sm) + 8 * 4096), blo = desc_sw32(smem_u32(sm) + 16 * 4096);
+    unsigned long long g0, g1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
+    const long long t0 = clock64();
+    for (int u = 0; u < units; u++) {
+      const uint32_t d = tmem_ptr + 128 + (u % 3) * 128;
+      for (int pass = 0; pass < 3; pass++) {
+        const bool ts = MODE == 1 || (MODE == 2 && pass < 2);
+        const uint64_t b = pass == 1 ? blo : bhi;
+        for (int kk = 0; kk < ks; kk++) {
+          const uint32_t acc = (pass | kk) ? 1 : 0;
+          if (ts)
+            asm volatile("{\n\t.reg .pred p, pe;\n\telect.sync _|pe, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
+                         "r"(tmem_ptr + kk * 8), "l"(b + kk * 256), "r"(idesc), "r"(acc) : "memory");
+          else
+            asm volatile("{\n\t.reg .pred p, pe;\n\telect.sync _|pe, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+                         "l"(alo + kk * 256), "l"(b + kk * 256), "r"(idesc), "r"(acc) : "memory");
+        }
+      }
+    }
+    asm volatile("{\n\t.reg .pred pe;\n\telect.sync _|pe, 0xffffffff;\n\t@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(&bar)) : "memory");
+    asm volatile("{\n\t.reg .pred p;\n\tW2:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra D2;\n\tbra W2;\n\tD2:\n\t}" ::"r"(
+                     smem_u32(&bar)), "r"(0) : "memory");
+    const long long t1 = clock64();
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
+    if (threadIdx.x == 0) { cycles[blockIdx.x] = t1 - t0; ns[blockIdx.x] = g1 - g0; }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_ptr), "r"(512));
+}
+
 int main() {
   long long* d_cyc; float* d_sink;
   cudaMalloc(&d_cyc, 1024 * sizeof(long long)); cudaMalloc(&d_sink, 4);
@@ -186,5 +245,29 @@ int main() {
     }
   }
   printf("cudaGetLastError: %s\n", cudaGetErrorString(cudaGetLastError()));
+  {
+    unsigned long long* d_ns; cudaMalloc(&d_ns, 1024 * 8);
+    static long long hc[1024]; static unsigned long long hn[1024];
+    const char* mn[] = {"SS,SS,SS", "TS,TS,TS", "TS,TS,SS"};
+    const size_t smem = 3 * 8 * 4096 + 1024;
+    cudaFuncSetAttribute(k_mma_mix<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_mma_mix<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(k_mma_mix<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    for (int grid : {1, 148})
+      for (uint32_t seed : {0u, 7u})
+        for (int mode = 0; mode < 3; mode++) {
+          const int units = 4000, ks = 5;
+          if (mode == 0) k_mma_mix<0><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns);
+          if (mode == 1) k_mma_mix<1><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns);
+          if (mode == 2) k_mma_mix<2><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns);
+          cudaDeviceSynchronize();
+          cudaMemcpy(hc, d_cyc, grid * 8, cudaMemcpyDeviceToHost); cudaMemcpy(hn, d_ns, grid * 8, cudaMemcpyDeviceToHost);
+          long long mc = 0; unsigned long long mns = 0;
+          for (int i = 0; i < grid; i++) { if (hc[i] > mc) mc = hc[i]; if (hn[i] > mns) mns = hn[i]; }
+          printf("mma mix %s grid=%3d data=%s: %.1f cycles per MMA, %.2f GHz\n", mn[mode], grid, seed ? "random" : "zeros",
+                 mc / (double)(units * 3 * ks), (double)mc / (double)mns);
+        }
+    printf("cudaGetLastError: %s\n", cudaGetErrorString(cudaGetLastError()));
+  }
   return 0;
 }
