@@ -83,6 +83,22 @@ int sgmm_score_all(sgmm_ctx* ctx, uint64_t f0, uint64_t f1, double* scores, uint
  * receive host copies.  An utterance whose end state is unreachable (S > 2T-1) gets cost +inf. */
 int sgmm_align(sgmm_ctx* ctx, int tdp_convention, sgmm_alignment_item* alignment, double* costs);
 
+/* Recognition lexicon: word w is the linear HMM word_states[word_off[w] .. word_off[w+1]) (automaton positions ->
+ * state ids), as Lexicon::get_automaton_for_word returns it (Lexicon.hpp:16-33, Lexicon.cpp:11-23,70-85).
+ * silence_word: Lexicon::silence_idx().  At most 255 words of at most 255 positions. */
+int sgmm_set_lexicon(sgmm_ctx* ctx, uint32_t n_words, const uint32_t* word_off, const uint32_t* word_states,
+                     uint32_t silence_word);
+
+/* Replaces Recognizer::recognizeSequence_pruned (Recognizer.cpp:103-232) and the per-segment OpenMP loop of
+ * Recognizer::recognize (:46-47): time-synchronous word-loop Viterbi over the lexicon with the TDPs of sgmm_set_tdp
+ * (destination-state convention, :167), word_penalty ("word-penalty", 0 for silence) and beam am_threshold
+ * ("am-threshold"; >= 1e30 disables pruning), for every utterance frame_off[u] .. frame_off[u+1] of the resident
+ * features.  words[word_off_out[u] .. word_off_out[u+1]) = the recognised word ids (silence dropped), scores[u]
+ * (optional) = score of the best word end at the last frame.  Fails if more than max_words words are produced. */
+int sgmm_recognize(sgmm_ctx* ctx, uint32_t n_utts, const uint64_t* frame_off, double word_penalty,
+                   double am_threshold, uint32_t* words, uint64_t max_words, uint32_t* word_off_out /* [n_utts+1] */,
+                   double* scores /* [n_utts] or NULL */);
+
 /* Upload an alignment produced elsewhere (e.g. the linear segmentation of Training.cpp:85-99). */
 int sgmm_set_alignment(sgmm_ctx* ctx, const sgmm_alignment_item* alignment, uint64_t n_frames);
 

@@ -172,6 +172,20 @@ class Oracle:
                                _p(states, C.c_uint32), _p(costs, C.c_double), int(threads))
         return states, costs
 
+    def recognize(self, x, word_off, word_states, silence_word=0, word_penalty=10.0, am_threshold=20.0):
+        """Recognizer::recognizeSequence_pruned over one utterance; returns (words, score of the best final word end)."""
+        x = _f32(x).reshape(-1, self.dim)
+        word_off = np.ascontiguousarray(word_off, np.uint32)
+        word_states = np.ascontiguousarray(word_states, np.uint32)
+        out = np.zeros(len(x) + 1, np.uint32)
+        score = C.c_double(0.0)
+        self.L.orc_recognize.restype = C.c_uint64
+        n = self.L.orc_recognize(self.h, *self._tdp_args(), _p(x, C.c_float), C.c_uint64(len(x)),
+                                 C.c_uint32(len(word_off) - 1), _p(word_off, C.c_uint32), _p(word_states, C.c_uint32),
+                                 C.c_uint32(silence_word), C.c_double(word_penalty), C.c_double(am_threshold),
+                                 _p(out, C.c_uint32), C.c_uint64(len(out)), C.byref(score))
+        return out[:n].copy(), float(score.value)
+
 
 class Reference:
     """The unmodified reference (oracle/_ref).  Same methods as ``Oracle``; indices are converted to the
@@ -292,6 +306,14 @@ class Reference:
                                _p(automata, C.c_uint16), _p(aut_off, C.c_uint32), _p(states, C.c_uint16),
                                _p(costs, C.c_double))
         return states.astype(np.uint32), costs
+
+    def edit_distance(self, ref, hyp):
+        r = np.ascontiguousarray(ref, np.uint16)
+        h = np.ascontiguousarray(hyp, np.uint16)
+        out = np.zeros(4, np.uint64)
+        self.L.ref_edit_distance(self.h, _p(r, C.c_uint16), C.c_uint64(len(r)), _p(h, C.c_uint16), C.c_uint64(len(h)),
+                                 _p(out, C.c_uint64))
+        return tuple(int(v) for v in out)
 
     def recognize(self, x):
         T = _f32(x).reshape(-1, self.dim).shape[0]

@@ -244,4 +244,14 @@ uint64_t ref_recognize(void* h, const float* x, uint64_t T, uint32_t* out_words,
   return out.size();
 }
 
+// Recognizer::editDistance (Recognizer.cpp:332-388): out = {total, substitutions, insertions, deletions}
+void ref_edit_distance(void* h, const uint16_t* ref, uint64_t n_ref, const uint16_t* hyp, uint64_t n_hyp, uint64_t* out) {
+  RefModel* m = static_cast<RefModel*>(h);
+  Lexicon lexicon = build_sietill_lexicon();
+  Recognizer rec(*m->config, lexicon, *m->mixtures, *m->tdp);
+  std::vector<WordIdx> r(ref, ref + n_ref), hy(hyp, hyp + n_hyp);
+  EDAccumulator e = rec.editDistance(r.begin(), r.end(), hy.begin(), hy.end());
+  out[0] = e.total_count; out[1] = e.substitute_count; out[2] = e.insert_count; out[3] = e.delete_count;
+}
+
 }  // extern "C"

@@ -556,3 +556,103 @@ double orc_align_batch(const orc_model *m, double loop, double forward, double s
   }
   return total;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * recognition (BASELINE config 4)
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Recognizer::recognizeSequence_pruned, Recognizer.cpp:103-232, restated over a lexicon given as arrays
+ * (word w = positions word_states[word_off[w] .. word_off[w+1]) ).  Kept literally:
+ *  - hypothesis table indexed max_len * word + position (:117-118), hypotheses visited in that order (:128);
+ *  - the start hypothesis is slot 0 with score 0 (:121);
+ *  - a hypothesis on the LAST position of its word only leaves the word: it enters position 0 and 1 of every word with
+ *    word_penalty (0 for silence) + tdp(first_state, init + 1) and — for BOTH entry positions — the emission score of
+ *    the word's FIRST state (:131-157);
+ *  - inside a word: jumps 0/1/2 with the DESTINATION state's tdp (:162-187);
+ *  - a candidate is dropped when its score before the emission already exceeds the target's (:142-145,172-175),
+ *    otherwise it replaces the target on strict improvement (:153,183);
+ *  - pruning against best + am_threshold, best word end per frame with strict '>' (:190-207);
+ *  - traceback over word ends, silence not emitted (:222-231); Book::bkp is 16 bits (Recognizer.hpp:79).
+ * Returns the number of words written to out_words (at most max_words are stored). */
+uint64_t orc_recognize(const orc_model *m, double loop, double forward, double skip, uint32_t silence_state,
+                       int max_approx, const float *x, uint64_t T, uint32_t n_words, const uint32_t *word_off,
+                       const uint32_t *word_states, uint32_t silence_word, double word_penalty,
+                       double am_threshold, uint32_t *out_words, uint64_t max_words, double *out_score) {
+  orc_tdp tdp = {loop, forward, skip, silence_state};
+  uint32_t max_len = 0, n_states = 0;
+  for (uint32_t w = 0; w < n_words; w++) {
+    uint32_t L = word_off[w + 1] - word_off[w];
+    if (L > max_len) max_len = L;
+    for (uint32_t p = word_off[w]; p < word_off[w + 1]; p++)
+      if (word_states[p] + 1 > n_states) n_states = word_states[p] + 1;
+  }
+  typedef struct { double score; uint16_t word, bkp; int state_idx; } book;
+  const size_t n_slots = (size_t)n_words * max_len;
+  book *cur = (book *)malloc(n_slots * sizeof(book)), *nxt = (book *)malloc(n_slots * sizeof(book));
+  book *tb = (book *)malloc((T + 1) * sizeof(book));
+  double *am = (double *)malloc(n_states * sizeof(double));
+  for (size_t i = 0; i < n_slots; i++) { book b = {INFINITY, 0, 0, 0}; cur[i] = b; nxt[i] = b; }
+  for (uint64_t t = 0; t <= T; t++) { book b = {0.0, 0, 0, 0}; tb[t] = b; }
+  for (uint32_t s = 0; s < n_states; s++) am[s] = INFINITY;
+  cur[0].score = 0.0;
+  for (uint64_t t = 1; t <= T; t++) {
+    const float *xt = x + (t - 1) * m->dim;
+    double best = INFINITY;
+    for (size_t i = 0; i < n_slots; i++) {
+      const book h = cur[i];
+      if (h.score == INFINITY) continue;
+      const uint32_t Lw = word_off[h.word + 1] - word_off[h.word];
+      if ((uint32_t)h.state_idx == Lw - 1) {
+        for (uint32_t w = 0; w < n_words; w++) {
+          const double wp = (w != silence_word) ? word_penalty : 0.0;
+          const uint32_t first = word_states[word_off[w]];
+          for (uint32_t init = 0; init <= 1; init++) {
+            book *tg = &nxt[(size_t)max_len * w + init];
+            double ns = h.score + wp + tdp_score(&tdp, first, init + 1);
+            if (ns > tg->score) continue;
+            if (am[first] == INFINITY) am[first] = orc_score(m, xt, first, max_approx);
+            ns += am[first];
+            if (tg->score > ns) {
+              tg->score = ns; tg->state_idx = (int)init; tg->bkp = (uint16_t)(t - 1); tg->word = (uint16_t)w;
+              if (ns < best) best = ns;
+            }
+          }
+        }
+      } else {
+        for (uint32_t jump = 0; jump <= 2; jump++) {
+          const uint32_t np = (uint32_t)h.state_idx + jump;
+          if (np >= Lw) break;
+          const uint32_t st = word_states[word_off[h.word] + np];
+          book *tg = &nxt[(size_t)max_len * h.word + np];
+          double ns = h.score + tdp_score(&tdp, st, jump);
+          if (ns > tg->score) continue;
+          if (am[st] == INFINITY) am[st] = orc_score(m, xt, st, max_approx);
+          ns += am[st];
+          if (tg->score > ns) {
+            tg->score = ns; tg->state_idx = (int)np; tg->bkp = h.bkp; tg->word = h.word;
+            if (ns < best) best = ns;
+          }
+        }
+      }
+    }
+    tb[t].score = INFINITY;
+    for (size_t i = 0; i < n_slots; i++) {
+      book *h = &nxt[i];
+      if (h->score > best + am_threshold) { h->score = INFINITY; continue; }
+      if ((uint32_t)h->state_idx == word_off[h->word + 1] - word_off[h->word] - 1 && tb[t].score > h->score) {
+        tb[t].score = h->score; tb[t].word = h->word; tb[t].bkp = h->bkp;
+      }
+    }
+    book *sw = cur; cur = nxt; nxt = sw;
+    for (size_t i = 0; i < n_slots; i++) { book b = {INFINITY, 0, 0, 0}; nxt[i] = b; }
+    for (uint32_t s = 0; s < n_states; s++) am[s] = INFINITY;
+  }
+  if (out_score) *out_score = tb[T].score;
+  uint64_t n = 0;
+  uint32_t *rev = (uint32_t *)malloc((T + 1) * sizeof(uint32_t));
+  for (uint64_t t = T; t > 0; t = tb[t].bkp)
+    if (tb[t].word != silence_word) rev[n++] = tb[t].word;
+  for (uint64_t i = 0; i < n && i < max_words; i++) out_words[i] = rev[n - 1 - i];
+  free(rev); free(cur); free(nxt); free(tb); free(am);
+  return n;
+}

@@ -136,6 +136,25 @@ class Context:
                                    _ptr(costs, C.c_double)))
         return ali, costs
 
+    def set_lexicon(self, automata, silence_word=0):
+        """automata: one array of state ids per word (positions of its linear HMM), e.g. synth.Lexicon().automata."""
+        word_off = np.concatenate([[0], np.cumsum([len(a) for a in automata])]).astype(np.uint32)
+        word_states = np.ascontiguousarray(np.concatenate(automata), np.uint32)
+        self._ck(self.L.sgmm_set_lexicon(self.h, C.c_uint32(len(automata)), _ptr(word_off, C.c_uint32),
+                                         _ptr(word_states, C.c_uint32), C.c_uint32(silence_word)))
+
+    def recognize(self, frame_off, word_penalty=10.0, am_threshold=20.0):
+        """Word-loop recognition of every utterance of the resident features -> (list of word-id arrays, scores)."""
+        frame_off = np.ascontiguousarray(frame_off, np.uint64)
+        U = len(frame_off) - 1
+        words = np.zeros(int(frame_off[-1]), np.uint32)
+        off = np.zeros(U + 1, np.uint32)
+        scores = np.zeros(U, np.float64)
+        self._ck(self.L.sgmm_recognize(self.h, C.c_uint32(U), _ptr(frame_off, C.c_uint64), C.c_double(word_penalty),
+                                       C.c_double(am_threshold), _ptr(words, C.c_uint32), C.c_uint64(len(words)),
+                                       _ptr(off, C.c_uint32), _ptr(scores, C.c_double)))
+        return [words[off[u]:off[u + 1]].copy() for u in range(U)], scores
+
     def set_alignment(self, states):
         if states.dtype != ALI_DTYPE:
             a = np.zeros(len(states), ALI_DTYPE)

@@ -236,4 +236,54 @@ uint64_t sthost_segment_automaton(const uint64_t* words, uint64_t n_words, uint1
   return a.num_states();
 }
 
+// Recognizer::editDistance (Recognizer.cpp:332-388): out = {total, substitutions, insertions, deletions}
+void sthost_edit_distance(const uint64_t* ref, uint64_t n_ref, const uint64_t* hyp, uint64_t n_hyp, uint64_t* out) {
+  std::vector<WordIdx> r(ref, ref + n_ref), h(hyp, hyp + n_hyp);
+  EDAccumulator e = editDistance(r.cbegin(), r.cend(), h.cbegin(), h.cend());
+  out[0] = e.total_count; out[1] = e.substitute_count; out[2] = e.insert_count; out[3] = e.delete_count;
+}
+
+// Recognizer::recognize (Recognizer.cpp:37-99) over the sietill digits lexicon with a model handle from
+// sthost_model_* / sthost_train.  hyp_words / hyp_off: recognised word ids per segment (hyp_off[n_utts + 1]);
+// stats = {WER %, SER %, total errors, substitutions, insertions, deletions, reference words, seconds}.
+int sthost_recognize(void* model, const float* x, uint64_t n_utts, const uint64_t* frame_off, const uint64_t* words,
+                     const uint64_t* word_off, double loop, double forward, double skip, double word_penalty,
+                     double am_threshold, uint64_t* hyp_words, uint64_t hyp_cap, uint64_t* hyp_off, double* stats) {
+  HostModel* h = static_cast<HostModel*>(model);
+  return guarded([&] {
+    Lexicon lex = build_sietill_lexicon();
+    std::vector<size_t> fo(frame_off, frame_off + n_utts + 1), wo(word_off, word_off + n_utts + 1);
+    std::vector<WordIdx> w(words, words + word_off[n_utts]);
+    Corpus corpus(x, h->model->dimension, fo, w, wo);
+    Configuration cfg = h->config;
+    cfg.set("tdp-loop", loop).set("tdp-forward", forward).set("tdp-skip", skip);
+    cfg.set("am-threshold", am_threshold).set("word-penalty", word_penalty);
+    cfg.set("max-recognition-runs", (unsigned)n_utts);
+    TdpModel tdp(cfg, lex.get_silence_automaton()[0]);
+    Recognizer rec(cfg, lex, *h->model, tdp);
+    rec.recognize(corpus);
+    uint64_t n = 0;
+    hyp_off[0] = 0;
+    for (size_t s = 0; s < rec.hypotheses.size(); s++) {
+      for (WordIdx v : rec.hypotheses[s]) {
+        if (n >= hyp_cap) throw std::runtime_error("sthost_recognize: hypothesis buffer too small");
+        hyp_words[n++] = v;
+      }
+      hyp_off[s + 1] = n;
+    }
+    if (stats) {
+      stats[0] = rec.wer; stats[1] = rec.ser; stats[2] = (double)rec.errors.total_count;
+      stats[3] = (double)rec.errors.substitute_count; stats[4] = (double)rec.errors.insert_count;
+      stats[5] = (double)rec.errors.delete_count; stats[6] = (double)rec.ref_total; stats[7] = rec.seconds;
+    }
+    // the single-sequence entry point must agree with the batch (first segment)
+    if (n_utts > 0) {
+      std::vector<WordIdx> one;
+      std::pair<FeatureIter, FeatureIter> f = corpus.get_feature_sequence(0);
+      rec.recognizeSequence_pruned(f.first, f.second, one);
+      if (one != rec.hypotheses[0]) throw std::runtime_error("sthost_recognize: recognizeSequence_pruned differs from the batch");
+    }
+  });
+}
+
 }  // extern "C"

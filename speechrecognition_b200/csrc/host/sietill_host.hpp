@@ -252,6 +252,7 @@ class MixtureModel : public FeatureScorer {
  private:
   friend class Aligner;
   friend class Trainer;
+  friend class Recognizer;
   void calculate_variance(DensityIdx var_idx, const double* mean);
   MixtureDensity create_mixture_density(DensityIdx var_index);
   void mark_dirty() { ++version_; }
@@ -317,6 +318,40 @@ class Aligner {
 
 void write_alignment(std::ostream& out, Alignment const& alignment, size_t max_aligns);   // Alignment.cpp:303-308
 void read_alignment(std::istream& in, Alignment& alignment, size_t& max_aligns);          // Alignment.cpp:310-317
+
+// ---- Recognizer.hpp:22-73 ----------------------------------------------------------------------------
+struct EDAccumulator {   // Util.hpp: edit-distance counts
+  size_t total_count = 0, substitute_count = 0, insert_count = 0, delete_count = 0;
+  EDAccumulator& operator+=(EDAccumulator const& o);
+};
+EDAccumulator editDistance(WordIter ref_begin, WordIter ref_end, WordIter hyp_begin, WordIter hyp_end);
+
+class Recognizer {
+ public:
+  // config keys and defaults as Recognizer.cpp:31-34: "am-threshold" 20, "word-penalty" 10, "pruned-search" true
+  // (the unpruned search is a stub in the reference, :234-240, and is not offered), "max-recognition-runs" 1000.
+  Recognizer(Configuration const& config, Lexicon const& lexicon, MixtureModel const& scorer, TdpModel const& tdp_model);
+
+  // Recognizer.cpp:37-99: recognises the first max-recognition-runs segments in ONE batched GPU call (the reference's
+  // OpenMP loop), then accumulates the edit distances.  Results are kept in the public fields below.
+  void recognize(Corpus const& corpus);
+  // Recognizer.cpp:103-232 for one sequence (a one-utterance batch on the scratch device context).
+  void recognizeSequence_pruned(FeatureIter feature_begin, FeatureIter feature_end, std::vector<WordIdx>& output);
+
+  std::vector<std::vector<WordIdx>> hypotheses;   // per segment, after recognize()
+  EDAccumulator errors;
+  size_t ref_total = 0, sentence_errors = 0;
+  double wer = 0.0, ser = 0.0, seconds = 0.0;
+
+ private:
+  void upload_lexicon(Device& dev) const;
+  const double am_threshold_, word_penalty_;
+  const bool pruned_search_;
+  const size_t max_recognition_runs_;
+  Lexicon const& lexicon_;
+  MixtureModel const& scorer_;
+  TdpModel const& tdp_model_;
+};
 
 // ---- Training.hpp:17-110 ----------------------------------------------------------------------------
 class Trainer {

@@ -185,6 +185,7 @@ struct TcParams {
   uint32_t nstage;             // B stages in the ring (<= kMaxStage)
   uint32_t stage_bytes;        // bytes of one ring stage (a full 128-density tile: 2 * ksteps * 128 * 32)
   uint32_t nhalf;              // frame halves (of 128) per task: 2 when 32 * ksteps <= 256 TMEM columns, else 1
+  uint32_t a_smem;             // where the A parts live: 0 hi TMEM / lo smem, 1 both smem, 2 hi smem / lo TMEM
   uint32_t debug;              // timing experiments only (results invalid): 1 = no epilogue math, 2 = no MMAs
   const float* Ahi;            // [n_frames][8 * ksteps] tf32 hi / lo of the A rows (k_tc_prep)
   const float* Alo;
@@ -225,7 +226,8 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* sAlo = smem_raw + (base - smem_u32(smem_raw));    // [half][kstep][128 rows][32 B], 32-byte swizzle
-  unsigned char* sB = sAlo + p.nhalf * (p.stage_bytes / 2);        // [stage][hi, lo][kstep][128 rows][32 B]
+  unsigned char* sAhi = sAlo + p.nhalf * (p.stage_bytes / 2);      // same layout (a_smem only)
+  unsigned char* sB = sAhi + (p.a_smem == 1 ? p.nhalf * (p.stage_bytes / 2) : 0u);   // [stage][hi, lo][kstep][128 rows][32 B]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sB + p.nstage * p.stage_bytes);
   uint64_t* a_full = bars;                 // A rows are in TMEM (8 epilogue warps arrive)
   uint64_t* full = bars + 1;
@@ -327,20 +329,32 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           if (prof) w_tempty += clock64() - c1;
           tc_fence_after();
           const uint32_t d = tmem_base + kAccCol + buf * BN;
-          const uint32_t ahi = tmem_base + h * KP;
-          const uint64_t alo = make_desc_sw32(smem_u32(sAlo + h * (p.stage_bytes / 2)));
+          // the A part kept in TMEM (columns [h * KP, +KP)) and the part(s) kept in shared memory, by p.a_smem:
+          // 0: hi in TMEM, lo in sA0;  1: lo in sA0, hi in sA1 (all three passes A-from-shared);  2: hi in sA0, lo in TMEM
+          const uint32_t a_t = tmem_base + h * KP;
+          const uint64_t a_s0 = make_desc_sw32(smem_u32(sAlo + h * (p.stage_bytes / 2)));
+          const uint64_t a_s1 = make_desc_sw32(smem_u32(sAhi + h * (p.stage_bytes / 2)));
+          const bool hi_t = p.a_smem == 0, lo_t = p.a_smem == 2;
+          const uint64_t hi_s = p.a_smem == 1 ? a_s1 : a_s0, lo_s = a_s0;
           if (!(p.debug & 2)) {
-            if (KS > 0) {
+            const uint32_t nk = KS > 0 ? (uint32_t)KS : ks;
+            if (hi_t) {
 #pragma unroll
-              for (uint32_t kk = 0; kk < (uint32_t)KS; kk++) tc_mma_tf32_ts(d, ahi + kk * 8, bhi + kk * kstride, idesc, kk);
+              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ts(d, a_t + kk * 8, bhi + kk * kstride, idesc, kk);
 #pragma unroll
-              for (uint32_t kk = 0; kk < (uint32_t)KS; kk++) tc_mma_tf32_ts(d, ahi + kk * 8, blo + kk * kstride, idesc, 1);
-#pragma unroll
-              for (uint32_t kk = 0; kk < (uint32_t)KS; kk++) tc_mma_tf32_ss(d, alo + kk * kstride, bhi + kk * kstride, idesc, 1);
+              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ts(d, a_t + kk * 8, blo + kk * kstride, idesc, 1);
             } else {
-              for (uint32_t kk = 0; kk < ks; kk++) tc_mma_tf32_ts(d, ahi + kk * 8, bhi + kk * kstride, idesc, kk);
-              for (uint32_t kk = 0; kk < ks; kk++) tc_mma_tf32_ts(d, ahi + kk * 8, blo + kk * kstride, idesc, 1);
-              for (uint32_t kk = 0; kk < ks; kk++) tc_mma_tf32_ss(d, alo + kk * kstride, bhi + kk * kstride, idesc, 1);
+#pragma unroll
+              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ss(d, hi_s + kk * kstride, bhi + kk * kstride, idesc, kk);
+#pragma unroll
+              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ss(d, hi_s + kk * kstride, blo + kk * kstride, idesc, 1);
+            }
+            if (lo_t) {
+#pragma unroll
+              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ts(d, a_t + kk * 8, bhi + kk * kstride, idesc, 1);
+            } else {
+#pragma unroll
+              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ss(d, lo_s + kk * kstride, bhi + kk * kstride, idesc, 1);
             }
           }
           if (h + 1 == nh) tc_commit_elect(&empty[stage]);   // stage reusable once every MMA that reads it is done
@@ -379,12 +393,20 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
         const float4* al = reinterpret_cast<const float4*>(p.Alo + fr * KP);
         const uint32_t acol = tlane + group * KP;
         // lo part: [kstep][row][32 B] with byte-address bit 7 (= row bit 2) XORed into bit 4
-        unsigned char* lo_row = sAlo + group * (p.stage_bytes / 2) + lrow * 32;
+        // shared-memory parts: [kstep][row][32 B] with byte-address bit 7 (= row bit 2) XORed into bit 4
+        unsigned char* s0_row = sAlo + group * (p.stage_bytes / 2) + lrow * 32;
+        unsigned char* s1_row = sAhi + group * (p.stage_bytes / 2) + lrow * 32;
         const uint32_t sw = ((lrow >> 2) & 1u) << 4;
+        const float4* to_t = p.a_smem == 0 ? ah : (p.a_smem == 2 ? al : nullptr);   // part kept in TMEM
+        const float4* to_s0 = p.a_smem == 2 ? ah : al;
         for (uint32_t kk = 0; kk < ks; kk++) {
-          tc_st8(acol + kk * 8, __ldg(ah + 2 * kk), __ldg(ah + 2 * kk + 1));
-          *reinterpret_cast<float4*>(lo_row + kk * 4096 + (0 ^ sw)) = __ldg(al + 2 * kk);
-          *reinterpret_cast<float4*>(lo_row + kk * 4096 + (16 ^ sw)) = __ldg(al + 2 * kk + 1);
+          if (to_t) tc_st8(acol + kk * 8, __ldg(to_t + 2 * kk), __ldg(to_t + 2 * kk + 1));
+          *reinterpret_cast<float4*>(s0_row + kk * 4096 + (0 ^ sw)) = __ldg(to_s0 + 2 * kk);
+          *reinterpret_cast<float4*>(s0_row + kk * 4096 + (16 ^ sw)) = __ldg(to_s0 + 2 * kk + 1);
+          if (p.a_smem == 1) {
+            *reinterpret_cast<float4*>(s1_row + kk * 4096 + (0 ^ sw)) = __ldg(ah + 2 * kk);
+            *reinterpret_cast<float4*>(s1_row + kk * 4096 + (16 ^ sw)) = __ldg(ah + 2 * kk + 1);
+          }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the MMA
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -717,8 +739,9 @@ namespace {
 
 // shared memory: Alo + the B ring (Ahi lives in tensor memory)
 constexpr size_t kSmemLimit = 227 * 1024;
-size_t tc_smem(uint32_t stage_bytes, int nhalf, int nstage) {   // Alo of every half + the B ring + barriers
-  return 1024 + (size_t)nhalf * (stage_bytes / 2) + (size_t)nstage * stage_bytes + 256 + 2 * 2 * 128 * 5 * sizeof(float);
+size_t tc_smem(uint32_t stage_bytes, int nhalf, int nstage, int a_smem) {   // A of every half + the B ring + barriers
+  return 1024 + (size_t)nhalf * (stage_bytes / 2) * (a_smem == 1 ? 2 : 1) + (size_t)nstage * stage_bytes + 256 +
+         2 * 2 * 128 * 5 * sizeof(float);
 }
 
 }  // namespace
@@ -731,8 +754,11 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   // two frame halves per CTA when their Ahi operands (KP columns each) fit the 128 TMEM columns set aside
   const int nhalf = (c->tc_halves == 1 || 2 * KP > 128) ? 1 : 2;
   const uint32_t stage_bytes = 2 * ks * 128 * 32;
+  // both A parts in shared memory when that still leaves three B stages (option tc_debug & 64 forces the TMEM form)
+  int a_smem = (c->tc_debug >> 6) & 3;   // experiment: tc_debug bits 6-7 select where the A parts live
+  if (a_smem == 1 && tc_smem(stage_bytes, nhalf, 2, 1) > kSmemLimit) a_smem = 0;
   int nstage = 1;
-  while (nstage < sgmm_tc::kMaxStage && tc_smem(stage_bytes, nhalf, nstage + 1) <= kSmemLimit) nstage++;
+  while (nstage < sgmm_tc::kMaxStage && tc_smem(stage_bytes, nhalf, nstage + 1, a_smem) <= kSmemLimit) nstage++;
   const uint32_t rows_per_task = 128u * nhalf;
   // Work is cut into frame ranges.  Normally there is one; while a chunked feature upload is in flight
   // (option "async_upload") there is one per chunk, each launched behind that chunk's copy event, so that the
@@ -765,7 +791,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
 
   TcParams p{};
   p.ksteps = ks; p.nstage = (uint32_t)nstage; p.stage_bytes = stage_bytes; p.nhalf = (uint32_t)nhalf;
-  p.debug = (uint32_t)c->tc_debug;
+  p.debug = (uint32_t)c->tc_debug; p.a_smem = (uint32_t)a_smem;
   p.prof = (c->tc_debug & 32) ? c->d_fallbacks.p : nullptr;
   p.Ahi = c->d_Ahi.p; p.Alo = c->d_Alo.p; p.n_frames = c->n_frames;
   p.Bimg = c->d_Bimg.p; p.tile_first = c->d_tile_first.p; p.tile_info = c->d_tile_info.p;
@@ -776,7 +802,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
-  const size_t smem = tc_smem(stage_bytes, nhalf, nstage);
+  const size_t smem = tc_smem(stage_bytes, nhalf, nstage, a_smem);
   RefineParams r{};
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
   r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;

@@ -135,6 +135,13 @@ struct sgmm_ctx {
   DevBuf<double> d_dense_scores;
   DevBuf<uint32_t> d_dense_argmin;
 
+  // ---- recognition (k_recognize.cu): lexicon tables + per-call buffers
+  uint32_t lex_words = 0, lex_live = 0, lex_silence = 0, lex_max_state = 0;
+  DevBuf<uint32_t> d_lex_info, d_lex_state, d_lex_base, d_lex_len, d_lex_first;
+  DevBuf<uint64_t> d_rec_frame_off, d_rec_tb_off;
+  DevBuf<uint32_t> d_rec_tb, d_rec_words, d_rec_nwords;
+  DevBuf<double> d_rec_score;
+
   // ---- NCCL (dlopen'ed lazily)
   void* nccl_comm = nullptr;
   int rank = 0, world = 1;
@@ -173,6 +180,10 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
                            uint32_t* d_argmin);
 int sgmm_effective_scorer(const sgmm_ctx* c);
 int sgmm_launch_viterbi(sgmm_ctx* c, int tdp_convention);
+int sgmm_build_lexicon(sgmm_ctx* c, uint32_t n_words, const uint32_t* word_off, const uint32_t* word_states,
+                       uint32_t silence_word);
+int sgmm_launch_recognize(sgmm_ctx* c, uint32_t u0, uint32_t n, uint64_t chunk_f0, double word_penalty,
+                          double am_threshold);
 // make the compute stream wait for a queued feature upload (option "async_upload"); no-op when resident
 inline int sgmm_wait_features(sgmm_ctx* c) {
   if (c->feat_pending) {

@@ -1,6 +1,7 @@
 // The compute entry points: score_all (K1), align (K1 gathered + K2), accumulate (K3 + K4 [+ NCCL]).
 #include <algorithm>
 #include <cstring>
+#include <vector>
 
 #include "sgmm_internal.cuh"
 
@@ -115,6 +116,77 @@ int sgmm_align(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* co
   c->have_alignment = true;
   c->ali_has_cols = true;
   c->E_model_version = c->model_version;
+  return 0;
+}
+
+int sgmm_set_lexicon(sgmm_ctx* c, uint32_t n_words, const uint32_t* word_off, const uint32_t* word_states,
+                     uint32_t silence_word) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  if (!word_off || !word_states) SGMM_FAIL(c, "set_lexicon: null argument");
+  if (word_off[0] != 0) SGMM_FAIL(c, "set_lexicon: offsets must start at 0");
+  return sgmm_build_lexicon(c, n_words, word_off, word_states, silence_word);
+}
+
+int sgmm_recognize(sgmm_ctx* c, uint32_t n_utts, const uint64_t* frame_off, double word_penalty, double am_threshold,
+                   uint32_t* words, uint64_t max_words, uint32_t* word_off_out, double* scores) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  reset_stage(c);
+  if (require(c, true, true, false)) return 1;
+  if (c->lex_words == 0) SGMM_FAIL(c, "no lexicon: call sgmm_set_lexicon first");
+  if (c->lex_max_state >= c->n_states) SGMM_FAIL(c, "lexicon names a state the model does not have");
+  if (!frame_off || !word_off_out || (!words && max_words)) SGMM_FAIL(c, "recognize: null argument");
+  if (frame_off[0] != 0 || frame_off[n_utts] != c->n_frames)
+    SGMM_FAIL(c, "recognize: frame offsets do not cover the resident features");
+  std::vector<uint64_t> tb_off(n_utts + 1, 0);
+  for (uint32_t u = 0; u < n_utts; u++) {
+    if (frame_off[u + 1] <= frame_off[u]) SGMM_FAIL(c, "recognize: empty utterance");
+    if (frame_off[u + 1] - frame_off[u] > 65535) SGMM_FAIL(c, "recognize: utterance longer than 65535 frames");
+    tb_off[u + 1] = tb_off[u] + (frame_off[u + 1] - frame_off[u]) + 1;
+  }
+  SGMM_CHECK(c, c->d_rec_frame_off.reserve(n_utts + 1));
+  SGMM_CHECK(c, c->d_rec_tb_off.reserve(n_utts + 1));
+  SGMM_CHECK(c, c->d_rec_tb.reserve(tb_off[n_utts]));
+  SGMM_CHECK(c, c->d_rec_words.reserve(c->n_frames));
+  SGMM_CHECK(c, c->d_rec_nwords.reserve(n_utts));
+  SGMM_CHECK(c, c->d_rec_score.reserve(n_utts));
+  SGMM_CHECK(c, cudaMemcpyAsync(c->d_rec_frame_off.p, frame_off, (n_utts + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  SGMM_CHECK(c, cudaMemcpyAsync(c->d_rec_tb_off.p, tb_off.data(), (n_utts + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  // dense emission scores for runs of whole utterances (<= ~256 MB of scores per run), then one warp per utterance
+  const uint32_t N = c->n_states;
+  const uint64_t budget = std::max<uint64_t>(65536, (256ull << 20) / (N * sizeof(double)));
+  for (uint32_t u0 = 0; u0 < n_utts;) {
+    uint32_t u1 = u0 + 1;
+    while (u1 < n_utts && frame_off[u1 + 1] - frame_off[u0] <= budget) u1++;
+    const uint64_t f0 = frame_off[u0], nf = frame_off[u1] - f0;
+    SGMM_CHECK(c, c->d_dense_scores.reserve((size_t)nf * N));
+    {
+      StageTimer st(c, SGMM_T_SCORE);
+      if (launch_emission_any(c, true, f0, nf, c->d_dense_scores.p, nullptr)) return 1;
+    }
+    {
+      StageTimer st(c, SGMM_T_VITERBI);
+      if (sgmm_launch_recognize(c, u0, u1 - u0, f0, word_penalty, am_threshold)) return 1;
+    }
+    u0 = u1;
+  }
+  std::vector<uint32_t> counts(n_utts), raw(c->n_frames);
+  {
+    StageTimer st(c, SGMM_T_D2H);
+    SGMM_CHECK(c, cudaMemcpyAsync(counts.data(), c->d_rec_nwords.p, n_utts * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    SGMM_CHECK(c, cudaMemcpyAsync(raw.data(), c->d_rec_words.p, c->n_frames * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    if (scores) SGMM_CHECK(c, cudaMemcpyAsync(scores, c->d_rec_score.p, n_utts * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  uint64_t total = 0;
+  word_off_out[0] = 0;
+  for (uint32_t u = 0; u < n_utts; u++) {
+    if (total + counts[u] > max_words) SGMM_FAIL(c, "recognize: word buffer too small");
+    for (uint32_t i = 0; i < counts[u]; i++) words[total + i] = raw[frame_off[u] + i];
+    total += counts[u];
+    word_off_out[u + 1] = (uint32_t)total;
+  }
   return 0;
 }
 

@@ -187,3 +187,33 @@ def segment_automaton(word_ids):
     out = np.zeros(4096, np.uint16)
     n = int(_lib().sthost_segment_automaton(_p(w, C.c_uint64), C.c_uint64(len(w)), _p(out, C.c_uint16), C.c_uint64(len(out))))
     return out[:n].copy()
+
+
+def edit_distance(ref, hyp):
+    """Recognizer::editDistance -> (total, substitutions, insertions, deletions)."""
+    r = np.ascontiguousarray(ref, np.uint64)
+    h = np.ascontiguousarray(hyp, np.uint64)
+    out = np.zeros(4, np.uint64)
+    _lib().sthost_edit_distance(_p(r, C.c_uint64), C.c_uint64(len(r)), _p(h, C.c_uint64), C.c_uint64(len(h)),
+                                _p(out, C.c_uint64))
+    return tuple(int(v) for v in out)
+
+
+def recognize(model, x, frame_off, words, word_off, tdp, word_penalty=10.0, am_threshold=20.0):
+    """Recognizer::recognize with a HostModel over the sietill digits lexicon.
+    Returns (list of recognised word-id arrays, dict of WER/SER/error counts)."""
+    L = _lib()
+    x = np.ascontiguousarray(x, np.float32)
+    fo = np.ascontiguousarray(frame_off, np.uint64)
+    w = np.ascontiguousarray(words, np.uint64)
+    wo = np.ascontiguousarray(word_off, np.uint64)
+    U = len(fo) - 1
+    hyp = np.zeros(int(fo[-1]) + 1, np.uint64)
+    off = np.zeros(U + 1, np.uint64)
+    stats = np.zeros(8, np.float64)
+    _ck(L, L.sthost_recognize(model.h, _p(x, C.c_float), C.c_uint64(U), _p(fo, C.c_uint64), _p(w, C.c_uint64),
+                              _p(wo, C.c_uint64), C.c_double(tdp[0]), C.c_double(tdp[1]), C.c_double(tdp[2]),
+                              C.c_double(word_penalty), C.c_double(am_threshold), _p(hyp, C.c_uint64),
+                              C.c_uint64(len(hyp)), _p(off, C.c_uint64), _p(stats, C.c_double)))
+    names = ["wer", "ser", "errors", "substitutions", "insertions", "deletions", "ref_words", "seconds"]
+    return [hyp[int(off[u]):int(off[u + 1])].astype(np.uint32) for u in range(U)], dict(zip(names, stats))

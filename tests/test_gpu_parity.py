@@ -307,3 +307,67 @@ def test_async_upload_same_results(scorer):
     s_sync, a_sync = ctx.score_all(0, 64)
     assert np.array_equal(s_async, s_sync) and np.array_equal(a_async, a_sync)
     ctx.close()
+
+
+@pytest.mark.parametrize("scorer", ["f64", "tc"])
+@pytest.mark.parametrize("scale,word_penalty,am_threshold", [(1.0, 10.0, 20.0), (1.0, 3.0, 1e30), (0.05, 10.0, 60.0)])
+def test_recognize_matches_oracle(scale, word_penalty, am_threshold, scorer):
+    """BASELINE config 4: batched word-loop recognition (Recognizer.cpp:103-232) — recognised word sequences and the
+    final word-end score identical to the oracle for the default beam, no beam, and negative emission scores."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    O0, corp, ali = helpers.trained_oracle(dim=25, n_utts=24, splits=2)
+    x = (corp["x"] * scale).astype(np.float32)
+    lex = synth.Lexicon()
+    O = O0
+    if scale != 1.0:                       # retrain on the scaled features: tiny variances, negative scores
+        O = Oracle(25, lex.num_states, "none", True, O0.tdp, O0.silence)
+        O.accumulate(ali, x, first_pass=True); O.finalize()
+    ctx = capi.Context(0)
+    ctx.set_model_tables(25, O.tables())
+    ctx.set_features(x)
+    ctx.set_tdp(*O.tdp, O.silence)
+    ctx.set_option("scorer", SCORERS[scorer])
+    ctx.set_lexicon(lex.automata, lex.silence)
+    got, scores = ctx.recognize(corp["frame_off"], word_penalty, am_threshold)
+    word_off = np.concatenate([[0], np.cumsum([len(a) for a in lex.automata])]).astype(np.uint32)
+    word_states = np.concatenate(lex.automata).astype(np.uint32)
+    n_words = 0
+    for u in range(len(corp["frame_off"]) - 1):
+        f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
+        want, want_score = O.recognize(x[f0:f1], word_off, word_states, lex.silence, word_penalty, am_threshold)
+        assert np.array_equal(got[u], want), (u, got[u], want)
+        assert scores[u] == want_score, (u, scores[u], want_score)
+        n_words += len(want)
+    assert n_words > 0
+    if scale < 1.0:
+        s, _ = ctx.score_all(0, 64)
+        assert (s < 0).any()               # the negative-score branch was exercised
+    ctx.close()
+
+
+def test_recognize_golden():
+    """Committed outputs of the unmodified reference Recognizer (tests/golden/recognize.npz)."""
+    import os
+    from oracle.binding import Oracle, TABLES
+    from speechrecognition_b200 import capi, synth
+    G = os.path.join(os.path.dirname(__file__), "golden")
+    c = np.load(os.path.join(G, "corpus.npz"))
+    rec = np.load(os.path.join(G, "trajectory_none.npz"))
+    g = np.load(os.path.join(G, "recognize.npz"))
+    dim = int(c["dim"])
+    lex = synth.Lexicon()
+    O = Oracle(dim, lex.num_states, "none", True, tuple(c["tdp"]), lex.silence_state)
+    O.load_tables({k: rec["t2_" + k] for k in TABLES})
+    O.finalize()
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, O.tables())
+    ctx.set_features(c["x"])
+    ctx.set_tdp(*[float(v) for v in c["tdp"]], lex.silence_state)
+    ctx.set_lexicon(lex.automata, lex.silence)
+    for ci, (wp, thr) in enumerate(g["configs"]):
+        got, _ = ctx.recognize(c["frame_off"], float(wp), float(thr))
+        words, off = g["words%d" % ci], g["off%d" % ci]
+        for u in range(len(c["frame_off"]) - 1):
+            assert np.array_equal(got[u], words[off[u]:off[u + 1]]), (ci, u)
+    ctx.close()

@@ -142,3 +142,23 @@ def test_model_accumulate_and_edit_detection(trained):
     H.accumulate(a, x)
     O.accumulate(ali2, x)
     assert np.array_equal(H.tables()["mean_wacc"], O.tables()["mean_wacc"])
+
+
+def test_recognizer_matches_oracle(trained):
+    """Recognizer::recognize through the host class (one batched GPU search) == orc_recognize per utterance, and the
+    WER bookkeeping (edit distance incl. the reference's column-0 behaviour) is consistent with the hypotheses."""
+    O, corp, ali, H = trained
+    lex = synth.Lexicon()
+    w, wo = words_of(corp)
+    word_off = np.concatenate([[0], np.cumsum([len(a) for a in lex.automata])]).astype(np.uint32)
+    word_states = np.concatenate(lex.automata).astype(np.uint32)
+    for wp, thr in ((10.0, 20.0), (4.0, 1e30)):
+        hyps, stats = hostapi.recognize(H, corp["x"], corp["frame_off"], w, wo, TDP, wp, thr)
+        errs = 0
+        for u in range(len(corp["frame_off"]) - 1):
+            f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
+            want, _ = O.recognize(corp["x"][f0:f1], word_off, word_states, lex.silence, wp, thr)
+            assert np.array_equal(hyps[u], want), (u, hyps[u], want)
+            errs += hostapi.edit_distance(corp["words"][u], hyps[u])[0]
+        assert stats["errors"] == errs and stats["ref_words"] == len(w)
+        assert stats["wer"] == pytest.approx(100.0 * errs / len(w))

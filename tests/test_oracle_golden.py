@@ -79,3 +79,27 @@ def test_unreachable_and_degenerate_alignments():
     assert np.all(st == 3) and np.isfinite(cost)                  # single position: loops only
     cost, st, pos = O.align_full(x[:3], [1, 2, 3, 4, 5])         # S == 2T-1: skipping every frame is the only path
     assert np.array_equal(pos, [0, 2, 4]) and np.isfinite(cost)
+
+
+def test_recognition_matches_reference():
+    """orc_recognize against the committed outputs of the unmodified Recognizer (tests/golden/recognize.npz,
+    tools/make_golden.py recognition()): final "none" model, every golden utterance, three beam / penalty settings."""
+    c = np.load(os.path.join(G, "corpus.npz"))
+    rec = np.load(os.path.join(G, "trajectory_none.npz"))
+    g = np.load(os.path.join(G, "recognize.npz"))
+    dim = int(c["dim"])
+    lex = synth.Lexicon()
+    O = Oracle(dim, lex.num_states, "none", True, tuple(c["tdp"]), lex.silence_state)
+    O.load_tables({k: rec["t2_" + k] for k in TABLES})
+    O.finalize()
+    word_off = np.concatenate([[0], np.cumsum([len(a) for a in lex.automata])]).astype(np.uint32)
+    word_states = np.concatenate(lex.automata).astype(np.uint32)
+    total = 0
+    for ci, (wp, thr) in enumerate(g["configs"]):
+        words, off = g["words%d" % ci], g["off%d" % ci]
+        for u in range(len(c["frame_off"]) - 1):
+            x = c["x"][int(c["frame_off"][u]):int(c["frame_off"][u + 1])]
+            got, _ = O.recognize(x, word_off, word_states, lex.silence, float(wp), float(thr))
+            assert np.array_equal(got, words[off[u]:off[u + 1]]), (ci, u)
+            total += len(got)
+    assert total > 0

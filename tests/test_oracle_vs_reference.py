@@ -55,3 +55,50 @@ def test_em_and_alignment_live(pooling):
         assert O.am_score(ali, x) == R.am_score(ali, x)
         s_o, a_o = O.min_score(x[:200]); s_r, a_r = R.min_score(x[:200])
         assert np.array_equal(s_o, s_r) and np.array_equal(a_o, a_r)
+
+
+@pytest.mark.parametrize("scale,word_penalty,am_threshold", [(1.0, 10.0, 20.0), (1.0, 3.0, 1e30), (0.05, 10.0, 60.0)])
+def test_recognize_live(scale, word_penalty, am_threshold):
+    """orc_recognize against the unmodified Recognizer::recognizeSequence_pruned (Recognizer.cpp:103-232): default
+    beam, no beam, and features scaled so that emission scores are NEGATIVE (the pre-emission rejection test of
+    :142-145 then drops candidates a plain minimum would keep)."""
+    rng = np.random.default_rng(5)
+    lex = synth.Lexicon()
+    d = 25
+    gen = synth.random_model(rng, d, lex.num_states, 2, "none")
+    corp = synth.make_corpus(rng, lex, gen, d, 16)
+    x = (corp["x"] * scale).astype(np.float32)
+    tdp = (3.0, 0.0, 30.0)
+    O = Oracle(d, 106, "none", True, tdp, 0)
+    R = Reference(d, 106, "none", True, tdp, 0, extra_config={"am-threshold": float(am_threshold),
+                                                             "word-penalty": float(word_penalty)})
+    ali = synth.linear_alignment(corp["frame_off"], corp["automata"], corp["aut_off"])
+    for M in (O, R):
+        M.accumulate(ali, x, True); M.finalize()
+    ali, _ = O.align_batch(x, corp["frame_off"], corp["automata"], corp["aut_off"], threads=4)
+    for M in (O, R):
+        M.accumulate(ali, x); M.finalize()
+    word_off = np.concatenate([[0], np.cumsum([len(a) for a in lex.automata])]).astype(np.uint32)
+    word_states = np.concatenate(lex.automata).astype(np.uint32)
+    n_nonempty = 0
+    for u in range(8):
+        f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
+        got, score = O.recognize(x[f0:f1], word_off, word_states, lex.silence, word_penalty, am_threshold)
+        want = R.recognize(x[f0:f1])
+        assert np.array_equal(got, want), (u, got, want)
+        n_nonempty += len(want) > 0
+    assert n_nonempty >= 4
+
+
+def test_edit_distance_live():
+    """The host mirror's editDistance (csrc/host/Recognizer.cpp) against Recognizer::editDistance (Recognizer.cpp:332-388)
+    on random word sequences, including the reference's column-0 behaviour for leading insertions."""
+    from speechrecognition_b200 import hostapi
+    R = Reference(9, 106, "none", True, (3.0, 0.0, 30.0), 0)
+    rng = np.random.default_rng(3)
+    cases = [([1, 2], [5, 6, 1, 2]), ([], [4, 4, 4]), ([1, 2, 3], []), ([], [])]
+    for _ in range(300):
+        nr, nh = int(rng.integers(0, 9)), int(rng.integers(0, 9))
+        cases.append((rng.integers(1, 5, nr).tolist(), rng.integers(1, 5, nh).tolist()))
+    for ref, hyp in cases:
+        assert hostapi.edit_distance(ref, hyp) == R.edit_distance(ref, hyp), (ref, hyp)

@@ -66,5 +66,31 @@ def main():
         print(pooling, "densities", R.num_densities(), "am", rec["am0"], rec["am2"])
 
 
+REC_CONFIGS = ((10.0, 20.0), (10.0, 1e30), (2.0, 45.0))   # (word-penalty, am-threshold); defaults first (Recognizer.cpp:31-32)
+
+
+def recognition():
+    """recognize.npz: Recognizer::recognizeSequence_pruned (Recognizer.cpp:103-232) on every golden utterance with the
+    final model of the "none" trajectory (mix_none.mix), for three (word-penalty, am-threshold) settings."""
+    c = np.load(os.path.join(OUT, "corpus.npz"))
+    lex = synth.Lexicon()
+    rec = {"configs": np.array(REC_CONFIGS)}
+    for ci, (wp, thr) in enumerate(REC_CONFIGS):
+        R = Reference(DIM, lex.num_states, "none", True, TDP, lex.silence_state, mix_path=os.path.join(OUT, "mix_none.mix"),
+                      extra_config={"am-threshold": float(thr), "word-penalty": float(wp)})
+        words, off = [], [0]
+        for u in range(len(c["frame_off"]) - 1):
+            w = R.recognize(c["x"][int(c["frame_off"][u]):int(c["frame_off"][u + 1])])
+            words.extend(int(v) for v in w)
+            off.append(len(words))
+        rec["words%d" % ci], rec["off%d" % ci] = np.array(words, np.uint32), np.array(off, np.uint32)
+        print("recognize", wp, thr, "->", off[-1], "words")
+    np.savez_compressed(os.path.join(OUT, "recognize.npz"), **rec)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "recognize":
+        recognition()
+    else:
+        main()
+        recognition()

@@ -100,7 +100,7 @@ __device__ __forceinline__ uint64_t desc_sw32(uint32_t saddr) {
   return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)6 << 61);
 }
 template <int TF32>
-__global__ void k_mma(int n, uint32_t N, long long* cycles) {
+__global__ void k_mma(int n, uint32_t N, long long* cycles, uint32_t M = 128) {
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_ptr;
   __shared__ uint64_t bar;
@@ -119,7 +119,7 @@ __global__ void k_mma(int n, uint32_t N, long long* cycles) {
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   if (threadIdx.x == 0) {
-    const uint32_t idesc = TF32 ? ((1u << 4) | (2u << 7) | (2u << 10) | ((N >> 3) << 17) | ((128u >> 4) << 24))
+    const uint32_t idesc = TF32 ? ((1u << 4) | (2u << 7) | (2u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24))
                                 : ((1u << 4) | (0u << 7) | (0u << 10) | ((N >> 3) << 17) | ((128u >> 4) << 24));   // f16 x f16 -> f32
     const uint64_t ad = desc_sw32(smem_u32(sm)), bd = desc_sw32(smem_u32(sm) + 4096);
     const long long t0 = clock64();
@@ -145,10 +145,10 @@ __global__ void k_mma(int n, uint32_t N, long long* cycles) {
 // ---- the GEMM kernel's issue pattern on every SM: units of `ks` k-steps x 3 passes into rotating accumulators.
 // MODE 0: all three passes A-from-shared (SS); 1: all A-from-TMEM (TS); 2: two TS passes + one SS pass (the kernel's mix)
 template <int MODE>
-__global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, unsigned long long* ns) {
+__global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, unsigned long long* ns, int commits) {
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_ptr;
-  __shared__ uint64_t bar;
+  __shared__ uint64_t bar, dummy[2];
   uint32_t x = seed + threadIdx.x * 2654435761u + blockIdx.x;
   for (int i = threadIdx.x; i < 3 * 8 * 4096 / 4; i += blockDim.x) {
     x = x * 1664525u + 1013904223u;
@@ -157,6 +157,8 @@ __global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, u
   const int warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&bar)), "r"(1));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&dummy[0])), "r"(1 << 20));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&dummy[1])), "r"(1 << 20));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -188,6 +190,8 @@ __global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, u
                          "l"(alo + kk * 256), "l"(b + kk * 256), "r"(idesc), "r"(acc) : "memory");
         }
       }
+      for (int cm = 0; cm < commits; cm++)
+        asm volatile("{\n\t.reg .pred pe;\n\telect.sync _|pe, 0xffffffff;\n\t@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(&dummy[cm & 1])) : "memory");
     }
     asm volatile("{\n\t.reg .pred pe;\n\telect.sync _|pe, 0xffffffff;\n\t@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(&bar)) : "memory");
     asm volatile("{\n\t.reg .pred p;\n\tW2:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra D2;\n\tbra W2;\n\tD2:\n\t}" ::"r"(
@@ -225,6 +229,18 @@ int main() {
     cudaMemcpy(&h, d_cyc, 8, cudaMemcpyDeviceToHost);
     printf("mma f16  128x%ux16: %.1f cycles per MMA\n", N, h / (double)n);
   }
+  for (uint32_t N : {32u, 64u, 128u, 256u}) {
+    const int n = 4096;
+    k_mma<1><<<1, 128, 16384>>>(n, N, d_cyc, 64u); cudaDeviceSynchronize();
+    cudaMemcpy(&h, d_cyc, 8, cudaMemcpyDeviceToHost);
+    printf("mma tf32 M=64 64x%ux8 : %.1f cycles per MMA\n", N, h / (double)n);
+  }
+  for (uint32_t N : {16u, 32u}) {
+    const int n = 4096;
+    k_mma<1><<<1, 128, 16384>>>(n, N, d_cyc, 128u); cudaDeviceSynchronize();
+    cudaMemcpy(&h, d_cyc, 8, cudaMemcpyDeviceToHost);
+    printf("mma tf32 M=128 128x%ux8 : %.1f cycles per MMA\n", N, h / (double)n);
+  }
   printf("cudaGetLastError: %s\n", cudaGetErrorString(cudaGetLastError()));
   const char* names[] = {"FMNMX", "FMNMX3", "FSETP+FSEL", "FFMA", "LOP3", "FFMA+SAT+FADD"};
   for (int nw : {4, 8}) {
@@ -253,18 +269,19 @@ int main() {
     cudaFuncSetAttribute(k_mma_mix<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(k_mma_mix<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(k_mma_mix<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    for (int grid : {1, 148})
-      for (uint32_t seed : {0u, 7u})
+    for (int grid : {148})
+      for (int commits : {0, 1, 2})
         for (int mode = 0; mode < 3; mode++) {
           const int units = 4000, ks = 5;
-          if (mode == 0) k_mma_mix<0><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns);
-          if (mode == 1) k_mma_mix<1><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns);
-          if (mode == 2) k_mma_mix<2><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns);
+          const uint32_t seed = 7u;
+          if (mode == 0) k_mma_mix<0><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns, commits);
+          if (mode == 1) k_mma_mix<1><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns, commits);
+          if (mode == 2) k_mma_mix<2><<<grid, 128, smem>>>(units, ks, seed, d_cyc, d_ns, commits);
           cudaDeviceSynchronize();
           cudaMemcpy(hc, d_cyc, grid * 8, cudaMemcpyDeviceToHost); cudaMemcpy(hn, d_ns, grid * 8, cudaMemcpyDeviceToHost);
           long long mc = 0; unsigned long long mns = 0;
           for (int i = 0; i < grid; i++) { if (hc[i] > mc) mc = hc[i]; if (hn[i] > mns) mns = hn[i]; }
-          printf("mma mix %s grid=%3d data=%s: %.1f cycles per MMA, %.2f GHz\n", mn[mode], grid, seed ? "random" : "zeros",
+          printf("mma mix %s grid=%3d commits/unit=%d: %.1f cycles per MMA, %.2f GHz\n", mn[mode], grid, commits,
                  mc / (double)(units * 3 * ks), (double)mc / (double)mns);
         }
     printf("cudaGetLastError: %s\n", cudaGetErrorString(cudaGetLastError()));
