@@ -19,7 +19,7 @@ ALI_DTYPE = np.dtype([("count", np.uint16), ("state", np.uint16), ("weight", np.
 # every symbol include/sietill_b200.h declares (checked by tests/test_capi_symbols.py)
 SYMBOLS = [
     "sgmm_create", "sgmm_destroy", "sgmm_last_error", "sgmm_version", "sgmm_set_model", "sgmm_set_features",
-    "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
+    "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_set_lexicon", "sgmm_recognize", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
     "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
     "sgmm_launch_count", "sgmm_timer_start", "sgmm_timer_stop", "sgmm_host_alloc", "sgmm_host_free",
     "sgmm_set_option", "sgmm_get_counter",
