@@ -371,3 +371,36 @@ def test_recognize_golden():
         for u in range(len(c["frame_off"]) - 1):
             assert np.array_equal(got[u], words[off[u]:off[u + 1]]), (ci, u)
     ctx.close()
+
+
+def test_stress_shape_config5():
+    """BASELINE config 5 shape: 4501 tied states x 64 densities, d = 48, per-state pooled variances; utterances are
+    chains of 50 x 3 random states.  A few utterances against the oracle: alignment, path costs, argmin densities
+    and accumulator counts bit-exact; u32 density indices (288 064 densities > 65 535)."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(synth.SEED)
+    n_states, nd, dim = 4501, 64, 48
+    tables = synth.random_model(rng, dim, n_states, nd, "mixture")
+    corp = synth.make_chain_corpus(rng, tables, dim, n_states, 6, T=400)
+    O = Oracle(dim, n_states, "mixture", True, (3.0, 0.0, 30.0), 0)
+    O.load_tables(tables)
+    want_states, want_costs = O.align_batch(corp["x"], corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, tables)
+    ctx.set_features(corp["x"])
+    ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"])
+    ctx.set_tdp(3.0, 0.0, 30.0, 0)
+    assert ctx.get_counter("scorer") == 3            # the tensor-core scorer takes this shape (7 k-steps)
+    got, costs = ctx.align()
+    assert np.array_equal(got["state"], want_states)
+    assert np.array_equal(costs, want_costs)
+    cnt, sx, sxx, ssum = ctx.accumulate(first_pass=False)
+    dens, score = ctx.last_frame_results()
+    want_dens = O.accumulate(want_states, corp["x"])
+    assert np.array_equal(dens, want_dens)
+    t = O.tables()
+    assert np.array_equal(cnt, t["mean_wacc"][t["mean_idx"].astype(np.int64)])
+    assert cnt.sum() == len(want_states) and len(cnt) == n_states * nd
+    np.testing.assert_allclose(sx, t["mean_acc"].reshape(-1, dim)[t["mean_idx"].astype(np.int64)], rtol=STAT_RTOL, atol=0)
+    ctx.close()
