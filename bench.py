@@ -208,7 +208,7 @@ def run_reference(args):
                                        "parallel utterance shards, accumulate single-threaded" % (args.ref_utts, frames, cores)},
             "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -339,6 +339,21 @@ def run_ours(args):
                 "traffic": None}
     roof["frac"] = roof["achieved"] / roof["peak"]
     roof["algorithmic_flops_per_step"] = alg_flops
+    # the same algorithmic flops over the WHOLE K1 stage (filter + f64 refinement + rescans): what a caller sees
+    roof["k1_stage"] = {"ms": stage["score"], "achieved": alg_flops / (stage["score"] / 1e3) / 1e12,
+                        "frac": alg_flops / (stage["score"] / 1e3) / 1e12 / roof["peak"]}
+    if scorer == 3:
+        # what the tensor pipe executes: pooled variances drop the x^2 block (K = d + 1, padded to 8), 3 MMAs per term
+        kp = 8 * ((args.dim + 1 + 7) // 8)
+        roof["executed"] = {"k": kp, "tf32_tflops": 3 * 2.0 * kp * dens_scored / t_kernel / 1e12,
+                            "tf32_peak": float(peaks.get("bf16_tflops", 1590.0)) / 2.0}
+    try:   # DRAM bytes per launch of the dominant kernel, from the committed `ncu --set full` summary of this command
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if tr.get("frames_per_gpu") == F and tr.get("kernel", "").split("<")[0] in roof["kernel"]:
+            roof["traffic"] = tr["dram_bytes_per_launch"]
+            roof["traffic_source"] = tr.get("source")
+    except Exception:
+        pass
     # Viterbi: algorithmic bytes = emission row read (f64) + AlignmentItem write per frame
     ncols = []
     for u in range(U):
@@ -371,12 +386,33 @@ def run_ours(args):
                                 "sample": "first %d utterances (%d frames) of the shard, one pass; alignment in %d parallel "
                                           "utterance shards (%.1f s), accumulate single-threaded (%.1f s)"
                                           % (args.ref_utts, r["frames"], cores, r["align_s"], r["accumulate_s"])}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else printed meanwhile (NCCL's version
+    banner, library chatter) was sent to stderr by quiet_stdout()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
+def quiet_stdout():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
 if __name__ == "__main__":
+    quiet_stdout()
     a = parse()
     if a.impl == "reference":
         run_reference(a)

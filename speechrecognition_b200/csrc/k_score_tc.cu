@@ -98,6 +98,33 @@ __device__ __forceinline__ void tc_mma_tf32_ss(uint32_t d_tmem, uint64_t adesc, 
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
       : "memory");
 }
+// One lane of the converged warp (elect.sync): the caller issues a whole unit's MMAs and commits inside
+// `if (tc_elect_one()) { ... }`, so the election and the uniform-register moves are paid once per unit instead of
+// once per MMA (the per-MMA form compiled to ~33 SASS instructions per MMA and left the tensor pipe ~50 % idle).
+__device__ __forceinline__ uint32_t tc_elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred pe;\n\t"
+      "elect.sync _|pe, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, pe;\n\t}" : "=r"(pred));
+  return pred;
+}
+__device__ __forceinline__ void tc_mma_ts_1(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred pa;\n\t"
+      "setp.ne.b32 pa, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, pa;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void tc_mma_ss_1(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred pa;\n\t"
+      "setp.ne.b32 pa, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, pa;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
 __device__ __forceinline__ void tc_commit_elect(uint64_t* bar) {
   asm volatile(
       "{\n\t.reg .pred pe;\n\t"
@@ -336,29 +363,32 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           const uint64_t a_s1 = make_desc_sw32(smem_u32(sAhi + h * (p.stage_bytes / 2)));
           const bool hi_t = p.a_smem == 0, lo_t = p.a_smem == 2;
           const uint64_t hi_s = p.a_smem == 1 ? a_s1 : a_s0, lo_s = a_s0;
-          if (!(p.debug & 2)) {
-            const uint32_t nk = KS > 0 ? (uint32_t)KS : ks;
-            if (hi_t) {
+          if (tc_elect_one()) {
+            if (!(p.debug & 2)) {
+              const uint32_t nk = KS > 0 ? (uint32_t)KS : ks;
+              if (hi_t) {
 #pragma unroll
-              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ts(d, a_t + kk * 8, bhi + kk * kstride, idesc, kk);
+                for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ts_1(d, a_t + kk * 8, bhi + kk * kstride, idesc, kk);
 #pragma unroll
-              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ts(d, a_t + kk * 8, blo + kk * kstride, idesc, 1);
-            } else {
+                for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ts_1(d, a_t + kk * 8, blo + kk * kstride, idesc, 1);
+              } else {
 #pragma unroll
-              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ss(d, hi_s + kk * kstride, bhi + kk * kstride, idesc, kk);
+                for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, hi_s + kk * kstride, bhi + kk * kstride, idesc, kk);
 #pragma unroll
-              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ss(d, hi_s + kk * kstride, blo + kk * kstride, idesc, 1);
+                for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, hi_s + kk * kstride, blo + kk * kstride, idesc, 1);
+              }
+              if (lo_t) {
+#pragma unroll
+                for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ts_1(d, a_t + kk * 8, bhi + kk * kstride, idesc, 1);
+              } else {
+#pragma unroll
+                for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, lo_s + kk * kstride, bhi + kk * kstride, idesc, 1);
+              }
             }
-            if (lo_t) {
-#pragma unroll
-              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ts(d, a_t + kk * 8, bhi + kk * kstride, idesc, 1);
-            } else {
-#pragma unroll
-              for (uint32_t kk = 0; kk < nk; kk++) tc_mma_tf32_ss(d, lo_s + kk * kstride, bhi + kk * kstride, idesc, 1);
-            }
+            if (h + 1 == nh) tc_commit(&empty[stage]);   // stage reusable once every MMA that reads it is done
+            tc_commit(&tfull[buf]);
           }
-          if (h + 1 == nh) tc_commit_elect(&empty[stage]);   // stage reusable once every MMA that reads it is done
-          tc_commit_elect(&tfull[buf]);
+          __syncwarp();
         }
       }
     }
