@@ -45,14 +45,17 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// suspend-time hint: a waiting warp sleeps in hardware until the phase completes instead of re-polling (polling loops
+// were ~23 % of all issued instructions and compete with the MMA-issuing warp for its scheduler)
+constexpr uint32_t kWaitHintNs = 20000;
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
       "@p bra DONE_%=;\n\t"
       "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity), "r"(kWaitHintNs) : "memory");
 }
 // busy poll (no suspend): lower wake-up latency for the MMA <-> epilogue hand-offs on the critical path
 __device__ __forceinline__ void mbar_spin(uint64_t* bar, uint32_t parity) {
@@ -231,6 +234,11 @@ struct TcParams {
   const uint32_t* uniq_off;
   const uint32_t* nuniq_pad;
   const uint64_t* E_off;
+  // packed tail tasks (task.x & 0x80000000): rows from several utterances against the union of their state lists
+  const uint4* pack_desc;            // {first entry in pack_uniq, states in the union, valid rows, 0}
+  const uint32_t* pack_uniq;
+  const sgmm_pack_row* pack_rows;    // [pack][128]
+  const uint16_t* pack_colmap;
   // dense mode
   int dense;
   uint64_t f0, nframes;
@@ -274,6 +282,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
   uint64_t row0;        // first A row (absolute frame index)
   uint32_t nvalid, nu, out_stride;
   const uint32_t* ulist = nullptr;
+  const sgmm_pack_row* prow = nullptr;   // packed task: per-row frame / output cell / column map
   uint64_t out_base;
   if (p.dense) {
     const uint64_t r0 = task * ROWS;
@@ -282,6 +291,12 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
     nu = p.n_states;
     out_stride = p.n_states;
     out_base = r0 * p.n_states;
+  } else if (p.tasks[task].x & 0x80000000u) {
+    const uint32_t id = p.tasks[task].x & 0x7fffffffu;
+    const uint4 d = p.pack_desc[id];
+    prow = p.pack_rows + (size_t)id * 128;
+    row0 = 0; nvalid = d.z; nu = d.y; out_stride = 0; out_base = 0;
+    ulist = p.pack_uniq + d.x;
   } else {
     const uint4 t = p.tasks[task];
     const uint64_t uf0 = p.frame_off[t.x];
@@ -418,7 +433,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
       const uint32_t tlane = tmem_base + ((quarter * 32) << 16);
       // A rows of this thread's frame: hi -> TMEM, lo -> shared memory (part 0 only)
       if (part == 0) {
-        const uint64_t fr = min(row0 + row, p.n_frames - 1);     // rows past the end are never read back
+        const uint64_t fr = prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1);   // rows past the end are never read back
         const float4* ah = reinterpret_cast<const float4*>(p.Ahi + fr * KP);
         const float4* al = reinterpret_cast<const float4*>(p.Alo + fr * KP);
         const uint32_t acol = tlane + group * KP;
@@ -444,7 +459,9 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
         __syncwarp();
         if (lane == 0) mbar_arrive(a_full);
       }
-      const float2 xn = p.xnorm[min(row0 + row, p.n_frames - 1)];
+      const float2 xn = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
+      const uint64_t my_cell = prow ? prow[row].cell : out_base + (uint64_t)row * out_stride;
+      const uint16_t* my_map = prow ? p.pack_colmap + prow[row].colmap : nullptr;
       float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
       uint32_t it = 0;
       long long e_wait = 0;
@@ -542,7 +559,8 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           else Bsecond = fminf(Bsecond, ob);
           if (row < nvalid) {
             const bool certain = Bacc == 1.0f && Bsecond > Bbest + BG;
-            p.cand[out_base + (uint64_t)row * out_stride + j] = certain ? (uint32_t)Bidx : kUncertain;
+            const uint32_t col = my_map ? (uint32_t)my_map[j] : j;     // packed: this frame's utterance may not use state j
+            if (col != 0xFFFFu || !my_map) p.cand[my_cell + col] = certain ? (uint32_t)Bidx : kUncertain;
           }
         }
       }
@@ -830,6 +848,8 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.tasks = nhalf == 2 ? c->d_tasks256.p : c->d_tasks128.p;
   p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
   p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p;
+  p.pack_desc = c->d_pack_desc.p; p.pack_uniq = c->d_pack_uniq.p; p.pack_rows = c->d_pack_rows.p;
+  p.pack_colmap = c->d_pack_colmap.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
   const size_t smem = tc_smem(stage_bytes, nhalf, nstage, a_smem);

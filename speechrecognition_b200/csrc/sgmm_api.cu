@@ -386,10 +386,6 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       tasks128.push_back(make_uint4(u, t0, 0, 0));
       t128_end.push_back(frame_off[u] + std::min(T, t0 + 128));
     }
-    for (uint32_t t0 = 0; t0 < T; t0 += 256) {
-      tasks256.push_back(make_uint4(u, t0, 0, 0));
-      t256_end.push_back(frame_off[u] + std::min(T, t0 + 256));
-    }
     int C = 0;
     for (int cc : kViterbiC) if ((uint32_t)cc * 32 >= S) { C = cc; break; }
     size_t sm = viterbi_smem(T, S, ncol[u], C);
@@ -400,6 +396,80 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     ViterbiClass& vc = classes[{C, bucket}];
     vc.C = C; vc.smem = bucket;
     vc.utts.push_back(u);
+  }
+  // ---- GEMM tasks of 256 frames.  The last task of an utterance often holds few frames (T = 279 leaves 23), yet a
+  // 128-row MMA half costs the same however many rows are valid.  Short tails of consecutive utterances are
+  // therefore PACKED into one 128-row half that is scored against the union of their state lists, when that
+  // is cheaper than one half per tail.  A packed task is {0x80000000 | pack id}; per row it carries the frame,
+  // the first emission cell of that frame's row, and a map union column -> column of the utterance's own list.
+  std::vector<uint4> pack_desc;                  // {first entry in pack_uniq, states in the union, valid rows, 0}
+  std::vector<uint32_t> pack_uniq;
+  std::vector<sgmm_pack_row> pack_rows;          // [pack][128]
+  std::vector<uint16_t> pack_colmap;
+  {
+    struct Seg { uint32_t u, t0, rows; };
+    std::vector<Seg> open;
+    uint32_t open_rows = 0;
+    uint64_t last_end = 0;
+    auto emit_plain = [&](uint32_t u, uint32_t t0, uint32_t T) {
+      tasks256.push_back(make_uint4(u, t0, 0, 0));
+      last_end = std::max(last_end, frame_off[u] + std::min(T, t0 + 256));
+      t256_end.push_back(last_end);
+    };
+    auto close_pack = [&]() {
+      if (open.empty()) return;
+      std::vector<uint32_t> uni;
+      size_t own = 0;
+      for (const Seg& sg : open) {
+        uni.insert(uni.end(), uniq.begin() + uniq_off[sg.u], uniq.begin() + uniq_off[sg.u + 1]);
+        own += uniq_off[sg.u + 1] - uniq_off[sg.u];
+      }
+      std::sort(uni.begin(), uni.end());
+      uni.erase(std::unique(uni.begin(), uni.end()), uni.end());
+      if (open.size() == 1 || uni.size() * 10 > own * 9) {       // the union saves < 10 %: one half per tail after all
+        for (const Seg& sg : open) emit_plain(sg.u, sg.t0, (uint32_t)(frame_off[sg.u + 1] - frame_off[sg.u]));
+      } else {
+        const uint32_t id = (uint32_t)pack_desc.size();
+        pack_desc.push_back(make_uint4((uint32_t)pack_uniq.size(), (uint32_t)uni.size(), open_rows, 0));
+        pack_uniq.insert(pack_uniq.end(), uni.begin(), uni.end());
+        pack_rows.resize((size_t)(id + 1) * 128);
+        sgmm_pack_row* rows = pack_rows.data() + (size_t)id * 128;
+        uint32_t r = 0;
+        uint64_t end = 0;
+        for (const Seg& sg : open) {
+          const uint32_t cm = (uint32_t)pack_colmap.size();
+          const uint32_t* ub = uniq.data() + uniq_off[sg.u];
+          const uint32_t nu_u = uniq_off[sg.u + 1] - uniq_off[sg.u];
+          for (uint32_t s : uni) {
+            const uint32_t* it = std::lower_bound(ub, ub + nu_u, s);
+            pack_colmap.push_back((it != ub + nu_u && *it == s) ? (uint16_t)(it - ub) : (uint16_t)0xFFFF);
+          }
+          for (uint32_t i = 0; i < sg.rows; i++, r++) {
+            rows[r].cell = E_off[sg.u] + (uint64_t)(sg.t0 + i) * ncol[sg.u];
+            rows[r].frame = (uint32_t)(frame_off[sg.u] + sg.t0 + i);
+            rows[r].colmap = cm;
+          }
+          end = std::max(end, frame_off[sg.u] + sg.t0 + sg.rows);
+        }
+        for (; r < 128; r++) rows[r] = rows[0];                   // rows past the end: any valid frame, never written
+        tasks256.push_back(make_uint4(0x80000000u | id, 0, 0, 0));
+        last_end = std::max(last_end, end);
+        t256_end.push_back(last_end);
+      }
+      open.clear(); open_rows = 0;
+    };
+    const uint32_t kPackMaxRows = 96;
+    for (uint32_t u = 0; u < U; u++) {
+      const uint32_t T = (uint32_t)(frame_off[u + 1] - frame_off[u]);
+      const uint32_t tail = T % 256;
+      const bool packable = c->tc_pack && frame_off[U] < 0xffffffffull && tail > 0 && tail <= kPackMaxRows;
+      if (packable && (open_rows + tail > 128 || open.size() >= 8)) close_pack();
+      for (uint32_t t0 = 0; t0 + 256 <= T; t0 += 256) emit_plain(u, t0, T);
+      if (tail == 0) continue;
+      if (packable) { open.push_back({u, T - tail, tail}); open_rows += tail; }
+      else emit_plain(u, T - tail, T);
+    }
+    close_pack();
   }
   for (auto& vc : c->vclasses) vc.d_utts.release();
   c->vclasses.clear();
@@ -418,8 +488,13 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       upload(c, c->d_pos2uniq, p2u.data(), p2u.size()) || upload(c, c->d_E_off, E_off.data(), E_off.size()) ||
       upload(c, c->d_tasks, tasks.data(), tasks.size()) || upload(c, c->d_tasks64, tasks64.data(), tasks64.size()) ||
       upload(c, c->d_tasks128, tasks128.data(), tasks128.size()) ||
-      upload(c, c->d_tasks256, tasks256.data(), tasks256.size()))
+      upload(c, c->d_tasks256, tasks256.data(), tasks256.size()) ||
+      upload(c, c->d_pack_desc, pack_desc.data(), pack_desc.size()) ||
+      upload(c, c->d_pack_uniq, pack_uniq.data(), pack_uniq.size()) ||
+      upload(c, c->d_pack_rows, pack_rows.data(), pack_rows.size()) ||
+      upload(c, c->d_pack_colmap, pack_colmap.data(), pack_colmap.size()))
     return 1;
+  c->n_packs = pack_desc.size();
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->max_aut_state = max_state; c->max_uniq = max_uniq;
   c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->n_tasks128 = tasks128.size(); c->n_tasks256 = tasks256.size(); c->E_elems = E_off[U];
@@ -520,6 +595,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "rescore_cache")) { c->use_cache = value != 0; return 0; }
   if (!strcmp(key, "tc_debug")) { c->tc_debug = (int)value; return 0; }
   if (!strcmp(key, "async_upload")) { c->async_upload = value != 0; return 0; }
+  if (!strcmp(key, "tc_pack")) { c->tc_pack = value != 0; return 0; }   // takes effect at the next sgmm_set_corpus
   if (!strcmp(key, "upload_chunks")) {
     if (value < 1 || value > sgmm_ctx::kFeatChunks) SGMM_FAIL(c, "set_option: upload_chunks out of range");
     c->feat_chunks = (int)value;

@@ -29,6 +29,12 @@ struct DevBuf {
   void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+struct sgmm_pack_row {   // one row of a packed GEMM task (sgmm_set_corpus)
+  uint64_t cell;     // first emission cell of this frame's row in the ragged emission matrix
+  uint32_t frame;    // absolute frame index
+  uint32_t colmap;   // first entry of this row's segment in the column map (union column -> own column, 0xFFFF: none)
+};
+
 struct ViterbiClass {  // utterances that share one launch (same lanes-per-position shape + smem size)
   int C = 0;                 // positions per lane
   size_t smem = 0;           // dynamic shared memory per CTA
@@ -104,6 +110,12 @@ struct sgmm_ctx {
   DevBuf<uint4> d_tasks128, d_tasks256;
   uint64_t n_tasks128 = 0, n_tasks256 = 0;
   std::vector<uint64_t> h_t128_end, h_t256_end;   // exclusive end frame of every task (ascending)
+  bool tc_pack = true;             // option "tc_pack": pack short utterance tails into shared 128-row GEMM halves
+  size_t n_packs = 0;
+  DevBuf<uint4> d_pack_desc;
+  DevBuf<uint32_t> d_pack_uniq;
+  DevBuf<sgmm_pack_row> d_pack_rows;
+  DevBuf<uint16_t> d_pack_colmap;
   int tc_debug = 0;                // option "tc_debug": timing experiments (k_score_tc.cu), never set in production
   int tc_halves = 0;               // option "tc_halves": 0 auto, 1 / 2 = frame halves (128 rows each) per GEMM CTA
   DevBuf<uint4> d_tasks, d_tasks64;   // emission warp-tasks {utt, t0, 0, 0}: 32-frame and 64-frame granules

@@ -145,12 +145,12 @@ __global__ void k_mma(int n, uint32_t N, long long* cycles, uint32_t M = 128) {
 // ---- the GEMM kernel's issue pattern on every SM: units of `ks` k-steps x 3 passes into rotating accumulators.
 // MODE 0: all three passes A-from-shared (SS); 1: all A-from-TMEM (TS); 2: two TS passes + one SS pass (the kernel's mix)
 template <int MODE>
-__global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, unsigned long long* ns, int commits) {
+__global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, unsigned long long* ns, int commits, uint32_t a_col = 0, uint32_t d_col = 128, uint32_t N = 128) {
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t tmem_ptr;
   __shared__ uint64_t bar, dummy[2];
   uint32_t x = seed + threadIdx.x * 2654435761u + blockIdx.x;
-  for (int i = threadIdx.x; i < 3 * 8 * 4096 / 4; i += blockDim.x) {
+  for (int i = threadIdx.x; i < 3 * 8 * 8192 / 4; i += blockDim.x) {
     x = x * 1664525u + 1013904223u;
     reinterpret_cast<float*>(sm)[i] = seed ? (float)(int)(x >> 20) * 1e-3f : 0.f;
   }
@@ -170,13 +170,13 @@ __global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, u
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   if (warp == 0) {   // converged warp, one elected lane issues (the kernel's pattern)
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
-    const uint64_t alo = desc_sw32(smem_u32(sm)), bhi = desc_sw32(smem_u32(sm) + 8 * 4096), blo = desc_sw32(smem_u32(sm) + 16 * 4096);
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((N >> 3) << 17) | ((128u >> 4) << 24);
+    const uint64_t alo = desc_sw32(smem_u32(sm)), bhi = desc_sw32(smem_u32(sm) + 8 * 4096), blo = desc_sw32(smem_u32(sm) + 8 * 4096 + 8 * 8192);
     unsigned long long g0, g1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
     const long long t0 = clock64();
     for (int u = 0; u < units; u++) {
-      const uint32_t d = tmem_ptr + 128 + (u % 3) * 128;
+      const uint32_t d = tmem_ptr + d_col + (N == 256 ? 0u : (u % 3) * 128);
       for (int pass = 0; pass < 3; pass++) {
         const bool ts = MODE == 1 || (MODE == 2 && pass < 2);
         const uint64_t b = pass == 1 ? blo : bhi;
@@ -184,7 +184,7 @@ __global__ void k_mma_mix(int units, int ks, uint32_t seed, long long* cycles, u
           const uint32_t acc = (pass | kk) ? 1 : 0;
           if (ts)
             asm volatile("{\n\t.reg .pred p, pe;\n\telect.sync _|pe, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
-                         "r"(tmem_ptr + kk * 8), "l"(b + kk * 256), "r"(idesc), "r"(acc) : "memory");
+                         "r"(tmem_ptr + a_col + kk * 8), "l"(b + kk * 256), "r"(idesc), "r"(acc) : "memory");
           else
             asm volatile("{\n\t.reg .pred p, pe;\n\telect.sync _|pe, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t@pe tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
                          "l"(alo + kk * 256), "l"(b + kk * 256), "r"(idesc), "r"(acc) : "memory");
@@ -265,7 +265,7 @@ int main() {
     unsigned long long* d_ns; cudaMalloc(&d_ns, 1024 * 8);
     static long long hc[1024]; static unsigned long long hn[1024];
     const char* mn[] = {"SS,SS,SS", "TS,TS,TS", "TS,TS,SS"};
-    const size_t smem = 3 * 8 * 4096 + 1024;
+    const size_t smem = 3 * 8 * 8192 + 1024;
     cudaFuncSetAttribute(k_mma_mix<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(k_mma_mix<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(k_mma_mix<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -284,6 +284,19 @@ int main() {
           printf("mma mix %s grid=%3d commits/unit=%d: %.1f cycles per MMA, %.2f GHz\n", mn[mode], grid, commits,
                  mc / (double)(units * 3 * ks), (double)mc / (double)mns);
         }
+    printf("cudaGetLastError: %s\n", cudaGetErrorString(cudaGetLastError()));
+    // A-in-TMEM placement and N = 256
+    struct { uint32_t a, d, N; } cfgs[] = {{0, 128, 128}, {448, 0, 128}, {384, 0, 128}, {0, 256, 256}, {256, 0, 256}};
+    for (auto& c : cfgs)
+      for (int mode = 0; mode < 2; mode++) {
+        if (mode == 0) k_mma_mix<0><<<148, 128, smem>>>(4000, 5, 7u, d_cyc, d_ns, 1, c.a, c.d, c.N);
+        else k_mma_mix<1><<<148, 128, smem>>>(4000, 5, 7u, d_cyc, d_ns, 1, c.a, c.d, c.N);
+        cudaDeviceSynchronize();
+        cudaMemcpy(hc, d_cyc, 148 * 8, cudaMemcpyDeviceToHost);
+        long long mc = 0;
+        for (int i = 0; i < 148; i++) if (hc[i] > mc) mc = hc[i];
+        printf("mma %s A col %u, D col %u, N=%u: %.1f cycles per MMA\n", mode ? "TS" : "SS", c.a, c.d, c.N, mc / (double)(4000 * 15));
+      }
     printf("cudaGetLastError: %s\n", cudaGetErrorString(cudaGetLastError()));
   }
   return 0;
