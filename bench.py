@@ -309,14 +309,20 @@ def run_ours(args):
     frames_total = F * world
     stage = {k: float(np.mean([s[k] for s in stages])) for k in stages[0]}
     dens_scored = densities_scored(tables, corp)
-    K = 2 * args.dim + 1
+    # Algorithmic contraction length per (frame, density).  SURVEY.md §8(d) quotes K = 2d+1 (x^2 | x | 1); the
+    # workload's variances are pooled per state (BASELINE configs[1]: "pooled diag cov"), where the x^2 block is a
+    # per-(frame, state) scalar and the contraction that has to be evaluated per density is K = d+1 (x | 1) — the
+    # reference's own production scorer does the same (rwth BatchFeatureScorer).  The roofline uses
+    # d+1, so that `frac` cannot exceed what the tensor pipe really did; the 2d+1 figure is kept alongside.
+    K = args.dim + 1
+    K_survey = 2 * args.dim + 1
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
     scorer = ctx.get_counter("scorer")
-    alg_flops = 2.0 * K * dens_scored          # 2*(2d+1) per (frame, density scored)
+    alg_flops = 2.0 * K * dens_scored          # 2*(d+1) per (frame, density scored), pooled variances
     if scorer == 3:
         t_kernel = stage["score_filter"] / 1e3
         bf16 = float(peaks.get("bf16_tflops", 1590.0))
@@ -339,6 +345,9 @@ def run_ours(args):
                 "traffic": None}
     roof["frac"] = roof["achieved"] / roof["peak"]
     roof["algorithmic_flops_per_step"] = alg_flops
+    roof["algorithmic_k"] = K
+    roof["survey_2d1"] = {"k": K_survey, "achieved": 2.0 * K_survey * dens_scored / t_kernel / 1e12,
+                          "note": "SURVEY §8(d) convention (unpooled K); exceeds what is executed for pooled models"}
     # the same algorithmic flops over the WHOLE K1 stage (filter + f64 refinement + rescans): what a caller sees
     roof["k1_stage"] = {"ms": stage["score"], "achieved": alg_flops / (stage["score"] / 1e3) / 1e12,
                         "frac": alg_flops / (stage["score"] / 1e3) / 1e12 / roof["peak"]}
@@ -346,7 +355,8 @@ def run_ours(args):
         # what the tensor pipe executes: pooled variances drop the x^2 block (K = d + 1, padded to 8), 3 MMAs per term
         kp = 8 * ((args.dim + 1 + 7) // 8)
         roof["executed"] = {"k": kp, "tf32_tflops": 3 * 2.0 * kp * dens_scored / t_kernel / 1e12,
-                            "tf32_peak": float(peaks.get("bf16_tflops", 1590.0)) / 2.0}
+                            "tf32_peak": float(peaks.get("bf16_tflops", 1590.0)) / 2.0,
+                            "note": "useful tf32 flops issued (3 MMAs per term, K padded to 8), excluding padded rows"}
     try:   # DRAM bytes per launch of the dominant kernel, from the committed `ncu --set full` summary of this command
         tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         if tr.get("frames_per_gpu") == F and tr.get("kernel", "").split("<")[0] in roof["kernel"]:

@@ -126,7 +126,14 @@ int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
 /* ---- options / counters -------------------------------------------------------------------- */
 /* "scorer": 0 = automatic choice by model shape, 1 = exact-f64 kernel, 2 = FP32-FFMA kernel with certified
  * f64 refinement, 3 = tcgen05 3xTF32 tensor-core GEMM with certified f64 refinement.  Every scorer returns
- * results bit-identical to the reference; the choice only moves time. */
+ * results bit-identical to the reference; the choice only moves time.
+ * "rescore_cache" (default 1): sgmm_accumulate after sgmm_align with an unchanged model looks the aligned cells' scores up.
+ * "async_upload" (default 0): sgmm_set_features queues chunked copies ("upload_chunks", 1..8, default 8) and returns;
+ *   the host buffer must stay untouched until the next compute call returns (use sgmm_host_alloc memory).
+ * "tc_halves" (0 auto, 1, 2): 128-frame halves per tensor-core CTA.  "tc_pack" (default 1; read by sgmm_set_corpus):
+ *   pack short utterance tails into shared 128-row halves.
+ * "tc_debug": timing experiments for the tensor-core kernel — any bit other than 32 (cycle profile, read with the
+ *   "tc_prof1".."tc_prof12" counters) makes results INVALID; never set in production. */
 int sgmm_set_option(sgmm_ctx* ctx, const char* key, int64_t value);
 /* "fallbacks": (frame, state) cells whose f32 top-2 gap was inside the error bound and were re-scanned in
  * f64 since the counter was last read; "scorer": the scorer the automatic choice resolves to. */
