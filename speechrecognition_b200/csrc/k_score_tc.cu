@@ -581,6 +581,293 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
 }
 
 
+// ---- N = 256 variant.  Measured (tools/ubench_epilogue.cu): an N = 128 tf32 MMA retires every 80-106 cycles (shared-
+// memory bandwidth with A from shared memory, ~101 cycles with A from TMEM), an N = 256 one at the full 128 cycles.
+// Tiles here are up to 256 densities wide: two 256-column accumulators (all of TMEM), both A parts in shared memory,
+// and a ring of three HALF stages — a tile's hi block [k-step][256 rows][32 B] and its lo block are separate slots, so
+// that three slots (3 x 40 KB at d = 33) keep one tile in use and half of the next in flight.  Per (tile, half) unit:
+// Ahi.Bhi, Alo.Bhi (hi slot), then Ahi.Blo (lo slot).  With two halves, half h always owns accumulator h.
+template <int KS>
+__global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  unsigned char* sA = smem_raw + (base - smem_u32(smem_raw));      // [half][hi, lo][kstep][128 rows][32 B], 32-byte swizzle
+  unsigned char* sB = sA + p.nhalf * 2 * (p.stage_bytes / 2);      // [slot][kstep][256 rows][32 B]; stage_bytes = one slot
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + p.nstage * p.stage_bytes);
+  uint64_t* a_full = bars;                 // A rows are in TMEM (8 epilogue warps arrive)
+  uint64_t* full = bars + 1;
+  uint64_t* empty = full + kMaxStage;
+  uint64_t* tfull = empty + kMaxStage;     // [3] accumulator complete
+  uint64_t* tempty = tfull + kNumAcc;      // accumulator drained (two of the slots used)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + kNumAcc);
+  float* xchg = reinterpret_cast<float*>(tmem_ptr + 4);   // [2 slots][2 halves][128 rows][5]: column-part merge
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint64_t task = blockIdx.x;
+  const uint32_t ROWS = BM * p.nhalf;
+  const uint32_t nstage = p.nstage, ks = KS > 0 ? (uint32_t)KS : p.ksteps, KP = 8 * ks;
+  constexpr uint32_t kstrideA = 4096 >> 4, kstrideB = 8192 >> 4;   // descriptor units between k-step blocks (128 / 256 rows)
+  const uint32_t a_part = p.stage_bytes / 2;   // bytes of one A part of one half: ksteps * 4 KB
+
+  // ---- task decode (uniform over the CTA)
+  uint64_t row0;        // first A row (absolute frame index)
+  uint32_t nvalid, nu, out_stride;
+  const uint32_t* ulist = nullptr;
+  const sgmm_pack_row* prow = nullptr;   // packed task: per-row frame / output cell / column map
+  uint64_t out_base;
+  if (p.dense) {
+    const uint64_t r0 = task * ROWS;
+    row0 = p.f0 + r0;
+    nvalid = (uint32_t)min((uint64_t)ROWS, p.nframes - r0);
+    nu = p.n_states;
+    out_stride = p.n_states;
+    out_base = r0 * p.n_states;
+  } else if (p.tasks[task].x & 0x80000000u) {
+    const uint32_t id = p.tasks[task].x & 0x7fffffffu;
+    const uint4 d = p.pack_desc[id];
+    prow = p.pack_rows + (size_t)id * 128;
+    row0 = 0; nvalid = d.z; nu = d.y; out_stride = 0; out_base = 0;
+    ulist = p.pack_uniq + d.x;
+  } else {
+    const uint4 t = p.tasks[task];
+    const uint64_t uf0 = p.frame_off[t.x];
+    const uint32_t T = (uint32_t)(p.frame_off[t.x + 1] - uf0);
+    row0 = uf0 + t.y;
+    nvalid = min(ROWS, T - t.y);
+    ulist = p.uniq + p.uniq_off[t.x];
+    nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
+    out_stride = p.nuniq_pad[t.x];
+    out_base = p.E_off[t.x] + (uint64_t)t.y * out_stride;
+  }
+  const uint32_t nh = nvalid > (uint32_t)BM ? 2u : 1u;   // halves that hold valid frames
+
+  // ---- one-time setup
+  if (warp == 0 && lane == 0) {
+    mbar_init(a_full, 4 * nh);
+    for (uint32_t i = 0; i < nstage; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (uint32_t i = 0; i < kNumAcc; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===== producer: two bulk copies per B tile (hi block, lo block), one ring slot each =====
+    if (lane == 0) {
+      uint32_t ld = 0;
+      for (uint32_t j = 0; j < nu; j++) {
+        const uint32_t s = ulist ? ulist[j] : j;
+        for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++) {
+          for (uint32_t op = 0; op < 2; op++, ld++) {
+            const uint32_t slot = ld % nstage, bytes = p.stage_bytes;
+            mbar_wait(&empty[slot], ((ld / nstage) & 1) ^ 1);
+            mbar_expect_tx(&full[slot], bytes);
+            bulk_load(sB + slot * bytes, p.Bimg + ((size_t)t * 2 + op) * (bytes / 4), bytes, &full[slot]);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: the whole warp walks the loop, one elected lane issues a unit's MMAs =====
+    mbar_wait(a_full, 0);
+    tc_fence_after();
+    uint32_t ld = 0, unit = 0;
+    for (uint32_t j = 0; j < nu; j++) {
+      const uint32_t s = ulist ? ulist[j] : j;
+      for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, ld += 2) {
+        const uint32_t N = p.tile_info[t].y;
+        const uint32_t idesc = make_idesc_tf32(BM, N);
+        const uint32_t slot_hi = ld % nstage, par_hi = (ld / nstage) & 1;
+        const uint32_t slot_lo = (ld + 1) % nstage, par_lo = ((ld + 1) / nstage) & 1;
+        const uint64_t bhi = make_desc_sw32(smem_u32(sB + slot_hi * p.stage_bytes));
+        const uint64_t blo = make_desc_sw32(smem_u32(sB + slot_lo * p.stage_bytes));
+        for (uint32_t h = 0; h < nh; h++, unit++) {
+          const uint32_t buf = unit & 1u, use = unit >> 1;
+          mbar_wait(&tempty[buf], (use & 1) ^ 1);
+          if (h == 0) mbar_wait(&full[slot_hi], par_hi);
+          tc_fence_after();
+          const uint32_t d = tmem_base + buf * 256;
+          const uint64_t ahi = make_desc_sw32(smem_u32(sA + (h * 2 + 0) * a_part));
+          const uint64_t alo = make_desc_sw32(smem_u32(sA + (h * 2 + 1) * a_part));
+          const uint32_t nk = KS > 0 ? (uint32_t)KS : ks;
+          if (tc_elect_one()) {
+#pragma unroll
+            for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, ahi + kk * kstrideA, bhi + kk * kstrideB, idesc, kk);
+#pragma unroll
+            for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, alo + kk * kstrideA, bhi + kk * kstrideB, idesc, 1);
+            if (h + 1 == nh) tc_commit(&empty[slot_hi]);    // the hi block is free once these MMAs are done
+          }
+          __syncwarp();
+          if (h == 0) mbar_wait(&full[slot_lo], par_lo);
+          tc_fence_after();
+          if (tc_elect_one()) {
+#pragma unroll
+            for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, ahi + kk * kstrideA, blo + kk * kstrideB, idesc, 1);
+            if (h + 1 == nh) tc_commit(&empty[slot_lo]);
+            tc_commit(&tfull[buf]);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ===== epilogue warps: (half, lane quarter, column part) =====
+    const uint32_t quarter = warp & 3;
+    const uint32_t group = ((uint32_t)(warp - 2) >> 2) & 1u;      // frame half
+    const uint32_t part = (uint32_t)(warp - 2) >> 3;              // columns [64 * part, 64 * part + 64) of every tile
+    if (group < nh) {
+      const uint32_t lrow = quarter * 32 + lane;
+      const uint32_t row = group * BM + lrow;
+      const uint32_t tlane = tmem_base + ((quarter * 32) << 16);
+      // A rows of this thread's frame: hi -> TMEM, lo -> shared memory (part 0 only)
+      if (part == 0) {
+        const uint64_t fr = prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1);   // rows past the end are never read back
+        const float4* ah = reinterpret_cast<const float4*>(p.Ahi + fr * KP);
+        const float4* al = reinterpret_cast<const float4*>(p.Alo + fr * KP);
+        // [kstep][row][32 B] with byte-address bit 7 (= row bit 2) XORed into bit 4
+        unsigned char* hi_row = sA + (group * 2 + 0) * a_part + lrow * 32;
+        unsigned char* lo_row = sA + (group * 2 + 1) * a_part + lrow * 32;
+        const uint32_t sw = ((lrow >> 2) & 1u) << 4;
+        for (uint32_t kk = 0; kk < ks; kk++) {
+          *reinterpret_cast<float4*>(hi_row + kk * 4096 + (0 ^ sw)) = __ldg(ah + 2 * kk);
+          *reinterpret_cast<float4*>(hi_row + kk * 4096 + (16 ^ sw)) = __ldg(ah + 2 * kk + 1);
+          *reinterpret_cast<float4*>(lo_row + kk * 4096 + (0 ^ sw)) = __ldg(al + 2 * kk);
+          *reinterpret_cast<float4*>(lo_row + kk * 4096 + (16 ^ sw)) = __ldg(al + 2 * kk + 1);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the MMA
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(a_full);
+      }
+      const float2 xn = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
+      const uint64_t my_cell = prow ? prow[row].cell : out_base + (uint64_t)row * out_stride;
+      const uint16_t* my_map = prow ? p.pack_colmap + prow[row].colmap : nullptr;
+      float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
+      uint32_t it = 0;
+      long long e_wait = 0;
+      const long long e_start = p.prof ? clock64() : 0;
+      for (uint32_t j = 0; j < nu; j++) {
+        const uint32_t s = ulist ? ulist[j] : j;
+        const float4 g = __ldg(p.sguard + s);
+        // certified bound on |f32 score - exact score| differences between two candidates (+0.1 %)
+        const float Gs = 2.002f * p.eps * (xn.x * g.x + xn.y * g.y + g.z);
+        float Bbest = INFINITY, Bsecond = INFINITY, Bacc = 0.f, Bidx = 0.f, BG = 0.f;
+        uint32_t n0 = 0;
+        for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, it++) {
+          const uint32_t N = p.tile_info[t].y;
+          const uint32_t unit = it * nh + group, buf = unit & 1u, use = unit >> 1;
+          long long e0 = 0;
+          if (p.prof) e0 = clock64();
+          mbar_wait(&tfull[buf], use & 1);
+          if (p.prof) e_wait += clock64() - e0;
+          tc_fence_after();
+          const uint32_t tcol = tlane + buf * 256;
+          const uint32_t c_lo = part * 128, c_hi = min(N, c_lo + 128);
+          float m = INFINITY, acc = 0.f, idx = 0.f, G = 0.f;
+          if (!(p.debug & 1) && c_lo < c_hi) {
+            uint32_t ra[16], rb[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) rb[e] = 0;
+            // pass 1: minimum of this part's columns (loads run one block ahead; four independent chains)
+            float mm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+            tc_ld16_nowait(tcol + c_lo, ra);
+            tc_ld_wait(ra);
+            for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
+              if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
+#pragma unroll
+              for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(ra[e]));
+              tc_ld_wait(rb);
+              if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
+              if (cc + 16 < c_hi) {
+#pragma unroll
+                for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(rb[e]));
+              }
+              tc_ld_wait(ra);
+            }
+            m = fminf(fminf(mm[0], mm[1]), fminf(mm[2], mm[3]));
+            // pass 2: every column within G of the minimum contributes c in (0, 1]; the minimum itself exactly 1
+            G = Gs + 4e-6f * fabsf(m);
+            const float invg = __fdividef(2.f, G), t0 = (m + G) * invg, ninvg = -invg;
+            tc_ld16_nowait(tcol + c_lo, ra);
+            tc_ld_wait(ra);
+            for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
+              if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
+              {
+                float a4[4] = {0.f, 0.f, 0.f, 0.f}, i4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int e = 0; e < 16; e++) {
+                  const float c = __saturatef(fmaf(__uint_as_float(ra[e]), ninvg, t0));
+                  a4[e & 3] += c;
+                  i4[e & 3] = fmaf(c, (float)e, i4[e & 3]);
+                }
+                const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]), ib = (i4[0] + i4[1]) + (i4[2] + i4[3]);
+                acc += ab;
+                idx += fmaf(ab, (float)cc, ib);
+              }
+              tc_ld_wait(rb);
+              if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
+              if (cc + 16 < c_hi) {
+                float a4[4] = {0.f, 0.f, 0.f, 0.f}, i4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int e = 0; e < 16; e++) {
+                  const float c = __saturatef(fmaf(__uint_as_float(rb[e]), ninvg, t0));
+                  a4[e & 3] += c;
+                  i4[e & 3] = fmaf(c, (float)e, i4[e & 3]);
+                }
+                const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]), ib = (i4[0] + i4[1]) + (i4[2] + i4[3]);
+                acc += ab;
+                idx += fmaf(ab, (float)(cc + 16), ib);
+              }
+              tc_ld_wait(ra);
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[buf]);
+          // merge with the state's earlier tiles
+          if (m < Bbest) { Bsecond = Bbest; Bbest = m; Bacc = acc; Bidx = (float)n0 + idx; BG = G; }
+          else Bsecond = fminf(Bsecond, m);
+          n0 += N;
+        }
+        // the two column parts of a (half, quarter) meet through shared memory once per state
+        float* slot = my_x + (j & 1) * (2 * BM * 5);
+        if (part == 1) { slot[0] = Bbest; slot[1] = Bsecond; slot[2] = Bacc; slot[3] = Bidx; slot[4] = BG; }
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + group * 4 + quarter) : "memory");
+        if (part == 0) {
+          const float ob = slot[0], os = slot[1];
+          if (ob < Bbest) { Bsecond = fminf(Bbest, os); Bbest = ob; Bacc = slot[2]; Bidx = slot[3]; BG = slot[4]; }
+          else Bsecond = fminf(Bsecond, ob);
+          if (row < nvalid) {
+            const bool certain = Bacc == 1.0f && Bsecond > Bbest + BG;
+            const uint32_t col = my_map ? (uint32_t)my_map[j] : j;     // packed: this frame's utterance may not use state j
+            if (col != 0xFFFFu || !my_map) p.cand[my_cell + col] = certain ? (uint32_t)Bidx : kUncertain;
+          }
+        }
+      }
+      if (p.prof && lane == 0 && quarter == 0) {   // one lane per (half, part) warp group
+        atomicAdd(p.prof + 8 + part, (unsigned long long)e_wait);                  // epilogue waiting for the tensor pipe
+        atomicAdd(p.prof + 10 + part, (unsigned long long)(clock64() - e_start));  // epilogue loop lifetime
+        atomicAdd(p.prof + 12, 1ull);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  }
+}
+
+
+
 // ---- refinement: certify the f32 argmin, evaluate the winner in f64, queue near-ties for a full f64 rescan
 struct RefineParams {
   ExactTables m;
@@ -787,6 +1074,9 @@ namespace {
 
 // shared memory: Alo + the B ring (Ahi lives in tensor memory)
 constexpr size_t kSmemLimit = 227 * 1024;
+size_t tc_smem256(uint32_t ks, int nhalf) {   // A (hi, lo) of every half + three half-stage slots + barriers + exchange
+  return 1024 + (size_t)nhalf * 2 * ks * 4096 + 3 * (size_t)ks * 8192 + 256 + 2 * 2 * 128 * 5 * sizeof(float);
+}
 size_t tc_smem(uint32_t stage_bytes, int nhalf, int nstage, int a_smem) {   // A of every half + the B ring + barriers
   return 1024 + (size_t)nhalf * (stage_bytes / 2) * (a_smem == 1 ? 2 : 1) + (size_t)nstage * stage_bytes + 256 +
          2 * 2 * 128 * 5 * sizeof(float);
@@ -799,14 +1089,18 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   using namespace sgmm_tc;
   if (!c->tc_ok) SGMM_FAIL(c, "tensor-core scorer not available for this model shape");
   const uint32_t KP = c->tc_KP, ks = c->tc_ksteps;
+  const bool wide = c->tc_tile_rows == 256;   // N = 256 kernel (B image built for it by sgmm_set_model)
   // two frame halves per CTA when their Ahi operands (KP columns each) fit the 128 TMEM columns set aside
-  const int nhalf = (c->tc_halves == 1 || 2 * KP > 128) ? 1 : 2;
-  const uint32_t stage_bytes = 2 * ks * 128 * 32;
+  // (wide kernel: when both halves' A parts fit shared memory next to the ring)
+  const int nhalf = wide ? ((c->tc_halves == 1 || tc_smem256(ks, 2) > kSmemLimit) ? 1 : 2)
+                         : ((c->tc_halves == 1 || 2 * KP > 128) ? 1 : 2);
+  const uint32_t stage_bytes = wide ? ks * 8192 : 2 * ks * 128 * 32;
   // both A parts in shared memory when that still leaves three B stages (option tc_debug & 64 forces the TMEM form)
   int a_smem = (c->tc_debug >> 6) & 3;   // experiment: tc_debug bits 6-7 select where the A parts live
   if (a_smem == 1 && tc_smem(stage_bytes, nhalf, 2, 1) > kSmemLimit) a_smem = 0;
   int nstage = 1;
   while (nstage < sgmm_tc::kMaxStage && tc_smem(stage_bytes, nhalf, nstage + 1, a_smem) <= kSmemLimit) nstage++;
+  if (wide) nstage = 3;
   const uint32_t rows_per_task = 128u * nhalf;
   // Work is cut into frame ranges.  Normally there is one; while a chunked feature upload is in flight
   // (option "async_upload") there is one per chunk, each launched behind that chunk's copy event, so that the
@@ -852,7 +1146,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.pack_colmap = c->d_pack_colmap.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
-  const size_t smem = tc_smem(stage_bytes, nhalf, nstage, a_smem);
+  const size_t smem = wide ? tc_smem256(ks, nhalf) : tc_smem(stage_bytes, nhalf, nstage, a_smem);
   RefineParams r{};
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
   r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;
@@ -897,7 +1191,13 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     if (g_end > g_prev) {
       const unsigned grid = (unsigned)(g_end - g_prev);
       p.tasks = dense ? nullptr : gemm_tasks + g_prev;
-      if (ks == 5) {          // d = 33 pooled (BASELINE configs 2-4)
+      if (wide && ks == 5) {
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm256<5><<<grid, 576, smem, st>>>(p);
+      } else if (wide) {
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm256<0><<<grid, 576, smem, st>>>(p);
+      } else if (ks == 5) {          // d = 33 pooled (BASELINE configs 2-4)
         SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_tc_gemm<5><<<grid, 576, smem, st>>>(p);
       } else if (ks == 7) {   // d = 48 pooled (config 5), d = 25 unpooled

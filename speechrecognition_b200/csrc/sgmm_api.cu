@@ -253,25 +253,32 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
       // descriptors name (Swizzle<1,4,3>: byte-address bit 7 XORed into bit 4), so a stage is filled by a single
       // bulk copy at full L2 line rate instead of 32-byte tensor-map rows.
       const uint32_t ks = KP / 8;
+      // tile width: 256 densities (N = 256 MMAs run at the full tensor rate, N = 128 ones do not — DESIGN.md §4) when
+      // some state is wider than 128 columns and three half-stage slots + one half's A parts fit shared memory
+      uint32_t widest = 0;
+      for (uint32_t s = 0; s < n_states; s++) widest = std::max(widest, col_off[s + 1] - col_off[s]);
+      const bool fits256 = 1024 + 2 * (size_t)ks * 4096 + 3 * (size_t)ks * 8192 + 256 + 5120 <= 227 * 1024;
+      const uint32_t TR = (c->tc_wide != 0 && fits256 && (widest > 128 || c->tc_wide == 1)) ? 256u : 128u;
+      c->tc_tile_rows = TR;
       std::vector<uint32_t> tile_first(n_states + 1, 0);
       std::vector<uint2> tile_info;           // {offset in 16-byte units, N}
       std::vector<float> img;
       for (uint32_t s = 0; s < n_states; s++) {
         const uint32_t nc = col_off[s + 1] - col_off[s];
-        for (uint32_t n0 = 0; n0 < nc; n0 += 128) {
+        for (uint32_t n0 = 0; n0 < nc; n0 += TR) {
           // every tile occupies a full ring stage: k-step blocks of 128 rows (rows >= N stay zero and are never
           // multiplied: the MMA's N says so), so tile t starts at t * stage bytes and descriptors step by 4 KB
-          const uint32_t N = std::min(128u, nc - n0);
+          const uint32_t N = std::min(TR, nc - n0);
           const size_t off = img.size();
           tile_info.push_back(make_uint2((uint32_t)(off / 4), N));
-          img.resize(off + (size_t)2 * ks * 128 * 8, 0.f);
+          img.resize(off + (size_t)2 * ks * TR * 8, 0.f);
           for (int op = 0; op < 2; op++) {
             const std::vector<float>& B = op ? Blo : Bhi;
-            float* base = img.data() + off + (size_t)op * ks * 128 * 8;
+            float* base = img.data() + off + (size_t)op * ks * TR * 8;
             for (uint32_t kk = 0; kk < ks; kk++)
               for (uint32_t r = 0; r < N; r++)
                 for (uint32_t e = 0; e < 8; e++) {
-                  const uint32_t lin = kk * 128 * 32 + r * 32 + e * 4;
+                  const uint32_t lin = kk * TR * 32 + r * 32 + e * 4;
                   const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
                   base[phys / 4] = B[(size_t)(col_off[s] + n0 + r) * KP + kk * 8 + e];
                 }
@@ -595,6 +602,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "rescore_cache")) { c->use_cache = value != 0; return 0; }
   if (!strcmp(key, "tc_debug")) { c->tc_debug = (int)value; return 0; }
   if (!strcmp(key, "async_upload")) { c->async_upload = value != 0; return 0; }
+  if (!strcmp(key, "tc_wide")) { c->tc_wide = (int)value; return 0; }   // takes effect at the next sgmm_set_model
   if (!strcmp(key, "tc_pack")) { c->tc_pack = value != 0; return 0; }   // takes effect at the next sgmm_set_corpus
   if (!strcmp(key, "upload_chunks")) {
     if (value < 1 || value > sgmm_ctx::kFeatChunks) SGMM_FAIL(c, "set_option: upload_chunks out of range");

@@ -75,6 +75,8 @@ struct sgmm_ctx {
   // tensor-core scorer (k_score_tc.cu): 3xTF32 operands, K-major, KP = padded K
   uint32_t tc_KP = 0, tc_ksteps = 0, tc_Dpad = 0;
   int tc_full = 0;                 // 1: K = x^2 | x | 1;  0: variances pooled per state, K = x | 1
+  uint32_t tc_tile_rows = 128;     // densities per B tile: 256 selects the N = 256 GEMM kernel (k_tc_gemm256)
+  int tc_wide = -1;                // option "tc_wide" (read by sgmm_set_model): -1 auto, 0 never, 1 whenever it fits
   bool tc_ok = false, tc_A_valid = false;
   DevBuf<float> d_Bimg, d_Ahi, d_Alo;
   DevBuf<uint32_t> d_tile_first;    // [n_states + 1] first B tile of every state
