@@ -675,7 +675,12 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
     }
   } else if (warp == 1) {
     // ===== MMA issuer: the whole warp walks the loop, one elected lane issues a unit's MMAs =====
+    const bool prof = p.prof != nullptr;
+    long long w_a = 0, w_full = 0, w_tempty = 0, c0 = 0, c1 = 0;
+    unsigned long long g0 = 0;
+    if (prof) { c0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0)); }
     mbar_wait(a_full, 0);
+    if (prof) w_a = clock64() - c0;
     tc_fence_after();
     uint32_t ld = 0, unit = 0;
     for (uint32_t j = 0; j < nu; j++) {
@@ -689,8 +694,11 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
         const uint64_t blo = make_desc_sw32(smem_u32(sB + slot_lo * p.stage_bytes));
         for (uint32_t h = 0; h < nh; h++, unit++) {
           const uint32_t buf = unit & 1u, use = unit >> 1;
+          if (prof) c1 = clock64();
           mbar_wait(&tempty[buf], (use & 1) ^ 1);
+          if (prof) { const long long c2 = clock64(); w_tempty += c2 - c1; c1 = c2; }
           if (h == 0) mbar_wait(&full[slot_hi], par_hi);
+          if (prof) w_full += clock64() - c1;
           tc_fence_after();
           const uint32_t d = tmem_base + buf * 256;
           const uint64_t ahi = make_desc_sw32(smem_u32(sA + (h * 2 + 0) * a_part));
@@ -704,7 +712,9 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
             if (h + 1 == nh) tc_commit(&empty[slot_hi]);    // the hi block is free once these MMAs are done
           }
           __syncwarp();
+          if (prof) c1 = clock64();
           if (h == 0) mbar_wait(&full[slot_lo], par_lo);
+          if (prof) w_full += clock64() - c1;
           tc_fence_after();
           if (tc_elect_one()) {
 #pragma unroll
@@ -715,6 +725,20 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           __syncwarp();
         }
       }
+    }
+    if (prof && lane == 0 && unit > 0) {
+      const uint32_t last = unit - 1;
+      mbar_wait(&tfull[last & 1u], (last >> 1) & 1);
+      const long long c2 = clock64();
+      unsigned long long g1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
+      atomicAdd(p.prof + 1, (unsigned long long)(c2 - c0));      // issue-warp lifetime, cycles
+      atomicAdd(p.prof + 2, g1 - g0);                            // the same in ns
+      atomicAdd(p.prof + 3, (unsigned long long)w_a);            // waiting for the A rows
+      atomicAdd(p.prof + 4, (unsigned long long)w_full);         // waiting for B slots
+      atomicAdd(p.prof + 5, (unsigned long long)w_tempty);       // waiting for the epilogue to hand an accumulator back
+      atomicAdd(p.prof + 6, (unsigned long long)unit * 3 * ks * 2);   // MMAs issued, in N = 128 equivalents
+      atomicAdd(p.prof + 7, 1ull);                               // CTAs
     }
   } else {
     // ===== epilogue warps: (half, lane quarter, column part) =====

@@ -13,7 +13,7 @@ ctx = capi.Context(0)
 ctx.set_model_tables(33, tables); ctx.set_features(corp["x"])
 ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"]); ctx.set_tdp(3.0, 0.0, 30.0, lex.silence_state)
 ctx.set_option("scorer", 3)
-for dbg in (32, 32 | 64, 32 | 128, 32 | 128 | 1 | 8 | 16, 32 | 1 | 8 | 16):
+for dbg in (32, 32 | 128):
     ctx.set_option("tc_debug", dbg)
     for _ in range(3):
         ctx.align(want_alignment=False, want_costs=False)
