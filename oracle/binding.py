@@ -307,6 +307,16 @@ class Reference:
                                _p(costs, C.c_double))
         return states.astype(np.uint32), costs
 
+    def linear_segmentation(self, x, automaton, approx=True):
+        x = _f32(x).reshape(-1, self.dim)
+        xp = self._pad(x)
+        aut = np.ascontiguousarray(automaton, np.uint16)
+        states = np.zeros(len(x), np.uint16)
+        bounds = np.zeros(2, np.uint64)
+        self.L.ref_linear_segmentation(self.h, int(approx), _p(xp, C.c_float), C.c_uint64(len(x)), _p(aut, C.c_uint16),
+                                       C.c_uint64(len(aut)), _p(states, C.c_uint16), _p(bounds, C.c_uint64))
+        return states.astype(np.uint32), (int(bounds[0]), int(bounds[1]))
+
     def edit_distance(self, ref, hyp):
         r = np.ascontiguousarray(ref, np.uint16)
         h = np.ascontiguousarray(hyp, np.uint16)

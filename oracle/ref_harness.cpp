@@ -31,6 +31,7 @@
 #include "Mixtures.hpp"
 #include "Alignment.hpp"
 #include "TdpModel.hpp"
+#include "Training.hpp"
 #include "Lexicon.hpp"
 #include "Recognizer.hpp"
 #undef private
@@ -252,6 +253,24 @@ void ref_edit_distance(void* h, const uint16_t* ref, uint64_t n_ref, const uint1
   std::vector<WordIdx> r(ref, ref + n_ref), hy(hyp, hyp + n_hyp);
   EDAccumulator e = rec.editDistance(r.begin(), r.end(), hy.begin(), hy.end());
   out[0] = e.total_count; out[1] = e.substitute_count; out[2] = e.insert_count; out[3] = e.delete_count;
+}
+
+// Trainer::linear_segmentation_approximation / linear_segmentation_running_sums (Training.cpp:350-546) on one utterance
+void ref_linear_segmentation(void* h, int approx, const float* x, uint64_t T, const uint16_t* automaton, uint64_t S,
+                             uint16_t* states, uint64_t* bounds) {
+  RefModel* m = static_cast<RefModel*>(h);
+  Lexicon lexicon = build_sietill_lexicon();
+  Trainer trainer(*m->config, lexicon, *m->mixtures, *m->tdp, true);
+  MarkovAutomaton aut;
+  for (uint64_t i = 0; i < S; i++) aut.states.push_back(automaton[i]);
+  std::vector<AlignmentItem> ali(T);
+  size_t d = m->mixtures->dimension;
+  FeatureIter fb(x, d), fe(x + T * d, d);
+  AlignmentIter ab(&ali[0], 1), ae(&ali[0] + T, 1);
+  std::pair<size_t, size_t> b = approx ? trainer.linear_segmentation_approximation(aut, fb, fe, ab, ae)
+                                       : trainer.linear_segmentation_running_sums(aut, fb, fe, ab, ae);
+  for (uint64_t t = 0; t < T; t++) states[t] = ali[t].state;
+  bounds[0] = b.first; bounds[1] = b.second;
 }
 
 }  // extern "C"

@@ -27,6 +27,7 @@ Trainer::Trainer(Configuration const& config, Lexicon const& lexicon, MixtureMod
       mixture_path_(config.get_string("mixture-path", "")), alignment_path_(config.get_string("alignment-path", "")),
       training_stats_path_(config.get_string("training-stats-path", "")), max_approx_(max_approx),
       realign_(config.get_bool("realign", true)), alignment_pruning_(config.get_bool("alignment-pruning", true)),
+      approx_linear_segmentation_(config.get_bool("approx-linear-segmentation", true)),
       lexicon_(lexicon), mixtures_(mixtures), tdp_model_(tdp_model), aligner_(mixtures, tdp_model, num_max_aligns_) {
   if (!max_approx) throw std::runtime_error("Trainer: only max-approx training is on the GPU path");
   if (alignment_pruning_ && !(pruning_threshold_ >= 1e30))
@@ -97,10 +98,12 @@ void Trainer::train(Corpus const& corpus, const Alignment* initial) {
     alignment_ = *initial;
   } else {
     alignment_.assign(total_frames, AlignmentItem());
-    for (SegmentIdx s = 0; s < U; s++) {
-      const size_t f0 = corpus.frame_offsets()[s], T = corpus.frame_offsets()[s + 1] - f0;
-      const size_t S = segment_automata[s].num_states();
-      for (size_t t = 0; t < T; t++) alignment_[f0 + t] = AlignmentItem(1, segment_automata[s][t * S / T], 0.0f);
+    Stopwatch sw(align_seconds);
+    for (SegmentIdx s = 0; s < U; s++) {      // Training.cpp:78-99
+      std::pair<FeatureIter, FeatureIter> f = corpus.get_feature_sequence(s);
+      AlignmentIter ab(alignment_.data() + corpus.frame_offsets()[s], 1), ae(alignment_.data() + corpus.frame_offsets()[s + 1], 1);
+      if (approx_linear_segmentation_) linear_segmentation_approximation(segment_automata[s], f.first, f.second, ab, ae);
+      else linear_segmentation_running_sums(segment_automata[s], f.first, f.second, ab, ae);
     }
   }
 
@@ -160,6 +163,100 @@ void Trainer::train(Corpus const& corpus, const Alignment* initial) {
     std::ostringstream name;
     name << i << ".mix";
     write_mix(name.str());
+  }
+}
+
+// ---- initial segmentation (Training.cpp:350-556) ------------------------------------------------------
+namespace {
+
+// f32 running sums of the first feature component and of its square (Training.cpp:364-381, :438-455)
+void energy_prefix_sums(FeatureIter begin, FeatureIter end, std::vector<float>& sum, std::vector<float>& sq) {
+  const size_t N = (size_t)(end - begin);
+  sum.assign(N, 0.0f); sq.assign(N, 0.0f);
+  size_t n = 0;
+  for (FeatureIter it = begin; it != end; ++it, ++n) {
+    const float c0 = **it;
+    sum[n] = c0; sq[n] = c0 * c0;
+    if (n > 0) { sum[n] += sum[n - 1]; sq[n] += sq[n - 1]; }
+  }
+}
+
+// within-segment scatter of frames [b, e] (Training.cpp:549-557): f32 differences, the rest in f64
+double segment_scatter(std::vector<float> const& sum, std::vector<float> const& sq, size_t b, size_t e) {
+  const double d = sum[e] - sum[b - 1];
+  double score = sq[e] - sq[b - 1];
+  score -= (d * d) / (e - b + 1);
+  return score;
+}
+
+}  // namespace
+
+std::pair<size_t, size_t> Trainer::linear_segmentation_approximation(MarkovAutomaton const& automaton, FeatureIter feature_begin,
+                                                                     FeatureIter feature_end, AlignmentIter align_begin,
+                                                                     AlignmentIter align_end) const {
+  const size_t N = (size_t)(feature_end - feature_begin);
+  std::vector<float> sum, sq;
+  energy_prefix_sums(feature_begin, feature_end, sum, sq);
+  std::pair<size_t, size_t> b(N / 2 - 1, N / 2);                  // :458-459
+  for (int sweep = 0; sweep < 3; sweep++) {                       // three coordinate-descent sweeps (:461)
+    float best = 1e10f;                                           // a float, as in the reference: every stored best is rounded
+    size_t pick = b.first;
+    for (size_t n = 1; n + 1 < b.second; n++) {                   // n = 1 .. second - 2 (:469-471)
+      const double c = segment_scatter(sum, sq, 1, n) + segment_scatter(sum, sq, n + 1, b.second);
+      if (c < best) { pick = n; best = (float)c; }
+    }
+    b.first = pick;
+    best = 1e10f; pick = b.second;
+    for (size_t n = b.first + 1; n + 1 < N; n++) {                // n = first + 1 .. N - 2 (:488-490)
+      const double c = segment_scatter(sum, sq, b.first + 1, n) + segment_scatter(sum, sq, n + 1, N - 1);
+      if (c < best) { pick = n; best = (float)c; }
+    }
+    b.second = pick;
+  }
+  linear_segmentation_alignment_mapping(automaton, b, align_begin, align_end);
+  return b;
+}
+
+std::pair<size_t, size_t> Trainer::linear_segmentation_running_sums(MarkovAutomaton const& automaton, FeatureIter feature_begin,
+                                                                    FeatureIter feature_end, AlignmentIter align_begin,
+                                                                    AlignmentIter align_end) const {
+  const size_t K = 4, N = (size_t)(feature_end - feature_begin);  // three segments: silence, speech, silence
+  std::vector<float> sum, sq;
+  energy_prefix_sums(feature_begin, feature_end, sum, sq);
+  std::vector<std::vector<float>> cost(K, std::vector<float>(N, 1e10f));
+  std::vector<std::vector<size_t>> back(K, std::vector<size_t>(N, 0));
+  cost[0][0] = 0.0f;
+  for (size_t k = 1; k < K; k++)
+    for (size_t n = 0; n < N; n++)
+      for (size_t m = 0; m < n; m++) {                            // boundary m before n; segment m+1 .. n (:399-410)
+        const double d = sum[n] - sum[m];
+        double local = sq[n] - sq[m];
+        local -= (d * d) / (n - m);
+        if (cost[k][n] > cost[k - 1][m] + local) {
+          back[k][n] = m;
+          cost[k][n] = (float)(cost[k - 1][m] + local);
+        }
+      }
+  std::pair<size_t, size_t> b;
+  b.second = back[K - 1][N - 1];
+  b.first = back[K - 2][b.second];
+  linear_segmentation_alignment_mapping(automaton, b, align_begin, align_end);
+  return b;
+}
+
+// Training.cpp:513-546: frames up to the first boundary -> position 0, after the second -> the last position, between
+// them linearly over ALL positions with an f32 slope; only state and count are written (weight keeps its value).
+void Trainer::linear_segmentation_alignment_mapping(MarkovAutomaton const& automaton, std::pair<size_t, size_t> const& boundaries,
+                                                    AlignmentIter const& align_begin, AlignmentIter const& align_end) const {
+  const double per_frame = ((float)automaton.num_states()) / (boundaries.second - boundaries.first);
+  size_t n = 0;
+  for (AlignmentIter it = align_begin; it != align_end; ++it, ++n) {
+    size_t pos;
+    if (n <= boundaries.first) pos = 0;
+    else if (n > boundaries.second) pos = automaton.num_states() - 1;
+    else pos = (size_t)(per_frame * (n - boundaries.first - 1));
+    (*it)->state = automaton[pos];
+    (*it)->count = 1;
   }
 }
 

@@ -286,4 +286,28 @@ int sthost_recognize(void* model, const float* x, uint64_t n_utts, const uint64_
   });
 }
 
+// Trainer::linear_segmentation_approximation (approx != 0) / linear_segmentation_running_sums over one utterance
+// (CPU only: a host-only model stands in for the Trainer's scorer).  states[T] receives the aligned states,
+// bounds[2] the two boundaries.
+int sthost_linear_segmentation(int approx, const float* x, uint64_t T, uint32_t dim, const uint16_t* automaton, uint64_t S,
+                               uint16_t* states, uint64_t* bounds) {
+  return guarded([&] {
+    Lexicon lex = build_sietill_lexicon();
+    Configuration cfg;
+    cfg.set("host-only", true).set("alignment-pruning", false);
+    MixtureModel model(cfg, dim, lex.num_states(), MixtureModel::NO_POOLING, true);
+    TdpModel tdp(cfg, lex.get_silence_automaton()[0]);
+    Trainer trainer(cfg, lex, model, tdp, true);
+    MarkovAutomaton aut;
+    aut.states.assign(automaton, automaton + S);
+    Alignment ali(T, AlignmentItem());
+    FeatureIter fb(x, dim), fe(x + T * dim, dim);
+    AlignmentIter ab(ali.data(), 1), ae(ali.data() + T, 1);
+    std::pair<size_t, size_t> b = approx ? trainer.linear_segmentation_approximation(aut, fb, fe, ab, ae)
+                                         : trainer.linear_segmentation_running_sums(aut, fb, fe, ab, ae);
+    for (uint64_t t = 0; t < T; t++) states[t] = ali[t].state;
+    bounds[0] = b.first; bounds[1] = b.second;
+  });
+}
+
 }  // extern "C"

@@ -362,10 +362,20 @@ class Trainer {
   Trainer(Configuration const& config, Lexicon const& lexicon, MixtureModel& mixtures, TdpModel const& tdp_model,
           bool max_approx);
 
-  // Training.cpp:51-235.  `initial` (optional) replaces the reference's energy-based linear segmentation
-  // (Training.cpp:85-99, outside this path — SURVEY.md §8 f3): all frames, one item each.  Without it an
-  // equal-length segmentation over the automaton positions is used.
+  // Training.cpp:51-235.  Without `initial`, the reference's initial segmentation is run (Training.cpp:78-99: the
+  // coordinate-descent approximation when "approx-linear-segmentation" is true — the default — else the exact
+  // 3-segment dynamic programme); `initial` (all frames, one item each) replaces it.
   void train(Corpus const& corpus, const Alignment* initial = nullptr);
+  // Training.cpp:350-424 / :429-510: speech / silence boundaries on the first feature component, then the linear
+  // mapping of frames to automaton positions (:513-546).  Host code as in the reference.
+  std::pair<size_t, size_t> linear_segmentation_running_sums(MarkovAutomaton const& automaton, FeatureIter feature_begin,
+                                                             FeatureIter feature_end, AlignmentIter align_begin,
+                                                             AlignmentIter align_end) const;
+  std::pair<size_t, size_t> linear_segmentation_approximation(MarkovAutomaton const& automaton, FeatureIter feature_begin,
+                                                              FeatureIter feature_end, AlignmentIter align_begin,
+                                                              AlignmentIter align_end) const;
+  void linear_segmentation_alignment_mapping(MarkovAutomaton const& automaton, std::pair<size_t, size_t> const& boundaries,
+                                             AlignmentIter const& align_begin, AlignmentIter const& align_end) const;
   MarkovAutomaton build_segment_automaton(WordIter segment_begin, WordIter segment_end) const;   // :239-253
   MixtureModel const& get_mixtures() const { return mixtures_; }
 
@@ -380,7 +390,7 @@ class Trainer {
   const unsigned min_obs_, num_splits_, num_aligns_, num_estimates_, num_max_aligns_;
   const double pruning_threshold_;
   const std::string mixture_path_, alignment_path_, training_stats_path_;
-  const bool max_approx_, realign_, alignment_pruning_;
+  const bool max_approx_, realign_, alignment_pruning_, approx_linear_segmentation_;
   Lexicon const& lexicon_;
   MixtureModel& mixtures_;
   TdpModel const& tdp_model_;

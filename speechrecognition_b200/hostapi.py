@@ -217,3 +217,16 @@ def recognize(model, x, frame_off, words, word_off, tdp, word_penalty=10.0, am_t
                               C.c_uint64(len(hyp)), _p(off, C.c_uint64), _p(stats, C.c_double)))
     names = ["wer", "ser", "errors", "substitutions", "insertions", "deletions", "ref_words", "seconds"]
     return [hyp[int(off[u]):int(off[u + 1])].astype(np.uint32) for u in range(U)], dict(zip(names, stats))
+
+
+def linear_segmentation(x, automaton, approx=True):
+    """Trainer::linear_segmentation_approximation / _running_sums on one utterance -> (states[T], (b1, b2))."""
+    L = _lib()
+    x = np.ascontiguousarray(x, np.float32)
+    aut = np.ascontiguousarray(automaton, np.uint16)
+    states = np.zeros(len(x), np.uint16)
+    bounds = np.zeros(2, np.uint64)
+    _ck(L, L.sthost_linear_segmentation(int(approx), _p(x, C.c_float), C.c_uint64(x.shape[0]), C.c_uint32(x.shape[1]),
+                                        _p(aut, C.c_uint16), C.c_uint64(len(aut)), _p(states, C.c_uint16),
+                                        _p(bounds, C.c_uint64)))
+    return states.astype(np.uint32), (int(bounds[0]), int(bounds[1]))

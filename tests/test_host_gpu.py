@@ -19,10 +19,10 @@ def words_of(corp):
     return w, off
 
 
-def oracle_train(O, corp, min_obs, num_splits, num_aligns, num_estimates, pruned=False):
+def oracle_train(O, corp, min_obs, num_splits, num_aligns, num_estimates, pruned=False, initial=None):
     """Trainer::train (Training.cpp:114-226) spelled out with the oracle's primitives."""
     x = corp["x"]
-    ali = synth.linear_alignment(corp["frame_off"], corp["automata"], corp["aut_off"])
+    ali = initial if initial is not None else synth.linear_alignment(corp["frame_off"], corp["automata"], corp["aut_off"])
     stats = []
     O.accumulate(ali, x, first_pass=True); O.finalize()
     stats.append((-1, 0, 0, O.am_score(ali, x)))
@@ -49,20 +49,31 @@ def oracle_train(O, corp, min_obs, num_splits, num_aligns, num_estimates, pruned
     return np.array(stats), ali
 
 
-@pytest.mark.parametrize("pooling,pruned", [("none", False), ("mixture", False), ("global", False), ("none", True)])
-def test_trainer_trajectory_matches_oracle(pooling, pruned, tmp_path):
+@pytest.mark.parametrize("pooling,pruned,segmentation", [("none", False, "given"), ("mixture", False, "given"),
+                                                         ("global", False, "given"), ("none", True, "given"),
+                                                         ("none", False, "reference")])
+def test_trainer_trajectory_matches_oracle(pooling, pruned, segmentation, tmp_path):
     rng = np.random.default_rng(21)
     dim, min_obs = 12, 12
     lex = synth.Lexicon()
     gen = synth.random_model(rng, dim, lex.num_states, 2, "none")
     corp = synth.make_corpus(rng, lex, gen, dim, 40, t_choices=([90, 140, 200], [0.5, 0.3, 0.2]), words_per_utt=(1, 3))
     O = Oracle(dim, lex.num_states, pooling, True, TDP, lex.silence_state)
-    want_stats, want_ali = oracle_train(O, corp, min_obs, 2, 2, 2, pruned)
+    if segmentation == "given":      # an initial alignment handed to Trainer::train
+        init = synth.linear_alignment(corp["frame_off"], corp["automata"], corp["aut_off"])
+    else:                            # the Trainer's own initial segmentation (Training.cpp:78-99, pinned against the
+        parts = []                   # reference in tests/test_oracle_vs_reference.py), energy contour on c0
+        for u in range(len(corp["frame_off"]) - 1):
+            f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
+            aut = corp["automata"][int(corp["aut_off"][u]):int(corp["aut_off"][u + 1])]
+            parts.append(hostapi.linear_segmentation(corp["x"][f0:f1], aut, approx=True)[0])
+        init = np.concatenate(parts)
+    want_stats, want_ali = oracle_train(O, corp, min_obs, 2, 2, 2, pruned, initial=init)
 
     w, wo = words_of(corp)
     stats, ali, model, timers = hostapi.train(dim, pooling, corp["x"], corp["frame_off"], w, wo, TDP, min_obs, 2, 2, 2,
-                                              alignment_pruning=pruned, mixture_path=str(tmp_path) + "/",
-                                              alignment_path=str(tmp_path) + "/")
+                                              alignment_pruning=pruned, initial=init if segmentation == "given" else None,
+                                              mixture_path=str(tmp_path) + "/", alignment_path=str(tmp_path) + "/")
     # same lines in the same order as the reference's training-stats file (Training.cpp:126,158,205)
     assert np.array_equal(stats[:, :3], want_stats[:, :3])
     np.testing.assert_allclose(stats[:, 3], want_stats[:, 3], rtol=1e-10)

@@ -102,3 +102,25 @@ def test_edit_distance_live():
         cases.append((rng.integers(1, 5, nr).tolist(), rng.integers(1, 5, nh).tolist()))
     for ref, hyp in cases:
         assert hostapi.edit_distance(ref, hyp) == R.edit_distance(ref, hyp), (ref, hyp)
+
+
+@pytest.mark.parametrize("approx", [True, False])
+def test_linear_segmentation_live(approx):
+    """The host Trainer's initial segmentation (csrc/host/Training.cpp) against the reference's
+    linear_segmentation_approximation / linear_segmentation_running_sums (Training.cpp:350-546): boundaries and the
+    frame -> state mapping, on utterances whose first component is a noisy silence / speech / silence energy contour."""
+    from speechrecognition_b200 import hostapi
+    R = Reference(9, 106, "none", True, (3.0, 0.0, 30.0), 0)
+    rng = np.random.default_rng(17)
+    lex = synth.Lexicon()
+    for u in range(12):
+        T = int(rng.integers(40, 260))
+        b1, b2 = sorted(rng.integers(5, T - 5, 2))
+        x = rng.normal(0, 1, (T, 9)).astype(np.float32)
+        x[:, 0] = rng.normal(0.2, 0.3, T)
+        x[b1:b2, 0] += rng.uniform(1.0, 4.0)
+        aut = lex.segment_automaton(rng.integers(1, 12, int(rng.integers(1, 4))))
+        got_states, got_b = hostapi.linear_segmentation(x, aut, approx)
+        want_states, want_b = R.linear_segmentation(x, aut, approx)
+        assert got_b == want_b, (u, got_b, want_b)
+        assert np.array_equal(got_states, want_states), u
