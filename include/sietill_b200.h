@@ -68,6 +68,11 @@ int sgmm_set_corpus(sgmm_ctx* ctx, uint32_t n_utts, const uint64_t* frame_off,
 /* TdpModel (TdpModel.cpp:19-29): silence_state always pays `forward`. */
 int sgmm_set_tdp(sgmm_ctx* ctx, double loop, double forward, double skip, uint32_t silence_state);
 
+/* Beam of Aligner::align_sequence_pruned (Alignment.cpp:227-239, "pruning-threshold"): after every frame t >= 1 the
+ * positions whose cost exceeds (best cost of the frame + pruning_threshold) die.  Applies to sgmm_align with
+ * SGMM_TDP_DESTINATION only (the reference's full aligner has no beam); +inf (the default) = exact search. */
+int sgmm_set_beam(sgmm_ctx* ctx, double pruning_threshold);
+
 /* ---- scoring (K1) --------------------------------------------------------------------------- */
 /* MixtureModel::min_score (Mixtures.cpp:696-713) for every frame in [f0, f1) and every state:
  * scores[(f-f0)*n_states + s] (f64, bit-identical to the reference), argmin likewise = position k
@@ -132,6 +137,8 @@ int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
  *   the host buffer must stay untouched until the next compute call returns (use sgmm_host_alloc memory).
  * "tc_halves" (0 auto, 1, 2): 128-frame halves per tensor-core CTA.  "tc_pack" (default 1; read by sgmm_set_corpus):
  *   pack short utterance tails into shared 128-row halves.
+ * "tc_wide" (-1 auto, 0, 1; read by sgmm_set_model): 256-density GEMM tiles (the N = 256 kernel) instead of 128;
+ *   auto picks them when some state has more than 128 densities and the tile ring fits shared memory.
  * "tc_debug": timing experiments for the tensor-core kernel — any bit other than 32 (cycle profile, read with the
  *   "tc_prof1".."tc_prof12" counters) makes results INVALID; never set in production. */
 int sgmm_set_option(sgmm_ctx* ctx, const char* key, int64_t value);

@@ -19,7 +19,7 @@ ALI_DTYPE = np.dtype([("count", np.uint16), ("state", np.uint16), ("weight", np.
 # every symbol include/sietill_b200.h declares (checked by tests/test_capi_symbols.py)
 SYMBOLS = [
     "sgmm_create", "sgmm_destroy", "sgmm_last_error", "sgmm_version", "sgmm_set_model", "sgmm_set_features",
-    "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_set_lexicon", "sgmm_recognize", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
+    "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_set_beam", "sgmm_set_lexicon", "sgmm_recognize", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
     "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
     "sgmm_launch_count", "sgmm_timer_start", "sgmm_timer_stop", "sgmm_host_alloc", "sgmm_host_free",
     "sgmm_set_option", "sgmm_get_counter",
@@ -119,6 +119,9 @@ class Context:
     def set_tdp(self, loop, forward, skip, silence_state=0):
         self._ck(self.L.sgmm_set_tdp(self.h, C.c_double(loop), C.c_double(forward), C.c_double(skip),
                                      C.c_uint32(silence_state)))
+
+    def set_beam(self, pruning_threshold=float("inf")):
+        self._ck(self.L.sgmm_set_beam(self.h, C.c_double(pruning_threshold)))
 
     # ---- compute
     def score_all(self, f0=0, f1=None, want_argmin=True):

@@ -1,6 +1,7 @@
 // Aligner: the reference's per-utterance signatures (src/sietill/Alignment.hpp:46-55) plus the batched
 // entry the training driver uses; both run K1 (gathered scoring) + K2 (Viterbi + backtrace) on the GPU.
 #include <istream>
+#include <limits>
 #include <ostream>
 
 #include "sietill_host.hpp"
@@ -27,7 +28,7 @@ void upload_corpus(Device& dev, std::vector<size_t> const& frame_off, std::vecto
 }  // namespace
 
 double Aligner::align_one(FeatureIter fb, FeatureIter fe, MarkovAutomaton const& ref, AlignmentIter ab, AlignmentIter ae,
-                          int convention) {
+                          int convention, double beam) {
   const size_t T = (size_t)(fe - fb);
   if (ab.size != 1 || (size_t)(ae - ab) != T) throw std::runtime_error("Aligner: alignment range does not match the features");
   if (fb.size != mixtures_.dimension) throw std::runtime_error("Aligner: feature dimension differs from the model's");
@@ -37,6 +38,7 @@ double Aligner::align_one(FeatureIter fb, FeatureIter fe, MarkovAutomaton const&
   upload_corpus(dev, {0, T}, {&ref});
   dev.check(sgmm_set_tdp(dev.ctx(), tdp_model_.loop(), tdp_model_.forward(), tdp_model_.skip(), tdp_model_.silence_state),
             "sgmm_set_tdp");
+  dev.check(sgmm_set_beam(dev.ctx(), beam), "sgmm_set_beam");
   double cost = 0.0;
   dev.check(sgmm_align(dev.ctx(), convention, reinterpret_cast<sgmm_alignment_item*>(*ab), &cost), "sgmm_align");
   if (*ab == mixtures_.resident_ali_) mixtures_.resident_ali_ = nullptr;   // host copy changed under the token
@@ -45,19 +47,17 @@ double Aligner::align_one(FeatureIter fb, FeatureIter fe, MarkovAutomaton const&
 
 double Aligner::align_sequence_full(FeatureIter feature_begin, FeatureIter feature_end, MarkovAutomaton const& reference,
                                     AlignmentIter align_begin, AlignmentIter align_end) {
-  return align_one(feature_begin, feature_end, reference, align_begin, align_end, SGMM_TDP_SOURCE);
+  return align_one(feature_begin, feature_end, reference, align_begin, align_end, SGMM_TDP_SOURCE,
+                   std::numeric_limits<double>::infinity());
 }
 
 double Aligner::align_sequence_pruned(FeatureIter feature_begin, FeatureIter feature_end, MarkovAutomaton const& reference,
                                       AlignmentIter align_begin, AlignmentIter align_end, double pruning_threshold) {
-  if (!(pruning_threshold >= 1e30))
-    throw std::runtime_error("Aligner: beam pruning is not on the GPU path; pass pruning_threshold >= 1e30 for the "
-                             "exact search with align_sequence_pruned's conventions");
-  return align_one(feature_begin, feature_end, reference, align_begin, align_end, SGMM_TDP_DESTINATION);
+  return align_one(feature_begin, feature_end, reference, align_begin, align_end, SGMM_TDP_DESTINATION, pruning_threshold);
 }
 
 void Aligner::align_corpus(Corpus const& corpus, std::vector<MarkovAutomaton> const& automata, Alignment& alignment,
-                           bool destination_tdp, std::vector<double>* costs) {
+                           bool destination_tdp, std::vector<double>* costs, double pruning_threshold) {
   const size_t U = corpus.get_corpus_size();
   if (automata.size() != U) throw std::runtime_error("Aligner: one automaton per segment expected");
   mixtures_.sync_device();
@@ -72,6 +72,8 @@ void Aligner::align_corpus(Corpus const& corpus, std::vector<MarkovAutomaton> co
   }
   dev.check(sgmm_set_tdp(dev.ctx(), tdp_model_.loop(), tdp_model_.forward(), tdp_model_.skip(), tdp_model_.silence_state),
             "sgmm_set_tdp");
+  dev.check(sgmm_set_beam(dev.ctx(), destination_tdp ? pruning_threshold : std::numeric_limits<double>::infinity()),
+            "sgmm_set_beam");
   alignment.resize(corpus.get_total_frame_count());
   if (costs) costs->resize(U);
   dev.check(sgmm_align(dev.ctx(), destination_tdp ? SGMM_TDP_DESTINATION : SGMM_TDP_SOURCE,

@@ -30,9 +30,6 @@ Trainer::Trainer(Configuration const& config, Lexicon const& lexicon, MixtureMod
       approx_linear_segmentation_(config.get_bool("approx-linear-segmentation", true)),
       lexicon_(lexicon), mixtures_(mixtures), tdp_model_(tdp_model), aligner_(mixtures, tdp_model, num_max_aligns_) {
   if (!max_approx) throw std::runtime_error("Trainer: only max-approx training is on the GPU path");
-  if (alignment_pruning_ && !(pruning_threshold_ >= 1e30))
-    throw std::runtime_error("Trainer: the GPU aligner is the exact search; set alignment-pruning false (or "
-                             "pruning-threshold >= 1e30 for the pruned aligner's conventions without a beam)");
 }
 
 // Training.cpp:239-253: sil w1 sil w2 ... sil
@@ -137,7 +134,7 @@ void Trainer::train(Corpus const& corpus, const Alignment* initial) {
       if (realign_) {
         {
           Stopwatch sw(align_seconds);
-          aligner_.align_corpus(corpus, segment_automata, alignment_, alignment_pruning_);
+          aligner_.align_corpus(corpus, segment_automata, alignment_, alignment_pruning_, nullptr, pruning_threshold_);
           ali_begin = ConstAlignmentIter(alignment_.data(), 1);
           ali_end = ConstAlignmentIter(alignment_.data() + alignment_.size(), 1);
         }

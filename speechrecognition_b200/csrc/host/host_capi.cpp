@@ -176,7 +176,7 @@ double sthost_tdp_score(double loop, double forward, double skip, uint32_t silen
 int sthost_train(uint32_t dim, int pooling, int device, const float* x, uint64_t n_utts, const uint64_t* frame_off,
                  const uint64_t* words, const uint64_t* word_off, double loop, double forward, double skip,
                  uint32_t min_obs, uint32_t num_splits, uint32_t num_aligns, uint32_t num_estimates, int alignment_pruning,
-                 const sgmm_alignment_item* initial, const char* mixture_path, const char* alignment_path,
+                 double pruning_threshold, const sgmm_alignment_item* initial, const char* mixture_path, const char* alignment_path,
                  double* stats, uint64_t stats_cap, uint64_t* n_stats, sgmm_alignment_item* final_alignment,
                  double* timers /* [4]: align, estimate, score, io seconds */, void** model_out) {
   HostModel* h = new HostModel();
@@ -188,7 +188,7 @@ int sthost_train(uint32_t dim, int pooling, int device, const float* x, uint64_t
     Configuration& cfg = h->config;
     cfg.set("device", (unsigned)device).set("tdp-loop", loop).set("tdp-forward", forward).set("tdp-skip", skip);
     cfg.set("min-obs", min_obs).set("num-splits", num_splits).set("num-aligns", num_aligns).set("num-estimates", num_estimates);
-    cfg.set("alignment-pruning", alignment_pruning != 0).set("pruning-threshold", 1e300);
+    cfg.set("alignment-pruning", alignment_pruning != 0).set("pruning-threshold", pruning_threshold);
     if (mixture_path && *mixture_path) cfg.set("mixture-path", std::string(mixture_path));
     if (alignment_path && *alignment_path) cfg.set("alignment-path", std::string(alignment_path));
     TdpModel tdp(cfg, lex.get_silence_automaton()[0]);

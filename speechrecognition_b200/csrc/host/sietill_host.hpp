@@ -18,6 +18,7 @@
 
 #include <iosfwd>
 #include <iterator>
+#include <limits>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -296,20 +297,20 @@ class Aligner {
   // Alignment.cpp:50-144; runs as a one-utterance batch on the GPU (K1 gathered + K2).
   double align_sequence_full(FeatureIter feature_begin, FeatureIter feature_end, MarkovAutomaton const& reference,
                              AlignmentIter align_begin, AlignmentIter align_end);
-  // Alignment.cpp:149-288.  The GPU path is the exact DP, so only an infinite beam is supported:
-  // pruning_threshold must be >= 1e30 (destination-state TDP convention, "highest state reached" end);
-  // anything smaller throws.
+  // Alignment.cpp:149-288: destination-state TDP convention, beam of pruning_threshold after every frame
+  // (:227-239), backtrace from the highest position alive in the last frame.  +inf = exact search.
   double align_sequence_pruned(FeatureIter feature_begin, FeatureIter feature_end, MarkovAutomaton const& reference,
                                AlignmentIter align_begin, AlignmentIter align_end, double pruning_threshold);
 
   // Batched: every utterance of the corpus in one call (the loop of Training.cpp:168-183).  `alignment`
   // covers all frames (num_max_aligns == 1); costs (optional) receives the per-utterance path costs.
   void align_corpus(Corpus const& corpus, std::vector<MarkovAutomaton> const& automata, Alignment& alignment,
-                    bool destination_tdp = false, std::vector<double>* costs = nullptr);
+                    bool destination_tdp = false, std::vector<double>* costs = nullptr,
+                    double pruning_threshold = std::numeric_limits<double>::infinity());
 
  private:
   double align_one(FeatureIter fb, FeatureIter fe, MarkovAutomaton const& ref, AlignmentIter ab, AlignmentIter ae,
-                   int convention);
+                   int convention, double beam);
   MixtureModel const& mixtures_;
   TdpModel const& tdp_model_;
   size_t max_aligns_;

@@ -56,6 +56,7 @@ struct VitParams {
   const double* E;
   double tdp_loop, tdp_forward, tdp_skip;
   uint32_t silence_state;
+  double beam;                 // DEST only: positions costlier than (frame best + beam) die; +inf = no pruning
   sgmm_alignment_item* ali;
   uint16_t* fcol;              // per frame: emission column of the aligned position
   double* costs;
@@ -70,8 +71,10 @@ __device__ __forceinline__ double pick(const double (&v)[C], int c) {
 }
 
 // DEST = false: align_sequence_full semantics (source-state TDP, tie order loop > forward > skip, end at S-1).
-// DEST = true : align_sequence_pruned with an infinite threshold (destination-state TDP, Alignment.cpp:191;
-//               candidates arrive skip, forward, loop and replace on strictly smaller cost, :199-204; the
+// DEST = true : align_sequence_pruned (destination-state TDP, Alignment.cpp:191; candidates arrive skip,
+//               forward, loop and replace on strictly smaller cost, :199-204; after every frame t >= 1 the
+//               positions with cost > best + threshold die, :227-239 — a dead position is +inf here, which
+//               never wins a strict comparison, exactly like a predecessor the reference skips; the
 //               backtrace starts from the highest position alive in the last frame, :245-256).
 template <int C, bool DEST>
 __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
@@ -135,6 +138,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     }
   }
   const double pf = p.tdp_forward;
+  const bool prune = DEST && p.beam < INF;
 
   for (uint32_t ti = 0; ti < n_tiles; ti++) {
     const uint32_t slot = ti % SGMM_STAGES;
@@ -191,6 +195,18 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
           j = f2 ? 0u : (f1 ? 1u : 2u);
         }
         w[c] |= j << sh;
+      }
+      if (prune) {
+        // best over the automaton's own positions only (lanes past S hold junk from column 0)
+        double best = INFd;
+#pragma unroll
+        for (int c = 0; c < C; c++)
+          if ((validmask >> c) & 1) best = fmin(best, nq[c]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
+        const double upper = __dadd_rn(best, p.beam);
+#pragma unroll
+        for (int c = 0; c < C; c++) nq[c] = nq[c] > upper ? INFd : nq[c];
       }
 #pragma unroll
       for (int c = 0; c < C; c++) q[c] = nq[c];
@@ -273,6 +289,7 @@ int sgmm_launch_viterbi(sgmm_ctx* c, int conv) {
     p.pos2uniq = c->d_pos2uniq.p; p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p;
     p.tdp_loop = c->tdp_loop; p.tdp_forward = c->tdp_forward; p.tdp_skip = c->tdp_skip;
     p.silence_state = c->silence_state;
+    p.beam = c->beam;
     p.ali = c->d_ali.p; p.fcol = c->d_fcol.p; p.costs = c->d_costs.p;
     int rc = 1;
     switch (vc.C) {

@@ -355,6 +355,13 @@ int sgmm_set_tdp(sgmm_ctx* c, double loop, double forward, double skip, uint32_t
   return 0;
 }
 
+int sgmm_set_beam(sgmm_ctx* c, double pruning_threshold) {
+  if (!c) return 1;
+  if (!(pruning_threshold >= 0.0)) SGMM_FAIL(c, "sgmm_set_beam: the threshold must be >= 0 (+inf disables pruning)");
+  c->beam = pruning_threshold;
+  return 0;
+}
+
 int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const uint32_t* automata,
                     const uint32_t* aut_off) {
   if (!c) return 1;

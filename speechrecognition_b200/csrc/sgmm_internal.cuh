@@ -133,6 +133,7 @@ struct sgmm_ctx {
 
   // ---- tdp
   double tdp_loop = 0, tdp_forward = 0, tdp_skip = 0;
+  double beam = __builtin_huge_val();   // sgmm_set_beam: pruning threshold of the destination-convention aligner
   uint32_t silence_state = 0;
 
   // ---- alignment + per-frame E-step results

@@ -73,6 +73,73 @@ def test_align_destination_convention(small25):
     ctx.align()  # leave the source-convention alignment resident for the following tests
 
 
+@pytest.mark.parametrize("threshold", [0.0, 5.0, 20.0, 40.0, 150.0])
+@pytest.mark.parametrize("fx", ["small25", "small33"])
+def test_align_pruned_beam(fx, threshold, request):
+    """Aligner::align_sequence_pruned with a finite beam (Alignment.cpp:227-239): paths, costs and — when the beam
+    kills the path to the last position — the "highest position alive" end, all as the reference has them."""
+    O, corp, ali, ctx = request.getfixturevalue(fx)
+    from speechrecognition_b200 import capi
+    ctx.set_beam(threshold)
+    got, costs = ctx.align(capi.TDP_DESTINATION)
+    ctx.set_beam()
+    short = 0
+    for u in range(len(corp["frame_off"]) - 1):
+        f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
+        aut = corp["automata"][corp["aut_off"][u]:corp["aut_off"][u + 1]]
+        c, st, pos = O.align_pruned(corp["x"][f0:f1], aut, threshold)
+        assert c == costs[u], u
+        assert np.array_equal(got["state"][f0:f1].astype(np.uint32), st), u
+        short += int(pos[-1] != len(aut) - 1)
+    if threshold <= 5.0:
+        assert short > 0                   # the tight beams did strand some paths before the last position
+    # the beam is a property of the destination convention only: the full aligner ignores it
+    ctx.set_beam(threshold)
+    again, costs2 = ctx.align()
+    ctx.set_beam()
+    ref, costs_ref = ctx.align()
+    assert np.array_equal(again, ref) and np.array_equal(costs2, costs_ref)
+
+
+def test_alignment_golden():
+    """Committed outputs of the unmodified reference (tests/golden/trajectory_none.npz, tools/make_golden.py): scores,
+    full and pruned alignments with their costs, and the accumulators of the following E-step."""
+    import os
+    from oracle.binding import TABLES
+    from speechrecognition_b200 import capi, synth
+    G = os.path.join(os.path.dirname(__file__), "golden")
+    c = np.load(os.path.join(G, "corpus.npz"))
+    rec = np.load(os.path.join(G, "trajectory_none.npz"))
+    dim = int(c["dim"])
+    lex = synth.Lexicon()
+    t1 = {k: rec["t1_" + k] for k in TABLES}
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, t1)
+    ctx.set_features(c["x"])
+    ctx.set_corpus(c["frame_off"], c["automata"], c["aut_off"])
+    ctx.set_tdp(*[float(v) for v in c["tdp"]], lex.silence_state)
+    sc, am = ctx.score_all(0, 64)
+    assert np.array_equal(sc, rec["scores64"]) and np.array_equal(am, rec["argmin64"])
+    f0, f1 = int(c["frame_off"][2]), int(c["frame_off"][3])
+    for thr, tag in ((40.0, "p40"), (1e300, "pinf")):
+        ctx.set_beam(thr)
+        got, costs = ctx.align(capi.TDP_DESTINATION)
+        assert costs[2] == float(rec["cost_" + tag])
+        assert np.array_equal(got["state"][f0:f1].astype(np.uint32), rec["ali_" + tag])
+    ctx.set_beam()
+    got, costs = ctx.align()
+    assert np.array_equal(got["state"].astype(np.uint32), rec["ali_full"])
+    assert np.array_equal(costs, rec["costs_full"])
+    cnt, sx, sxx, _ = ctx.accumulate(first_pass=False)
+    t2 = {k: rec["t2_" + k] for k in TABLES}
+    want_cnt, want_sx = helpers.packed_stats(t2, dim)
+    assert np.array_equal(cnt, want_cnt)
+    np.testing.assert_allclose(sx, want_sx, rtol=STAT_RTOL, atol=1e-9)
+    want_sxx = t2["var_acc"].reshape(-1, dim)[t2["var_idx"].astype(np.int64)] - 1e-4
+    np.testing.assert_allclose(sxx, want_sxx, rtol=1e-9, atol=1e-7)
+    ctx.close()
+
+
 @pytest.mark.parametrize("fx", ["small25", "small33"])
 def test_accumulate_matches_oracle(fx, request):
     O, corp, ali, ctx = request.getfixturevalue(fx)

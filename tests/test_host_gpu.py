@@ -39,7 +39,7 @@ def oracle_train(O, corp, min_obs, num_splits, num_aligns, num_estimates, pruned
                 for u in range(len(corp["frame_off"]) - 1):
                     f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
                     aut = corp["automata"][int(corp["aut_off"][u]):int(corp["aut_off"][u + 1])]
-                    parts.append(O.align_pruned(x[f0:f1], aut, 1e300)[1])
+                    parts.append(O.align_pruned(x[f0:f1], aut, 1e300 if pruned is True else float(pruned))[1])
                 ali = np.concatenate(parts)
             else:
                 ali, _ = O.align_batch(x, corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
@@ -51,6 +51,7 @@ def oracle_train(O, corp, min_obs, num_splits, num_aligns, num_estimates, pruned
 
 @pytest.mark.parametrize("pooling,pruned,segmentation", [("none", False, "given"), ("mixture", False, "given"),
                                                          ("global", False, "given"), ("none", True, "given"),
+                                                         ("none", 50.0, "given"), ("none", 12.0, "given"),
                                                          ("none", False, "reference")])
 def test_trainer_trajectory_matches_oracle(pooling, pruned, segmentation, tmp_path):
     rng = np.random.default_rng(21)
@@ -72,7 +73,8 @@ def test_trainer_trajectory_matches_oracle(pooling, pruned, segmentation, tmp_pa
 
     w, wo = words_of(corp)
     stats, ali, model, timers = hostapi.train(dim, pooling, corp["x"], corp["frame_off"], w, wo, TDP, min_obs, 2, 2, 2,
-                                              alignment_pruning=pruned, initial=init if segmentation == "given" else None,
+                                              alignment_pruning=bool(pruned), initial=init if segmentation == "given" else None,
+                                              pruning_threshold=float("inf") if isinstance(pruned, bool) else pruned,
                                               mixture_path=str(tmp_path) + "/", alignment_path=str(tmp_path) + "/")
     # same lines in the same order as the reference's training-stats file (Training.cpp:126,158,205)
     assert np.array_equal(stats[:, :3], want_stats[:, :3])
@@ -127,8 +129,10 @@ def test_per_utterance_aligner_signatures(trained):
         want_cost, want_states, _ = O.align_pruned(corp["x"][f0:f1], aut, 1e300)
         cost, got = H.align_sequence(TDP, O.silence, corp["x"][f0:f1], aut, pruned=True, threshold=1e300)
         assert cost == want_cost and np.array_equal(got["state"].astype(np.uint32), want_states)
-    with pytest.raises(hostapi.HostError, match="beam pruning is not on the GPU path"):
-        H.align_sequence(TDP, O.silence, corp["x"][:50], corp["automata"][:10], pruned=True, threshold=100.0)
+        for thr in (4.0, 35.0):
+            want_cost, want_states, _ = O.align_pruned(corp["x"][f0:f1], aut, thr)
+            cost, got = H.align_sequence(TDP, O.silence, corp["x"][f0:f1], aut, pruned=True, threshold=thr)
+            assert cost == want_cost and np.array_equal(got["state"].astype(np.uint32), want_states)
 
 
 def test_model_accumulate_and_edit_detection(trained):
