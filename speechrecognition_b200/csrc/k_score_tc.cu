@@ -916,6 +916,12 @@ struct RefineParams {
   unsigned long long* rescan;  // [0] count, [1..cap] cell ids
   unsigned long long cap;
   unsigned long long* fallback_count;
+  // state-major kernel
+  const uint4* sm_items;
+  const uint4* sm_ent_a;
+  const uint2* sm_ent_b;
+  uint32_t sm_rw;              // doubles per table row: mean row, norm, padding (2 * odd: bank spread for LDS.128)
+  uint32_t sm_maxnd;           // most densities in one state
 };
 
 // cell -> (frame, state); returns false for the padding column of a gathered row
@@ -1056,6 +1062,186 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
   }
 }
 
+// exact score of one density from a shared-memory table row {mean[dim], norm}: exact_score_unrolled's operation
+// order (two running sums over even / odd dimensions, then the odd tail), hence the same bits
+template <uint32_t DIM>
+__device__ __forceinline__ double sm_exact(const double* row, double logw, const float* xr, const double* iv) {
+  constexpr int NP = DIM / 2;
+  static_assert(NP % 4 == 0, "dimension pairs are walked in blocks of four");
+  double l0 = 0.0, l1 = 0.0;
+#pragma unroll
+  for (int g = 0; g < NP; g += 4) {          // four 16-byte units in flight: keeps the kernel inside 64 registers
+    double2 mu[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) mu[j] = *reinterpret_cast<const double2*>(row + 2 * (g + j));
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int ip = g + j;
+      const double2 v = *reinterpret_cast<const double2*>(iv + 2 * ip);
+      double a = __dsub_rn((double)xr[2 * ip], mu[j].x);
+      double b = __dsub_rn((double)xr[2 * ip + 1], mu[j].y);
+      a = __dmul_rn(a, a); b = __dmul_rn(b, b);
+      a = __dmul_rn(a, v.x); b = __dmul_rn(b, v.y);
+      l0 = __dadd_rn(l0, a); l1 = __dadd_rn(l1, b);
+    }
+  }
+  double dist = __dadd_rn(l0, l1);
+  if (DIM & 1) {
+    const double c = __dsub_rn((double)xr[DIM - 1], row[DIM - 1]);
+    dist = __dadd_rn(dist, __dmul_rn(__dmul_rn(c, c), iv[DIM - 1]));
+  }
+  return __dsub_rn(__dadd_rn(row[DIM], __dmul_rn(dist, 0.5)), logw);
+}
+
+// whole-state rescan of one cell, densities first, first + step, ... (out of line: only taken when the rescan list is full)
+template <uint32_t DIM>
+__device__ __noinline__ void sm_rescan(const double* tbl, const double* lw, const float* xb, const double* iv, uint32_t nd,
+                                       uint32_t RW, uint32_t first, uint32_t step, double& rb_out, uint32_t& rk_out) {
+  double rb = 1e10;
+  uint32_t rk = 0xffffffffu;
+  for (uint32_t k = first; k < nd; k += step) {
+    const double sc = sm_exact<DIM>(tbl + (size_t)k * RW, lw[k], xb, iv);
+    if (sc < rb) { rb = sc; rk = k; }
+  }
+  rb_out = rb; rk_out = rk;
+}
+
+// State-major refinement (gathered, pooled models).  One CTA per item = (block of utterances, state): the state's
+// f64 mean rows + norms (nd x RW doubles, 72 KB at 256 densities, d = 33), its log weights and its inverse-variance
+// row are loaded into shared memory ONCE and serve every frame of the block's utterances that visit the state,
+// so the per-cell gather of the winner's mean row (272 B) is a shared-memory read instead of an L2 -> SM gather;
+// what streams from L2 is the feature rows (132 B per cell, contiguous).  A warp owns 32 consecutive cells of the
+// item (consecutive frames of an utterance, except across utterance boundaries): it stages their feature rows into its
+// own tile with coalesced loads, then thread = cell evaluates the certified winner with exact_score_unrolled's
+// operation order (same bits).  Near-tie cells are queued for k_tc_rescan as in the frame-major kernel.
+template <uint32_t DIM>
+__global__ void __launch_bounds__(1024, 1) k_tc_refine_sm(RefineParams p) {
+  extern __shared__ __align__(16) unsigned char sm_raw[];
+  constexpr uint32_t kMaxEnt = 128, kMaxChunks = 2048;
+  constexpr uint32_t dim = DIM, kRowB = DIM * 4;
+  // Odd dimensions: the tile's rows are the frames' rows as they lie in global memory (stride = dim floats, odd, so
+  // thread = row reads are conflict-free) and arrive by 1-D bulk copies.  Even dimensions need a padded stride and
+  // take the element-wise cp.async path.
+  constexpr bool kBulk = (DIM & 1u) != 0;
+  constexpr uint32_t XS = dim | 1u;
+  constexpr uint32_t kTileB = 32 * XS * 4 + 64;              // + alignment slack of two bulk segments
+  const uint4 item = p.sm_items[blockIdx.x];
+  const uint32_t s = item.x, n_ent = item.z, n_cells = item.w;
+  const uint32_t k0 = p.state_off[s], nd = p.state_off[s + 1] - k0;
+  const uint32_t RW = p.sm_rw, dimP = p.m.dimP;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nthr = blockDim.x;
+  double* tbl = reinterpret_cast<double*>(sm_raw);           // [nd][RW]
+  double* lw = tbl + (size_t)p.sm_maxnd * RW;                // [nd]
+  double* iv = lw + ((p.sm_maxnd + 1u) & ~1u);               // [dimP], 16-byte aligned
+  uint4* ent_a = reinterpret_cast<uint4*>(iv + dimP);        // [kMaxEnt]
+  uint2* ent_b = reinterpret_cast<uint2*>(ent_a + kMaxEnt);  // [kMaxEnt]
+  uint16_t* chunk_ent = reinterpret_cast<uint16_t*>(ent_b + kMaxEnt);   // [kMaxChunks] entry of a chunk's first cell
+  uint64_t* bar = reinterpret_cast<uint64_t*>(chunk_ent + kMaxChunks) + warp;   // [32] one mbarrier per warp
+  unsigned char* tile = reinterpret_cast<unsigned char*>(chunk_ent + kMaxChunks) + 256 + warp * kTileB;
+  uint32_t n_rescans = 0;
+
+  if (lane == 0) mbar_init(bar, 1);
+  for (uint32_t i = threadIdx.x; i < nd * dimP; i += nthr) {
+    const uint32_t k = i / dimP, q = i - k * dimP;
+    if (q < dim) tbl[(size_t)k * RW + q] = __ldg(p.m.meanR + (size_t)(k0 + k) * dimP + q);
+  }
+  for (uint32_t k = threadIdx.x; k < nd; k += nthr) {
+    tbl[(size_t)k * RW + dim] = __ldg(p.m.norm + k0 + k);
+    lw[k] = __ldg(p.m.logw + k0 + k);
+  }
+  if (nd > 0)
+    for (uint32_t q = threadIdx.x; q < dimP; q += nthr) iv[q] = __ldg(p.m.invU + (size_t)__ldg(p.m.var_of + k0) * dimP + q);
+  for (uint32_t i = threadIdx.x; i < n_ent; i += nthr) {
+    ent_a[i] = p.sm_ent_a[item.y + i];
+    ent_b[i] = p.sm_ent_b[item.y + i];
+  }
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j * 32 < n_cells; j += nthr) {
+    uint32_t lo = 0, hi = n_ent;                             // largest entry with cells-before <= 32 j
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (ent_a[mid].w <= j * 32) lo = mid; else hi = mid;
+    }
+    chunk_ent[j] = (uint16_t)lo;
+  }
+  __syncthreads();
+
+  const unsigned char* xbytes = reinterpret_cast<const unsigned char*>(p.x);
+  uint32_t phase = 0;
+  for (uint32_t c0 = warp * 32; c0 < n_cells; c0 += nthr) {
+    const uint32_t nvalid = min(32u, n_cells - c0);
+    const uint32_t i = min(c0 + lane, n_cells - 1);          // lanes past the end repeat the last cell, write nothing
+    uint32_t e = chunk_ent[c0 >> 5];
+    while (e + 1 < n_ent && ent_a[e + 1].w <= i) e++;
+    const uint4 ea = ent_a[e];
+    const uint32_t t = i - ea.w;
+    const uint64_t cell = (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)t * ea.z;
+    const uint32_t frame = ent_b[e].x + t;                    // (the launcher takes this kernel below 2^32 frames only)
+    const uint32_t i1 = nd ? __ldg(p.cand + cell) : 0u;
+    // ---- stage the 32 feature rows
+    const float* xr;
+    __syncwarp();                                             // every lane is done with the previous tile
+    const uint32_t e0 = __shfl_sync(0xffffffffu, e, 0);
+    const uint32_t later = __ballot_sync(0xffffffffu, e != e0);
+    const uint32_t n0 = later ? (uint32_t)__ffs(later) - 1u : 32u;          // rows of the first utterance
+    const uint32_t e1 = __shfl_sync(0xffffffffu, e, n0 & 31u);
+    if (kBulk && __all_sync(0xffffffffu, e == e0 || e == e1)) {
+      // at most two utterances: each one's rows are contiguous in global memory -> one bulk copy each, from the
+      // 16-byte-aligned address below the first row (the tile keeps the same phase a)
+      const uint32_t fa = __shfl_sync(0xffffffffu, frame, 0), fb = __shfl_sync(0xffffffffu, frame, n0 & 31u);
+      const uint32_t rows_a = min(n0, nvalid), rows_b = nvalid - rows_a;
+      const size_t src_a = (size_t)fa * kRowB, src_b = (size_t)fb * kRowB;
+      const uint32_t a_a = (uint32_t)src_a & 15u, a_b = (uint32_t)src_b & 15u;
+      const uint32_t size_a = (rows_a * kRowB + a_a + 15u) & ~15u, size_b = rows_b ? (rows_b * kRowB + a_b + 15u) & ~15u : 0u;
+      if (lane == 0) {
+        mbar_expect_tx(bar, size_a + size_b);
+        bulk_load(tile, xbytes + src_a - a_a, size_a, bar);
+        if (rows_b) bulk_load(tile + size_a, xbytes + src_b - a_b, size_b, bar);
+      }
+      xr = reinterpret_cast<const float*>(lane < n0 ? tile + a_a + lane * kRowB : tile + size_a + a_b + (lane - n0) * kRowB);
+      mbar_wait(bar, phase);
+      phase ^= 1u;
+    } else {
+      // general case: element f = it * 32 + lane of the tile is (row r, column q), walked incrementally; the row's
+      // frame comes from its lane (asynchronous 4-byte copies, all in flight at once)
+      uint32_t r = lane / dim, q = lane - r * dim, dst = smem_u32(tile) + (r * XS + q) * 4u;
+#pragma unroll 4
+      for (uint32_t it = 0; it < dim; it++) {
+        const uint32_t fr = __shfl_sync(0xffffffffu, frame, r);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(p.x + (size_t)fr * dim + q) : "memory");
+        q += 32; dst += 32 * 4;
+        if (q >= dim) { q -= dim; r++; dst += (XS - dim) * 4; }
+        if (dim < 32 && q >= dim) { q -= dim; r++; dst += (XS - dim) * 4; }
+      }
+      asm volatile("cp.async.wait_all;" ::: "memory");
+      __syncwarp();
+      xr = reinterpret_cast<const float*>(tile) + lane * XS;
+    }
+    if (c0 + lane >= n_cells) continue;
+    double best = 1e10;
+    uint32_t bk = 0;
+    if (nd) {
+      if (i1 < nd) {
+        const double sc = sm_exact<DIM>(tbl + (size_t)i1 * RW, lw[i1], xr, iv);
+        if (sc < best) { best = sc; bk = i1; }
+      } else {
+        // near-ties are queued for k_tc_rescan (a rescan inside this kernel was measured: one warp walking 256
+        // densities holds its CTA back for ~10k cycles, +0.5 ms per 13 M cells)
+        const unsigned long long slot = atomicAdd(p.rescan, 1ull);
+        if (slot < p.cap) { p.rescan[1 + slot] = cell; continue; }
+        double rb;                                  // list full: rescan here
+        uint32_t rk;
+        sm_rescan<DIM>(tbl, lw, xr, iv, nd, RW, 0u, 1u, rb, rk);
+        best = rb; bk = rk == 0xffffffffu ? 0u : rk; n_rescans++;
+      }
+    }
+    p.out[cell] = best;
+    if (p.amin16) p.amin16[cell] = (uint16_t)bk;
+  }
+  if (n_rescans && p.fallback_count) atomicAdd(p.fallback_count, (unsigned long long)n_rescans);
+}
+
 // one warp per queued near-tie cell: exact f64 rescan of the whole state, first minimum wins
 __global__ void __launch_bounds__(256) k_tc_rescan(RefineParams p) {
   const uint32_t lane = threadIdx.x & 31;
@@ -1190,6 +1376,22 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
                      (r.pooled ? (size_t)(dense ? c->n_states : c->max_uniq) * c->dimP * sizeof(double) : 0);
   if (rsm > 200 * 1024) r.pooled = 0;
   const size_t rsm_used = r.pooled ? rsm : 128 * (2 * (size_t)c->npair + 2) * sizeof(float);
+  // state-major refinement: gathered, pooled, unrolled dimensions, and the widest state's table fits shared memory
+  uint32_t sm_rw = c->dim + 1;
+  while ((sm_rw & 1) || !((sm_rw >> 1) & 1)) sm_rw++;        // 2 * odd doubles per row
+  uint32_t sm_maxnd = 0;
+  for (uint32_t s = 0; s + 1 < c->h_state_off.size(); s++) sm_maxnd = std::max(sm_maxnd, c->h_state_off[s + 1] - c->h_state_off[s]);
+  // one CTA per SM: as many warps (each with its own 32-row feature tile) as fit next to the table
+  const size_t sm_fixed = ((size_t)sm_maxnd * sm_rw + ((sm_maxnd + 1u) & ~1u) + c->dimP) * sizeof(double) +
+                          128 * (sizeof(uint4) + sizeof(uint2)) + 2048 * sizeof(uint16_t) + 1024;
+  const size_t sm_tile = 32 * (size_t)(c->dim | 1u) * sizeof(float) + 64;
+  int sm_warps = sm_fixed + 8 * sm_tile <= kSmemLimit ? (int)std::min<size_t>(32, (kSmemLimit - sm_fixed) / sm_tile) : 0;
+  const size_t sm_smem = sm_fixed + (size_t)sm_warps * sm_tile;
+  const bool sm_dim = c->dim == 24 || c->dim == 25 || c->dim == 32 || c->dim == 33 || c->dim == 48 || c->dim == 49;
+  const bool sm_can = !dense && !c->tc_full && sm_dim && sm_warps >= 8 && c->n_sm_items > 0 && c->n_frames < 0xffffffffull;
+  const bool use_sm = sm_can && c->tc_refine != 1;
+  r.sm_items = c->d_sm_items.p; r.sm_ent_a = c->d_sm_ent_a.p; r.sm_ent_b = c->d_sm_ent_b.p;
+  r.sm_rw = sm_rw; r.sm_maxnd = sm_maxnd;
   const bool one = ranges.size() == 1;
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER], c->stream);
   uint64_t f_prev = 0, g_prev = 0;
@@ -1242,7 +1444,20 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE], c->stream);
   // refinement of every cell in one launch (alternating GEMM and refinement launches per range wastes the SMs at
   // every switch: a GEMM CTA needs the whole shared memory of an SM, so it waits for all refinement CTAs there)
-  {
+  if (use_sm) {
+    const unsigned sgrid = (unsigned)c->n_sm_items;
+#define SGMM_SM_CASE(D)                                                                                              \
+  case D:                                                                                                            \
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_smem)); \
+    k_tc_refine_sm<D><<<sgrid, 32 * sm_warps, sm_smem, c->stream>>>(r);                                                       \
+    break;
+    switch (c->dim) {
+      SGMM_SM_CASE(24) SGMM_SM_CASE(25) SGMM_SM_CASE(32) SGMM_SM_CASE(33) SGMM_SM_CASE(48) SGMM_SM_CASE(49)
+      default: SGMM_FAIL(c, "state-major refinement: unsupported dimension");
+    }
+#undef SGMM_SM_CASE
+    SGMM_LAUNCH_CHECK(c);
+  } else {
     const unsigned rgrid = dense ? (unsigned)((dense_nframes + 127) / 128) : (unsigned)c->n_tasks128;
     r.tasks = dense ? nullptr : c->d_tasks128.p;
     switch (c->npair) {   // common feature dimensions get a fully unrolled row walk

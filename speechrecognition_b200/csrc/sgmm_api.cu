@@ -93,6 +93,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_Bimg.release(); c->d_tile_first.release(); c->d_tile_info.release(); c->d_Ahi.release(); c->d_Alo.release();
   c->d_xnorm.release(); c->d_sguard_tc.release(); c->d_col_off.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
+  c->d_sm_items.release(); c->d_sm_ent_a.release(); c->d_sm_ent_b.release();
   for (int i = 0; i < 2; i++) { c->d_keys[i].release(); c->d_vals[i].release(); }
   c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release();
   c->d_partial.release(); c->d_acc.release(); c->d_score_part.release();
@@ -485,6 +486,42 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     }
     close_pack();
   }
+  // ---- state-major refinement items.  Utterances are cut into blocks of about kSmBlockFrames frames (at most
+  // kSmMaxEntries utterances); an item is one state of one block and lists the block's utterances that visit it.
+  // Items are ordered block-major so that the CTAs in flight write into a few MB of the emission matrix.
+  std::vector<uint4> sm_items, sm_ent_a;
+  std::vector<uint2> sm_ent_b;
+  {
+    const uint64_t kSmBlockFrames = 32768;
+    const uint32_t kSmMaxEntries = 128;
+    std::vector<std::vector<std::pair<uint32_t, uint32_t>>> by_state(max_state + 1);   // state -> (utt, column)
+    std::vector<uint32_t> touched;
+    uint32_t u0 = 0;
+    while (u0 < U) {
+      uint32_t u1 = u0;
+      while (u1 < U && u1 - u0 < kSmMaxEntries && (u1 == u0 || frame_off[u1 + 1] - frame_off[u0] <= kSmBlockFrames)) u1++;
+      touched.clear();
+      for (uint32_t u = u0; u < u1; u++)
+        for (uint32_t j = uniq_off[u]; j < uniq_off[u + 1]; j++) {
+          if (by_state[uniq[j]].empty()) touched.push_back(uniq[j]);
+          by_state[uniq[j]].push_back({u, j - uniq_off[u]});
+        }
+      std::sort(touched.begin(), touched.end());
+      for (uint32_t s : touched) {
+        uint32_t cells = 0;
+        const uint32_t first = (uint32_t)sm_ent_a.size();
+        for (auto& uc : by_state[s]) {
+          const uint64_t cell0 = E_off[uc.first] + uc.second, f0 = frame_off[uc.first];
+          sm_ent_a.push_back(make_uint4((uint32_t)cell0, (uint32_t)(cell0 >> 32), ncol[uc.first], cells));
+          sm_ent_b.push_back(make_uint2((uint32_t)f0, (uint32_t)(f0 >> 32)));
+          cells += (uint32_t)(frame_off[uc.first + 1] - f0);
+        }
+        sm_items.push_back(make_uint4(s, first, (uint32_t)by_state[s].size(), cells));
+        by_state[s].clear();
+      }
+      u0 = u1;
+    }
+  }
   for (auto& vc : c->vclasses) vc.d_utts.release();
   c->vclasses.clear();
   for (auto& kv : classes) {
@@ -506,9 +543,13 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       upload(c, c->d_pack_desc, pack_desc.data(), pack_desc.size()) ||
       upload(c, c->d_pack_uniq, pack_uniq.data(), pack_uniq.size()) ||
       upload(c, c->d_pack_rows, pack_rows.data(), pack_rows.size()) ||
-      upload(c, c->d_pack_colmap, pack_colmap.data(), pack_colmap.size()))
+      upload(c, c->d_pack_colmap, pack_colmap.data(), pack_colmap.size()) ||
+      upload(c, c->d_sm_items, sm_items.data(), sm_items.size()) ||
+      upload(c, c->d_sm_ent_a, sm_ent_a.data(), sm_ent_a.size()) ||
+      upload(c, c->d_sm_ent_b, sm_ent_b.data(), sm_ent_b.size()))
     return 1;
   c->n_packs = pack_desc.size();
+  c->n_sm_items = sm_items.size();
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->max_aut_state = max_state; c->max_uniq = max_uniq;
   c->n_utts = U; c->n_tasks = tasks.size(); c->n_tasks64 = tasks64.size(); c->n_tasks128 = tasks128.size(); c->n_tasks256 = tasks256.size(); c->E_elems = E_off[U];
@@ -610,6 +651,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_debug")) { c->tc_debug = (int)value; return 0; }
   if (!strcmp(key, "async_upload")) { c->async_upload = value != 0; return 0; }
   if (!strcmp(key, "tc_wide")) { c->tc_wide = (int)value; return 0; }   // takes effect at the next sgmm_set_model
+  if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
   if (!strcmp(key, "tc_pack")) { c->tc_pack = value != 0; return 0; }   // takes effect at the next sgmm_set_corpus
   if (!strcmp(key, "upload_chunks")) {
     if (value < 1 || value > sgmm_ctx::kFeatChunks) SGMM_FAIL(c, "set_option: upload_chunks out of range");

@@ -114,6 +114,13 @@ struct sgmm_ctx {
   std::vector<uint64_t> h_t128_end, h_t256_end;   // exclusive end frame of every task (ascending)
   bool tc_pack = true;             // option "tc_pack": pack short utterance tails into shared 128-row GEMM halves
   size_t n_packs = 0;
+  // state-major refinement (k_tc_refine_sm): work items (block of utterances, state) and, per item, the
+  // utterances of the block that visit the state
+  int tc_refine = 0;               // option "tc_refine": 0 automatic, 1 frame-major kernel, 2 state-major kernel
+  size_t n_sm_items = 0;
+  DevBuf<uint4> d_sm_items;        // {state, first entry, entries, cells}
+  DevBuf<uint4> d_sm_ent_a;        // {first cell lo, hi (E_off[u] + column), cells per frame (ncol), cells before}
+  DevBuf<uint2> d_sm_ent_b;        // {first frame lo, hi}
   DevBuf<uint4> d_pack_desc;
   DevBuf<uint32_t> d_pack_uniq;
   DevBuf<sgmm_pack_row> d_pack_rows;

@@ -266,7 +266,7 @@ def test_ffma_scorer_ties_and_near_ties():
 
 @pytest.mark.parametrize("halves", [1, 2])
 @pytest.mark.parametrize("dim,nd,pooling", [(33, 200, "mixture"), (25, 40, "none"), (33, 256, "global"), (12, 17, "none"),
-                                            (48, 64, "mixture"), (48, 30, "none")])
+                                            (48, 64, "mixture"), (48, 30, "none"), (25, 70, "mixture"), (32, 150, "global")])
 def test_tensor_core_scorer_exact(dim, nd, pooling, halves):
     """tcgen05 3xTF32 GEMM + certified refinement: dense scores/argmins and batched alignments bit-identical to
     the oracle, in the pooled (K = d+1) and the full (K = 2d+1) operand forms, with ragged state sizes."""
@@ -305,6 +305,52 @@ def test_tensor_core_scorer_exact(dim, nd, pooling, halves):
     got, costs = ctx.align()
     assert np.array_equal(costs, want_costs)
     assert np.array_equal(got["state"].astype(np.uint32), want_states)
+    # both refinement kernels (frame-major; state-major with the state's table in shared memory): same bits
+    for mode in (1, 2, 0):
+        ctx.set_option("tc_refine", mode)
+        again, costs2 = ctx.align()
+        assert np.array_equal(again, got) and np.array_equal(costs2, costs), mode
+    ctx.close()
+
+
+@pytest.mark.parametrize("dim", [33, 32, 25])
+def test_state_major_refinement_short_utterances(dim):
+    """Utterances of 3..40 frames: a warp's 32 cells of one state then span several utterances (bulk-copy staging
+    takes at most two, the rest goes through the element-wise path); near-ties planted so that the rescan queue is used."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(5)
+    n_states, nd = 12, 64
+    t = synth.random_model(rng, dim, n_states, nd, "mixture")
+    means = t["means"].reshape(-1, dim)
+    means[1] = means[0]                                    # exact duplicate density: a tie the filter cannot certify
+    auts, xs, f_off, a_off = [], [], [0], [0]
+    for u in range(150):
+        S = int(rng.integers(1, 4))
+        aut = rng.integers(0, n_states, size=S).astype(np.uint32)
+        T = int(rng.integers(max(3, S), 41))
+        st = aut[synth.sample_path(rng, T, S)]
+        xs.append(synth.emit_frames(rng, t, dim, st)); auts.append(aut)
+        f_off.append(f_off[-1] + T); a_off.append(a_off[-1] + S)
+    x = np.concatenate(xs).astype(np.float32)
+    frame_off, aut_off, automata = np.array(f_off, np.uint64), np.array(a_off, np.uint32), np.concatenate(auts)
+    O = Oracle(dim, n_states, "mixture", True, (3.0, 0.0, 30.0), 0)
+    O.load_tables(t)
+    want_states, want_costs = O.align_batch(x, frame_off, automata, aut_off, threads=8)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, t); ctx.set_features(x)
+    ctx.set_corpus(frame_off, automata, aut_off); ctx.set_tdp(3.0, 0.0, 30.0, 0)
+    ctx.set_option("scorer", 3)
+    for mode in (2, 1):
+        ctx.set_option("tc_refine", mode)
+        got, costs = ctx.align()
+        assert np.array_equal(got["state"].astype(np.uint32), want_states), mode
+        assert np.array_equal(costs, want_costs), mode
+        cnt, sx, sxx, ssum = ctx.accumulate(first_pass=False)
+        dens, _ = ctx.last_frame_results()
+        P = Oracle(dim, n_states, "mixture", True, (3.0, 0.0, 30.0), 0)
+        P.load_tables(t)
+        assert np.array_equal(dens, P.accumulate(want_states, x)), mode     # cached argmins of the aligned cells
     ctx.close()
 
 
