@@ -1137,7 +1137,8 @@ __global__ void __launch_bounds__(1024, 1) k_tc_refine_sm(RefineParams p) {
   uint2* ent_b = reinterpret_cast<uint2*>(ent_a + kMaxEnt);  // [kMaxEnt]
   uint16_t* chunk_ent = reinterpret_cast<uint16_t*>(ent_b + kMaxEnt);   // [kMaxChunks] entry of a chunk's first cell
   uint64_t* bar = reinterpret_cast<uint64_t*>(chunk_ent + kMaxChunks) + warp;   // [32] one mbarrier per warp
-  unsigned char* tile = reinterpret_cast<unsigned char*>(chunk_ent + kMaxChunks) + 256 + warp * kTileB;
+  uint8_t* perm = reinterpret_cast<uint8_t*>(chunk_ent + kMaxChunks) + 256 + warp * 32;   // [32][32] lane permutation
+  unsigned char* tile = reinterpret_cast<unsigned char*>(chunk_ent + kMaxChunks) + 1280 + warp * kTileB;
   uint32_t n_rescans = 0;
 
   if (lane == 0) mbar_init(bar, 1);
@@ -1180,7 +1181,7 @@ __global__ void __launch_bounds__(1024, 1) k_tc_refine_sm(RefineParams p) {
     const uint32_t frame = ent_b[e].x + t;                    // (the launcher takes this kernel below 2^32 frames only)
     const uint32_t i1 = nd ? __ldg(p.cand + cell) : 0u;
     // ---- stage the 32 feature rows
-    const float* xr;
+    uint32_t xr_off;                                          // byte offset of this lane's row inside the tile
     __syncwarp();                                             // every lane is done with the previous tile
     const uint32_t e0 = __shfl_sync(0xffffffffu, e, 0);
     const uint32_t later = __ballot_sync(0xffffffffu, e != e0);
@@ -1199,7 +1200,7 @@ __global__ void __launch_bounds__(1024, 1) k_tc_refine_sm(RefineParams p) {
         bulk_load(tile, xbytes + src_a - a_a, size_a, bar);
         if (rows_b) bulk_load(tile + size_a, xbytes + src_b - a_b, size_b, bar);
       }
-      xr = reinterpret_cast<const float*>(lane < n0 ? tile + a_a + lane * kRowB : tile + size_a + a_b + (lane - n0) * kRowB);
+      xr_off = lane < n0 ? a_a + lane * kRowB : size_a + a_b + (lane - n0) * kRowB;
       mbar_wait(bar, phase);
       phase ^= 1u;
     } else {
@@ -1216,28 +1217,49 @@ __global__ void __launch_bounds__(1024, 1) k_tc_refine_sm(RefineParams p) {
       }
       asm volatile("cp.async.wait_all;" ::: "memory");
       __syncwarp();
-      xr = reinterpret_cast<const float*>(tile) + lane * XS;
+      xr_off = lane * XS * 4u;
     }
-    if (c0 + lane >= n_cells) continue;
+    // Lanes swap cells so that the 8 lanes of a quarter-warp (one LDS.128 wavefront group) gather table rows from
+    // different 16-byte bank groups: a row's group is (winner + unit) mod 8, so cells are ranked by winner mod 8 and
+    // dealt round-robin to the four quarters (10.1 -> 7.8 wavefronts per table load).
+    const bool valid = c0 + lane < n_cells;
+    uint32_t src;
+    {
+      const uint32_t key = (valid && i1 < nd) ? (i1 & 7u) : (lane & 7u);
+      const uint32_t lt = (1u << lane) - 1u;
+      uint32_t rank = 0;
+#pragma unroll
+      for (uint32_t c = 0; c < 8; c++) {
+        const uint32_t m = __ballot_sync(0xffffffffu, key == c);
+        rank += c < key ? __popc(m) : (c == key ? __popc(m & lt) : 0u);
+      }
+      perm[((rank & 3u) << 3) | (rank >> 2)] = (uint8_t)lane;
+      __syncwarp();
+      src = perm[lane];
+    }
+    const uint64_t my_cell = __shfl_sync(0xffffffffu, cell, src);
+    const uint32_t my_i1 = __shfl_sync(0xffffffffu, i1, src);
+    const float* my_xr = reinterpret_cast<const float*>(tile + __shfl_sync(0xffffffffu, xr_off, src));
+    if (!__shfl_sync(0xffffffffu, (uint32_t)valid, src)) continue;
     double best = 1e10;
     uint32_t bk = 0;
     if (nd) {
-      if (i1 < nd) {
-        const double sc = sm_exact<DIM>(tbl + (size_t)i1 * RW, lw[i1], xr, iv);
-        if (sc < best) { best = sc; bk = i1; }
+      if (my_i1 < nd) {
+        const double sc = sm_exact<DIM>(tbl + (size_t)my_i1 * RW, lw[my_i1], my_xr, iv);
+        if (sc < best) { best = sc; bk = my_i1; }
       } else {
         // near-ties are queued for k_tc_rescan (a rescan inside this kernel was measured: one warp walking 256
         // densities holds its CTA back for ~10k cycles, +0.5 ms per 13 M cells)
         const unsigned long long slot = atomicAdd(p.rescan, 1ull);
-        if (slot < p.cap) { p.rescan[1 + slot] = cell; continue; }
+        if (slot < p.cap) { p.rescan[1 + slot] = my_cell; continue; }
         double rb;                                  // list full: rescan here
         uint32_t rk;
-        sm_rescan<DIM>(tbl, lw, xr, iv, nd, RW, 0u, 1u, rb, rk);
+        sm_rescan<DIM>(tbl, lw, my_xr, iv, nd, RW, 0u, 1u, rb, rk);
         best = rb; bk = rk == 0xffffffffu ? 0u : rk; n_rescans++;
       }
     }
-    p.out[cell] = best;
-    if (p.amin16) p.amin16[cell] = (uint16_t)bk;
+    p.out[my_cell] = best;
+    if (p.amin16) p.amin16[my_cell] = (uint16_t)bk;
   }
   if (n_rescans && p.fallback_count) atomicAdd(p.fallback_count, (unsigned long long)n_rescans);
 }
@@ -1383,7 +1405,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   for (uint32_t s = 0; s + 1 < c->h_state_off.size(); s++) sm_maxnd = std::max(sm_maxnd, c->h_state_off[s + 1] - c->h_state_off[s]);
   // one CTA per SM: as many warps (each with its own 32-row feature tile) as fit next to the table
   const size_t sm_fixed = ((size_t)sm_maxnd * sm_rw + ((sm_maxnd + 1u) & ~1u) + c->dimP) * sizeof(double) +
-                          128 * (sizeof(uint4) + sizeof(uint2)) + 2048 * sizeof(uint16_t) + 1024;
+                          128 * (sizeof(uint4) + sizeof(uint2)) + 2048 * sizeof(uint16_t) + 1280;
   const size_t sm_tile = 32 * (size_t)(c->dim | 1u) * sizeof(float) + 64;
   int sm_warps = sm_fixed + 8 * sm_tile <= kSmemLimit ? (int)std::min<size_t>(32, (kSmemLimit - sm_fixed) / sm_tile) : 0;
   const size_t sm_smem = sm_fixed + (size_t)sm_warps * sm_tile;
