@@ -922,6 +922,12 @@ struct RefineParams {
   const uint2* sm_ent_b;
   uint32_t sm_rw;              // doubles per table row: mean row, norm, padding (2 * odd: bank spread for LDS.128)
   uint32_t sm_maxnd;           // most densities in one state
+  // two-stage rescan: f32 tables of the FFMA scorer ([D][4 * dv4] mean and h = 1 / (2 var), c = norm - log w) and
+  // the per-state constants of its certified error bound {cmin, |c| max, M max}
+  const float4* mu32T;         // [dv4][D]
+  const float4* h32;
+  const float* c32;
+  const float4* sguard;
 };
 
 // cell -> (frame, state); returns false for the padding column of a gathered row
@@ -1297,6 +1303,88 @@ __global__ void __launch_bounds__(256) k_tc_rescan(RefineParams p) {
   }
 }
 
+// Two-stage rescan of the queued near-tie cells, one warp per cell.  Stage 1 scores every density of the state in
+// f32 (direct form c + sum h (x - mu)^2 on the FFMA scorer's tables, lane l takes densities l, l + 32, ...) and finds
+// the f32 minimum m.  A density whose f32 score exceeds m by more than k_emission_ffma's rigorous bound on the
+// evaluation error of both (k_score_ffma.cu, header) has a strictly larger f64 score than the f32 winner and cannot
+// be the reference's argmin; stage 2 evaluates only the others (typically two or three) in f64, in the reference's
+// operation order, first minimum wins.  Same results as k_tc_rescan with ~1 % of its f64 work and half its bytes.
+// Pooled models only (one h row per state).
+template <int DV4>
+__global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t nwarps = (uint64_t)gridDim.x * (blockDim.x >> 5);
+  const unsigned long long count = min(p.rescan[0], p.cap);
+  const float eps = 2.384185791015625e-07f;   // 2^-22, as k_emission_ffma
+  const float dterm = (float)(p.m.dim + 8);
+  for (uint64_t i = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < count; i += nwarps) {
+    const uint64_t e = p.rescan[1 + i];
+    uint64_t frame;
+    uint32_t s;
+    decode_cell(p, e, frame, s);
+    const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
+    const float* xf = p.x + frame * p.m.dim;
+    float xr[4 * DV4];
+#pragma unroll
+    for (int q = 0; q < 4 * DV4; q++) xr[q] = q < (int)p.m.dim ? __ldg(xf + q) : 0.f;
+    const float4 g = __ldg(p.sguard + s);     // {cmin, cabs, Mmax, -}
+    // pooled models only: every density of the state has the same h row -> the first one's, broadcast from L1
+    const float4* hrow = p.h32 + (size_t)k0 * DV4;
+    constexpr int kKeep = 8;                    // f32 scores of the first 8 rounds stay in registers for stage 2
+    float keep[kKeep];
+    auto score32 = [&](uint32_t k) {
+      float acc = 0.f;
+#pragma unroll
+      for (int v = 0; v < DV4; v++) {
+        const float4 m = __ldg(p.mu32T + (size_t)v * p.m.Dtot + k), h = __ldg(hrow + v);
+        float t;
+        t = xr[4 * v + 0] - m.x; acc = fmaf(t * h.x, t, acc);
+        t = xr[4 * v + 1] - m.y; acc = fmaf(t * h.y, t, acc);
+        t = xr[4 * v + 2] - m.z; acc = fmaf(t * h.z, t, acc);
+        t = xr[4 * v + 3] - m.w; acc = fmaf(t * h.w, t, acc);
+      }
+      return acc + __ldg(p.c32 + k);
+    };
+    float m32 = INFINITY;
+#pragma unroll
+    for (int j = 0; j < kKeep; j++) {
+      const uint32_t k = k0 + lane + 32 * j;
+      keep[j] = k < k1 ? score32(k) : INFINITY;
+      m32 = fminf(m32, keep[j]);                // fminf drops NaNs; they are kept below
+    }
+    for (uint32_t k = k0 + lane + 32 * kKeep; k < k1; k += 32) m32 = fminf(m32, score32(k));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m32 = fminf(m32, __shfl_xor_sync(0xffffffffu, m32, o));
+    double best = 1e10;
+    uint32_t bk = 0xffffffffu;
+    auto stage2 = [&](uint32_t k, float sc) {
+      const float dist = fmaxf(sc - g.x, 0.f);
+      const float guard = 2.f * eps * (dterm * dist + 2.f * sqrtf(dist * g.z) + g.y);
+      if ((sc - m32) > guard) return;           // certainly not the minimum (false for NaN: those are evaluated)
+      const double sd = sgmm_exact_score(p.m, xf, k);
+      if (sd < best) { best = sd; bk = k - k0; }
+    };
+#pragma unroll
+    for (int j = 0; j < kKeep; j++) {
+      const uint32_t k = k0 + lane + 32 * j;
+      if (k < k1) stage2(k, keep[j]);
+    }
+    for (uint32_t k = k0 + lane + 32 * kKeep; k < k1; k += 32) stage2(k, score32(k));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const uint32_t ok = __shfl_xor_sync(0xffffffffu, bk, o);
+      if (ob < best || (ob == best && ok < bk)) { best = ob; bk = ok; }
+    }
+    if (lane == 0) {
+      p.out[e] = best;
+      if (p.argmin) p.argmin[e] = bk == 0xffffffffu ? 0 : bk;
+      if (p.amin16) p.amin16[e] = bk == 0xffffffffu ? 0 : (uint16_t)bk;
+      if (p.fallback_count) atomicAdd(p.fallback_count, 1ull);
+    }
+  }
+}
+
 }  // namespace sgmm_tc
 
 // ---------------------------------------------------------------------------------------------------
@@ -1497,7 +1585,14 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     SGMM_LAUNCH_CHECK(c);
   }
   c->stage_ms[SGMM_T_SCORE_FILTER] = -1.f;
-  k_tc_rescan<<<148 * 16, 256, 0, c->stream>>>(r);
+  r.mu32T = c->d_mu32T.p; r.h32 = c->d_h32.p; r.c32 = c->d_c32.p; r.sguard = c->d_sguard.p;
+  switch ((c->tc_rescan == 1 || c->tc_full) ? 0u : c->dv4) {   // option tc_rescan 1: the plain full-f64 rescan (same results)
+    case 7: k_tc_rescan2<7><<<148 * 16, 256, 0, c->stream>>>(r); break;
+    case 9: k_tc_rescan2<9><<<148 * 16, 256, 0, c->stream>>>(r); break;
+    case 12: k_tc_rescan2<12><<<148 * 16, 256, 0, c->stream>>>(r); break;
+    case 16: k_tc_rescan2<16><<<148 * 16, 256, 0, c->stream>>>(r); break;
+    default: k_tc_rescan<<<148 * 16, 256, 0, c->stream>>>(r); break;
+  }
   SGMM_LAUNCH_CHECK(c);
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE + 1], c->stream);
   c->stage_ms[SGMM_T_SCORE_REFINE] = -1.f;

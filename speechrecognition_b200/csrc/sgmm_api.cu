@@ -88,7 +88,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_norm.release(); c->d_logw.release(); c->d_state_off.release(); c->d_x.release();
   c->d_frame_off.release(); c->d_E_off.release(); c->d_aut.release(); c->d_aut_off.release();
   c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
-  c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_h32.release(); c->d_c32.release();
+  c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_mu32T.release(); c->d_h32.release(); c->d_c32.release();
   c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release(); c->d_tasks256.release(); c->d_Amin.release(); c->d_fcol.release();
   c->d_Bimg.release(); c->d_tile_first.release(); c->d_tile_info.release(); c->d_Ahi.release(); c->d_Alo.release();
   c->d_xnorm.release(); c->d_sguard_tc.release(); c->d_col_off.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
@@ -196,6 +196,12 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
         upload(c, c->d_h32, reinterpret_cast<const float4*>(h32.data()), (size_t)D * dv4) ||
         upload(c, c->d_c32, c32.data(), (size_t)D) || upload(c, c->d_sguard, sg.data(), sg.size()))
       return 1;
+    // density-minor twin of the mean table for the two-stage rescan (lane = density: consecutive lanes read
+    // consecutive 16-byte units)
+    std::vector<float> mu32T((size_t)D * row);
+    for (uint32_t j = 0; j < D; j++)
+      for (uint32_t v = 0; v < dv4; v++) memcpy(&mu32T[((size_t)v * D + j) * 4], &mu32[j * row + 4 * v], 4 * sizeof(float));
+    if (upload(c, c->d_mu32T, reinterpret_cast<const float4*>(mu32T.data()), (size_t)D * dv4)) return 1;
   }
   // Tensor-core scorer operands (k_score_tc.cu).  Columns = densities, state-major, every state padded to a
   // multiple of 16 columns with never-winning dummies.  B row of density j:
@@ -651,6 +657,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_debug")) { c->tc_debug = (int)value; return 0; }
   if (!strcmp(key, "async_upload")) { c->async_upload = value != 0; return 0; }
   if (!strcmp(key, "tc_wide")) { c->tc_wide = (int)value; return 0; }   // takes effect at the next sgmm_set_model
+  if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
   if (!strcmp(key, "tc_pack")) { c->tc_pack = value != 0; return 0; }   // takes effect at the next sgmm_set_corpus
   if (!strcmp(key, "upload_chunks")) {

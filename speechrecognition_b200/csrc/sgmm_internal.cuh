@@ -70,6 +70,7 @@ struct sgmm_ctx {
   uint32_t dv4 = 0;
   int scorer = 0;   // 0 auto, 1 exact f64, 2 f32 FFMA + certified refinement
   DevBuf<float4> d_mu32, d_h32, d_sguard;
+  DevBuf<float4> d_mu32T;          // [dv4][D]: the mean table density-minor (two-stage rescan)
   DevBuf<float> d_c32;
   DevBuf<unsigned long long> d_fallbacks;
   // tensor-core scorer (k_score_tc.cu): 3xTF32 operands, K-major, KP = padded K
@@ -117,6 +118,7 @@ struct sgmm_ctx {
   // state-major refinement (k_tc_refine_sm): work items (block of utterances, state) and, per item, the
   // utterances of the block that visit the state
   int tc_refine = 0;               // option "tc_refine": 0 automatic, 1 frame-major kernel, 2 state-major kernel
+  int tc_rescan = 0;               // option "tc_rescan": 0 two-stage (f32 prefilter, f64 candidates), 1 full f64 scan
   size_t n_sm_items = 0;
   DevBuf<uint4> d_sm_items;        // {state, first entry, entries, cells}
   DevBuf<uint4> d_sm_ent_a;        // {first cell lo, hi (E_off[u] + column), cells per frame (ncol), cells before}

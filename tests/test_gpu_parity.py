@@ -301,6 +301,11 @@ def test_tensor_core_scorer_exact(dim, nd, pooling, halves):
     assert np.array_equal(got_a, want_a)
     assert np.array_equal(got_s, want_s)
     assert fb < 0.25 * got_s.size, f"{fb} of {got_s.size} cells fell back to the f64 rescan"
+    ctx.set_option("tc_rescan", 1)                 # plain full-f64 rescan instead of the two-stage one: same bits
+    got_s1, got_a1 = ctx.score_all(0, n)
+    assert np.array_equal(got_a1, want_a) and np.array_equal(got_s1, want_s)
+    assert ctx.get_counter("fallbacks") == fb
+    ctx.set_option("tc_rescan", 0)
     want_states, want_costs = O.align_batch(corp["x"], corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
     got, costs = ctx.align()
     assert np.array_equal(costs, want_costs)
@@ -341,8 +346,9 @@ def test_state_major_refinement_short_utterances(dim):
     ctx.set_model_tables(dim, t); ctx.set_features(x)
     ctx.set_corpus(frame_off, automata, aut_off); ctx.set_tdp(3.0, 0.0, 30.0, 0)
     ctx.set_option("scorer", 3)
-    for mode in (2, 1):
+    for mode, rescan in ((2, 0), (1, 0), (2, 1)):
         ctx.set_option("tc_refine", mode)
+        ctx.set_option("tc_rescan", rescan)
         got, costs = ctx.align()
         assert np.array_equal(got["state"].astype(np.uint32), want_states), mode
         assert np.array_equal(costs, want_costs), mode

@@ -16,7 +16,8 @@ ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"]); ctx.set_td
 res = {}
 modes = [int(a) for a in sys.argv[2:]] or [1, 2, 1, 2]
 for mode in modes:
-    ctx.set_option("tc_refine", mode)
+    ctx.set_option("tc_refine", mode % 10)
+    ctx.set_option("tc_rescan", mode // 10)
     ms = []
     for it in range(6):
         ali, costs = ctx.align()
@@ -25,6 +26,8 @@ for mode in modes:
     keys = ms[0].keys()
     print("tc_refine", mode, {k: round(float(np.mean([m[k] for m in ms])), 3) for k in keys}, flush=True)
     res[mode] = (ali.copy(), costs.copy())
-if 1 in res and 2 in res:
-    assert np.array_equal(res[1][0], res[2][0]) and np.array_equal(res[1][1], res[2][1])
+ks = list(res)
+if len(ks) > 1:
+    for k in ks[1:]:
+        assert np.array_equal(res[ks[0]][0], res[k][0]) and np.array_equal(res[ks[0]][1], res[k][1])
     print("identical alignments and costs")
