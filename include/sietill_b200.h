@@ -137,6 +137,9 @@ int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
  *   the host buffer must stay untouched until the next compute call returns (use sgmm_host_alloc memory).
  * "tc_halves" (0 auto, 1, 2): 128-frame halves per tensor-core CTA.  "tc_pack" (default 1; read by sgmm_set_corpus):
  *   pack short utterance tails into shared 128-row halves.
+ * "tc_refine" (0 auto, 1, 2): refinement kernel of the tensor-core scorer — 1 frame-major (winner's mean row gathered
+ *   from L2), 2 state-major (the state's mean table in shared memory; gathered scoring of pooled models only).
+ *   "tc_rescan" (0, 1): 0 two-stage rescan of near-tie cells (f32 prefilter, f64 candidates), 1 full f64 scan.
  * "tc_wide" (-1 auto, 0, 1; read by sgmm_set_model): 256-density GEMM tiles (the N = 256 kernel) instead of 128;
  *   auto picks them when some state has more than 128 densities and the tile ring fits shared memory.
  * "tc_debug": timing experiments for the tensor-core kernel — any bit other than 32 (cycle profile, read with the

@@ -1123,7 +1123,7 @@ __device__ __noinline__ void sm_rescan(const double* tbl, const double* lw, cons
 template <uint32_t DIM>
 __global__ void __launch_bounds__(1024, 1) k_tc_refine_sm(RefineParams p) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
-  constexpr uint32_t kMaxEnt = 128, kMaxChunks = 2048;
+  constexpr uint32_t kMaxEnt = kSmMaxEntries, kMaxChunks = kSmBlockFrames / 32;
   constexpr uint32_t dim = DIM, kRowB = DIM * 4;
   // Odd dimensions: the tile's rows are the frames' rows as they lie in global memory (stride = dim floats, odd, so
   // thread = row reads are conflict-free) and arrive by 1-D bulk copies.  Even dimensions need a padded stride and
@@ -1493,7 +1493,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   for (uint32_t s = 0; s + 1 < c->h_state_off.size(); s++) sm_maxnd = std::max(sm_maxnd, c->h_state_off[s + 1] - c->h_state_off[s]);
   // one CTA per SM: as many warps (each with its own 32-row feature tile) as fit next to the table
   const size_t sm_fixed = ((size_t)sm_maxnd * sm_rw + ((sm_maxnd + 1u) & ~1u) + c->dimP) * sizeof(double) +
-                          128 * (sizeof(uint4) + sizeof(uint2)) + 2048 * sizeof(uint16_t) + 1280;
+                          kSmMaxEntries * (sizeof(uint4) + sizeof(uint2)) + (kSmBlockFrames / 32) * sizeof(uint16_t) + 1280;
   const size_t sm_tile = 32 * (size_t)(c->dim | 1u) * sizeof(float) + 64;
   int sm_warps = sm_fixed + 8 * sm_tile <= kSmemLimit ? (int)std::min<size_t>(32, (kSmemLimit - sm_fixed) / sm_tile) : 0;
   const size_t sm_smem = sm_fixed + (size_t)sm_warps * sm_tile;

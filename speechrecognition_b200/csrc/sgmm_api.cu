@@ -498,8 +498,6 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   std::vector<uint4> sm_items, sm_ent_a;
   std::vector<uint2> sm_ent_b;
   {
-    const uint64_t kSmBlockFrames = 32768;
-    const uint32_t kSmMaxEntries = 128;
     std::vector<std::vector<std::pair<uint32_t, uint32_t>>> by_state(max_state + 1);   // state -> (utt, column)
     std::vector<uint32_t> touched;
     uint32_t u0 = 0;

@@ -29,6 +29,11 @@ struct DevBuf {
   void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+// state-major refinement: a block of utterances holds at most this many utterances / frames (an item's cells are
+// <= kSmBlockFrames, i.e. <= kSmBlockFrames / 32 warp chunks)
+constexpr uint32_t kSmMaxEntries = 256;
+constexpr uint32_t kSmBlockFrames = 65536;
+
 struct sgmm_pack_row {   // one row of a packed GEMM task (sgmm_set_corpus)
   uint64_t cell;     // first emission cell of this frame's row in the ragged emission matrix
   uint32_t frame;    // absolute frame index
