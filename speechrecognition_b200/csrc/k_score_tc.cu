@@ -27,6 +27,8 @@
 #include <algorithm>
 #include <vector>
 
+#include <cuda_fp16.h>
+
 #include "sgmm_internal.cuh"
 
 namespace sgmm_tc {
@@ -128,6 +130,15 @@ __device__ __forceinline__ void tc_mma_ss_1(uint32_t d_tmem, uint64_t adesc, uin
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
       : "memory");
 }
+// kind::f16 (A, B fp16, K = 16 per instruction = one 32-byte atom row, fp32 accumulate)
+__device__ __forceinline__ void tc_mma_ss_f16_1(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred pa;\n\t"
+      "setp.ne.b32 pa, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, pa;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
 __device__ __forceinline__ void tc_commit_elect(uint64_t* bar) {
   asm volatile(
       "{\n\t.reg .pred pe;\n\t"
@@ -178,6 +189,11 @@ __host__ __device__ inline uint32_t make_idesc_tf32(uint32_t M, uint32_t N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
+// D = f32, A = B = f16, both K-major
+__host__ __device__ inline uint32_t make_idesc_f16(uint32_t M, uint32_t N) {
+  return (1u << 4) | (0u << 7) | (0u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
 __device__ __forceinline__ float tf32_rna(float v) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
@@ -207,6 +223,54 @@ __global__ void k_tc_prep(const float* __restrict__ x, uint64_t n_frames, uint32
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) { s2 += __shfl_xor_sync(0xffffffffu, s2, o); s4 += __shfl_xor_sync(0xffffffffu, s4, o); }
   if (lane == 0) xnorm[f] = make_float2(sqrtf(s2) * 1.0001f, sqrtf(s4) * 1.0001f);   // ||x||, ||x^2|| (rounded up)
+}
+
+// A operand builder of the fp16 form (pooled models): row f = s_f * [x | 1 | 0...], s_f = the power of two that
+// brings max(|x|, 1) of the row into [2^14, 2^15), each entry split into fp16 hi + fp16 lo (11 + 11 bits; the lo
+// part of an entry below 2^-3 is subnormal: exact to 2^-25 if the tensor core keeps subnormals, and what would be
+// lost if it flushed them is added to the row's norm, so the certified bound holds either way).  The row scale is
+// common to all columns of the row and the state's column scale (sgmm_set_model) to all candidates of a (frame,
+// state) cell, so neither changes which column is the minimum; the epilogue's bound is linear in both.
+// xnorm[f] = {||s_f x|| (rounded up) + flush / (2 eps), s_f}.  A row with a non-finite feature becomes NaN: every
+// cell of that frame is then "uncertain" and rescanned in f64.
+__global__ void k_tc_prep16(const float* __restrict__ x, uint64_t n_frames, uint32_t dim, uint32_t KH, float inv2eps,
+                            __half* __restrict__ Ahi, __half* __restrict__ Alo, float2* __restrict__ xnorm) {
+  const uint64_t f = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (f >= n_frames) return;
+  const float* xf = x + f * dim;
+  float mx = 1.f;
+  bool bad = false;
+  for (uint32_t k = lane; k < dim; k += 32) {
+    const float v = fabsf(xf[k]);
+    bad |= !(v < 1048576.f);                       // (and the row scale stays a normal fp16 number)
+    mx = fmaxf(mx, v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  bad = __any_sync(0xffffffffu, bad);
+  int e;
+  frexpf(mx, &e);                                  // mx = m * 2^e, m in [0.5, 1)  ->  mx * 2^(15 - e) in [2^14, 2^15)
+  const float sf = ldexpf(1.f, 15 - e);
+  float s2 = 0.f, fl = 0.f;
+  for (uint32_t k = lane; k < KH; k += 32) {
+    float a = 0.f;
+    if (k < dim) a = xf[k] * sf;                   // exact (power of two; |a| < 2^15)
+    else if (k == dim) a = sf;
+    if (k < dim) s2 += a * a;
+    __half hi = __float2half_rn(a);
+    const float r = a - __half2float(hi);          // exact
+    __half lo = __float2half_rn(r);
+    // subnormal parts (below 2^-14): rounded to 2^-25 if kept, lost entirely if the tensor core flushes them
+    if (r != 0.f && fabsf(r) < 6.103515625e-05f) fl += fmaxf(fabsf(r), 2.98023223876953125e-08f);
+    if (a != 0.f && fabsf(a) < 6.103515625e-05f) fl += fabsf(a);
+    if (bad) { hi = __float2half_rn(nanf("")); lo = hi; }
+    Ahi[f * KH + k] = hi;
+    Alo[f * KH + k] = lo;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { s2 += __shfl_xor_sync(0xffffffffu, s2, o); fl += __shfl_xor_sync(0xffffffffu, fl, o); }
+  if (lane == 0) xnorm[f] = make_float2(sqrtf(s2) * 1.0001f + fl * inv2eps, sf);
 }
 
 
@@ -587,7 +651,9 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
 // and a ring of three HALF stages — a tile's hi block [k-step][256 rows][32 B] and its lo block are separate slots, so
 // that three slots (3 x 40 KB at d = 33) keep one tile in use and half of the next in flight.  Per (tile, half) unit:
 // Ahi.Bhi, Alo.Bhi (hi slot), then Ahi.Blo (lo slot).  With two halves, half h always owns accumulator h.
-template <int KS>
+// F16: operands are fp16 hi / lo pairs (k-step = 16 halves) and the MMAs kind::f16 — same bytes per k-step, same
+// shared-memory images and descriptors, K = d + 1 = 34 takes 3 k-steps instead of 5 (see k_tc_prep16).
+template <int KS, bool F16>
 __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -683,11 +749,15 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
     if (prof) w_a = clock64() - c0;
     tc_fence_after();
     uint32_t ld = 0, unit = 0;
+    auto mma1 = [](uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+      if (F16) tc_mma_ss_f16_1(d_tmem, adesc, bdesc, idesc, acc);
+      else tc_mma_ss_1(d_tmem, adesc, bdesc, idesc, acc);
+    };
     for (uint32_t j = 0; j < nu; j++) {
       const uint32_t s = ulist ? ulist[j] : j;
       for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, ld += 2) {
         const uint32_t N = p.tile_info[t].y;
-        const uint32_t idesc = make_idesc_tf32(BM, N);
+        const uint32_t idesc = F16 ? make_idesc_f16(BM, N) : make_idesc_tf32(BM, N);
         const uint32_t slot_hi = ld % nstage, par_hi = (ld / nstage) & 1;
         const uint32_t slot_lo = (ld + 1) % nstage, par_lo = ((ld + 1) / nstage) & 1;
         const uint64_t bhi = make_desc_sw32(smem_u32(sB + slot_hi * p.stage_bytes));
@@ -706,9 +776,9 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           const uint32_t nk = KS > 0 ? (uint32_t)KS : ks;
           if (tc_elect_one()) {
 #pragma unroll
-            for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, ahi + kk * kstrideA, bhi + kk * kstrideB, idesc, kk);
+            for (uint32_t kk = 0; kk < nk; kk++) mma1(d, ahi + kk * kstrideA, bhi + kk * kstrideB, idesc, kk);
 #pragma unroll
-            for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, alo + kk * kstrideA, bhi + kk * kstrideB, idesc, 1);
+            for (uint32_t kk = 0; kk < nk; kk++) mma1(d, alo + kk * kstrideA, bhi + kk * kstrideB, idesc, 1);
             if (h + 1 == nh) tc_commit(&empty[slot_hi]);    // the hi block is free once these MMAs are done
           }
           __syncwarp();
@@ -718,7 +788,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           tc_fence_after();
           if (tc_elect_one()) {
 #pragma unroll
-            for (uint32_t kk = 0; kk < nk; kk++) tc_mma_ss_1(d, ahi + kk * kstrideA, blo + kk * kstrideB, idesc, 1);
+            for (uint32_t kk = 0; kk < nk; kk++) mma1(d, ahi + kk * kstrideA, blo + kk * kstrideB, idesc, 1);
             if (h + 1 == nh) tc_commit(&empty[slot_lo]);
             tc_commit(&tfull[buf]);
           }
@@ -1394,8 +1464,8 @@ namespace {
 
 // shared memory: Alo + the B ring (Ahi lives in tensor memory)
 constexpr size_t kSmemLimit = 227 * 1024;
-size_t tc_smem256(uint32_t ks, int nhalf) {   // A (hi, lo) of every half + three half-stage slots + barriers + exchange
-  return 1024 + (size_t)nhalf * 2 * ks * 4096 + 3 * (size_t)ks * 8192 + 256 + 2 * 2 * 128 * 5 * sizeof(float);
+size_t tc_smem256(uint32_t ks, int nhalf, int nslot = 3) {   // A (hi, lo) of every half + half-stage slots + barriers + exchange
+  return 1024 + (size_t)nhalf * 2 * ks * 4096 + (size_t)nslot * ks * 8192 + 256 + 2 * 2 * 128 * 5 * sizeof(float);
 }
 size_t tc_smem(uint32_t stage_bytes, int nhalf, int nstage, int a_smem) {   // A of every half + the B ring + barriers
   return 1024 + (size_t)nhalf * (stage_bytes / 2) * (a_smem == 1 ? 2 : 1) + (size_t)nstage * stage_bytes + 256 +
@@ -1408,8 +1478,9 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
                             uint32_t* d_argmin) {
   using namespace sgmm_tc;
   if (!c->tc_ok) SGMM_FAIL(c, "tensor-core scorer not available for this model shape");
-  const uint32_t KP = c->tc_KP, ks = c->tc_ksteps;
   const bool wide = c->tc_tile_rows == 256;   // N = 256 kernel (B image built for it by sgmm_set_model)
+  const bool f16 = wide && c->tc_f16_ok && c->tc_f16 != 0;   // fp16 hi / lo operands: 16 terms per k-step
+  const uint32_t ks = f16 ? c->tc_ks16 : c->tc_ksteps, KP = f16 ? 8 * ks : c->tc_KP;   // KP: 4-byte words per A row
   // two frame halves per CTA when their Ahi operands (KP columns each) fit the 128 TMEM columns set aside
   // (wide kernel: when both halves' A parts fit shared memory next to the ring)
   const int nhalf = wide ? ((c->tc_halves == 1 || tc_smem256(ks, 2) > kSmemLimit) ? 1 : 2)
@@ -1420,7 +1491,11 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   if (a_smem == 1 && tc_smem(stage_bytes, nhalf, 2, 1) > kSmemLimit) a_smem = 0;
   int nstage = 1;
   while (nstage < sgmm_tc::kMaxStage && tc_smem(stage_bytes, nhalf, nstage + 1, a_smem) <= kSmemLimit) nstage++;
-  if (wide) nstage = 3;
+  if (wide) {
+    nstage = 3;
+    while (nstage < sgmm_tc::kMaxStage && tc_smem256(ks, nhalf, nstage + 1) <= kSmemLimit) nstage++;
+    if (!f16) nstage = 3;   // (the tf32 form was tuned with three slots)
+  }
   const uint32_t rows_per_task = 128u * nhalf;
   // Work is cut into frame ranges.  Normally there is one; while a chunked feature upload is in flight
   // (option "async_upload") there is one per chunk, each launched behind that chunk's copy event, so that the
@@ -1434,7 +1509,8 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     ranges.push_back({c->n_frames, -1});
   }
   c->feat_pending = 0;
-  const bool need_prep = !c->tc_A_valid;
+  const bool need_prep = !c->tc_A_valid || c->tc_A_form != (f16 ? 1 : 0);
+  c->tc_A_form = f16 ? 1 : 0;
   if (need_prep) {
     SGMM_CHECK(c, c->d_Ahi.reserve((size_t)c->n_frames * KP));
     SGMM_CHECK(c, c->d_Alo.reserve((size_t)c->n_frames * KP));
@@ -1458,6 +1534,10 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.Ahi = c->d_Ahi.p; p.Alo = c->d_Alo.p; p.n_frames = c->n_frames;
   p.Bimg = c->d_Bimg.p; p.tile_first = c->d_tile_first.p; p.tile_info = c->d_tile_info.p;
   p.xnorm = c->d_xnorm.p; p.sguard = c->d_sguard_tc.p; p.eps = c->tc_eps;
+  if (f16) {
+    p.Bimg = reinterpret_cast<const float*>(c->d_Bimg16.p); p.tile_info = c->d_tile_info16.p;
+    p.sguard = c->d_sguard16.p; p.eps = c->tc_eps16;
+  }
   p.n_tasks = n_tasks;
   p.tasks = nhalf == 2 ? c->d_tasks256.p : c->d_tasks128.p;
   p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
@@ -1466,7 +1546,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.pack_colmap = c->d_pack_colmap.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
-  const size_t smem = wide ? tc_smem256(ks, nhalf) : tc_smem(stage_bytes, nhalf, nstage, a_smem);
+  const size_t smem = wide ? tc_smem256(ks, nhalf, nstage) : tc_smem(stage_bytes, nhalf, nstage, a_smem);
   RefineParams r{};
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
   r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;
@@ -1516,9 +1596,15 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     if (rg.ev >= 0) SGMM_CHECK(c, cudaStreamWaitEvent(st, c->feat_ev[rg.ev], 0));
     if (need_prep && rg.f_end > f_prev) {
       const uint64_t nf = rg.f_end - f_prev;
-      k_tc_prep<<<(unsigned)((nf + 7) / 8), 256, 0, st>>>(c->d_x.p + f_prev * c->dim, nf, c->dim, c->tc_full, KP,
-                                                                c->d_Ahi.p + f_prev * KP, c->d_Alo.p + f_prev * KP,
-                                                                c->d_xnorm.p + f_prev);
+      if (f16)
+        k_tc_prep16<<<(unsigned)((nf + 7) / 8), 256, 0, st>>>(c->d_x.p + f_prev * c->dim, nf, c->dim, 2 * KP, 0.5f / c->tc_eps16,
+                                                                    reinterpret_cast<__half*>(c->d_Ahi.p + f_prev * KP),
+                                                                    reinterpret_cast<__half*>(c->d_Alo.p + f_prev * KP),
+                                                                    c->d_xnorm.p + f_prev);
+      else
+        k_tc_prep<<<(unsigned)((nf + 7) / 8), 256, 0, st>>>(c->d_x.p + f_prev * c->dim, nf, c->dim, c->tc_full, KP,
+                                                                  c->d_Ahi.p + f_prev * KP, c->d_Alo.p + f_prev * KP,
+                                                                  c->d_xnorm.p + f_prev);
       SGMM_LAUNCH_CHECK(c);
     }
     f_prev = rg.f_end;
@@ -1527,12 +1613,18 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     if (g_end > g_prev) {
       const unsigned grid = (unsigned)(g_end - g_prev);
       p.tasks = dense ? nullptr : gemm_tasks + g_prev;
-      if (wide && ks == 5) {
-        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_tc_gemm256<5><<<grid, 576, smem, st>>>(p);
+      if (f16 && ks == 3) {          // d = 32..46 pooled, fp16 operands
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm256<3, true><<<grid, 576, smem, st>>>(p);
+      } else if (f16) {
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm256<0, true><<<grid, 576, smem, st>>>(p);
+      } else if (wide && ks == 5) {
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<5, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm256<5, false><<<grid, 576, smem, st>>>(p);
       } else if (wide) {
-        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_tc_gemm256<0><<<grid, 576, smem, st>>>(p);
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm256<0, false><<<grid, 576, smem, st>>>(p);
       } else if (ks == 5) {          // d = 33 pooled (BASELINE configs 2-4)
         SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_tc_gemm<5><<<grid, 576, smem, st>>>(p);

@@ -1,5 +1,6 @@
 // extern "C" entry points of libsietill_b200.so (declared in include/sietill_b200.h).
 // Host-side glue only: buffer management, table packing (K5), launch ordering, copies, NCCL.
+#include <cuda_fp16.h>
 #include <dlfcn.h>
 
 #include <algorithm>
@@ -88,7 +89,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_norm.release(); c->d_logw.release(); c->d_state_off.release(); c->d_x.release();
   c->d_frame_off.release(); c->d_E_off.release(); c->d_aut.release(); c->d_aut_off.release();
   c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
-  c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_mu32T.release(); c->d_h32.release(); c->d_c32.release();
+  c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_mu32T.release(); c->d_Bimg16.release(); c->d_tile_info16.release(); c->d_sguard16.release(); c->d_h32.release(); c->d_c32.release();
   c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release(); c->d_tasks256.release(); c->d_Amin.release(); c->d_fcol.release();
   c->d_Bimg.release(); c->d_tile_first.release(); c->d_tile_info.release(); c->d_Ahi.release(); c->d_Alo.release();
   c->d_xnorm.release(); c->d_sguard_tc.release(); c->d_col_off.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
@@ -111,6 +112,108 @@ void sgmm_destroy(sgmm_ctx* c) {
 }
 
 // K5: pack the f64 parameter tables dim-pair-major (see k_score.cu).
+// fp16 form of the tensor-core operands (pooled models, 256-column tiles; k_tc_gemm256<KS, true>).  B row of density
+// j of state s: t_s * [ g_0..g_{d-1} | c | 0.. ], t_s = the power of two that brings the state's largest |entry| into
+// [2^13, 2^14), every entry split into fp16 hi + fp16 lo.  K = d + 1 takes ceil((d + 1) / 16) k-steps of 16 halves
+// (3 at d = 33, against 5 tf32 k-steps of 8) at the same cycles per MMA.  Per-state guard constants, in the slots
+// the epilogue multiplies with k_tc_prep16's {||s x||, s}: {max ||t g|| + flush terms, max |t c| + flush, 0}.
+static int build_f16_image(sgmm_ctx* c, bool enable, uint32_t dim, uint32_t n_states, const uint32_t* state_off,
+                           const double* mean, const double* inv_var, const double* norm, const double* log_weight,
+                           const std::vector<uint32_t>& col_off, const std::vector<uint32_t>& tile_first) {
+  c->tc_f16_ok = false;
+  if (!enable) return 0;
+  const uint32_t TR = 256, K = dim + 1, ks = (K + 15) / 16, KH = 16 * ks;
+  // error model of one split dot product against |a|.|b| (cf. tc_eps): 2^-22 per operand split, 2^-22 for the dropped
+  // lo.lo term; fp32 accumulation of 3 * 16 * ksteps products, assumed to truncate (2^-23 each)
+  const float eps = 3.f * 2.384185791015625e-07f + 3.f * 16.f * (float)ks * 1.1920928955078125e-07f;
+  const double inv2eps = 1.0 / (2.0 * (double)eps);
+  const uint32_t Dpad = col_off[n_states];
+  std::vector<__half> Bhi((size_t)Dpad * KH, __float2half(0.f)), Blo((size_t)Dpad * KH, __float2half(0.f));
+  std::vector<float4> sg(n_states, make_float4(0.f, 0.f, 0.f, 0.f));
+  std::vector<double> row(K);
+  for (uint32_t s = 0; s < n_states; s++) {
+    const uint32_t nreal = state_off[s + 1] - state_off[s];
+    double bmax = 0.0;
+    for (uint32_t j = state_off[s]; j < state_off[s + 1]; j++) {
+      double cc = norm[j] - log_weight[j];
+      for (uint32_t i = 0; i < dim; i++) {
+        const double mu = mean[(size_t)j * dim + i], iv = inv_var[(size_t)j * dim + i];
+        bmax = std::max(bmax, std::fabs(iv * mu));
+        cc += 0.5 * iv * mu * mu;
+      }
+      bmax = std::max(bmax, std::fabs(cc));
+    }
+    if (!(bmax < 1e300)) return 0;                       // non-finite model entries: keep the tf32 form
+    int e = 0;
+    std::frexp(std::max(bmax, 1e-300), &e);              // bmax = m 2^e, m in [0.5, 1)
+    const double ts = std::ldexp(1.0, 14 - e);           // bmax * ts in [2^13, 2^14)
+    double Gmax = 0.0, cabs = 0.0, flg = 0.0, flc = 0.0;
+    for (uint32_t q = 0; q < col_off[s + 1] - col_off[s]; q++) {
+      const size_t r = col_off[s] + q;
+      std::fill(row.begin(), row.end(), 0.0);
+      if (q >= nreal) {
+        row[dim] = 60000.0;                              // never-winning dummy (a certified dummy is rescanned)
+      } else {
+        const uint32_t j = state_off[s] + q;
+        double cc = norm[j] - log_weight[j];
+        for (uint32_t i = 0; i < dim; i++) {
+          const double mu = mean[(size_t)j * dim + i], iv = inv_var[(size_t)j * dim + i];
+          row[i] = -iv * mu * ts;
+          cc += 0.5 * iv * mu * mu;
+        }
+        row[dim] = cc * ts;
+      }
+      double G = 0.0, flrow = 0.0;
+      for (uint32_t k = 0; k < K; k++) {
+        const __half hi = __float2half_rn((float)row[k]);
+        const double rem = row[k] - (double)__half2float(hi);
+        const __half lo = __float2half_rn((float)rem);
+        Bhi[r * KH + k] = hi; Blo[r * KH + k] = lo;
+        double fl = 0.0;                                  // subnormal parts: see k_tc_prep16
+        if (rem != 0.0 && std::fabs(rem) < 6.103515625e-05) fl += std::max(std::fabs(rem), 2.98023223876953125e-08);
+        if (row[k] != 0.0 && std::fabs(row[k]) < 6.103515625e-05) fl += std::fabs(row[k]);
+        if (q < nreal) {
+          if (k < dim) { G += row[k] * row[k]; flrow = std::max(flrow, fl); }
+          else { cabs = std::max(cabs, std::fabs(row[k])); flc = std::max(flc, fl); }
+        }
+      }
+      if (q < nreal) { Gmax = std::max(Gmax, std::sqrt(G)); flg = std::max(flg, flrow); }
+    }
+    // a flushed / rounded B entry b_i errs by fl_i |a_i| <= fl_i ||a||: fold max_i fl_i * sqrt(d) / (2 eps) into the norm
+    sg[s] = make_float4((float)((Gmax + flg * std::sqrt((double)dim) * inv2eps) * 1.0001),
+                        (float)((cabs + flc * inv2eps) * 1.0001), 0.f, 0.f);
+  }
+  std::vector<uint2> tile_info;
+  std::vector<__half> img;
+  for (uint32_t s = 0; s < n_states; s++) {
+    const uint32_t nc = col_off[s + 1] - col_off[s];
+    for (uint32_t n0 = 0; n0 < nc; n0 += TR) {
+      const uint32_t N = std::min(TR, nc - n0);
+      const size_t off = img.size();
+      tile_info.push_back(make_uint2((uint32_t)(off / 8), N));     // 16-byte units
+      img.resize(off + (size_t)2 * ks * TR * 16, __float2half(0.f));
+      for (int op = 0; op < 2; op++) {
+        const std::vector<__half>& B = op ? Blo : Bhi;
+        __half* base = img.data() + off + (size_t)op * ks * TR * 16;
+        for (uint32_t kk = 0; kk < ks; kk++)
+          for (uint32_t r = 0; r < N; r++)
+            for (uint32_t e = 0; e < 16; e++) {
+              const uint32_t lin = kk * TR * 32 + r * 32 + e * 2;
+              const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
+              base[phys / 2] = B[(size_t)(col_off[s] + n0 + r) * KH + kk * 16 + e];
+            }
+      }
+    }
+    if (tile_info.size() != tile_first[s + 1]) { c->err = "f16 image: tile count differs from the tf32 image"; return 1; }
+  }
+  if (upload(c, c->d_Bimg16, img.data(), img.size()) || upload(c, c->d_tile_info16, tile_info.data(), tile_info.size()) ||
+      upload(c, c->d_sguard16, sg.data(), sg.size()))
+    return 1;
+  if (cudaStreamSynchronize(c->stream) != cudaSuccess) { c->err = "f16 image upload failed"; return 1; }
+  c->tc_ks16 = ks; c->tc_eps16 = eps; c->tc_f16_ok = true;
+  return 0;
+}
+
 int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t* state_off,
                    const double* mean, const double* inv_var, const double* norm, const double* log_weight) {
   if (!c) return 1;
@@ -303,6 +406,9 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
       // dropped lo.lo term another 2^-22; fp32 accumulation of 3 * 8 * ksteps terms, assumed to truncate
       // (2^-23 each).  The guard doubles this (two candidates).
       c->tc_eps = 3.f * 2.384185791015625e-07f + 3.f * 8.f * (float)c->tc_ksteps * 1.1920928955078125e-07f;
+      if (build_f16_image(c, pooled && TR == 256 && c->tc_f16 != 0, dim, n_states, state_off, mean, inv_var, norm, log_weight,
+                          col_off, tile_first))
+        return 1;
     }
     c->tc_A_valid = false;
   }
@@ -655,6 +761,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_debug")) { c->tc_debug = (int)value; return 0; }
   if (!strcmp(key, "async_upload")) { c->async_upload = value != 0; return 0; }
   if (!strcmp(key, "tc_wide")) { c->tc_wide = (int)value; return 0; }   // takes effect at the next sgmm_set_model
+  if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
   if (!strcmp(key, "tc_pack")) { c->tc_pack = value != 0; return 0; }   // takes effect at the next sgmm_set_corpus

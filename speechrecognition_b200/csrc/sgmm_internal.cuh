@@ -1,5 +1,6 @@
 // Internal declarations shared by the .cu files of libsietill_b200.so (sm_100a only).
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
@@ -123,6 +124,15 @@ struct sgmm_ctx {
   // state-major refinement (k_tc_refine_sm): work items (block of utterances, state) and, per item, the
   // utterances of the block that visit the state
   int tc_refine = 0;               // option "tc_refine": 0 automatic, 1 frame-major kernel, 2 state-major kernel
+  // fp16 operand form of the wide GEMM (build_f16_image / k_tc_prep16)
+  int tc_f16 = -1;                 // option "tc_f16": -1 / 1 use it when available, 0 never
+  bool tc_f16_ok = false;
+  uint32_t tc_ks16 = 0;
+  float tc_eps16 = 0.f;
+  DevBuf<__half> d_Bimg16;
+  DevBuf<uint2> d_tile_info16;
+  DevBuf<float4> d_sguard16;
+  int tc_A_form = 0;               // which form the resident A rows (d_Ahi / d_Alo / d_xnorm) are in: 0 tf32, 1 fp16
   int tc_rescan = 0;               // option "tc_rescan": 0 two-stage (f32 prefilter, f64 candidates), 1 full f64 scan
   size_t n_sm_items = 0;
   DevBuf<uint4> d_sm_items;        // {state, first entry, entries, cells}

@@ -318,6 +318,52 @@ def test_tensor_core_scorer_exact(dim, nd, pooling, halves):
     ctx.close()
 
 
+@pytest.mark.parametrize("scale", [1.0, 3e-4, 700.0])
+def test_fp16_operand_form_matches_tf32_and_oracle(scale):
+    """The wide GEMM's fp16 hi/lo operand form (option tc_f16; rows and states scaled by powers of two) against the
+    tf32 form and the oracle: dense scores / argmins and alignments bit-identical, for features far below and far
+    above unit scale, a frame with a huge feature (rescanned in f64) and planted near-duplicate densities."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(31)
+    dim, nd = 33, 200
+    lex = synth.Lexicon()
+    t = synth.random_model(rng, dim, lex.num_states, nd, "mixture")
+    t["means"] *= scale                             # the model lives at the features' scale
+    t["vars"] *= scale ** 2
+    t["vars_inv"] /= scale ** 2
+    t["norm"] += dim * np.log(scale)
+    means = t["means"].reshape(-1, dim)
+    for k, rel in ((1, 0.0), (3, 1e-9), (5, 1e-6), (7, 1e-4)):     # near-duplicates of density 0 of state 0
+        means[k] = means[0] * (1.0 + rel)
+    corp = synth.make_corpus(rng, lex, t, dim, 6)
+    x = corp["x"].copy()
+    x[17, 4] = 3.0e6 * scale                        # beyond the fp16 row scaling: the frame becomes NaN -> rescanned
+    tdp = (3.0, 0.0, 30.0)
+    O = Oracle(dim, lex.num_states, "mixture", True, tdp, lex.silence_state)
+    O.load_tables(t)
+    n = 400
+    want_s, want_a = O.min_score(x[:n])
+    want_states, want_costs = O.align_batch(x, corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, t); ctx.set_features(x)
+    ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"]); ctx.set_tdp(*tdp, lex.silence_state)
+    ctx.set_option("scorer", 3)
+    fbs = []
+    for f16 in (1, 0, 1):
+        ctx.set_option("tc_f16", f16)
+        ctx.get_counter("fallbacks")
+        got_s, got_a = ctx.score_all(0, n)
+        fbs.append(ctx.get_counter("fallbacks"))
+        assert np.array_equal(got_a, want_a), f16
+        assert np.array_equal(got_s, want_s), f16
+        got, costs = ctx.align()
+        assert np.array_equal(got["state"].astype(np.uint32), want_states), f16
+        assert np.array_equal(costs, want_costs), f16
+    assert fbs[0] == fbs[2] and fbs[0] < 0.1 * want_s.size, fbs      # the fp16 form certifies nearly everything, too
+    ctx.close()
+
+
 @pytest.mark.parametrize("dim", [33, 32, 25])
 def test_state_major_refinement_short_utterances(dim):
     """Utterances of 3..40 frames: a warp's 32 cells of one state then span several utterances (bulk-copy staging

@@ -17,7 +17,8 @@ res = {}
 modes = [int(a) for a in sys.argv[2:]] or [1, 2, 1, 2]
 for mode in modes:
     ctx.set_option("tc_refine", mode % 10)
-    ctx.set_option("tc_rescan", mode // 10)
+    ctx.set_option("tc_rescan", (mode // 10) % 10)
+    ctx.set_option("tc_f16", 0 if mode >= 100 else 1)
     ms = []
     for it in range(6):
         ali, costs = ctx.align()
