@@ -37,35 +37,59 @@ __global__ void __launch_bounds__(kSortWarps * 32) k_sort_hist(const uint32_t* _
   }
 }
 
-// Exclusive prefix sum of n u32 values by ONE block (n is at most a few hundred thousand here).
+// Exclusive prefix sum of n u32 values by ONE block (n is at most a few hundred thousand here): tiles of 4096
+// values, four consecutive ones per thread (coalesced 16-byte accesses), warp-shuffle scans, a running carry.
 // mode 0: v = in[i];  mode 1: v = ceil(in[i] / SGMM_RED_BLOCK).  out has n + 1 entries (out[n] = total).
 __global__ void __launch_bounds__(1024) k_excl_scan(const uint32_t* in, uint32_t* out,  // may alias
-                                                   
                                                     uint32_t n, int mode) {
-  __shared__ uint32_t sums[1024];
-  const uint32_t tid = threadIdx.x;
-  const uint32_t per = (n + 1023) / 1024;
-  const uint32_t beg = min(n, tid * per), end = min(n, beg + per);
-  uint32_t acc = 0;
-  for (uint32_t i = beg; i < end; i++) {
-    const uint32_t v = in[i];
-    acc += mode ? (v + SGMM_RED_BLOCK - 1) / SGMM_RED_BLOCK : v;
-  }
-  sums[tid] = acc;
-  __syncthreads();
-  for (uint32_t off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan
-    const uint32_t v = tid >= off ? sums[tid - off] : 0;
+  __shared__ uint32_t wexcl[32];     // exclusive scan of the warp totals of the current tile
+  __shared__ uint32_t tile_total;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  uint32_t carry = 0;
+  for (uint32_t base = 0; base < n; base += 4096) {
+    const uint32_t i = base + tid * 4;
+    uint32_t v[4] = {0, 0, 0, 0};
+    if (i + 3 < n) {
+      const uint4 q = *reinterpret_cast<const uint4*>(in + i);
+      v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+    } else {
+      for (uint32_t j = 0; j < 4; j++) if (i + j < n) v[j] = in[i + j];
+    }
+    if (mode)
+      for (uint32_t j = 0; j < 4; j++) v[j] = (v[j] + SGMM_RED_BLOCK - 1) / SGMM_RED_BLOCK;
+    const uint32_t t = v[0] + v[1] + v[2] + v[3];
+    uint32_t inc = t;                                         // inclusive scan of the thread totals inside the warp
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+      if ((int)lane >= o) inc += u;
+    }
+    if (lane == 31) wexcl[warp] = inc;                        // warp total
     __syncthreads();
-    sums[tid] += v;
+    if (warp == 0) {
+      const uint32_t w = wexcl[lane];
+      uint32_t winc = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, winc, o);
+        if ((int)lane >= o) winc += u;
+      }
+      wexcl[lane] = winc - w;
+      if (lane == 31) tile_total = winc;
+    }
     __syncthreads();
+    uint32_t run = carry + wexcl[warp] + (inc - t);
+    if (i + 3 < n) {
+      uint4 q;
+      q.x = run; run += v[0]; q.y = run; run += v[1]; q.z = run; run += v[2]; q.w = run;
+      *reinterpret_cast<uint4*>(out + i) = q;
+    } else {
+      for (uint32_t j = 0; j < 4; j++) if (i + j < n) { out[i + j] = run; run += v[j]; }
+    }
+    carry += tile_total;
+    __syncthreads();                                          // wexcl / tile_total are rewritten by the next tile
   }
-  uint32_t run = tid ? sums[tid - 1] : 0;
-  for (uint32_t i = beg; i < end; i++) {
-    const uint32_t v = in[i];
-    out[i] = run;
-    run += mode ? (v + SGMM_RED_BLOCK - 1) / SGMM_RED_BLOCK : v;
-  }
-  if (tid == 1023) out[n] = sums[1023];
+  if (tid == 0) out[n] = carry;
 }
 
 __global__ void __launch_bounds__(kSortWarps * 32) k_sort_scatter(const uint32_t* __restrict__ keys_in,
