@@ -16,8 +16,9 @@
 //     cp.async.bulk;
 //   * the epilogue is two passes over the accumulator tile kept in TMEM: pass 1 the plain minimum (FMNMX, ALU
 //     pipe), pass 2 counts and locates every column within the certified error bound of it with saturating FMAs
-//     (FMA pipe): c = sat((min + G - v) * 2/G), acc += c, idx += c * column.  acc == 1 exactly <=> the minimum is
-//     the only candidate, and idx is then its column.  FSETP/FSEL-based top-2 tracking measured 2x slower.
+//     (FMA pipe): c = sat((min + G - v) * 2^100) in {0, 1}, sum += c * (1 + column / 4096) (tc_count16).  count == 1
+//     exactly <=> the minimum is the only candidate below min + G, and the fraction is then its column.
+//     FSETP/FSEL-based top-2 tracking measured 2x slower.
 //
 // Like the FFMA scorer this kernel is a FILTER: k_tc_refine evaluates the certified winner's score in f64 in
 // the reference's exact operation order (Mixtures.cpp:645-713) and queues uncertified cells for a full f64
@@ -169,6 +170,26 @@ __device__ __forceinline__ void tc_ld_wait(uint32_t (&r)[16]) {
                  "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
                :
                : "memory");
+}
+
+// Pass 2 of the epilogue for one block of 16 accumulator columns.  c = sat((thr - v) * 2^100) is EXACTLY 1 for
+// v < thr and EXACTLY 0 for v >= thr (the products are exact power-of-two scalings; for 1e-20 < |thr| < 1e8 two
+// different floats around thr differ by >= 2^-91, so a positive difference saturates; the caller guards that
+// range).  One FMA per column then adds c * (1 + e / 4096): the block sum is count + (sum of the selected
+// columns' offsets) / 4096, exact in f32 (count <= 16, offsets sum <= 120).  2 FMA-pipe instructions per
+// column instead of 3 (saturating FMA, add, FMA).
+__device__ __forceinline__ void tc_count16(const uint32_t (&r)[16], float nbig, float T, float cc, float& acc,
+                                           float& idx) {
+  float a4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int e = 0; e < 16; e++) {
+    const float c = __saturatef(fmaf(__uint_as_float(r[e]), nbig, T));
+    a4[e & 3] = fmaf(c, 1.0f + (float)e * (1.0f / 4096.0f), a4[e & 3]);
+  }
+  const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]);
+  const float cnt = floorf(ab);
+  acc += cnt;
+  idx += fmaf(cnt, cc, (ab - cnt) * 4096.0f);
 }
 
 // Shared-memory matrix descriptor, K-major, SWIZZLE_32B.  One k-step (8 tf32 = 32 bytes) of a 128-row operand
@@ -569,41 +590,21 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
               tc_ld_wait(ra);
             }
             m = fminf(fminf(mm[0], mm[1]), fminf(mm[2], mm[3]));
-            // pass 2: every column within G of the minimum contributes c in (0, 1]; the minimum itself exactly 1
+            // pass 2: count and locate every column below min + G (the minimum itself always counts)
             G = Gs + 4e-6f * fabsf(m);
-            const float invg = __fdividef(2.f, G), t0 = (m + G) * invg, ninvg = -invg;
+            const float thr = m + G, nbig = -0x1p100f, T = thr * 0x1p100f;
+            const bool thr_ok = fabsf(thr) > 1e-20f && fabsf(thr) < 1e8f;   // else c may be fractional: uncertain
             tc_ld16_nowait(tcol + c_lo, ra);
             tc_ld_wait(ra);
             for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
               if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
-              {
-                float a4[4] = {0.f, 0.f, 0.f, 0.f}, i4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                for (int e = 0; e < 16; e++) {
-                  const float c = __saturatef(fmaf(__uint_as_float(ra[e]), ninvg, t0));
-                  a4[e & 3] += c;
-                  i4[e & 3] = fmaf(c, (float)e, i4[e & 3]);
-                }
-                const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]), ib = (i4[0] + i4[1]) + (i4[2] + i4[3]);
-                acc += ab;
-                idx += fmaf(ab, (float)cc, ib);
-              }
+              tc_count16(ra, nbig, T, (float)cc, acc, idx);
               tc_ld_wait(rb);
               if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
-              if (cc + 16 < c_hi) {
-                float a4[4] = {0.f, 0.f, 0.f, 0.f}, i4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                for (int e = 0; e < 16; e++) {
-                  const float c = __saturatef(fmaf(__uint_as_float(rb[e]), ninvg, t0));
-                  a4[e & 3] += c;
-                  i4[e & 3] = fmaf(c, (float)e, i4[e & 3]);
-                }
-                const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]), ib = (i4[0] + i4[1]) + (i4[2] + i4[3]);
-                acc += ab;
-                idx += fmaf(ab, (float)(cc + 16), ib);
-              }
+              if (cc + 16 < c_hi) tc_count16(rb, nbig, T, (float)(cc + 16), acc, idx);
               tc_ld_wait(ra);
             }
+            if (!thr_ok) acc = 2.f;
           }
           tc_fence_before();
           __syncwarp();
@@ -885,41 +886,21 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
               tc_ld_wait(ra);
             }
             m = fminf(fminf(mm[0], mm[1]), fminf(mm[2], mm[3]));
-            // pass 2: every column within G of the minimum contributes c in (0, 1]; the minimum itself exactly 1
+            // pass 2: count and locate every column below min + G (the minimum itself always counts)
             G = Gs + 4e-6f * fabsf(m);
-            const float invg = __fdividef(2.f, G), t0 = (m + G) * invg, ninvg = -invg;
+            const float thr = m + G, nbig = -0x1p100f, T = thr * 0x1p100f;
+            const bool thr_ok = fabsf(thr) > 1e-20f && fabsf(thr) < 1e8f;   // else c may be fractional: uncertain
             tc_ld16_nowait(tcol + c_lo, ra);
             tc_ld_wait(ra);
             for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
               if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
-              {
-                float a4[4] = {0.f, 0.f, 0.f, 0.f}, i4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                for (int e = 0; e < 16; e++) {
-                  const float c = __saturatef(fmaf(__uint_as_float(ra[e]), ninvg, t0));
-                  a4[e & 3] += c;
-                  i4[e & 3] = fmaf(c, (float)e, i4[e & 3]);
-                }
-                const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]), ib = (i4[0] + i4[1]) + (i4[2] + i4[3]);
-                acc += ab;
-                idx += fmaf(ab, (float)cc, ib);
-              }
+              tc_count16(ra, nbig, T, (float)cc, acc, idx);
               tc_ld_wait(rb);
               if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
-              if (cc + 16 < c_hi) {
-                float a4[4] = {0.f, 0.f, 0.f, 0.f}, i4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                for (int e = 0; e < 16; e++) {
-                  const float c = __saturatef(fmaf(__uint_as_float(rb[e]), ninvg, t0));
-                  a4[e & 3] += c;
-                  i4[e & 3] = fmaf(c, (float)e, i4[e & 3]);
-                }
-                const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]), ib = (i4[0] + i4[1]) + (i4[2] + i4[3]);
-                acc += ab;
-                idx += fmaf(ab, (float)(cc + 16), ib);
-              }
+              if (cc + 16 < c_hi) tc_count16(rb, nbig, T, (float)(cc + 16), acc, idx);
               tc_ld_wait(ra);
             }
+            if (!thr_ok) acc = 2.f;
           }
           tc_fence_before();
           __syncwarp();

@@ -792,6 +792,13 @@ int sgmm_get_counter(sgmm_ctx* c, const char* key, int64_t* value) {
     return 0;
   }
   if (!strcmp(key, "scorer")) { *value = sgmm_effective_scorer(c); return 0; }
+  // operand form the wide GEMM runs with (k_score_tc.cu): 0 tf32 hi/lo (3xTF32), 1 fp16 hi/lo (kind::f16);
+  // k-steps per tile of that form
+  if (!strcmp(key, "tc_form")) { *value = (c->tc_ok && c->tc_tile_rows == 256 && c->tc_f16_ok && c->tc_f16 != 0) ? 1 : 0; return 0; }
+  if (!strcmp(key, "tc_ksteps")) {
+    *value = (c->tc_ok && c->tc_tile_rows == 256 && c->tc_f16_ok && c->tc_f16 != 0) ? c->tc_ks16 : c->tc_ksteps;
+    return 0;
+  }
   if (!strncmp(key, "tc_prof", 7)) {   // cycle counters of the instrumented GEMM (option tc_debug & 32); read-and-clear
     const int i = atoi(key + 7);
     if (i < 1 || i > 15 || !c->d_fallbacks.p) SGMM_FAIL(c, "get_counter: tc_prof index out of range");
