@@ -235,43 +235,49 @@ __global__ void k_score_final(const double* __restrict__ part, int n, double* __
 
 }  // namespace
 
-// Sorts frames by c->d_fdens, reduces into c->d_acc = [count | sum_x | sum_xx | score_sum].
-int sgmm_launch_accumulate(sgmm_ctx* c) {
+// Stable sort of the frame ids 0 .. n_frames-1 by keys[f] in [0, n_keys): *sorted receives the permutation (device).
+int sgmm_sort_frames(sgmm_ctx* c, const uint32_t* keys, uint32_t n_keys, const uint32_t** sorted) {
   const uint64_t n = c->n_frames;
-  const uint32_t D = c->Dtot, dim = c->dim;
   if (n >= (1ull << 32)) SGMM_FAIL(c, "accumulate: more than 2^32 frames per context");
   const uint32_t n_chunks = (uint32_t)((n + SGMM_SORT_CHUNK - 1) / SGMM_SORT_CHUNK);
   SGMM_CHECK(c, c->d_keys[0].reserve(n)); SGMM_CHECK(c, c->d_keys[1].reserve(n));
   SGMM_CHECK(c, c->d_vals[0].reserve(n)); SGMM_CHECK(c, c->d_vals[1].reserve(n));
   SGMM_CHECK(c, c->d_hist.reserve((size_t)256 * n_chunks + 1));
+  int bits = 1;
+  while ((1ull << bits) < (uint64_t)n_keys) bits++;
+  const int passes = (bits + 7) / 8;
+  const uint32_t sort_grid = (n_chunks + kSortWarps - 1) / kSortWarps;
+  const uint32_t* keys_in = keys;
+  const uint32_t* vals_in = nullptr;
+  int cur = 0;
+  StageTimer st(c, SGMM_T_SORT);
+  for (int pass = 0; pass < passes && n > 0; pass++) {
+    const int shift = 8 * pass;
+    k_sort_hist<<<sort_grid, kSortWarps * 32, 0, c->stream>>>(keys_in, n, shift, n_chunks, c->d_hist.p);
+    SGMM_LAUNCH_CHECK(c);
+    k_excl_scan<<<1, 1024, 0, c->stream>>>(c->d_hist.p, c->d_hist.p, 256 * n_chunks, 0);
+    SGMM_LAUNCH_CHECK(c);
+    k_sort_scatter<<<sort_grid, kSortWarps * 32, 0, c->stream>>>(keys_in, vals_in, c->d_keys[cur].p,
+                                                                c->d_vals[cur].p, n, shift, n_chunks,
+                                                                c->d_hist.p);
+    SGMM_LAUNCH_CHECK(c);
+    keys_in = c->d_keys[cur].p;
+    vals_in = c->d_vals[cur].p;
+    cur ^= 1;
+  }
+  *sorted = vals_in;
+  return 0;
+}
+
+// Sorts frames by c->d_fdens, reduces into c->d_acc = [count | sum_x | sum_xx | score_sum].
+int sgmm_launch_accumulate(sgmm_ctx* c) {
+  const uint64_t n = c->n_frames;
+  const uint32_t D = c->Dtot, dim = c->dim;
   SGMM_CHECK(c, c->d_seg_off.reserve(D + 2)); SGMM_CHECK(c, c->d_item_off.reserve(D + 1));
   const size_t max_items = n / SGMM_RED_BLOCK + D + 1;
   SGMM_CHECK(c, c->d_partial.reserve(max_items * 2 * dim));
-
-  int bits = 1;
-  while ((1ull << bits) < (uint64_t)D + 1) bits++;   // keys are 0..D (D = dummy slot of empty mixtures)
-  const int passes = (bits + 7) / 8;
-  const uint32_t sort_grid = (n_chunks + kSortWarps - 1) / kSortWarps;
-  const uint32_t* keys_in = c->d_fdens.p;
   const uint32_t* vals_in = nullptr;
-  int cur = 0;
-  {
-    StageTimer st(c, SGMM_T_SORT);
-    for (int pass = 0; pass < passes && n > 0; pass++) {
-      const int shift = 8 * pass;
-      k_sort_hist<<<sort_grid, kSortWarps * 32, 0, c->stream>>>(keys_in, n, shift, n_chunks, c->d_hist.p);
-      SGMM_LAUNCH_CHECK(c);
-      k_excl_scan<<<1, 1024, 0, c->stream>>>(c->d_hist.p, c->d_hist.p, 256 * n_chunks, 0);
-      SGMM_LAUNCH_CHECK(c);
-      k_sort_scatter<<<sort_grid, kSortWarps * 32, 0, c->stream>>>(keys_in, vals_in, c->d_keys[cur].p,
-                                                                  c->d_vals[cur].p, n, shift, n_chunks,
-                                                                  c->d_hist.p);
-      SGMM_LAUNCH_CHECK(c);
-      keys_in = c->d_keys[cur].p;
-      vals_in = c->d_vals[cur].p;
-      cur ^= 1;
-    }
-  }
+  if (sgmm_sort_frames(c, c->d_fdens.p, D + 1, &vals_in)) return 1;   // keys are 0..D (D = dummy slot of empty mixtures)
   {
     StageTimer st(c, SGMM_T_REDUCE);
     k_excl_scan<<<1, 1024, 0, c->stream>>>(c->d_cnt_u32.p, c->d_seg_off.p, D + 1, 0);

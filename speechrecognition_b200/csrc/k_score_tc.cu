@@ -16,7 +16,7 @@
 //     cp.async.bulk;
 //   * the epilogue is two passes over the accumulator tile kept in TMEM: pass 1 the plain minimum (FMNMX, ALU
 //     pipe), pass 2 counts and locates every column within the certified error bound of it with saturating FMAs
-//     (FMA pipe): c = sat((min + G - v) * 2^100) in {0, 1}, sum += c * (1 + column / 4096) (tc_count16).  count == 1
+//     (FMA pipe): c = sat((min + G - v) * 2^100) in {0, 1}, packed sums of c * (1 + block / 4096) (TcCount).  count == 1
 //     exactly <=> the minimum is the only candidate below min + G, and the fraction is then its column.
 //     FSETP/FSEL-based top-2 tracking measured 2x slower.
 //
@@ -172,25 +172,50 @@ __device__ __forceinline__ void tc_ld_wait(uint32_t (&r)[16]) {
                : "memory");
 }
 
-// Pass 2 of the epilogue for one block of 16 accumulator columns.  c = sat((thr - v) * 2^100) is EXACTLY 1 for
-// v < thr and EXACTLY 0 for v >= thr (the products are exact power-of-two scalings; for 1e-20 < |thr| < 1e8 two
-// different floats around thr differ by >= 2^-91, so a positive difference saturates; the caller guards that
-// range).  One FMA per column then adds c * (1 + e / 4096): the block sum is count + (sum of the selected
-// columns' offsets) / 4096, exact in f32 (count <= 16, offsets sum <= 120).  2 FMA-pipe instructions per
-// column instead of 3 (saturating FMA, add, FMA).
-__device__ __forceinline__ void tc_count16(const uint32_t (&r)[16], float nbig, float T, float cc, float& acc,
-                                           float& idx) {
-  float a4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-  for (int e = 0; e < 16; e++) {
-    const float c = __saturatef(fmaf(__uint_as_float(r[e]), nbig, T));
-    a4[e & 3] = fmaf(c, 1.0f + (float)e * (1.0f / 4096.0f), a4[e & 3]);
+// Pass 2 of the epilogue: count and locate the accumulator columns below thr, 16 columns per call.
+// c = sat((thr - v) * 2^100) is EXACTLY 1 for v < thr and EXACTLY 0 for v >= thr (the products are exact
+// power-of-two scalings; for 1e-20 < |thr| < 1e8 two different floats around thr differ by >= 2^-91, so a positive
+// difference saturates; the caller guards that range).  Column e = 8 h + 2 q + l of block b adds c * W[h] to lane l
+// of the packed accumulator A[q], W[h] = 1 + (2 b + h) / 4096, with one FFMA2 (fma.rn.f32x2) per two columns:
+// 1.5 FMA-pipe instructions per column.  All sums are exact (count <= 128, 12 fraction bits).  At the end
+// sum A = count + ..., and when count == 1 the fraction names (b, h) and the one non-zero accumulator names (q, l).
+struct TcCount {
+  unsigned long long A[4], W[2];
+  __device__ __forceinline__ static unsigned long long pack(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
   }
-  const float ab = (a4[0] + a4[1]) + (a4[2] + a4[3]);
-  const float cnt = floorf(ab);
-  acc += cnt;
-  idx += fmaf(cnt, cc, (ab - cnt) * 4096.0f);
-}
+  __device__ __forceinline__ void init() {
+#pragma unroll
+    for (int q = 0; q < 4; q++) A[q] = 0ull;
+    W[0] = pack(1.0f, 1.0f);
+    W[1] = pack(1.0f + 1.0f / 4096.0f, 1.0f + 1.0f / 4096.0f);
+  }
+  __device__ __forceinline__ void block16(const uint32_t (&r)[16], float nbig, float T) {
+#pragma unroll
+    for (int pq = 0; pq < 8; pq++) {
+      const float c0 = __saturatef(fmaf(__uint_as_float(r[2 * pq]), nbig, T));
+      const float c1 = __saturatef(fmaf(__uint_as_float(r[2 * pq + 1]), nbig, T));
+      asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(A[pq & 3]) : "l"(pack(c0, c1)), "l"(W[pq >> 2]));
+    }
+    const unsigned long long step = pack(2.0f / 4096.0f, 2.0f / 4096.0f);
+    asm("add.rn.f32x2 %0, %0, %1;" : "+l"(W[0]) : "l"(step));
+    asm("add.rn.f32x2 %0, %0, %1;" : "+l"(W[1]) : "l"(step));
+  }
+  // acc = number of columns below thr; idx = the column (relative to the first block) when acc == 1
+  __device__ __forceinline__ void finish(float& acc, float& idx) const {
+    float a[8];
+#pragma unroll
+    for (int q = 0; q < 4; q++) asm("mov.b64 {%0, %1}, %2;" : "=f"(a[2 * q]), "=f"(a[2 * q + 1]) : "l"(A[q]));
+    const float total = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+    float ql = a[1];
+#pragma unroll
+    for (int e = 2; e < 8; e++) ql = fmaf(a[e], (float)e, ql);
+    acc = floorf(total);
+    idx = fmaf((total - acc) * 4096.0f, 8.0f, rintf(ql));
+  }
+};
 
 // Shared-memory matrix descriptor, K-major, SWIZZLE_32B.  One k-step (8 tf32 = 32 bytes) of a 128-row operand
 // is its own 4 KB block [128 rows][32 B]: 8-row groups are 256 B apart (SBO), LBO unused.  K = 2d+1 or d+1 is
@@ -594,16 +619,20 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
             G = Gs + 4e-6f * fabsf(m);
             const float thr = m + G, nbig = -0x1p100f, T = thr * 0x1p100f;
             const bool thr_ok = fabsf(thr) > 1e-20f && fabsf(thr) < 1e8f;   // else c may be fractional: uncertain
+            TcCount cnt;
+            cnt.init();
             tc_ld16_nowait(tcol + c_lo, ra);
             tc_ld_wait(ra);
             for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
               if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
-              tc_count16(ra, nbig, T, (float)cc, acc, idx);
+              cnt.block16(ra, nbig, T);
               tc_ld_wait(rb);
               if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
-              if (cc + 16 < c_hi) tc_count16(rb, nbig, T, (float)(cc + 16), acc, idx);
+              if (cc + 16 < c_hi) cnt.block16(rb, nbig, T);
               tc_ld_wait(ra);
             }
+            cnt.finish(acc, idx);
+            idx += (float)c_lo;
             if (!thr_ok) acc = 2.f;
           }
           tc_fence_before();
@@ -890,16 +919,20 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
             G = Gs + 4e-6f * fabsf(m);
             const float thr = m + G, nbig = -0x1p100f, T = thr * 0x1p100f;
             const bool thr_ok = fabsf(thr) > 1e-20f && fabsf(thr) < 1e8f;   // else c may be fractional: uncertain
+            TcCount cnt;
+            cnt.init();
             tc_ld16_nowait(tcol + c_lo, ra);
             tc_ld_wait(ra);
             for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
               if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
-              tc_count16(ra, nbig, T, (float)cc, acc, idx);
+              cnt.block16(ra, nbig, T);
               tc_ld_wait(rb);
               if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
-              if (cc + 16 < c_hi) tc_count16(rb, nbig, T, (float)(cc + 16), acc, idx);
+              if (cc + 16 < c_hi) cnt.block16(rb, nbig, T);
               tc_ld_wait(ra);
             }
+            cnt.finish(acc, idx);
+            idx += (float)c_lo;
             if (!thr_ok) acc = 2.f;
           }
           tc_fence_before();

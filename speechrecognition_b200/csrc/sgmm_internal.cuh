@@ -151,6 +151,8 @@ struct sgmm_ctx {
   DevBuf<uint16_t> d_fcol;        // per frame: emission column of the aligned position (written by the backtrace)
   uint64_t model_version = 1, E_model_version = 0;
   bool use_cache = true;          // option "rescore_cache"
+  bool max_approx = true;         // option "max_approx": score() = min_score (1) or sum_score (0), Mixtures.cpp:737-744
+  bool E_max_approx = true;       // which of the two the resident emission matrix holds
   bool ali_has_cols = false;      // resident alignment came from sgmm_align (d_fcol valid)
   std::vector<ViterbiClass> vclasses;
   DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)
@@ -234,6 +236,12 @@ inline int sgmm_wait_features(sgmm_ctx* c) {
 int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass);
 int sgmm_launch_rescore_cached(sgmm_ctx* c);
 int sgmm_launch_accumulate(sgmm_ctx* c);
+int sgmm_sort_frames(sgmm_ctx* c, const uint32_t* keys, uint32_t n_keys, const uint32_t** sorted);
+// non-max-approx branch (k_soft.cu)
+int sgmm_launch_emission_sum(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
+                             uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin);
+int sgmm_launch_sum_aligned(sgmm_ctx* c);
+int sgmm_launch_accumulate_soft(sgmm_ctx* c);
 int sgmm_launch_score_sum(sgmm_ctx* c);
 int sgmm_nccl_allreduce(sgmm_ctx* c, double* d_buf, size_t n);
 
