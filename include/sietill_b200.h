@@ -120,8 +120,19 @@ int sgmm_set_alignment(sgmm_ctx* ctx, const sgmm_alignment_item* alignment, uint
 int sgmm_accumulate(sgmm_ctx* ctx, int first_pass, double* count, double* sum_x, double* sum_xx,
                     double* score_sum);
 
+/* The posterior-weighted branch of MixtureModel::accumulate (max_approx == false, not the first pass;
+ * Mixtures.cpp:300-357) over the resident alignment: for frame f with aligned state m,
+ * p_k = exp(-density_score(x_f, m, k)) normalised by their in-order sum (:310-324), entries below 1e-8 skipped
+ * (:336-338); count[j] += p_k, sum_x[j*dim..] += p_k * x, sum_xx[j*dim..] += (p_k * x) * x for j = state_off[m] + k.
+ * Same output layout, NULL rules and all-reduce as sgmm_accumulate.  score_sum receives
+ * sum_f sum_score(x_f, m) (Mixtures.cpp:719-728) — the normaliser is the same sum — i.e. calc_am_score's numerator
+ * for a model built with max_approx == false.  Density scores are bit-identical to the reference; exp / log are the
+ * device's (<= 1 ulp), the statistics agree to ~1e-13 relative. */
+int sgmm_accumulate_soft(sgmm_ctx* ctx, double* count, double* sum_x, double* sum_xx, double* score_sum);
+
 /* Trainer::calc_am_score's numerator alone (Training.cpp:585-612): sum over the resident alignment of
- * min_score(x_f, state_f).first with the current model (all-reduced if a communicator is attached). */
+ * score(x_f, state_f) with the current model — min_score(...).first, or sum_score when option "max_approx" is 0
+ * (all-reduced if a communicator is attached). */
 int sgmm_am_score_sum(sgmm_ctx* ctx, double* score_sum);
 
 /* Per-frame results of the last sgmm_accumulate / sgmm_am_score_sum (tests, diagnostics):
@@ -129,7 +140,11 @@ int sgmm_am_score_sum(sgmm_ctx* ctx, double* score_sum);
 int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
 
 /* ---- options / counters -------------------------------------------------------------------- */
-/* "scorer": 0 = automatic choice by model shape, 1 = exact-f64 kernel, 2 = FP32-FFMA kernel with certified
+/* "max_approx" (default 1): what FeatureScorer::score means (MixtureModel's constructor argument, Mixtures.cpp:737-744):
+ *   1 = min_score (maximum approximation), 0 = sum_score = -log sum_k exp(-density_score_k) (:719-728).  With 0,
+ *   sgmm_score_all / sgmm_align / sgmm_recognize / sgmm_am_score_sum use sum scores (exact-f64 kernel; argmin outputs
+ *   are 0).  Independent of which accumulate entry point is called, as in the reference (Training.cpp:145-149).
+ * "scorer": 0 = automatic choice by model shape, 1 = exact-f64 kernel, 2 = FP32-FFMA kernel with certified
  * f64 refinement, 3 = tcgen05 3xTF32 tensor-core GEMM with certified f64 refinement.  Every scorer returns
  * results bit-identical to the reference; the choice only moves time.
  * "rescore_cache" (default 1): sgmm_accumulate after sgmm_align with an unchanged model looks the aligned cells' scores up.

@@ -128,6 +128,13 @@ class Oracle:
                                    C.c_uint64(n), _p(scores, C.c_double), _p(argmin, C.c_uint32))
         return scores, argmin
 
+    def score(self, x):
+        """FeatureScorer::score of every (frame, state): min or sum score per self.max_approx."""
+        x = _f32(x).reshape(-1, self.dim)
+        scores = np.zeros((len(x), self.n_mix), np.float64)
+        self.L.orc_score_batch(self.h, _p(x, C.c_float), C.c_uint64(len(x)), self.max_approx, _p(scores, C.c_double))
+        return scores
+
     def am_score(self, states, x):
         states = np.ascontiguousarray(states, np.uint32)
         x = _f32(x)
@@ -270,6 +277,16 @@ class Reference:
         self.L.ref_min_score(self.h, _p(xp, C.c_float), C.c_uint64(F), _p(st, C.c_uint16),
                              C.c_uint64(len(st)), _p(scores, C.c_double), _p(argmin, C.c_uint16))
         return scores, argmin.astype(np.uint32)
+
+    def score(self, x):
+        """FeatureScorer::score of every (frame, state) (Mixtures.cpp:737-744)."""
+        F = _f32(x).reshape(-1, self.dim).shape[0]
+        xp = self._pad(x)
+        st = np.arange(self.n_mix, dtype=np.uint16)
+        scores = np.zeros((F, self.n_mix), np.float64)
+        self.L.ref_score(self.h, _p(xp, C.c_float), C.c_uint64(F), _p(st, C.c_uint16), C.c_uint64(self.n_mix),
+                         _p(scores, C.c_double))
+        return scores
 
     def am_score(self, states, x):
         st = np.ascontiguousarray(states, np.uint16)

@@ -239,6 +239,14 @@ void orc_min_score_batch(const orc_model *m, const float *x, uint64_t n_frames, 
   }
 }
 
+/* FeatureScorer::score for every (frame, state): min_score or sum_score per max_approx (Mixtures.cpp:737-744) */
+void orc_score_batch(const orc_model *m, const float *x, uint64_t n_frames, int max_approx, double *scores) {
+#pragma omp parallel for schedule(static)
+  for (int64_t f = 0; f < (int64_t)n_frames; f++)
+    for (uint32_t j = 0; j < m->n_mix; j++)
+      scores[(size_t)f * m->n_mix + j] = orc_score(m, x + (size_t)f * m->dim, j, max_approx);
+}
+
 /* Trainer::calc_am_score, Training.cpp:585-612: sequential f64 sum of score(x_f, aligned state) / frames */
 double orc_am_score(const orc_model *m, const uint32_t *states, const float *x, uint64_t n_frames,
                     int max_approx) {

@@ -12,6 +12,9 @@
 // state's frames are cut into items of kSoftItem consecutive frames, one CTA walks an item in frame order keeping
 // the state's accumulators [2 dim + 1][densities] in shared memory, then one thread per accumulator adds the items'
 // partials in item order.  The summation tree depends only on the data.
+#include <algorithm>
+#include <initializer_list>
+
 #include "sgmm_internal.cuh"
 
 namespace {
@@ -26,7 +29,7 @@ ExactTables exact_tables(const sgmm_ctx* c) {
 
 // ---- sum scores of (frame, state) cells ---------------------------------------------------------------------
 // One warp per 32 consecutive frames of one utterance (gathered) or of the dense range; lane = frame.  Table reads
-// are warp-uniform (one density at a time, all lanes), features come from shared memory as f64.
+// are warp-uniform (one density at a time, all lanes); every lane walks its own feature row (L1-resident).
 struct SumParams {
   ExactTables m;
   const uint32_t* state_off;
@@ -118,4 +121,233 @@ __global__ void __launch_bounds__(128) k_sum_aligned(SumAlignedParams p) {
   p.fdens[f] = p.m.Dtot;   // dummy slot: the per-frame density of the max-approx E-step does not exist here
 }
 
+
+// ---- posterior-weighted accumulation ----------------------------------------------------------------------------
+constexpr uint32_t kSoftItem = 2048;     // frames per item (one CTA), walked in sub-blocks of SB frames
+constexpr int kSoftThreads = 512;
+
+// keys for the stable sort by aligned state + per-state frame counts (integer atomics: order-independent)
+__global__ void __launch_bounds__(256) k_soft_keys(const sgmm_alignment_item* __restrict__ ali, uint64_t n,
+                                                   uint32_t n_states, uint32_t Dtot, uint32_t* __restrict__ keys,
+                                                   uint32_t* __restrict__ cnt, uint32_t* __restrict__ fdens) {
+  const uint64_t f = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n) return;
+  uint32_t s = ali[f].state;
+  if (s >= n_states) s = 0;
+  keys[f] = s;
+  fdens[f] = Dtot;
+  atomicAdd(cnt + s, 1u);
+}
+
+// seg_off[s] = first sorted position of state s, item_off[s] = first item of state s (n_states is small)
+__global__ void k_soft_offsets(const uint32_t* __restrict__ cnt, uint32_t n_states, uint32_t* __restrict__ seg_off,
+                               uint32_t* __restrict__ item_off) {
+  if (threadIdx.x || blockIdx.x) return;
+  uint32_t a = 0, b = 0;
+  for (uint32_t s = 0; s < n_states; s++) {
+    seg_off[s] = a; item_off[s] = b;
+    a += cnt[s];
+    b += (cnt[s] + kSoftItem - 1) / kSoftItem;
+  }
+  seg_off[n_states] = a; item_off[n_states] = b;
+}
+
+struct SoftParams {
+  ExactTables m;
+  const uint32_t* state_off;
+  const float* x;
+  const uint32_t* sorted;      // frame ids, stably sorted by aligned state
+  const uint32_t* seg_off;
+  const uint32_t* item_off;
+  uint32_t n_states;
+  uint32_t SB;                 // frames per sub-block
+  uint32_t maxE;               // partial stride: max densities per state * (2 dim + 1)
+  double* partial;             // [item][maxE]
+  double* fscore;              // per frame: sum score (-log of the normaliser)
+};
+
+__global__ void __launch_bounds__(kSoftThreads, 1) k_soft_partial(SoftParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const uint32_t item = blockIdx.x;
+  if (item >= p.item_off[p.n_states]) return;
+  uint32_t lo = 0, hi = p.n_states;          // state owning this item: largest s with item_off[s] <= item
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (p.item_off[mid] <= item) lo = mid; else hi = mid;
+  }
+  const uint32_t s = lo;
+  const uint32_t beg = p.seg_off[s] + (item - p.item_off[s]) * kSoftItem;
+  const uint32_t end = min(p.seg_off[s + 1], beg + kSoftItem);
+  const uint32_t k0 = p.state_off[s], nd = p.state_off[s + 1] - k0, d = p.m.dim;
+  const uint32_t nE = nd * (2 * d + 1), ndp = nd | 1u, SB = p.SB;
+  double* acc = reinterpret_cast<double*>(smem);            // [2 d + 1][nd]
+  double* P = acc + (size_t)(p.maxE);                       // [SB][ndp]
+  double* X = P + (size_t)SB * ((p.maxE / (2 * d + 1)) | 1u);   // [SB][d]
+  double* sums = X + (size_t)SB * d;                        // [SB]
+  uint32_t* fr = reinterpret_cast<uint32_t*>(sums + SB);    // [SB]
+  const uint32_t tid = threadIdx.x;
+  for (uint32_t e = tid; e < nE; e += kSoftThreads) acc[e] = 0.0;
+
+  for (uint32_t i0 = beg; i0 < end; i0 += SB) {
+    const uint32_t nf = min(SB, end - i0);
+    if (tid < nf) fr[tid] = p.sorted[i0 + tid];
+    __syncthreads();
+    for (uint32_t q = tid; q < nf * d; q += kSoftThreads) {
+      const uint32_t j = q / d, i = q - j * d;
+      X[j * d + i] = (double)__ldg(p.x + (uint64_t)fr[j] * d + i);
+    }
+    // membership_probabilities[k] = exp(-1 * density_score), Mixtures.cpp:310
+    for (uint32_t q = tid; q < nf * nd; q += kSoftThreads) {
+      const uint32_t j = q / nd, k = q - j * nd;
+      P[j * ndp + k] = exp(-sgmm_exact_score(p.m, p.x + (uint64_t)fr[j] * d, k0 + k));
+    }
+    __syncthreads();
+    if (tid < nf) {                       // std::accumulate(..., 0.0) in density order, :319-320
+      double a = 0.0;
+      for (uint32_t k = 0; k < nd; k++) a = __dadd_rn(a, P[tid * ndp + k]);
+      sums[tid] = a;
+      p.fscore[fr[tid]] = -log(a);        // == sum_score(x, s), :719-728 (same terms, same order)
+    }
+    __syncthreads();
+    for (uint32_t q = tid; q < nf * nd; q += kSoftThreads) {   // divides<double>, :322-323
+      const uint32_t j = q / nd, k = q - j * nd;
+      P[j * ndp + k] = __ddiv_rn(P[j * ndp + k], sums[j]);
+    }
+    __syncthreads();
+    for (uint32_t e = tid; e < nE; e += kSoftThreads) {
+      const uint32_t c = e / nd, k = e - c * nd;
+      double v = acc[e];
+      if (c < d) {                        // mean accumulator: x + scale * y, :46-56
+        for (uint32_t j = 0; j < nf; j++) {
+          const double w = P[j * ndp + k];
+          if (w < 1e-8) continue;         // :336-338 (a NaN weight is NOT skipped, as in the reference)
+          v = __dadd_rn(v, __dmul_rn(w, X[j * d + c]));
+        }
+      } else if (c < 2 * d) {             // variance accumulator: x + scale * y * y, :58-68
+        for (uint32_t j = 0; j < nf; j++) {
+          const double w = P[j * ndp + k];
+          if (w < 1e-8) continue;
+          const double y = X[j * d + (c - d)];
+          v = __dadd_rn(v, __dmul_rn(__dmul_rn(w, y), y));
+        }
+      } else {                            // weight accumulators, :343-344
+        for (uint32_t j = 0; j < nf; j++) {
+          const double w = P[j * ndp + k];
+          if (w < 1e-8) continue;
+          v = __dadd_rn(v, w);
+        }
+      }
+      acc[e] = v;
+    }
+    __syncthreads();
+  }
+  double* out = p.partial + (size_t)item * p.maxE;
+  for (uint32_t e = tid; e < nE; e += kSoftThreads) out[e] = acc[e];
+}
+
+// one thread per (density, accumulator column): add the items' partials in item order
+__global__ void __launch_bounds__(256) k_soft_final(const double* __restrict__ partial, uint32_t maxE,
+                                                    const uint32_t* __restrict__ item_off,
+                                                    const uint32_t* __restrict__ state_off, uint32_t n_states,
+                                                    uint32_t Dtot, uint32_t dim, double* __restrict__ accum) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t W = 2 * dim + 1;
+  if (t >= (uint64_t)Dtot * W) return;
+  const uint32_t j = (uint32_t)(t / W), c = (uint32_t)(t - (uint64_t)j * W);
+  uint32_t lo = 0, hi = n_states;            // state of density j: largest s with state_off[s] <= j
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (state_off[mid] <= j) lo = mid; else hi = mid;
+  }
+  const uint32_t s = lo, nd = state_off[s + 1] - state_off[s], k = j - state_off[s];
+  double a = 0.0;
+  for (uint32_t it = item_off[s]; it < item_off[s + 1]; it++)
+    a = __dadd_rn(a, partial[(size_t)it * maxE + (size_t)c * nd + k]);
+  double* count = accum;
+  double* sum_x = accum + Dtot;
+  double* sum_xx = accum + Dtot + (size_t)Dtot * dim;
+  if (c < dim) sum_x[(size_t)j * dim + c] = a;
+  else if (c < 2 * dim) sum_xx[(size_t)j * dim + (c - dim)] = a;
+  else count[j] = a;
+}
+
 }  // namespace
+
+int sgmm_launch_emission_sum(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
+                             uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin) {
+  if (n_tasks == 0) return 0;
+  SumParams p{};
+  p.m = exact_tables(c);
+  p.state_off = c->d_state_off.p;
+  p.x = c->d_x.p;
+  p.n_tasks = n_tasks;
+  p.tasks = d_tasks;
+  p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
+  p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p; p.Amin = c->d_Amin.p;
+  p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
+  p.scores = d_scores; p.argmin = d_argmin;
+  const uint64_t grid = (n_tasks + kSumWarps - 1) / kSumWarps;
+  k_emission_sum<<<(unsigned)grid, kSumWarps * 32, 0, c->stream>>>(p);
+  SGMM_LAUNCH_CHECK(c);
+  return 0;
+}
+
+int sgmm_launch_sum_aligned(sgmm_ctx* c) {
+  if (c->n_frames == 0) return 0;
+  SumAlignedParams p{};
+  p.m = exact_tables(c);
+  p.state_off = c->d_state_off.p;
+  p.x = c->d_x.p; p.ali = c->d_ali.p; p.n_frames = c->n_frames; p.n_states = c->n_states;
+  p.fscore = c->d_fscore.p; p.fdens = c->d_fdens.p;
+  k_sum_aligned<<<(unsigned)((c->n_frames + 127) / 128), 128, 0, c->stream>>>(p);
+  SGMM_LAUNCH_CHECK(c);
+  return 0;
+}
+
+// d_acc[count | sum_x | sum_xx] = posterior-weighted statistics of the resident alignment; d_fscore = sum scores
+int sgmm_launch_accumulate_soft(sgmm_ctx* c) {
+  const uint64_t n = c->n_frames;
+  const uint32_t N = c->n_states, D = c->Dtot, dim = c->dim, W = 2 * dim + 1;
+  const uint32_t maxE = c->max_dens * W;
+  uint32_t SB = 0;
+  size_t smem = 0;
+  for (uint32_t sb : {32u, 16u, 8u}) {
+    const size_t need = 8 * ((size_t)maxE + (size_t)sb * (c->max_dens | 1u) + (size_t)sb * dim + sb) + 4 * (size_t)sb;
+    if (need <= 227 * 1024) { SB = sb; smem = need; break; }
+  }
+  if (!SB) SGMM_FAIL(c, "accumulate_soft: a state's accumulators (densities x (2 dim + 1) doubles) exceed shared memory");
+  SGMM_CHECK(c, c->d_cnt_u32.reserve(std::max<size_t>(D + 2, N + 1)));
+  SGMM_CHECK(c, c->d_seg_off.reserve(std::max<size_t>(D + 2, N + 1)));
+  SGMM_CHECK(c, c->d_item_off.reserve(std::max<size_t>(D + 1, N + 1)));
+  const size_t max_items = n / kSoftItem + N + 1;
+  SGMM_CHECK(c, c->d_partial.reserve(max_items * (size_t)maxE));
+  SGMM_CHECK(c, cudaMemsetAsync(c->d_cnt_u32.p, 0, (N + 1) * sizeof(uint32_t), c->stream));
+  SGMM_CHECK(c, c->d_soft_keys.reserve(n));   // the sort ping-pongs through d_keys[]: its input lives elsewhere
+  uint32_t* keys = c->d_soft_keys.p;
+  if (n) {
+    k_soft_keys<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->d_ali.p, n, N, D, keys, c->d_cnt_u32.p, c->d_fdens.p);
+    SGMM_LAUNCH_CHECK(c);
+  }
+  const uint32_t* sorted = nullptr;
+  if (sgmm_sort_frames(c, keys, N, &sorted)) return 1;
+  StageTimer st(c, SGMM_T_REDUCE);
+  k_soft_offsets<<<1, 32, 0, c->stream>>>(c->d_cnt_u32.p, N, c->d_seg_off.p, c->d_item_off.p);
+  SGMM_LAUNCH_CHECK(c);
+  if (n) {
+    SoftParams p{};
+    p.m = exact_tables(c);
+    p.state_off = c->d_state_off.p; p.x = c->d_x.p; p.sorted = sorted;
+    p.seg_off = c->d_seg_off.p; p.item_off = c->d_item_off.p; p.n_states = N; p.SB = SB; p.maxE = maxE;
+    p.partial = c->d_partial.p; p.fscore = c->d_fscore.p;
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_soft_partial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_soft_partial<<<(unsigned)max_items, kSoftThreads, smem, c->stream>>>(p);
+    SGMM_LAUNCH_CHECK(c);
+  }
+  const uint64_t tot = (uint64_t)D * W;
+  if (tot) {
+    k_soft_final<<<(unsigned)((tot + 255) / 256), 256, 0, c->stream>>>(c->d_partial.p, maxE, c->d_item_off.p,
+                                                                      c->d_state_off.p, N, D, dim, c->d_acc.p);
+    SGMM_LAUNCH_CHECK(c);
+  }
+  return 0;
+}

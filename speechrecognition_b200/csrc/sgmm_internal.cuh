@@ -170,7 +170,7 @@ struct sgmm_ctx {
   DevBuf<double> d_fscore;
 
   // ---- accumulation
-  DevBuf<uint32_t> d_keys[2], d_vals[2], d_hist, d_cnt_u32, d_seg_off, d_item_off;
+  DevBuf<uint32_t> d_keys[2], d_vals[2], d_hist, d_cnt_u32, d_seg_off, d_item_off, d_soft_keys;
   DevBuf<double> d_partial, d_acc;   // d_acc = [count D | sum_x D*d | sum_xx D*d | score_sum 1]
   DevBuf<double> d_score_part;
   DevBuf<double> d_dense_scores;

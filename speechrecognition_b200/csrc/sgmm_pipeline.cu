@@ -27,6 +27,11 @@ void reset_stage(sgmm_ctx* c) {
 
 // emission scoring through whichever scorer is selected
 int launch_emission_any(sgmm_ctx* c, bool dense, uint64_t f0, uint64_t nf, double* scores, uint32_t* argmin) {
+  if (!c->max_approx) {   // score() = sum_score (Mixtures.cpp:737-744): every density contributes, exact f64 only
+    if (sgmm_wait_features(c)) return 1;
+    if (dense) return sgmm_launch_emission_sum(c, nullptr, (nf + 31) / 32, true, f0, nf, scores, argmin);
+    return sgmm_launch_emission_sum(c, c->d_tasks.p, c->n_tasks, false, 0, 0, nullptr, nullptr);
+  }
   const int sc = sgmm_effective_scorer(c);
   if (sc == 3) return sgmm_launch_emission_tc(c, dense, f0, nf, scores, argmin);   // consumes upload chunks itself
   if (sgmm_wait_features(c)) return 1;
@@ -116,6 +121,7 @@ int sgmm_align(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* co
   c->have_alignment = true;
   c->ali_has_cols = true;
   c->E_model_version = c->model_version;
+  c->E_max_approx = c->max_approx;
   return 0;
 }
 
@@ -221,7 +227,9 @@ static int rescore_common(sgmm_ctx* c, bool first_pass) {
   SGMM_CHECK(c, cudaMemsetAsync(c->d_cnt_u32.p, 0, (c->Dtot + 1) * sizeof(uint32_t), c->stream));
   StageTimer st(c, SGMM_T_RESCORE);
   // the alignment pass already scored these cells with this very model: look the results up
-  const bool cached = !first_pass && c->ali_has_cols && c->E_model_version == c->model_version && c->use_cache;
+  // (the resident emission matrix must hold min scores + argmins: not after an alignment with sum scores)
+  const bool cached = !first_pass && c->ali_has_cols && c->E_model_version == c->model_version && c->use_cache &&
+                      c->E_max_approx;
   if (cached ? sgmm_launch_rescore_cached(c) : sgmm_launch_rescore(c, first_pass)) return 1;
   if (sgmm_launch_score_sum(c)) return 1;
   return 0;
@@ -247,11 +255,49 @@ int sgmm_accumulate(sgmm_ctx* c, int first_pass, double* count, double* sum_x, d
   return 0;
 }
 
+int sgmm_accumulate_soft(sgmm_ctx* c, double* count, double* sum_x, double* sum_xx, double* score_sum) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  reset_stage(c);
+  if (require(c, true, true, false)) return 1;
+  if (!c->have_alignment) SGMM_FAIL(c, "no alignment resident: call sgmm_align or sgmm_set_alignment first");
+  if (sgmm_wait_features(c)) return 1;
+  SGMM_CHECK(c, c->d_fdens.reserve(c->n_frames));
+  SGMM_CHECK(c, c->d_fscore.reserve(c->n_frames));
+  SGMM_CHECK(c, c->d_acc.reserve(acc_len(c)));
+  if (sgmm_launch_accumulate_soft(c)) return 1;
+  {
+    StageTimer st(c, SGMM_T_RESCORE);
+    if (sgmm_launch_score_sum(c)) return 1;
+  }
+  if (sgmm_nccl_allreduce(c, c->d_acc.p, acc_len(c))) return 1;
+  const size_t D = c->Dtot, d = c->dim;
+  {
+    StageTimer st(c, SGMM_T_D2H);
+    if (count) SGMM_CHECK(c, cudaMemcpyAsync(count, c->d_acc.p, D * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (sum_x) SGMM_CHECK(c, cudaMemcpyAsync(sum_x, c->d_acc.p + D, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (sum_xx) SGMM_CHECK(c, cudaMemcpyAsync(sum_xx, c->d_acc.p + D + D * d, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (score_sum) SGMM_CHECK(c, cudaMemcpyAsync(score_sum, c->d_acc.p + D + 2 * D * d, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
 int sgmm_am_score_sum(sgmm_ctx* c, double* score_sum) {
   if (!c) return 1;
   cudaSetDevice(c->device);
   reset_stage(c);
-  if (rescore_common(c, false)) return 1;
+  if (!c->max_approx) {   // calc_am_score through score() = sum_score
+    if (require(c, true, true, false)) return 1;
+    if (!c->have_alignment) SGMM_FAIL(c, "no alignment resident: call sgmm_align or sgmm_set_alignment first");
+    if (sgmm_wait_features(c)) return 1;
+    SGMM_CHECK(c, c->d_fdens.reserve(c->n_frames));
+    SGMM_CHECK(c, c->d_fscore.reserve(c->n_frames));
+    SGMM_CHECK(c, c->d_acc.reserve(acc_len(c)));
+    StageTimer st(c, SGMM_T_RESCORE);
+    if (sgmm_launch_sum_aligned(c)) return 1;
+    if (sgmm_launch_score_sum(c)) return 1;
+  } else if (rescore_common(c, false)) return 1;
   double* slot = c->d_acc.p + (size_t)c->Dtot * (1 + 2 * (size_t)c->dim);
   if (sgmm_nccl_allreduce(c, slot, 1)) return 1;
   if (score_sum) SGMM_CHECK(c, cudaMemcpyAsync(score_sum, slot, sizeof(double), cudaMemcpyDeviceToHost, c->stream));

@@ -1,0 +1,118 @@
+"""-m gpu: the NON-max-approx branch through the C-ABI against the oracle — sum_score
+(Mixtures.cpp:719-728) in dense scoring, alignment and the AM score; the posterior-weighted E-step (:300-357).
+
+Density scores are bit-identical to the reference; exp / log are the device's f64 functions (<= 1 ulp from
+glibc's), so these comparisons use rtol = 1e-12 (north_star allows 1e-5) and the alignments must be equal.
+The oracle's own non-max-approx branch is pinned bit for bit against the unmodified reference in
+tests/test_oracle_vs_reference.py::test_sum_score_and_soft_accumulation_live."""
+import numpy as np
+import pytest
+
+from oracle.binding import Oracle
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-12
+
+
+def sum_model(pooling, dim, seed):
+    O, corp, ali = helpers.trained_oracle(dim=dim, n_utts=12, splits=2, pooling=pooling, seed=seed)
+    P = Oracle(dim, O.n_mix, pooling, False, O.tdp, O.silence)      # same parameters, score() = sum_score
+    P.load_tables(O.tables())
+    ctx = helpers.gpu_context(P, corp, dim)
+    ctx.set_option("max_approx", 0)
+    return P, corp, ali, ctx
+
+
+@pytest.fixture(scope="module", params=[("none", 25, 3), ("mixture", 33, 5)])
+def soft(request):
+    P, corp, ali, ctx = sum_model(*request.param)
+    yield P, corp, ali, ctx, request.param[0]
+    ctx.close()
+
+
+def test_sum_scores_dense(soft):
+    P, corp, ali, ctx, _ = soft
+    scores, argmin = ctx.score_all(0, 400)
+    want = P.score(corp["x"][:400])
+    assert np.array_equal(np.isinf(scores), np.isinf(want))       # emptied mixtures: -log(0) = +inf on both sides
+    np.testing.assert_allclose(scores, want, rtol=RTOL)
+    assert not argmin.any()
+    # and the max-approx answer is something else
+    ctx.set_option("max_approx", 1)
+    mins, _ = ctx.score_all(0, 400)
+    ctx.set_option("max_approx", 0)
+    fin = np.isfinite(want) & (want < 600.0)     # beyond that exp(-score) is subnormal and -log of it is coarse
+    assert np.all(mins[fin] >= scores[fin] - 1e-9) and np.any(mins[fin] > scores[fin] + 1e-6)
+
+
+def test_align_with_sum_scores(soft):
+    P, corp, ali, ctx, _ = soft
+    got, costs = ctx.align()
+    want_states, want_costs = P.align_batch(corp["x"], corp["frame_off"], corp["automata"], corp["aut_off"])
+    assert np.array_equal(got["state"].astype(np.uint32), want_states)
+    np.testing.assert_allclose(costs, want_costs, rtol=RTOL)
+    # AM score through score() = sum_score (Training.cpp:585-612)
+    am = P.am_score(want_states, corp["x"])
+    assert abs(ctx.am_score_sum() / len(want_states) - am) <= RTOL * abs(am)
+
+
+def test_accumulate_soft_matches_oracle(soft):
+    P, corp, ali, ctx, pooling = soft
+    dim = P.dim
+    ctx.set_alignment(ali)
+    cnt, sx, sxx, ssum = ctx.accumulate_soft()
+    Q = Oracle(dim, P.n_mix, pooling, False, P.tdp, P.silence)
+    Q.load_tables(P.tables())
+    Q.accumulate(ali, corp["x"], False, False)
+    t = Q.tables()
+    want_cnt, want_sx = helpers.packed_stats(t, dim)
+    np.testing.assert_allclose(cnt, want_cnt, rtol=1e-11, atol=1e-12)
+    np.testing.assert_allclose(sx, want_sx, rtol=1e-11, atol=1e-9)
+    # variance statistics: fold the per-density sums into the reference's (possibly pooled) slots; it seeds 1e-4
+    vi = t["var_idx"].astype(np.int64)
+    fold = np.zeros_like(t["var_acc"].reshape(-1, dim))
+    np.add.at(fold, vi, sxx)
+    used = np.zeros(len(fold), bool)
+    used[vi] = True
+    np.testing.assert_allclose(fold[used], t["var_acc"].reshape(-1, dim)[used] - 1e-4, rtol=1e-9, atol=1e-7)
+    wfold = np.zeros(len(fold))
+    np.add.at(wfold, vi, cnt)
+    np.testing.assert_allclose(wfold[used], t["var_wacc"][used], rtol=1e-11, atol=1e-12)
+    # posteriors of a frame sum to 1 (minus the skipped entries below 1e-8): total weight = frames aligned to states
+    # that still have densities
+    live = np.diff(t["mix_offsets"])[ali] > 0
+    assert abs(cnt.sum() - live.sum()) < 1e-4
+    # by-product: calc_am_score's numerator with sum scores
+    am = P.am_score(ali, corp["x"])
+    assert np.isinf(am) or abs(ssum / len(ali) - am) <= RTOL * abs(am)
+    assert ctx.am_score_sum() == ssum or (np.isinf(ssum) and np.isinf(ctx.am_score_sum()))
+    # deterministic: same bits on a second run
+    again = ctx.accumulate_soft()
+    for a, b in zip((cnt, sx, sxx), again[:3]):
+        assert np.array_equal(a, b)
+
+
+def test_max_approx_estep_after_sum_alignment(soft):
+    """accumulate(max_approx = true) on an alignment computed with sum scores must not look the (sum) scores up."""
+    P, corp, ali, ctx, pooling = soft
+    got, _ = ctx.align()
+    states = got["state"].astype(np.uint32)
+    cnt, sx, sxx, _ = ctx.accumulate(first_pass=False)
+    Q = Oracle(P.dim, P.n_mix, pooling, True, P.tdp, P.silence)
+    Q.load_tables(P.tables())
+    want_dens = Q.accumulate(states, corp["x"], False, True)
+    dens, _ = ctx.last_frame_results()
+    assert np.array_equal(dens, want_dens)
+    want_cnt, want_sx = helpers.packed_stats(Q.tables(), P.dim)
+    assert np.array_equal(cnt, want_cnt)
+    np.testing.assert_allclose(sx, want_sx, rtol=1e-12, atol=1e-9)
+
+
+def test_soft_errors_are_loud():
+    from speechrecognition_b200 import capi
+    ctx = capi.Context(0)
+    with pytest.raises(capi.SgmmError):
+        ctx.accumulate_soft()             # no model / features / alignment
+    ctx.close()

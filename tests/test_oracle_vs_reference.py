@@ -124,3 +124,36 @@ def test_linear_segmentation_live(approx):
         want_states, want_b = R.linear_segmentation(x, aut, approx)
         assert got_b == want_b, (u, got_b, want_b)
         assert np.array_equal(got_states, want_states), u
+
+
+@pytest.mark.parametrize("pooling", ["none", "mixture"])
+def test_sum_score_and_soft_accumulation_live(pooling):
+    """models built with max_approx == false — sum_score (Mixtures.cpp:719-728) in scoring,
+    alignment and the AM score, posterior-weighted accumulate (:300-357).  Oracle == reference bit for bit
+    (same libm)."""
+    rng = np.random.default_rng(11)
+    lex = synth.Lexicon()
+    d = 25
+    gen = synth.random_model(rng, d, lex.num_states, 2, "none")
+    corp = synth.make_corpus(rng, lex, gen, d, 16)
+    tdp = (3.0, 0.0, 30.0)
+    O = Oracle(d, 106, pooling, False, tdp, 0)
+    R = Reference(d, 106, pooling, False, tdp, 0)
+    ali = synth.linear_alignment(corp["frame_off"], corp["automata"], corp["aut_off"])
+    x = corp["x"]
+    O.accumulate(ali, x, True); R.accumulate(ali, x, True)
+    O.finalize(); R.finalize()
+    for it in range(2):
+        O.split(30); R.split(30)
+        O.accumulate(ali, x, False, False); R.accumulate(ali, x, False, False)
+        same(O.tables(), R.tables(), "soft-acc")
+        O.finalize(); R.finalize()
+        same(O.tables(), R.tables(), "soft-fin")
+        so, sr = O.score(x[:200]), R.score(x[:200])
+        assert np.array_equal(so, sr, equal_nan=True)
+        a_o, c_o = O.align_batch(x, corp["frame_off"], corp["automata"], corp["aut_off"])
+        a_r, c_r = R.align_batch(x, corp["frame_off"], corp["automata"], corp["aut_off"])
+        assert np.array_equal(a_o, a_r) and np.array_equal(c_o, c_r)
+        assert O.am_score(a_o, x) == R.am_score(a_r, x)
+        ali = a_o
+    assert O.num_densities() > 150
