@@ -164,6 +164,8 @@ void MixtureModel::sync_device() const {
   device_->check(sgmm_set_model(device_->ctx(), (uint32_t)dimension, (uint32_t)mixtures_.size(), off.data(), pm.data(),
                                 pv.data(), pn.data(), pw.data()),
                  "sgmm_set_model");
+  // FeatureScorer::score on this context = min_score or sum_score, as the constructor's max_approx says (:737-744)
+  device_->check(sgmm_set_option(device_->ctx(), "max_approx", max_approx_ ? 1 : 0), "sgmm_set_option");
   uploaded_version_ = version_;
 }
 
@@ -210,8 +212,6 @@ void MixtureModel::comm_init(int rank, int world_size, const void* id, size_t id
 // ---- E-step (Mixtures.cpp:278-372) on the GPU ------------------------------------------------------------
 void MixtureModel::accumulate(ConstAlignmentIter alignment_begin, ConstAlignmentIter alignment_end,
                               FeatureIter feature_begin, FeatureIter feature_end, bool first_pass, bool max_approx) {
-  if (!first_pass && !max_approx)
-    fail("accumulate: the posterior-weighted (non max-approx) E-step is not on the GPU path");
   if (alignment_begin.size != 1) fail("accumulate: num-max-aligns must be 1");
   const size_t n = (size_t)(feature_end - feature_begin);
   if ((size_t)(alignment_end - alignment_begin) != n) fail("accumulate: alignment and feature ranges differ in length");
@@ -231,8 +231,11 @@ void MixtureModel::accumulate(ConstAlignmentIter alignment_begin, ConstAlignment
   const size_t D = off.back(), d = dimension;
   std::vector<double> count(D), sum_x(D * d), sum_xx(D * d);
   double score_sum = 0.0;
-  device_->check(sgmm_accumulate(c, first_pass ? 1 : 0, count.data(), sum_x.data(), sum_xx.data(), &score_sum),
-                 "sgmm_accumulate");
+  if (!first_pass && !max_approx)   // posterior-weighted branch, :300-357 (score_sum = sum of sum scores)
+    device_->check(sgmm_accumulate_soft(c, count.data(), sum_x.data(), sum_xx.data(), &score_sum), "sgmm_accumulate_soft");
+  else
+    device_->check(sgmm_accumulate(c, first_pass ? 1 : 0, count.data(), sum_x.data(), sum_xx.data(), &score_sum),
+                   "sgmm_accumulate");
   last_score_sum_ = score_sum;
   // fold the per-density statistics into the reference's slots (:333-357); the variance sums start
   // from the 1e-4 seed exactly once, whatever the number of GPUs behind the all-reduce
@@ -377,6 +380,14 @@ void MixtureModel::prepare_sequence(FeatureIter const& start, FeatureIter const&
     s.check(sgmm_set_features(s.ctx(), *start, T, (uint32_t)dimension), "sgmm_set_features");
     s.check(sgmm_score_all(s.ctx(), 0, T, seq_scores_.data(), seq_argmin_.data()), "sgmm_score_all");
   }
+  seq_sum_scores_.clear();
+  if (!max_approx_ && T) {   // score() of this model is sum_score: a second batched pass with the other semantics
+    seq_sum_scores_.resize(T * N);
+    s.check(sgmm_set_option(s.ctx(), "max_approx", 0), "sgmm_set_option");
+    const int rc = sgmm_score_all(s.ctx(), 0, T, seq_sum_scores_.data(), nullptr);
+    sgmm_set_option(s.ctx(), "max_approx", 1);
+    s.check(rc, "sgmm_score_all");
+  }
   seq_begin_ = *start;
   seq_frames_ = T;
   seq_version_ = version_;
@@ -399,8 +410,27 @@ std::pair<double, DensityIdx> MixtureModel::min_score(FeatureIter const& iter, S
   return std::make_pair(sc[mixture_idx], (DensityIdx)am[mixture_idx]);
 }
 
-double MixtureModel::score(FeatureIter const& iter, StateIdx mixture_idx) const {
-  if (!max_approx_) fail("score: sum_score (non max-approx) is not on the GPU path");
+// Mixtures.cpp:719-728; `weights` is ignored there as well
+double MixtureModel::sum_score(FeatureIter const& iter, StateIdx mixture_idx, std::vector<double>*) const {
+  if (mixture_idx >= mixtures_.size()) fail("sum_score: mixture index out of range");
+  const size_t N = mixtures_.size();
+  if (seq_begin_ && seq_version_ == version_ && !seq_sum_scores_.empty() && *iter >= seq_begin_ &&
+      *iter < seq_begin_ + seq_frames_ * dimension) {
+    const size_t t = (size_t)(*iter - seq_begin_) / dimension;
+    return seq_sum_scores_[t * N + mixture_idx];
+  }
+  Device& s = scratch();   // not prepared: one frame through the sum kernel
+  std::vector<double> sc(N);
+  s.check(sgmm_set_features(s.ctx(), *iter, 1, (uint32_t)dimension), "sgmm_set_features");
+  s.check(sgmm_set_option(s.ctx(), "max_approx", 0), "sgmm_set_option");
+  const int rc = sgmm_score_all(s.ctx(), 0, 1, sc.data(), nullptr);
+  sgmm_set_option(s.ctx(), "max_approx", 1);
+  s.check(rc, "sgmm_score_all");
+  return sc[mixture_idx];
+}
+
+double MixtureModel::score(FeatureIter const& iter, StateIdx mixture_idx) const {   // :737-744
+  if (!max_approx_) return sum_score(iter, mixture_idx, nullptr);
   return min_score(iter, mixture_idx).first;
 }
 

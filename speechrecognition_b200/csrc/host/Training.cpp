@@ -29,7 +29,6 @@ Trainer::Trainer(Configuration const& config, Lexicon const& lexicon, MixtureMod
       realign_(config.get_bool("realign", true)), alignment_pruning_(config.get_bool("alignment-pruning", true)),
       approx_linear_segmentation_(config.get_bool("approx-linear-segmentation", true)),
       lexicon_(lexicon), mixtures_(mixtures), tdp_model_(tdp_model), aligner_(mixtures, tdp_model, num_max_aligns_) {
-  if (!max_approx) throw std::runtime_error("Trainer: only max-approx training is on the GPU path");
 }
 
 // Training.cpp:239-253: sil w1 sil w2 ... sil

@@ -126,6 +126,30 @@ int sthost_model_accumulate(void* h, const sgmm_alignment_item* ali, const float
   });
 }
 
+// MixtureModel::accumulate(..., first_pass = false, max_approx = false): the posterior-weighted E-step
+int sthost_model_accumulate_soft(void* h, const sgmm_alignment_item* ali, const float* x, uint64_t n_frames,
+                                 double* score_sum) {
+  return guarded([&] {
+    MixtureModel& m = *static_cast<HostModel*>(h)->model;
+    const AlignmentItem* a = reinterpret_cast<const AlignmentItem*>(ali);
+    m.accumulate(ConstAlignmentIter(a, 1), ConstAlignmentIter(a + n_frames, 1), FeatureIter(x, m.dimension),
+                 FeatureIter(x + n_frames * m.dimension, m.dimension), false, false);
+    if (score_sum) *score_sum = m.last_score_sum();
+  });
+}
+
+// FeatureScorer::score per (frame, state) — sum_score for a model built with max_approx == false
+int sthost_model_scores(void* h, const float* x, uint64_t T, int prepared, double* scores) {
+  return guarded([&] {
+    MixtureModel& m = *static_cast<HostModel*>(h)->model;
+    const size_t N = m.num_mixtures();
+    FeatureIter b(x, m.dimension), e(x + T * m.dimension, m.dimension);
+    if (prepared) m.prepare_sequence(b, e);
+    for (uint64_t t = 0; t < T; t++)
+      for (size_t s = 0; s < N; s++) scores[t * N + s] = m.score(b + (ptrdiff_t)t, (StateIdx)s);
+  });
+}
+
 // FeatureScorer idiom: prepare_sequence, then min_score per (frame, state); prepared == 0 skips the
 // prepare call so that every lookup goes through the one-frame path
 int sthost_model_score_sequence(void* h, const float* x, uint64_t T, int prepared, double* scores, uint32_t* argmin) {
@@ -176,7 +200,8 @@ double sthost_tdp_score(double loop, double forward, double skip, uint32_t silen
 int sthost_train(uint32_t dim, int pooling, int device, const float* x, uint64_t n_utts, const uint64_t* frame_off,
                  const uint64_t* words, const uint64_t* word_off, double loop, double forward, double skip,
                  uint32_t min_obs, uint32_t num_splits, uint32_t num_aligns, uint32_t num_estimates, int alignment_pruning,
-                 double pruning_threshold, const sgmm_alignment_item* initial, const char* mixture_path, const char* alignment_path,
+                 double pruning_threshold, int max_approx, const sgmm_alignment_item* initial, const char* mixture_path,
+                 const char* alignment_path,
                  double* stats, uint64_t stats_cap, uint64_t* n_stats, sgmm_alignment_item* final_alignment,
                  double* timers /* [4]: align, estimate, score, io seconds */, void** model_out) {
   HostModel* h = new HostModel();
@@ -192,8 +217,8 @@ int sthost_train(uint32_t dim, int pooling, int device, const float* x, uint64_t
     if (mixture_path && *mixture_path) cfg.set("mixture-path", std::string(mixture_path));
     if (alignment_path && *alignment_path) cfg.set("alignment-path", std::string(alignment_path));
     TdpModel tdp(cfg, lex.get_silence_automaton()[0]);
-    h->model.reset(new MixtureModel(cfg, dim, lex.num_states(), pooling_of(pooling), true));
-    Trainer trainer(cfg, lex, *h->model, tdp, true);
+    h->model.reset(new MixtureModel(cfg, dim, lex.num_states(), pooling_of(pooling), max_approx != 0));
+    Trainer trainer(cfg, lex, *h->model, tdp, max_approx != 0);
     Alignment init;
     if (initial) {
       init.resize(fo.back());

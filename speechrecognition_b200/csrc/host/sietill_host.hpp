@@ -213,7 +213,7 @@ class MixtureModel : public FeatureScorer {
   ~MixtureModel();
 
   void reset_accumulators();                                             // Mixtures.cpp:237-245
-  // E-step on the GPU (K3 + K4); max_approx == false is not on this path and throws.
+  // E-step on the GPU (K3 + K4); max_approx == false is the posterior-weighted branch (sgmm_accumulate_soft).
   void accumulate(ConstAlignmentIter alignment_begin, ConstAlignmentIter alignment_end, FeatureIter feature_begin,
                   FeatureIter feature_end, bool first_pass, bool max_approx = true);
   void finalize();                                                       // Mixtures.cpp:374-461 (host, f64)
@@ -222,6 +222,7 @@ class MixtureModel : public FeatureScorer {
   size_t num_densities() const;                                          // Mixtures.cpp:580-582
 
   std::pair<double, DensityIdx> min_score(FeatureIter const& iter, StateIdx mixture_idx) const;  // :696-713
+  double sum_score(FeatureIter const& iter, StateIdx mixture_idx, std::vector<double>* weights) const;  // :719-728
   void prepare_sequence(FeatureIter const& start, FeatureIter const& end) override;  // scores the whole sequence (K1)
   double score(FeatureIter const& iter, StateIdx mixture_idx) const override;        // lookup, or a 1-frame K1 call
 
@@ -283,6 +284,7 @@ class MixtureModel : public FeatureScorer {
   mutable size_t seq_frames_ = 0;
   mutable uint64_t seq_version_ = 0;
   mutable std::vector<double> seq_scores_;
+  mutable std::vector<double> seq_sum_scores_;   // sum scores of the prepared sequence (models with max_approx == false)
   mutable std::vector<uint32_t> seq_argmin_;
   mutable std::unique_ptr<Device> scratch_;          // one-off sequences (per-utterance API)
   mutable uint64_t scratch_version_ = 0;

@@ -114,6 +114,23 @@ class HostModel:
                                                    C.c_uint64(len(ali)), int(first_pass), C.byref(s)))
         return s.value
 
+    def accumulate_soft(self, ali, x):
+        """MixtureModel::accumulate(first_pass=false, max_approx=false).  Returns the sum of the frames' sum scores."""
+        ali = as_alignment(ali)
+        x = np.ascontiguousarray(x, np.float32)
+        s = C.c_double(0.0)
+        _ck(self.L, self.L.sthost_model_accumulate_soft(self.h, ali.ctypes.data_as(C.c_void_p), _p(x, C.c_float),
+                                                        C.c_uint64(len(ali)), C.byref(s)))
+        return s.value
+
+    def scores(self, x, prepared=True):
+        """FeatureScorer::score per (frame, state): sum scores for a model built with max_approx=False."""
+        x = np.ascontiguousarray(x, np.float32).reshape(-1, self.dim)
+        sc = np.zeros((len(x), self.n_mix), np.float64)
+        _ck(self.L, self.L.sthost_model_scores(self.h, _p(x, C.c_float), C.c_uint64(len(x)), int(prepared),
+                                               _p(sc, C.c_double)))
+        return sc
+
     def score_sequence(self, x, prepared=True):
         x = np.ascontiguousarray(x, np.float32).reshape(-1, self.dim)
         sc = np.zeros((len(x), self.n_mix), np.float64)
@@ -145,7 +162,7 @@ def as_alignment(a):
 
 def train(dim, pooling, x, frame_off, words, word_off, tdp, min_obs, num_splits, num_aligns, num_estimates,
           alignment_pruning=False, initial=None, mixture_path="", alignment_path="", device=0,
-          pruning_threshold=float("inf")):
+          pruning_threshold=float("inf"), max_approx=True):
     """Trainer::train on the sietill digits lexicon.  Returns (stats[n,4], final alignment, HostModel, timers)."""
     L = _lib()
     x = np.ascontiguousarray(x, np.float32)
@@ -163,7 +180,7 @@ def train(dim, pooling, x, frame_off, words, word_off, tdp, min_obs, num_splits,
     _ck(L, L.sthost_train(C.c_uint32(dim), POOLING[pooling], device, _p(x, C.c_float), C.c_uint64(U), _p(fo, C.c_uint64),
                           _p(w, C.c_uint64), _p(wo, C.c_uint64), C.c_double(tdp[0]), C.c_double(tdp[1]), C.c_double(tdp[2]),
                           C.c_uint32(min_obs), C.c_uint32(num_splits), C.c_uint32(num_aligns), C.c_uint32(num_estimates),
-                          int(alignment_pruning), C.c_double(pruning_threshold), None if init is None else init.ctypes.data_as(C.c_void_p),
+                          int(alignment_pruning), C.c_double(pruning_threshold), int(max_approx), None if init is None else init.ctypes.data_as(C.c_void_p),
                           mixture_path.encode(), alignment_path.encode(), _p(stats, C.c_double), C.c_uint64(cap),
                           C.byref(n_stats), final.ctypes.data_as(C.c_void_p), _p(timers, C.c_double), C.byref(h)))
     model = HostModel(dim, 106, _handle=h)

@@ -96,6 +96,36 @@ def test_trainer_trajectory_matches_oracle(pooling, pruned, segmentation, tmp_pa
     assert timers["align"] > 0 and timers["estimate"] > 0
 
 
+@pytest.mark.parametrize("pooling", ["mixture", "none"])
+def test_trainer_without_max_approx_matches_oracle(pooling):
+    """SURVEY §8 f4 through the host classes: MixtureModel / Trainer built with max_approx == false — sum scores in
+    the alignment and the AM score (Mixtures.cpp:719-744), posterior-weighted E-step (:300-357)."""
+    rng = np.random.default_rng(33)
+    dim, min_obs = 12, 12
+    lex = synth.Lexicon()
+    gen = synth.random_model(rng, dim, lex.num_states, 2, "none")
+    corp = synth.make_corpus(rng, lex, gen, dim, 40, t_choices=([90, 140, 200], [0.5, 0.3, 0.2]), words_per_utt=(1, 3))
+    O = Oracle(dim, lex.num_states, pooling, False, TDP, lex.silence_state)
+    init = synth.linear_alignment(corp["frame_off"], corp["automata"], corp["aut_off"])
+    want_stats, want_ali = oracle_train(O, corp, min_obs, 2, 2, 2, False, initial=init)
+    w, wo = words_of(corp)
+    stats, ali, model, _ = hostapi.train(dim, pooling, corp["x"], corp["frame_off"], w, wo, TDP, min_obs, 2, 2, 2,
+                                         initial=init, max_approx=False)
+    assert np.array_equal(stats[:, :3], want_stats[:, :3])
+    np.testing.assert_allclose(stats[:, 3], want_stats[:, 3], rtol=1e-10)
+    assert np.array_equal(ali["state"].astype(np.uint32), want_ali)
+    got, want = model.tables(), O.tables()
+    for k in ("mix_offsets", "mean_idx", "var_idx", "mean_refs", "var_refs"):
+        assert np.array_equal(got[k], want[k]), k          # topology: exact
+    for k in ("mean_wacc", "var_wacc", "means", "mean_acc", "var_acc", "vars_inv", "norm", "mean_wlog"):
+        np.testing.assert_allclose(got[k], want[k], rtol=1e-9, atol=1e-12, equal_nan=True, err_msg=k)
+    # FeatureScorer::score of such a model is the sum score, prepared or one frame at a time
+    x = corp["x"][:40]
+    want_sc = O.score(x)
+    np.testing.assert_allclose(model.scores(x, prepared=True), want_sc, rtol=1e-12)
+    np.testing.assert_allclose(model.scores(x[:3], prepared=False), want_sc[:3], rtol=1e-12)
+
+
 @pytest.fixture(scope="module")
 def trained():
     O, corp, ali = helpers.trained_oracle(dim=25, n_utts=12, splits=2)
