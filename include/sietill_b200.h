@@ -73,6 +73,20 @@ int sgmm_set_tdp(sgmm_ctx* ctx, double loop, double forward, double skip, uint32
  * SGMM_TDP_DESTINATION only (the reference's full aligner has no beam); +inf (the default) = exact search. */
 int sgmm_set_beam(sgmm_ctx* ctx, double pruning_threshold);
 
+/* Load-time feature processing on the device: SignalAnalysis::process_features (SignalAnalysis.cpp:379-399) for every
+ * utterance frame_off[u] .. frame_off[u+1] of `raw` ([n_frames][n_file] f32, the frames as they lie in the .mm2 files,
+ * Corpus.cpp:95-101): first derivatives of the first n_first columns and second derivatives of the first n_second
+ * ("n-features-first", "n-features-second", "deriv-step"; add_deltas, :320-337), then — if mean / stddev
+ * ([n_file + n_first + n_second] f64, the two blobs of the normalization file, :371-375) are given — (x - mean) / stddev
+ * with the reference's two f32 roundings (:389-394), then, if energy_max_norm, column 0 minus its maximum over the
+ * utterance (:341-350).  Bit-identical to the reference.  The processed [n_frames][total] matrix becomes the
+ * context's resident feature matrix exactly as after sgmm_set_features (dim = total); `out` (may be NULL) receives
+ * a host copy.  Requires n_second <= n_first <= n_file and more than deriv_step frames per utterance (the reference
+ * reads out of bounds otherwise). */
+int sgmm_process_features(sgmm_ctx* ctx, const float* raw, uint64_t n_frames, uint32_t n_file, uint32_t n_first,
+                          uint32_t n_second, uint32_t deriv_step, uint32_t n_utts, const uint64_t* frame_off,
+                          const double* mean, const double* stddev, int energy_max_norm, float* out);
+
 /* ---- scoring (K1) --------------------------------------------------------------------------- */
 /* MixtureModel::min_score (Mixtures.cpp:696-713) for every frame in [f0, f1) and every state:
  * scores[(f-f0)*n_states + s] (f64, bit-identical to the reference), argmin likewise = position k

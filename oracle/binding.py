@@ -348,3 +348,42 @@ class Reference:
         out = np.zeros(256, np.uint32)
         n = self.L.ref_recognize(self.h, _p(xp, C.c_float), C.c_uint64(T), _p(out, C.c_uint32), C.c_uint64(256))
         return out[:n].copy()
+
+
+# ---- load-time feature processing: SignalAnalysis::process_features, one utterance at a time ----------
+def oracle_process_features(raw, n_first=12, n_second=1, deriv_step=3, mean=None, stddev=None, energy_max_norm=True):
+    if not os.path.exists(ORACLE_SO):
+        build_port()
+    L = C.CDLL(ORACLE_SO)
+    raw = np.ascontiguousarray(raw, np.float32)
+    T, nf = raw.shape
+    out = np.zeros((T, nf + n_first + n_second), np.float32)
+    m = None if mean is None else np.ascontiguousarray(mean, np.float64)
+    sd = None if stddev is None else np.ascontiguousarray(stddev, np.float64)
+    L.orc_process_features(_p(raw, C.c_float), C.c_uint64(T), C.c_uint32(nf), C.c_uint32(n_first), C.c_uint32(n_second),
+                           C.c_uint32(deriv_step), _p(m, C.c_double), _p(sd, C.c_double), int(energy_max_norm),
+                           _p(out, C.c_float))
+    return out
+
+
+def reference_process_features(raw, n_first=12, n_second=1, deriv_step=3, mean=None, stddev=None, energy_max_norm=True):
+    """The unmodified SignalAnalysis (oracle/_ref)."""
+    L = C.CDLL(REF_SO)
+    L.ref_process_features.restype = C.c_uint64
+    raw = np.ascontiguousarray(raw, np.float32)
+    T, nf = raw.shape
+    cfg = {"verbosity": "noLog", "n-features-file": int(nf), "n-features-first": int(n_first),
+           "n-features-second": int(n_second), "deriv-step": int(deriv_step), "energy-max-norm": bool(energy_max_norm)}
+    fd, path = tempfile.mkstemp(suffix=".json")
+    with os.fdopen(fd, "w") as f:
+        json.dump(cfg, f)
+    out = np.zeros((T, nf + n_first + n_second), np.float32)
+    m = None if mean is None else np.ascontiguousarray(mean, np.float64)
+    sd = None if stddev is None else np.ascontiguousarray(stddev, np.float64)
+    try:
+        nt = L.ref_process_features(path.encode(), _p(m, C.c_double), _p(sd, C.c_double), _p(raw, C.c_float),
+                                    C.c_uint64(T), _p(out, C.c_float))
+    finally:
+        os.unlink(path)
+    assert nt == out.shape[1]
+    return out

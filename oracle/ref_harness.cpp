@@ -34,6 +34,7 @@
 #include "Training.hpp"
 #include "Lexicon.hpp"
 #include "Recognizer.hpp"
+#include "SignalAnalysis.hpp"
 #undef private
 #undef protected
 
@@ -271,6 +272,26 @@ void ref_linear_segmentation(void* h, int approx, const float* x, uint64_t T, co
                                        : trainer.linear_segmentation_running_sums(aut, fb, fe, ab, ae);
   for (uint64_t t = 0; t < T; t++) states[t] = ali[t].state;
   bounds[0] = b.first; bounds[1] = b.second;
+}
+
+
+// SignalAnalysis::process_features (SignalAnalysis.cpp:379-399) on one utterance.  config_json carries
+// "n-features-file" / "n-features-first" / "n-features-second" / "deriv-step" / "energy-max-norm"; mean / stddev
+// (may be NULL) are what read_normalization_file (:371-375) would have loaded.  Returns n_features_total.
+uint64_t ref_process_features(const char* config_json, const double* mean, const double* stddev, const float* raw,
+                              uint64_t T, float* out) {
+  Silencer quiet;
+  Configuration config{std::string(config_json)};
+  SignalAnalysis sa(config);
+  if (mean) {
+    sa.mean_.assign(mean, mean + sa.n_features_total);
+    sa.stddev_.assign(stddev, stddev + sa.n_features_total);
+    sa.apply_mean_var_normalization_ = true;
+  }
+  std::vector<float> f(raw, raw + T * sa.n_features_in_file);
+  sa.process_features(f);
+  std::copy(f.begin(), f.end(), out);
+  return sa.n_features_total;
 }
 
 }  // extern "C"

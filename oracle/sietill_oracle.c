@@ -664,3 +664,33 @@ uint64_t orc_recognize(const orc_model *m, double loop, double forward, double s
   free(rev); free(cur); free(nxt); free(tb); free(am);
   return n;
 }
+
+/* ---- load-time feature processing ------------------------------------------------------------- */
+/* SignalAnalysis::process_features, SignalAnalysis.cpp:379-399, on ONE utterance: raw [T][nf] -> out [T][nt],
+ * nt = nf + n1 + n2.  add_deltas :320-337, mean / variance normalisation :389-394 (mean == NULL: not applied),
+ * energy_max_normalization :341-350.  Needs T > step and n2 <= n1 <= nf, as the reference does. */
+void orc_process_features(const float *raw, uint64_t T, uint32_t nf, uint32_t n1, uint32_t n2, uint32_t step,
+                          const double *mean, const double *stddev, int energy_max_norm, float *out) {
+  const uint32_t nt = nf + n1 + n2;
+  for (uint64_t t = 0; t < T; t++)                                             /* :383-387 */
+    for (uint32_t i = 0; i < nf; i++) out[t * nt + i] = raw[t * nf + i];
+  for (uint64_t t = 0; t < T; t++) {                                           /* :322-328 */
+    const uint64_t a = t > step ? t : step;
+    for (uint32_t i = 0; i < n1; i++) out[t * nt + nf + i] = out[a * nt + i] - out[(a - step) * nt + i];
+  }
+  for (uint64_t t = 0; t < T; t++) {                                           /* :329-336 */
+    const uint64_t b = (t < T - 1 - step ? t : T - 1 - step) + step;
+    for (uint32_t i = 0; i < n2; i++) out[t * nt + nf + n1 + i] = out[b * nt + nf + i] - out[t * nt + nf + i];
+  }
+  if (mean) {                                                                  /* :389-394: two passes, f32 stores */
+    for (uint64_t t = 0; t < T; t++) {
+      for (uint32_t c = 0; c < nt; c++) out[t * nt + c] = (float)((double)out[t * nt + c] - mean[c]);
+      for (uint32_t c = 0; c < nt; c++) out[t * nt + c] = (float)((double)out[t * nt + c] / stddev[c]);
+    }
+  }
+  if (energy_max_norm) {                                                       /* :341-350 */
+    float mx = -INFINITY;
+    for (uint64_t t = 0; t < T; t++) mx = out[t * nt] > mx ? out[t * nt] : mx;
+    for (uint64_t t = 0; t < T; t++) out[t * nt] -= mx;
+  }
+}

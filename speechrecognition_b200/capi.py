@@ -20,7 +20,7 @@ ALI_DTYPE = np.dtype([("count", np.uint16), ("state", np.uint16), ("weight", np.
 SYMBOLS = [
     "sgmm_create", "sgmm_destroy", "sgmm_last_error", "sgmm_version", "sgmm_set_model", "sgmm_set_features",
     "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_set_beam", "sgmm_set_lexicon", "sgmm_recognize", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
-    "sgmm_accumulate_soft",
+    "sgmm_accumulate_soft", "sgmm_process_features",
     "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
     "sgmm_launch_count", "sgmm_timer_start", "sgmm_timer_stop", "sgmm_host_alloc", "sgmm_host_free",
     "sgmm_set_option", "sgmm_get_counter",
@@ -108,6 +108,24 @@ class Context:
         assert x.ndim == 2
         self._ck(self.L.sgmm_set_features(self.h, _ptr(x, C.c_float), C.c_uint64(x.shape[0]), C.c_uint32(x.shape[1])))
         self.n_frames = x.shape[0]
+
+    def process_features(self, raw, frame_off, n_first=12, n_second=1, deriv_step=3, mean=None, stddev=None,
+                         energy_max_norm=True, want=True):
+        """SignalAnalysis::process_features on the device; the result becomes the resident feature matrix."""
+        raw = np.ascontiguousarray(raw, np.float32)
+        assert raw.ndim == 2
+        fo = np.ascontiguousarray(frame_off, np.uint64)
+        nt = raw.shape[1] + n_first + n_second
+        mean = None if mean is None else np.ascontiguousarray(mean, np.float64)
+        stddev = None if stddev is None else np.ascontiguousarray(stddev, np.float64)
+        out = np.empty((raw.shape[0], nt), np.float32) if want else None
+        self._ck(self.L.sgmm_process_features(self.h, _ptr(raw, C.c_float), C.c_uint64(raw.shape[0]),
+                                              C.c_uint32(raw.shape[1]), C.c_uint32(n_first), C.c_uint32(n_second),
+                                              C.c_uint32(deriv_step), C.c_uint32(len(fo) - 1), _ptr(fo, C.c_uint64),
+                                              _ptr(mean, C.c_double), _ptr(stddev, C.c_double), int(energy_max_norm),
+                                              _ptr(out, C.c_float)))
+        self.n_frames = raw.shape[0]
+        return out
 
     def set_corpus(self, frame_off, automata, aut_off):
         frame_off = np.ascontiguousarray(frame_off, np.uint64)

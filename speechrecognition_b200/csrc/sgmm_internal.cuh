@@ -99,6 +99,10 @@ struct sgmm_ctx {
   uint64_t n_frames = 0;
   uint32_t feat_dim = 0;
   DevBuf<float> d_x;
+  // sgmm_process_features (k_features.cu): raw file frames, utterance offsets, {mean, stddev}
+  DevBuf<float> d_raw;
+  DevBuf<uint64_t> d_feat_off;
+  DevBuf<double> d_feat_norm;
   // option "async_upload": sgmm_set_features returns once the chunked copies are queued on copy_stream; the GEMM
   // scorer consumes the chunks as they land (k_score_tc.cu), every other consumer waits for the last one
   static constexpr int kFeatChunks = 8;

@@ -103,3 +103,25 @@ def test_recognition_matches_reference():
             assert np.array_equal(got, words[off[u]:off[u + 1]]), (ci, u)
             total += len(got)
     assert total > 0
+
+
+def _feature_cases():
+    g = np.load(os.path.join(G, "features.npz"))
+    for ci, (nf, n1, n2, step, norm, emax) in enumerate(g["cases"]):
+        mean = g["mean%d" % ci] if norm else None
+        std = g["std%d" % ci] if norm else None
+        yield g["raw%d" % ci], g["off%d" % ci], g["out%d" % ci], int(n1), int(n2), int(step), mean, std, bool(emax)
+
+
+def test_feature_processing_matches_reference():
+    """SURVEY §8 f3: SignalAnalysis::process_features (deltas, mean / variance and energy-max normalisation) —
+    the oracle against the committed outputs of the unmodified reference, bit for bit."""
+    from oracle.binding import oracle_process_features
+    n = 0
+    for raw, off, want, n1, n2, step, mean, std, emax in _feature_cases():
+        for u in range(len(off) - 1):
+            a, b = int(off[u]), int(off[u + 1])
+            got = oracle_process_features(raw[a:b], n1, n2, step, mean, std, emax)
+            assert np.array_equal(got.view(np.uint32), want[a:b].view(np.uint32))
+            n += 1
+    assert n == 20

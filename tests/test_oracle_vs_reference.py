@@ -157,3 +157,18 @@ def test_sum_score_and_soft_accumulation_live(pooling):
         assert O.am_score(a_o, x) == R.am_score(a_r, x)
         ali = a_o
     assert O.num_densities() > 150
+
+
+@pytest.mark.parametrize("nf,n1,n2,step,norm,emax", [(12, 12, 1, 3, True, True), (12, 12, 1, 3, False, True),
+                                                      (7, 7, 7, 1, True, False), (20, 4, 2, 5, True, True)])
+def test_feature_processing_live(nf, n1, n2, step, norm, emax):
+    """SignalAnalysis::process_features: oracle == unmodified reference, bit for bit, on fresh inputs."""
+    rng = np.random.default_rng(nf * 100 + step)
+    nt = nf + n1 + n2
+    mean = rng.uniform(-5, 5, nt) if norm else None
+    std = rng.uniform(0.2, 9.0, nt) if norm else None
+    for T in (step + 1, step + 2, 50, 333):
+        raw = (rng.standard_normal((T, nf)) * 7.0 + 3.0).astype(np.float32)
+        a = binding.oracle_process_features(raw, n1, n2, step, mean, std, emax)
+        b = binding.reference_process_features(raw, n1, n2, step, mean, std, emax)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))

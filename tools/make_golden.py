@@ -88,9 +88,43 @@ def recognition():
     np.savez_compressed(os.path.join(OUT, "recognize.npz"), **rec)
 
 
+FEAT_CASES = [  # (n_file, n_first, n_second, deriv_step, normalise, energy_max_norm)
+    (12, 12, 1, 3, True, True),      # the bundled digits setup (SignalAnalysis.cpp:53-56, Normalization.bin)
+    (12, 12, 1, 3, False, False),
+    (9, 5, 5, 2, True, False),
+    (16, 16, 0, 1, False, True),
+    (33, 0, 0, 3, True, True),
+]
+
+
+def features():
+    """features.npz: SignalAnalysis::process_features (SignalAnalysis.cpp:379-399) of the unmodified reference on
+    seeded raw frames, one utterance per call, for the parameter sets above."""
+    from oracle.binding import reference_process_features
+    rng = np.random.default_rng(20161107)
+    rec = {"cases": np.array([[int(v) for v in c] for c in FEAT_CASES])}
+    for ci, (nf, n1, n2, step, norm, emax) in enumerate(FEAT_CASES):
+        lens = [step + 1, 37, 64, 5 + step]
+        raw = (rng.standard_normal((sum(lens), nf)) * rng.uniform(0.5, 20.0, nf) + rng.uniform(-30, 30, nf)).astype(np.float32)
+        nt = nf + n1 + n2
+        mean = rng.uniform(-20, 20, nt) if norm else None
+        std = rng.uniform(0.3, 15.0, nt) if norm else None
+        off = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+        out = np.concatenate([reference_process_features(raw[int(off[u]):int(off[u + 1])], n1, n2, step, mean, std, emax)
+                              for u in range(len(lens))])
+        rec["raw%d" % ci], rec["off%d" % ci], rec["out%d" % ci] = raw, off, out
+        if norm:
+            rec["mean%d" % ci], rec["std%d" % ci] = mean, std
+    np.savez_compressed(os.path.join(OUT, "features.npz"), **rec)
+    print("features:", len(FEAT_CASES), "cases")
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "recognize":
         recognition()
+    elif len(sys.argv) > 1 and sys.argv[1] == "features":
+        features()
     else:
         main()
         recognition()
+        features()
