@@ -27,33 +27,44 @@ __device__ __forceinline__ float delta1(const FeatParams& p, uint64_t f0, uint32
   return __fsub_rn(__ldg(p.raw + (f0 + a) * p.nf + i), __ldg(p.raw + (f0 + a - p.step) * p.nf + i));
 }
 
+constexpr int kFeatFrames = 32;   // frames per CTA: their utterances are looked up once, then elements are coalesced
+
 __global__ void __launch_bounds__(256) k_feat_process(FeatParams p) {
-  const uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= p.n_frames * p.nt) return;
-  const uint64_t f = e / p.nt;
-  const uint32_t c = (uint32_t)(e - f * p.nt);
-  uint32_t lo = 0, hi = p.n_utts;            // utterance of frame f: largest u with frame_off[u] <= f
-  while (hi - lo > 1) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (p.frame_off[mid] <= f) lo = mid; else hi = mid;
+  __shared__ uint64_t s_f0[kFeatFrames];
+  __shared__ uint32_t s_T[kFeatFrames];
+  const uint64_t fb = (uint64_t)blockIdx.x * kFeatFrames;
+  if (threadIdx.x < kFeatFrames && fb + threadIdx.x < p.n_frames) {
+    const uint64_t f = fb + threadIdx.x;
+    uint32_t lo = 0, hi = p.n_utts;            // utterance of frame f: largest u with frame_off[u] <= f
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (p.frame_off[mid] <= f) lo = mid; else hi = mid;
+    }
+    s_f0[threadIdx.x] = p.frame_off[lo];
+    s_T[threadIdx.x] = (uint32_t)(p.frame_off[lo + 1] - p.frame_off[lo]);
   }
-  const uint64_t f0 = p.frame_off[lo];
-  const uint32_t T = (uint32_t)(p.frame_off[lo + 1] - f0), t = (uint32_t)(f - f0);
-  float v;
-  if (c < p.nf) {
-    v = __ldg(p.raw + f * p.nf + c);                                       // :383-387
-  } else if (c < p.nf + p.n1) {
-    v = delta1(p, f0, t, c - p.nf);                                        // :322-328
-  } else {                                                                 // :329-336: forward difference of the
-    const uint32_t i = c - p.nf - p.n1;                                    // first derivatives (column n_file + i)
-    const uint32_t b = min(t, T - 1 - p.step) + p.step;
-    v = __fsub_rn(delta1(p, f0, b, i), delta1(p, f0, t, i));
+  __syncthreads();
+  const uint32_t nfr = (uint32_t)min((uint64_t)kFeatFrames, p.n_frames - fb);
+  for (uint32_t q = threadIdx.x; q < nfr * p.nt; q += 256) {
+    const uint32_t j = q / p.nt, c = q - j * p.nt;
+    const uint64_t f = fb + j, f0 = s_f0[j];
+    const uint32_t T = s_T[j], t = (uint32_t)(f - f0);
+    float v;
+    if (c < p.nf) {
+      v = __ldg(p.raw + f * p.nf + c);                                     // :383-387
+    } else if (c < p.nf + p.n1) {
+      v = delta1(p, f0, t, c - p.nf);                                      // :322-328
+    } else {                                                               // :329-336: forward difference of the
+      const uint32_t i = c - p.nf - p.n1;                                  // first derivatives (column n_file + i)
+      const uint32_t b = min(t, T - 1 - p.step) + p.step;
+      v = __fsub_rn(delta1(p, f0, b, i), delta1(p, f0, t, i));
+    }
+    if (p.mean) {                                                          // :389-394, two f32 roundings
+      v = (float)__dsub_rn((double)v, __ldg(p.mean + c));
+      v = (float)__ddiv_rn((double)v, __ldg(p.stddev + c));
+    }
+    p.out[fb * p.nt + q] = v;
   }
-  if (p.mean) {                                                            // :389-394, two f32 roundings
-    v = (float)__dsub_rn((double)v, __ldg(p.mean + c));
-    v = (float)__ddiv_rn((double)v, __ldg(p.stddev + c));
-  }
-  p.out[e] = v;
 }
 
 // :341-350 — one warp per utterance: maximum of column 0, then subtract it from every frame's column 0
@@ -109,7 +120,7 @@ extern "C" int sgmm_process_features(sgmm_ctx* c, const float* raw, uint64_t n_f
   p.mean = mean ? c->d_feat_norm.p : nullptr; p.stddev = mean ? c->d_feat_norm.p + nt : nullptr;
   const uint64_t total = n_frames * nt;
   if (total) {
-    k_feat_process<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(p);
+    k_feat_process<<<(unsigned)((n_frames + kFeatFrames - 1) / kFeatFrames), 256, 0, c->stream>>>(p);
     SGMM_LAUNCH_CHECK(c);
     if (energy_max_norm) {
       k_feat_energy_max<<<(n_utts + 3) / 4, 128, 0, c->stream>>>(c->d_x.p, c->d_feat_off.p, n_utts, nt);

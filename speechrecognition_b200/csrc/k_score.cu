@@ -104,6 +104,26 @@ __device__ __forceinline__ void min_over_state(const ModelView& m, uint32_t k0, 
   }
 }
 
+// sum_score (Mixtures.cpp:719-728): acc += exp(-score_k) in density order from 0.0, result -log(acc).  Same score
+// chains as min_over_state (two densities in flight); the additions stay in mixture order.
+__device__ __forceinline__ double sum_over_state(const ModelView& m, uint32_t k0, uint32_t k1,
+                                                 const double2* __restrict__ xs, int xstride, double xtail) {
+  double acc = 0.0;
+  uint32_t k = k0;
+  for (; k + 2 <= k1; k += 2) {
+    double sc[2];
+    score_densities<2>(m, k, xs, xstride, xtail, sc);
+    const double e0 = exp(-sc[0]), e1 = exp(-sc[1]);
+    acc = __dadd_rn(__dadd_rn(acc, e0), e1);
+  }
+  if (k < k1) {
+    double sc[1];
+    score_densities<1>(m, k, xs, xstride, xtail, sc);
+    acc = __dadd_rn(acc, exp(-sc[0]));
+  }
+  return -log(acc);
+}
+
 // Cooperative, coalesced load of `nvalid` consecutive frames into this warp's shared f64 tile.
 __device__ __forceinline__ void load_frames(const float* __restrict__ x, uint64_t fbase, uint32_t nvalid,
                                             uint32_t dim, uint32_t npair, double2* xs, double* xt, int lane) {
@@ -124,6 +144,7 @@ __host__ __device__ inline size_t emis_smem_per_warp(uint32_t npair) {
   return (size_t)npair * 32 * sizeof(double2) + 32 * sizeof(double) + 32 * 33 * sizeof(double);
 }
 
+template <bool SUM>
 __global__ void __launch_bounds__(kEmisWarps * 32) k_emission_f64(EmisParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -169,8 +190,9 @@ __global__ void __launch_bounds__(kEmisWarps * 32) k_emission_f64(EmisParams p) 
     for (uint32_t jj = 0; jj < jn; jj++) {
       const uint32_t s = ulist ? ulist[j0 + jj] : j0 + jj;
       double best;
-      uint32_t bk;
-      min_over_state(p.m, p.m.state_off[s], p.m.state_off[s + 1], my_xs, 32, xtail, best, bk);
+      uint32_t bk = 0;
+      if (SUM) best = sum_over_state(p.m, p.m.state_off[s], p.m.state_off[s + 1], my_xs, 32, xtail);
+      else min_over_state(p.m, p.m.state_off[s], p.m.state_off[s + 1], my_xs, 32, xtail, best, bk);
       stage[lane * 33 + jj] = best;
       if (amin && lane < (int)nvalid) amin[(uint64_t)lane * out_stride + j0 + jj] = bk;
       if (amin16 && lane < (int)nvalid) amin16[(uint64_t)lane * out_stride + j0 + jj] = (uint16_t)bk;
@@ -274,8 +296,8 @@ ModelView model_view(const sgmm_ctx* c) {
 
 }  // namespace
 
-int sgmm_launch_emission(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
-                         uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin) {
+static int launch_emission_f64(sgmm_ctx* c, bool sum, const uint4* d_tasks, uint64_t n_tasks, bool dense,
+                               uint64_t dense_f0, uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin) {
   if (n_tasks == 0) return 0;
   EmisParams p{};
   p.m = model_view(c);
@@ -287,11 +309,24 @@ int sgmm_launch_emission(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bo
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.scores = d_scores; p.argmin = d_argmin;
   const size_t smem = kEmisWarps * emis_smem_per_warp(c->npair);
-  SGMM_CHECK(c, cudaFuncSetAttribute(k_emission_f64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SGMM_CHECK(c, cudaFuncSetAttribute(k_emission_f64<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  SGMM_CHECK(c, cudaFuncSetAttribute(k_emission_f64<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const uint64_t grid = (n_tasks + kEmisWarps - 1) / kEmisWarps;
-  k_emission_f64<<<(unsigned)grid, kEmisWarps * 32, smem, c->stream>>>(p);
+  if (sum) k_emission_f64<true><<<(unsigned)grid, kEmisWarps * 32, smem, c->stream>>>(p);
+  else k_emission_f64<false><<<(unsigned)grid, kEmisWarps * 32, smem, c->stream>>>(p);
   SGMM_LAUNCH_CHECK(c);
   return 0;
+}
+
+int sgmm_launch_emission(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
+                         uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin) {
+  return launch_emission_f64(c, false, d_tasks, n_tasks, dense, dense_f0, dense_nframes, d_scores, d_argmin);
+}
+
+// score() = sum_score (option max_approx = 0): the same kernel with the sum reduction over a state's densities
+int sgmm_launch_emission_sum(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
+                             uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin) {
+  return launch_emission_f64(c, true, d_tasks, n_tasks, dense, dense_f0, dense_nframes, d_scores, d_argmin);
 }
 
 int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass) {

@@ -1469,6 +1469,127 @@ __global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
   }
 }
 
+// ---- sum scores with an f32 pruner (option max_approx = 0) ---------------------------------------------
+// score = -log sum_k exp(-s_k) (Mixtures.cpp:719-728).  A density whose score exceeds the state's minimum by more than
+// kSumDelta = 45 adds less than e^-45 = 2.9e-20 of the sum; 65535 of them stay below a quarter of an f64 ulp, so leaving them
+// out changes the result by less than one rounding (and by nothing at all when the minimum is >= 700: their exp
+// underflows to exactly 0).  One warp per (frame, state) cell: stage 1 scores every density in f32 (lanes =
+// densities, the FFMA scorer's tables) and takes the minimum m; a density with  f32 score - m > 45 + guard  (guard =
+// k_emission_ffma's rigorous bound on the evaluation error of both scores) is certainly more than 45 above the true
+// minimum; stage 2 evaluates the others in f64 (the reference's operation order) and adds their exp(-s) in mixture
+// order.  NaN scores fail the test and are evaluated.
+constexpr float kSumDelta = 45.0f;
+
+template <int DV4>
+__global__ void __launch_bounds__(256) k_sum_pruned(RefineParams p) {
+  // One CTA per granule of 32 consecutive frames (of one utterance, or of the dense range); the eight warps walk
+  // the granule's states TOGETHER (warp w takes frames w, w + 8, ...), so a state's f32 table (36 KB at 256 x 33) is
+  // pulled into L1 once per 32 cells instead of once per cell.
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float eps = 2.384185791015625e-07f;   // 2^-22, as k_emission_ffma
+  const float dterm = (float)(p.m.dim + 8);
+  uint64_t fbase, obase;
+  uint32_t nvalid, nu, ostride;
+  const uint32_t* ulist = nullptr;
+  if (p.dense) {
+    const uint64_t r0 = (uint64_t)blockIdx.x * 32;
+    fbase = p.f0 + r0;
+    nvalid = (uint32_t)min((uint64_t)32, p.n_cells / p.n_states - r0);
+    nu = p.n_states; ostride = p.n_states; obase = r0 * p.n_states;
+  } else {
+    const uint4 t = p.tasks[blockIdx.x];
+    const uint64_t uf0 = p.frame_off[t.x];
+    fbase = uf0 + t.y;
+    nvalid = min(32u, (uint32_t)(p.frame_off[t.x + 1] - uf0) - t.y);
+    ulist = p.uniq + p.uniq_off[t.x];
+    nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
+    ostride = p.nuniq_pad[t.x];
+    obase = p.E_off[t.x] + (uint64_t)t.y * ostride;
+  }
+  for (uint32_t cell = warp; cell < nu * 4 * 8; cell += 8) {
+    const uint32_t j = cell / 32, fr = cell % 32;       // all warps share j: fr = warp, warp + 8, warp + 16, warp + 24
+    if (fr >= nvalid) continue;
+    const uint32_t s = ulist ? ulist[j] : j;
+    const uint64_t frame = fbase + fr, e = obase + (uint64_t)fr * ostride + j;
+    const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
+    const float* xf = p.x + frame * p.m.dim;
+    float xr[4 * DV4];
+#pragma unroll
+    for (int q = 0; q < 4 * DV4; q++) xr[q] = q < (int)p.m.dim ? __ldg(xf + q) : 0.f;
+    const float4 g = __ldg(p.sguard + s);     // {cmin, cabs, Mmax, -}
+    auto score32 = [&](uint32_t k) {
+      const float4* hrow = p.h32 + (size_t)(p.pooled ? k0 : k) * DV4;   // pooled: the state's one row, broadcast
+      float acc = 0.f;
+#pragma unroll
+      for (int v = 0; v < DV4; v++) {
+        const float4 m = __ldg(p.mu32T + (size_t)v * p.m.Dtot + k), h = __ldg(hrow + v);
+        float t;
+        t = xr[4 * v + 0] - m.x; acc = fmaf(t * h.x, t, acc);
+        t = xr[4 * v + 1] - m.y; acc = fmaf(t * h.y, t, acc);
+        t = xr[4 * v + 2] - m.z; acc = fmaf(t * h.z, t, acc);
+        t = xr[4 * v + 3] - m.w; acc = fmaf(t * h.w, t, acc);
+      }
+      return acc + __ldg(p.c32 + k);
+    };
+    constexpr int kKeep = 8;                    // f32 scores of the first 8 rounds stay in registers for stage 2
+    float keep[kKeep];
+    float m32 = INFINITY;
+#pragma unroll
+    for (int j = 0; j < kKeep; j++) {
+      const uint32_t k = k0 + lane + 32 * j;
+      keep[j] = k < k1 ? score32(k) : INFINITY;
+      m32 = fminf(m32, keep[j]);
+    }
+    for (uint32_t k = k0 + lane + 32 * kKeep; k < k1; k += 32) m32 = fminf(m32, score32(k));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m32 = fminf(m32, __shfl_xor_sync(0xffffffffu, m32, o));
+    double acc = 0.0;                           // Mixtures.cpp:721
+    // stage 2, per group of 8 rounds (256 densities, in density order): ballot the kept densities, hand the i-th kept
+    // one to lane i (all of a group's survivors are evaluated in ONE divergent pass: row-major f64 mean rows, the
+    // reference's operation order), then add their exp(-s) in density order through shuffles
+    auto keep_test = [&](uint32_t k, float sc) {
+      if (k >= k1) return false;
+      const float dist = fmaxf(sc - g.x, 0.f);
+      const float guard = 2.f * eps * (dterm * dist + 2.f * sqrtf(dist * g.z) + g.y);
+      return !((sc - m32) > kSumDelta + guard);   // NaN scores are kept
+    };
+    for (uint32_t gbase = k0; gbase < k1; gbase += 32 * kKeep) {
+      uint32_t masks[kKeep];
+      uint32_t total = 0;
+#pragma unroll
+      for (int j = 0; j < kKeep; j++) {
+        const uint32_t k = gbase + 32 * j + lane;
+        bool take = false;
+        if (gbase + 32 * j < k1) take = keep_test(k, gbase == k0 ? keep[j] : (k < k1 ? score32(k) : INFINITY));
+        masks[j] = __ballot_sync(0xffffffffu, take);
+        total += __popc(masks[j]);
+      }
+      for (uint32_t done = 0; done < total; done += 32) {
+        // the (done + lane)-th kept density of the group
+        uint32_t want = done + lane, mine = 0xffffffffu;
+        bool found = false;
+#pragma unroll
+        for (int j = 0; j < kKeep; j++) {
+          const uint32_t c = __popc(masks[j]);
+          if (!found) {
+            if (want < c) { mine = gbase + 32 * j + __fns(masks[j], 0, want + 1); found = true; }
+            else want -= c;
+          }
+        }
+        double ev = 0.0;
+        if (mine != 0xffffffffu) ev = exp(-sgmm_exact_score_rm(p.m, xf, mine));
+        const uint32_t nb = min(32u, total - done);
+        for (uint32_t l = 0; l < nb; l++) acc = __dadd_rn(acc, __shfl_sync(0xffffffffu, ev, l));
+      }
+    }
+    if (lane == 0) {
+      p.out[e] = -log(acc);                     // :727
+      if (p.argmin) p.argmin[e] = 0;
+      if (p.amin16) p.amin16[e] = 0;
+    }
+  }
+}
+
 }  // namespace sgmm_tc
 
 // ---------------------------------------------------------------------------------------------------
@@ -1702,5 +1823,40 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   SGMM_LAUNCH_CHECK(c);
   cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE + 1], c->stream);
   c->stage_ms[SGMM_T_SCORE_REFINE] = -1.f;
+  return 0;
+}
+
+// Sum scores of every cell (dense: nframes x n_states, gathered: the ragged emission matrix) through k_sum_pruned.
+int sgmm_launch_emission_sum_pruned(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t dense_nframes, double* d_scores,
+                                    uint32_t* d_argmin, bool* handled) {
+  using namespace sgmm_tc;
+  *handled = false;
+  if (!c->sum_prune || !(c->dv4 == 7 || c->dv4 == 9 || c->dv4 == 12 || c->dv4 == 16) || !c->d_mu32T.p) return 0;
+  RefineParams r{};
+  r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
+  r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;
+  r.m.meanR = c->d_meanR.p; r.m.invU = c->d_invU.p; r.m.var_of = c->d_var_of.p; r.m.dimP = c->dimP;
+  r.state_off = c->d_state_off.p; r.x = c->d_x.p;
+  r.n_cells = dense ? dense_nframes * c->n_states : c->E_elems;
+  r.dense = dense ? 1 : 0; r.f0 = dense_f0; r.n_states = c->n_states; r.n_utts = c->n_utts;
+  r.frame_off = c->d_frame_off.p; r.E_off = c->d_E_off.p; r.uniq = c->d_uniq.p; r.uniq_off = c->d_uniq_off.p;
+  r.nuniq_pad = c->d_nuniq_pad.p;
+  r.out = dense ? d_scores : c->d_E.p; r.argmin = dense ? d_argmin : nullptr;
+  r.amin16 = dense ? nullptr : c->d_Amin.p;
+  r.pooled = c->pooled_states ? 1 : 0;
+  r.mu32T = c->d_mu32T.p; r.h32 = c->d_h32.p; r.c32 = c->d_c32.p; r.sguard = c->d_sguard.p;
+  if (r.n_cells == 0) { *handled = true; return 0; }
+  if (!dense)   // padding columns of the ragged matrix are never written by the kernel: keep them defined
+    SGMM_CHECK(c, cudaMemsetAsync(c->d_E.p, 0, c->E_elems * sizeof(double), c->stream));
+  r.tasks = dense ? nullptr : c->d_tasks.p;       // granules of 32 frames
+  const unsigned grid = dense ? (unsigned)((dense_nframes + 31) / 32) : (unsigned)c->n_tasks;
+  switch (c->dv4) {
+    case 7: k_sum_pruned<7><<<grid, 256, 0, c->stream>>>(r); break;
+    case 9: k_sum_pruned<9><<<grid, 256, 0, c->stream>>>(r); break;
+    case 12: k_sum_pruned<12><<<grid, 256, 0, c->stream>>>(r); break;
+    default: k_sum_pruned<16><<<grid, 256, 0, c->stream>>>(r); break;
+  }
+  SGMM_LAUNCH_CHECK(c);
+  *handled = true;
   return 0;
 }

@@ -7,6 +7,7 @@
 // Density scores are the reference's f64 operation order (sgmm_exact_score), so they are bit-identical; exp / log are
 // CUDA's f64 functions (<= 1 ulp from glibc's), hence sum scores and soft statistics agree to ~1e-15 relative, not
 // bit for bit (tests demand 1e-12).  FP64-pipe bound; this branch has no f32 filter (every density contributes).
+// The (frame, state) emission pass with sum scores is k_emission_f64<true> in k_score.cu.
 //
 // Soft accumulation is deterministic: frames are stably sorted by aligned state (the radix sort of k_accum.cu), a
 // state's frames are cut into items of kSoftItem consecutive frames, one CTA walks an item in frame order keeping
@@ -27,77 +28,11 @@ ExactTables exact_tables(const sgmm_ctx* c) {
   return m;
 }
 
-// ---- sum scores of (frame, state) cells ---------------------------------------------------------------------
-// One warp per 32 consecutive frames of one utterance (gathered) or of the dense range; lane = frame.  Table reads
-// are warp-uniform (one density at a time, all lanes); every lane walks its own feature row (L1-resident).
-struct SumParams {
-  ExactTables m;
-  const uint32_t* state_off;
-  const float* x;
-  uint64_t n_tasks;
-  const uint4* tasks;
-  const uint64_t* frame_off;
-  const uint32_t* uniq;
-  const uint32_t* uniq_off;
-  const uint32_t* nuniq_pad;
-  const uint64_t* E_off;
-  double* E;
-  uint16_t* Amin;
-  int dense;
-  uint64_t f0, nframes;
-  uint32_t n_states;
-  double* scores;
-  uint32_t* argmin;
-};
-
-constexpr int kSumWarps = 4;
-
 __device__ __forceinline__ double sum_score_lane(const ExactTables& m, const float* __restrict__ xs, uint32_t k0,
                                                  uint32_t k1) {
   double acc = 0.0;                                                        // Mixtures.cpp:721
   for (uint32_t k = k0; k < k1; k++) acc = __dadd_rn(acc, exp(-sgmm_exact_score(m, xs, k)));   // :723-725
   return -log(acc);                                                        // :727
-}
-
-__global__ void __launch_bounds__(kSumWarps * 32) k_emission_sum(SumParams p) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint64_t task = (uint64_t)blockIdx.x * kSumWarps + warp;
-  if (task >= p.n_tasks) return;
-  uint64_t fbase;
-  uint32_t nvalid, nu, out_stride;
-  const uint32_t* ulist = nullptr;
-  double* out;
-  uint32_t* amin = nullptr;
-  uint16_t* amin16 = nullptr;
-  if (p.dense) {
-    const uint64_t r0 = task * 32;
-    fbase = p.f0 + r0;
-    nvalid = (uint32_t)min((uint64_t)32, p.nframes - r0);
-    nu = p.n_states;
-    out_stride = p.n_states;
-    out = p.scores ? p.scores + r0 * p.n_states : nullptr;
-    amin = p.argmin ? p.argmin + r0 * p.n_states : nullptr;
-  } else {
-    const uint4 t = p.tasks[task];
-    const uint64_t uf0 = p.frame_off[t.x];
-    const uint32_t T = (uint32_t)(p.frame_off[t.x + 1] - uf0);
-    fbase = uf0 + t.y;
-    nvalid = min(32u, T - t.y);
-    ulist = p.uniq + p.uniq_off[t.x];
-    nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
-    out_stride = p.nuniq_pad[t.x];
-    out = p.E + p.E_off[t.x] + (uint64_t)t.y * out_stride;
-    amin16 = p.Amin + p.E_off[t.x] + (uint64_t)t.y * out_stride;
-  }
-  if (lane >= (int)nvalid) return;
-  const float* xf = p.x + (fbase + lane) * p.m.dim;
-  for (uint32_t j = 0; j < nu; j++) {
-    const uint32_t s = ulist ? ulist[j] : j;
-    const double sc = sum_score_lane(p.m, xf, p.state_off[s], p.state_off[s + 1]);
-    if (out) out[(uint64_t)lane * out_stride + j] = sc;
-    if (amin) amin[(uint64_t)lane * out_stride + j] = 0;       // no density is singled out by the sum
-    if (amin16) amin16[(uint64_t)lane * out_stride + j] = 0;
-  }
 }
 
 // sum score of every frame against its ALIGNED state (Trainer::calc_am_score with max_approx_ == false)
@@ -272,25 +207,6 @@ __global__ void __launch_bounds__(256) k_soft_final(const double* __restrict__ p
 }
 
 }  // namespace
-
-int sgmm_launch_emission_sum(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
-                             uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin) {
-  if (n_tasks == 0) return 0;
-  SumParams p{};
-  p.m = exact_tables(c);
-  p.state_off = c->d_state_off.p;
-  p.x = c->d_x.p;
-  p.n_tasks = n_tasks;
-  p.tasks = d_tasks;
-  p.frame_off = c->d_frame_off.p; p.uniq = c->d_uniq.p; p.uniq_off = c->d_uniq_off.p;
-  p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p; p.Amin = c->d_Amin.p;
-  p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
-  p.scores = d_scores; p.argmin = d_argmin;
-  const uint64_t grid = (n_tasks + kSumWarps - 1) / kSumWarps;
-  k_emission_sum<<<(unsigned)grid, kSumWarps * 32, 0, c->stream>>>(p);
-  SGMM_LAUNCH_CHECK(c);
-  return 0;
-}
 
 int sgmm_launch_sum_aligned(sgmm_ctx* c) {
   if (c->n_frames == 0) return 0;

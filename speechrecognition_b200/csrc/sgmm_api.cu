@@ -316,6 +316,7 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
     for (uint32_t s = 0; s < n_states && pooled; s++)
       for (uint32_t j = state_off[s] + 1; j < state_off[s + 1] && pooled; j++)
         pooled = memcmp(inv_var + (size_t)j * dim, inv_var + (size_t)state_off[s] * dim, dim * sizeof(double)) == 0;
+    c->pooled_states = pooled;
     const uint32_t Kused = pooled ? dim + 1 : 2 * dim + 1;
     const uint32_t KP = (Kused + 7) / 8 * 8;     // whole k-steps of 8 (32-byte swizzle atoms: no further padding)
     c->tc_ok = KP / 8 <= 13;                     // A (hi, lo) = 16 * ksteps TMEM columns per 128 frames, <= 256
@@ -762,6 +763,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "async_upload")) { c->async_upload = value != 0; return 0; }
   if (!strcmp(key, "tc_wide")) { c->tc_wide = (int)value; return 0; }   // takes effect at the next sgmm_set_model
   if (!strcmp(key, "max_approx")) { c->max_approx = value != 0; return 0; }
+  if (!strcmp(key, "sum_prune")) { c->sum_prune = value != 0; return 0; }
   if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }

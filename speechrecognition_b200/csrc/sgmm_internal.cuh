@@ -157,6 +157,8 @@ struct sgmm_ctx {
   bool use_cache = true;          // option "rescore_cache"
   bool max_approx = true;         // option "max_approx": score() = min_score (1) or sum_score (0), Mixtures.cpp:737-744
   bool E_max_approx = true;       // which of the two the resident emission matrix holds
+  bool sum_prune = true;          // option "sum_prune": sum scores through the f32-pruned kernel (k_sum_pruned)
+  bool pooled_states = false;     // every state's densities share one inverse-variance row (set by sgmm_set_model)
   bool ali_has_cols = false;      // resident alignment came from sgmm_align (d_fcol valid)
   std::vector<ViterbiClass> vclasses;
   DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)
@@ -245,6 +247,9 @@ int sgmm_sort_frames(sgmm_ctx* c, const uint32_t* keys, uint32_t n_keys, const u
 int sgmm_launch_emission_sum(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
                              uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin);
 int sgmm_launch_sum_aligned(sgmm_ctx* c);
+// f32-pruned sum scores (k_score_tc.cu); *handled = false when the model shape has no f32 tables
+int sgmm_launch_emission_sum_pruned(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t dense_nframes, double* d_scores,
+                                    uint32_t* d_argmin, bool* handled);
 int sgmm_launch_accumulate_soft(sgmm_ctx* c);
 int sgmm_launch_score_sum(sgmm_ctx* c);
 int sgmm_nccl_allreduce(sgmm_ctx* c, double* d_buf, size_t n);

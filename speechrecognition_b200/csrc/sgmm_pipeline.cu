@@ -29,6 +29,9 @@ void reset_stage(sgmm_ctx* c) {
 int launch_emission_any(sgmm_ctx* c, bool dense, uint64_t f0, uint64_t nf, double* scores, uint32_t* argmin) {
   if (!c->max_approx) {   // score() = sum_score (Mixtures.cpp:737-744): every density contributes, exact f64 only
     if (sgmm_wait_features(c)) return 1;
+    bool handled = false;   // f32-pruned kernel when the model has f32 tables (dim <= 64), else the plain f64 sum
+    if (sgmm_launch_emission_sum_pruned(c, dense, f0, nf, scores, argmin, &handled)) return 1;
+    if (handled) return 0;
     if (dense) return sgmm_launch_emission_sum(c, nullptr, (nf + 31) / 32, true, f0, nf, scores, argmin);
     return sgmm_launch_emission_sum(c, c->d_tasks.p, c->n_tasks, false, 0, 0, nullptr, nullptr);
   }

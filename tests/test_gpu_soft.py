@@ -47,6 +47,20 @@ def test_sum_scores_dense(soft):
     assert np.all(mins[fin] >= scores[fin] - 1e-9) and np.any(mins[fin] > scores[fin] + 1e-6)
 
 
+def test_pruned_sum_equals_full_sum(soft):
+    """The f32-pruned kernel (k_sum_pruned: densities certainly more than 45 above the state's minimum are left
+    out) against the plain f64 sum over every density: at most a rounding apart."""
+    P, corp, ali, ctx, _ = soft
+    ctx.set_option("sum_prune", 0)
+    full, _ = ctx.score_all(0, 600)
+    ctx.set_option("sum_prune", 1)
+    pruned, _ = ctx.score_all(0, 600)
+    assert np.array_equal(np.isinf(full), np.isinf(pruned))
+    fin = np.isfinite(full)
+    assert np.max(np.abs(pruned[fin] - full[fin]) / np.abs(full[fin])) <= 4.5e-16
+    assert np.mean(pruned[fin] == full[fin]) > 0.99
+
+
 def test_align_with_sum_scores(soft):
     P, corp, ali, ctx, _ = soft
     got, costs = ctx.align()
