@@ -7,5 +7,5 @@ timeout 600 python bench.py --impl reference > gpurun_out/w/bench_ref.json 2> gp
 timeout 600 python bench.py > gpurun_out/w/bench.json 2> gpurun_out/w/bench.err
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/w/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/w/ncu_l.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_tc_gemm256 -s 2 -c 1 -o gpurun_out/w/gemm -f python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/w/ncu_g.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_viterbi -s 8 -c 1 -o gpurun_out/w/vit -f python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/w/ncu_v.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_tc_refine_sm -s 1 -c 1 -o gpurun_out/w/refine -f python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/w/ncu_v.log 2>&1
 tail -3 gpurun_out/w/pytest.log; cat gpurun_out/w/bench.json
