@@ -158,6 +158,8 @@ int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
  *   1 = min_score (maximum approximation), 0 = sum_score = -log sum_k exp(-density_score_k) (:719-728).  With 0,
  *   sgmm_score_all / sgmm_align / sgmm_recognize / sgmm_am_score_sum use sum scores (exact-f64 kernel; argmin outputs
  *   are 0).  Independent of which accumulate entry point is called, as in the reference (Training.cpp:145-149).
+ * "sum_prune" (default 1): sum scores through the f32-pruned kernel (densities certainly more than 45 above the state's
+ *   minimum are left out: at most one rounding from the full sum); 0 = plain f64 sum over every density.
  * "scorer": 0 = automatic choice by model shape, 1 = exact-f64 kernel, 2 = FP32-FFMA kernel with certified
  * f64 refinement, 3 = tcgen05 3xTF32 tensor-core GEMM with certified f64 refinement.  Every scorer returns
  * results bit-identical to the reference; the choice only moves time.
@@ -171,6 +173,7 @@ int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
  *   "tc_rescan" (0, 1): 0 two-stage rescan of near-tie cells (f32 prefilter, f64 candidates), 1 full f64 scan.
  * "tc_wide" (-1 auto, 0, 1; read by sgmm_set_model): 256-density GEMM tiles (the N = 256 kernel) instead of 128;
  *   auto picks them when some state has more than 128 densities and the tile ring fits shared memory.
+ * "tc_epi16" (default 0): sixteen instead of eight epilogue warps per GEMM unit (measured slower; kept as an A/B switch).
  * "tc_debug": timing experiments for the tensor-core kernel — any bit other than 32 (cycle profile, read with the
  *   "tc_prof1".."tc_prof12" counters) makes results INVALID; never set in production. */
 int sgmm_set_option(sgmm_ctx* ctx, const char* key, int64_t value);

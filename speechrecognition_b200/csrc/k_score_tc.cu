@@ -217,6 +217,50 @@ struct TcCount {
   }
 };
 
+// The two passes of the epilogue over accumulator columns [c_lo, c_hi) of one TMEM lane (= frame row): the minimum
+// m, the certified bound G = Gs + 4e-6 |m|, and (acc, idx) = number of columns below m + G and — when that is 1 —
+// the column.  Loads run one 16-column block ahead.
+__device__ __forceinline__ void tc_scan_columns(uint32_t tcol, uint32_t c_lo, uint32_t c_hi, float Gs, float& m,
+                                                float& acc, float& idx, float& G) {
+  uint32_t ra[16], rb[16];
+#pragma unroll
+  for (int e = 0; e < 16; e++) rb[e] = 0;
+  float mm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+  tc_ld16_nowait(tcol + c_lo, ra);
+  tc_ld_wait(ra);
+  for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
+    if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
+#pragma unroll
+    for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(ra[e]));
+    tc_ld_wait(rb);
+    if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
+    if (cc + 16 < c_hi) {
+#pragma unroll
+      for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(rb[e]));
+    }
+    tc_ld_wait(ra);
+  }
+  m = fminf(fminf(mm[0], mm[1]), fminf(mm[2], mm[3]));
+  G = Gs + 4e-6f * fabsf(m);
+  const float thr = m + G, nbig = -0x1p100f, T = thr * 0x1p100f;
+  const bool thr_ok = fabsf(thr) > 1e-20f && fabsf(thr) < 1e8f;   // else c may be fractional: uncertain
+  TcCount cnt;
+  cnt.init();
+  tc_ld16_nowait(tcol + c_lo, ra);
+  tc_ld_wait(ra);
+  for (uint32_t cc = c_lo; cc < c_hi; cc += 32) {
+    if (cc + 16 < c_hi) tc_ld16_nowait(tcol + cc + 16, rb);
+    cnt.block16(ra, nbig, T);
+    tc_ld_wait(rb);
+    if (cc + 32 < c_hi) tc_ld16_nowait(tcol + cc + 32, ra);
+    if (cc + 16 < c_hi) cnt.block16(rb, nbig, T);
+    tc_ld_wait(ra);
+  }
+  cnt.finish(acc, idx);
+  idx += (float)c_lo;
+  if (!thr_ok) acc = 2.f;
+}
+
 // Shared-memory matrix descriptor, K-major, SWIZZLE_32B.  One k-step (8 tf32 = 32 bytes) of a 128-row operand
 // is its own 4 KB block [128 rows][32 B]: 8-row groups are 256 B apart (SBO), LBO unused.  K = 2d+1 or d+1 is
 // short and odd-sized here (34 -> 5 k-steps at d = 33), so 32-byte atoms waste no shared memory or L2
@@ -683,7 +727,10 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
 // Ahi.Bhi, Alo.Bhi (hi slot), then Ahi.Blo (lo slot).  With two halves, half h always owns accumulator h.
 // F16: operands are fp16 hi / lo pairs (k-step = 16 halves) and the MMAs kind::f16 — same bytes per k-step, same
 // shared-memory images and descriptors, K = d + 1 = 34 takes 3 k-steps instead of 5 (see k_tc_prep16).
-template <int KS, bool F16>
+// E16: all sixteen epilogue warps work on every unit — warp = (lane quarter, one of four 64-column parts), each thread
+// owning the same row of BOTH halves — so that an accumulator is handed back in about half the time; the parts of a
+// (half, quarter) meet through shared memory once per state (three writers, one reader, 128-thread named barrier).
+template <int KS, bool F16, bool E16 = false>
 __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -739,9 +786,9 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
 
   // ---- one-time setup
   if (warp == 0 && lane == 0) {
-    mbar_init(a_full, 4 * nh);
+    mbar_init(a_full, E16 ? 4 : 4 * nh);
     for (uint32_t i = 0; i < nstage; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (uint32_t i = 0; i < kNumAcc; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 8); }
+    for (uint32_t i = 0; i < kNumAcc; i++) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], E16 ? 16 : 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -839,6 +886,107 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
       atomicAdd(p.prof + 5, (unsigned long long)w_tempty);       // waiting for the epilogue to hand an accumulator back
       atomicAdd(p.prof + 6, (unsigned long long)unit * 3 * ks * 2);   // MMAs issued, in N = 128 equivalents
       atomicAdd(p.prof + 7, 1ull);                               // CTAs
+    }
+  } else if (E16) {
+    // ===== epilogue warps, sixteen per unit: (lane quarter, 64-column part); thread = one row of both halves =====
+    const uint32_t quarter = warp & 3;
+    const uint32_t part = (uint32_t)(warp - 2) >> 2;              // columns [64 * part, 64 * part + 64) of every tile
+    const uint32_t lrow = quarter * 32 + lane;
+    const uint32_t tlane = tmem_base + ((quarter * 32) << 16);
+    if (part == 0) {   // A rows of this thread's frames (both halves): hi and lo parts into shared memory
+      for (uint32_t g = 0; g < nh; g++) {
+        const uint32_t row = g * BM + lrow;
+        const uint64_t fr = prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1);
+        const float4* ah = reinterpret_cast<const float4*>(p.Ahi + fr * KP);
+        const float4* al = reinterpret_cast<const float4*>(p.Alo + fr * KP);
+        unsigned char* hi_row = sA + (g * 2 + 0) * a_part + lrow * 32;
+        unsigned char* lo_row = sA + (g * 2 + 1) * a_part + lrow * 32;
+        const uint32_t sw = ((lrow >> 2) & 1u) << 4;
+        for (uint32_t kk = 0; kk < ks; kk++) {
+          *reinterpret_cast<float4*>(hi_row + kk * 4096 + (0 ^ sw)) = __ldg(ah + 2 * kk);
+          *reinterpret_cast<float4*>(hi_row + kk * 4096 + (16 ^ sw)) = __ldg(ah + 2 * kk + 1);
+          *reinterpret_cast<float4*>(lo_row + kk * 4096 + (0 ^ sw)) = __ldg(al + 2 * kk);
+          *reinterpret_cast<float4*>(lo_row + kk * 4096 + (16 ^ sw)) = __ldg(al + 2 * kk + 1);
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(a_full);
+    }
+    float2 xn[2];
+    uint64_t my_cell[2];
+    const uint16_t* my_map[2];
+#pragma unroll
+    for (int g = 0; g < 2; g++) {
+      const uint32_t row = min((uint32_t)g, nh - 1) * BM + lrow;
+      xn[g] = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
+      my_cell[g] = prow ? prow[row].cell : out_base + (uint64_t)row * out_stride;
+      my_map[g] = prow ? p.pack_colmap + prow[row].colmap : nullptr;
+    }
+    uint32_t it = 0;
+    for (uint32_t j = 0; j < nu; j++) {
+      const uint32_t s = ulist ? ulist[j] : j;
+      const float4 g4 = __ldg(p.sguard + s);
+      float Gs[2], Bbest[2], Bsecond[2], Bacc[2], Bidx[2], BG[2];
+#pragma unroll
+      for (int g = 0; g < 2; g++) {
+        Gs[g] = 2.002f * p.eps * (xn[g].x * g4.x + xn[g].y * g4.y + g4.z);
+        Bbest[g] = INFINITY; Bsecond[g] = INFINITY; Bacc[g] = 0.f; Bidx[g] = 0.f; BG[g] = 0.f;
+      }
+      uint32_t n0 = 0;
+      for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, it++) {
+        const uint32_t N = p.tile_info[t].y;
+        const uint32_t c_lo = part * 64, c_hi = min(N, c_lo + 64);
+#pragma unroll
+        for (int g = 0; g < 2; g++) {
+          if ((uint32_t)g < nh) {
+            const uint32_t unit = it * nh + g, buf = unit & 1u, use = unit >> 1;
+            mbar_wait(&tfull[buf], use & 1);
+            tc_fence_after();
+            float m = INFINITY, acc = 0.f, idx = 0.f, G = 0.f;
+            if (!(p.debug & 1) && c_lo < c_hi) tc_scan_columns(tlane + buf * 256, c_lo, c_hi, Gs[g], m, acc, idx, G);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[buf]);
+            if (m < Bbest[g]) { Bsecond[g] = Bbest[g]; Bbest[g] = m; Bacc[g] = acc; Bidx[g] = (float)n0 + idx; BG[g] = G; }
+            else Bsecond[g] = fminf(Bsecond[g], m);
+          }
+        }
+        n0 += N;
+      }
+      // the four column parts of a (half, quarter) meet through shared memory once per state
+      float* slots = xchg + (size_t)(j & 1) * (2 * 3 * BM * 5);    // [slot][half][part - 1][row][5]
+      if (part > 0) {
+#pragma unroll
+        for (int g = 0; g < 2; g++) {
+          if ((uint32_t)g < nh) {
+            float* sl = slots + ((size_t)(g * 3 + part - 1) * BM + lrow) * 5;
+            sl[0] = Bbest[g]; sl[1] = Bsecond[g]; sl[2] = Bacc[g]; sl[3] = Bidx[g]; sl[4] = BG[g];
+          }
+        }
+      }
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + quarter) : "memory");
+      if (part == 0) {
+#pragma unroll
+        for (int g = 0; g < 2; g++) {
+          if ((uint32_t)g < nh) {
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+              const float* sl = slots + ((size_t)(g * 3 + q) * BM + lrow) * 5;
+              const float ob = sl[0], os = sl[1];
+              if (ob < Bbest[g]) { Bsecond[g] = fminf(Bbest[g], os); Bbest[g] = ob; Bacc[g] = sl[2]; Bidx[g] = sl[3]; BG[g] = sl[4]; }
+              else Bsecond[g] = fminf(Bsecond[g], ob);
+            }
+            const uint32_t row = g * BM + lrow;
+            if (row < nvalid) {
+              const bool certain = Bacc[g] == 1.0f && Bsecond[g] > Bbest[g] + BG[g];
+              const uint32_t col = my_map[g] ? (uint32_t)my_map[g][j] : j;
+              if (col != 0xFFFFu || !my_map[g]) p.cand[my_cell[g] + col] = certain ? (uint32_t)Bidx[g] : kUncertain;
+            }
+          }
+        }
+      }
     }
   } else {
     // ===== epilogue warps: (half, lane quarter, column part) =====
@@ -1600,7 +1748,7 @@ namespace {
 // shared memory: Alo + the B ring (Ahi lives in tensor memory)
 constexpr size_t kSmemLimit = 227 * 1024;
 size_t tc_smem256(uint32_t ks, int nhalf, int nslot = 3) {   // A (hi, lo) of every half + half-stage slots + barriers + exchange
-  return 1024 + (size_t)nhalf * 2 * ks * 4096 + (size_t)nslot * ks * 8192 + 256 + 2 * 2 * 128 * 5 * sizeof(float);
+  return 1024 + (size_t)nhalf * 2 * ks * 4096 + (size_t)nslot * ks * 8192 + 256 + 2 * 2 * 3 * 128 * 5 * sizeof(float);
 }
 size_t tc_smem(uint32_t stage_bytes, int nhalf, int nstage, int a_smem) {   // A of every half + the B ring + barriers
   return 1024 + (size_t)nhalf * (stage_bytes / 2) * (a_smem == 1 ? 2 : 1) + (size_t)nstage * stage_bytes + 256 +
@@ -1748,7 +1896,10 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     if (g_end > g_prev) {
       const unsigned grid = (unsigned)(g_end - g_prev);
       p.tasks = dense ? nullptr : gemm_tasks + g_prev;
-      if (f16 && ks == 3) {          // d = 32..46 pooled, fp16 operands
+      if (f16 && ks == 3 && c->tc_epi16) {   // d = 32..46 pooled, fp16 operands, sixteen epilogue warps per unit
+        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<3, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tc_gemm256<3, true, true><<<grid, 576, smem, st>>>(p);
+      } else if (f16 && ks == 3) {   // d = 32..46 pooled, fp16 operands
         SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_tc_gemm256<3, true><<<grid, 576, smem, st>>>(p);
       } else if (f16) {

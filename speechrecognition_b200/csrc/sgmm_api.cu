@@ -764,6 +764,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_wide")) { c->tc_wide = (int)value; return 0; }   // takes effect at the next sgmm_set_model
   if (!strcmp(key, "max_approx")) { c->max_approx = value != 0; return 0; }
   if (!strcmp(key, "sum_prune")) { c->sum_prune = value != 0; return 0; }
+  if (!strcmp(key, "tc_epi16")) { c->tc_epi16 = (int)value; return 0; }
   if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }

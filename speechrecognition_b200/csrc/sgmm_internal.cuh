@@ -137,6 +137,7 @@ struct sgmm_ctx {
   DevBuf<uint2> d_tile_info16;
   DevBuf<float4> d_sguard16;
   int tc_A_form = 0;               // which form the resident A rows (d_Ahi / d_Alo / d_xnorm) are in: 0 tf32, 1 fp16
+  int tc_epi16 = 0;                // option "tc_epi16": sixteen epilogue warps per GEMM unit (k_tc_gemm256<.., E16>)
   int tc_rescan = 0;               // option "tc_rescan": 0 two-stage (f32 prefilter, f64 candidates), 1 full f64 scan
   size_t n_sm_items = 0;
   DevBuf<uint4> d_sm_items;        // {state, first entry, entries, cells}
