@@ -35,6 +35,8 @@ struct RecParams {
   const uint32_t* word_base;   // [n_words] first live slot of the word
   const uint32_t* word_len;    // [n_words]
   const uint32_t* word_first;  // [n_words] first state
+  const uint32_t* slot_order;  // [n_live] slots in processing order: the word-entry slots (positions 0 and 1) first
+  int stage_rows;              // emission rows staged in shared memory one frame ahead (cp.async)
   double loop, forward, skip, word_penalty, am_threshold;
   uint32_t silence_state;
   // outputs
@@ -60,14 +62,19 @@ __global__ void __launch_bounds__(kRecWarps * 32) k_recognize(RecParams p) {
   uint32_t* s_base = s_state + nl;
   uint32_t* s_len = s_base + W;
   uint32_t* s_first = s_len + W;
-  const size_t lex_words = (size_t)2 * nl + 3 * W;
+  uint32_t* s_ord = s_first + W;
+  const size_t lex_words = (size_t)3 * nl + 3 * W;
   double* warp_mem = reinterpret_cast<double*>(smem_raw + ((lex_words * 4 + 15) & ~(size_t)15));
-  const size_t per_warp = (size_t)2 * nl + ((2 * nl + 3) / 4);   // doubles: 2 score buffers + 2 u16 bkp buffers
+  const size_t row_d = p.stage_rows ? (size_t)2 * p.n_states : 0;   // two staged emission rows
+  const size_t per_warp = (size_t)2 * nl + ((2 * nl + 3) / 4) + row_d;   // doubles: 2 score buffers + 2 u16 bkp buffers + rows
   double* sc0 = warp_mem + warp * per_warp;
   double* sc1 = sc0 + nl;
   uint16_t* bk0 = reinterpret_cast<uint16_t*>(sc1 + nl);
   uint16_t* bk1 = bk0 + nl;
-  for (uint32_t i = threadIdx.x; i < nl; i += blockDim.x) { s_info[i] = p.slot_info[i]; s_state[i] = p.slot_state[i]; }
+  double* srow = sc0 + (size_t)2 * nl + ((2 * nl + 3) / 4);
+  for (uint32_t i = threadIdx.x; i < nl; i += blockDim.x) {
+    s_info[i] = p.slot_info[i]; s_state[i] = p.slot_state[i]; s_ord[i] = p.slot_order[i];
+  }
   for (uint32_t i = threadIdx.x; i < W; i += blockDim.x) {
     s_base[i] = p.word_base[i]; s_len[i] = p.word_len[i]; s_first[i] = p.word_first[i];
   }
@@ -88,10 +95,26 @@ __global__ void __launch_bounds__(kRecWarps * 32) k_recognize(RecParams p) {
 
   double* prev = sc0; double* next = sc1;
   uint16_t* pbk = bk0; uint16_t* nbk = bk1;
+  // emission row of frame t - 1 -> srow[(t - 1) & 1], copied one frame ahead (8-byte cp.async, any n_states)
+  auto stage_row = [&](uint32_t fr) {
+    const double* src = E + (size_t)fr * p.n_states;
+    double* dst = srow + (size_t)(fr & 1u) * p.n_states;
+    for (uint32_t k = lane; k < p.n_states; k += 32)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + k)), "l"(src + k) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (p.stage_rows && T > 0) stage_row(0);
   for (uint32_t t = 1; t <= T; t++) {
     const double* am = E + (size_t)(t - 1) * p.n_states;
+    if (p.stage_rows) {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncwarp();
+      if (t < T) stage_row(t);          // the other buffer: its last readers finished before the previous frame's end
+      am = srow + (size_t)((t - 1) & 1u) * p.n_states;
+    }
     double my_best = inf;
-    for (uint32_t i = lane; i < nl; i += 32) {
+    for (uint32_t oi = lane; oi < nl; oi += 32) {
+      const uint32_t i = s_ord[oi];
       const uint32_t info = s_info[i];
       const uint32_t w = info & 0xffu, pos = (info >> 8) & 0xffu, L = (info >> 16) & 0xffu;
       const bool in_word = (info >> 31) != 0;          // pos < L (a real position of the word)
@@ -102,7 +125,7 @@ __global__ void __launch_bounds__(kRecWarps * 32) k_recognize(RecParams p) {
       const bool entry = pos <= 1;
       if (entry) {
         const uint32_t first = s_first[w];
-        am_e = __ldg(am + first);
+        am_e = am[first];
         pre_e = tdp_of(p, first, pos + 1);
       }
       const double wp = (w != p.silence_word) ? p.word_penalty : 0.0;
@@ -119,7 +142,7 @@ __global__ void __launch_bounds__(kRecWarps * 32) k_recognize(RecParams p) {
       // ... then the word's own positions, ascending: pos-2, pos-1, pos (never its last position, which only exits) ...
       if (in_word) {
         const uint32_t st = s_state[i];
-        const double am_s = __ldg(am + st);
+        const double am_s = am[st];
 #pragma unroll
         for (int jump = 2; jump >= 0; jump--) {
           if ((int)pos - jump < 0) continue;
@@ -219,8 +242,13 @@ int sgmm_build_lexicon(sgmm_ctx* c, uint32_t n_words, const uint32_t* word_off, 
     SGMM_CHECK(c, cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
     return 0;
   };
+  // processing order: the entry slots (positions 0 / 1: they walk every word end) first, so that they share warp
+  // iterations instead of making every iteration wait for one of them
+  std::vector<uint32_t> order;
+  for (uint32_t i = 0; i < info.size(); i++) if (((info[i] >> 8) & 0xffu) <= 1) order.push_back(i);
+  for (uint32_t i = 0; i < info.size(); i++) if (((info[i] >> 8) & 0xffu) > 1) order.push_back(i);
   if (up(c->d_lex_info, info) || up(c->d_lex_state, state) || up(c->d_lex_base, base) || up(c->d_lex_len, len) ||
-      up(c->d_lex_first, first))
+      up(c->d_lex_first, first) || up(c->d_lex_order, order))
     return 1;
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   return 0;
@@ -234,14 +262,19 @@ int sgmm_launch_recognize(sgmm_ctx* c, uint32_t u0, uint32_t n, uint64_t chunk_f
   p.frame_off = c->d_rec_frame_off.p; p.u0 = u0; p.n_utts = n;
   p.n_words = c->lex_words; p.n_live = c->lex_live; p.silence_word = c->lex_silence;
   p.slot_info = c->d_lex_info.p; p.slot_state = c->d_lex_state.p; p.word_base = c->d_lex_base.p;
-  p.word_len = c->d_lex_len.p; p.word_first = c->d_lex_first.p;
+  p.word_len = c->d_lex_len.p; p.word_first = c->d_lex_first.p; p.slot_order = c->d_lex_order.p;
   p.loop = c->tdp_loop; p.forward = c->tdp_forward; p.skip = c->tdp_skip; p.silence_state = c->silence_state;
   p.word_penalty = word_penalty; p.am_threshold = am_threshold;
   p.tb = c->d_rec_tb.p; p.tb_off = c->d_rec_tb_off.p; p.words_raw = c->d_rec_words.p;
   p.n_words_out = c->d_rec_nwords.p; p.score_out = c->d_rec_score.p;
   const size_t nl = c->lex_live, W = c->lex_words;
-  const size_t lex_bytes = ((2 * nl + 3 * W) * 4 + 15) & ~(size_t)15;
-  const size_t per_warp = (2 * nl + ((2 * nl + 3) / 4)) * sizeof(double);
+  const size_t lex_bytes = ((3 * nl + 3 * W) * 4 + 15) & ~(size_t)15;
+  size_t per_warp = (2 * nl + ((2 * nl + 3) / 4) + 2 * (size_t)c->n_states) * sizeof(double);
+  p.stage_rows = 1;
+  if (lex_bytes + kRecWarps * per_warp > 96 * 1024) {   // many states: read the emission rows from L2 instead
+    p.stage_rows = 0;
+    per_warp = (2 * nl + ((2 * nl + 3) / 4)) * sizeof(double);
+  }
   const size_t smem = lex_bytes + kRecWarps * per_warp;
   if (smem > 200 * 1024) SGMM_FAIL(c, "recognize: lexicon too large for shared memory");
   SGMM_CHECK(c, cudaFuncSetAttribute(k_recognize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -185,7 +185,7 @@ struct sgmm_ctx {
 
   // ---- recognition (k_recognize.cu): lexicon tables + per-call buffers
   uint32_t lex_words = 0, lex_live = 0, lex_silence = 0, lex_max_state = 0;
-  DevBuf<uint32_t> d_lex_info, d_lex_state, d_lex_base, d_lex_len, d_lex_first;
+  DevBuf<uint32_t> d_lex_info, d_lex_state, d_lex_base, d_lex_len, d_lex_first, d_lex_order;
   DevBuf<uint64_t> d_rec_frame_off, d_rec_tb_off;
   DevBuf<uint32_t> d_rec_tb, d_rec_words, d_rec_nwords;
   DevBuf<double> d_rec_score;

@@ -162,9 +162,10 @@ int sgmm_recognize(sgmm_ctx* c, uint32_t n_utts, const uint64_t* frame_off, doub
   SGMM_CHECK(c, c->d_rec_score.reserve(n_utts));
   SGMM_CHECK(c, cudaMemcpyAsync(c->d_rec_frame_off.p, frame_off, (n_utts + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
   SGMM_CHECK(c, cudaMemcpyAsync(c->d_rec_tb_off.p, tb_off.data(), (n_utts + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
-  // dense emission scores for runs of whole utterances (<= ~256 MB of scores per run), then one warp per utterance
+  // dense emission scores for runs of whole utterances (<= ~4 GB of scores per run: the search is one warp per
+  // utterance and latency-bound, so a run should hold thousands of utterances), then one warp per utterance
   const uint32_t N = c->n_states;
-  const uint64_t budget = std::max<uint64_t>(65536, (256ull << 20) / (N * sizeof(double)));
+  const uint64_t budget = std::max<uint64_t>(65536, (4096ull << 20) / (N * sizeof(double)));
   for (uint32_t u0 = 0; u0 < n_utts;) {
     uint32_t u1 = u0 + 1;
     while (u1 < n_utts && frame_off[u1 + 1] - frame_off[u0] <= budget) u1++;
