@@ -88,7 +88,8 @@ int sgmm_process_features(sgmm_ctx* ctx, const float* raw, uint64_t n_frames, ui
                           const double* mean, const double* stddev, int energy_max_norm, float* out);
 
 /* ---- scoring (K1) --------------------------------------------------------------------------- */
-/* MixtureModel::min_score (Mixtures.cpp:696-713) for every frame in [f0, f1) and every state:
+/* MixtureModel::min_score (Mixtures.cpp:696-713; sum_score, :719-728, when option "max_approx" is 0) for every frame
+ * in [f0, f1) and every state:
  * scores[(f-f0)*n_states + s] (f64, bit-identical to the reference), argmin likewise = position k
  * within mixtures_[s].  Either output may be NULL.  Replaces the per-cell score() calls of
  * Alignment.cpp:90 / Recognizer.cpp:149,179 by one batched pass (the prepare_sequence idiom of
