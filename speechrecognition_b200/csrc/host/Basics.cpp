@@ -149,4 +149,40 @@ std::vector<size_t> shard_utterances(std::vector<size_t> const& frame_off, int w
   return bounds;
 }
 
+// ---- SignalAnalysis (load-time feature processing, SignalAnalysis.cpp:46-56,371-399) ---------------------------
+SignalAnalysis::SignalAnalysis(Configuration const& config)
+    : energy_max_norm(config.get_bool("energy-max-norm", true)),
+      n_features_in_file(config.get_uint("n-features-file", 12u)),
+      n_features_first(config.get_uint("n-features-first", 12u)),
+      n_features_second(config.get_uint("n-features-second", 1u)),
+      n_features_total(n_features_in_file + n_features_first + n_features_second),
+      deriv_step(config.get_uint("deriv-step", 3u)) {}
+
+void SignalAnalysis::read_normalization_file(std::istream& in) {
+  std::vector<double> mean(n_features_total), stddev(n_features_total);
+  in.read(reinterpret_cast<char*>(mean.data()), (std::streamsize)(sizeof(double) * mean.size()));
+  in.read(reinterpret_cast<char*>(stddev.data()), (std::streamsize)(sizeof(double) * stddev.size()));
+  if (!in) throw std::runtime_error("SignalAnalysis: normalization file too short");
+  set_normalization(mean, stddev);
+}
+
+void SignalAnalysis::set_normalization(std::vector<double> const& mean, std::vector<double> const& stddev) {
+  if (mean.size() != n_features_total || stddev.size() != n_features_total)
+    throw std::runtime_error("SignalAnalysis: normalization vectors must have n_features_total entries");
+  mean_ = mean;
+  stddev_ = stddev;
+  apply_mean_var_normalization_ = true;
+}
+
+void SignalAnalysis::process_features(Device& dev, const float* raw, size_t n_frames, std::vector<size_t> const& frame_off,
+                                      float* out) const {
+  if (frame_off.size() < 2) throw std::runtime_error("SignalAnalysis: no segments");
+  std::vector<uint64_t> off(frame_off.begin(), frame_off.end());
+  dev.check(sgmm_process_features(dev.ctx(), raw, n_frames, (uint32_t)n_features_in_file, (uint32_t)n_features_first,
+                                  (uint32_t)n_features_second, (uint32_t)deriv_step, (uint32_t)(off.size() - 1), off.data(),
+                                  apply_mean_var_normalization_ ? mean_.data() : nullptr,
+                                  apply_mean_var_normalization_ ? stddev_.data() : nullptr, energy_max_norm ? 1 : 0, out),
+            "sgmm_process_features");
+}
+
 }  // namespace sietill_b200

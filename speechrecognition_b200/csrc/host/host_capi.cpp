@@ -335,4 +335,26 @@ int sthost_linear_segmentation(int approx, const float* x, uint64_t T, uint32_t 
   });
 }
 
+
+// SignalAnalysis (n-features-file/first/second, deriv-step, energy-max-norm as in the reference's configuration) with an
+// optional normalization FILE (the reference's format): process all segments on the GPU of `model`'s context.
+int sthost_process_features(void* model, uint32_t n_file, uint32_t n_first, uint32_t n_second, uint32_t deriv_step,
+                            int energy_max_norm, const char* normalization_path, const float* raw, uint64_t n_frames,
+                            uint64_t n_utts, const uint64_t* frame_off, float* out) {
+  HostModel* h = static_cast<HostModel*>(model);
+  return guarded([&] {
+    Configuration cfg;
+    cfg.set("n-features-file", n_file).set("n-features-first", n_first).set("n-features-second", n_second);
+    cfg.set("deriv-step", deriv_step).set("energy-max-norm", energy_max_norm != 0);
+    SignalAnalysis sa(cfg);
+    if (normalization_path && *normalization_path) {
+      std::ifstream in(normalization_path, std::ios::binary);
+      if (!in.good()) throw std::runtime_error(std::string("cannot open ") + normalization_path);
+      sa.read_normalization_file(in);
+    }
+    std::vector<size_t> fo(frame_off, frame_off + n_utts + 1);
+    sa.process_features(h->model->device(), raw, n_frames, fo, out);
+  });
+}
+
 }  // extern "C"

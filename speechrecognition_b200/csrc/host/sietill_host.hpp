@@ -199,6 +199,29 @@ class Device {
   sgmm_ctx* ctx_ = nullptr;
 };
 
+// ---- SignalAnalysis.hpp:17-118, the load-time half: process_features on the GPU ---------------------------
+// Same configuration keys and defaults as the reference (SignalAnalysis.cpp:46-56); the normalization file is the
+// reference's (two blobs of n_features_total doubles: mean, stddev, :363-375).  process_features replaces the
+// per-segment call of Corpus::read (Corpus.cpp:101) by ONE batched device pass over all segments; the processed
+// matrix stays resident on `dev` as its feature matrix (sgmm_process_features).
+class SignalAnalysis {
+ public:
+  const bool energy_max_norm;
+  const size_t n_features_in_file, n_features_first, n_features_second, n_features_total, deriv_step;
+
+  explicit SignalAnalysis(Configuration const& config);
+  void read_normalization_file(std::istream& in);                       // SignalAnalysis.cpp:371-375
+  void set_normalization(std::vector<double> const& mean, std::vector<double> const& stddev);
+  // raw: [n_frames][n_features_in_file]; frame_off: n_segments + 1 segment boundaries (in frames);
+  // out: [n_frames][n_features_total] or nullptr (keep the result on the device only)
+  void process_features(Device& dev, const float* raw, size_t n_frames, std::vector<size_t> const& frame_off,
+                        float* out) const;
+
+ private:
+  bool apply_mean_var_normalization_ = false;
+  std::vector<double> mean_, stddev_;
+};
+
 // ---- Mixtures.hpp:16-93 -----------------------------------------------------------------------------
 class MixtureModel : public FeatureScorer {
  public:

@@ -1629,7 +1629,7 @@ __global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
 constexpr float kSumDelta = 45.0f;
 
 template <int DV4>
-__global__ void __launch_bounds__(256) k_sum_pruned(RefineParams p) {
+__global__ void __launch_bounds__(256, 3) k_sum_pruned(RefineParams p) {
   // One CTA per granule of 32 consecutive frames (of one utterance, or of the dense range); the eight warps walk
   // the granule's states TOGETHER (warp w takes frames w, w + 8, ...), so a state's f32 table (36 KB at 256 x 33) is
   // pulled into L1 once per 32 cells instead of once per cell.

@@ -131,6 +131,19 @@ class HostModel:
                                                _p(sc, C.c_double)))
         return sc
 
+    def process_features(self, raw, frame_off, n_first=12, n_second=1, deriv_step=3, energy_max_norm=True,
+                         normalization_path=""):
+        """SignalAnalysis::process_features for all segments on this model's GPU context; returns the processed matrix
+        (which also stays resident as the context's feature matrix)."""
+        raw = np.ascontiguousarray(raw, np.float32)
+        fo = np.ascontiguousarray(frame_off, np.uint64)
+        out = np.empty((raw.shape[0], raw.shape[1] + n_first + n_second), np.float32)
+        _ck(self.L, self.L.sthost_process_features(self.h, C.c_uint32(raw.shape[1]), C.c_uint32(n_first), C.c_uint32(n_second),
+                                                   C.c_uint32(deriv_step), int(energy_max_norm), str(normalization_path).encode(),
+                                                   _p(raw, C.c_float), C.c_uint64(raw.shape[0]), C.c_uint64(len(fo) - 1),
+                                                   _p(fo, C.c_uint64), _p(out, C.c_float)))
+        return out
+
     def score_sequence(self, x, prepared=True):
         x = np.ascontiguousarray(x, np.float32).reshape(-1, self.dim)
         sc = np.zeros((len(x), self.n_mix), np.float64)

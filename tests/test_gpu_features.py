@@ -62,3 +62,28 @@ def test_feature_processing_errors_are_loud():
     with pytest.raises(capi.SgmmError):
         ctx.process_features(raw, np.array([0, 9], np.uint64), 12, 1, 3)
     ctx.close()
+
+
+def test_host_signal_analysis_with_normalization_file(tmp_path):
+    """The host class SignalAnalysis (same configuration keys, the reference's normalization-file format: two blobs of
+    n_features_total doubles, SignalAnalysis.cpp:363-375) driving the device pass, against the oracle."""
+    from speechrecognition_b200 import hostapi
+    rng = np.random.default_rng(9)
+    lens = [120, 4, 279, 33]
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    raw = (rng.standard_normal((int(off[-1]), 12)) * 5.0 + 1.0).astype(np.float32)
+    mean, std = rng.uniform(-2, 2, 25), rng.uniform(0.5, 4.0, 25)
+    path = tmp_path / "Normalization.bin"
+    path.write_bytes(mean.astype("<f8").tobytes() + std.astype("<f8").tobytes())
+    want = np.concatenate([oracle_process_features(raw[int(off[u]):int(off[u + 1])], 12, 1, 3, mean, std, True)
+                           for u in range(len(lens))])
+    model = hostapi.HostModel(25, 106, "none")
+    got = model.process_features(raw, off, 12, 1, 3, True, str(path))
+    assert np.array_equal(bits(got), bits(want))
+    got2 = model.process_features(raw, off, 12, 1, 3, False, "")          # no file: deltas only
+    want2 = np.concatenate([oracle_process_features(raw[int(off[u]):int(off[u + 1])], 12, 1, 3, None, None, False)
+                            for u in range(len(lens))])
+    assert np.array_equal(bits(got2), bits(want2))
+    with pytest.raises(RuntimeError):
+        model.process_features(raw, off, 12, 1, 3, True, str(tmp_path / "missing.bin"))
+    model.close()
