@@ -130,3 +130,43 @@ def test_soft_errors_are_loud():
     with pytest.raises(capi.SgmmError):
         ctx.accumulate_soft()             # no model / features / alignment
     ctx.close()
+
+
+def test_soft_accumulation_many_states():
+    """More than 256 states: the stable sort by aligned state takes two radix passes; odd dimension, 5 densities per
+    state, a random alignment (every state receives frames)."""
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(12)
+    n_states, nd, dim = 700, 5, 9
+    tables = synth.random_model(rng, dim, n_states, nd, "none")
+    corp = synth.make_chain_corpus(rng, tables, dim, n_states, 12, T=300, phones=30, spp=3)
+    x = corp["x"]
+    ali = rng.integers(0, n_states, size=len(x)).astype(np.uint32)
+    P = Oracle(dim, n_states, "none", False, (3.0, 0.0, 30.0), 0)
+    P.load_tables(tables)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, tables)
+    ctx.set_features(x)
+    ctx.set_option("max_approx", 0)
+    ctx.set_alignment(ali)
+    cnt, sx, sxx, ssum = ctx.accumulate_soft()
+    P.accumulate(ali, x, False, False)
+    t = P.tables()
+    want_cnt, want_sx = helpers.packed_stats(t, dim)
+    np.testing.assert_allclose(cnt, want_cnt, rtol=1e-11, atol=1e-12)
+    np.testing.assert_allclose(sx, want_sx, rtol=1e-11, atol=1e-9)
+    vi = t["var_idx"].astype(np.int64)
+    np.testing.assert_allclose(sxx, t["var_acc"].reshape(-1, dim)[vi] - 1e-4, rtol=1e-9, atol=1e-7)
+    # a frame far from every density of its state: exp underflows, the normaliser is 0, the reference accumulates NaN
+    x2 = x.copy()
+    x2[5] = 1e4
+    ctx.set_features(x2)
+    ctx.set_alignment(ali)
+    cnt2, _, _, ssum2 = ctx.accumulate_soft()
+    Q = Oracle(dim, n_states, "none", False, (3.0, 0.0, 30.0), 0)
+    Q.load_tables(tables)
+    Q.accumulate(ali, x2, False, False)
+    want2, _ = helpers.packed_stats(Q.tables(), dim)
+    assert np.array_equal(np.isnan(cnt2), np.isnan(want2)) and np.isnan(cnt2).sum() == nd
+    assert np.isinf(ssum2)
+    ctx.close()
