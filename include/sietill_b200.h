@@ -165,7 +165,7 @@ int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
  * f64 refinement, 3 = tcgen05 3xTF32 tensor-core GEMM with certified f64 refinement.  Every scorer returns
  * results bit-identical to the reference; the choice only moves time.
  * "rescore_cache" (default 1): sgmm_accumulate after sgmm_align with an unchanged model looks the aligned cells' scores up.
- * "async_upload" (default 0): sgmm_set_features queues chunked copies ("upload_chunks", 1..8, default 8) and returns;
+ * "async_upload" (default 0): sgmm_set_features queues chunked copies ("upload_chunks", 1..16, default 16) and returns;
  *   the host buffer must stay untouched until the next compute call returns (use sgmm_host_alloc memory).
  * "tc_halves" (0 auto, 1, 2): 128-frame halves per tensor-core CTA.  "tc_pack" (default 1; read by sgmm_set_corpus):
  *   pack short utterance tails into shared 128-row halves.

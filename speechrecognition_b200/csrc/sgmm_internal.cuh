@@ -57,7 +57,7 @@ struct sgmm_ctx {
   cudaEvent_t ev[2 * SGMM_T_COUNT] = {nullptr};
   cudaEvent_t tev[2] = {nullptr, nullptr};
   // side streams so that independent launches (the Viterbi shape classes) overlap
-  static constexpr int kAux = 8;
+  static constexpr int kAux = 16;
   cudaStream_t aux[kAux] = {nullptr};
   cudaEvent_t ev_fork = nullptr, ev_join[kAux] = {nullptr};
 
@@ -105,9 +105,9 @@ struct sgmm_ctx {
   DevBuf<double> d_feat_norm;
   // option "async_upload": sgmm_set_features returns once the chunked copies are queued on copy_stream; the GEMM
   // scorer consumes the chunks as they land (k_score_tc.cu), every other consumer waits for the last one
-  static constexpr int kFeatChunks = 8;
+  static constexpr int kFeatChunks = 16;
   bool async_upload = false;
-  int feat_chunks = 8;                        // option "upload_chunks" (1..kFeatChunks)
+  int feat_chunks = 16;                       // option "upload_chunks" (1..kFeatChunks)
   int feat_pending = 0;                       // chunks of the upload in flight (0: features resident)
   uint64_t feat_chunk_end[kFeatChunks] = {0};   // exclusive end frame of every chunk
   cudaStream_t copy_stream = nullptr;

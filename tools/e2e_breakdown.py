@@ -16,7 +16,7 @@ x_pin = capi.pinned_empty(corp["x"].shape, np.float32); x_pin[...] = corp["x"]
 ali_pin = capi.pinned_empty((F,), capi.ALI_DTYPE); cost_pin = capi.pinned_empty((U,), np.float64)
 D = int(tables["mix_offsets"][-1])
 stat_pin = (capi.pinned_empty((D,), np.float64), capi.pinned_empty((D, 33), np.float64), capi.pinned_empty((D, 33), np.float64))
-for mode in ("sync", 1, 2, 4, 6, 8):
+for mode in ("sync", 1, 4, 8, 10, 12, 16):
     ctx.set_option("async_upload", 0 if mode == "sync" else 1)
     if mode != "sync":
         ctx.set_option("upload_chunks", mode)
