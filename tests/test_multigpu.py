@@ -46,8 +46,10 @@ def _worker(rank, world, port, out_dir):
     ali, costs = ctx.align()
     cnt, sx, sxx, ssum = ctx.accumulate(first_pass=False)
     am = ctx.am_score_sum()
+    # the posterior-weighted E-step goes through the same all-reduce (same alignment, sum scores)
+    scnt, ssx, ssxx, sssum = ctx.accumulate_soft()
     np.savez(os.path.join(out_dir, "rank%d.npz" % rank), ali=ali["state"], costs=costs, cnt=cnt, sx=sx, sxx=sxx,
-             ssum=ssum, am=am, f0=f0, f1=f1, u0=u0, u1=u1)
+             ssum=ssum, am=am, f0=f0, f1=f1, u0=u0, u1=u1, scnt=scnt, ssx=ssx, ssxx=ssxx, sssum=sssum)
     ctx.close()
     dist.destroy_process_group()
 
@@ -60,6 +62,7 @@ def test_two_ranks_equal_one_gpu(tmp_path):
     ctx = helpers.gpu_context(O, corp, 33)
     ali, costs = ctx.align()
     cnt, sx, sxx, ssum = ctx.accumulate(first_pass=False)
+    scnt, ssx, ssxx, sssum = ctx.accumulate_soft()
     ctx.close()
     r = [np.load(tmp_path / ("rank%d.npz" % k)) for k in range(world)]
     for k in range(world):
@@ -70,5 +73,9 @@ def test_two_ranks_equal_one_gpu(tmp_path):
         np.testing.assert_allclose(r[k]["sxx"], sxx, rtol=1e-12, atol=1e-12)
         assert float(r[k]["ssum"]) == pytest.approx(ssum, rel=1e-12)
         assert float(r[k]["am"]) == pytest.approx(ssum, rel=1e-12)
+        np.testing.assert_allclose(r[k]["scnt"], scnt, rtol=1e-11, atol=1e-12)      # soft statistics, all-reduced
+        np.testing.assert_allclose(r[k]["ssx"], ssx, rtol=1e-11, atol=1e-10)
+        np.testing.assert_allclose(r[k]["ssxx"], ssxx, rtol=1e-11, atol=1e-10)
+        assert float(r[k]["sssum"]) == pytest.approx(sssum, rel=1e-12)
     assert np.array_equal(r[0]["sx"], r[1]["sx"]) and np.array_equal(r[0]["sxx"], r[1]["sxx"])
     assert int(r[0]["f1"]) == int(r[1]["f0"]) and int(r[1]["f1"]) == len(corp["x"])
