@@ -211,6 +211,32 @@ def run_reference(args):
     emit(line)
 
 
+def bind_near_gpu(local):
+    """Multi-GPU runs: keep this rank (and the pinned host buffers it first touches) on the CPUs NVML reports as local
+    to its GPU, so that eight simultaneous uploads do not all cross one socket's memory controllers.  Returns the
+    number of CPUs bound to, or 0 when nothing was changed."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        phys = local
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if local < len(ids) and ids[local].isdigit():
+                phys = int(ids[local])
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        words = (max(os.cpu_count() or 1, 1) + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        near = {64 * i + b for i, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+        allowed = near & set(os.sched_getaffinity(0))
+        if allowed and allowed != set(os.sched_getaffinity(0)):
+            os.sched_setaffinity(0, allowed)
+            return len(allowed)
+    except Exception:
+        pass
+    return 0
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -219,6 +245,7 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    near_cpus = bind_near_gpu(local) if world > 1 else 0
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -392,7 +419,8 @@ def run_ours(args):
         "metric": "frames/sec scored+aligned+accumulated (GMM+Viterbi+EM)", "value": frames_total * args.steps / (ms / 1e3),
         "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic", "config": config_dict(args, F, {"parallelism": "dp%d (utterance shards)" % world}),
+        "dtype": "f64", "data": "synthetic", "config": config_dict(args, F, {"parallelism": "dp%d (utterance shards)" % world,
+                                                               "cpu_binding": ("rank bound to the %d CPUs local to its GPU" % near_cpus) if near_cpus else "none"}),
         "clocks": clocks,
         "e2e": {"value": frames_total * args.steps / (ms_e2e / 1e3), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
