@@ -1130,6 +1130,7 @@ struct RefineParams {
   const uint32_t* state_off;
   const float* x;
   const uint32_t* cand;        // GEMM verdict per cell: certified argmin column, or kUncertain
+  const sgmm_alignment_item* ali;   // k_sum_pruned, dense == 2: one cell per frame, its aligned state
   uint64_t n_cells;
   int dense;
   uint64_t f0;
@@ -1639,7 +1640,12 @@ __global__ void __launch_bounds__(256, 3) k_sum_pruned(RefineParams p) {
   uint64_t fbase, obase;
   uint32_t nvalid, nu, ostride;
   const uint32_t* ulist = nullptr;
-  if (p.dense) {
+  if (p.dense == 2) {              // every frame against its aligned state (calc_am_score): out[frame]
+    const uint64_t r0 = (uint64_t)blockIdx.x * 32;
+    fbase = r0;
+    nvalid = (uint32_t)min((uint64_t)32, p.n_cells - r0);
+    nu = 1; ostride = 1; obase = r0;
+  } else if (p.dense) {
     const uint64_t r0 = (uint64_t)blockIdx.x * 32;
     fbase = p.f0 + r0;
     nvalid = (uint32_t)min((uint64_t)32, p.n_cells / p.n_states - r0);
@@ -1657,8 +1663,8 @@ __global__ void __launch_bounds__(256, 3) k_sum_pruned(RefineParams p) {
   for (uint32_t cell = warp; cell < nu * 4 * 8; cell += 8) {
     const uint32_t j = cell / 32, fr = cell % 32;       // all warps share j: fr = warp, warp + 8, warp + 16, warp + 24
     if (fr >= nvalid) continue;
-    const uint32_t s = ulist ? ulist[j] : j;
     const uint64_t frame = fbase + fr, e = obase + (uint64_t)fr * ostride + j;
+    const uint32_t s = p.dense == 2 ? min((uint32_t)p.ali[frame].state, p.n_states - 1) : (ulist ? ulist[j] : j);
     const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
     const float* xf = p.x + frame * p.m.dim;
     float xr[4 * DV4];
@@ -2009,5 +2015,33 @@ int sgmm_launch_emission_sum_pruned(sgmm_ctx* c, bool dense, uint64_t dense_f0, 
   }
   SGMM_LAUNCH_CHECK(c);
   *handled = true;
+  return 0;
+}
+
+// Sum score of every frame against its aligned state through k_sum_pruned (Trainer::calc_am_score with sum scores).
+int sgmm_launch_sum_aligned_pruned(sgmm_ctx* c, bool* handled) {
+  using namespace sgmm_tc;
+  *handled = false;
+  if (!c->sum_prune || !(c->dv4 == 7 || c->dv4 == 9 || c->dv4 == 12 || c->dv4 == 16) || !c->d_mu32T.p) return 0;
+  *handled = true;
+  if (c->n_frames == 0) return 0;
+  RefineParams r{};
+  r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
+  r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;
+  r.m.meanR = c->d_meanR.p; r.m.invU = c->d_invU.p; r.m.var_of = c->d_var_of.p; r.m.dimP = c->dimP;
+  r.state_off = c->d_state_off.p; r.x = c->d_x.p; r.ali = c->d_ali.p;
+  r.n_cells = c->n_frames; r.dense = 2; r.n_states = c->n_states;
+  r.out = c->d_fscore.p;
+  r.pooled = c->pooled_states ? 1 : 0;
+  r.mu32T = c->d_mu32T.p; r.h32 = c->d_h32.p; r.c32 = c->d_c32.p; r.sguard = c->d_sguard.p;
+  SGMM_CHECK(c, cudaMemsetAsync(c->d_fdens.p, 0xff, c->n_frames * sizeof(uint32_t), c->stream));   // no per-frame density
+  const unsigned grid = (unsigned)((c->n_frames + 31) / 32);
+  switch (c->dv4) {
+    case 7: k_sum_pruned<7><<<grid, 256, 0, c->stream>>>(r); break;
+    case 9: k_sum_pruned<9><<<grid, 256, 0, c->stream>>>(r); break;
+    case 12: k_sum_pruned<12><<<grid, 256, 0, c->stream>>>(r); break;
+    default: k_sum_pruned<16><<<grid, 256, 0, c->stream>>>(r); break;
+  }
+  SGMM_LAUNCH_CHECK(c);
   return 0;
 }

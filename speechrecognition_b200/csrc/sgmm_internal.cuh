@@ -248,6 +248,7 @@ int sgmm_sort_frames(sgmm_ctx* c, const uint32_t* keys, uint32_t n_keys, const u
 int sgmm_launch_emission_sum(sgmm_ctx* c, const uint4* d_tasks, uint64_t n_tasks, bool dense, uint64_t dense_f0,
                              uint64_t dense_nframes, double* d_scores, uint32_t* d_argmin);
 int sgmm_launch_sum_aligned(sgmm_ctx* c);
+int sgmm_launch_sum_aligned_pruned(sgmm_ctx* c, bool* handled);
 // f32-pruned sum scores (k_score_tc.cu); *handled = false when the model shape has no f32 tables
 int sgmm_launch_emission_sum_pruned(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t dense_nframes, double* d_scores,
                                     uint32_t* d_argmin, bool* handled);

@@ -299,7 +299,9 @@ int sgmm_am_score_sum(sgmm_ctx* c, double* score_sum) {
     SGMM_CHECK(c, c->d_fscore.reserve(c->n_frames));
     SGMM_CHECK(c, c->d_acc.reserve(acc_len(c)));
     StageTimer st(c, SGMM_T_RESCORE);
-    if (sgmm_launch_sum_aligned(c)) return 1;
+    bool handled = false;
+    if (sgmm_launch_sum_aligned_pruned(c, &handled)) return 1;
+    if (!handled && sgmm_launch_sum_aligned(c)) return 1;
     if (sgmm_launch_score_sum(c)) return 1;
   } else if (rescore_common(c, false)) return 1;
   double* slot = c->d_acc.p + (size_t)c->Dtot * (1 + 2 * (size_t)c->dim);
