@@ -114,14 +114,16 @@ __global__ void __launch_bounds__(kSoftThreads, 1) k_soft_partial(SoftParams p) 
   const uint32_t beg = p.seg_off[s] + (item - p.item_off[s]) * kSoftItem;
   const uint32_t end = min(p.seg_off[s + 1], beg + kSoftItem);
   const uint32_t k0 = p.state_off[s], nd = p.state_off[s + 1] - k0, d = p.m.dim;
-  const uint32_t nE = nd * (2 * d + 1), ndp = nd | 1u, SB = p.SB;
-  double* acc = reinterpret_cast<double*>(smem);            // [2 d + 1][nd]
-  double* P = acc + (size_t)(p.maxE);                       // [SB][ndp]
-  double* X = P + (size_t)SB * ((p.maxE / (2 * d + 1)) | 1u);   // [SB][d]
+  const uint32_t W = 2 * d + 1, Wp = W | 1u, nE = nd * W, ndp = nd | 1u, SB = p.SB;
+  const uint32_t maxnd = p.maxE / W, nwords = (maxnd + 31) / 32;
+  double* acc = reinterpret_cast<double*>(smem);            // [nd][Wp] (odd row stride: conflict-free column walks)
+  double* P = acc + (size_t)maxnd * Wp;                     // [SB][ndp]
+  double* X = P + (size_t)SB * (maxnd | 1u);                // [SB][d]
   double* sums = X + (size_t)SB * d;                        // [SB]
   uint32_t* fr = reinterpret_cast<uint32_t*>(sums + SB);    // [SB]
-  const uint32_t tid = threadIdx.x;
-  for (uint32_t e = tid; e < nE; e += kSoftThreads) acc[e] = 0.0;
+  uint32_t* masks = fr + SB;                                // [SB][nwords]: densities whose posterior is not skipped
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (uint32_t e = tid; e < nd * Wp; e += kSoftThreads) acc[e] = 0.0;
 
   for (uint32_t i0 = beg; i0 < end; i0 += SB) {
     const uint32_t nf = min(SB, end - i0);
@@ -144,40 +146,47 @@ __global__ void __launch_bounds__(kSoftThreads, 1) k_soft_partial(SoftParams p) 
       p.fscore[fr[tid]] = -log(a);        // == sum_score(x, s), :719-728 (same terms, same order)
     }
     __syncthreads();
-    for (uint32_t q = tid; q < nf * nd; q += kSoftThreads) {   // divides<double>, :322-323
-      const uint32_t j = q / nd, k = q - j * nd;
-      P[j * ndp + k] = __ddiv_rn(P[j * ndp + k], sums[j]);
+    // divides<double> (:322-323) and the skip test (:336-338: "< 1e-8" — a NaN weight is NOT skipped, as in the
+    // reference): warp = frame, one ballot per 32 densities
+    for (uint32_t j = warp; j < nf; j += kSoftThreads / 32) {
+      for (uint32_t r = 0; r < nwords; r++) {
+        const uint32_t k = 32 * r + lane;
+        bool keep = false;
+        if (k < nd) {
+          const double w = __ddiv_rn(P[j * ndp + k], sums[j]);
+          P[j * ndp + k] = w;
+          keep = !(w < 1e-8);
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) masks[j * nwords + r] = m;
+      }
     }
     __syncthreads();
-    for (uint32_t e = tid; e < nE; e += kSoftThreads) {
-      const uint32_t c = e / nd, k = e - c * nd;
-      double v = acc[e];
-      if (c < d) {                        // mean accumulator: x + scale * y, :46-56
-        for (uint32_t j = 0; j < nf; j++) {
+    // one task per (accumulator column c, word of 32 densities): frames in order, only the kept densities — a frame's
+    // posterior mass sits on one or two of them
+    for (uint32_t idx = tid; idx < W * nwords; idx += kSoftThreads) {
+      const uint32_t wi = idx / W, c = idx - wi * W;
+      for (uint32_t j = 0; j < nf; j++) {
+        uint32_t m = masks[j * nwords + wi];
+        while (m) {
+          const uint32_t k = 32 * wi + (uint32_t)__ffs(m) - 1u;
+          m &= m - 1;
           const double w = P[j * ndp + k];
-          if (w < 1e-8) continue;         // :336-338 (a NaN weight is NOT skipped, as in the reference)
-          v = __dadd_rn(v, __dmul_rn(w, X[j * d + c]));
-        }
-      } else if (c < 2 * d) {             // variance accumulator: x + scale * y * y, :58-68
-        for (uint32_t j = 0; j < nf; j++) {
-          const double w = P[j * ndp + k];
-          if (w < 1e-8) continue;
-          const double y = X[j * d + (c - d)];
-          v = __dadd_rn(v, __dmul_rn(__dmul_rn(w, y), y));
-        }
-      } else {                            // weight accumulators, :343-344
-        for (uint32_t j = 0; j < nf; j++) {
-          const double w = P[j * ndp + k];
-          if (w < 1e-8) continue;
-          v = __dadd_rn(v, w);
+          double v = acc[k * Wp + c];
+          if (c < d) v = __dadd_rn(v, __dmul_rn(w, X[j * d + c]));                       // x + scale * y, :46-56
+          else if (c < 2 * d) { const double y = X[j * d + (c - d)]; v = __dadd_rn(v, __dmul_rn(__dmul_rn(w, y), y)); }   // :58-68
+          else v = __dadd_rn(v, w);                                                       // weights, :343-344
+          acc[k * Wp + c] = v;
         }
       }
-      acc[e] = v;
     }
     __syncthreads();
   }
   double* out = p.partial + (size_t)item * p.maxE;
-  for (uint32_t e = tid; e < nE; e += kSoftThreads) out[e] = acc[e];
+  for (uint32_t e = tid; e < nE; e += kSoftThreads) {       // partial layout [column][density]
+    const uint32_t c = e / nd, k = e - c * nd;
+    out[e] = acc[k * Wp + c];
+  }
 }
 
 // one thread per (density, accumulator column): add the items' partials in item order
@@ -228,7 +237,8 @@ int sgmm_launch_accumulate_soft(sgmm_ctx* c) {
   uint32_t SB = 0;
   size_t smem = 0;
   for (uint32_t sb : {32u, 16u, 8u}) {
-    const size_t need = 8 * ((size_t)maxE + (size_t)sb * (c->max_dens | 1u) + (size_t)sb * dim + sb) + 4 * (size_t)sb;
+    const size_t need = 8 * ((size_t)c->max_dens * (W | 1u) + (size_t)sb * (c->max_dens | 1u) + (size_t)sb * dim + sb) +
+                        4 * (size_t)sb * (1 + (c->max_dens + 31) / 32);
     if (need <= 227 * 1024) { SB = sb; smem = need; break; }
   }
   if (!SB) SGMM_FAIL(c, "accumulate_soft: a state's accumulators (densities x (2 dim + 1) doubles) exceed shared memory");
