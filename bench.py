@@ -286,9 +286,9 @@ def run_ours(args):
     def step_e2e():
         # host buffers in, host buffers out: the upload is queued in chunks (option async_upload) and the scorer
         # starts on the first chunk while the rest is still crossing PCIe
+        # realign + estimate in one call (sgmm_align_accumulate): the alignment copy overlaps the E-step
         ctx.set_features(x_pin)
-        ctx.align(out=ali_pin, out_costs=cost_pin)
-        return ctx.accumulate(first_pass=False, out=stat_pin)
+        return ctx.align_accumulate(ali_pin, cost_pin, stat_pin)
 
     def max_over_ranks(v):
         if world == 1:

@@ -135,6 +135,11 @@ int sgmm_set_alignment(sgmm_ctx* ctx, const sgmm_alignment_item* alignment, uint
 int sgmm_accumulate(sgmm_ctx* ctx, int first_pass, double* count, double* sum_x, double* sum_xx,
                     double* score_sum);
 
+/* sgmm_align followed by sgmm_accumulate(first_pass = 0) in one call — the realign + estimate pair of Trainer::train
+ * (Training.cpp:168-201).  Results are those of the two calls; the alignment / cost copies overlap the E-step. */
+int sgmm_align_accumulate(sgmm_ctx* ctx, int tdp_convention, sgmm_alignment_item* alignment, double* costs,
+                          double* count, double* sum_x, double* sum_xx, double* score_sum);
+
 /* The posterior-weighted branch of MixtureModel::accumulate (max_approx == false, not the first pass;
  * Mixtures.cpp:300-357) over the resident alignment: for frame f with aligned state m,
  * p_k = exp(-density_score(x_f, m, k)) normalised by their in-order sum (:310-324), entries below 1e-8 skipped

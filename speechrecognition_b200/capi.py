@@ -20,7 +20,7 @@ ALI_DTYPE = np.dtype([("count", np.uint16), ("state", np.uint16), ("weight", np.
 SYMBOLS = [
     "sgmm_create", "sgmm_destroy", "sgmm_last_error", "sgmm_version", "sgmm_set_model", "sgmm_set_features",
     "sgmm_set_corpus", "sgmm_set_tdp", "sgmm_set_beam", "sgmm_set_lexicon", "sgmm_recognize", "sgmm_score_all", "sgmm_align", "sgmm_set_alignment", "sgmm_accumulate",
-    "sgmm_accumulate_soft", "sgmm_process_features",
+    "sgmm_accumulate_soft", "sgmm_process_features", "sgmm_align_accumulate",
     "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
     "sgmm_launch_count", "sgmm_timer_start", "sgmm_timer_stop", "sgmm_host_alloc", "sgmm_host_free",
     "sgmm_set_option", "sgmm_get_counter",
@@ -201,6 +201,15 @@ class Context:
         ssum = np.zeros(1, np.float64)
         self._ck(self.L.sgmm_accumulate(self.h, int(first_pass), _ptr(cnt, C.c_double), _ptr(sx, C.c_double),
                                         _ptr(sxx, C.c_double), _ptr(ssum, C.c_double)))
+        return cnt, sx, sxx, float(ssum[0])
+
+    def align_accumulate(self, out_ali, out_costs, out_stats, convention=TDP_SOURCE):
+        """sgmm_align + sgmm_accumulate(first_pass=False) in one call; all outputs into caller buffers."""
+        cnt, sx, sxx = out_stats
+        ssum = np.zeros(1, np.float64)
+        self._ck(self.L.sgmm_align_accumulate(self.h, int(convention), out_ali.ctypes.data_as(C.c_void_p),
+                                              _ptr(out_costs, C.c_double), _ptr(cnt, C.c_double), _ptr(sx, C.c_double),
+                                              _ptr(sxx, C.c_double), _ptr(ssum, C.c_double)))
         return cnt, sx, sxx, float(ssum[0])
 
     def accumulate_soft(self):

@@ -287,6 +287,58 @@ int sgmm_accumulate_soft(sgmm_ctx* c, double* count, double* sum_x, double* sum_
   return 0;
 }
 
+// sgmm_align followed by sgmm_accumulate(first_pass = 0) in ONE call — the realign + estimate pair of
+// Trainer::train (Training.cpp:168-201).  Same results as the two calls; the host copies of the alignment and the path
+// costs travel on the copy stream while the E-step kernels run, and there is one synchronisation instead of two.
+int sgmm_align_accumulate(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* costs, double* count,
+                          double* sum_x, double* sum_xx, double* score_sum) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  reset_stage(c);
+  if (require(c, true, true, true)) return 1;
+  if (conv != SGMM_TDP_SOURCE && conv != SGMM_TDP_DESTINATION) SGMM_FAIL(c, "align: bad tdp_convention");
+  SGMM_CHECK(c, c->d_E.reserve(c->E_elems + 2));
+  SGMM_CHECK(c, c->d_Amin.reserve(c->E_elems + 2));
+  SGMM_CHECK(c, c->d_fcol.reserve(c->n_frames));
+  SGMM_CHECK(c, c->d_ali.reserve(c->n_frames));
+  SGMM_CHECK(c, c->d_costs.reserve(c->n_utts));
+  {
+    StageTimer st(c, SGMM_T_SCORE);
+    if (launch_emission_any(c, false, 0, 0, nullptr, nullptr)) return 1;
+  }
+  {
+    StageTimer st(c, SGMM_T_VITERBI);
+    if (sgmm_launch_viterbi(c, conv)) return 1;
+  }
+  c->have_alignment = true;
+  c->ali_has_cols = true;
+  c->E_model_version = c->model_version;
+  c->E_max_approx = c->max_approx;
+  // alignment + costs go home on the copy stream, behind the Viterbi launches, beside the E-step
+  SGMM_CHECK(c, cudaEventRecord(c->ev_fork, c->stream));
+  SGMM_CHECK(c, cudaStreamWaitEvent(c->copy_stream, c->ev_fork, 0));
+  if (alignment)
+    SGMM_CHECK(c, cudaMemcpyAsync(alignment, c->d_ali.p, c->n_frames * sizeof(sgmm_alignment_item),
+                                  cudaMemcpyDeviceToHost, c->copy_stream));
+  if (costs)
+    SGMM_CHECK(c, cudaMemcpyAsync(costs, c->d_costs.p, c->n_utts * sizeof(double), cudaMemcpyDeviceToHost,
+                                  c->copy_stream));
+  if (rescore_common(c, false)) return 1;
+  if (sgmm_launch_accumulate(c)) return 1;
+  if (sgmm_nccl_allreduce(c, c->d_acc.p, acc_len(c))) return 1;
+  const size_t D = c->Dtot, d = c->dim;
+  {
+    StageTimer st(c, SGMM_T_D2H);
+    if (count) SGMM_CHECK(c, cudaMemcpyAsync(count, c->d_acc.p, D * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (sum_x) SGMM_CHECK(c, cudaMemcpyAsync(sum_x, c->d_acc.p + D, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (sum_xx) SGMM_CHECK(c, cudaMemcpyAsync(sum_xx, c->d_acc.p + D + D * d, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (score_sum) SGMM_CHECK(c, cudaMemcpyAsync(score_sum, c->d_acc.p + D + 2 * D * d, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->copy_stream));
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
 int sgmm_am_score_sum(sgmm_ctx* c, double* score_sum) {
   if (!c) return 1;
   cudaSetDevice(c->device);

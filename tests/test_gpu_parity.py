@@ -571,3 +571,21 @@ def test_stress_shape_config5():
     assert cnt.sum() == len(want_states) and len(cnt) == n_states * nd
     np.testing.assert_allclose(sx, t["mean_acc"].reshape(-1, dim)[t["mean_idx"].astype(np.int64)], rtol=STAT_RTOL, atol=0)
     ctx.close()
+
+
+def test_align_accumulate_equals_the_two_calls(small33):
+    """sgmm_align_accumulate (one call, the alignment copy overlapping the E-step) == sgmm_align + sgmm_accumulate."""
+    from speechrecognition_b200 import capi
+    O, corp, ali, ctx = small33
+    got, costs = ctx.align()
+    cnt, sx, sxx, ssum = ctx.accumulate(first_pass=False)
+    D, d, F, U = ctx.D, ctx.dim, ctx.n_frames, len(corp["frame_off"]) - 1
+    a2 = capi.pinned_empty((F,), capi.ALI_DTYPE)
+    c2 = capi.pinned_empty((U,), np.float64)
+    st = (capi.pinned_empty((D,), np.float64), capi.pinned_empty((D, d), np.float64), capi.pinned_empty((D, d), np.float64))
+    for _ in range(2):
+        a2[...] = 0; c2[...] = 0
+        r = ctx.align_accumulate(a2, c2, st)
+        assert np.array_equal(a2["state"], got["state"]) and np.array_equal(a2["count"], got["count"])
+        assert np.array_equal(c2, costs)
+        assert np.array_equal(r[0], cnt) and np.array_equal(r[1], sx) and np.array_equal(r[2], sxx) and r[3] == ssum
