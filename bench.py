@@ -126,7 +126,7 @@ class ClockSampler(threading.Thread):
                 "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
-def cpu_reference_rate(args, tables, corp, lex, n_utts, threads):
+def cpu_reference_rate(args, tables, corp, lex, n_utts, threads, keep=False):
     """frames/s of the reference's own CPU path (align_sequence_full per utterance + accumulate) on the
     first n_utts utterances, `threads` utterance shards in parallel (the reference itself is single-threaded,
     Training.cpp:168-183; independent shards are how it would use more cores)."""
@@ -151,6 +151,7 @@ def cpu_reference_rate(args, tables, corp, lex, n_utts, threads):
         M.load_tables(tables)
     shards = np.array_split(np.arange(n_utts), threads)
     states = np.zeros(F, np.uint32)
+    costs = np.zeros(n_utts, np.float64)
 
     def work(idx):
         if len(idx) == 0:
@@ -159,10 +160,11 @@ def cpu_reference_rate(args, tables, corp, lex, n_utts, threads):
         f0, f1 = int(fo[u0]), int(fo[u1])
         a0, a1 = int(ao[u0]), int(ao[u1])
         if kind == "reference":
-            st, _ = M.align_batch(x[f0:f1], fo[u0:u1 + 1] - fo[u0], corp["automata"][a0:a1], ao[u0:u1 + 1] - ao[u0])
+            st, cs = M.align_batch(x[f0:f1], fo[u0:u1 + 1] - fo[u0], corp["automata"][a0:a1], ao[u0:u1 + 1] - ao[u0])
         else:
-            st, _ = M.align_batch(x[f0:f1], fo[u0:u1 + 1] - fo[u0], corp["automata"][a0:a1], ao[u0:u1 + 1] - ao[u0], 1)
+            st, cs = M.align_batch(x[f0:f1], fo[u0:u1 + 1] - fo[u0], corp["automata"][a0:a1], ao[u0:u1 + 1] - ao[u0], 1)
         states[f0:f1] = st
+        costs[u0:u1] = cs
 
     t0 = time.perf_counter()
     ths = [threading.Thread(target=work, args=(s,)) for s in shards]
@@ -172,8 +174,92 @@ def cpu_reference_rate(args, tables, corp, lex, n_utts, threads):
     t1 = time.perf_counter()
     M.accumulate(states, x)     # single-threaded, as in the reference
     t_acc = time.perf_counter() - t1
-    return {"frames": F, "seconds": t_align + t_acc, "align_s": t_align, "accumulate_s": t_acc, "kind": kind,
-            "value": F / (t_align + t_acc)}
+    out = {"frames": F, "seconds": t_align + t_acc, "align_s": t_align, "accumulate_s": t_acc, "kind": kind,
+           "value": F / (t_align + t_acc), "n_utts": n_utts}
+    if keep:   # what the checker computed, for parity_check: alignment, path costs, E-step statistics of the sample
+        t = M.tables()
+        mi = t["mean_idx"].astype(np.int64)
+        out.update(states=states, costs=costs, count=t["mean_wacc"][mi], sum_x=t["mean_acc"].reshape(-1, args.dim)[mi])
+    return out
+
+
+def grouped_sums(x, keys, n_keys):
+    """f64 sum of the rows of x per key (sorted segments, np.add.reduceat): an independent restatement of K4."""
+    order = np.argsort(keys, kind="stable")
+    ks = keys[order]
+    starts = np.flatnonzero(np.r_[True, ks[1:] != ks[:-1]])
+    out = np.zeros((n_keys, x.shape[1]), np.float64)
+    xs = x[order].astype(np.float64)
+    out[ks[starts]] = np.add.reduceat(xs, starts, axis=0)
+    outq = np.zeros((n_keys, x.shape[1]), np.float64)
+    outq[ks[starts]] = np.add.reduceat(xs * xs, starts, axis=0)
+    return out, outq
+
+
+def parity_check(ctx, args, tables, corp, ref, bufs):
+    """One pass of the benchmarked call (sgmm_align_accumulate over the WHOLE shard, same kernels, same packing, same
+    chunked upload) compared with what the CPU checker (oracle/_ref, else the oracle port) computed for the first
+    ref["n_utts"] utterances — alignment, path costs, chosen densities (as counts), sum_x — plus two size-independent
+    properties over the whole shard: every frame is counted exactly once, and the device's segmented sums equal a
+    numpy restatement fed with the device's own per-frame density choices."""
+    ali_pin, cost_pin, stat_pin, x_pin = bufs
+    ctx.set_features(x_pin)
+    cnt, sx, sxx, ssum = ctx.align_accumulate(ali_pin, cost_pin, stat_pin)
+    dens, fscore = ctx.last_frame_results()
+    n, F = ref["n_utts"], ref["frames"]
+    off = tables["mix_offsets"].astype(np.int64)
+    st = ali_pin["state"].astype(np.int64)
+    glob = off[st] + dens.astype(np.int64)
+    D = int(off[-1])
+    out = {"utts": int(n), "frames": int(F), "checker": ref["kind"]}
+    out["alignment_equal"] = bool(np.array_equal(ali_pin["state"][:F].astype(np.uint32), ref["states"]))
+    out["costs_equal"] = bool(np.array_equal(np.asarray(cost_pin[:n]), ref["costs"]))
+    out["counts_equal"] = bool(np.array_equal(np.bincount(glob[:F], minlength=D).astype(np.float64), ref["count"]))
+    sxs, _ = grouped_sums(corp["x"][:F], glob[:F], D)
+    den = np.maximum(np.abs(ref["sum_x"]), 1e-9)
+    out["sum_x_max_rel"] = float(np.max(np.abs(sxs - ref["sum_x"]) / den))
+    # whole shard
+    Fall = len(st)
+    out["shard_frames"] = int(Fall)
+    out["shard_count_total_ok"] = bool(float(np.sum(cnt)) == float(Fall) and
+                                       np.array_equal(np.bincount(glob, minlength=D).astype(np.float64), np.asarray(cnt)))
+    wx, wxx = grouped_sums(corp["x"], glob, D)
+    out["shard_sum_x_max_rel"] = float(np.max(np.abs(wx - sx) / np.maximum(np.abs(wx), 1e-9)))
+    out["shard_sum_xx_max_rel"] = float(np.max(np.abs(wxx - sxx) / np.maximum(np.abs(wxx), 1e-9)))
+    out["shard_score_sum_rel"] = float(abs(float(np.sum(fscore)) - ssum) / max(abs(ssum), 1e-300))
+    out["ok"] = bool(out["alignment_equal"] and out["costs_equal"] and out["counts_equal"] and
+                     out["sum_x_max_rel"] <= 1e-9 and out["shard_count_total_ok"] and
+                     out["shard_sum_x_max_rel"] <= 1e-9 and out["shard_sum_xx_max_rel"] <= 1e-9 and
+                     out["shard_score_sum_rel"] <= 1e-9)
+    return out
+
+
+def allreduce_check(ctx, dist, torch, rank, world, F_local, stat_bufs):
+    """N > 1: the statistics every rank holds after sgmm_accumulate's ncclAllReduce against the per-rank partial sums
+    (option "allreduce" = 0) gathered through torch.distributed and added in rank order on rank 0."""
+    cnt, sx, sxx, _ = ctx.accumulate(first_pass=False, out=stat_bufs)
+    red = [np.array(cnt), np.array(sx), np.array(sxx)]
+    ctx.set_option("allreduce", 0)
+    pc, px, pxx, _ = ctx.accumulate(first_pass=False, out=stat_bufs)
+    ctx.set_option("allreduce", 1)
+    part = torch.from_numpy(np.concatenate([np.asarray(pc).ravel(), np.asarray(px).ravel(), np.asarray(pxx).ravel(),
+                                            [float(F_local)]])).cuda()
+    gathered = [torch.empty_like(part) for _ in range(world)] if rank == 0 else None
+    dist.gather(part, gathered, dst=0)
+    if rank != 0:
+        return None
+    tot = np.zeros(part.numel(), np.float64)
+    for g in gathered:
+        tot += g.cpu().numpy()
+    D, d = red[1].shape
+    want_c, want_x, want_xx, frames = tot[:D], tot[D:D + D * d].reshape(D, d), tot[D + D * d:D + 2 * D * d].reshape(D, d), tot[-1]
+    rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-9)))
+    out = {"ranks": world, "frames_all_ranks": int(frames), "count_sum_equals_frames": bool(float(red[0].sum()) == frames),
+           "counts_equal": bool(np.array_equal(red[0], want_c)), "sum_x_max_rel": rel(red[1], want_x),
+           "sum_xx_max_rel": rel(red[2], want_xx)}
+    out["ok"] = bool(out["count_sum_equals_frames"] and out["counts_equal"] and out["sum_x_max_rel"] <= 1e-12 and
+                     out["sum_xx_max_rel"] <= 1e-12)
+    return out
 
 
 def config_dict(args, frames_per_gpu, extra=None):
@@ -329,6 +415,7 @@ def run_ours(args):
     h2d = x_pin.nbytes
     d2h = ali_pin.nbytes + U * 8 + sum(a.nbytes for a in out[:3]) + 8
 
+    ar_check = allreduce_check(ctx, dist, torch, rank, world, F, stat_pin) if world > 1 else None
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -436,14 +523,21 @@ def run_ours(args):
     }
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
-        r = cpu_reference_rate(args, tables, corp, lex, args.ref_utts, cores)
+        r = cpu_reference_rate(args, tables, corp, lex, args.ref_utts, cores, keep=True)
+        line["parity_check"] = parity_check(ctx, args, tables, corp, r, (ali_pin, cost_pin, stat_pin, x_pin))
         line["cpu_baseline"] = {"value": r["value"], "unit": "frames/s", "cores": cores, "kind": r["kind"],
                                 "sample": "first %d utterances (%d frames) of the shard, one pass; alignment in %d parallel "
                                           "utterance shards (%.1f s), accumulate single-threaded (%.1f s)"
                                           % (args.ref_utts, r["frames"], cores, r["align_s"], r["accumulate_s"])}
+    if ar_check is not None:
+        line["allreduce_check"] = ar_check
     emit(line)
     if world > 1:
         dist.destroy_process_group()
+    bad = [k for k in ("parity_check", "allreduce_check") if k in line and not line[k]["ok"]]
+    if bad:
+        sys.stderr.write("bench.py: %s FAILED: %s\n" % (", ".join(bad), json.dumps({k: line[k] for k in bad})))
+        sys.exit(3)
 
 
 _REAL_STDOUT = None

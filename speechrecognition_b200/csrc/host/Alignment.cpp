@@ -64,11 +64,20 @@ void Aligner::align_corpus(Corpus const& corpus, std::vector<MarkovAutomaton> co
   std::pair<FeatureIter, FeatureIter> all = corpus.get_all_features();
   mixtures_.set_corpus_features(all.first, all.second);
   Device& dev = mixtures_.device();
-  if (corpus_key_ != &corpus) {
+  // the resident corpus layout is keyed on its CONTENT (frame offsets + automata), not on the Corpus address: changed
+  // automata or a recycled address must not reuse stale tables
+  uint64_t key = 0xCBF29CE484222325ull ^ U;
+  for (size_t v : corpus.frame_offsets()) key = (key ^ (uint64_t)v) * 0x100000001B3ull;
+  for (size_t u = 0; u < U; u++) {
+    key = (key ^ (uint64_t)automata[u].states.size()) * 0x100000001B3ull;
+    for (StateIdx st : automata[u].states) key = (key ^ (uint64_t)st) * 0x100000001B3ull;
+  }
+  if (!corpus_key_valid_ || corpus_key_ != key) {
     std::vector<MarkovAutomaton const*> ptrs(U);
     for (size_t u = 0; u < U; u++) ptrs[u] = &automata[u];
     upload_corpus(dev, corpus.frame_offsets(), ptrs);
-    corpus_key_ = &corpus;
+    corpus_key_ = key;
+    corpus_key_valid_ = true;
   }
   dev.check(sgmm_set_tdp(dev.ctx(), tdp_model_.loop(), tdp_model_.forward(), tdp_model_.skip(), tdp_model_.silence_state),
             "sgmm_set_tdp");

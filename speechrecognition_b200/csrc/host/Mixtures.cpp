@@ -72,7 +72,7 @@ uint64_t alignment_checksum(const AlignmentItem* items, size_t n) {
 }
 
 // ---- Device -----------------------------------------------------------------------------------------
-Device::Device(int device_index) {
+Device::Device(int device_index) : index_(device_index) {
   if (sgmm_create(device_index, &ctx_) != 0)
     throw std::runtime_error(std::string("sgmm_create: ") + sgmm_last_error(nullptr));
 }
@@ -171,7 +171,7 @@ void MixtureModel::sync_device() const {
 
 Device& MixtureModel::scratch() const {
   if (!device_) fail("built host-only: no GPU context (there is no CPU scoring path)");
-  if (!scratch_) scratch_.reset(new Device(0));
+  if (!scratch_) scratch_.reset(new Device(device_->index()));   // same GPU as the main context
   if (scratch_version_ != version_) {
     std::vector<uint32_t> off;
     std::vector<double> pm, pv, pn, pw;

@@ -58,7 +58,11 @@ double Trainer::calc_am_score(Corpus const& corpus, Alignment const& alignment) 
   }
   double sum = 0.0;
   dev.check(sgmm_am_score_sum(dev.ctx(), &sum), "sgmm_am_score_sum");
-  return sum / (double)corpus.get_total_frame_count();
+  // with a communicator attached the sum is over every rank's shard: divide by the frames behind it
+  int64_t frames = 0;
+  dev.check(sgmm_get_counter(dev.ctx(), "frames_global", &frames), "sgmm_get_counter(frames_global)");
+  (void)corpus;
+  return sum / (double)frames;
 }
 
 void Trainer::train(Corpus const& corpus, const Alignment* initial) {

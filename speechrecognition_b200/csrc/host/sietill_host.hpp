@@ -193,10 +193,12 @@ class Device {
   Device(Device const&) = delete;
   Device& operator=(Device const&) = delete;
   sgmm_ctx* ctx() const { return ctx_; }
+  int index() const { return index_; }
   void check(int rc, const char* what) const;   // throws std::runtime_error(what + sgmm_last_error)
 
  private:
   sgmm_ctx* ctx_ = nullptr;
+  int index_ = 0;
 };
 
 // ---- SignalAnalysis.hpp:17-118, the load-time half: process_features on the GPU ---------------------------
@@ -339,7 +341,8 @@ class Aligner {
   MixtureModel const& mixtures_;
   TdpModel const& tdp_model_;
   size_t max_aligns_;
-  const void* corpus_key_ = nullptr;   // corpus whose automata are resident
+  uint64_t corpus_key_ = 0;            // content hash (frame offsets + automata) of the resident corpus layout
+  bool corpus_key_valid_ = false;
 };
 
 void write_alignment(std::ostream& out, Alignment const& alignment, size_t max_aligns);   // Alignment.cpp:303-308

@@ -225,11 +225,14 @@ __global__ void __launch_bounds__(256) k_score_partial(const double* __restrict_
   }
   if (threadIdx.x == 0) part[blockIdx.x] = sh[0];
 }
-__global__ void k_score_final(const double* __restrict__ part, int n, double* __restrict__ out) {
+// out[0] = the score sum, out[1] = the number of frames it covers (both travel in the all-reduce payload, so that
+// calc_am_score divides the global sum by the global frame count)
+__global__ void k_score_final(const double* __restrict__ part, int n, double n_frames, double* __restrict__ out) {
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     double a = 0.0;
     for (int i = 0; i < n; i++) a = __dadd_rn(a, part[i]);
-    *out = a;
+    out[0] = a;
+    out[1] = n_frames;
   }
 }
 
@@ -299,13 +302,13 @@ int sgmm_launch_accumulate(sgmm_ctx* c) {
   return 0;
 }
 
-// d_acc[last] = sum of c->d_fscore
+// d_acc[D (1 + 2 dim)] = sum of c->d_fscore, the slot after it = the frame count
 int sgmm_launch_score_sum(sgmm_ctx* c) {
   SGMM_CHECK(c, c->d_score_part.reserve(kScoreBlocks));
   double* out = c->d_acc.p + (size_t)c->Dtot * (1 + 2 * (size_t)c->dim);
   k_score_partial<<<kScoreBlocks, 256, 0, c->stream>>>(c->d_fscore.p, c->n_frames, c->d_score_part.p);
   SGMM_LAUNCH_CHECK(c);
-  k_score_final<<<1, 32, 0, c->stream>>>(c->d_score_part.p, kScoreBlocks, out);
+  k_score_final<<<1, 32, 0, c->stream>>>(c->d_score_part.p, kScoreBlocks, (double)c->n_frames, out);
   SGMM_LAUNCH_CHECK(c);
   return 0;
 }

@@ -1872,7 +1872,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   r.sm_items = c->d_sm_items.p; r.sm_ent_a = c->d_sm_ent_a.p; r.sm_ent_b = c->d_sm_ent_b.p;
   r.sm_rw = sm_rw; r.sm_maxnd = sm_maxnd;
   const bool one = ranges.size() == 1;
-  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER], c->stream);
+  sgmm_stage_begin(c, SGMM_T_SCORE_FILTER);
   uint64_t f_prev = 0, g_prev = 0;
   // several ranges: each on its own side stream, so that the next range's CTAs fill the SMs that the tail of the
   // previous one leaves idle; all of them rejoin the main stream before the rescan
@@ -1934,8 +1934,8 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   }
   if (!one)
     for (size_t ri = 0; ri < ranges.size(); ri++) SGMM_CHECK(c, cudaStreamWaitEvent(c->stream, c->ev_join[ri], 0));
-  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_FILTER + 1], c->stream);
-  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE], c->stream);
+  sgmm_stage_end(c, SGMM_T_SCORE_FILTER);
+  sgmm_stage_begin(c, SGMM_T_SCORE_REFINE);
   // refinement of every cell in one launch (alternating GEMM and refinement launches per range wastes the SMs at
   // every switch: a GEMM CTA needs the whole shared memory of an SM, so it waits for all refinement CTAs there)
   if (use_sm) {
@@ -1968,7 +1968,6 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     }
     SGMM_LAUNCH_CHECK(c);
   }
-  c->stage_ms[SGMM_T_SCORE_FILTER] = -1.f;
   r.mu32T = c->d_mu32T.p; r.h32 = c->d_h32.p; r.c32 = c->d_c32.p; r.sguard = c->d_sguard.p;
   switch ((c->tc_rescan == 1 || c->tc_full) ? 0u : c->dv4) {   // option tc_rescan 1: the plain full-f64 rescan (same results)
     case 7: k_tc_rescan2<7><<<148 * 16, 256, 0, c->stream>>>(r); break;
@@ -1978,8 +1977,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     default: k_tc_rescan<<<148 * 16, 256, 0, c->stream>>>(r); break;
   }
   SGMM_LAUNCH_CHECK(c);
-  cudaEventRecord(c->ev[2 * SGMM_T_SCORE_REFINE + 1], c->stream);
-  c->stage_ms[SGMM_T_SCORE_REFINE] = -1.f;
+  sgmm_stage_end(c, SGMM_T_SCORE_REFINE);
   return 0;
 }
 

@@ -238,7 +238,9 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     end_s = hi ? hi - 1 : 0;
   }
   const double mine = pick<C>(q, (int)(end_s % C));
-  const double cost = __shfl_sync(0xffffffffu, mine, (int)(end_s / C));
+  // a one-frame utterance never enters the reference's frame loop: align_sequence_full returns current_costs[S-1],
+  // still +inf (Alignment.cpp:62-63,142); the pruned aligner returns the start node's score
+  const double cost = (!DEST && T == 1) ? INF : __shfl_sync(0xffffffffu, mine, (int)(end_s / C));
 
   if (lane == 0) {
     if (p.costs) p.costs[u] = cost;

@@ -21,9 +21,7 @@ int upload(sgmm_ctx* c, DevBuf<T>& buf, const T* src, size_t n) {
   return 0;
 }
 
-void begin_call(sgmm_ctx* c) {
-  for (int i = 0; i < SGMM_T_COUNT; i++) c->stage_ms[i] = 0.f;
-}
+void begin_call(sgmm_ctx* c) { sgmm_stage_reset(c); }
 
 constexpr int kViterbiC[] = {2, 3, 4, 5, 6, 8, 10, 12, 16};
 
@@ -227,6 +225,8 @@ int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t*
     if (state_off[s + 1] < state_off[s]) SGMM_FAIL(c, "set_model: state_off not monotone");
     max_d = std::max(max_d, state_off[s + 1] - state_off[s]);
   }
+  // the per-cell argmin is stored in 16 bits (d_Amin; DensityIdx is uint16_t in the reference too, Types.hpp:17)
+  if (max_d > 65535) SGMM_FAIL(c, "set_model: a state has more than 65535 densities (DensityIdx is 16 bit)");
   const uint32_t npair = dim / 2;
   std::vector<double2> mT((size_t)npair * D), vT((size_t)npair * D);
   std::vector<double> mt(D, 0.0), vt(D, 0.0);
@@ -667,6 +667,10 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   c->h_t128_end.swap(t128_end); c->h_t256_end.swap(t256_end);
   c->h_frame_off.assign(frame_off, frame_off + U + 1);
   c->h_aut_off.assign(aut_off, aut_off + U + 1);
+  // whatever the emission matrix / aligned columns held belongs to the previous corpus layout: the cached E-step
+  // (k_rescore_cached) must not index it with the new offsets
+  c->ali_has_cols = false;
+  c->E_model_version = 0;
   return 0;
 }
 
@@ -706,7 +710,7 @@ bool load_nccl(std::string& err) {
 }  // namespace
 
 int sgmm_nccl_allreduce(sgmm_ctx* c, double* d_buf, size_t n) {
-  if (!c->nccl_comm || c->world <= 1) return 0;
+  if (!c->nccl_comm || c->world <= 1 || !c->allreduce) return 0;
   StageTimer st(c, SGMM_T_ALLREDUCE);
   const int ncclFloat64 = 8, ncclSum = 0;
   int rc = g_nccl.AllReduce(d_buf, d_buf, n, ncclFloat64, ncclSum, c->nccl_comm, c->stream);
@@ -741,11 +745,7 @@ int sgmm_stage_ms(sgmm_ctx* c, float* ms) {
   cudaSetDevice(c->device);
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   for (int i = 0; i < SGMM_T_COUNT; i++) {
-    if (c->stage_ms[i] < 0.f) {
-      float v = 0.f;
-      cudaEventElapsedTime(&v, c->ev[2 * i], c->ev[2 * i + 1]);
-      c->stage_ms[i] = v;
-    }
+    sgmm_stage_fold(c, i);
     ms[i] = c->stage_ms[i];
   }
   return 0;
@@ -768,6 +768,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
+  if (!strcmp(key, "allreduce")) { c->allreduce = value != 0; return 0; }   // 0: sgmm_accumulate* return this rank's partial sums
   if (!strcmp(key, "tc_pack")) { c->tc_pack = value != 0; return 0; }   // takes effect at the next sgmm_set_corpus
   if (!strcmp(key, "upload_chunks")) {
     if (value < 1 || value > sgmm_ctx::kFeatChunks) SGMM_FAIL(c, "set_option: upload_chunks out of range");
@@ -796,6 +797,15 @@ int sgmm_get_counter(sgmm_ctx* c, const char* key, int64_t* value) {
     return 0;
   }
   if (!strcmp(key, "scorer")) { *value = sgmm_effective_scorer(c); return 0; }
+  if (!strcmp(key, "frames_global")) {   // frames behind the last (all-reduced) statistics / AM-score sum
+    if (!c->d_acc.p || c->Dtot == 0) SGMM_FAIL(c, "get_counter: no statistics yet");
+    double v = 0.0;
+    SGMM_CHECK(c, cudaMemcpyAsync(&v, c->d_acc.p + (size_t)c->Dtot * (1 + 2 * (size_t)c->dim) + 1, sizeof(v), cudaMemcpyDeviceToHost, c->stream));
+    SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+    *value = (int64_t)v;
+    return 0;
+  }
+  if (!strcmp(key, "packs")) { *value = (int64_t)c->n_packs; return 0; }   // packed GEMM tasks of the resident corpus
   // operand form the wide GEMM runs with (k_score_tc.cu): 0 tf32 hi/lo (3xTF32), 1 fp16 hi/lo (kind::f16);
   // k-steps per tile of that form
   if (!strcmp(key, "tc_form")) { *value = (c->tc_ok && c->tc_tile_rows == 256 && c->tc_f16_ok && c->tc_f16 != 0) ? 1 : 0; return 0; }

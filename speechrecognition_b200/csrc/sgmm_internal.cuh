@@ -53,8 +53,12 @@ struct sgmm_ctx {
   cudaStream_t stream = nullptr;
   std::string err;
   uint64_t launches = 0;
+  // stage stopwatch: a stage may be bracketed several times per call (chunk loops); every bracket gets its own event
+  // pair out of a ring, sgmm_stage_ms adds them up (ring full: the pairs are folded into stage_ms after a sync)
+  static constexpr int kStageRing = 8;
   float stage_ms[SGMM_T_COUNT] = {0};
-  cudaEvent_t ev[2 * SGMM_T_COUNT] = {nullptr};
+  int stage_n[SGMM_T_COUNT] = {0};
+  cudaEvent_t ev[2 * SGMM_T_COUNT * kStageRing] = {nullptr};
   cudaEvent_t tev[2] = {nullptr, nullptr};
   // side streams so that independent launches (the Viterbi shape classes) overlap
   static constexpr int kAux = 16;
@@ -193,6 +197,7 @@ struct sgmm_ctx {
   // ---- NCCL (dlopen'ed lazily)
   void* nccl_comm = nullptr;
   int rank = 0, world = 1;
+  bool allreduce = true;          // option "allreduce": 0 leaves the per-rank partial sums un-reduced (checks)
 };
 
 #define SGMM_CHECK(ctx, call)                                                             \
@@ -213,10 +218,30 @@ struct sgmm_ctx {
     SGMM_CHECK(ctx, cudaGetLastError());           \
   } while (0)
 
-struct StageTimer {  // CUDA-event bracket on the context's stream, accumulated into stage_ms at read time
+// CUDA-event brackets on the context's stream; sgmm_stage_ms sums every bracket of a stage since the call began
+inline void sgmm_stage_fold(sgmm_ctx* c, int idx) {
+  for (int i = 0; i < c->stage_n[idx]; i++) {
+    cudaEvent_t a = c->ev[2 * (idx * sgmm_ctx::kStageRing + i)], b = c->ev[2 * (idx * sgmm_ctx::kStageRing + i) + 1];
+    float v = 0.f;
+    if (cudaEventSynchronize(b) == cudaSuccess && cudaEventElapsedTime(&v, a, b) == cudaSuccess) c->stage_ms[idx] += v;
+  }
+  c->stage_n[idx] = 0;
+}
+inline void sgmm_stage_begin(sgmm_ctx* c, int idx) {
+  if (c->stage_n[idx] == sgmm_ctx::kStageRing) sgmm_stage_fold(c, idx);
+  cudaEventRecord(c->ev[2 * (idx * sgmm_ctx::kStageRing + c->stage_n[idx])], c->stream);
+}
+inline void sgmm_stage_end(sgmm_ctx* c, int idx) {
+  cudaEventRecord(c->ev[2 * (idx * sgmm_ctx::kStageRing + c->stage_n[idx]) + 1], c->stream);
+  c->stage_n[idx]++;
+}
+inline void sgmm_stage_reset(sgmm_ctx* c) {
+  for (int i = 0; i < SGMM_T_COUNT; i++) { c->stage_ms[i] = 0.f; c->stage_n[i] = 0; }
+}
+struct StageTimer {
   sgmm_ctx* c; int idx;
-  StageTimer(sgmm_ctx* c, int idx) : c(c), idx(idx) { cudaEventRecord(c->ev[2 * idx], c->stream); }
-  ~StageTimer() { cudaEventRecord(c->ev[2 * idx + 1], c->stream); c->stage_ms[idx] = -1.f; }
+  StageTimer(sgmm_ctx* c, int idx) : c(c), idx(idx) { sgmm_stage_begin(c, idx); }
+  ~StageTimer() { sgmm_stage_end(c, idx); }
 };
 
 // kernels / launchers (defined in k_*.cu)

@@ -19,11 +19,10 @@ int require(sgmm_ctx* c, bool model, bool feats, bool corpus) {
   return 0;
 }
 
-inline size_t acc_len(const sgmm_ctx* c) { return (size_t)c->Dtot * (1 + 2 * (size_t)c->dim) + 1; }
+// [count D | sum_x D*d | sum_xx D*d | score_sum | frames]: one contiguous block = the all-reduce payload
+inline size_t acc_len(const sgmm_ctx* c) { return (size_t)c->Dtot * (1 + 2 * (size_t)c->dim) + 2; }
 
-void reset_stage(sgmm_ctx* c) {
-  for (int i = 0; i < SGMM_T_COUNT; i++) c->stage_ms[i] = 0.f;
-}
+void reset_stage(sgmm_ctx* c) { sgmm_stage_reset(c); }
 
 // emission scoring through whichever scorer is selected
 int launch_emission_any(sgmm_ctx* c, bool dense, uint64_t f0, uint64_t nf, double* scores, uint32_t* argmin) {
@@ -357,7 +356,7 @@ int sgmm_am_score_sum(sgmm_ctx* c, double* score_sum) {
     if (sgmm_launch_score_sum(c)) return 1;
   } else if (rescore_common(c, false)) return 1;
   double* slot = c->d_acc.p + (size_t)c->Dtot * (1 + 2 * (size_t)c->dim);
-  if (sgmm_nccl_allreduce(c, slot, 1)) return 1;
+  if (sgmm_nccl_allreduce(c, slot, 2)) return 1;
   if (score_sum) SGMM_CHECK(c, cudaMemcpyAsync(score_sum, slot, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   return 0;
