@@ -126,7 +126,28 @@ class ClockSampler(threading.Thread):
                 "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
-def cpu_reference_rate(args, tables, corp, lex, n_utts, threads, keep=False):
+def checker_model(args, tables, lex):
+    """The CPU checker's model object for `tables` and the parameter tables it REALLY holds.  The unmodified reference
+    can only load a model from a .mix file, whose read() re-runs finalize on the stored statistics
+    (Mixtures.cpp:748-878): its parameters then differ from `tables` in the last bits, so the GPU arm is given the
+    checker's own tables — both sides score with bit-identical parameters."""
+    from oracle import binding
+    tdp = (3.0, 0.0, 30.0)
+    if binding.have_ref():
+        import tempfile
+        from speechrecognition_b200 import mixio
+        with tempfile.NamedTemporaryFile(suffix=".mix", delete=False) as f:
+            path = f.name
+        mixio.write_mix(path, args.dim, tables)
+        M = binding.Reference(args.dim, lex.num_states, "mixture", True, tdp, lex.silence_state, mix_path=path)
+        os.unlink(path)
+        return M, "reference", M.tables()
+    M = binding.Oracle(args.dim, lex.num_states, "mixture", True, tdp, lex.silence_state)
+    M.load_tables(tables)
+    return M, "port", tables
+
+
+def cpu_reference_rate(args, tables, corp, lex, n_utts, threads, keep=False, model=None):
     """frames/s of the reference's own CPU path (align_sequence_full per utterance + accumulate) on the
     first n_utts utterances, `threads` utterance shards in parallel (the reference itself is single-threaded,
     Training.cpp:168-183; independent shards are how it would use more cores)."""
@@ -136,19 +157,7 @@ def cpu_reference_rate(args, tables, corp, lex, n_utts, threads, keep=False):
     ao = corp["aut_off"][:n_utts + 1].astype(np.uint32)
     F = int(fo[-1])
     x = corp["x"][:F]
-    tdp = (3.0, 0.0, 30.0)
-    kind = "reference" if binding.have_ref() else "port"
-    if kind == "reference":
-        import tempfile
-        from speechrecognition_b200 import mixio
-        with tempfile.NamedTemporaryFile(suffix=".mix", delete=False) as f:
-            path = f.name
-        mixio.write_mix(path, args.dim, tables)
-        M = binding.Reference(args.dim, lex.num_states, "mixture", True, tdp, lex.silence_state, mix_path=path)
-        os.unlink(path)
-    else:
-        M = binding.Oracle(args.dim, lex.num_states, "mixture", True, tdp, lex.silence_state)
-        M.load_tables(tables)
+    M, kind, _ = model if model is not None else checker_model(args, tables, lex)
     shards = np.array_split(np.arange(n_utts), threads)
     states = np.zeros(F, np.uint32)
     costs = np.zeros(n_utts, np.float64)
@@ -338,6 +347,10 @@ def run_ours(args):
 
     lex, tables, corp = make_workload(args, rank)
     F, U = int(corp["frame_off"][-1]), args.utts
+    checker = None
+    if world == 1 and not args.no_cpu_baseline:
+        checker = checker_model(args, tables, lex)
+        tables = checker[2]          # the parameters the checker scores with, bit for bit
     ctx = capi.Context(local)
     if world > 1:
         uid = torch.from_numpy(capi.Context.comm_unique_id() if rank == 0 else np.zeros(128, np.uint8)).cuda()
@@ -523,7 +536,7 @@ def run_ours(args):
     }
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
-        r = cpu_reference_rate(args, tables, corp, lex, args.ref_utts, cores, keep=True)
+        r = cpu_reference_rate(args, tables, corp, lex, args.ref_utts, cores, keep=True, model=checker)
         line["parity_check"] = parity_check(ctx, args, tables, corp, r, (ali_pin, cost_pin, stat_pin, x_pin))
         line["cpu_baseline"] = {"value": r["value"], "unit": "frames/s", "cores": cores, "kind": r["kind"],
                                 "sample": "first %d utterances (%d frames) of the shard, one pass; alignment in %d parallel "
