@@ -49,10 +49,38 @@ const char* sgmm_version(void);
  * density j = state_off[s] + k is the k-th entry of mixtures_[s].  mean / inv_var are [D*dim] f64
  * (means_ / vars_inv_ rows), norm[D] = norm_[var_idx], log_weight[D] = mean_weights_log_[mean_idx].
  * The device keeps them in f64 and evaluates density_score_sse's exact operation order
- * (Mixtures.cpp:645-690). */
+ * (Mixtures.cpp:645-690).  One upload of the four arrays; every derived table (transposes, f32 / tf32 / fp16 operand
+ * images, guard constants) is built by device kernels.  Transactional: the new model is built beside the current one
+ * and swapped in on success — after a failed call the context still holds the previous model. */
 int sgmm_set_model(sgmm_ctx* ctx, uint32_t dim, uint32_t n_states, const uint32_t* state_off,
                    const double* mean, const double* inv_var, const double* norm,
                    const double* log_weight);
+
+/* MixtureModel::finalize + calculate_variance (Mixtures.cpp:374-461, :251-275) ON THE DEVICE, from the
+ * statistics the last sgmm_accumulate / sgmm_accumulate_soft / sgmm_align_accumulate call left resident (already
+ * all-reduced over the ranks): mean = sum_x / count, weight = count / (sum of the state's counts), log weight,
+ * variance = (var_seed + sum_xx [pooled over the state / over everything]) / count - mean_ref^2 around the density's own
+ * (pooling 0 = NO_POOLING), the state's (1 = MIXTURE_POOLING) or the global (2 = GLOBAL_POOLING) mean, its inverse and
+ * norm = (d log 2 pi + sum_i log var_i) / 2 — the reference's operation order (sums over densities and dimensions
+ * in index order; divisions, products and square roots are IEEE-exact on both sides; `log` is the device's, <= 1 ulp from
+ * glibc's).  var_seed is minimal_variance_value_ (1e-4, Mixtures.cpp:243), added once whatever the number of GPUs.
+ * The new parameters replace the context's model exactly as sgmm_set_model would — every derived table is rebuilt on
+ * the device — without leaving the GPU; the topology (state_off) is unchanged.  Split / eliminate stay host-side
+ * topology edits (fetch what they need with sgmm_get_statistics / sgmm_get_model, then sgmm_set_model). */
+int sgmm_mstep(sgmm_ctx* ctx, int pooling, double var_seed);
+
+/* Host copies of the current model's parameters, state-major as in sgmm_set_model (any pointer may be NULL); var[D*dim]
+ * and weight[D] (vars_ / mean_weights_) exist only after sgmm_mstep. */
+int sgmm_get_model(sgmm_ctx* ctx, double* mean, double* inv_var, double* norm, double* log_weight, double* var,
+                   double* weight);
+
+/* Host copies of the statistics of the last accumulate call (same layout and NULL rules as sgmm_accumulate's outputs);
+ * they stay resident on the device until the next accumulate call. */
+int sgmm_get_statistics(sgmm_ctx* ctx, double* count, double* sum_x, double* sum_xx, double* score_sum);
+
+/* Test hook: the raw bytes of one derived table of the current model ("meanT", "invT", "meanR", "invU", "mu32", "h32",
+ * "mu32T", "c32", "sguard", "Bimg", "sguard_tc", "Bimg16", "sguard16", ...).  *bytes receives the size; out may be NULL. */
+int sgmm_debug_table(sgmm_ctx* ctx, const char* name, void* out, size_t cap, size_t* bytes);
 
 /* ---- corpus --------------------------------------------------------------------------------- */
 /* Corpus::features_ (Corpus.hpp:75-81): one contiguous row-major float[n_frames * dim]; one H2D copy,
@@ -180,11 +208,16 @@ int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
  * "tc_wide" (-1 auto, 0, 1; read by sgmm_set_model): 256-density GEMM tiles (the N = 256 kernel) instead of 128;
  *   auto picks them when some state has more than 128 densities and the tile ring fits shared memory.
  * "tc_epi16" (default 0): sixteen instead of eight epilogue warps per GEMM unit (measured slower; kept as an A/B switch).
+ * "host_tables" (default 0; read by sgmm_set_model): 1 = derive the model tables on the host (the previous builder, kept
+ *   as the checker of the device builder: same tables, same bits).
+ * "allreduce" (default 1): 0 = sgmm_accumulate* skip the ncclAllReduce and return this rank's partial sums (checks).
  * "tc_debug": timing experiments for the tensor-core kernel — any bit other than 32 (cycle profile, read with the
  *   "tc_prof1".."tc_prof12" counters) makes results INVALID; never set in production. */
 int sgmm_set_option(sgmm_ctx* ctx, const char* key, int64_t value);
 /* "fallbacks": (frame, state) cells whose f32 top-2 gap was inside the error bound and were re-scanned in
- * f64 since the counter was last read; "scorer": the scorer the automatic choice resolves to. */
+ * f64 since the counter was last read; "scorer": the scorer the automatic choice resolves to; "tc_form": 1 when the wide
+ * GEMM runs fp16 hi/lo operands; "packs": packed GEMM tasks of the resident corpus; "frames_global": frames behind the
+ * last all-reduced statistics / AM-score sum (every rank's shard). */
 int sgmm_get_counter(sgmm_ctx* ctx, const char* key, int64_t* value);
 
 /* ---- multi-GPU ------------------------------------------------------------------------------ */
@@ -202,7 +235,8 @@ enum {
   SGMM_T_REDUCE = 5, SGMM_T_ALLREDUCE = 6, SGMM_T_D2H = 7,
   SGMM_T_SCORE_FILTER = 8,   /* part of SCORE: the f32 / tensor-core candidate kernel (k_tc_gemm) */
   SGMM_T_SCORE_REFINE = 9,   /* part of SCORE: f64 certification + rescan kernels */
-  SGMM_T_COUNT = 10
+  SGMM_T_MSTEP = 10,         /* sgmm_mstep / sgmm_set_model: parameter kernels + device table build (K5) */
+  SGMM_T_COUNT = 11
 };
 int sgmm_stage_ms(sgmm_ctx* ctx, float* ms /* [SGMM_T_COUNT] */);
 /* Device-side stopwatch on the context's stream (CUDA events): start, then stop returns the elapsed ms

@@ -11,7 +11,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsietill_b200.so")
 
-T_NAMES = ["h2d", "score", "viterbi", "rescore", "sort", "reduce", "allreduce", "d2h", "score_filter", "score_refine"]
+T_NAMES = ["h2d", "score", "viterbi", "rescore", "sort", "reduce", "allreduce", "d2h", "score_filter", "score_refine", "mstep"]
 TDP_SOURCE, TDP_DESTINATION = 0, 1
 
 ALI_DTYPE = np.dtype([("count", np.uint16), ("state", np.uint16), ("weight", np.float32)])  # Types.hpp:29-38
@@ -23,7 +23,7 @@ SYMBOLS = [
     "sgmm_accumulate_soft", "sgmm_process_features", "sgmm_align_accumulate",
     "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
     "sgmm_launch_count", "sgmm_timer_start", "sgmm_timer_stop", "sgmm_host_alloc", "sgmm_host_free",
-    "sgmm_set_option", "sgmm_get_counter",
+    "sgmm_set_option", "sgmm_get_counter", "sgmm_mstep", "sgmm_get_model", "sgmm_get_statistics", "sgmm_debug_table",
 ]
 
 _lib = None
@@ -102,6 +102,39 @@ class Context:
         mi, vi = t["mean_idx"].astype(np.int64), t["var_idx"].astype(np.int64)
         self.set_model(dim, t["mix_offsets"], t["means"].reshape(-1, dim)[mi], t["vars_inv"].reshape(-1, dim)[vi],
                        t["norm"][vi], t["mean_wlog"][mi])
+
+    POOLING = {"none": 0, "mixture": 1, "global": 2}
+
+    def mstep(self, pooling, var_seed=1e-4):
+        """MixtureModel::finalize on the device from the resident statistics; the new model replaces the current one."""
+        self._ck(self.L.sgmm_mstep(self.h, int(self.POOLING.get(pooling, pooling)), C.c_double(var_seed)))
+
+    def get_model(self, want_var=False):
+        D, d = self.D, self.dim
+        mean, inv = np.empty((D, d), np.float64), np.empty((D, d), np.float64)
+        norm, logw = np.empty(D, np.float64), np.empty(D, np.float64)
+        var = np.empty((D, d), np.float64) if want_var else None
+        w = np.empty(D, np.float64) if want_var else None
+        self._ck(self.L.sgmm_get_model(self.h, _ptr(mean, C.c_double), _ptr(inv, C.c_double), _ptr(norm, C.c_double),
+                                       _ptr(logw, C.c_double), _ptr(var, C.c_double), _ptr(w, C.c_double)))
+        return {"mean": mean, "inv_var": inv, "norm": norm, "log_weight": logw, "var": var, "weight": w}
+
+    def get_statistics(self):
+        D, d = self.D, self.dim
+        cnt, sx, sxx = np.empty(D, np.float64), np.empty((D, d), np.float64), np.empty((D, d), np.float64)
+        ssum = np.zeros(1, np.float64)
+        self._ck(self.L.sgmm_get_statistics(self.h, _ptr(cnt, C.c_double), _ptr(sx, C.c_double), _ptr(sxx, C.c_double),
+                                            _ptr(ssum, C.c_double)))
+        return cnt, sx, sxx, float(ssum[0])
+
+    def debug_table(self, name):
+        """Raw bytes of one derived model table (tests: device builder vs host builder)."""
+        n = C.c_size_t(0)
+        self._ck(self.L.sgmm_debug_table(self.h, name.encode(), None, C.c_size_t(0), C.byref(n)))
+        out = np.empty(n.value, np.uint8)
+        if n.value:
+            self._ck(self.L.sgmm_debug_table(self.h, name.encode(), out.ctypes.data_as(C.c_void_p), C.c_size_t(n.value), C.byref(n)))
+        return out
 
     def set_features(self, x):
         x = np.ascontiguousarray(x, np.float32)

@@ -90,6 +90,7 @@ MixtureModel::MixtureModel(Configuration const& config, size_t dimension, size_t
   const std::string action = config.get_string("action", "");
   // "host-only": M-step and file formats without a GPU (CPU tests); every compute method then throws
   if (!config.get_bool("host-only", false)) device_.reset(new Device((int)config.get_uint("device", 0)));
+  device_mstep_ = device_ && config.get_bool("device-mstep", true);
   if (!from.empty() && action == "recognize") {
     std::ifstream in(from.c_str(), std::ios::binary);
     if (!in.good()) fail("cannot open " + from);
@@ -127,6 +128,7 @@ MixtureDensity MixtureModel::create_mixture_density(DensityIdx var_index) {
 
 // Mixtures.cpp:237-245: the second-order sums restart at 1e-4, not 0.
 void MixtureModel::reset_accumulators() {
+  stats_on_device_ = false;
   std::fill(mean_accumulators_.begin(), mean_accumulators_.end(), 0.0);
   std::fill(mean_weight_accumulators_.begin(), mean_weight_accumulators_.end(), 0.0);
   std::fill(var_accumulators_.begin(), var_accumulators_.end(), minimal_variance_value_);
@@ -158,6 +160,7 @@ void pack_tables(size_t dim, std::vector<Mixture> const& mixtures, std::vector<d
 void MixtureModel::sync_device() const {
   if (!device_) fail("built host-only: no GPU context (there is no CPU scoring path)");
   if (uploaded_version_ == version_) return;
+  ensure_host();
   std::vector<uint32_t> off;
   std::vector<double> pm, pv, pn, pw;
   pack_tables(dimension, mixtures_, means_, vars_inv_, norm_, mean_weights_log_, off, pm, pv, pn, pw);
@@ -173,6 +176,7 @@ Device& MixtureModel::scratch() const {
   if (!device_) fail("built host-only: no GPU context (there is no CPU scoring path)");
   if (!scratch_) scratch_.reset(new Device(device_->index()));   // same GPU as the main context
   if (scratch_version_ != version_) {
+    ensure_host();
     std::vector<uint32_t> off;
     std::vector<double> pm, pv, pn, pw;
     pack_tables(dimension, mixtures_, means_, vars_inv_, norm_, mean_weights_log_, off, pm, pv, pn, pw);
@@ -226,31 +230,60 @@ void MixtureModel::accumulate(ConstAlignmentIter alignment_begin, ConstAlignment
     resident_ali_frames_ = n;
     resident_ali_sum_ = sum;
   }
+  double score_sum = 0.0;
+  if (!first_pass && !max_approx)   // posterior-weighted branch, :300-357 (score_sum = sum of sum scores)
+    device_->check(sgmm_accumulate_soft(c, nullptr, nullptr, nullptr, &score_sum), "sgmm_accumulate_soft");
+  else
+    device_->check(sgmm_accumulate(c, first_pass ? 1 : 0, nullptr, nullptr, nullptr, &score_sum), "sgmm_accumulate");
+  last_score_sum_ = score_sum;
+  // the statistics stay on the GPU (one all-reduced block); finalize() consumes them there, the host arrays follow on demand
+  stats_on_device_ = true;
+  if (!device_mstep_) ensure_host();
+}
+
+// Whatever the GPU holds that the host arrays do not: the accumulators of the last accumulate() and / or the parameters
+// of the last device finalize().  The per-density statistics are folded into the reference's slots (:333-357); the
+// variance sums start from the 1e-4 seed exactly once, whatever the number of GPUs behind the all-reduce.
+void MixtureModel::ensure_host() const {
+  if (!stats_on_device_ && !params_on_device_) return;
+  MixtureModel& self = *const_cast<MixtureModel*>(this);
+  sgmm_ctx* c = device_->ctx();
   std::vector<uint32_t> off(mixtures_.size() + 1, 0);
   for (size_t m = 0; m < mixtures_.size(); m++) off[m + 1] = off[m] + (uint32_t)mixtures_[m].size();
   const size_t D = off.back(), d = dimension;
-  std::vector<double> count(D), sum_x(D * d), sum_xx(D * d);
-  double score_sum = 0.0;
-  if (!first_pass && !max_approx)   // posterior-weighted branch, :300-357 (score_sum = sum of sum scores)
-    device_->check(sgmm_accumulate_soft(c, count.data(), sum_x.data(), sum_xx.data(), &score_sum), "sgmm_accumulate_soft");
-  else
-    device_->check(sgmm_accumulate(c, first_pass ? 1 : 0, count.data(), sum_x.data(), sum_xx.data(), &score_sum),
-                   "sgmm_accumulate");
-  last_score_sum_ = score_sum;
-  // fold the per-density statistics into the reference's slots (:333-357); the variance sums start
-  // from the 1e-4 seed exactly once, whatever the number of GPUs behind the all-reduce
-  reset_accumulators();
-  size_t j = 0;
-  for (Mixture const& mix : mixtures_)
-    for (MixtureDensity const& md : mix) {
-      mean_weight_accumulators_[md.mean_idx] += count[j];
-      var_weight_accumulators_[md.var_idx] += count[j];
-      double* ma = &mean_accumulators_[(size_t)md.mean_idx * d];
-      double* va = &var_accumulators_[(size_t)md.var_idx * d];
-      for (size_t i = 0; i < d; i++) ma[i] += sum_x[j * d + i];
-      for (size_t i = 0; i < d; i++) va[i] += sum_xx[j * d + i];
-      j++;
-    }
+  if (stats_on_device_) {
+    std::vector<double> count(D), sum_x(D * d), sum_xx(D * d);
+    device_->check(sgmm_get_statistics(c, count.data(), sum_x.data(), sum_xx.data(), nullptr), "sgmm_get_statistics");
+    self.reset_accumulators();
+    size_t j = 0;
+    for (Mixture const& mix : mixtures_)
+      for (MixtureDensity const& md : mix) {
+        self.mean_weight_accumulators_[md.mean_idx] += count[j];
+        self.var_weight_accumulators_[md.var_idx] += count[j];
+        double* ma = &self.mean_accumulators_[(size_t)md.mean_idx * d];
+        double* va = &self.var_accumulators_[(size_t)md.var_idx * d];
+        for (size_t i = 0; i < d; i++) ma[i] += sum_x[j * d + i];
+        for (size_t i = 0; i < d; i++) va[i] += sum_xx[j * d + i];
+        j++;
+      }
+    stats_on_device_ = false;
+  }
+  if (params_on_device_) {   // exactly what the device scores with (its log differs from glibc's by <= 1 ulp)
+    std::vector<double> mean(D * d), inv(D * d), var(D * d), norm(D), logw(D), w(D);
+    device_->check(sgmm_get_model(c, mean.data(), inv.data(), norm.data(), logw.data(), var.data(), w.data()), "sgmm_get_model");
+    size_t j = 0;
+    for (Mixture const& mix : mixtures_)
+      for (MixtureDensity const& md : mix) {
+        memcpy(&self.means_[(size_t)md.mean_idx * d], &mean[j * d], d * sizeof(double));
+        memcpy(&self.vars_[(size_t)md.var_idx * d], &var[j * d], d * sizeof(double));
+        memcpy(&self.vars_inv_[(size_t)md.var_idx * d], &inv[j * d], d * sizeof(double));
+        self.norm_[md.var_idx] = norm[j];
+        self.mean_weights_[md.mean_idx] = w[j];
+        self.mean_weights_log_[md.mean_idx] = logw[j];
+        j++;
+      }
+    params_on_device_ = false;
+  }
 }
 
 // ---- M-step (host, f64) ------------------------------------------------------------------------------------
@@ -269,8 +302,24 @@ void MixtureModel::calculate_variance(DensityIdx var_idx, const double* mean) {
   norm_[var_idx] = n / 2;
 }
 
-// Mixtures.cpp:374-461
+// Mixtures.cpp:374-461.  With the statistics still on the GPU the M-step runs there (sgmm_mstep: the same operation
+// order; every derived table is rebuilt by device kernels) and the model never leaves the device.
 void MixtureModel::finalize() {
+  if (stats_on_device_ && device_mstep_) {
+    const int pooling = var_model == NO_POOLING ? 0 : var_model == MIXTURE_POOLING ? 1 : 2;
+    device_->check(sgmm_mstep(device_->ctx(), pooling, minimal_variance_value_), "sgmm_mstep");
+    device_->check(sgmm_set_option(device_->ctx(), "max_approx", max_approx_ ? 1 : 0), "sgmm_set_option");
+    mark_dirty();
+    uploaded_version_ = version_;
+    params_on_device_ = true;
+    return;
+  }
+  ensure_host();
+  finalize_host();
+  mark_dirty();
+}
+
+void MixtureModel::finalize_host() {
   const size_t d = dimension;
   double total_observations = 0.0;
   std::vector<double> pooled(d);
@@ -308,13 +357,13 @@ void MixtureModel::finalize() {
     for (size_t i = 0; i < d; i++) pooled[i] = pooled[i] / total_observations;
     calculate_variance(0, pooled.data());
   }
-  mark_dirty();
 }
 
 // Mixtures.cpp:465-543: mixtures ascending, densities descending; the clone goes to the end of the mixture
 // with mean - sigma (the original moves to mean + sigma); weight, log weight and count are copied, not
 // halved; with NO_POOLING the variance slot is cloned too.
 void MixtureModel::split(size_t min_obs) {
+  ensure_host();
   const size_t d = dimension;
   for (Mixture& mix : mixtures_) {
     for (size_t k = mix.size(); k-- > 0;) {
@@ -348,6 +397,7 @@ void MixtureModel::split(size_t min_obs) {
 
 // Mixtures.cpp:547-576: drop densities seen fewer than min_obs times (descending inside a mixture).
 void MixtureModel::eliminate(double min_obs) {
+  ensure_host();
   for (size_t m = 0; m < mixtures_.size(); m++) {
     Mixture& mix = mixtures_[m];
     for (size_t k = mix.size(); k-- > 0;) {
@@ -438,6 +488,7 @@ double MixtureModel::score(FeatureIter const& iter, StateIdx mixture_idx) const 
 void MixtureModel::read(std::istream& in) {
   char magic[8];
   in.read(magic, sizeof(magic));
+  stats_on_device_ = params_on_device_ = false;   // the file replaces everything
   if (in.gcount() != (std::streamsize)sizeof(magic)) fail("Error reading magic header");
   if (memcmp(magic, kMagic, 8) != 0) fail("Invalid magic header");
   uint32_t version, dim;
@@ -491,6 +542,7 @@ void MixtureModel::read(std::istream& in) {
 }
 
 void MixtureModel::write(std::ostream& out) const {
+  ensure_host();
   out.write(kMagic, sizeof(kMagic));
   put(out, kVersion);
   put(out, (uint32_t)dimension);
@@ -519,6 +571,7 @@ void MixtureModel::write(std::ostream& out) const {
 
 // ---- raw tables (tests) ------------------------------------------------------------------------------------
 MixtureModel::Tables MixtureModel::export_tables() const {
+  ensure_host();
   Tables t;
   t.means = means_; t.mean_acc = mean_accumulators_; t.mean_w = mean_weights_; t.mean_wlog = mean_weights_log_;
   t.mean_wacc = mean_weight_accumulators_; t.vars = vars_; t.vars_inv = vars_inv_; t.var_acc = var_accumulators_;
@@ -535,6 +588,7 @@ MixtureModel::Tables MixtureModel::export_tables() const {
 
 void MixtureModel::import_tables(Tables const& t) {
   if (t.mix_offsets.size() != mixtures_.size() + 1) fail("import_tables: wrong number of mixtures");
+  stats_on_device_ = params_on_device_ = false;
   means_ = t.means; mean_accumulators_ = t.mean_acc; mean_weights_ = t.mean_w; mean_weights_log_ = t.mean_wlog;
   mean_weight_accumulators_ = t.mean_wacc; vars_ = t.vars; vars_inv_ = t.vars_inv; var_accumulators_ = t.var_acc;
   var_weight_accumulators_ = t.var_wacc; norm_ = t.norm;

@@ -10,6 +10,7 @@ using namespace sietill_b200;
 
 namespace {
 thread_local std::string g_err;
+int g_device_mstep = 1;   // default of the "device-mstep" key for models built through this shim (tests run both)
 
 struct HostModel {
   Configuration config;
@@ -40,12 +41,13 @@ void copy_out(T* dst, std::vector<T> const& src) {
 extern "C" {
 
 const char* sthost_last_error() { return g_err.c_str(); }
+void sthost_set_device_mstep(int on) { g_device_mstep = on; }
 
 void* sthost_model_create(uint32_t dim, uint32_t n_mix, int pooling, int max_approx, int host_only, int device,
                           const char* load_from) {
   HostModel* h = new HostModel();
   const int rc = guarded([&] {
-    h->config.set("host-only", host_only != 0).set("device", (unsigned)device);
+    h->config.set("host-only", host_only != 0).set("device", (unsigned)device).set("device-mstep", g_device_mstep != 0);
     if (load_from && *load_from) h->config.set("load-mixtures-from", std::string(load_from)).set("action", std::string("recognize"));
     h->model.reset(new MixtureModel(h->config, dim, n_mix, pooling_of(pooling), max_approx != 0));
   });
@@ -211,6 +213,7 @@ int sthost_train(uint32_t dim, int pooling, int device, const float* x, uint64_t
     std::vector<WordIdx> w(words, words + word_off[n_utts]);
     Corpus corpus(x, dim, fo, w, wo);
     Configuration& cfg = h->config;
+    cfg.set("device-mstep", g_device_mstep != 0);
     cfg.set("device", (unsigned)device).set("tdp-loop", loop).set("tdp-forward", forward).set("tdp-skip", skip);
     cfg.set("min-obs", min_obs).set("num-splits", num_splits).set("num-aligns", num_aligns).set("num-estimates", num_estimates);
     cfg.set("alignment-pruning", alignment_pruning != 0).set("pruning-threshold", pruning_threshold);

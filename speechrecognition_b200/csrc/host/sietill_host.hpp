@@ -232,7 +232,11 @@ class MixtureModel : public FeatureScorer {
   const size_t dimension;
   const VarianceModel var_model;
 
-  // config keys: "load-mixtures-from" (+ "action" == "recognize"), as Mixtures.cpp:158-193; "device" (GPU index).
+  // config keys: "load-mixtures-from" (+ "action" == "recognize"), as Mixtures.cpp:158-193; "device" (GPU index);
+  // "device-mstep" (default true): accumulate() leaves the statistics on the GPU and finalize() runs there
+  // (sgmm_mstep) — the host copies of the accumulators / parameters are fetched lazily, only when a
+  // host-side method needs them (split, eliminate, write, the per-sequence scoring API); false = the statistics come
+  // home after every accumulate() and finalize() is the host code below.
   MixtureModel(Configuration const& config, size_t dimension, size_t num_mixtures, VarianceModel var_model,
                bool max_approx);
   ~MixtureModel();
@@ -241,7 +245,7 @@ class MixtureModel : public FeatureScorer {
   // E-step on the GPU (K3 + K4); max_approx == false is the posterior-weighted branch (sgmm_accumulate_soft).
   void accumulate(ConstAlignmentIter alignment_begin, ConstAlignmentIter alignment_end, FeatureIter feature_begin,
                   FeatureIter feature_end, bool first_pass, bool max_approx = true);
-  void finalize();                                                       // Mixtures.cpp:374-461 (host, f64)
+  void finalize();                                                       // Mixtures.cpp:374-461 (device, or host f64)
   void split(size_t min_obs);                                            // Mixtures.cpp:465-543
   void eliminate(double min_obs);                                        // Mixtures.cpp:547-576
   size_t num_densities() const;                                          // Mixtures.cpp:580-582
@@ -281,8 +285,14 @@ class MixtureModel : public FeatureScorer {
   friend class Trainer;
   friend class Recognizer;
   void calculate_variance(DensityIdx var_idx, const double* mean);
+  void finalize_host();
   MixtureDensity create_mixture_density(DensityIdx var_index);
   void mark_dirty() { ++version_; }
+  // device-resident M-step: which side holds the current accumulators / parameters
+  bool device_mstep_ = true;
+  mutable bool stats_on_device_ = false;    // the accumulators of the last accumulate() are on the GPU only
+  mutable bool params_on_device_ = false;   // the parameters of the last finalize() are on the GPU only
+  void ensure_host() const;                 // fetch whatever is device-only into the host arrays
 
   bool max_approx_;
   std::vector<double> means_, mean_accumulators_, mean_weights_, mean_weights_log_, mean_weight_accumulators_;

@@ -30,6 +30,8 @@
 
 #include <cuda_fp16.h>
 
+#include <cstring>
+
 #include "sgmm_internal.cuh"
 
 namespace sgmm_tc {
@@ -1798,7 +1800,15 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     ranges.push_back({c->n_frames, -1});
   }
   c->feat_pending = 0;
-  const bool need_prep = !c->tc_A_valid || c->tc_A_form != (f16 ? 1 : 0);
+  // the A rows (split / scaled features) depend on the features and on the operand form, never on the parameter
+  // values: a new model of the same shape (every EM iteration) reuses them
+  float eps_now = f16 ? c->tc_eps16 : c->tc_eps;
+  uint32_t eps_bits;
+  memcpy(&eps_bits, &eps_now, 4);
+  const uint64_t a_key = ((uint64_t)KP << 40) ^ ((uint64_t)(f16 ? 1 : 0) << 36) ^ ((uint64_t)(c->tc_full ? 1 : 0) << 37) ^
+                         ((uint64_t)c->dim << 44) ^ eps_bits;
+  const bool need_prep = !c->tc_A_valid || c->tc_A_key != a_key;
+  c->tc_A_key = a_key;
   c->tc_A_form = f16 ? 1 : 0;
   if (need_prep) {
     SGMM_CHECK(c, c->d_Ahi.reserve((size_t)c->n_frames * KP));

@@ -82,21 +82,23 @@ void sgmm_destroy(sgmm_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
-  c->d_meanT.release(); c->d_invT.release(); c->d_mean_tail.release(); c->d_inv_tail.release();
-  c->d_meanR.release(); c->d_invU.release(); c->d_var_of.release();
-  c->d_norm.release(); c->d_logw.release(); c->d_state_off.release(); c->d_x.release();
+  c->release_all(); c->spare.release_all();
+  c->d_x.release(); c->d_raw.release(); c->d_feat_off.release(); c->d_feat_norm.release();
   c->d_frame_off.release(); c->d_E_off.release(); c->d_aut.release(); c->d_aut_off.release();
   c->d_uniq.release(); c->d_uniq_off.release(); c->d_nuniq_pad.release(); c->d_pos2uniq.release();
-  c->d_tasks.release(); c->d_tasks64.release(); c->d_mu32.release(); c->d_mu32T.release(); c->d_Bimg16.release(); c->d_tile_info16.release(); c->d_sguard16.release(); c->d_h32.release(); c->d_c32.release();
-  c->d_sguard.release(); c->d_fallbacks.release(); c->d_tasks128.release(); c->d_tasks256.release(); c->d_Amin.release(); c->d_fcol.release();
-  c->d_Bimg.release(); c->d_tile_first.release(); c->d_tile_info.release(); c->d_Ahi.release(); c->d_Alo.release();
-  c->d_xnorm.release(); c->d_sguard_tc.release(); c->d_col_off.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
+  c->d_tasks.release(); c->d_tasks64.release(); c->d_tasks128.release(); c->d_tasks256.release();
+  c->d_fallbacks.release(); c->d_Amin.release(); c->d_fcol.release(); c->d_Ahi.release(); c->d_Alo.release();
+  c->d_xnorm.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
   c->d_sm_items.release(); c->d_sm_ent_a.release(); c->d_sm_ent_b.release();
+  c->d_pack_desc.release(); c->d_pack_uniq.release(); c->d_pack_rows.release(); c->d_pack_colmap.release();
   for (int i = 0; i < 2; i++) { c->d_keys[i].release(); c->d_vals[i].release(); }
-  c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release();
+  c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release(); c->d_soft_keys.release();
   c->d_partial.release(); c->d_acc.release(); c->d_score_part.release();
-  c->d_dense_scores.release(); c->d_dense_argmin.release();
+  c->d_dense_scores.release(); c->d_dense_argmin.release(); c->d_model_flags.release(); c->d_mstep_tmp.release();
+  c->d_lex_info.release(); c->d_lex_state.release(); c->d_lex_base.release(); c->d_lex_len.release(); c->d_lex_first.release();
+  c->d_lex_order.release(); c->d_rec_frame_off.release(); c->d_rec_tb_off.release(); c->d_rec_tb.release();
+  c->d_rec_words.release(); c->d_rec_nwords.release(); c->d_rec_score.release();
   for (auto& vc : c->vclasses) vc.d_utts.release();
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
   for (auto& ev : c->tev) if (ev) cudaEventDestroy(ev);
@@ -107,322 +109,6 @@ void sgmm_destroy(sgmm_ctx* c) {
   for (auto& ev : c->feat_ev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(c->stream);
   delete c;
-}
-
-// K5: pack the f64 parameter tables dim-pair-major (see k_score.cu).
-// fp16 form of the tensor-core operands (pooled models, 256-column tiles; k_tc_gemm256<KS, true>).  B row of density
-// j of state s: t_s * [ g_0..g_{d-1} | c | 0.. ], t_s = the power of two that brings the state's largest |entry| into
-// [2^13, 2^14), every entry split into fp16 hi + fp16 lo.  K = d + 1 takes ceil((d + 1) / 16) k-steps of 16 halves
-// (3 at d = 33, against 5 tf32 k-steps of 8) at the same cycles per MMA.  Per-state guard constants, in the slots
-// the epilogue multiplies with k_tc_prep16's {||s x||, s}: {max ||t g|| + flush terms, max |t c| + flush, 0}.
-static int build_f16_image(sgmm_ctx* c, bool enable, uint32_t dim, uint32_t n_states, const uint32_t* state_off,
-                           const double* mean, const double* inv_var, const double* norm, const double* log_weight,
-                           const std::vector<uint32_t>& col_off, const std::vector<uint32_t>& tile_first) {
-  c->tc_f16_ok = false;
-  if (!enable) return 0;
-  const uint32_t TR = 256, K = dim + 1, ks = (K + 15) / 16, KH = 16 * ks;
-  // error model of one split dot product against |a|.|b| (cf. tc_eps): 2^-22 per operand split, 2^-22 for the dropped
-  // lo.lo term; fp32 accumulation of 3 * 16 * ksteps products, assumed to truncate (2^-23 each)
-  const float eps = 3.f * 2.384185791015625e-07f + 3.f * 16.f * (float)ks * 1.1920928955078125e-07f;
-  const double inv2eps = 1.0 / (2.0 * (double)eps);
-  const uint32_t Dpad = col_off[n_states];
-  std::vector<__half> Bhi((size_t)Dpad * KH, __float2half(0.f)), Blo((size_t)Dpad * KH, __float2half(0.f));
-  std::vector<float4> sg(n_states, make_float4(0.f, 0.f, 0.f, 0.f));
-  std::vector<double> row(K);
-  for (uint32_t s = 0; s < n_states; s++) {
-    const uint32_t nreal = state_off[s + 1] - state_off[s];
-    double bmax = 0.0;
-    for (uint32_t j = state_off[s]; j < state_off[s + 1]; j++) {
-      double cc = norm[j] - log_weight[j];
-      for (uint32_t i = 0; i < dim; i++) {
-        const double mu = mean[(size_t)j * dim + i], iv = inv_var[(size_t)j * dim + i];
-        bmax = std::max(bmax, std::fabs(iv * mu));
-        cc += 0.5 * iv * mu * mu;
-      }
-      bmax = std::max(bmax, std::fabs(cc));
-    }
-    if (!(bmax < 1e300)) return 0;                       // non-finite model entries: keep the tf32 form
-    int e = 0;
-    std::frexp(std::max(bmax, 1e-300), &e);              // bmax = m 2^e, m in [0.5, 1)
-    const double ts = std::ldexp(1.0, 14 - e);           // bmax * ts in [2^13, 2^14)
-    double Gmax = 0.0, cabs = 0.0, flg = 0.0, flc = 0.0;
-    for (uint32_t q = 0; q < col_off[s + 1] - col_off[s]; q++) {
-      const size_t r = col_off[s] + q;
-      std::fill(row.begin(), row.end(), 0.0);
-      if (q >= nreal) {
-        row[dim] = 60000.0;                              // never-winning dummy (a certified dummy is rescanned)
-      } else {
-        const uint32_t j = state_off[s] + q;
-        double cc = norm[j] - log_weight[j];
-        for (uint32_t i = 0; i < dim; i++) {
-          const double mu = mean[(size_t)j * dim + i], iv = inv_var[(size_t)j * dim + i];
-          row[i] = -iv * mu * ts;
-          cc += 0.5 * iv * mu * mu;
-        }
-        row[dim] = cc * ts;
-      }
-      double G = 0.0, flrow = 0.0;
-      for (uint32_t k = 0; k < K; k++) {
-        const __half hi = __float2half_rn((float)row[k]);
-        const double rem = row[k] - (double)__half2float(hi);
-        const __half lo = __float2half_rn((float)rem);
-        Bhi[r * KH + k] = hi; Blo[r * KH + k] = lo;
-        double fl = 0.0;                                  // subnormal parts: see k_tc_prep16
-        if (rem != 0.0 && std::fabs(rem) < 6.103515625e-05) fl += std::max(std::fabs(rem), 2.98023223876953125e-08);
-        if (row[k] != 0.0 && std::fabs(row[k]) < 6.103515625e-05) fl += std::fabs(row[k]);
-        if (q < nreal) {
-          if (k < dim) { G += row[k] * row[k]; flrow = std::max(flrow, fl); }
-          else { cabs = std::max(cabs, std::fabs(row[k])); flc = std::max(flc, fl); }
-        }
-      }
-      if (q < nreal) { Gmax = std::max(Gmax, std::sqrt(G)); flg = std::max(flg, flrow); }
-    }
-    // a flushed / rounded B entry b_i errs by fl_i |a_i| <= fl_i ||a||: fold max_i fl_i * sqrt(d) / (2 eps) into the norm
-    sg[s] = make_float4((float)((Gmax + flg * std::sqrt((double)dim) * inv2eps) * 1.0001),
-                        (float)((cabs + flc * inv2eps) * 1.0001), 0.f, 0.f);
-  }
-  std::vector<uint2> tile_info;
-  std::vector<__half> img;
-  for (uint32_t s = 0; s < n_states; s++) {
-    const uint32_t nc = col_off[s + 1] - col_off[s];
-    for (uint32_t n0 = 0; n0 < nc; n0 += TR) {
-      const uint32_t N = std::min(TR, nc - n0);
-      const size_t off = img.size();
-      tile_info.push_back(make_uint2((uint32_t)(off / 8), N));     // 16-byte units
-      img.resize(off + (size_t)2 * ks * TR * 16, __float2half(0.f));
-      for (int op = 0; op < 2; op++) {
-        const std::vector<__half>& B = op ? Blo : Bhi;
-        __half* base = img.data() + off + (size_t)op * ks * TR * 16;
-        for (uint32_t kk = 0; kk < ks; kk++)
-          for (uint32_t r = 0; r < N; r++)
-            for (uint32_t e = 0; e < 16; e++) {
-              const uint32_t lin = kk * TR * 32 + r * 32 + e * 2;
-              const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
-              base[phys / 2] = B[(size_t)(col_off[s] + n0 + r) * KH + kk * 16 + e];
-            }
-      }
-    }
-    if (tile_info.size() != tile_first[s + 1]) { c->err = "f16 image: tile count differs from the tf32 image"; return 1; }
-  }
-  if (upload(c, c->d_Bimg16, img.data(), img.size()) || upload(c, c->d_tile_info16, tile_info.data(), tile_info.size()) ||
-      upload(c, c->d_sguard16, sg.data(), sg.size()))
-    return 1;
-  if (cudaStreamSynchronize(c->stream) != cudaSuccess) { c->err = "f16 image upload failed"; return 1; }
-  c->tc_ks16 = ks; c->tc_eps16 = eps; c->tc_f16_ok = true;
-  return 0;
-}
-
-int sgmm_set_model(sgmm_ctx* c, uint32_t dim, uint32_t n_states, const uint32_t* state_off,
-                   const double* mean, const double* inv_var, const double* norm, const double* log_weight) {
-  if (!c) return 1;
-  cudaSetDevice(c->device);
-  if (dim < 2 || dim > 128) SGMM_FAIL(c, "set_model: dim must be in [2, 128]");
-  if (n_states == 0 || n_states > 65535) SGMM_FAIL(c, "set_model: n_states must be in [1, 65535] (StateIdx is 16 bit)");
-  const uint32_t D = state_off[n_states];
-  if (state_off[0] != 0 || D == 0) SGMM_FAIL(c, "set_model: bad state_off");
-  uint32_t max_d = 0;
-  for (uint32_t s = 0; s < n_states; s++) {
-    if (state_off[s + 1] < state_off[s]) SGMM_FAIL(c, "set_model: state_off not monotone");
-    max_d = std::max(max_d, state_off[s + 1] - state_off[s]);
-  }
-  // the per-cell argmin is stored in 16 bits (d_Amin; DensityIdx is uint16_t in the reference too, Types.hpp:17)
-  if (max_d > 65535) SGMM_FAIL(c, "set_model: a state has more than 65535 densities (DensityIdx is 16 bit)");
-  const uint32_t npair = dim / 2;
-  std::vector<double2> mT((size_t)npair * D), vT((size_t)npair * D);
-  std::vector<double> mt(D, 0.0), vt(D, 0.0);
-  for (uint32_t j = 0; j < D; j++) {
-    const double* mu = mean + (size_t)j * dim;
-    const double* iv = inv_var + (size_t)j * dim;
-    for (uint32_t ip = 0; ip < npair; ip++) {
-      mT[(size_t)ip * D + j] = make_double2(mu[2 * ip], mu[2 * ip + 1]);
-      vT[(size_t)ip * D + j] = make_double2(iv[2 * ip], iv[2 * ip + 1]);
-    }
-    if (dim & 1) { mt[j] = mu[dim - 1]; vt[j] = iv[dim - 1]; }
-  }
-  if (upload(c, c->d_meanT, mT.data(), mT.size()) || upload(c, c->d_invT, vT.data(), vT.size()) ||
-      upload(c, c->d_mean_tail, mt.data(), mt.size()) || upload(c, c->d_inv_tail, vt.data(), vt.size()) ||
-      upload(c, c->d_norm, norm, (size_t)D) || upload(c, c->d_logw, log_weight, (size_t)D) ||
-      upload(c, c->d_state_off, state_off, (size_t)n_states + 1))
-    return 1;
-  // row-major twins for the refinement kernels: padded mean rows, distinct variance rows
-  {
-    const uint32_t dimP = (dim + 3) & ~3u;       // rows 32-byte aligned for 256-bit loads
-    std::vector<double> mR((size_t)D * dimP, 0.0), vU;
-    std::vector<uint32_t> var_of(D);
-    std::map<std::string, uint32_t> seen;
-    for (uint32_t j = 0; j < D; j++) {
-      memcpy(&mR[(size_t)j * dimP], mean + (size_t)j * dim, dim * sizeof(double));
-      const double* iv = inv_var + (size_t)j * dim;
-      // consecutive densities of a pooled state share the row: test the previous one before hashing
-      if (j > 0 && memcmp(iv, inv_var + (size_t)(j - 1) * dim, dim * sizeof(double)) == 0) { var_of[j] = var_of[j - 1]; continue; }
-      std::string key(reinterpret_cast<const char*>(iv), dim * sizeof(double));
-      auto it = seen.find(key);
-      if (it == seen.end()) {
-        it = seen.emplace(std::move(key), (uint32_t)(vU.size() / dimP)).first;
-        vU.resize(vU.size() + dimP, 0.0);
-        memcpy(&vU[(size_t)it->second * dimP], iv, dim * sizeof(double));
-      }
-      var_of[j] = it->second;
-    }
-    if (upload(c, c->d_meanR, mR.data(), mR.size()) || upload(c, c->d_invU, vU.data(), vU.size()) ||
-        upload(c, c->d_var_of, var_of.data(), var_of.size()))
-      return 1;
-    SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
-    c->dimP = dimP; c->n_var_rows = (uint32_t)(vU.size() / dimP);
-  }
-  // f32 tables for the FFMA scorer (k_score_ffma.cu): mean, h = inv_var / 2, c = norm - log w, and the
-  // per-state constants of the certified error bound.
-  const uint32_t dv4 = dim <= 28 ? 7 : dim <= 36 ? 9 : dim <= 48 ? 12 : dim <= 64 ? 16 : 0;
-  std::vector<float> mu32, h32, c32;
-  std::vector<float4> sg(n_states, make_float4(0.f, 0.f, 0.f, 0.f));
-  if (dv4) {
-    const size_t row = 4 * (size_t)dv4;
-    mu32.assign((size_t)D * row, 0.f); h32.assign((size_t)D * row, 0.f); c32.assign(D, 0.f);
-    for (uint32_t s = 0; s < n_states; s++) {
-      double cmin = INFINITY, cabs = 0.0, Mmax = 0.0;
-      for (uint32_t j = state_off[s]; j < state_off[s + 1]; j++) {
-        double M = 0.0;
-        for (uint32_t i = 0; i < dim; i++) {
-          const double mu = mean[(size_t)j * dim + i], h = 0.5 * inv_var[(size_t)j * dim + i];
-          mu32[j * row + i] = (float)mu; h32[j * row + i] = (float)h;
-          M += h * mu * mu;
-        }
-        const double cc = norm[j] - log_weight[j];
-        c32[j] = (float)cc;
-        cmin = std::min(cmin, cc); cabs = std::max(cabs, std::fabs(cc)); Mmax = std::max(Mmax, M);
-      }
-      // round the guard constants conservatively (cmin down, the others up)
-      sg[s] = make_float4(nextafterf((float)cmin, -INFINITY), nextafterf((float)cabs, INFINITY),
-                          nextafterf((float)Mmax, INFINITY), 0.f);
-    }
-    if (upload(c, c->d_mu32, reinterpret_cast<const float4*>(mu32.data()), (size_t)D * dv4) ||
-        upload(c, c->d_h32, reinterpret_cast<const float4*>(h32.data()), (size_t)D * dv4) ||
-        upload(c, c->d_c32, c32.data(), (size_t)D) || upload(c, c->d_sguard, sg.data(), sg.size()))
-      return 1;
-    // density-minor twin of the mean table for the two-stage rescan (lane = density: consecutive lanes read
-    // consecutive 16-byte units)
-    std::vector<float> mu32T((size_t)D * row);
-    for (uint32_t j = 0; j < D; j++)
-      for (uint32_t v = 0; v < dv4; v++) memcpy(&mu32T[((size_t)v * D + j) * 4], &mu32[j * row + 4 * v], 4 * sizeof(float));
-    if (upload(c, c->d_mu32T, reinterpret_cast<const float4*>(mu32T.data()), (size_t)D * dv4)) return 1;
-  }
-  // Tensor-core scorer operands (k_score_tc.cu).  Columns = densities, state-major, every state padded to a
-  // multiple of 16 columns with never-winning dummies.  B row of density j:
-  //   full  : [ h_0..h_{d-1} | g_0..g_{d-1} | c | 0.. ]   h = inv_var/2, g = -inv_var*mu, c = norm - logw + sum h mu^2
-  //   pooled: [ g_0..g_{d-1} | c | 0.. ]  when all densities of every state share one variance vector (the
-  //           x^2 block is then the same for all candidates of a state and drops out of the argmin).
-  {
-    bool pooled = true;
-    for (uint32_t s = 0; s < n_states && pooled; s++)
-      for (uint32_t j = state_off[s] + 1; j < state_off[s + 1] && pooled; j++)
-        pooled = memcmp(inv_var + (size_t)j * dim, inv_var + (size_t)state_off[s] * dim, dim * sizeof(double)) == 0;
-    c->pooled_states = pooled;
-    const uint32_t Kused = pooled ? dim + 1 : 2 * dim + 1;
-    const uint32_t KP = (Kused + 7) / 8 * 8;     // whole k-steps of 8 (32-byte swizzle atoms: no further padding)
-    c->tc_ok = KP / 8 <= 13;                     // A (hi, lo) = 16 * ksteps TMEM columns per 128 frames, <= 256
-    if (c->tc_ok) {
-      const uint32_t nsq = pooled ? 0 : dim;
-      std::vector<uint32_t> col_off(n_states + 1, 0);
-      for (uint32_t s = 0; s < n_states; s++)
-        col_off[s + 1] = col_off[s] + (state_off[s + 1] - state_off[s] + 15) / 16 * 16;
-      const uint32_t Dpad = col_off[n_states];
-      std::vector<float> Bhi((size_t)Dpad * KP, 0.f), Blo((size_t)Dpad * KP, 0.f);
-      std::vector<float4> sgt(n_states, make_float4(0.f, 0.f, 0.f, 0.f));
-      auto tf32 = [](float v) {   // round to nearest, ties away (cvt.rna.tf32.f32)
-        uint32_t u; memcpy(&u, &v, 4);
-        if ((u & 0x7f800000u) == 0x7f800000u) return v;
-        u += 0x1000u; u &= 0xffffe000u;
-        float r; memcpy(&r, &u, 4); return r;
-      };
-      auto put = [&](size_t row, uint32_t k, double v) {
-        const float hi = tf32((float)v);
-        Bhi[row * KP + k] = hi;
-        Blo[row * KP + k] = tf32((float)(v - (double)hi));
-      };
-      for (uint32_t s = 0; s < n_states; s++) {
-        double Gmax = 0.0, Hmax = 0.0, cabs = 0.0;
-        const uint32_t nreal = state_off[s + 1] - state_off[s];
-        for (uint32_t q = 0; q < col_off[s + 1] - col_off[s]; q++) {
-          const size_t row = col_off[s] + q;
-          if (q >= nreal) { put(row, nsq + dim, 1e30); continue; }
-          const uint32_t j = state_off[s] + q;
-          double cc = norm[j] - log_weight[j], G = 0.0, H = 0.0;
-          for (uint32_t i = 0; i < dim; i++) {
-            const double mu = mean[(size_t)j * dim + i], iv = inv_var[(size_t)j * dim + i];
-            const double h = 0.5 * iv, g = -iv * mu;
-            if (!pooled) { put(row, i, h); H += h * h; }
-            put(row, nsq + i, g); G += g * g;
-            cc += h * mu * mu;
-          }
-          put(row, nsq + dim, cc);
-          Gmax = std::max(Gmax, std::sqrt(G)); Hmax = std::max(Hmax, std::sqrt(H)); cabs = std::max(cabs, std::fabs(cc));
-        }
-        sgt[s] = make_float4((float)(Gmax * 1.0001), (float)(Hmax * 1.0001), (float)(cabs * 1.0001), 0.f);
-      }
-      // B as the GEMM kernel consumes it: per state, tiles of up to 128 densities; every tile is ONE contiguous
-      // block [hi, lo][k-step][N rows][8 floats] already in the 32-byte-swizzled shared-memory image the MMA
-      // descriptors name (Swizzle<1,4,3>: byte-address bit 7 XORed into bit 4), so a stage is filled by a single
-      // bulk copy at full L2 line rate instead of 32-byte tensor-map rows.
-      const uint32_t ks = KP / 8;
-      // tile width: 256 densities (N = 256 MMAs run at the full tensor rate, N = 128 ones do not — DESIGN.md §4) when
-      // some state is wider than 128 columns and three half-stage slots + one half's A parts fit shared memory
-      uint32_t widest = 0;
-      for (uint32_t s = 0; s < n_states; s++) widest = std::max(widest, col_off[s + 1] - col_off[s]);
-      const bool fits256 = 1024 + 2 * (size_t)ks * 4096 + 3 * (size_t)ks * 8192 + 256 + 5120 <= 227 * 1024;
-      const uint32_t TR = (c->tc_wide != 0 && fits256 && (widest > 128 || c->tc_wide == 1)) ? 256u : 128u;
-      c->tc_tile_rows = TR;
-      std::vector<uint32_t> tile_first(n_states + 1, 0);
-      std::vector<uint2> tile_info;           // {offset in 16-byte units, N}
-      std::vector<float> img;
-      for (uint32_t s = 0; s < n_states; s++) {
-        const uint32_t nc = col_off[s + 1] - col_off[s];
-        for (uint32_t n0 = 0; n0 < nc; n0 += TR) {
-          // every tile occupies a full ring stage: k-step blocks of 128 rows (rows >= N stay zero and are never
-          // multiplied: the MMA's N says so), so tile t starts at t * stage bytes and descriptors step by 4 KB
-          const uint32_t N = std::min(TR, nc - n0);
-          const size_t off = img.size();
-          tile_info.push_back(make_uint2((uint32_t)(off / 4), N));
-          img.resize(off + (size_t)2 * ks * TR * 8, 0.f);
-          for (int op = 0; op < 2; op++) {
-            const std::vector<float>& B = op ? Blo : Bhi;
-            float* base = img.data() + off + (size_t)op * ks * TR * 8;
-            for (uint32_t kk = 0; kk < ks; kk++)
-              for (uint32_t r = 0; r < N; r++)
-                for (uint32_t e = 0; e < 8; e++) {
-                  const uint32_t lin = kk * TR * 32 + r * 32 + e * 4;
-                  const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
-                  base[phys / 4] = B[(size_t)(col_off[s] + n0 + r) * KP + kk * 8 + e];
-                }
-          }
-        }
-        tile_first[s + 1] = (uint32_t)tile_info.size();
-      }
-      if (upload(c, c->d_Bimg, img.data(), img.size()) || upload(c, c->d_tile_first, tile_first.data(), tile_first.size()) ||
-          upload(c, c->d_tile_info, tile_info.data(), tile_info.size()) ||
-          upload(c, c->d_col_off, col_off.data(), col_off.size()) || upload(c, c->d_sguard_tc, sgt.data(), sgt.size()))
-        return 1;
-      SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
-      c->tc_KP = KP; c->tc_ksteps = (Kused + 7) / 8; c->tc_Dpad = Dpad; c->tc_full = pooled ? 0 : 1;
-      // error model of one 3xTF32 dot product against |a|.|b|: hi/lo split leaves 2^-22 per operand and the
-      // dropped lo.lo term another 2^-22; fp32 accumulation of 3 * 8 * ksteps terms, assumed to truncate
-      // (2^-23 each).  The guard doubles this (two candidates).
-      c->tc_eps = 3.f * 2.384185791015625e-07f + 3.f * 8.f * (float)c->tc_ksteps * 1.1920928955078125e-07f;
-      if (build_f16_image(c, pooled && TR == 256 && c->tc_f16 != 0, dim, n_states, state_off, mean, inv_var, norm, log_weight,
-                          col_off, tile_first))
-        return 1;
-    }
-    c->tc_A_valid = false;
-  }
-  if (!c->d_fallbacks.p) {
-    SGMM_CHECK(c, c->d_fallbacks.reserve(16));   // [0] rescanned cells, [1..15] k_tc_gemm cycle profile (tc_debug & 32)
-    SGMM_CHECK(c, cudaMemsetAsync(c->d_fallbacks.p, 0, 16 * sizeof(unsigned long long), c->stream));
-  }
-  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));  // the staging vectors die here
-  c->dv4 = dv4;
-  c->dim = dim; c->npair = npair; c->n_states = n_states; c->Dtot = D; c->max_dens = max_d;
-  c->h_state_off.assign(state_off, state_off + n_states + 1);
-  c->model_version++;
-  return 0;
 }
 
 int sgmm_set_features(sgmm_ctx* c, const float* x, uint64_t n_frames, uint32_t dim) {
@@ -768,6 +454,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
+  if (!strcmp(key, "host_tables")) { c->host_tables = value != 0; return 0; }   // read by sgmm_set_model
   if (!strcmp(key, "allreduce")) { c->allreduce = value != 0; return 0; }   // 0: sgmm_accumulate* return this rank's partial sums
   if (!strcmp(key, "tc_pack")) { c->tc_pack = value != 0; return 0; }   // takes effect at the next sgmm_set_corpus
   if (!strcmp(key, "upload_chunks")) {

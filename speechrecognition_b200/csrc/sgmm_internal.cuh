@@ -48,7 +48,61 @@ struct ViterbiClass {  // utterances that share one launch (same lanes-per-posit
   DevBuf<uint32_t> d_utts;
 };
 
-struct sgmm_ctx {
+// Everything sgmm_set_model / sgmm_mstep derive from the model parameters (K5).  Kept apart from the context so that a new
+// model is built into a spare set and swapped in only when every step succeeded.
+struct SgmmModel {
+  // exact f64 tables, dim-pair-major: tabT[ip * Dtot + j] = {mean.x, mean.y} etc.
+  uint32_t dim = 0, npair = 0, n_states = 0, Dtot = 0, max_dens = 0;
+  std::vector<uint32_t> h_state_off;
+  // the parameters as sgmm_set_model takes them (state-major, row-major f64): the device table builder's input
+  DevBuf<double> d_mean_src, d_inv_src;
+  DevBuf<double2> d_meanT, d_invT;
+  DevBuf<double> d_mean_tail, d_inv_tail, d_norm, d_logw;
+  // row-major copies for one-thread-per-cell refinement: meanR[D][dimP] (dimP = dim rounded up to 4, rows 32-byte
+  // aligned), the DISTINCT variance rows invU[V][dimP] and var_of[D] (pooled models: V = n_states or 1)
+  uint32_t dimP = 0, n_var_rows = 0;
+  DevBuf<double> d_meanR, d_invU;
+  DevBuf<uint32_t> d_var_of;
+  DevBuf<uint32_t> d_state_off;
+  // f32 tables of the FFMA / tensor scorers: [D][4*dv4] mean and h = 1/(2 var), c = norm - log w, per-state guard constants
+  uint32_t dv4 = 0;
+  DevBuf<float4> d_mu32, d_h32, d_sguard;
+  DevBuf<float4> d_mu32T;          // [dv4][D]: the mean table density-minor (two-stage rescan)
+  DevBuf<float> d_c32;
+  // tensor-core scorer (k_score_tc.cu): 3xTF32 operands, K-major, KP = padded K
+  uint32_t tc_KP = 0, tc_ksteps = 0, tc_Dpad = 0;
+  int tc_full = 0;                 // 1: K = x^2 | x | 1;  0: variances pooled per state, K = x | 1
+  uint32_t tc_tile_rows = 128;     // densities per B tile: 256 selects the N = 256 GEMM kernel (k_tc_gemm256)
+  bool tc_ok = false;
+  DevBuf<float> d_Bimg;
+  DevBuf<uint32_t> d_tile_first;    // [n_states + 1] first B tile of every state
+  DevBuf<uint2> d_tile_info;        // per tile {offset into d_Bimg in 16-byte units, densities N (multiple of 16)}
+  DevBuf<float4> d_sguard_tc;      // per state {max ||g||, max ||h||, max |c|, -}
+  DevBuf<uint32_t> d_col_off;
+  float tc_eps = 0.f;
+  // fp16 operand form of the wide GEMM (build_f16_image / k_tc_prep16)
+  bool tc_f16_ok = false;
+  uint32_t tc_ks16 = 0;
+  float tc_eps16 = 0.f;
+  DevBuf<__half> d_Bimg16;
+  DevBuf<uint2> d_tile_info16;
+  DevBuf<float4> d_sguard16;
+  bool pooled_states = false;     // every state's densities share one inverse-variance row
+  // topology-only facts kept for sgmm_mstep (the M-step changes parameters, not the layout)
+  std::vector<uint32_t> h_col_off, h_tile_first;
+  size_t img_elems = 0, img16_elems = 0;   // sizes of d_Bimg (floats) / d_Bimg16 (halves)
+  std::vector<uint32_t> h_var_of;          // variance row of every density (consecutive-duplicate folding)
+
+  void release_all() {
+    d_mean_src.release(); d_inv_src.release(); d_meanT.release(); d_invT.release(); d_mean_tail.release();
+    d_inv_tail.release(); d_norm.release(); d_logw.release(); d_meanR.release(); d_invU.release(); d_var_of.release();
+    d_state_off.release(); d_mu32.release(); d_h32.release(); d_sguard.release(); d_mu32T.release(); d_c32.release();
+    d_Bimg.release(); d_tile_first.release(); d_tile_info.release(); d_sguard_tc.release(); d_col_off.release();
+    d_Bimg16.release(); d_tile_info16.release(); d_sguard16.release();
+  }
+};
+
+struct sgmm_ctx : SgmmModel {
   int device = 0;
   cudaStream_t stream = nullptr;
   std::string err;
@@ -65,39 +119,24 @@ struct sgmm_ctx {
   cudaStream_t aux[kAux] = {nullptr};
   cudaEvent_t ev_fork = nullptr, ev_join[kAux] = {nullptr};
 
-  // ---- model (exact f64 tables, dim-pair-major: tabT[ip * Dtot + j] = {mean.x, mean.y} etc.)
-  uint32_t dim = 0, npair = 0, n_states = 0, Dtot = 0, max_dens = 0;
-  std::vector<uint32_t> h_state_off;
-  DevBuf<double2> d_meanT, d_invT;
-  DevBuf<double> d_mean_tail, d_inv_tail, d_norm, d_logw;
-  // row-major copies for one-thread-per-cell refinement: meanR[D][dimP] (dimP = dim rounded up to 4, rows 32-byte
-  // aligned), the DISTINCT variance rows invU[V][dimP] and var_of[D] (pooled models: V = n_states or 1)
-  uint32_t dimP = 0, n_var_rows = 0;
-  DevBuf<double> d_meanR, d_invU;
-  DevBuf<uint32_t> d_var_of;
-  DevBuf<uint32_t> d_state_off;
-  // f32 tables of the FFMA / tensor scorers: [D][4*dv4] mean and h = 1/(2 var), c = norm - log w, per-state guard constants
-  uint32_t dv4 = 0;
+  // ---- scorer state that is not part of the model tables
   int scorer = 0;   // 0 auto, 1 exact f64, 2 f32 FFMA + certified refinement
-  DevBuf<float4> d_mu32, d_h32, d_sguard;
-  DevBuf<float4> d_mu32T;          // [dv4][D]: the mean table density-minor (two-stage rescan)
-  DevBuf<float> d_c32;
   DevBuf<unsigned long long> d_fallbacks;
-  // tensor-core scorer (k_score_tc.cu): 3xTF32 operands, K-major, KP = padded K
-  uint32_t tc_KP = 0, tc_ksteps = 0, tc_Dpad = 0;
-  int tc_full = 0;                 // 1: K = x^2 | x | 1;  0: variances pooled per state, K = x | 1
-  uint32_t tc_tile_rows = 128;     // densities per B tile: 256 selects the N = 256 GEMM kernel (k_tc_gemm256)
   int tc_wide = -1;                // option "tc_wide" (read by sgmm_set_model): -1 auto, 0 never, 1 whenever it fits
-  bool tc_ok = false, tc_A_valid = false;
-  DevBuf<float> d_Bimg, d_Ahi, d_Alo;
-  DevBuf<uint32_t> d_tile_first;    // [n_states + 1] first B tile of every state
-  DevBuf<uint2> d_tile_info;        // per tile {offset into d_Bimg in 16-byte units, densities N (multiple of 16)}
+  bool tc_A_valid = false;
+  DevBuf<float> d_Ahi, d_Alo;
   DevBuf<float2> d_xnorm;
-  DevBuf<float4> d_sguard_tc;      // per state {max ||g||, max ||h||, max |c|, -}
-  DevBuf<uint32_t> d_col_off, d_ci1;
+  DevBuf<uint32_t> d_ci1;
   DevBuf<unsigned long long> d_rescan;   // [0] = count, [1..] = cell ids
   size_t rescan_cap = 0;
-  float tc_eps = 0.f;
+  int host_tables = 0;             // option "host_tables": 1 = build the K5 tables on the host (the checker of the device builder)
+  SgmmModel spare;                 // sgmm_set_model / sgmm_mstep build here, then swap: a failed call leaves the model untouched
+  DevBuf<int> d_model_flags;       // device builder: [0] non-finite fp16-image entries
+  // device-resident M-step (k_model.cu): variances [D][dim], weights [D], per-state totals, global-pooling scratch
+  DevBuf<double> d_mstep_tmp;
+  bool var_valid = false;          // d_mstep_tmp holds the current model's variances / weights (after sgmm_mstep)
+  bool stats_valid = false;        // d_acc holds the statistics of the last sgmm_accumulate* call ...
+  uint32_t stats_model_D = 0;      // ... for a model with this many densities
 
   // ---- features
   uint64_t n_frames = 0;
@@ -132,14 +171,8 @@ struct sgmm_ctx {
   // state-major refinement (k_tc_refine_sm): work items (block of utterances, state) and, per item, the
   // utterances of the block that visit the state
   int tc_refine = 0;               // option "tc_refine": 0 automatic, 1 frame-major kernel, 2 state-major kernel
-  // fp16 operand form of the wide GEMM (build_f16_image / k_tc_prep16)
-  int tc_f16 = -1;                 // option "tc_f16": -1 / 1 use it when available, 0 never
-  bool tc_f16_ok = false;
-  uint32_t tc_ks16 = 0;
-  float tc_eps16 = 0.f;
-  DevBuf<__half> d_Bimg16;
-  DevBuf<uint2> d_tile_info16;
-  DevBuf<float4> d_sguard16;
+  int tc_f16 = -1;                 // option "tc_f16": -1 / 1 use the fp16 operand form when available, 0 never
+  uint64_t tc_A_key = 0;           // shape / form the resident A rows were prepared for
   int tc_A_form = 0;               // which form the resident A rows (d_Ahi / d_Alo / d_xnorm) are in: 0 tf32, 1 fp16
   int tc_epi16 = 0;                // option "tc_epi16": sixteen epilogue warps per GEMM unit (k_tc_gemm256<.., E16>)
   int tc_rescan = 0;               // option "tc_rescan": 0 two-stage (f32 prefilter, f64 candidates), 1 full f64 scan
@@ -163,7 +196,6 @@ struct sgmm_ctx {
   bool max_approx = true;         // option "max_approx": score() = min_score (1) or sum_score (0), Mixtures.cpp:737-744
   bool E_max_approx = true;       // which of the two the resident emission matrix holds
   bool sum_prune = true;          // option "sum_prune": sum scores through the f32-pruned kernel (k_sum_pruned)
-  bool pooled_states = false;     // every state's densities share one inverse-variance row (set by sgmm_set_model)
   bool ali_has_cols = false;      // resident alignment came from sgmm_align (d_fcol valid)
   std::vector<ViterbiClass> vclasses;
   DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)

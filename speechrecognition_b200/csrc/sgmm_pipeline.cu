@@ -246,6 +246,7 @@ int sgmm_accumulate(sgmm_ctx* c, int first_pass, double* count, double* sum_x, d
   if (rescore_common(c, first_pass != 0)) return 1;
   if (sgmm_launch_accumulate(c)) return 1;
   if (sgmm_nccl_allreduce(c, c->d_acc.p, acc_len(c))) return 1;
+  c->stats_valid = true; c->stats_model_D = c->Dtot;
   const size_t D = c->Dtot, d = c->dim;
   {
     StageTimer st(c, SGMM_T_D2H);
@@ -274,6 +275,7 @@ int sgmm_accumulate_soft(sgmm_ctx* c, double* count, double* sum_x, double* sum_
     if (sgmm_launch_score_sum(c)) return 1;
   }
   if (sgmm_nccl_allreduce(c, c->d_acc.p, acc_len(c))) return 1;
+  c->stats_valid = true; c->stats_model_D = c->Dtot;
   const size_t D = c->Dtot, d = c->dim;
   {
     StageTimer st(c, SGMM_T_D2H);
@@ -282,6 +284,22 @@ int sgmm_accumulate_soft(sgmm_ctx* c, double* count, double* sum_x, double* sum_
     if (sum_xx) SGMM_CHECK(c, cudaMemcpyAsync(sum_xx, c->d_acc.p + D + D * d, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     if (score_sum) SGMM_CHECK(c, cudaMemcpyAsync(score_sum, c->d_acc.p + D + 2 * D * d, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   }
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// The statistics of the last sgmm_accumulate* call, still resident (and all-reduced): host copies on demand, so that a
+// caller running the M-step on the device (sgmm_mstep) pays the 2 D (d + 1) doubles only when it needs them (.mix
+// output, split / eliminate).
+int sgmm_get_statistics(sgmm_ctx* c, double* count, double* sum_x, double* sum_xx, double* score_sum) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  if (!c->stats_valid || c->stats_model_D != c->Dtot) SGMM_FAIL(c, "get_statistics: no statistics resident");
+  const size_t D = c->Dtot, d = c->dim;
+  if (count) SGMM_CHECK(c, cudaMemcpyAsync(count, c->d_acc.p, D * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (sum_x) SGMM_CHECK(c, cudaMemcpyAsync(sum_x, c->d_acc.p + D, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (sum_xx) SGMM_CHECK(c, cudaMemcpyAsync(sum_xx, c->d_acc.p + D + D * d, D * d * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (score_sum) SGMM_CHECK(c, cudaMemcpyAsync(score_sum, c->d_acc.p + D + 2 * D * d, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -325,6 +343,7 @@ int sgmm_align_accumulate(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment,
   if (rescore_common(c, false)) return 1;
   if (sgmm_launch_accumulate(c)) return 1;
   if (sgmm_nccl_allreduce(c, c->d_acc.p, acc_len(c))) return 1;
+  c->stats_valid = true; c->stats_model_D = c->Dtot;
   const size_t D = c->Dtot, d = c->dim;
   {
     StageTimer st(c, SGMM_T_D2H);

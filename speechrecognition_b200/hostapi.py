@@ -33,6 +33,12 @@ def _lib():
     return L
 
 
+def set_device_mstep(on):
+    """Default of the "device-mstep" key for models created afterwards: True = MixtureModel::finalize runs on the GPU
+    (sgmm_mstep) and the statistics stay there; False = statistics come home, finalize is host code."""
+    _lib().sthost_set_device_mstep(int(bool(on)))
+
+
 def _p(a, t):
     return None if a is None else a.ctypes.data_as(C.POINTER(t))
 
