@@ -36,6 +36,13 @@ def parse():
     ap.add_argument("--dim", type=int, default=33)
     ap.add_argument("--ref-utts", type=int, default=96, help="utterances of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="em", choices=["em", "recognize", "stress"],
+                    help="em (default): the EM iteration, with the recognition pass (configs[3]) and the 4501x64x48 stress "
+                         "(configs[4]) appended as other_workloads; recognize / stress: only that one, as other_workloads")
+    ap.add_argument("--no-other-workloads", action="store_true")
+    ap.add_argument("--stress-utts", type=int, default=2000, help="utterances of 500 frames per GPU (configs[4])")
+    ap.add_argument("--rec-check-utts", type=int, default=32)
+    ap.add_argument("--stress-check-utts", type=int, default=16)
     return ap.parse_args()
 
 
@@ -271,6 +278,181 @@ def allreduce_check(ctx, dist, torch, rank, world, F_local, stat_bufs):
     return out
 
 
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def _tc_roofline(ctx, flops, filter_ms, peaks):
+    """Tensor roofline of the filter GEMM that ran (fp16 hi/lo form: bf16 peak / 3; 3xTF32 form: bf16 peak / 2 / 3)."""
+    bf16 = float(peaks.get("bf16_tflops", 1590.0))
+    form = ctx.get_counter("tc_form")
+    peak = bf16 / 3.0 if form == 1 else bf16 / 6.0
+    ach = flops / (filter_ms / 1e3) / 1e12 if filter_ms > 0 else 0.0
+    return {"bound": "tensor", "kernel": "k_tc_gemm256 (kind::f16 hi/lo)" if form == 1 else "k_tc_gemm (kind::tf32, 3xTF32)",
+            "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "kernel_ms": filter_ms,
+            "peak_source": ("MEASURED_PEAKS.json bf16_tflops" if peaks else "fallback 1590") + (" / 3" if form == 1 else " / 2 / 3")}
+
+
+def workload_recognize(args, capi, local, rank, world, sync, steps, warmup):
+    """BASELINE configs[3]: recognition pass — dense acoustic scoring of every state + time-synchronous word-loop Viterbi
+    over the sietill digit HMMs with TDPs (Recognizer.cpp:103-232), batched over this rank's utterance shard."""
+    from concurrent.futures import ThreadPoolExecutor
+    lex = synth.Lexicon()
+    tables = synth.random_model(np.random.default_rng(synth.SEED), args.dim, lex.num_states, args.dens, "mixture")
+    corp = synth.make_corpus(np.random.default_rng(synth.SEED + 101 + rank), lex, tables, args.dim, args.utts)
+    F, U = int(corp["frame_off"][-1]), args.utts
+    ctx = capi.Context(local)
+    ctx.set_model_tables(args.dim, tables)
+    x_pin = capi.pinned_empty(corp["x"].shape, np.float32)
+    x_pin[...] = corp["x"]
+    ctx.set_features(x_pin)
+    ctx.set_tdp(3.0, 0.0, 30.0, lex.silence_state)
+    ctx.set_lexicon(lex.automata, lex.silence)
+    wp, thr = 10.0, 20.0
+    for _ in range(warmup):
+        hyp, _ = ctx.recognize(corp["frame_off"], wp, thr)
+    sync()
+    ctx.timer_start()
+    stages = []
+    for _ in range(steps):
+        ctx.recognize(corp["frame_off"], wp, thr)
+        stages.append(ctx.stage_ms())
+    ms = ctx.timer_stop()
+    sync()
+    ctx.timer_start()
+    for _ in range(steps):
+        ctx.set_features(x_pin)
+        ctx.recognize(corp["frame_off"], wp, thr)
+    ms_e2e = ctx.timer_stop()
+    stage = {k: float(np.mean([s[k] for s in stages])) for k in ("score", "score_filter", "score_refine", "viterbi", "d2h")}
+    out = {"frames": F, "utterances": U, "ms": ms / steps, "ms_e2e": ms_e2e / steps, "stage_ms": stage,
+           "h2d_bytes_per_step": int(x_pin.nbytes), "d2h_bytes_per_step": int(4 * F + 12 * U)}
+    D = int(tables["mix_offsets"][-1])
+    out["roofline"] = _tc_roofline(ctx, 2.0 * (args.dim + 1) * D * F, stage["score_filter"], _peaks())
+    if rank == 0:   # parity: the first utterances through the oracle port's Recognizer restatement
+        from oracle.binding import Oracle
+        O = Oracle(args.dim, lex.num_states, "mixture", True, (3.0, 0.0, 30.0), lex.silence_state)
+        O.load_tables(tables)
+        word_off = np.concatenate([[0], np.cumsum([len(a) for a in lex.automata])]).astype(np.uint32)
+        word_states = np.concatenate(lex.automata).astype(np.uint32)
+        n = min(args.rec_check_utts, U)
+        fo = corp["frame_off"]
+
+        def one(u):
+            return O.recognize(corp["x"][int(fo[u]):int(fo[u + 1])], word_off, word_states, lex.silence, wp, thr)[0]
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(os.cpu_count() or 1) as ex:
+            want = list(ex.map(one, range(n)))
+        dt = time.perf_counter() - t0
+        same = sum(int(np.array_equal(hyp[u], want[u])) for u in range(n))
+        exact = sum(int(np.array_equal(hyp[u], corp["words"][u])) for u in range(U))
+        out["parity_check"] = {"utts": n, "word_sequences_equal": same, "ok": same == n, "checker": "port",
+                               "sentences_equal_to_truth": exact}
+        out["cpu_baseline"] = {"value": float(fo[n]) / dt, "unit": "frames/s", "cores": os.cpu_count() or 1, "kind": "port",
+                               "sample": "first %d utterances, one thread each" % n}
+    ctx.close()
+    return out
+
+
+def workload_stress(args, capi, local, rank, world, sync, steps, warmup):
+    """BASELINE configs[4]: rwth-asr-shaped stress — 4501 tied states x 64 densities, 48-dim features, 1 M synthetic
+    frames (2000 utterances x 500 frames, chains of 150 positions) per rank: scoring + alignment (+ accumulate)."""
+    n_states, nd, dim, n_utts = 4501, 64, 48, args.stress_utts
+    rng = np.random.default_rng(synth.SEED)
+    tables = synth.random_model(rng, dim, n_states, nd, "mixture")
+    corp = synth.make_chain_corpus(np.random.default_rng(synth.SEED + 201 + rank), tables, dim, n_states, n_utts, T=500)
+    F = int(corp["frame_off"][-1])
+    ctx = capi.Context(local)
+    ctx.set_model_tables(dim, tables)
+    x_pin = capi.pinned_empty(corp["x"].shape, np.float32)
+    x_pin[...] = corp["x"]
+    ctx.set_features(x_pin)
+    ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"])
+    ctx.set_tdp(3.0, 0.0, 30.0, 0)
+    ali_pin = capi.pinned_empty((F,), capi.ALI_DTYPE)
+    cost_pin = capi.pinned_empty((n_utts,), np.float64)
+
+    def step():
+        ctx.align(want_alignment=False, want_costs=False)
+        st = ctx.stage_ms()
+        ctx.accumulate(first_pass=False, want=False)
+        st2 = ctx.stage_ms()
+        for k in ("rescore", "sort", "reduce", "allreduce"):
+            st[k] = st2[k]
+        return st
+    for _ in range(warmup):
+        step()
+    sync()
+    ctx.timer_start()
+    stages = [step() for _ in range(steps)]
+    ms = ctx.timer_stop()
+    sync()
+    ctx.timer_start()
+    for _ in range(steps):
+        ctx.set_features(x_pin)
+        ctx.align(out=ali_pin, out_costs=cost_pin)
+        ctx.accumulate(first_pass=False, want=False)
+    ms_e2e = ctx.timer_stop()
+    stage = {k: float(np.mean([s[k] for s in stages])) for k in ("score", "score_filter", "score_refine", "viterbi", "rescore", "sort", "reduce")}
+    dens = 0
+    for u in range(n_utts):
+        a = corp["automata"][int(corp["aut_off"][u]):int(corp["aut_off"][u + 1])]
+        dens += len(np.unique(a)) * nd * int(corp["frame_off"][u + 1] - corp["frame_off"][u])
+    out = {"frames": F, "utterances": n_utts, "states": n_states, "densities_per_state": nd, "dim": dim, "ms": ms / steps,
+           "ms_e2e": ms_e2e / steps, "stage_ms": stage, "scorer": {1: "f64", 2: "ffma", 3: "tcgen05"}[ctx.get_counter("scorer")],
+           "h2d_bytes_per_step": int(x_pin.nbytes), "d2h_bytes_per_step": int(ali_pin.nbytes + cost_pin.nbytes)}
+    out["roofline"] = _tc_roofline(ctx, 2.0 * (dim + 1) * dens, stage["score_filter"], _peaks())
+    if rank == 0:   # parity: the first utterances through the oracle port (u32 density ids)
+        from oracle.binding import Oracle
+        O = Oracle(dim, n_states, "mixture", True, (3.0, 0.0, 30.0), 0)
+        O.load_tables(tables)
+        n = min(args.stress_check_utts, n_utts)
+        fo, ao = corp["frame_off"][:n + 1], corp["aut_off"][:n + 1]
+        t0 = time.perf_counter()
+        st, costs = O.align_batch(corp["x"][:int(fo[-1])], fo, corp["automata"][:int(ao[-1])], ao, threads=os.cpu_count() or 1)
+        dt = time.perf_counter() - t0
+        out["parity_check"] = {"utts": n, "alignment_equal": bool(np.array_equal(ali_pin["state"][:int(fo[-1])].astype(np.uint32), st)),
+                               "costs_equal": bool(np.array_equal(np.asarray(cost_pin[:n]), costs)), "checker": "port"}
+        out["parity_check"]["ok"] = out["parity_check"]["alignment_equal"] and out["parity_check"]["costs_equal"]
+        out["cpu_baseline"] = {"value": float(fo[-1]) / dt, "unit": "frames/s", "cores": os.cpu_count() or 1, "kind": "port",
+                               "sample": "alignment of the first %d utterances, utterances in parallel" % n}
+    ctx.close()
+    return out
+
+
+def run_other_workloads(args, capi, torch, dist, local, rank, world, which):
+    """The configurations BASELINE.json names besides the EM iteration, measured on every rank's own shard (they shard by
+    utterance with no collective): per workload frames/s over all ranks (max of the ranks' device times), stage times,
+    the roofline fraction of the kernel that ran, a parity check against the oracle on a sample."""
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_max(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    res = {}
+    for name, fn in (("recognize", workload_recognize), ("stress_4501x64x48", workload_stress)):
+        if name.split("_")[0] not in which:
+            continue
+        r = fn(args, capi, local, rank, world, sync, max(2, min(args.steps, 3)), 2)
+        ms, ms_e2e = reduce_max(r["ms"]), reduce_max(r["ms_e2e"])
+        r["n_gpus"] = world
+        r["value"] = r["frames"] * world / (ms / 1e3)
+        r["e2e_value"] = r["frames"] * world / (ms_e2e / 1e3)
+        r["unit"] = "frames/s"
+        r["ms"], r["ms_e2e"] = ms, ms_e2e
+        res[name] = r
+    return res
+
+
 def config_dict(args, frames_per_gpu, extra=None):
     c = {"workload": "BASELINE configs[1] shape (106 states x %d densities, d=%d, per-state pooled diag cov) "
                      "run as configs[2]'s full EM iteration: score + Viterbi-align + accumulate + M-step (finalize and the model "
@@ -447,7 +629,25 @@ def run_ours(args):
     h2d = x_pin.nbytes
     d2h = ali_pin.nbytes + U * 8 + sum(a.nbytes for a in out[:3]) + 8
 
+    # what the box can move: every rank copies its pinned feature block H2D at the same time, nothing else running
+    # (plain cudaMemcpyAsync through torch) -> aggregate GB/s, the ceiling of the streaming end-to-end number
+    xt = torch.from_numpy(x_pin.reshape(-1))
+    dev_buf = torch.empty(xt.numel(), dtype=torch.float32, device="cuda")
+    dev_buf.copy_(xt)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(5):
+        dev_buf.copy_(xt, non_blocking=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    h2d_ms = max_over_ranks(ev0.elapsed_time(ev1) / 5)
+    del dev_buf
+    barrier()
     ar_check = allreduce_check(ctx, dist, torch, rank, world, F, stat_pin) if world > 1 else None
+    others = {}
+    if not args.no_other_workloads:
+        others = run_other_workloads(args, capi, torch, dist, local, rank, world, ("recognize", "stress"))
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -542,7 +742,11 @@ def run_ours(args):
                                                                "cpu_binding": ("rank bound to the %d CPUs local to its GPU" % near_cpus) if near_cpus else "none"}),
         "clocks": clocks,
         "e2e": {"value": frames_total * args.steps / (ms_e2e / 1e3), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps},
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
+                "h2d_ceiling_gbs": h2d * world / (h2d_ms / 1e3) / 1e9, "h2d_copy_alone_ms": h2d_ms,
+                "note": "every step re-uploads the features (a corpus larger than HBM streams like this; training proper "
+                        "keeps them resident = `value`); h2d_ceiling_gbs = all ranks copying their block at once, nothing "
+                        "else running; h2d_copy_alone_ms of the step is pure transfer time the GEMM overlaps only partly"},
         "gpu_launches": int(launches),
         "stage_ms_per_step": stage,
         "roofline": roof,
@@ -562,12 +766,54 @@ def run_ours(args):
                                           % (args.ref_utts, r["frames"], cores, r["align_s"], r["accumulate_s"])}
     if ar_check is not None:
         line["allreduce_check"] = ar_check
+    if others:
+        line["other_workloads"] = others
     emit(line)
     if world > 1:
         dist.destroy_process_group()
     bad = [k for k in ("parity_check", "allreduce_check") if k in line and not line[k]["ok"]]
+    bad += ["other_workloads." + k for k, v in others.items() if "parity_check" in v and not v["parity_check"]["ok"]]
     if bad:
-        sys.stderr.write("bench.py: %s FAILED: %s\n" % (", ".join(bad), json.dumps({k: line[k] for k in bad})))
+        sys.stderr.write("bench.py: %s FAILED\n" % ", ".join(bad))
+        sys.exit(3)
+
+
+def run_single_workload(args):
+    """--workload recognize | stress: that configuration alone, as the main line (same keys as the EM line)."""
+    import torch
+    import torch.distributed as dist
+    from speechrecognition_b200 import capi
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    sampler = ClockSampler(local)
+    sampler.start()
+    res = run_other_workloads(args, capi, torch, dist, local, rank, world, (args.workload,))
+    sampler.stop_flag = True
+    if world > 1:
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    name, r = next(iter(res.items()))
+    line = {"metric": "frames/sec scored+aligned (GMM+Viterbi)" if name.startswith("stress") else
+            "frames/sec scored+recognised (GMM + word-loop Viterbi)", "value": r["value"], "unit": "frames/s", "n_gpus": world,
+            "steps": max(2, min(args.steps, 3)), "warmup": 2, "ms_per_step": r["ms"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "BASELINE configs[%d]: %s" % (4 if name.startswith("stress") else 3, name),
+                       "frames_per_gpu": r["frames"], "utterances_per_gpu": r["utterances"], "seed": synth.SEED,
+                       "l2": "inputs exceed L2"},
+            "clocks": sampler.summary(),
+            "e2e": {"value": r["e2e_value"], "unit": "frames/s", "h2d_bytes_per_step": r["h2d_bytes_per_step"],
+                    "d2h_bytes_per_step": r["d2h_bytes_per_step"], "ms_per_step": r["ms_e2e"]},
+            "gpu_launches": None, "stage_ms_per_step": r["stage_ms"], "roofline": dict(r["roofline"], traffic=None)}
+    for k in ("parity_check", "cpu_baseline"):
+        if k in r:
+            line[k] = r[k]
+    emit(line)
+    if "parity_check" in r and not r["parity_check"]["ok"]:
         sys.exit(3)
 
 
@@ -596,5 +842,7 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload in ("recognize", "stress"):
+        run_single_workload(a)
     else:
         run_ours(a)

@@ -282,6 +282,13 @@ void MixtureModel::ensure_host() const {
         self.mean_weights_log_[md.mean_idx] = logw[j];
         j++;
       }
+    // The reference recomputes the variance slot of a mixture that eliminate() emptied from a 0/0 pooled mean
+    // (Mixtures.cpp:425, see finalize_host): no density uses it, the device never builds it; the host copy follows suit.
+    if (var_model == MIXTURE_POOLING) {
+      const std::vector<double> nan_mean(d, std::nan(""));
+      for (size_t m = 0; m < mixtures_.size(); m++)
+        if (mixtures_[m].empty()) self.calculate_variance(stale_first_[m].var_idx, nan_mean.data());
+    }
     params_on_device_ = false;
   }
 }

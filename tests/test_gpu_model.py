@@ -175,8 +175,9 @@ def test_set_model_is_transactional():
     z = np.zeros((70000, dim))
     with pytest.raises(capi.SgmmError):
         ctx.set_model(dim, huge, z, z + 1.0, np.zeros(70000), np.zeros(70000))
+    D = int(tables["mix_offsets"][-1])
     with pytest.raises(capi.SgmmError):
-        ctx.set_model(1, *args[1:])                                               # dim out of range
+        ctx.set_model(1, tables["mix_offsets"], np.zeros((D, 1)), np.ones((D, 1)), np.zeros(D), np.zeros(D))   # dim out of range
     ctx.dim, ctx.n_states, ctx.D = dim, lex.num_states, int(tables["mix_offsets"][-1])
     a1, c1 = ctx.align()
     s1, m1 = ctx.score_all(0, 100)
