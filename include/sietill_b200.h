@@ -187,6 +187,21 @@ int sgmm_am_score_sum(sgmm_ctx* ctx, double* score_sum);
  * density[f] = k chosen for frame f, score[f] = its min score.  Either may be NULL. */
 int sgmm_last_frame_results(sgmm_ctx* ctx, uint32_t* density, double* score);
 
+/* Allocation-free variant of the deterministic score sum (the numerator of Trainer::calc_am_score as sgmm_am_score_sum /
+ * sgmm_accumulate compute it).  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid allocation).  Unlike every
+ * other entry point, d_values[n] (f64) and d_sum[1] are DEVICE pointers on the context's GPU, and the call only ENQUEUES
+ * its two kernels on `stream` (a cudaStream_t; NULL = the context's own stream) without synchronising: *d_sum is valid
+ * once the stream has passed that point.  It calls no cudaMalloc / cudaFree or any allocating routine: the partial sums
+ * live in a file-scope 128 KB __device__ array (one per GPU that loads the library, held until the process exits), which
+ * limits a call to n <= 67 108 864 values (16 384 partials of 4 096 values) — larger n is rejected with an error.  Every
+ * call shares that array: calls that overlap on the GPU (several streams / threads / concurrently replayed graphs) race
+ * and must be serialised by the caller; nothing in it has to be cleared between calls (a call overwrites exactly the
+ * partials it reads).  The first call on a device looks the array's address up (cudaGetSymbolAddress): make it outside
+ * a graph capture (n = 0 is a valid warm-up).  The summation tree is fixed by n alone (bit-reproducible run to run); it
+ * differs from sgmm_am_score_sum's tree, so the two agree to ~1e-15 relative, not bit for bit. */
+int sgmm_score_sum_static(sgmm_ctx* ctx, const double* d_values, uint64_t n, double* d_sum, void* stream);
+
 /* ---- options / counters -------------------------------------------------------------------- */
 /* "max_approx" (default 1): what FeatureScorer::score means (MixtureModel's constructor argument, Mixtures.cpp:737-744):
  *   1 = min_score (maximum approximation), 0 = sum_score = -log sum_k exp(-density_score_k) (:719-728).  With 0,

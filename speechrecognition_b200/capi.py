@@ -23,7 +23,7 @@ SYMBOLS = [
     "sgmm_accumulate_soft", "sgmm_process_features", "sgmm_align_accumulate",
     "sgmm_am_score_sum", "sgmm_last_frame_results", "sgmm_comm_unique_id", "sgmm_comm_init", "sgmm_stage_ms",
     "sgmm_launch_count", "sgmm_timer_start", "sgmm_timer_stop", "sgmm_host_alloc", "sgmm_host_free",
-    "sgmm_set_option", "sgmm_get_counter", "sgmm_mstep", "sgmm_get_model", "sgmm_get_statistics", "sgmm_debug_table",
+    "sgmm_set_option", "sgmm_get_counter", "sgmm_mstep", "sgmm_get_model", "sgmm_get_statistics", "sgmm_debug_table", "sgmm_score_sum_static",
 ]
 
 _lib = None
@@ -255,6 +255,11 @@ class Context:
         self._ck(self.L.sgmm_accumulate_soft(self.h, _ptr(cnt, C.c_double), _ptr(sx, C.c_double),
                                              _ptr(sxx, C.c_double), _ptr(ssum, C.c_double)))
         return cnt, sx, sxx, float(ssum[0])
+
+    def score_sum_static(self, d_values_ptr, n, d_sum_ptr, stream_ptr=0):
+        """sgmm_score_sum_static: DEVICE pointers (ints), enqueue only — the caller synchronises `stream`."""
+        self._ck(self.L.sgmm_score_sum_static(self.h, C.c_void_p(d_values_ptr), C.c_uint64(n), C.c_void_p(d_sum_ptr),
+                                              C.c_void_p(stream_ptr)))
 
     def am_score_sum(self):
         ssum = np.zeros(1, np.float64)
