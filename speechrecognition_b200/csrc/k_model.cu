@@ -68,6 +68,7 @@ int model_layout(sgmm_ctx* c, SgmmModel& m, uint32_t dim, uint32_t n_states, con
   const uint32_t KP = (Kused + 7) / 8 * 8;     // whole k-steps of 8 (32-byte swizzle atoms: no further padding)
   m.tc_ok = KP / 8 <= 13;                      // A (hi, lo) = 16 * ksteps TMEM columns per 128 frames, <= 256
   m.tc_f16_ok = false;
+  m.tc_rem16 = 0;
   m.h_col_off.assign(n_states + 1, 0);
   for (uint32_t s = 0; s < n_states; s++)
     m.h_col_off[s + 1] = m.h_col_off[s] + (state_off[s + 1] - state_off[s] + 15) / 16 * 16;
@@ -117,6 +118,8 @@ int model_layout(sgmm_ctx* c, SgmmModel& m, uint32_t dim, uint32_t n_states, con
     SGMM_CHECK(c, m.d_Bimg16.reserve(img16)); SGMM_CHECK(c, m.d_sguard16.reserve(n_states));
     if (upload(c, m.d_tile_info16, tile_info16.data(), tile_info16.size())) return 1;
     m.tc_ks16 = ks16;
+    const uint32_t rem = K16 % 16;
+    m.tc_rem16 = (c->tc_rem != 0 && K16 >= 16 && rem > 0 && 3 * rem <= 16) ? rem : 0;
     // error model of one split dot product against |a|.|b| (cf. tc_eps): 2^-22 per operand split, 2^-22 for the
     // dropped lo.lo term; fp32 accumulation of 3 * 16 * ksteps products, assumed to truncate (2^-23 each)
     m.tc_eps16 = 3.f * 2.384185791015625e-07f + 3.f * 16.f * (float)ks16 * 1.1920928955078125e-07f;
@@ -140,7 +143,7 @@ struct BuildParams {
   // tensor operands
   const uint32_t* col_off; const uint32_t* tile_first; const uint2* tile_info; const uint2* tile_info16;
   float* Bimg; __half* Bimg16; float4* sguard_tc; float4* sguard16;
-  uint32_t KP, ks, TR, nsq, ks16;
+  uint32_t KP, ks, TR, nsq, ks16, rem16;
   double inv2eps16;
   int* flags;
 };
@@ -324,10 +327,15 @@ __global__ void __launch_bounds__(128) k_model_f16(BuildParams p) {
       const __half hi = __float2half_rn(__double2float_rn(v));
       const double rem = __dsub_rn(v, (double)__half2float(hi));
       const __half lo = __float2half_rn(__double2float_rn(rem));
-      const uint32_t lin = (k / 16) * p.TR * 32 + r * 32 + (k % 16) * 2;
-      const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
-      base[phys / 2] = hi;
-      base[(size_t)p.ks16 * p.TR * 16 + phys / 2] = lo;
+      auto put = [&](uint32_t img, uint32_t kpos, __half val) {   // img 0: the hi slot's image, 1: the lo slot's
+        const uint32_t lin = (kpos / 16) * p.TR * 32 + r * 32 + (kpos % 16) * 2;
+        const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
+        base[(size_t)img * p.ks16 * p.TR * 16 + phys / 2] = val;
+      };
+      const uint32_t kfull = K - p.rem16;                         // terms in whole k-steps (all of them when not packed)
+      if (p.rem16 && k >= kfull) {   // packed remainder: [hi | hi | lo] in the hi slot's last k-step (sgmm_internal.cuh)
+        put(0, k, hi); put(0, k + p.rem16, hi); put(0, k + 2 * p.rem16, lo);
+      } else { put(0, k, hi); put(1, k, lo); }
       double fl = 0.0;                              // subnormal parts: see k_tc_prep16
       if (rem != 0.0 && fabs(rem) < 6.103515625e-05) fl = __dadd_rn(fl, hmax(fabs(rem), 2.98023223876953125e-08));
       if (v != 0.0 && fabs(v) < 6.103515625e-05) fl = __dadd_rn(fl, fabs(v));
@@ -361,7 +369,7 @@ int model_build_device(sgmm_ctx* c, SgmmModel& m) {
   p.mu32T = reinterpret_cast<float*>(m.d_mu32T.p); p.c32 = m.d_c32.p; p.sguard = m.d_sguard.p;
   p.col_off = m.d_col_off.p; p.tile_first = m.d_tile_first.p; p.tile_info = m.d_tile_info.p; p.tile_info16 = m.d_tile_info16.p;
   p.Bimg = m.d_Bimg.p; p.Bimg16 = m.d_Bimg16.p; p.sguard_tc = m.d_sguard_tc.p; p.sguard16 = m.d_sguard16.p;
-  p.KP = m.tc_KP; p.ks = m.tc_KP / 8; p.TR = m.tc_tile_rows; p.nsq = m.tc_full ? m.dim : 0; p.ks16 = m.tc_ks16;
+  p.KP = m.tc_KP; p.ks = m.tc_KP / 8; p.TR = m.tc_tile_rows; p.nsq = m.tc_full ? m.dim : 0; p.ks16 = m.tc_ks16; p.rem16 = m.tc_rem16;
   p.inv2eps16 = m.tc_eps16 > 0.f ? 1.0 / (2.0 * (double)m.tc_eps16) : 0.0;
   SGMM_CHECK(c, c->d_model_flags.reserve(4));
   SGMM_CHECK(c, cudaMemsetAsync(c->d_model_flags.p, 0, 4 * sizeof(int), c->stream));
@@ -543,10 +551,14 @@ int model_build_host(sgmm_ctx* c, SgmmModel& m, const double* mean, const double
           const __half hi = __float2half_rn((float)row[k]);
           const double rem = row[k] - (double)__half2float(hi);
           const __half lo = __float2half_rn((float)rem);
-          const uint32_t lin = (k / 16) * TR * 32 + r * 32 + (k % 16) * 2;
-          const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
-          base[phys / 2] = hi;
-          base[(size_t)ks16 * TR * 16 + phys / 2] = lo;
+          auto put = [&](uint32_t img, uint32_t kpos, __half val) {
+            const uint32_t lin = (kpos / 16) * TR * 32 + r * 32 + (kpos % 16) * 2;
+            const uint32_t phys = lin ^ (((lin >> 7) & 1u) << 4);
+            base[(size_t)img * ks16 * TR * 16 + phys / 2] = val;
+          };
+          const uint32_t rem16 = m.tc_rem16, kfull = K - rem16;
+          if (rem16 && k >= kfull) { put(0, k, hi); put(0, k + rem16, hi); put(0, k + 2 * rem16, lo); }
+          else { put(0, k, hi); put(1, k, lo); }
           double fl = 0.0;                                  // subnormal parts: see k_tc_prep16
           if (rem != 0.0 && std::fabs(rem) < 6.103515625e-05) fl += std::max(std::fabs(rem), 2.98023223876953125e-08);
           if (row[k] != 0.0 && std::fabs(row[k]) < 6.103515625e-05) fl += std::fabs(row[k]);

@@ -452,6 +452,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "sum_prune")) { c->sum_prune = value != 0; return 0; }
   if (!strcmp(key, "tc_epi16")) { c->tc_epi16 = (int)value; return 0; }
   if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
+  if (!strcmp(key, "tc_rem")) { c->tc_rem = (int)value; return 0; }   // read by sgmm_set_model
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
   if (!strcmp(key, "host_tables")) { c->host_tables = value != 0; return 0; }   // read by sgmm_set_model
@@ -492,6 +493,7 @@ int sgmm_get_counter(sgmm_ctx* c, const char* key, int64_t* value) {
     *value = (int64_t)v;
     return 0;
   }
+  if (!strcmp(key, "tc_rem")) { *value = c->tc_f16_ok ? c->tc_rem16 : 0; return 0; }   // packed K remainder in use (terms)
   if (!strcmp(key, "packs")) { *value = (int64_t)c->n_packs; return 0; }   // packed GEMM tasks of the resident corpus
   // operand form the wide GEMM runs with (k_score_tc.cu): 0 tf32 hi/lo (3xTF32), 1 fp16 hi/lo (kind::f16);
   // k-steps per tile of that form

@@ -83,6 +83,10 @@ struct SgmmModel {
   // fp16 operand form of the wide GEMM (build_f16_image / k_tc_prep16)
   bool tc_f16_ok = false;
   uint32_t tc_ks16 = 0;
+  // packed remainder (option "tc_rem"): K = 16 q + r with 0 < 3 r <= 16 — the r trailing terms of the three products
+  // hi.hi, lo.hi, hi.lo share ONE k-step ([Ahi r | Alo r | Ahi r] . [Bhi r | Bhi r | Blo r]) instead of three mostly
+  // empty ones: 3 q + 1 MMAs per unit instead of 3 (q + 1) (7 instead of 9 at d = 33).  0 = not packed.
+  uint32_t tc_rem16 = 0;
   float tc_eps16 = 0.f;
   DevBuf<__half> d_Bimg16;
   DevBuf<uint2> d_tile_info16;
@@ -171,6 +175,7 @@ struct sgmm_ctx : SgmmModel {
   // state-major refinement (k_tc_refine_sm): work items (block of utterances, state) and, per item, the
   // utterances of the block that visit the state
   int tc_refine = 0;               // option "tc_refine": 0 automatic, 1 frame-major kernel, 2 state-major kernel
+  int tc_rem = 1;                  // option "tc_rem" (read by sgmm_set_model): pack the K remainder of the fp16 form
   int tc_f16 = -1;                 // option "tc_f16": -1 / 1 use the fp16 operand form when available, 0 never
   uint64_t tc_A_key = 0;           // shape / form the resident A rows were prepared for
   int tc_A_form = 0;               // which form the resident A rows (d_Ahi / d_Alo / d_xnorm) are in: 0 tf32, 1 fp16
