@@ -139,82 +139,92 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
   }
   const double pf = p.tdp_forward;
   const bool prune = DEST && p.beam < INF;
+  // Lane 0 has no left neighbour.  Instead of masking the shuffled costs every frame, the penalties of the transitions
+  // that would enter from it are +inf: cost + inf = +inf never wins a strict comparison (costs are never -inf), which
+  // is what the reference's missing predecessor amounts to.
+  const double pf0 = lane == 0 ? INFd : pf;          // forward into this lane's first position
+  if (lane == 0) { pk[0] = INFd; if (C > 1) pk[C > 1 ? 1 : 0] = INFd; }
 
+  // One frame of the recursion.  The backpointer is kept as the two raw comparison flags (bit 0 = first comparison,
+  // bit 1 = second), set by predicated ORs with the frame's mask; the backtrace decodes them.
+  auto frame = [&](const double* __restrict__ row, const uint32_t m1) {
+    double e[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) e[c] = row[col[c]];
+    // the two costs that cross the lane boundary (positions s-1 and s-2 of this lane's first position)
+    const double Q1 = __shfl_up_sync(0xffffffffu, q[C - 1], 1);
+    const double Q2 = __shfl_up_sync(0xffffffffu, q[C - 2], 1);
+    double nq[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+      const double p1 = c > 0 ? q[c > 0 ? c - 1 : 0] : Q1;
+      const double p2 = c > 1 ? q[c > 1 ? c - 2 : 0] : (c == 1 ? Q1 : Q2);
+      const double pfc = c == 0 ? pf0 : pf;
+      bool f1, f2;
+      if (!DEST) {
+        // current = local + min{loop, forward, skip}, ties loop > forward > skip (Alignment.cpp:96-113)
+        const double lv = __dadd_rn(q[c], pl[c]);
+        const double fv = __dadd_rn(p1, pfc);
+        const double kv = __dadd_rn(p2, pk[c]);
+        f1 = fv < lv;
+        const double mn = f1 ? fv : lv;
+        f2 = kv < mn;
+        nq[c] = __dadd_rn(e[c], f2 ? kv : mn);      // jump = f2 ? 2 : f1
+      } else {
+        // (prev + tdp) + emission; candidates arrive skip, forward, loop and replace on strictly smaller cost
+        // (Alignment.cpp:190-204).  Dead predecessors are +inf and never win a strict comparison.
+        const double ck = __dadd_rn(__dadd_rn(p2, pk[c]), e[c]);
+        const double cf = __dadd_rn(__dadd_rn(p1, pfc), e[c]);
+        const double cl = __dadd_rn(__dadd_rn(q[c], pl[c]), e[c]);
+        f1 = cf < ck;
+        const double mn = f1 ? cf : ck;
+        f2 = cl < mn;
+        nq[c] = f2 ? cl : mn;                       // jump = f2 ? 0 : (f1 ? 1 : 2)
+      }
+      if (f1) w[c] |= m1;
+      if (f2) w[c] |= m1 << 1;
+    }
+    if (prune) {
+      // best over the automaton's own positions only (lanes past S hold junk from column 0)
+      double best = INFd;
+#pragma unroll
+      for (int c = 0; c < C; c++)
+        if ((validmask >> c) & 1) best = fmin(best, nq[c]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
+      const double upper = __dadd_rn(best, p.beam);
+#pragma unroll
+      for (int c = 0; c < C; c++) nq[c] = nq[c] > upper ? INFd : nq[c];
+    }
+#pragma unroll
+    for (int c = 0; c < C; c++) q[c] = nq[c];
+  };
+
+  // SGMM_TILE_T = 16 frames per emission tile = one 32-bit backpointer word per position and tile
+  static_assert(SGMM_TILE_T == 16, "one backpointer word per tile");
   for (uint32_t ti = 0; ti < n_tiles; ti++) {
     const uint32_t slot = ti % SGMM_STAGES;
     mbar_wait(&bars[slot], (ti / SGMM_STAGES) & 1);
     const double* tile = tiles + slot * tile_elems;
-    const uint32_t t0 = ti * SGMM_TILE_T;
-    const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - t0);
-#pragma unroll 4
-    for (uint32_t tt = 0; tt < rows; tt++) {
-      const uint32_t t = t0 + tt;
-      const double* row = tile + tt * ncol;
-      // positions past the automaton read column 0: their costs never reach a valid position (jumps only go forward)
-      double e[C];
-#pragma unroll
-      for (int c = 0; c < C; c++) e[c] = row[col[c]];
-      if (t == 0) {
+    const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - ti * SGMM_TILE_T);
+    if (ti > 0 && rows == SGMM_TILE_T) {
+      // full tile: unrolled, the frame masks are immediates
+#pragma unroll(C <= 4 ? 16 : (C <= 8 ? 4 : 2))
+      for (int tt = 0; tt < SGMM_TILE_T; tt++) frame(tile + (uint32_t)tt * ncol, 1u << (2 * tt));
+    } else {
+      uint32_t tt = 0;
+      if (ti == 0) {
         // Q(0,0) = emission(0, ref[0]); every other position starts at +inf (Alignment.cpp:62-63,77)
+        const double e0 = tile[col[0]];
 #pragma unroll
-        for (int c = 0; c < C; c++) q[c] = (lane == 0 && c == 0) ? e[0] : INFd;
-        continue;
+        for (int c = 0; c < C; c++) q[c] = (lane == 0 && c == 0) ? e0 : INFd;
+        tt = 1;
       }
-      // the two costs that cross the lane boundary (positions s-1 and s-2 of this lane's first position)
-      double Q1 = __shfl_up_sync(0xffffffffu, q[C - 1], 1);
-      double Q2 = __shfl_up_sync(0xffffffffu, q[C - 2], 1);
-      if (lane == 0) { Q1 = INFd; Q2 = INFd; }
-      double nq[C];
-      const uint32_t sh = 2 * (t & 15);
-#pragma unroll
-      for (int c = 0; c < C; c++) {
-        const double p1 = c > 0 ? q[c > 0 ? c - 1 : 0] : Q1;
-        const double p2 = c > 1 ? q[c > 1 ? c - 2 : 0] : (c == 1 ? Q1 : Q2);
-        uint32_t j;
-        if (!DEST) {
-          // current = local + min{loop, forward, skip}, ties loop > forward > skip (Alignment.cpp:96-113)
-          const double lv = __dadd_rn(q[c], pl[c]);
-          const double fv = __dadd_rn(p1, pf);
-          const double kv = __dadd_rn(p2, pk[c]);
-          const bool f1 = fv < lv;
-          const double m1 = f1 ? fv : lv;
-          const bool f2 = kv < m1;
-          const double best = f2 ? kv : m1;
-          j = f2 ? 2u : (f1 ? 1u : 0u);
-          nq[c] = __dadd_rn(e[c], best);
-        } else {
-          // (prev + tdp) + emission; candidates arrive skip, forward, loop and replace on strictly smaller cost
-          // (Alignment.cpp:190-204).  Dead predecessors are +inf and never win a strict comparison.
-          const double ck = __dadd_rn(__dadd_rn(p2, pk[c]), e[c]);
-          const double cf = __dadd_rn(__dadd_rn(p1, pf), e[c]);
-          const double cl = __dadd_rn(__dadd_rn(q[c], pl[c]), e[c]);
-          const bool f1 = cf < ck;
-          const double m1 = f1 ? cf : ck;
-          const bool f2 = cl < m1;
-          nq[c] = f2 ? cl : m1;
-          j = f2 ? 0u : (f1 ? 1u : 2u);
-        }
-        w[c] |= j << sh;
-      }
-      if (prune) {
-        // best over the automaton's own positions only (lanes past S hold junk from column 0)
-        double best = INFd;
-#pragma unroll
-        for (int c = 0; c < C; c++)
-          if ((validmask >> c) & 1) best = fmin(best, nq[c]);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
-        const double upper = __dadd_rn(best, p.beam);
-#pragma unroll
-        for (int c = 0; c < C; c++) nq[c] = nq[c] > upper ? INFd : nq[c];
-      }
-#pragma unroll
-      for (int c = 0; c < C; c++) q[c] = nq[c];
-      if ((t & 15) == 15 || t == T - 1) {
-#pragma unroll
-        for (int c = 0; c < C; c++) { bpw[(size_t)(t >> 4) * 32 * C + c * 32 + lane] = w[c]; w[c] = 0; }
-      }
+#pragma unroll 1
+      for (; tt < rows; tt++) frame(tile + tt * ncol, 1u << (2 * tt));
     }
+#pragma unroll
+    for (int c = 0; c < C; c++) { bpw[(size_t)ti * 32 * C + c * 32 + lane] = w[c]; w[c] = 0; }
     __syncwarp();
     const uint32_t nxt = ti + SGMM_STAGES;
     if (lane == 0 && nxt < n_tiles) {
@@ -251,7 +261,8 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
       out[t] = make_uint2(1u | ((uint32_t)sref[s] << 16), one);
       p.fcol[f0 + t] = scol[s];
       const uint32_t word = bpw[(size_t)(t >> 4) * 32 * C + (s % C) * 32 + s / C];
-      const uint32_t j = (word >> (2 * (t & 15))) & 3u;
+      const uint32_t v = (word >> (2 * (t & 15))) & 3u;           // raw comparison flags of the forward pass
+      const uint32_t j = DEST ? ((v & 2u) ? 0u : ((v & 1u) ? 1u : 2u)) : ((v & 2u) ? 2u : v);
       s = s >= j ? s - j : 0;
     }
     // frame 0: the full aligner writes reference[state reached] (= position 0 on any valid path); the
@@ -259,6 +270,216 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     out[0] = make_uint2(1u | ((uint32_t)sref[DEST ? 0 : s] << 16), one);
     p.fcol[f0] = scol[DEST ? 0 : s];
   }
+}
+
+// Multi-warp form for LONG utterances (T >= kVitMwMinFrames, sgmm_set_corpus): the automaton's positions are split over
+// W = 4 warps — thread g of the CTA owns positions [g C, (g + 1) C) — so that a frame costs C <= 4 positions per lane on
+// FOUR sub-partitions' FP64 pipes instead of up to 16 positions per lane on one (the one-warp kernel walked the 1399-frame
+// utterances at ~340 cycles per frame: they were the critical path of the whole stage).  Inside a warp the two boundary
+// costs cross lanes by shuffle as before; across warps lane 31 leaves {q[C-1], q[C-2]} in a double-buffered shared-memory
+// slot and ONE CTA barrier per frame makes them visible.  Same additions and comparisons in the same order as k_viterbi:
+// same bits.  The beam of the destination convention needs the frame's minimum over all warps: every warp leaves its
+// minimum next to the boundary costs, and each thread prunes its own costs AND the neighbour's boundary costs it reads in
+// the next frame with the same bound — still one barrier per frame.
+constexpr int kVitW = SGMM_VIT_MW_WARPS;
+template <int C, bool DEST>
+__global__ void __launch_bounds__(32 * kVitW) k_viterbi_mw(VitParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  constexpr int NT = 32 * kVitW;
+  const int g = threadIdx.x, lane = g & 31, warp = g >> 5;
+  if (blockIdx.x >= p.n_utts) return;
+  const uint32_t u = p.utts[blockIdx.x];
+  const uint64_t f0 = p.frame_off[u];
+  const uint32_t T = (uint32_t)(p.frame_off[u + 1] - f0);
+  const uint32_t a0 = p.aut_off[u];
+  const uint32_t S = p.aut_off[u + 1] - a0;
+  const uint32_t ncol = p.nuniq_pad[u];
+  const double* Eu = p.E + p.E_off[u];
+  const double INF = CUDART_INF;
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                          // SGMM_STAGES mbarriers
+  double* xq = reinterpret_cast<double*>(smem + 64);                           // [2 frames][W][q[C-1], q[C-2], warp min, -]
+  uint32_t* sh_hi = reinterpret_cast<uint32_t*>(xq + 2 * kVitW * 4);           // highest live position (DEST), + pad
+  double* tiles = reinterpret_cast<double*>(sh_hi + 4);                        // STAGES x TILE_T x ncol
+  const size_t tile_elems = (size_t)SGMM_TILE_T * ncol;
+  uint32_t* bpw = reinterpret_cast<uint32_t*>(tiles + SGMM_STAGES * tile_elems);   // ceil(T/16) x NT x C words
+  uint16_t* sref = reinterpret_cast<uint16_t*>(bpw + (size_t)((T + 15) / 16) * NT * C);
+  uint16_t* scol = sref + S;
+
+  const uint32_t n_tiles = (T + SGMM_TILE_T - 1) / SGMM_TILE_T;
+  if (g == 0) {
+    for (int i = 0; i < SGMM_STAGES; i++) mbar_init(&bars[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    *sh_hi = 0;
+  }
+  for (uint32_t s = g; s < S; s += NT) { sref[s] = (uint16_t)p.aut[a0 + s]; scol[s] = p.pos2uniq[a0 + s]; }
+  __syncthreads();
+  if (g == 0) {
+    for (uint32_t i = 0; i < SGMM_STAGES && i < n_tiles; i++) {
+      const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - i * SGMM_TILE_T);
+      const uint32_t bytes = rows * ncol * sizeof(double);
+      mbar_expect_tx(&bars[i], bytes);
+      tma_load_1d(tiles + i * tile_elems, Eu + (size_t)i * tile_elems, bytes, &bars[i]);
+    }
+  }
+
+  double q[C], pl[C], pk[C];
+  uint32_t col[C], w[C];
+  uint32_t validmask = 0;
+#pragma unroll
+  for (int c = 0; c < C; c++) {
+    const uint32_t s = g * C + c;
+    q[c] = INF; w[c] = 0; col[c] = 0;
+    pl[c] = p.tdp_loop; pk[c] = p.tdp_skip;
+    if (s < S) {
+      validmask |= 1u << c;
+      col[c] = scol[s];
+      if (sref[s] == p.silence_state) pl[c] = p.tdp_forward;
+      const uint32_t src = DEST ? s : (s >= 2 ? s - 2 : 0);
+      if (sref[src] == p.silence_state) pk[c] = p.tdp_forward;
+    }
+  }
+  const double pf = p.tdp_forward;
+  const bool prune = DEST && p.beam < INF;
+  double upper_prev = INF;        // pruning bound of the previous frame (applied to the neighbour's boundary costs)
+
+  for (uint32_t ti = 0; ti < n_tiles; ti++) {
+    const uint32_t slot = ti % SGMM_STAGES;
+    mbar_wait(&bars[slot], (ti / SGMM_STAGES) & 1);
+    const double* tile = tiles + slot * tile_elems;
+    const uint32_t t0 = ti * SGMM_TILE_T;
+    const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - t0);
+    for (uint32_t tt = 0; tt < rows; tt++) {
+      const uint32_t t = t0 + tt;
+      const double* row = tile + tt * ncol;
+      double e[C];
+#pragma unroll
+      for (int c = 0; c < C; c++) e[c] = row[col[c]];
+      double* xw = xq + ((t & 1) * kVitW + warp) * 4;
+      if (t == 0) {
+#pragma unroll
+        for (int c = 0; c < C; c++) q[c] = (g == 0 && c == 0) ? e[0] : INF;
+      } else {
+        double Q1 = __shfl_up_sync(0xffffffffu, q[C - 1], 1);
+        double Q2 = __shfl_up_sync(0xffffffffu, q[C - 2], 1);
+        if (lane == 0) {
+          if (warp == 0) { Q1 = INF; Q2 = INF; }
+          else {
+            const double* xr = xq + (((t - 1) & 1) * kVitW + warp - 1) * 4;
+            Q1 = xr[0]; Q2 = xr[1];
+            if (prune) { Q1 = Q1 > upper_prev ? INF : Q1; Q2 = Q2 > upper_prev ? INF : Q2; }
+          }
+        }
+        double nq[C];
+        const uint32_t sh = 2 * (t & 15);
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+          const double p1 = c > 0 ? q[c > 0 ? c - 1 : 0] : Q1;
+          const double p2 = c > 1 ? q[c > 1 ? c - 2 : 0] : (c == 1 ? Q1 : Q2);
+          uint32_t j;
+          if (!DEST) {
+            const double lv = __dadd_rn(q[c], pl[c]);
+            const double fv = __dadd_rn(p1, pf);
+            const double kv = __dadd_rn(p2, pk[c]);
+            const bool f1 = fv < lv;
+            const double m1 = f1 ? fv : lv;
+            const bool f2 = kv < m1;
+            const double best = f2 ? kv : m1;
+            j = f2 ? 2u : (f1 ? 1u : 0u);
+            nq[c] = __dadd_rn(e[c], best);
+          } else {
+            const double ck = __dadd_rn(__dadd_rn(p2, pk[c]), e[c]);
+            const double cf = __dadd_rn(__dadd_rn(p1, pf), e[c]);
+            const double cl = __dadd_rn(__dadd_rn(q[c], pl[c]), e[c]);
+            const bool f1 = cf < ck;
+            const double m1 = f1 ? cf : ck;
+            const bool f2 = cl < m1;
+            nq[c] = f2 ? cl : m1;
+            j = f2 ? 0u : (f1 ? 1u : 2u);
+          }
+          w[c] |= j << sh;
+        }
+        if (prune) {
+          double best = INF;
+#pragma unroll
+          for (int c = 0; c < C; c++)
+            if ((validmask >> c) & 1) best = fmin(best, nq[c]);
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
+          if (lane == 0) xw[2] = best;
+        }
+#pragma unroll
+        for (int c = 0; c < C; c++) q[c] = nq[c];
+      }
+      if (lane == 31) { xw[0] = q[C - 1]; xw[1] = q[C - 2]; }      // (unpruned; the reader applies the frame's bound)
+      __syncthreads();                                             // the frame's one barrier
+      if (prune && t >= 1) {
+        const double* xb = xq + (t & 1) * kVitW * 4;
+        double best = xb[2];
+#pragma unroll
+        for (int ww = 1; ww < kVitW; ww++) best = fmin(best, xb[ww * 4 + 2]);
+        const double upper = __dadd_rn(best, p.beam);
+#pragma unroll
+        for (int c = 0; c < C; c++) q[c] = q[c] > upper ? INF : q[c];
+        upper_prev = upper;
+      }
+      if (t >= 1 && ((t & 15) == 15 || t == T - 1)) {
+#pragma unroll
+        for (int c = 0; c < C; c++) { bpw[(size_t)(t >> 4) * NT * C + c * NT + g] = w[c]; w[c] = 0; }
+      }
+    }
+    // every thread has passed the barrier of the tile's last frame: the slot can be refilled
+    const uint32_t nxt = ti + SGMM_STAGES;
+    if (g == 0 && nxt < n_tiles) {
+      const uint32_t nrows = min((uint32_t)SGMM_TILE_T, T - nxt * SGMM_TILE_T);
+      const uint32_t bytes = nrows * ncol * sizeof(double);
+      mbar_expect_tx(&bars[slot], bytes);
+      tma_load_1d(tiles + slot * tile_elems, Eu + (size_t)nxt * tile_elems, bytes, &bars[slot]);
+    }
+  }
+
+  // end position and path cost
+  uint32_t end_s = S - 1;
+  if (DEST) {
+    uint32_t hi = 0;
+#pragma unroll
+    for (int c = 0; c < C; c++)
+      if (((validmask >> c) & 1) && q[c] < INF) hi = g * C + c + 1;
+    if (hi) atomicMax(sh_hi, hi);
+    __syncthreads();
+    hi = *sh_hi;
+    end_s = hi ? hi - 1 : 0;
+  }
+  if ((uint32_t)g == end_s / C && p.costs) p.costs[u] = (!DEST && T == 1) ? INF : pick<C>(q, (int)(end_s % C));
+  __syncthreads();   // the last backpointer words are in shared memory
+
+  if (g == 0) {
+    uint2* out = reinterpret_cast<uint2*>(p.ali + f0);
+    const uint32_t one = __float_as_uint(1.0f);
+    uint32_t s = end_s;
+    for (uint32_t t = T - 1; t >= 1; t--) {
+      out[t] = make_uint2(1u | ((uint32_t)sref[s] << 16), one);
+      p.fcol[f0 + t] = scol[s];
+      const uint32_t word = bpw[(size_t)(t >> 4) * NT * C + (s % C) * NT + s / C];
+      const uint32_t j = (word >> (2 * (t & 15))) & 3u;
+      s = s >= j ? s - j : 0;
+    }
+    out[0] = make_uint2(1u | ((uint32_t)sref[DEST ? 0 : s] << 16), one);
+    p.fcol[f0] = scol[DEST ? 0 : s];
+  }
+}
+
+template <int C>
+int launch_mw(sgmm_ctx* c, const VitParams& p, size_t smem, int conv, cudaStream_t stream) {
+  if (conv == SGMM_TDP_SOURCE) {
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_viterbi_mw<C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_viterbi_mw<C, false><<<p.n_utts, 32 * kVitW, smem, stream>>>(p);
+  } else {
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_viterbi_mw<C, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_viterbi_mw<C, true><<<p.n_utts, 32 * kVitW, smem, stream>>>(p);
+  }
+  SGMM_LAUNCH_CHECK(c);
+  return 0;
 }
 
 template <int C>
@@ -294,6 +515,16 @@ int sgmm_launch_viterbi(sgmm_ctx* c, int conv) {
     p.beam = c->beam;
     p.ali = c->d_ali.p; p.fcol = c->d_fcol.p; p.costs = c->d_costs.p;
     int rc = 1;
+    if (vc.W == kVitW) {
+      switch (vc.C) {
+        case 2: rc = launch_mw<2>(c, p, vc.smem, conv, stream); break;
+        case 3: rc = launch_mw<3>(c, p, vc.smem, conv, stream); break;
+        case 4: rc = launch_mw<4>(c, p, vc.smem, conv, stream); break;
+        default: SGMM_FAIL(c, "viterbi: unsupported positions-per-lane class of the multi-warp kernel");
+      }
+      if (rc) return rc;
+      continue;
+    }
     switch (vc.C) {
       case 2: rc = launch_c<2>(c, p, vc.smem, conv, stream); break;
       case 3: rc = launch_c<3>(c, p, vc.smem, conv, stream); break;

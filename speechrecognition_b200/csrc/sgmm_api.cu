@@ -25,10 +25,11 @@ void begin_call(sgmm_ctx* c) { sgmm_stage_reset(c); }
 
 constexpr int kViterbiC[] = {2, 3, 4, 5, 6, 8, 10, 12, 16};
 
-size_t viterbi_smem(uint32_t T, uint32_t S, uint32_t ncol, int C) {
+size_t viterbi_smem(uint32_t T, uint32_t S, uint32_t ncol, int C, int W = 1) {
   size_t b = 64;
+  if (W > 1) b += 2 * (size_t)W * 4 * sizeof(double) + 16;     // k_viterbi_mw: boundary-cost exchange + end position
   b += (size_t)SGMM_STAGES * SGMM_TILE_T * ncol * sizeof(double);
-  b += (size_t)((T + 15) / 16) * 32 * C * sizeof(uint32_t);
+  b += (size_t)((T + 15) / 16) * 32 * W * C * sizeof(uint32_t);
   b += 2 * (size_t)S * sizeof(uint16_t);
   return (b + 15) & ~(size_t)15;
 }
@@ -172,7 +173,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
   std::vector<uint64_t> E_off(U + 1, 0);
   std::vector<uint4> tasks, tasks64, tasks128, tasks256;
   std::vector<uint64_t> t128_end, t256_end;
-  std::map<std::pair<int, size_t>, ViterbiClass> classes;
+  std::map<std::pair<int, size_t>, ViterbiClass> classes;   // key: (C + 100 W, shared-memory bucket)
   uint32_t max_state = 0, max_uniq = 0;
   for (uint32_t u = 0; u < U; u++) {
     if (frame_off[u + 1] <= frame_off[u]) SGMM_FAIL(c, "set_corpus: empty utterance");
@@ -200,15 +201,17 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       tasks128.push_back(make_uint4(u, t0, 0, 0));
       t128_end.push_back(frame_off[u] + std::min(T, t0 + 128));
     }
+    // long utterances: positions split over four warps (k_viterbi_mw), C <= 4 positions per lane
+    const int W = (c->vit_mw && T >= (uint32_t)c->vit_mw) ? SGMM_VIT_MW_WARPS : 1;
     int C = 0;
-    for (int cc : kViterbiC) if ((uint32_t)cc * 32 >= S) { C = cc; break; }
-    size_t sm = viterbi_smem(T, S, ncol[u], C);
+    for (int cc : kViterbiC) if ((uint32_t)cc * 32 * W >= S) { C = cc; break; }
+    size_t sm = viterbi_smem(T, S, ncol[u], C, W);
     if (sm > 227 * 1024) SGMM_FAIL(c, "set_corpus: utterance trellis exceeds shared memory (T*S too large)");
     size_t bucket = 8 * 1024;  // classes by shared-memory bucket so short utterances keep high occupancy
     while (bucket < sm) bucket += bucket < 64 * 1024 ? 8 * 1024 : 32 * 1024;
     bucket = std::min(bucket, (size_t)227 * 1024);
-    ViterbiClass& vc = classes[{C, bucket}];
-    vc.C = C; vc.smem = bucket;
+    ViterbiClass& vc = classes[{C + 100 * W, bucket}];
+    vc.C = C; vc.W = W; vc.smem = bucket;
     vc.utts.push_back(u);
   }
   // ---- GEMM tasks of 256 frames.  The last task of an utterance often holds few frames (T = 279 leaves 23), yet a
@@ -327,6 +330,17 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
       return frame_off[a + 1] - frame_off[a] > frame_off[b + 1] - frame_off[b];
     });
     c->vclasses.push_back(std::move(kv.second));
+  }
+  // launch order (sgmm_launch_viterbi forks the classes over side streams): the class whose longest utterance is the
+  // most work goes first — a frame costs about (1 + 2C) issue slots per lane — so the few very long utterances start at
+  // once and the many short ones fill the machine around them
+  {
+    auto longest = [&](const ViterbiClass& vc) {
+      const uint32_t u = vc.utts.front();
+      return (uint64_t)(frame_off[u + 1] - frame_off[u]) * (uint64_t)(1 + 2 * vc.C);
+    };
+    std::stable_sort(c->vclasses.begin(), c->vclasses.end(),
+                     [&](const ViterbiClass& a, const ViterbiClass& b) { return longest(a) > longest(b); });
   }
   for (auto& vc : c->vclasses)
     if (upload(c, vc.d_utts, vc.utts.data(), vc.utts.size())) return 1;
@@ -453,6 +467,10 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_epi16")) { c->tc_epi16 = (int)value; return 0; }
   if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
   if (!strcmp(key, "tc_rem")) { c->tc_rem = (int)value; return 0; }   // read by sgmm_set_model
+  if (!strcmp(key, "vit_mw")) {   // read by sgmm_set_corpus: 0 = never, 1 = default threshold, n > 1 = utterances of >= n frames
+    c->vit_mw = value <= 0 ? 0 : (value == 1 ? SGMM_VIT_MW_MIN_FRAMES : (int)value);
+    return 0;
+  }
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
   if (!strcmp(key, "host_tables")) { c->host_tables = value != 0; return 0; }   // read by sgmm_set_model

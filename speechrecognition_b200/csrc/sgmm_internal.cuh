@@ -11,6 +11,8 @@
 #define SGMM_WARP 32
 #define SGMM_TILE_T 16      // Viterbi: time steps per emission tile
 #define SGMM_STAGES 3       // Viterbi: emission tiles in flight (cp.async.bulk ring)
+#define SGMM_VIT_MW_WARPS 4        // k_viterbi_mw: warps per utterance
+#define SGMM_VIT_MW_MIN_FRAMES 1000  // utterances at least this long take the multi-warp Viterbi kernel
 #define SGMM_SORT_CHUNK 2048  // radix sort: keys per warp-chunk
 #define SGMM_RED_BLOCK 256    // segmented reduce: frames per partial
 
@@ -43,6 +45,7 @@ struct sgmm_pack_row {   // one row of a packed GEMM task (sgmm_set_corpus)
 
 struct ViterbiClass {  // utterances that share one launch (same lanes-per-position shape + smem size)
   int C = 0;                 // positions per lane
+  int W = 1;                 // warps per utterance: 1 = k_viterbi, 4 = k_viterbi_mw (long utterances)
   size_t smem = 0;           // dynamic shared memory per CTA
   std::vector<uint32_t> utts;
   DevBuf<uint32_t> d_utts;
@@ -203,6 +206,7 @@ struct sgmm_ctx : SgmmModel {
   bool sum_prune = true;          // option "sum_prune": sum scores through the f32-pruned kernel (k_sum_pruned)
   bool ali_has_cols = false;      // resident alignment came from sgmm_align (d_fcol valid)
   std::vector<ViterbiClass> vclasses;
+  int vit_mw = SGMM_VIT_MW_MIN_FRAMES;   // option "vit_mw" (read by sgmm_set_corpus): utterances of at least this many frames take k_viterbi_mw; 0 = never
   DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)
 
   // ---- tdp

@@ -589,3 +589,44 @@ def test_align_accumulate_equals_the_two_calls(small33):
         assert np.array_equal(a2["state"], got["state"]) and np.array_equal(a2["count"], got["count"])
         assert np.array_equal(c2, costs)
         assert np.array_equal(r[0], cnt) and np.array_equal(r[1], sx) and np.array_equal(r[2], sxx) and r[3] == ssum
+
+
+@pytest.mark.parametrize("beam", [float("inf"), 60.0, 15.0])
+def test_multiwarp_viterbi_long_utterances(beam):
+    """k_viterbi_mw (utterances of >= 384 frames: positions split over four warps, one CTA barrier per frame) against the
+    oracle and against the one-warp kernel (option vit_mw = 0): states and f64 path costs bit-identical in the full aligner
+    (source convention) and in the pruned one (destination convention, finite beams included)."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(77)
+    dim = 25
+    lex = synth.Lexicon()
+    tables = synth.random_model(rng, dim, lex.num_states, 3, "none")
+    corp = synth.make_corpus(rng, lex, tables, dim, 14, t_choices=([500, 701, 1399, 279], [0.4, 0.2, 0.2, 0.2]), words_per_utt=(3, 7))
+    # one very long automaton (S > 256: four positions per lane over four warps)
+    O = Oracle(dim, lex.num_states, "none", True, helpers.TDP, lex.silence_state)
+    O.load_tables(tables)
+    res = {}
+    for mw in (1, 0):
+        ctx = capi.Context(0)
+        ctx.set_option("vit_mw", mw)
+        ctx.set_model_tables(dim, tables)
+        ctx.set_features(corp["x"])
+        ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"])
+        ctx.set_tdp(*helpers.TDP, lex.silence_state)
+        full = ctx.align(capi.TDP_SOURCE)
+        ctx.set_beam(beam)
+        pruned = ctx.align(capi.TDP_DESTINATION)
+        res[mw] = (full[0]["state"].copy(), full[1].copy(), pruned[0]["state"].copy(), pruned[1].copy())
+        ctx.close()
+    for a, b in zip(res[1], res[0]):
+        assert np.array_equal(a, b)
+    want_states, want_costs = O.align_batch(corp["x"], corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
+    assert np.array_equal(res[1][0].astype(np.uint32), want_states) and np.array_equal(res[1][1], want_costs)
+    thr = 1e300 if beam == float("inf") else beam
+    for u in range(len(corp["frame_off"]) - 1):
+        f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
+        aut = corp["automata"][corp["aut_off"][u]:corp["aut_off"][u + 1]]
+        c, st, _ = O.align_pruned(corp["x"][f0:f1], aut, thr)
+        assert c == res[1][3][u], (u, f1 - f0, len(aut))
+        assert np.array_equal(res[1][2][f0:f1].astype(np.uint32), st), (u, f1 - f0, len(aut))
