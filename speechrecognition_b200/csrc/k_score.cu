@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(kEmisWarps * 32) k_emission_f64(EmisParams p) 
     ulist = p.uniq + p.uniq_off[t.x];
     nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
     out_stride = p.nuniq_pad[t.x];
-    out = p.E + p.E_off[t.x] + (uint64_t)t.y * out_stride;
+    out = p.E + p.E_off[t.x] + (uint64_t)t.y * out_stride;       // t.y is a multiple of 16: first cell of its tile
     amin16 = p.Amin + p.E_off[t.x] + (uint64_t)t.y * out_stride;
   }
   load_frames(p.x, fbase, nvalid, p.m.dim, p.m.npair, xs, xt, lane);
@@ -193,10 +193,19 @@ __global__ void __launch_bounds__(kEmisWarps * 32) k_emission_f64(EmisParams p) 
       uint32_t bk = 0;
       if (SUM) best = sum_over_state(p.m, p.m.state_off[s], p.m.state_off[s + 1], my_xs, 32, xtail);
       else min_over_state(p.m, p.m.state_off[s], p.m.state_off[s + 1], my_xs, 32, xtail, best, bk);
+      if (amin16) {
+        // gathered: the tiled layout (sgmm_cell_rel) runs along the frames, lane = frame stores straight away
+        if (lane < (int)nvalid) {
+          const uint64_t cell = sgmm_cell_rel(out_stride, lane, j0 + jj);
+          out[cell] = best;
+          amin16[cell] = (uint16_t)bk;
+        }
+        continue;
+      }
       stage[lane * 33 + jj] = best;
       if (amin && lane < (int)nvalid) amin[(uint64_t)lane * out_stride + j0 + jj] = bk;
-      if (amin16 && lane < (int)nvalid) amin16[(uint64_t)lane * out_stride + j0 + jj] = (uint16_t)bk;
     }
+    if (amin16) continue;
     __syncwarp();
     if (out && lane < (int)jn)
       for (uint32_t r = 0; r < nvalid; r++) out[(uint64_t)r * out_stride + j0 + lane] = stage[r * 33 + lane];
@@ -277,7 +286,7 @@ __global__ void __launch_bounds__(256) k_rescore_cached(CachedParams p) {
     const uint32_t mid = (lo + hi) >> 1;
     if (p.frame_off[mid] <= f) lo = mid; else hi = mid;
   }
-  const uint64_t e = p.E_off[lo] + (f - p.frame_off[lo]) * p.nuniq_pad[lo] + p.fcol[f];
+  const uint64_t e = p.E_off[lo] + sgmm_cell_rel(p.nuniq_pad[lo], (uint32_t)(f - p.frame_off[lo]), p.fcol[f]);
   const uint32_t s = p.ali[f].state;
   const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
   const uint32_t gid = (k1 > k0) ? k0 + p.Amin[e] : p.Dtot;

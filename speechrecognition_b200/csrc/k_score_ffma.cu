@@ -206,9 +206,11 @@ __global__ void __launch_bounds__(kWarps * 32) k_emission_ffma(Params p) {
           }
         }
       }
-      if (out) out[(uint64_t)row * out_stride + j] = best;
-      if (amin) amin[(uint64_t)row * out_stride + j] = bk;
-      if (amin16) amin16[(uint64_t)row * out_stride + j] = (uint16_t)bk;
+      // gathered (amin16): the tiled layout of sgmm_cell_rel; the task starts on a tile boundary
+      const uint64_t cell = amin16 ? sgmm_cell_rel(out_stride, row, j) : (uint64_t)row * out_stride + j;
+      if (out) out[cell] = best;
+      if (amin) amin[cell] = bk;
+      if (amin16) amin16[cell] = (uint16_t)bk;
     }
   }
   if (p.fallback_count && n_fallback) atomicAdd(p.fallback_count, n_fallback);

@@ -32,6 +32,8 @@
 
 #include <cstring>
 
+#include <mutex>
+
 #include "sgmm_internal.cuh"
 
 namespace sgmm_tc {
@@ -535,6 +537,16 @@ constexpr uint32_t kUncertain = 0x80000000u;
 constexpr uint32_t kAccCol = 128;    // TMEM: columns [0, 128) hold Ahi of both halves, then three 128-column accumulators
 constexpr uint32_t kNumAcc = 3;
 
+// Verdict cell of (row, column).  Dense: row-major, row_cell = first cell of the row.  Gathered: the tiled layout of
+// sgmm_cell_rel — row_cell = first cell of the row's 16-frame tile + (t & 15), so that the 32 rows of a TMEM lane quarter
+// (consecutive frames) store two full 64-byte runs per column instead of 32 sectors.
+__device__ __forceinline__ uint64_t tc_row_cell(uint64_t out_base, uint32_t row, uint32_t out_stride, bool tiled) {
+  return tiled ? out_base + (uint64_t)(row >> 4) * (16u * out_stride) + (row & 15u) : out_base + (uint64_t)row * out_stride;
+}
+__device__ __forceinline__ uint64_t tc_cell(uint64_t row_cell, uint32_t col, bool tiled) {
+  return tiled ? (row_cell & ~15ull) + (col << 4) + (((uint32_t)row_cell ^ col) & 15u) : row_cell + col;
+}
+
 // Warps: 0 = bulk-copy producer, 1 = TMEM allocator + MMA issuer, 2..17 = epilogue: warp 2 + 8 * part + 4 * half + i
 // reduces columns [64 * part, +64) of frame half `half` (TMEM lane quarter = warp_id % 4).  With two valid halves, group g owns frame half g and accumulator g on
 // every tile.  With one valid half (short tail of an utterance, or large K) group 0 works alone and the two
@@ -743,7 +755,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
         if (lane == 0) mbar_arrive(a_full);
       }
       const float2 xn = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
-      const uint64_t my_cell = prow ? prow[row].cell : out_base + (uint64_t)row * out_stride;
+      const uint64_t my_cell = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, !p.dense);
       const uint16_t* my_map = prow ? p.pack_colmap + prow[row].colmap : nullptr;
       float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
       uint32_t it = 0;
@@ -827,7 +839,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           if (row < nvalid) {
             const bool certain = Bacc == 1.0f && Bsecond > Bbest + BG;
             const uint32_t col = my_map ? (uint32_t)my_map[j] : j;     // packed: this frame's utterance may not use state j
-            if (col != 0xFFFFu || !my_map) p.cand[my_cell + col] = certain ? (uint32_t)Bidx : kUncertain;
+            if (col != 0xFFFFu || !my_map) p.cand[tc_cell(my_cell, col, !p.dense)] = certain ? (uint32_t)Bidx : kUncertain;
           }
         }
       }
@@ -1080,7 +1092,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
     for (int g = 0; g < 2; g++) {
       const uint32_t row = min((uint32_t)g, nh - 1) * BM + lrow;
       xn[g] = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
-      my_cell[g] = prow ? prow[row].cell : out_base + (uint64_t)row * out_stride;
+      my_cell[g] = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, !p.dense);
       my_map[g] = prow ? p.pack_colmap + prow[row].colmap : nullptr;
     }
     uint32_t it = 0;
@@ -1147,7 +1159,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
             if (row < nvalid) {
               const bool certain = Bacc[g] == 1.0f && Bsecond[g] > Bbest[g] + BG[g];
               const uint32_t col = my_map[g] ? (uint32_t)my_map[g][j] : j;
-              if (col != 0xFFFFu || !my_map[g]) p.cand[my_cell[g] + col] = certain ? (uint32_t)Bidx[g] : kUncertain;
+              if (col != 0xFFFFu || !my_map[g]) p.cand[tc_cell(my_cell[g], col, !p.dense)] = certain ? (uint32_t)Bidx[g] : kUncertain;
             }
           }
         }
@@ -1183,7 +1195,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
         if (lane == 0) mbar_arrive(a_full);
       }
       const float2 xn = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
-      const uint64_t my_cell = prow ? prow[row].cell : out_base + (uint64_t)row * out_stride;
+      const uint64_t my_cell = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, !p.dense);
       const uint16_t* my_map = prow ? p.pack_colmap + prow[row].colmap : nullptr;
       float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
       uint32_t it = 0;
@@ -1272,7 +1284,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           if (row < nvalid) {
             const bool certain = Bacc == 1.0f && Bsecond > Bbest + BG;
             const uint32_t col = my_map ? (uint32_t)my_map[j] : j;     // packed: this frame's utterance may not use state j
-            if (col != 0xFFFFu || !my_map) p.cand[my_cell + col] = certain ? (uint32_t)Bidx : kUncertain;
+            if (col != 0xFFFFu || !my_map) p.cand[tc_cell(my_cell, col, !p.dense)] = certain ? (uint32_t)Bidx : kUncertain;
           }
         }
       }
@@ -1325,6 +1337,8 @@ struct RefineParams {
   const uint2* sm_ent_b;
   uint32_t sm_rw;              // doubles per table row: mean row, norm, padding (2 * odd: bank spread for LDS.128)
   uint32_t sm_maxnd;           // most densities in one state
+  const uint32_t* sm_ivoff;    // per item: first double of its state's inverse-variance row in invU / c_iv (k_sm_ivoff)
+  uint32_t sm_lq;              // entries of the CTA-local near-tie list (0: none, every near-tie goes straight to the global queue)
   // two-stage rescan: f32 tables of the FFMA scorer ([D][4 * dv4] mean and h = 1 / (2 var), c = norm - log w) and
   // the per-state constants of its certified error bound {cmin, |c| max, M max}
   const float4* mu32T;         // [dv4][D]
@@ -1345,12 +1359,16 @@ __device__ __forceinline__ bool decode_cell(const RefineParams& p, uint64_t e, u
     const uint32_t mid = (lo + hi) >> 1;
     if (p.E_off[mid] <= e) lo = mid; else hi = mid;
   }
+  // inverse of sgmm_cell_rel
   const uint64_t local = e - p.E_off[lo];
   const uint32_t ncol = p.nuniq_pad[lo];
-  const uint32_t j = (uint32_t)(local % ncol);
+  const uint64_t tile = local / (16u * ncol);
+  const uint32_t rem = (uint32_t)(local - tile * 16u * ncol);
+  const uint32_t j = rem >> 4;
+  const uint64_t t = tile * 16u + ((rem ^ j) & 15u);
   const uint32_t nu = p.uniq_off[lo + 1] - p.uniq_off[lo];
-  if (j >= nu) return false;
-  frame = p.frame_off[lo] + local / ncol;
+  if (j >= nu || t >= p.frame_off[lo + 1] - p.frame_off[lo]) return false;   // padding column / padding frames
+  frame = p.frame_off[lo] + t;
   s = p.uniq[p.uniq_off[lo] + j];
   return true;
 }
@@ -1440,9 +1458,20 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
     }
     __syncthreads();
   }
-  const uint32_t ncell = nrows * ncol;
+  // dense: cells are row-major.  Gathered: the granule starts on a tile boundary of the tiled layout (sgmm_cell_rel), its
+  // cells are [tile][column][16 frames] and consecutive threads walk a column's 16-frame run.
+  const bool tiled = !p.dense;
+  const uint32_t ncell = tiled ? ((nrows + 15u) >> 4) * 16u * ncol : nrows * ncol;
   for (uint32_t i = threadIdx.x; i < ncell; i += 256) {
-    const uint32_t r = i / ncol, j = i - r * ncol;
+    uint32_t r, j;
+    if (tiled) {
+      const uint32_t tile = i / (16u * ncol), rem = i - tile * 16u * ncol;
+      j = rem >> 4;
+      r = tile * 16u + ((rem ^ j) & 15u);
+      if (r >= nrows) continue;                  // padding frames of the last tile
+    } else {
+      r = i / ncol; j = i - r * ncol;
+    }
     if (j >= nu) continue;                       // padding column of a gathered row
     const uint64_t e = cell0 + i, frame = frame0 + r;
     const uint32_t s = ulist ? ulist[j] : j;
@@ -1472,23 +1501,42 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
 }
 
 // exact score of one density from a shared-memory table row {mean[dim], norm}: exact_score_unrolled's operation
-// order (two running sums over even / odd dimensions, then the odd tail), hence the same bits
-template <uint32_t DIM>
-__device__ __forceinline__ double sm_exact(const double* row, double logw, const float* xr, const double* iv) {
+// order (two running sums over even / odd dimensions, then the odd tail), hence the same bits.  VEC: the feature row is
+// 16-byte aligned (even dimensions) and is read as float4.
+// The inverse-variance rows of the model, as many as fit (kCivDoubles), in the constant bank: every thread of a
+// state-major refinement CTA reads the SAME row, and a warp-uniform LDS.128 still costs two shared-memory wavefronts
+// (measured: 33 of the ~200 wavefronts per 32 cells, on the pipe that bounds the kernel); constant-bank operands come
+// through the uniform datapath instead.  One copy per device and process: refine_civ_bind hands it from owner to owner.
+constexpr uint32_t kCivDoubles = 5632;       // 44 KB of the 64 KB bank
+__constant__ double c_iv[kCivDoubles];
+
+// CIV: the inverse variances are c_iv[ivoff ...] instead of iv[...]
+template <uint32_t DIM, bool VEC, bool CIV>
+__device__ __forceinline__ double sm_exact(const double* row, double logw, const float* xr, const double* iv, uint32_t ivoff) {
   constexpr int NP = DIM / 2;
   static_assert(NP % 4 == 0, "dimension pairs are walked in blocks of four");
   double l0 = 0.0, l1 = 0.0;
 #pragma unroll
-  for (int g = 0; g < NP; g += 4) {          // four 16-byte units in flight: keeps the kernel inside 64 registers
+  for (int g = 0; g < NP; g += 4) {          // four 16-byte units of the mean row in flight
     double2 mu[4];
+    float xv[8];
 #pragma unroll
     for (int j = 0; j < 4; j++) mu[j] = *reinterpret_cast<const double2*>(row + 2 * (g + j));
+    if (VEC) {
+      const float4 x0 = *reinterpret_cast<const float4*>(xr + 2 * g), x1 = *reinterpret_cast<const float4*>(xr + 2 * g + 4);
+      xv[0] = x0.x; xv[1] = x0.y; xv[2] = x0.z; xv[3] = x0.w; xv[4] = x1.x; xv[5] = x1.y; xv[6] = x1.z; xv[7] = x1.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; j++) xv[j] = xr[2 * g + j];
+    }
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int ip = g + j;
-      const double2 v = *reinterpret_cast<const double2*>(iv + 2 * ip);
-      double a = __dsub_rn((double)xr[2 * ip], mu[j].x);
-      double b = __dsub_rn((double)xr[2 * ip + 1], mu[j].y);
+      double2 v;
+      if (CIV) v = make_double2(c_iv[ivoff + 2 * ip], c_iv[ivoff + 2 * ip + 1]);
+      else v = *reinterpret_cast<const double2*>(iv + 2 * ip);
+      double a = __dsub_rn((double)xv[2 * j], mu[j].x);
+      double b = __dsub_rn((double)xv[2 * j + 1], mu[j].y);
       a = __dmul_rn(a, a); b = __dmul_rn(b, b);
       a = __dmul_rn(a, v.x); b = __dmul_rn(b, v.y);
       l0 = __dadd_rn(l0, a); l1 = __dadd_rn(l1, b);
@@ -1497,60 +1545,87 @@ __device__ __forceinline__ double sm_exact(const double* row, double logw, const
   double dist = __dadd_rn(l0, l1);
   if (DIM & 1) {
     const double c = __dsub_rn((double)xr[DIM - 1], row[DIM - 1]);
-    dist = __dadd_rn(dist, __dmul_rn(__dmul_rn(c, c), iv[DIM - 1]));
+    dist = __dadd_rn(dist, __dmul_rn(__dmul_rn(c, c), CIV ? c_iv[ivoff + DIM - 1] : iv[DIM - 1]));
   }
   return __dsub_rn(__dadd_rn(row[DIM], __dmul_rn(dist, 0.5)), logw);
 }
 
 // whole-state rescan of one cell, densities first, first + step, ... (out of line: only taken when the rescan list is full)
-template <uint32_t DIM>
+template <uint32_t DIM, bool VEC>
 __device__ __noinline__ void sm_rescan(const double* tbl, const double* lw, const float* xb, const double* iv, uint32_t nd,
                                        uint32_t RW, uint32_t first, uint32_t step, double& rb_out, uint32_t& rk_out) {
   double rb = 1e10;
   uint32_t rk = 0xffffffffu;
   for (uint32_t k = first; k < nd; k += step) {
-    const double sc = sm_exact<DIM>(tbl + (size_t)k * RW, lw[k], xb, iv);
+    const double sc = sm_exact<DIM, VEC, false>(tbl + (size_t)k * RW, lw[k], xb, iv, 0u);
     if (sc < rb) { rb = sc; rk = k; }
   }
   rb_out = rb; rk_out = rk;
+}
+
+// per item of the state-major refinement: where its state's inverse-variance row starts (model-dependent, so not part of
+// the corpus's item list)
+__global__ void k_sm_ivoff(const uint4* __restrict__ items, uint32_t n, const uint32_t* __restrict__ state_off,
+                           const uint32_t* __restrict__ var_of, uint32_t dimP, uint32_t* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t s = items[i].x, k0 = state_off[s];
+  out[i] = state_off[s + 1] > k0 ? var_of[k0] * dimP : 0u;
 }
 
 // State-major refinement (gathered, pooled models).  One CTA per item = (block of utterances, state): the state's
 // f64 mean rows + norms (nd x RW doubles, 72 KB at 256 densities, d = 33), its log weights and its inverse-variance
 // row are loaded into shared memory ONCE and serve every frame of the block's utterances that visit the state,
 // so the per-cell gather of the winner's mean row (272 B) is a shared-memory read instead of an L2 -> SM gather;
-// what streams from L2 is the feature rows (132 B per cell, contiguous).  A warp owns 32 consecutive cells of the
-// item (consecutive frames of an utterance, except across utterance boundaries): it stages their feature rows into its
-// own tile with coalesced loads, then thread = cell evaluates the certified winner with exact_score_unrolled's
-// operation order (same bits).  Near-tie cells are queued for k_tc_rescan as in the frame-major kernel.
-template <uint32_t DIM>
-__global__ void __launch_bounds__(1024, 1) k_tc_refine_sm(RefineParams p) {
+// what streams from L2 is the feature rows (132 B per cell, contiguous).
+//   * A warp's unit of work is a CHUNK: 32 consecutive frames [32 c, 32 c + 32) of ONE utterance in the state's column.
+//     In the tiled emission layout (sgmm_cell_rel) its verdicts are two 64-byte runs and its scores two full 128-byte
+//     lines; its feature rows are one contiguous run of global memory (odd dimensions: ONE bulk copy from the
+//     16-byte-aligned address below the first row, rows keep their odd stride = conflict-free thread = row reads;
+//     dimensions that are multiples of four: one bulk copy per row into a 16-byte-padded stride, read as float4).
+//   * Every warp owns TWO tiles: the next chunk's rows and verdicts are in flight while the current chunk is evaluated.
+//   * thread = cell evaluates the certified winner with exact_score_unrolled's operation order (same bits); lanes swap
+//     cells first so that the 8 lanes of a quarter-warp (one LDS.128 wavefront group) gather table rows from different
+//     16-byte bank groups (a row's group is (winner + unit) mod 8).
+// Near-tie cells are queued for k_tc_rescan as in the frame-major kernel.
+template <uint32_t DIM, bool CIV>   // CIV: the model's inverse-variance rows are in the constant bank (c_iv)
+__global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
-  constexpr uint32_t kMaxEnt = kSmMaxEntries, kMaxChunks = kSmBlockFrames / 32;
+  constexpr uint32_t kMaxEnt = kSmMaxEntries, kMaxChunks = kSmMaxChunks;
+  constexpr bool kOdd = (DIM & 1u) != 0;
+  static_assert(kOdd || DIM % 4 == 0, "even dimensions take one 16-byte-aligned bulk copy per row");
   constexpr uint32_t dim = DIM, kRowB = DIM * 4;
-  // Odd dimensions: the tile's rows are the frames' rows as they lie in global memory (stride = dim floats, odd, so
-  // thread = row reads are conflict-free) and arrive by 1-D bulk copies.  Even dimensions need a padded stride and
-  // take the element-wise cp.async path.
-  constexpr bool kBulk = (DIM & 1u) != 0;
-  constexpr uint32_t XS = dim | 1u;
-  constexpr uint32_t kTileB = 32 * XS * 4 + 64;              // + alignment slack of two bulk segments
+  constexpr uint32_t kRowS = kOdd ? kRowB : kRowB + 16;      // tile row stride: odd word count / odd 16-byte count
+  constexpr uint32_t kTileB = 32 * kRowS + (kOdd ? 32 : 0);  // odd: + the alignment slack of the one bulk copy
+  // The constant-bank reads of the chunk loop must come out as LDCU (uniform datapath, immediate offsets): per-thread
+  // LDC measured SLOWER than the shared-memory broadcast.  The compiler emits LDCU only inside warp-uniform control flow
+  // and from an offset it can prove uniform — a value loaded from a uniform address (sm_ivoff[blockIdx.x]; the chain
+  // state -> first density -> variance row is not followed), and a warp index passed through a lane-0 broadcast.
   const uint4 item = p.sm_items[blockIdx.x];
-  const uint32_t s = item.x, n_ent = item.z, n_cells = item.w;
-  const uint32_t k0 = p.state_off[s], nd = p.state_off[s + 1] - k0;
+  const uint32_t s = item.x, n_ent = item.z, n_chunks = __shfl_sync(0xffffffffu, item.w, 0);
+  const uint32_t k0 = p.state_off[s], nd = __shfl_sync(0xffffffffu, p.state_off[s + 1] - k0, 0);
   const uint32_t RW = p.sm_rw, dimP = p.m.dimP;
-  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nthr = blockDim.x;
+  const uint32_t lane = threadIdx.x & 31, warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const uint32_t nthr = blockDim.x, nwarp = blockDim.x >> 5;
   double* tbl = reinterpret_cast<double*>(sm_raw);           // [nd][RW]
   double* lw = tbl + (size_t)p.sm_maxnd * RW;                // [nd]
   double* iv = lw + ((p.sm_maxnd + 1u) & ~1u);               // [dimP], 16-byte aligned
-  uint4* ent_a = reinterpret_cast<uint4*>(iv + dimP);        // [kMaxEnt]
-  uint2* ent_b = reinterpret_cast<uint2*>(ent_a + kMaxEnt);  // [kMaxEnt]
-  uint16_t* chunk_ent = reinterpret_cast<uint16_t*>(ent_b + kMaxEnt);   // [kMaxChunks] entry of a chunk's first cell
-  uint64_t* bar = reinterpret_cast<uint64_t*>(chunk_ent + kMaxChunks) + warp;   // [32] one mbarrier per warp
-  uint8_t* perm = reinterpret_cast<uint8_t*>(chunk_ent + kMaxChunks) + 256 + warp * 32;   // [32][32] lane permutation
-  unsigned char* tile = reinterpret_cast<unsigned char*>(chunk_ent + kMaxChunks) + 1280 + warp * kTileB;
+  uint4* ent_a = reinterpret_cast<uint4*>(iv + dimP);        // [kMaxEnt] {E_off lo, hi, ncol | column << 16, chunks before}
+  uint2* ent_b = reinterpret_cast<uint2*>(ent_a + kMaxEnt);  // [kMaxEnt] {first frame, frames}
+  uint16_t* chunk_ent = reinterpret_cast<uint16_t*>(ent_b + kMaxEnt);   // [kMaxChunks] entry of a chunk
+  unsigned char* tail = reinterpret_cast<unsigned char*>(chunk_ent + kMaxChunks);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(tail) + 2 * warp;         // [nwarp][2] one mbarrier per tile
+  uint8_t* perm = tail + 16 * nwarp + warp * 32;                         // [nwarp][32] lane permutation
+  uint32_t* verdict = reinterpret_cast<uint32_t*>(tail + 48 * nwarp) + warp * 64;   // [nwarp][2][32] GEMM verdicts of a chunk
+  unsigned char* tiles = tail + 304 * nwarp + (size_t)warp * 2 * kTileB; // [nwarp][2][kTileB]
+  // near-ties of the item: collected here and appended to the global queue as ONE run at the end, so that the rescan
+  // kernel finds the cells of a state next to each other (it keeps a state's f32 tables in L1 across a run)
+  unsigned long long* lq = reinterpret_cast<unsigned long long*>(tail + 304 * nwarp + (size_t)nwarp * 2 * kTileB);   // [sm_lq]
+  uint32_t* lq_n = reinterpret_cast<uint32_t*>(lq + p.sm_lq);            // {entries, -, first slot of the run lo, hi}
   uint32_t n_rescans = 0;
+  if (threadIdx.x == 0) lq_n[0] = 0u;
 
-  if (lane == 0) mbar_init(bar, 1);
+  if (lane == 0) { mbar_init(bar, 1); mbar_init(bar + 1, 1); }
   for (uint32_t i = threadIdx.x; i < nd * dimP; i += nthr) {
     const uint32_t k = i / dimP, q = i - k * dimP;
     if (q < dim) tbl[(size_t)k * RW + q] = __ldg(p.m.meanR + (size_t)(k0 + k) * dimP + q);
@@ -1559,116 +1634,164 @@ __global__ void __launch_bounds__(1024, 1) k_tc_refine_sm(RefineParams p) {
     tbl[(size_t)k * RW + dim] = __ldg(p.m.norm + k0 + k);
     lw[k] = __ldg(p.m.logw + k0 + k);
   }
-  if (nd > 0)
-    for (uint32_t q = threadIdx.x; q < dimP; q += nthr) iv[q] = __ldg(p.m.invU + (size_t)__ldg(p.m.var_of + k0) * dimP + q);
+  const uint32_t ivoff = p.sm_ivoff[blockIdx.x];   // the state's row of invU / c_iv (k_sm_ivoff); a load from a uniform address
+  if (nd > 0)   // (kept in shared memory too: the in-kernel rescan of a full queue reads it there)
+    for (uint32_t q = threadIdx.x; q < dimP; q += nthr) iv[q] = __ldg(p.m.invU + (size_t)ivoff + q);
   for (uint32_t i = threadIdx.x; i < n_ent; i += nthr) {
     ent_a[i] = p.sm_ent_a[item.y + i];
     ent_b[i] = p.sm_ent_b[item.y + i];
   }
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
-  for (uint32_t j = threadIdx.x; j * 32 < n_cells; j += nthr) {
-    uint32_t lo = 0, hi = n_ent;                             // largest entry with cells-before <= 32 j
+  for (uint32_t j = threadIdx.x; j < n_chunks; j += nthr) {
+    uint32_t lo = 0, hi = n_ent;                             // largest entry with chunks-before <= j
     while (hi - lo > 1) {
       const uint32_t mid = (lo + hi) >> 1;
-      if (ent_a[mid].w <= j * 32) lo = mid; else hi = mid;
+      if (ent_a[mid].w <= j) lo = mid; else hi = mid;
     }
     chunk_ent[j] = (uint16_t)lo;
   }
   __syncthreads();
 
   const unsigned char* xbytes = reinterpret_cast<const unsigned char*>(p.x);
-  uint32_t phase = 0;
-  for (uint32_t c0 = warp * 32; c0 < n_cells; c0 += nthr) {
-    const uint32_t nvalid = min(32u, n_cells - c0);
-    const uint32_t i = min(c0 + lane, n_cells - 1);          // lanes past the end repeat the last cell, write nothing
-    uint32_t e = chunk_ent[c0 >> 5];
-    while (e + 1 < n_ent && ent_a[e + 1].w <= i) e++;
+  // A chunk in flight: where its cells are, how many are valid, its first frame and the alignment of its first row.
+  // Its verdicts travel by cp.async into the warp's own shared-memory slots: a register destination would have to stay
+  // live across the evaluation of the previous chunk, and the compiler spilled it straight away (measured: every chunk
+  // then waited a full global-memory latency on the spill store).
+  struct Chunk { uint64_t tile0; uint32_t col, nvalid, f0, al; };
+  auto issue = [&](uint32_t j, uint32_t b) {
+    Chunk ck;
+    const uint32_t e = chunk_ent[j];
     const uint4 ea = ent_a[e];
-    const uint32_t t = i - ea.w;
-    const uint64_t cell = (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)t * ea.z;
-    const uint32_t frame = ent_b[e].x + t;                    // (the launcher takes this kernel below 2^32 frames only)
-    const uint32_t i1 = nd ? __ldg(p.cand + cell) : 0u;
-    // ---- stage the 32 feature rows
-    uint32_t xr_off;                                          // byte offset of this lane's row inside the tile
-    __syncwarp();                                             // every lane is done with the previous tile
-    const uint32_t e0 = __shfl_sync(0xffffffffu, e, 0);
-    const uint32_t later = __ballot_sync(0xffffffffu, e != e0);
-    const uint32_t n0 = later ? (uint32_t)__ffs(later) - 1u : 32u;          // rows of the first utterance
-    const uint32_t e1 = __shfl_sync(0xffffffffu, e, n0 & 31u);
-    if (kBulk && __all_sync(0xffffffffu, e == e0 || e == e1)) {
-      // at most two utterances: each one's rows are contiguous in global memory -> one bulk copy each, from the
-      // 16-byte-aligned address below the first row (the tile keeps the same phase a)
-      const uint32_t fa = __shfl_sync(0xffffffffu, frame, 0), fb = __shfl_sync(0xffffffffu, frame, n0 & 31u);
-      const uint32_t rows_a = min(n0, nvalid), rows_b = nvalid - rows_a;
-      const size_t src_a = (size_t)fa * kRowB, src_b = (size_t)fb * kRowB;
-      const uint32_t a_a = (uint32_t)src_a & 15u, a_b = (uint32_t)src_b & 15u;
-      const uint32_t size_a = (rows_a * kRowB + a_a + 15u) & ~15u, size_b = rows_b ? (rows_b * kRowB + a_b + 15u) & ~15u : 0u;
-      if (lane == 0) {
-        mbar_expect_tx(bar, size_a + size_b);
-        bulk_load(tile, xbytes + src_a - a_a, size_a, bar);
-        if (rows_b) bulk_load(tile + size_a, xbytes + src_b - a_b, size_b, bar);
-      }
-      xr_off = lane < n0 ? a_a + lane * kRowB : size_a + a_b + (lane - n0) * kRowB;
-      mbar_wait(bar, phase);
-      phase ^= 1u;
-    } else {
-      // general case: element f = it * 32 + lane of the tile is (row r, column q), walked incrementally; the row's
-      // frame comes from its lane (asynchronous 4-byte copies, all in flight at once)
-      uint32_t r = lane / dim, q = lane - r * dim, dst = smem_u32(tile) + (r * XS + q) * 4u;
-#pragma unroll 4
-      for (uint32_t it = 0; it < dim; it++) {
-        const uint32_t fr = __shfl_sync(0xffffffffu, frame, r);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(p.x + (size_t)fr * dim + q) : "memory");
-        q += 32; dst += 32 * 4;
-        if (q >= dim) { q -= dim; r++; dst += (XS - dim) * 4; }
-        if (dim < 32 && q >= dim) { q -= dim; r++; dst += (XS - dim) * 4; }
-      }
-      asm volatile("cp.async.wait_all;" ::: "memory");
-      __syncwarp();
-      xr_off = lane * XS * 4u;
+    const uint2 eb = ent_b[e];
+    const uint32_t t0 = (j - ea.w) * 32u, ncol = ea.z & 0xffffu;
+    ck.col = ea.z >> 16;
+    ck.nvalid = min(32u, eb.y - t0);
+    ck.f0 = eb.x + t0;                                       // (the launcher takes this kernel below 2^32 frames only)
+    // first cell of the chunk's first 16-frame tile, in the state's column; lane l is frame t0 + l:
+    //   cell = tile0 + (l >> 4) * 16 ncol + ((l ^ col) & 15)
+    ck.tile0 = (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)(t0 >> 4) * (16u * ncol) + (ck.col << 4);
+    if (lane < ck.nvalid) {
+      const uint64_t cell = ck.tile0 + (uint64_t)(lane >> 4) * (16u * ncol) + ((lane ^ ck.col) & 15u);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(verdict + b * 32 + lane)), "l"(p.cand + cell) : "memory");
     }
-    // Lanes swap cells so that the 8 lanes of a quarter-warp (one LDS.128 wavefront group) gather table rows from
-    // different 16-byte bank groups: a row's group is (winner + unit) mod 8, so cells are ranked by winner mod 8 and
-    // dealt round-robin to the four quarters (10.1 -> 7.8 wavefronts per table load).
-    const bool valid = c0 + lane < n_cells;
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    ck.tile0 |= (uint64_t)ncol << 48;                       // (cells stay below 2^48)
+    unsigned char* tile = tiles + b * kTileB;
+    const size_t src = (size_t)ck.f0 * kRowB;
+    ck.al = 0u;
+    if (kOdd) {
+      ck.al = (uint32_t)src & 15u;
+      const uint32_t size = (ck.nvalid * kRowB + ck.al + 15u) & ~15u;
+      if (lane == 0) {
+        mbar_expect_tx(bar + b, size);
+        bulk_load(tile, xbytes + src - ck.al, size, bar + b);
+      }
+    } else {
+      if (lane == 0) mbar_expect_tx(bar + b, ck.nvalid * kRowB);
+      __syncwarp();
+      if (lane < ck.nvalid) bulk_load(tile + lane * kRowS, xbytes + src + (size_t)lane * kRowB, kRowB, bar + b);
+    }
+    return ck;
+  };
+
+  uint32_t phases = 0u;                                       // bit b: parity the next wait on tile b expects
+  uint32_t b = 0;
+  Chunk cur{};
+  if (warp < n_chunks) cur = issue(warp, 0);
+  for (uint32_t j = warp; j < n_chunks; j += nwarp, b ^= 1u) {
+    __syncwarp();                                             // every lane is done with the other tile
+    Chunk nxt{};
+    const bool more = j + nwarp < n_chunks;
+    if (more) nxt = issue(j + nwarp, b ^ 1u);
+    const uint32_t ncol = (uint32_t)(cur.tile0 >> 48);
+    const uint64_t tile0 = cur.tile0 & 0xffffffffffffull;
+    // this chunk's verdicts have landed (the next chunk's group may still be in flight); each lane reads its own slot
+    if (more) asm volatile("cp.async.wait_group 1;" ::: "memory");
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
+    const uint32_t i1 = (nd && lane < cur.nvalid) ? verdict[b * 32 + lane] : 0u;
+    // ---- lanes swap cells: rank the cells by winner mod 8 (ties by lane) and deal the ranks round-robin to the four
+    // quarter-warps, so that a quarter's eight table rows start in different 16-byte bank groups where possible
+    const bool valid = lane < cur.nvalid;
     uint32_t src;
     {
       const uint32_t key = (valid && i1 < nd) ? (i1 & 7u) : (lane & 7u);
-      const uint32_t lt = (1u << lane) - 1u;
-      uint32_t rank = 0;
+      uint32_t lt = 0u, eq = 0xffffffffu;
 #pragma unroll
-      for (uint32_t c = 0; c < 8; c++) {
-        const uint32_t m = __ballot_sync(0xffffffffu, key == c);
-        rank += c < key ? __popc(m) : (c == key ? __popc(m & lt) : 0u);
+      for (int bit = 2; bit >= 0; bit--) {
+        const uint32_t m = __ballot_sync(0xffffffffu, (key >> bit) & 1u);
+        if ((key >> bit) & 1u) { lt |= eq & ~m; eq &= m; } else { eq &= ~m; }
       }
+      const uint32_t rank = __popc(lt) + __popc(eq & ((1u << lane) - 1u));
       perm[((rank & 3u) << 3) | (rank >> 2)] = (uint8_t)lane;
       __syncwarp();
       src = perm[lane];
     }
-    const uint64_t my_cell = __shfl_sync(0xffffffffu, cell, src);
     const uint32_t my_i1 = __shfl_sync(0xffffffffu, i1, src);
-    const float* my_xr = reinterpret_cast<const float*>(tile + __shfl_sync(0xffffffffu, xr_off, src));
-    if (!__shfl_sync(0xffffffffu, (uint32_t)valid, src)) continue;
-    double best = 1e10;
-    uint32_t bk = 0;
-    if (nd) {
-      if (my_i1 < nd) {
-        const double sc = sm_exact<DIM>(tbl + (size_t)my_i1 * RW, lw[my_i1], my_xr, iv);
+    const uint64_t my_cell = tile0 + (uint64_t)(src >> 4) * (16u * ncol) + ((src ^ cur.col) & 15u);
+    const float* my_xr = reinterpret_cast<const float*>(tiles + b * kTileB + (kOdd ? cur.al + src * kRowB : src * kRowS));
+    mbar_wait(bar + b, (phases >> b) & 1u);
+    phases ^= 1u << b;
+    // the winner's exact score, evaluated by EVERY lane (lanes without a certified winner take row 0 and drop the
+    // result): the warp stays converged, so the uniform datapath can feed the constant-bank operands
+    const bool act = src < cur.nvalid, cert = act && my_i1 < nd;
+    const uint32_t ki = cert ? my_i1 : 0u;
+    const double sc = sm_exact<DIM, !kOdd, CIV>(tbl + (size_t)ki * RW, lw[ki], my_xr, iv, ivoff);
+    if (act) {
+      double best = 1e10;                              // min_score's own start, Mixtures.cpp:699
+      uint32_t bk = 0;
+      bool queued = false;
+      if (cert) {
         if (sc < best) { best = sc; bk = my_i1; }
-      } else {
+      } else if (nd) {
         // near-ties are queued for k_tc_rescan (a rescan inside this kernel was measured: one warp walking 256
         // densities holds its CTA back for ~10k cycles, +0.5 ms per 13 M cells)
-        const unsigned long long slot = atomicAdd(p.rescan, 1ull);
-        if (slot < p.cap) { p.rescan[1 + slot] = my_cell; continue; }
-        double rb;                                  // list full: rescan here
-        uint32_t rk;
-        sm_rescan<DIM>(tbl, lw, my_xr, iv, nd, RW, 0u, 1u, rb, rk);
-        best = rb; bk = rk == 0xffffffffu ? 0u : rk; n_rescans++;
+        const uint32_t ls = p.sm_lq ? atomicAdd(lq_n, 1u) : 0xffffffffu;
+        unsigned long long slot = 0ull;
+        if (ls < p.sm_lq) {
+          lq[ls] = my_cell;
+          queued = true;
+        } else if ((slot = atomicAdd(p.rescan, 1ull)) < p.cap) {   // local list full: straight to the global queue
+          p.rescan[1 + slot] = my_cell;
+          queued = true;
+        } else {                                     // both lists full: rescan here
+          double rb;
+          uint32_t rk;
+          sm_rescan<DIM, !kOdd>(tbl, lw, my_xr, iv, nd, RW, 0u, 1u, rb, rk);
+          best = rb; bk = rk == 0xffffffffu ? 0u : rk; n_rescans++;
+        }
+      }
+      if (!queued) {
+        p.out[my_cell] = best;
+        if (p.amin16) p.amin16[my_cell] = (uint16_t)bk;
       }
     }
-    p.out[my_cell] = best;
-    if (p.amin16) p.amin16[my_cell] = (uint16_t)bk;
+    cur = nxt;
+  }
+  // ---- the item's near-ties: one run of the global queue
+  if (p.sm_lq) {
+    __syncthreads();
+    const uint32_t nq = min(lq_n[0], p.sm_lq);
+    if (threadIdx.x == 0 && nq) {
+      const unsigned long long base = atomicAdd(p.rescan, (unsigned long long)nq);
+      lq_n[2] = (uint32_t)base; lq_n[3] = (uint32_t)(base >> 32);
+    }
+    __syncthreads();
+    const unsigned long long base = ((unsigned long long)lq_n[3] << 32) | lq_n[2];
+    for (uint32_t i = threadIdx.x; i < nq; i += nthr) {
+      const unsigned long long cell = lq[i];
+      if (base + i < p.cap) { p.rescan[1 + base + i] = cell; continue; }
+      // the global queue is full: rescan here, from the features in global memory
+      uint64_t frame;
+      uint32_t st;
+      decode_cell(p, cell, frame, st);
+      double rb;
+      uint32_t rk;
+      sm_rescan<DIM, !kOdd>(tbl, lw, p.x + frame * dim, iv, nd, RW, 0u, 1u, rb, rk);
+      p.out[cell] = rb;
+      if (p.amin16) p.amin16[cell] = rk == 0xffffffffu ? (uint16_t)0 : (uint16_t)rk;
+      n_rescans++;
+    }
   }
   if (n_rescans && p.fallback_count) atomicAdd(p.fallback_count, (unsigned long long)n_rescans);
 }
@@ -1716,11 +1839,16 @@ __global__ void __launch_bounds__(256) k_tc_rescan(RefineParams p) {
 template <int DV4>
 __global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
   const uint32_t lane = threadIdx.x & 31;
-  const uint64_t nwarps = (uint64_t)gridDim.x * (blockDim.x >> 5);
   const unsigned long long count = min(p.rescan[0], p.cap);
   const float eps = 2.384185791015625e-07f;   // 2^-22, as k_emission_ffma
   const float dterm = (float)(p.m.dim + 8);
-  for (uint64_t i = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < count; i += nwarps) {
+  // A CTA takes kRun CONSECUTIVE queue entries at a time (its eight warps walk them together): the state-major
+  // refinement appends an item's near-ties as one run, so the entries of a run share a state and its f32 tables (36 KB
+  // at 256 x 33) stay in this SM's L1 instead of crossing the L2 once per cell (measured: the kernel was L2-bound).
+  constexpr uint64_t kRun = 64;
+  const uint64_t wpb = blockDim.x >> 5;
+  for (uint64_t i0 = (uint64_t)blockIdx.x * kRun; i0 < count; i0 += (uint64_t)gridDim.x * kRun)
+  for (uint64_t i = i0 + (threadIdx.x >> 5); i < min((uint64_t)count, i0 + kRun); i += wpb) {
     const uint64_t e = p.rescan[1 + i];
     uint64_t frame;
     uint32_t s;
@@ -1833,7 +1961,7 @@ __global__ void __launch_bounds__(256, 3) k_sum_pruned(RefineParams p) {
   for (uint32_t cell = warp; cell < nu * 4 * 8; cell += 8) {
     const uint32_t j = cell / 32, fr = cell % 32;       // all warps share j: fr = warp, warp + 8, warp + 16, warp + 24
     if (fr >= nvalid) continue;
-    const uint64_t frame = fbase + fr, e = obase + (uint64_t)fr * ostride + j;
+    const uint64_t frame = fbase + fr, e = obase + (p.dense ? (uint64_t)fr * ostride + j : sgmm_cell_rel(ostride, fr, j));
     const uint32_t s = p.dense == 2 ? min((uint32_t)p.ali[frame].state, p.n_states - 1) : (ulist ? ulist[j] : j);
     const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
     const float* xf = p.x + frame * p.m.dim;
@@ -1919,6 +2047,57 @@ __global__ void __launch_bounds__(256, 3) k_sum_pruned(RefineParams p) {
 // ---------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------
+
+// c_iv is one table per device and process, shared by every context.  A context that finds another owner's rows there
+// (or an older model's) replaces them — after the last kernel that read the old rows (an event recorded behind every
+// launch that uses the table) — on its own stream, in front of its launch.  The mutex is held from bind to release so
+// that bind + launch + event are one step.
+namespace {
+using sgmm_tc::c_iv;
+using sgmm_tc::kCivDoubles;
+struct CivSlot {
+  std::mutex mu;
+  uint64_t owner = 0, version = 0;
+  cudaEvent_t last_use = nullptr;
+  bool used = false;
+};
+constexpr int kCivDevices = 64;
+CivSlot g_civ[kCivDevices];
+
+int refine_civ_bind(sgmm_ctx* c, bool* civ) {
+  *civ = false;
+  const size_t n = (size_t)c->n_var_rows * c->dimP;
+  if (!c->tc_civ || n == 0 || n > kCivDoubles || c->device < 0 || c->device >= kCivDevices) return 0;
+  CivSlot& g = g_civ[c->device];
+  g.mu.lock();
+  if (!g.last_use && cudaEventCreateWithFlags(&g.last_use, cudaEventDisableTiming) != cudaSuccess) {
+    g.mu.unlock();
+    SGMM_FAIL(c, "refine: cannot create the constant-table event");
+  }
+  if (g.owner != c->serial || g.version != c->model_version) {
+    cudaError_t e = g.used ? cudaStreamWaitEvent(c->stream, g.last_use, 0) : cudaSuccess;
+    if (e == cudaSuccess)
+      e = cudaMemcpyToSymbolAsync(c_iv, c->d_invU.p, n * sizeof(double), 0, cudaMemcpyDeviceToDevice, c->stream);
+    if (e != cudaSuccess) {
+      g.owner = 0;
+      g.mu.unlock();
+      SGMM_FAIL(c, std::string("refine: constant-table upload: ") + cudaGetErrorString(e));
+    }
+    g.owner = c->serial; g.version = c->model_version;
+  }
+  *civ = true;
+  return 0;
+}
+
+int refine_civ_release(sgmm_ctx* c) {
+  CivSlot& g = g_civ[c->device];
+  const cudaError_t e = cudaEventRecord(g.last_use, c->stream);
+  g.used = true;
+  g.mu.unlock();
+  if (e != cudaSuccess) SGMM_FAIL(c, std::string("refine: constant-table event: ") + cudaGetErrorString(e));
+  return 0;
+}
+}  // namespace
 namespace {
 
 // shared memory: Alo + the B ring (Ahi lives in tensor memory)
@@ -2043,17 +2222,23 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   while ((sm_rw & 1) || !((sm_rw >> 1) & 1)) sm_rw++;        // 2 * odd doubles per row
   uint32_t sm_maxnd = 0;
   for (uint32_t s = 0; s + 1 < c->h_state_off.size(); s++) sm_maxnd = std::max(sm_maxnd, c->h_state_off[s + 1] - c->h_state_off[s]);
-  // one CTA per SM: as many warps (each with its own 32-row feature tile) as fit next to the table
+  // one CTA per SM: as many warps (each with its own PAIR of 32-row feature tiles, mbarriers and lane permutation) as
+  // fit next to the table — the carve-up of k_tc_refine_sm
   const size_t sm_fixed = ((size_t)sm_maxnd * sm_rw + ((sm_maxnd + 1u) & ~1u) + c->dimP) * sizeof(double) +
-                          kSmMaxEntries * (sizeof(uint4) + sizeof(uint2)) + (kSmBlockFrames / 32) * sizeof(uint16_t) + 1280;
-  const size_t sm_tile = 32 * (size_t)(c->dim | 1u) * sizeof(float) + 64;
-  int sm_warps = sm_fixed + 8 * sm_tile <= kSmemLimit ? (int)std::min<size_t>(32, (kSmemLimit - sm_fixed) / sm_tile) : 0;
-  const size_t sm_smem = sm_fixed + (size_t)sm_warps * sm_tile;
+                          kSmMaxEntries * (sizeof(uint4) + sizeof(uint2)) + kSmMaxChunks * sizeof(uint16_t);
+  const size_t sm_tile = (c->dim & 1u) ? 32 * (size_t)c->dim * sizeof(float) + 32 : 32 * ((size_t)c->dim * sizeof(float) + 16);
+  const size_t sm_warp = 304 + 2 * sm_tile;
+  int sm_warps = sm_fixed + 8 * sm_warp <= kSmemLimit ? (int)std::min<size_t>(16, (kSmemLimit - sm_fixed) / sm_warp) : 0;
+  const size_t sm_tiles = sm_fixed + (size_t)sm_warps * sm_warp;
+  const size_t lq_want = c->tc_lq <= 0 ? 0 : (c->tc_lq == 1 ? 1024 : (size_t)c->tc_lq);
+  const uint32_t sm_lq = (lq_want && sm_tiles + 16 + 64 * 8 <= kSmemLimit) ? (uint32_t)std::min<size_t>(lq_want, (kSmemLimit - sm_tiles - 16) / 8) : 0u;
+  const size_t sm_smem = sm_tiles + (sm_lq ? (size_t)sm_lq * 8 + 16 : 0);
   const bool sm_dim = c->dim == 24 || c->dim == 25 || c->dim == 32 || c->dim == 33 || c->dim == 48 || c->dim == 49;
-  const bool sm_can = !dense && !c->tc_full && sm_dim && sm_warps >= 8 && c->n_sm_items > 0 && c->n_frames < 0xffffffffull;
+  const bool sm_can = !dense && !c->tc_full && sm_dim && sm_warps >= 8 && c->n_sm_items > 0 && c->n_frames < 0xffffffffull &&
+                      c->max_uniq < 0xffffu;
   const bool use_sm = sm_can && c->tc_refine != 1;
   r.sm_items = c->d_sm_items.p; r.sm_ent_a = c->d_sm_ent_a.p; r.sm_ent_b = c->d_sm_ent_b.p;
-  r.sm_rw = sm_rw; r.sm_maxnd = sm_maxnd;
+  r.sm_rw = sm_rw; r.sm_maxnd = sm_maxnd; r.sm_lq = sm_lq;
   const bool one = ranges.size() == 1;
   sgmm_stage_begin(c, SGMM_T_SCORE_FILTER);
   uint64_t f_prev = 0, g_prev = 0;
@@ -2123,10 +2308,21 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   // every switch: a GEMM CTA needs the whole shared memory of an SM, so it waits for all refinement CTAs there)
   if (use_sm) {
     const unsigned sgrid = (unsigned)c->n_sm_items;
+    SGMM_CHECK(c, c->d_sm_ivoff.reserve(sgrid));
+    k_sm_ivoff<<<(sgrid + 255) / 256, 256, 0, c->stream>>>(c->d_sm_items.p, sgrid, c->d_state_off.p, c->d_var_of.p, c->dimP, c->d_sm_ivoff.p);
+    SGMM_LAUNCH_CHECK(c);
+    r.sm_ivoff = c->d_sm_ivoff.p;
+    bool civ = false;
+    if (refine_civ_bind(c, &civ)) return 1;
 #define SGMM_SM_CASE(D)                                                                                              \
   case D:                                                                                                            \
-    SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_smem)); \
-    k_tc_refine_sm<D><<<sgrid, 32 * sm_warps, sm_smem, c->stream>>>(r);                                                       \
+    if (civ) {                                                                                                       \
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_smem)); \
+      k_tc_refine_sm<D, true><<<sgrid, 32 * sm_warps, sm_smem, c->stream>>>(r);                                      \
+    } else {                                                                                                         \
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_smem)); \
+      k_tc_refine_sm<D, false><<<sgrid, 32 * sm_warps, sm_smem, c->stream>>>(r);                                     \
+    }                                                                                                                \
     break;
     switch (c->dim) {
       SGMM_SM_CASE(24) SGMM_SM_CASE(25) SGMM_SM_CASE(32) SGMM_SM_CASE(33) SGMM_SM_CASE(48) SGMM_SM_CASE(49)
@@ -2134,6 +2330,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     }
 #undef SGMM_SM_CASE
     SGMM_LAUNCH_CHECK(c);
+    if (civ && refine_civ_release(c)) return 1;
   } else {
     const unsigned rgrid = dense ? (unsigned)((dense_nframes + 127) / 128) : (unsigned)c->n_tasks128;
     r.tasks = dense ? nullptr : c->d_tasks128.p;

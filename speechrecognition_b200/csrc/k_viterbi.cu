@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
   if (lane == 0) {
     for (uint32_t i = 0; i < SGMM_STAGES && i < n_tiles; i++) {
       const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - i * SGMM_TILE_T);
-      const uint32_t bytes = rows * ncol * sizeof(double);
+      const uint32_t bytes = SGMM_TILE_T * ncol * sizeof(double);   // whole tiles: [column][16 frames] (sgmm_cell_rel)
       mbar_expect_tx(&bars[i], bytes);
       tma_load_1d(tiles + i * tile_elems, Eu + (size_t)i * tile_elems, bytes, &bars[i]);
     }
@@ -131,7 +131,8 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     pk[c] = p.tdp_skip;
     if (s < S) {
       validmask |= 1u << c;
-      col[c] = p.pos2uniq[a0 + s];
+      const uint32_t cj = p.pos2uniq[a0 + s];
+      col[c] = (cj << 4) | (cj & 15u);   // cell of (frame tt, column cj) inside a tile: col[c] ^ tt  (sgmm_cell_rel)
       if (sref[s] == p.silence_state) pl[c] = p.tdp_forward;
       const uint32_t src = DEST ? s : (s >= 2 ? s - 2 : 0);
       if (sref[src] == p.silence_state) pk[c] = p.tdp_forward;
@@ -147,10 +148,10 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
 
   // One frame of the recursion.  The backpointer is kept as the two raw comparison flags (bit 0 = first comparison,
   // bit 1 = second), set by predicated ORs with the frame's mask; the backtrace decodes them.
-  auto frame = [&](const double* __restrict__ row, const uint32_t m1) {
+  auto frame = [&](const double* __restrict__ tile, const uint32_t tt, const uint32_t m1) {
     double e[C];
 #pragma unroll
-    for (int c = 0; c < C; c++) e[c] = row[col[c]];
+    for (int c = 0; c < C; c++) e[c] = tile[col[c] ^ tt];
     // the two costs that cross the lane boundary (positions s-1 and s-2 of this lane's first position)
     const double Q1 = __shfl_up_sync(0xffffffffu, q[C - 1], 1);
     const double Q2 = __shfl_up_sync(0xffffffffu, q[C - 2], 1);
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     if (ti > 0 && rows == SGMM_TILE_T) {
       // full tile: unrolled, the frame masks are immediates
 #pragma unroll(C <= 4 ? 16 : (C <= 8 ? 4 : 2))
-      for (int tt = 0; tt < SGMM_TILE_T; tt++) frame(tile + (uint32_t)tt * ncol, 1u << (2 * tt));
+      for (int tt = 0; tt < SGMM_TILE_T; tt++) frame(tile, (uint32_t)tt, 1u << (2 * tt));
     } else {
       uint32_t tt = 0;
       if (ti == 0) {
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
         tt = 1;
       }
 #pragma unroll 1
-      for (; tt < rows; tt++) frame(tile + tt * ncol, 1u << (2 * tt));
+      for (; tt < rows; tt++) frame(tile, tt, 1u << (2 * tt));
     }
 #pragma unroll
     for (int c = 0; c < C; c++) { bpw[(size_t)ti * 32 * C + c * 32 + lane] = w[c]; w[c] = 0; }
@@ -229,7 +230,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     const uint32_t nxt = ti + SGMM_STAGES;
     if (lane == 0 && nxt < n_tiles) {
       const uint32_t nrows = min((uint32_t)SGMM_TILE_T, T - nxt * SGMM_TILE_T);
-      const uint32_t bytes = nrows * ncol * sizeof(double);
+      const uint32_t bytes = SGMM_TILE_T * ncol * sizeof(double);
       mbar_expect_tx(&bars[slot], bytes);
       tma_load_1d(tiles + slot * tile_elems, Eu + (size_t)nxt * tile_elems, bytes, &bars[slot]);
     }
@@ -317,7 +318,7 @@ __global__ void __launch_bounds__(32 * kVitW) k_viterbi_mw(VitParams p) {
   if (g == 0) {
     for (uint32_t i = 0; i < SGMM_STAGES && i < n_tiles; i++) {
       const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - i * SGMM_TILE_T);
-      const uint32_t bytes = rows * ncol * sizeof(double);
+      const uint32_t bytes = SGMM_TILE_T * ncol * sizeof(double);   // whole tiles: [column][16 frames] (sgmm_cell_rel)
       mbar_expect_tx(&bars[i], bytes);
       tma_load_1d(tiles + i * tile_elems, Eu + (size_t)i * tile_elems, bytes, &bars[i]);
     }
@@ -333,7 +334,7 @@ __global__ void __launch_bounds__(32 * kVitW) k_viterbi_mw(VitParams p) {
     pl[c] = p.tdp_loop; pk[c] = p.tdp_skip;
     if (s < S) {
       validmask |= 1u << c;
-      col[c] = scol[s];
+      col[c] = ((uint32_t)scol[s] << 4) | (scol[s] & 15u);   // cell inside a tile: col[c] ^ tt  (sgmm_cell_rel)
       if (sref[s] == p.silence_state) pl[c] = p.tdp_forward;
       const uint32_t src = DEST ? s : (s >= 2 ? s - 2 : 0);
       if (sref[src] == p.silence_state) pk[c] = p.tdp_forward;
@@ -351,10 +352,9 @@ __global__ void __launch_bounds__(32 * kVitW) k_viterbi_mw(VitParams p) {
     const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - t0);
     for (uint32_t tt = 0; tt < rows; tt++) {
       const uint32_t t = t0 + tt;
-      const double* row = tile + tt * ncol;
       double e[C];
 #pragma unroll
-      for (int c = 0; c < C; c++) e[c] = row[col[c]];
+      for (int c = 0; c < C; c++) e[c] = tile[col[c] ^ tt];
       double* xw = xq + ((t & 1) * kVitW + warp) * 4;
       if (t == 0) {
 #pragma unroll
@@ -432,7 +432,7 @@ __global__ void __launch_bounds__(32 * kVitW) k_viterbi_mw(VitParams p) {
     const uint32_t nxt = ti + SGMM_STAGES;
     if (g == 0 && nxt < n_tiles) {
       const uint32_t nrows = min((uint32_t)SGMM_TILE_T, T - nxt * SGMM_TILE_T);
-      const uint32_t bytes = nrows * ncol * sizeof(double);
+      const uint32_t bytes = SGMM_TILE_T * ncol * sizeof(double);
       mbar_expect_tx(&bars[slot], bytes);
       tma_load_1d(tiles + slot * tile_elems, Eu + (size_t)nxt * tile_elems, bytes, &bars[slot]);
     }

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <atomic>
 #include <map>
 #include <string>
 
@@ -63,6 +64,7 @@ int sgmm_create(int device, sgmm_ctx** out) {
   }
   sgmm_ctx* c = new sgmm_ctx();
   c->device = device;
+  { static std::atomic<uint64_t> next_serial{1}; c->serial = next_serial.fetch_add(1); }
   if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
     g_create_error = "cudaStreamCreate failed";
     delete c;
@@ -91,7 +93,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_fallbacks.release(); c->d_Amin.release(); c->d_fcol.release(); c->d_Ahi.release(); c->d_Alo.release();
   c->d_xnorm.release(); c->d_ci1.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
-  c->d_sm_items.release(); c->d_sm_ent_a.release(); c->d_sm_ent_b.release();
+  c->d_sm_items.release(); c->d_sm_ent_a.release(); c->d_sm_ent_b.release(); c->d_sm_ivoff.release();
   c->d_pack_desc.release(); c->d_pack_uniq.release(); c->d_pack_rows.release(); c->d_pack_colmap.release();
   for (int i = 0; i < 2; i++) { c->d_keys[i].release(); c->d_vals[i].release(); }
   c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release(); c->d_soft_keys.release();
@@ -194,7 +196,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     uniq_off[u + 1] = (uint32_t)uniq.size();
     ncol[u] = ((uint32_t)us.size() + 1u) & ~1u;
     max_uniq = std::max(max_uniq, (uint32_t)us.size());
-    E_off[u + 1] = E_off[u] + (uint64_t)T * ncol[u];
+    E_off[u + 1] = E_off[u] + sgmm_cells_of(T, ncol[u]);   // whole 16-frame tiles (sgmm_cell_rel)
     for (uint32_t t0 = 0; t0 < T; t0 += 32) tasks.push_back(make_uint4(u, t0, 0, 0));
     for (uint32_t t0 = 0; t0 < T; t0 += 64) tasks64.push_back(make_uint4(u, t0, 0, 0));
     for (uint32_t t0 = 0; t0 < T; t0 += 128) {
@@ -262,7 +264,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
             pack_colmap.push_back((it != ub + nu_u && *it == s) ? (uint16_t)(it - ub) : (uint16_t)0xFFFF);
           }
           for (uint32_t i = 0; i < sg.rows; i++, r++) {
-            rows[r].cell = E_off[sg.u] + (uint64_t)(sg.t0 + i) * ncol[sg.u];
+            rows[r].cell = E_off[sg.u] + (uint64_t)((sg.t0 + i) >> 4) * (16u * ncol[sg.u]) + ((sg.t0 + i) & 15u);
             rows[r].frame = (uint32_t)(frame_off[sg.u] + sg.t0 + i);
             rows[r].colmap = cm;
           }
@@ -308,15 +310,16 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
         }
       std::sort(touched.begin(), touched.end());
       for (uint32_t s : touched) {
-        uint32_t cells = 0;
+        uint32_t chunks = 0;
         const uint32_t first = (uint32_t)sm_ent_a.size();
         for (auto& uc : by_state[s]) {
-          const uint64_t cell0 = E_off[uc.first] + uc.second, f0 = frame_off[uc.first];
-          sm_ent_a.push_back(make_uint4((uint32_t)cell0, (uint32_t)(cell0 >> 32), ncol[uc.first], cells));
-          sm_ent_b.push_back(make_uint2((uint32_t)f0, (uint32_t)(f0 >> 32)));
-          cells += (uint32_t)(frame_off[uc.first + 1] - f0);
+          const uint64_t e0 = E_off[uc.first], f0 = frame_off[uc.first];
+          const uint32_t T = (uint32_t)(frame_off[uc.first + 1] - f0);
+          sm_ent_a.push_back(make_uint4((uint32_t)e0, (uint32_t)(e0 >> 32), ncol[uc.first] | (uc.second << 16), chunks));
+          sm_ent_b.push_back(make_uint2((uint32_t)f0, T));
+          chunks += (T + 31u) / 32u;
         }
-        sm_items.push_back(make_uint4(s, first, (uint32_t)by_state[s].size(), cells));
+        sm_items.push_back(make_uint4(s, first, (uint32_t)by_state[s].size(), chunks));
         by_state[s].clear();
       }
       u0 = u1;
@@ -473,6 +476,8 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   }
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
+  if (!strcmp(key, "tc_civ")) { c->tc_civ = value != 0; return 0; }
+  if (!strcmp(key, "tc_lq")) { c->tc_lq = (int)value; return 0; }   // 0 none, 1 default size, n > 1 entries
   if (!strcmp(key, "host_tables")) { c->host_tables = value != 0; return 0; }   // read by sgmm_set_model
   if (!strcmp(key, "allreduce")) { c->allreduce = value != 0; return 0; }   // 0: sgmm_accumulate* return this rank's partial sums
   if (!strcmp(key, "tc_pack")) { c->tc_pack = value != 0; return 0; }   // takes effect at the next sgmm_set_corpus

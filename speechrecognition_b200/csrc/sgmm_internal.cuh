@@ -13,6 +13,22 @@
 #define SGMM_STAGES 3       // Viterbi: emission tiles in flight (cp.async.bulk ring)
 #define SGMM_VIT_MW_WARPS 4        // k_viterbi_mw: warps per utterance
 #define SGMM_VIT_MW_MIN_FRAMES 1000  // utterances at least this long take the multi-warp Viterbi kernel
+// ---- layout of the gathered (ragged) emission matrix, shared by the GEMM verdicts (d_ci1) and the argmin array (d_Amin):
+// utterance u holds ceil(T_u / 16) tiles of [column][16 frames]; inside a column's 16-frame run (128 B of doubles, one
+// full line) frame t sits at (t ^ column) & 15:
+//     cell(u, t, j) = E_off[u] + (t >> 4) * 16 * ncol_u + j * 16 + ((t ^ j) & 15)
+//   * a warp whose lanes are 32 consecutive frames of one column (GEMM epilogue: lane = TMEM row; refinement: lane = frame)
+//     touches two full lines, instead of 32 sectors in the frame-major [T][ncol] form;
+//   * a Viterbi tile (16 frames, all columns) is still ONE contiguous run of 16 * ncol doubles = one bulk copy, and the
+//     xor spreads a frame's columns over the 16 eight-byte bank pairs exactly as the row-major tile did.
+// Frames T_u .. of the last tile are padding: never written, never read by the recursion.
+#define SGMM_E_TILE 16
+__host__ __device__ __forceinline__ uint64_t sgmm_cell_rel(uint32_t ncol, uint32_t t, uint32_t j) {
+  return (uint64_t)(t >> 4) * (16u * ncol) + (j << 4) + ((t ^ j) & 15u);
+}
+__host__ __device__ __forceinline__ uint64_t sgmm_cells_of(uint32_t T, uint32_t ncol) {
+  return (uint64_t)((T + 15u) >> 4) * 16u * ncol;
+}
 #define SGMM_SORT_CHUNK 2048  // radix sort: keys per warp-chunk
 #define SGMM_RED_BLOCK 256    // segmented reduce: frames per partial
 
@@ -32,13 +48,14 @@ struct DevBuf {
   void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
-// state-major refinement: a block of utterances holds at most this many utterances / frames (an item's cells are
-// <= kSmBlockFrames, i.e. <= kSmBlockFrames / 32 warp chunks)
+// state-major refinement: a block of utterances holds at most this many utterances / frames; an item's chunks (32
+// consecutive frames of ONE utterance, the last chunk of an utterance may be short) are therefore at most kSmMaxChunks
 constexpr uint32_t kSmMaxEntries = 256;
 constexpr uint32_t kSmBlockFrames = 65536;
+constexpr uint32_t kSmMaxChunks = kSmBlockFrames / 32 + kSmMaxEntries;
 
 struct sgmm_pack_row {   // one row of a packed GEMM task (sgmm_set_corpus)
-  uint64_t cell;     // first emission cell of this frame's row in the ragged emission matrix
+  uint64_t cell;     // first cell of this frame's 16-frame tile in the ragged emission matrix + (t & 15)  (sgmm_cell_rel)
   uint32_t frame;    // absolute frame index
   uint32_t colmap;   // first entry of this row's segment in the column map (union column -> own column, 0xFFFF: none)
 };
@@ -178,6 +195,8 @@ struct sgmm_ctx : SgmmModel {
   // state-major refinement (k_tc_refine_sm): work items (block of utterances, state) and, per item, the
   // utterances of the block that visit the state
   int tc_refine = 0;               // option "tc_refine": 0 automatic, 1 frame-major kernel, 2 state-major kernel
+  int tc_civ = 1;                  // option "tc_civ": state-major refinement reads the inverse variances from the constant bank (0: shared memory)
+  int tc_lq = 1;                   // option "tc_lq": state-major refinement queues an item's near-ties as one run (0: cell by cell)
   int tc_rem = 1;                  // option "tc_rem" (read by sgmm_set_model): pack the K remainder of the fp16 form
   int tc_f16 = -1;                 // option "tc_f16": -1 / 1 use the fp16 operand form when available, 0 never
   uint64_t tc_A_key = 0;           // shape / form the resident A rows were prepared for
@@ -185,9 +204,10 @@ struct sgmm_ctx : SgmmModel {
   int tc_epi16 = 0;                // option "tc_epi16": sixteen epilogue warps per GEMM unit (k_tc_gemm256<.., E16>)
   int tc_rescan = 0;               // option "tc_rescan": 0 two-stage (f32 prefilter, f64 candidates), 1 full f64 scan
   size_t n_sm_items = 0;
-  DevBuf<uint4> d_sm_items;        // {state, first entry, entries, cells}
-  DevBuf<uint4> d_sm_ent_a;        // {first cell lo, hi (E_off[u] + column), cells per frame (ncol), cells before}
-  DevBuf<uint2> d_sm_ent_b;        // {first frame lo, hi}
+  DevBuf<uint4> d_sm_items;        // {state, first entry, entries, chunks}
+  DevBuf<uint4> d_sm_ent_a;        // {E_off[u] lo, hi, ncol | column << 16, chunks before}
+  DevBuf<uint2> d_sm_ent_b;        // {first frame (< 2^32: the launcher checks), frames}
+  DevBuf<uint32_t> d_sm_ivoff;     // per item: offset of its state's inverse-variance row (k_sm_ivoff, every refinement launch)
   DevBuf<uint4> d_pack_desc;
   DevBuf<uint32_t> d_pack_uniq;
   DevBuf<sgmm_pack_row> d_pack_rows;
@@ -196,10 +216,11 @@ struct sgmm_ctx : SgmmModel {
   int tc_halves = 0;               // option "tc_halves": 0 auto, 1 / 2 = frame halves (128 rows each) per GEMM CTA
   DevBuf<uint4> d_tasks, d_tasks64;   // emission warp-tasks {utt, t0, 0, 0}: 32-frame and 64-frame granules
   uint64_t n_tasks = 0, n_tasks64 = 0, E_elems = 0;
-  DevBuf<double> d_E;             // ragged emission matrix, utterance u: [T_u][nuniq_pad_u]
+  DevBuf<double> d_E;             // ragged emission matrix, utterance u: [ceil(T_u / 16)][nuniq_pad_u][16] (sgmm_cell_rel)
   DevBuf<uint16_t> d_Amin;        // argmin density of every emission cell (same indexing as d_E)
   DevBuf<uint16_t> d_fcol;        // per frame: emission column of the aligned position (written by the backtrace)
   uint64_t model_version = 1, E_model_version = 0;
+  uint64_t serial = 0;            // unique per context of this process (sgmm_create): keys caches that outlive a context
   bool use_cache = true;          // option "rescore_cache"
   bool max_approx = true;         // option "max_approx": score() = min_score (1) or sum_score (0), Mixtures.cpp:737-744
   bool E_max_approx = true;       // which of the two the resident emission matrix holds
