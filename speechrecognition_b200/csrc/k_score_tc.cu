@@ -1347,30 +1347,15 @@ struct RefineParams {
   const float4* sguard;
 };
 
-// cell -> (frame, state); returns false for the padding column of a gathered row
-__device__ __forceinline__ bool decode_cell(const RefineParams& p, uint64_t e, uint64_t& frame, uint32_t& s) {
-  if (p.dense) {
-    frame = p.f0 + e / p.n_states;
-    s = (uint32_t)(e % p.n_states);
-    return true;
-  }
-  uint32_t lo = 0, hi = p.n_utts;          // largest u with E_off[u] <= e
-  while (hi - lo > 1) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (p.E_off[mid] <= e) lo = mid; else hi = mid;
-  }
-  // inverse of sgmm_cell_rel
-  const uint64_t local = e - p.E_off[lo];
-  const uint32_t ncol = p.nuniq_pad[lo];
-  const uint64_t tile = local / (16u * ncol);
-  const uint32_t rem = (uint32_t)(local - tile * 16u * ncol);
-  const uint32_t j = rem >> 4;
-  const uint64_t t = tile * 16u + ((rem ^ j) & 15u);
-  const uint32_t nu = p.uniq_off[lo + 1] - p.uniq_off[lo];
-  if (j >= nu || t >= p.frame_off[lo + 1] - p.frame_off[lo]) return false;   // padding column / padding frames
-  frame = p.frame_off[lo] + t;
-  s = p.uniq[p.uniq_off[lo] + j];
-  return true;
+// The near-tie queue: rescan[0] = entries, then 16 bytes per entry {cell, frame | state << 40}.  The producer knows the
+// cell's frame and state; carrying them spares the rescan a 12-step binary search over E_off per cell (dependent global
+// loads: most of that kernel's time, measured).
+__device__ __forceinline__ void rq_put(unsigned long long* q, unsigned long long slot, uint64_t cell, uint64_t frame, uint32_t s) {
+  *reinterpret_cast<ulonglong2*>(q + 2 + 2 * slot) = make_ulonglong2(cell, frame | ((unsigned long long)s << 40));
+}
+__device__ __forceinline__ void rq_get(const unsigned long long* q, unsigned long long slot, uint64_t& cell, uint64_t& frame, uint32_t& s) {
+  const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(q + 2 + 2 * slot);
+  cell = v.x; frame = v.y & 0xffffffffffull; s = (uint32_t)(v.y >> 40);
 }
 
 // exact score from the row-major tables with NP dimension pairs known at compile time: every load of the mean
@@ -1486,7 +1471,7 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
         if (sc < best) { best = sc; bk = i1; }
       } else {
         const unsigned long long slot = atomicAdd(p.rescan, 1ull);
-        if (slot < p.cap) { p.rescan[1 + slot] = e; continue; }
+        if (slot < p.cap) { rq_put(p.rescan, slot, e, frame, s); continue; }
         const float* xf = p.x + frame * p.m.dim;   // list full: rescan here
         for (uint32_t k = k0; k < k1; k++) {
           const double sc = sgmm_exact_score(p.m, xf, k);
@@ -1620,8 +1605,8 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
   unsigned char* tiles = tail + 304 * nwarp + (size_t)warp * 2 * kTileB; // [nwarp][2][kTileB]
   // near-ties of the item: collected here and appended to the global queue as ONE run at the end, so that the rescan
   // kernel finds the cells of a state next to each other (it keeps a state's f32 tables in L1 across a run)
-  unsigned long long* lq = reinterpret_cast<unsigned long long*>(tail + 304 * nwarp + (size_t)nwarp * 2 * kTileB);   // [sm_lq]
-  uint32_t* lq_n = reinterpret_cast<uint32_t*>(lq + p.sm_lq);            // {entries, -, first slot of the run lo, hi}
+  unsigned long long* lq = reinterpret_cast<unsigned long long*>(tail + 304 * nwarp + (size_t)nwarp * 2 * kTileB);   // [sm_lq] {cell, frame}
+  uint32_t* lq_n = reinterpret_cast<uint32_t*>(lq + 2 * p.sm_lq);            // {entries, -, first slot of the run lo, hi}
   uint32_t n_rescans = 0;
   if (threadIdx.x == 0) lq_n[0] = 0u;
 
@@ -1749,10 +1734,10 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
         const uint32_t ls = p.sm_lq ? atomicAdd(lq_n, 1u) : 0xffffffffu;
         unsigned long long slot = 0ull;
         if (ls < p.sm_lq) {
-          lq[ls] = my_cell;
+          lq[2 * ls] = my_cell; lq[2 * ls + 1] = cur.f0 + src;
           queued = true;
         } else if ((slot = atomicAdd(p.rescan, 1ull)) < p.cap) {   // local list full: straight to the global queue
-          p.rescan[1 + slot] = my_cell;
+          rq_put(p.rescan, slot, my_cell, cur.f0 + src, s);
           queued = true;
         } else {                                     // both lists full: rescan here
           double rb;
@@ -1779,12 +1764,9 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     __syncthreads();
     const unsigned long long base = ((unsigned long long)lq_n[3] << 32) | lq_n[2];
     for (uint32_t i = threadIdx.x; i < nq; i += nthr) {
-      const unsigned long long cell = lq[i];
-      if (base + i < p.cap) { p.rescan[1 + base + i] = cell; continue; }
+      const unsigned long long cell = lq[2 * i], frame = lq[2 * i + 1];
+      if (base + i < p.cap) { rq_put(p.rescan, base + i, cell, frame, s); continue; }
       // the global queue is full: rescan here, from the features in global memory
-      uint64_t frame;
-      uint32_t st;
-      decode_cell(p, cell, frame, st);
       double rb;
       uint32_t rk;
       sm_rescan<DIM, !kOdd>(tbl, lw, p.x + frame * dim, iv, nd, RW, 0u, 1u, rb, rk);
@@ -1799,13 +1781,13 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
 // one warp per queued near-tie cell: exact f64 rescan of the whole state, first minimum wins
 __global__ void __launch_bounds__(256) k_tc_rescan(RefineParams p) {
   const uint32_t lane = threadIdx.x & 31;
+  uint32_t n_done = 0;   // cells this warp finished: ONE atomic per warp at the end (same-address atomics serialise)
   const uint64_t nwarps = (uint64_t)gridDim.x * (blockDim.x >> 5);
   const unsigned long long count = min(p.rescan[0], p.cap);
   for (uint64_t i = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); i < count; i += nwarps) {
-    const uint64_t e = p.rescan[1 + i];
-    uint64_t frame;
+    uint64_t e, frame;
     uint32_t s;
-    decode_cell(p, e, frame, s);
+    rq_get(p.rescan, i, e, frame, s);
     const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
     const float* xf = p.x + frame * p.m.dim;
     double best = 1e10;
@@ -1824,9 +1806,10 @@ __global__ void __launch_bounds__(256) k_tc_rescan(RefineParams p) {
       p.out[e] = best;
       if (p.argmin) p.argmin[e] = bk == 0xffffffffu ? 0 : bk;
       if (p.amin16) p.amin16[e] = bk == 0xffffffffu ? 0 : (uint16_t)bk;
-      if (p.fallback_count) atomicAdd(p.fallback_count, 1ull);
+      n_done++;
     }
   }
+  if (lane == 0 && n_done && p.fallback_count) atomicAdd(p.fallback_count, (unsigned long long)n_done);
 }
 
 // Two-stage rescan of the queued near-tie cells, one warp per cell.  Stage 1 scores every density of the state in
@@ -1839,6 +1822,7 @@ __global__ void __launch_bounds__(256) k_tc_rescan(RefineParams p) {
 template <int DV4>
 __global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
   const uint32_t lane = threadIdx.x & 31;
+  uint32_t n_done = 0;   // cells this warp finished: ONE atomic per warp at the end (same-address atomics serialise)
   const unsigned long long count = min(p.rescan[0], p.cap);
   const float eps = 2.384185791015625e-07f;   // 2^-22, as k_emission_ffma
   const float dterm = (float)(p.m.dim + 8);
@@ -1849,10 +1833,9 @@ __global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
   const uint64_t wpb = blockDim.x >> 5;
   for (uint64_t i0 = (uint64_t)blockIdx.x * kRun; i0 < count; i0 += (uint64_t)gridDim.x * kRun)
   for (uint64_t i = i0 + (threadIdx.x >> 5); i < min((uint64_t)count, i0 + kRun); i += wpb) {
-    const uint64_t e = p.rescan[1 + i];
-    uint64_t frame;
+    uint64_t e, frame;
     uint32_t s;
-    decode_cell(p, e, frame, s);
+    rq_get(p.rescan, i, e, frame, s);
     const uint32_t k0 = p.state_off[s], k1 = p.state_off[s + 1];
     const float* xf = p.x + frame * p.m.dim;
     float xr[4 * DV4];
@@ -1888,19 +1871,44 @@ __global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
     for (int o = 16; o > 0; o >>= 1) m32 = fminf(m32, __shfl_xor_sync(0xffffffffu, m32, o));
     double best = 1e10;
     uint32_t bk = 0xffffffffu;
-    auto stage2 = [&](uint32_t k, float sc) {
+    // stage 2, per group of 8 rounds (256 densities): ballot the densities the f32 bound cannot exclude, hand the i-th of
+    // them to lane i and evaluate all of a group's survivors in ONE divergent pass from the row-major f64 tables
+    // (sgmm_exact_score_rm: the reference's operation order).  Evaluating them where they fell — lane by lane, round by
+    // round — was eight divergent single-lane passes per cell: ~30 % of the kernel's issued instructions.
+    auto keep_test = [&](uint32_t k, float sc) {
+      if (k >= k1) return false;
       const float dist = fmaxf(sc - g.x, 0.f);
       const float guard = 2.f * eps * (dterm * dist + 2.f * sqrtf(dist * g.z) + g.y);
-      if ((sc - m32) > guard) return;           // certainly not the minimum (false for NaN: those are evaluated)
-      const double sd = sgmm_exact_score(p.m, xf, k);
-      if (sd < best) { best = sd; bk = k - k0; }
+      return !((sc - m32) > guard);             // NaN scores are kept
     };
+    for (uint32_t gbase = k0; gbase < k1; gbase += 32 * kKeep) {
+      uint32_t masks[kKeep];
+      uint32_t total = 0;
 #pragma unroll
-    for (int j = 0; j < kKeep; j++) {
-      const uint32_t k = k0 + lane + 32 * j;
-      if (k < k1) stage2(k, keep[j]);
+      for (int j = 0; j < kKeep; j++) {
+        const uint32_t k = gbase + 32 * j + lane;
+        bool take = false;
+        if (gbase + 32 * j < k1) take = keep_test(k, gbase == k0 ? keep[j] : (k < k1 ? score32(k) : INFINITY));
+        masks[j] = __ballot_sync(0xffffffffu, take);
+        total += __popc(masks[j]);
+      }
+      for (uint32_t done = 0; done < total; done += 32) {
+        uint32_t want = done + lane, mine = 0xffffffffu;   // the (done + lane)-th surviving density of the group
+        bool found = false;
+#pragma unroll
+        for (int j = 0; j < kKeep; j++) {
+          const uint32_t cnt = __popc(masks[j]);
+          if (!found) {
+            if (want < cnt) { mine = gbase + 32 * j + __fns(masks[j], 0, want + 1); found = true; }
+            else want -= cnt;
+          }
+        }
+        if (mine != 0xffffffffu) {
+          const double sd = sgmm_exact_score_rm(p.m, xf, mine);
+          if (sd < best || (sd == best && mine - k0 < bk)) { best = sd; bk = mine - k0; }   // first minimum wins
+        }
+      }
     }
-    for (uint32_t k = k0 + lane + 32 * kKeep; k < k1; k += 32) stage2(k, score32(k));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const double ob = __shfl_xor_sync(0xffffffffu, best, o);
@@ -1911,9 +1919,10 @@ __global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
       p.out[e] = best;
       if (p.argmin) p.argmin[e] = bk == 0xffffffffu ? 0 : bk;
       if (p.amin16) p.amin16[e] = bk == 0xffffffffu ? 0 : (uint16_t)bk;
-      if (p.fallback_count) atomicAdd(p.fallback_count, 1ull);
+      n_done++;
     }
   }
+  if (lane == 0 && n_done && p.fallback_count) atomicAdd(p.fallback_count, (unsigned long long)n_done);
 }
 
 // ---- sum scores with an f32 pruner (option max_approx = 0) ---------------------------------------------
@@ -2173,7 +2182,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   if (n_tasks == 0) return 0;
   SGMM_CHECK(c, c->d_ci1.reserve(n_cells));
   const size_t cap = (size_t)std::max<uint64_t>(1024, n_cells / 8);
-  SGMM_CHECK(c, c->d_rescan.reserve(cap + 1));
+  SGMM_CHECK(c, c->d_rescan.reserve(2 * cap + 2));   // [0] entries, [1] -, then {cell, frame | state << 40} per entry
   c->rescan_cap = cap;
   SGMM_CHECK(c, cudaMemsetAsync(c->d_rescan.p, 0, sizeof(unsigned long long), c->stream));
 
@@ -2231,8 +2240,8 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   int sm_warps = sm_fixed + 8 * sm_warp <= kSmemLimit ? (int)std::min<size_t>(16, (kSmemLimit - sm_fixed) / sm_warp) : 0;
   const size_t sm_tiles = sm_fixed + (size_t)sm_warps * sm_warp;
   const size_t lq_want = c->tc_lq <= 0 ? 0 : (c->tc_lq == 1 ? 1024 : (size_t)c->tc_lq);
-  const uint32_t sm_lq = (lq_want && sm_tiles + 16 + 64 * 8 <= kSmemLimit) ? (uint32_t)std::min<size_t>(lq_want, (kSmemLimit - sm_tiles - 16) / 8) : 0u;
-  const size_t sm_smem = sm_tiles + (sm_lq ? (size_t)sm_lq * 8 + 16 : 0);
+  const uint32_t sm_lq = (lq_want && sm_tiles + 16 + 64 * 16 <= kSmemLimit) ? (uint32_t)std::min<size_t>(lq_want, (kSmemLimit - sm_tiles - 16) / 16) : 0u;
+  const size_t sm_smem = sm_tiles + (sm_lq ? (size_t)sm_lq * 16 + 16 : 0);
   const bool sm_dim = c->dim == 24 || c->dim == 25 || c->dim == 32 || c->dim == 33 || c->dim == 48 || c->dim == 49;
   const bool sm_can = !dense && !c->tc_full && sm_dim && sm_warps >= 8 && c->n_sm_items > 0 && c->n_frames < 0xffffffffull &&
                       c->max_uniq < 0xffffu;
@@ -2349,7 +2358,8 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     SGMM_LAUNCH_CHECK(c);
   }
   r.mu32T = c->d_mu32T.p; r.h32 = c->d_h32.p; r.c32 = c->d_c32.p; r.sguard = c->d_sguard.p;
-  switch ((c->tc_rescan == 1 || c->tc_full) ? 0u : c->dv4) {   // option tc_rescan 1: the plain full-f64 rescan (same results)
+  // option tc_rescan 1: the plain full-f64 rescan (same results)
+  switch ((c->tc_rescan == 1 || c->tc_full) ? 0u : c->dv4) {
     case 7: k_tc_rescan2<7><<<148 * 16, 256, 0, c->stream>>>(r); break;
     case 9: k_tc_rescan2<9><<<148 * 16, 256, 0, c->stream>>>(r); break;
     case 12: k_tc_rescan2<12><<<148 * 16, 256, 0, c->stream>>>(r); break;
