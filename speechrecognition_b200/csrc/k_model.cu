@@ -354,7 +354,9 @@ __global__ void __launch_bounds__(128) k_model_f16(BuildParams p) {
     // a flushed / rounded B entry b_i errs by fl_i |a_i| <= fl_i ||a||: fold max_i fl_i * sqrt(d) / (2 eps) into the norm
     const double gn = __dadd_rn(Gmax, __dmul_rn(__dmul_rn(flg, __dsqrt_rn((double)p.dim)), p.inv2eps16));
     const double cn = __dadd_rn(cabs, __dmul_rn(flc, p.inv2eps16));
-    p.sguard16[s] = make_float4(__double2float_rn(__dmul_rn(gn, 1.0001)), __double2float_rn(__dmul_rn(cn, 1.0001)), 0.f, 0.f);
+    // .w: 1 / t_s (a power of two) — un-scales an accumulator value into a score in the tolerance mode's epilogue
+    p.sguard16[s] = make_float4(__double2float_rn(__dmul_rn(gn, 1.0001)), __double2float_rn(__dmul_rn(cn, 1.0001)), 0.f,
+                                __double2float_rn(__ddiv_rn(1.0, ts)));
   }
 }
 
@@ -571,7 +573,7 @@ int model_build_host(sgmm_ctx* c, SgmmModel& m, const double* mean, const double
       }
       // a flushed / rounded B entry b_i errs by fl_i |a_i| <= fl_i ||a||: fold max_i fl_i * sqrt(d) / (2 eps) into the norm
       sg[s] = make_float4((float)((Gmax + flg * std::sqrt((double)dim) * inv2eps) * 1.0001),
-                          (float)((cabs + flc * inv2eps) * 1.0001), 0.f, 0.f);
+                          (float)((cabs + flc * inv2eps) * 1.0001), 0.f, (float)(1.0 / ts));
       tile += (nc + TR - 1) / TR;
     }
     if (finite) {

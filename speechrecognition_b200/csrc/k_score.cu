@@ -295,6 +295,69 @@ __global__ void __launch_bounds__(256) k_rescore_cached(CachedParams p) {
   atomicAdd(p.cnt + gid, 1u);
 }
 
+// K3 of the tolerance mode (option "tolerance"): the alignment came from f32 scores, but the tensor filter's VERDICTS of
+// that pass are still in place — for every (frame, state) cell the certified f64 argmin, or "uncertain".  One thread
+// per frame looks its aligned cell up: a certified winner is evaluated in f64 (the reference's operation order, one
+// density); an uncertain cell (0.25 %) is scanned by the whole warp, lanes = densities, first minimum wins.  The E-step
+// therefore sees the exact min_score / argmin of Mixtures.cpp:296-298 for the alignment it is given.
+struct VerdictParams {
+  CachedParams c;
+  const uint32_t* cand;
+  const float* x;
+  ExactTables m;
+};
+
+__global__ void __launch_bounds__(256) k_rescore_verdict(VerdictParams p) {
+  const uint64_t f = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t lane = threadIdx.x & 31;
+  const bool valid = f < p.c.n_frames;
+  uint32_t k0 = 0, k1 = 0, v = 0;
+  if (valid) {
+    uint32_t lo = 0, hi = p.c.n_utts;            // utterance of frame f: largest u with frame_off[u] <= f
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (p.c.frame_off[mid] <= f) lo = mid; else hi = mid;
+    }
+    const uint64_t e = p.c.E_off[lo] + sgmm_cell_rel(p.c.nuniq_pad[lo], (uint32_t)(f - p.c.frame_off[lo]), p.c.fcol[f]);
+    const uint32_t s = p.c.ali[f].state;
+    k0 = p.c.state_off[s]; k1 = p.c.state_off[s + 1];
+    v = p.cand[e];
+  }
+  const bool unc = valid && k1 > k0 && !(v < k1 - k0);
+  double best = 1e10;                            // min_score's start value, Mixtures.cpp:699
+  uint32_t bk = 0;
+  if (valid && k1 > k0 && !unc) {
+    const double sc = sgmm_exact_score_rm(p.m, p.x + f * p.m.dim, k0 + v);
+    if (sc < best) { best = sc; bk = v; }
+  }
+  uint32_t todo = __ballot_sync(0xffffffffu, unc);
+  while (todo) {
+    const int src = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const uint64_t fs = __shfl_sync(0xffffffffu, f, src);
+    const uint32_t a0 = __shfl_sync(0xffffffffu, k0, src), a1 = __shfl_sync(0xffffffffu, k1, src);
+    double rb = 1e10;
+    uint32_t rk = 0xffffffffu;
+    for (uint32_t k = a0 + lane; k < a1; k += 32) {
+      const double sc = sgmm_exact_score_rm(p.m, p.x + fs * p.m.dim, k);
+      if (sc < rb) { rb = sc; rk = k - a0; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ob = __shfl_xor_sync(0xffffffffu, rb, o);
+      const uint32_t ok = __shfl_xor_sync(0xffffffffu, rk, o);
+      if (ob < rb || (ob == rb && ok < rk)) { rb = ob; rk = ok; }
+    }
+    if ((int)lane == src) { best = rb; bk = rk == 0xffffffffu ? 0u : rk; }
+  }
+  if (valid) {
+    const uint32_t gid = (k1 > k0) ? k0 + bk : p.c.Dtot;
+    p.c.fdens[f] = gid;
+    p.c.fscore[f] = best;
+    atomicAdd(p.c.cnt + gid, 1u);
+  }
+}
+
 ModelView model_view(const sgmm_ctx* c) {
   ModelView m;
   m.meanT = c->d_meanT.p; m.invT = c->d_invT.p; m.mean_tail = c->d_mean_tail.p; m.inv_tail = c->d_inv_tail.p;
@@ -350,6 +413,22 @@ int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass) {
   const uint64_t warps = (c->n_frames + 31) / 32;
   const uint64_t grid = (warps + kRescoreWarps - 1) / kRescoreWarps;
   k_rescore_f64<<<(unsigned)grid, kRescoreWarps * 32, smem, c->stream>>>(p);
+  SGMM_LAUNCH_CHECK(c);
+  return 0;
+}
+
+int sgmm_launch_rescore_verdict(sgmm_ctx* c) {
+  if (c->n_frames == 0) return 0;
+  VerdictParams p{};
+  p.c.ali = c->d_ali.p; p.c.fcol = c->d_fcol.p;
+  p.c.frame_off = c->d_frame_off.p; p.c.E_off = c->d_E_off.p; p.c.nuniq_pad = c->d_nuniq_pad.p;
+  p.c.state_off = c->d_state_off.p; p.c.n_utts = c->n_utts; p.c.Dtot = c->Dtot; p.c.n_frames = c->n_frames;
+  p.c.fdens = c->d_fdens.p; p.c.fscore = c->d_fscore.p; p.c.cnt = c->d_cnt_u32.p;
+  p.cand = c->d_ci1.p; p.x = c->d_x.p;
+  p.m.meanT = c->d_meanT.p; p.m.invT = c->d_invT.p; p.m.mean_tail = c->d_mean_tail.p; p.m.inv_tail = c->d_inv_tail.p;
+  p.m.norm = c->d_norm.p; p.m.logw = c->d_logw.p; p.m.dim = c->dim; p.m.npair = c->npair; p.m.Dtot = c->Dtot;
+  p.m.meanR = c->d_meanR.p; p.m.invU = c->d_invU.p; p.m.var_of = c->d_var_of.p; p.m.dimP = c->dimP;
+  k_rescore_verdict<<<(unsigned)((c->n_frames + 255) / 256), 256, 0, c->stream>>>(p);
   SGMM_LAUNCH_CHECK(c);
   return 0;
 }

@@ -532,6 +532,8 @@ struct TcParams {
   // column of the certified minimum within the state's (padded) density list, or kUncertain
   uint32_t* cand;
   unsigned long long* prof;   // cycle profile (debug & 32), else NULL
+  int tol;                    // tolerance mode (fp16 form, k_tc_gemm256): besides the verdict, e32[cell] = min accumulator / (s_f t_s)
+  float* e32;                 // = the state's best score minus the frame's x^2 term (k_tol_finish adds it)
 };
 constexpr uint32_t kUncertain = 0x80000000u;
 constexpr uint32_t kAccCol = 128;    // TMEM: columns [0, 128) hold Ahi of both halves, then three 128-column accumulators
@@ -1284,7 +1286,11 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           if (row < nvalid) {
             const bool certain = Bacc == 1.0f && Bsecond > Bbest + BG;
             const uint32_t col = my_map ? (uint32_t)my_map[j] : j;     // packed: this frame's utterance may not use state j
-            if (col != 0xFFFFu || !my_map) p.cand[tc_cell(my_cell, col, !p.dense)] = certain ? (uint32_t)Bidx : kUncertain;
+            if (col != 0xFFFFu || !my_map) {
+              const uint64_t cell = tc_cell(my_cell, col, !p.dense);
+              p.cand[cell] = certain ? (uint32_t)Bidx : kUncertain;
+              if (F16 && p.tol) p.e32[cell] = Bbest * (g.w / xn.y);
+            }
           }
         }
       }
@@ -1925,6 +1931,53 @@ __global__ void __launch_bounds__(256) k_tc_rescan2(RefineParams p) {
   if (lane == 0 && n_done && p.fallback_count) atomicAdd(p.fallback_count, (unsigned long long)n_done);
 }
 
+// ---- tolerance mode (experiment, option "tolerance"; NOT bit-identical to the reference) -------------------------------
+// The filter's epilogue left  r = min_k (c_k - sum_d x_d mu_kd / var_d)  per cell (f32, cell-indexed like the emission
+// matrix); the state's score is  r + Q,  Q = sum_d x_d^2 / (2 var_sd)  — the x^2 block that pooled variances make common to
+// all densities of a state and that the GEMM therefore leaves out.  One CTA per granule of 128 frames of one utterance:
+// the frames' rows in shared memory, thread = frame walks the utterance's columns; a warp's 32 frames of a column are
+// two 64-byte runs of the tiled layout.  h = 1 / (2 var) comes from the FFMA scorer's f32 table.
+template <int DV4>
+__global__ void __launch_bounds__(128) k_tol_finish(RefineParams p, float* __restrict__ e32) {
+  extern __shared__ __align__(16) float tf_sm[];            // [nu][4 DV4] h rows of the utterance's states, then [128][dim | 1] feature rows
+  const uint4 t = p.tasks[blockIdx.x];
+  const uint64_t uf0 = p.frame_off[t.x];
+  const uint32_t nrows = min(128u, (uint32_t)(p.frame_off[t.x + 1] - uf0) - t.y);
+  const uint32_t ncol = p.nuniq_pad[t.x], nu = p.uniq_off[t.x + 1] - p.uniq_off[t.x];
+  const uint32_t* ulist = p.uniq + p.uniq_off[t.x];
+  const uint32_t dim = p.m.dim, XS = dim | 1u;
+  float* hs = tf_sm;
+  float* xs = tf_sm + (size_t)nu * 4 * DV4;
+  for (uint32_t i = threadIdx.x; i < nu * 4 * DV4; i += 128) {
+    const uint32_t j = i / (4 * DV4), q = i - j * (4 * DV4);
+    const uint32_t s = ulist[j], k0 = p.state_off[s];
+    // pooled: the state's one h = 1 / (2 var) row (the FFMA scorer's table, zero-padded to 4 DV4); NaN marks an empty mixture
+    hs[i] = p.state_off[s + 1] > k0 ? __ldg(reinterpret_cast<const float*>(p.h32 + (size_t)k0 * DV4) + q) : __int_as_float(0x7fc00000);
+  }
+  for (uint32_t i = threadIdx.x; i < nrows * dim; i += 128) {
+    const uint32_t r = i / dim, q = i - r * dim;
+    xs[r * XS + q] = __ldg(p.x + (uf0 + t.y + r) * dim + q);
+  }
+  __syncthreads();
+  const uint32_t r = threadIdx.x;
+  if (r >= nrows) return;
+  float x2[4 * DV4];
+#pragma unroll
+  for (int d = 0; d < 4 * DV4; d++) { const float v = d < (int)dim ? xs[r * XS + d] : 0.f; x2[d] = v * v; }
+  float* out = e32 + p.E_off[t.x] + (uint64_t)t.y * ncol;   // t.y is a multiple of 16: first cell of its tile
+  for (uint32_t j = 0; j < nu; j++) {
+    const float4* h = reinterpret_cast<const float4*>(hs + (size_t)j * 4 * DV4);
+    float q = 0.f;
+#pragma unroll
+    for (int v = 0; v < DV4; v++) {
+      const float4 hv = h[v];
+      q = fmaf(x2[4 * v], hv.x, q); q = fmaf(x2[4 * v + 1], hv.y, q); q = fmaf(x2[4 * v + 2], hv.z, q); q = fmaf(x2[4 * v + 3], hv.w, q);
+    }
+    const uint64_t cell = sgmm_cell_rel(ncol, r, j);
+    out[cell] = q == q ? out[cell] + q : 1e10f;             // empty mixture: min_score's start value
+  }
+}
+
 // ---- sum scores with an f32 pruner (option max_approx = 0) ---------------------------------------------
 // score = -log sum_k exp(-s_k) (Mixtures.cpp:719-728).  A density whose score exceeds the state's minimum by more than
 // kSumDelta = 45 adds less than e^-45 = 2.9e-20 of the sum; 65535 of them stay below a quarter of an f64 ulp, so leaving them
@@ -2206,6 +2259,11 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.pack_colmap = c->d_pack_colmap.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
+  if (c->tol && !dense) {
+    if (!(f16 && !epi16 && !c->tc_full)) SGMM_FAIL(c, "tolerance mode: needs the fp16 tensor form (pooled model, 256-column tiles, tc_epi16 = 0)");
+    SGMM_CHECK(c, c->d_e32.reserve(n_cells + 2));
+    p.tol = 1; p.e32 = c->d_e32.p;
+  }
   const size_t smem = wide ? tc_smem256(ks, nhalf, nstage, epi16) : tc_smem(stage_bytes, nhalf, nstage, a_smem);
   RefineParams r{};
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
@@ -2312,6 +2370,29 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   if (!one)
     for (size_t ri = 0; ri < ranges.size(); ri++) SGMM_CHECK(c, cudaStreamWaitEvent(c->stream, c->ev_join[ri], 0));
   sgmm_stage_end(c, SGMM_T_SCORE_FILTER);
+  if (p.tol) {
+    // tolerance mode: e32 holds f32 scores minus the x^2 term; add it, and that is the emission matrix Viterbi reads
+    // (the verdicts stay in d_ci1: the E-step looks the aligned cells' winners up there, k_rescore_verdict)
+    sgmm_stage_begin(c, SGMM_T_SCORE_REFINE);
+    r.tasks = c->d_tasks128.p;
+    r.h32 = c->d_h32.p;
+    const size_t fsm = ((size_t)c->max_uniq * 4 * c->dv4 + 128 * (size_t)(c->dim | 1u)) * sizeof(float);
+    if (fsm > kSmemLimit) SGMM_FAIL(c, "tolerance mode: too many distinct states in one utterance");
+#define SGMM_TOL_CASE(V)                                                                                        \
+  case V:                                                                                                       \
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_tol_finish<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm)); \
+    k_tol_finish<V><<<(unsigned)c->n_tasks128, 128, fsm, c->stream>>>(r, c->d_e32.p);                            \
+    break;
+    switch (c->dv4) {
+      SGMM_TOL_CASE(7) SGMM_TOL_CASE(9) SGMM_TOL_CASE(12) SGMM_TOL_CASE(16)
+      default: SGMM_FAIL(c, "tolerance mode: unsupported feature dimension");
+    }
+#undef SGMM_TOL_CASE
+    SGMM_LAUNCH_CHECK(c);
+    sgmm_stage_end(c, SGMM_T_SCORE_REFINE);
+    c->tol_active = true;
+    return 0;
+  }
   sgmm_stage_begin(c, SGMM_T_SCORE_REFINE);
   // refinement of every cell in one launch (alternating GEMM and refinement launches per range wastes the SMs at
   // every switch: a GEMM CTA needs the whole shared memory of an SM, so it waits for all refinement CTAs there)

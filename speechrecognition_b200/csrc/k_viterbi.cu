@@ -53,7 +53,8 @@ struct VitParams {
   const uint16_t* pos2uniq;    // per automaton position: column in the utterance's emission row
   const uint32_t* nuniq_pad;
   const uint64_t* E_off;
-  const double* E;
+  const double* E;             // emission matrix; f32 == 1: the same cells as floats (tolerance mode: the filter's scores)
+  int f32;
   double tdp_loop, tdp_forward, tdp_skip;
   uint32_t silence_state;
   double beam;                 // DEST only: positions costlier than (frame best + beam) die; +inf = no pruning
@@ -76,7 +77,7 @@ __device__ __forceinline__ double pick(const double (&v)[C], int c) {
 //               positions with cost > best + threshold die, :227-239 — a dead position is +inf here, which
 //               never wins a strict comparison, exactly like a predecessor the reference skips; the
 //               backtrace starts from the highest position alive in the last frame, :245-256).
-template <int C, bool DEST>
+template <int C, bool DEST, typename ET = double>   // ET: element type of the emission matrix (float: tolerance mode)
 __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x;
@@ -87,12 +88,12 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
   const uint32_t a0 = p.aut_off[u];
   const uint32_t S = p.aut_off[u + 1] - a0;
   const uint32_t ncol = p.nuniq_pad[u];
-  const double* Eu = p.E + p.E_off[u];
+  const ET* Eu = reinterpret_cast<const ET*>(p.E) + p.E_off[u];
   const double INF = CUDART_INF;
 
   // shared memory carve-up
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                          // SGMM_STAGES mbarriers
-  double* tiles = reinterpret_cast<double*>(smem + 64);                        // STAGES x TILE_T x ncol
+  ET* tiles = reinterpret_cast<ET*>(smem + 64);                        // STAGES x TILE_T x ncol
   const size_t tile_elems = (size_t)SGMM_TILE_T * ncol;
   uint32_t* bpw = reinterpret_cast<uint32_t*>(tiles + SGMM_STAGES * tile_elems);  // ceil(T/16) x 32C words
   uint16_t* sref = reinterpret_cast<uint16_t*>(bpw + (size_t)((T + 15) / 16) * 32 * C);  // automaton states
@@ -108,7 +109,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
   if (lane == 0) {
     for (uint32_t i = 0; i < SGMM_STAGES && i < n_tiles; i++) {
       const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - i * SGMM_TILE_T);
-      const uint32_t bytes = SGMM_TILE_T * ncol * sizeof(double);   // whole tiles: [column][16 frames] (sgmm_cell_rel)
+      const uint32_t bytes = SGMM_TILE_T * ncol * sizeof(ET);   // whole tiles: [column][16 frames] (sgmm_cell_rel)
       mbar_expect_tx(&bars[i], bytes);
       tma_load_1d(tiles + i * tile_elems, Eu + (size_t)i * tile_elems, bytes, &bars[i]);
     }
@@ -148,10 +149,10 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
 
   // One frame of the recursion.  The backpointer is kept as the two raw comparison flags (bit 0 = first comparison,
   // bit 1 = second), set by predicated ORs with the frame's mask; the backtrace decodes them.
-  auto frame = [&](const double* __restrict__ tile, const uint32_t tt, const uint32_t m1) {
+  auto frame = [&](const ET* __restrict__ tile, const uint32_t tt, const uint32_t m1) {
     double e[C];
 #pragma unroll
-    for (int c = 0; c < C; c++) e[c] = tile[col[c] ^ tt];
+    for (int c = 0; c < C; c++) e[c] = (double)tile[col[c] ^ tt];
     // the two costs that cross the lane boundary (positions s-1 and s-2 of this lane's first position)
     const double Q1 = __shfl_up_sync(0xffffffffu, q[C - 1], 1);
     const double Q2 = __shfl_up_sync(0xffffffffu, q[C - 2], 1);
@@ -206,7 +207,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
   for (uint32_t ti = 0; ti < n_tiles; ti++) {
     const uint32_t slot = ti % SGMM_STAGES;
     mbar_wait(&bars[slot], (ti / SGMM_STAGES) & 1);
-    const double* tile = tiles + slot * tile_elems;
+    const ET* tile = tiles + slot * tile_elems;
     const uint32_t rows = min((uint32_t)SGMM_TILE_T, T - ti * SGMM_TILE_T);
     if (ti > 0 && rows == SGMM_TILE_T) {
       // full tile: unrolled, the frame masks are immediates
@@ -216,7 +217,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
       uint32_t tt = 0;
       if (ti == 0) {
         // Q(0,0) = emission(0, ref[0]); every other position starts at +inf (Alignment.cpp:62-63,77)
-        const double e0 = tile[col[0]];
+        const double e0 = (double)tile[col[0]];
 #pragma unroll
         for (int c = 0; c < C; c++) q[c] = (lane == 0 && c == 0) ? e0 : INFd;
         tt = 1;
@@ -230,7 +231,7 @@ __global__ void __launch_bounds__(32) k_viterbi(VitParams p) {
     const uint32_t nxt = ti + SGMM_STAGES;
     if (lane == 0 && nxt < n_tiles) {
       const uint32_t nrows = min((uint32_t)SGMM_TILE_T, T - nxt * SGMM_TILE_T);
-      const uint32_t bytes = SGMM_TILE_T * ncol * sizeof(double);
+      const uint32_t bytes = SGMM_TILE_T * ncol * sizeof(ET);
       mbar_expect_tx(&bars[slot], bytes);
       tma_load_1d(tiles + slot * tile_elems, Eu + (size_t)nxt * tile_elems, bytes, &bars[slot]);
     }
@@ -484,7 +485,11 @@ int launch_mw(sgmm_ctx* c, const VitParams& p, size_t smem, int conv, cudaStream
 
 template <int C>
 int launch_c(sgmm_ctx* c, const VitParams& p, size_t smem, int conv, cudaStream_t stream) {
-  if (conv == SGMM_TDP_SOURCE) {
+  if (p.f32) {   // tolerance mode (experiment): the full aligner on the filter's f32 scores
+    if (conv != SGMM_TDP_SOURCE) SGMM_FAIL(c, "viterbi: the tolerance mode supports the full aligner only");
+    SGMM_CHECK(c, cudaFuncSetAttribute(k_viterbi<C, false, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_viterbi<C, false, float><<<p.n_utts, 32, smem, stream>>>(p);
+  } else if (conv == SGMM_TDP_SOURCE) {
     SGMM_CHECK(c, cudaFuncSetAttribute(k_viterbi<C, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_viterbi<C, false><<<p.n_utts, 32, smem, stream>>>(p);
   } else {
@@ -510,12 +515,14 @@ int sgmm_launch_viterbi(sgmm_ctx* c, int conv) {
     p.utts = vc.d_utts.p; p.n_utts = (uint32_t)vc.utts.size();
     p.frame_off = c->d_frame_off.p; p.aut = c->d_aut.p; p.aut_off = c->d_aut_off.p;
     p.pos2uniq = c->d_pos2uniq.p; p.nuniq_pad = c->d_nuniq_pad.p; p.E_off = c->d_E_off.p; p.E = c->d_E.p;
+    if (c->tol_active) { p.E = reinterpret_cast<const double*>(c->d_e32.p); p.f32 = 1; }
     p.tdp_loop = c->tdp_loop; p.tdp_forward = c->tdp_forward; p.tdp_skip = c->tdp_skip;
     p.silence_state = c->silence_state;
     p.beam = c->beam;
     p.ali = c->d_ali.p; p.fcol = c->d_fcol.p; p.costs = c->d_costs.p;
     int rc = 1;
     if (vc.W == kVitW) {
+      if (p.f32) SGMM_FAIL(c, "viterbi: the tolerance mode needs option vit_mw = 0 before sgmm_set_corpus");
       switch (vc.C) {
         case 2: rc = launch_mw<2>(c, p, vc.smem, conv, stream); break;
         case 3: rc = launch_mw<3>(c, p, vc.smem, conv, stream); break;

@@ -151,6 +151,7 @@ struct sgmm_ctx : SgmmModel {
   DevBuf<float> d_Ahi, d_Alo;
   DevBuf<float2> d_xnorm;
   DevBuf<uint32_t> d_ci1;
+  DevBuf<float> d_e32;             // tolerance mode: the f32 emission matrix (cell-indexed like d_E)
   DevBuf<unsigned long long> d_rescan;   // [0] = count, [1..] = cell ids
   size_t rescan_cap = 0;
   int host_tables = 0;             // option "host_tables": 1 = build the K5 tables on the host (the checker of the device builder)
@@ -195,6 +196,9 @@ struct sgmm_ctx : SgmmModel {
   // state-major refinement (k_tc_refine_sm): work items (block of utterances, state) and, per item, the
   // utterances of the block that visit the state
   int tc_refine = 0;               // option "tc_refine": 0 automatic, 1 frame-major kernel, 2 state-major kernel
+  int tol = 0;                     // option "tolerance" (experiment, default off): Viterbi consumes the tensor filter's f32 scores; no
+                                   // refinement; only the aligned cells are re-scored in f64 (K3).  NOT bit-identical to the reference.
+  bool tol_active = false;         // the last alignment pass ran in tolerance mode (its emission matrix is f32: d_e32)
   int tc_civ = 1;                  // option "tc_civ": state-major refinement reads the inverse variances from the constant bank (0: shared memory)
   int tc_lq = 1;                   // option "tc_lq": state-major refinement queues an item's near-ties as one run (0: cell by cell)
   int tc_rem = 1;                  // option "tc_rem" (read by sgmm_set_model): pack the K remainder of the fp16 form
@@ -219,7 +223,7 @@ struct sgmm_ctx : SgmmModel {
   DevBuf<double> d_E;             // ragged emission matrix, utterance u: [ceil(T_u / 16)][nuniq_pad_u][16] (sgmm_cell_rel)
   DevBuf<uint16_t> d_Amin;        // argmin density of every emission cell (same indexing as d_E)
   DevBuf<uint16_t> d_fcol;        // per frame: emission column of the aligned position (written by the backtrace)
-  uint64_t model_version = 1, E_model_version = 0;
+  uint64_t model_version = 1, E_model_version = 0, tol_model_version = 0;
   uint64_t serial = 0;            // unique per context of this process (sgmm_create): keys caches that outlive a context
   bool use_cache = true;          // option "rescore_cache"
   bool max_approx = true;         // option "max_approx": score() = min_score (1) or sum_score (0), Mixtures.cpp:737-744
@@ -329,6 +333,7 @@ inline int sgmm_wait_features(sgmm_ctx* c) {
 }
 int sgmm_launch_rescore(sgmm_ctx* c, bool first_pass);
 int sgmm_launch_rescore_cached(sgmm_ctx* c);
+int sgmm_launch_rescore_verdict(sgmm_ctx* c);   // tolerance mode: winners from the filter's verdicts of the alignment pass
 int sgmm_launch_accumulate(sgmm_ctx* c);
 int sgmm_sort_frames(sgmm_ctx* c, const uint32_t* keys, uint32_t n_keys, const uint32_t** sorted);
 // non-max-approx branch (k_soft.cu)

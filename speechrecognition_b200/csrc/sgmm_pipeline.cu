@@ -102,6 +102,7 @@ int sgmm_align(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* co
   SGMM_CHECK(c, c->d_fcol.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_ali.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_costs.reserve(c->n_utts));
+  c->tol_active = false;
   {
     StageTimer st(c, SGMM_T_SCORE);
     if (launch_emission_any(c, false, 0, 0, nullptr, nullptr)) return 1;
@@ -122,7 +123,8 @@ int sgmm_align(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment, double* co
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
   c->have_alignment = true;
   c->ali_has_cols = true;
-  c->E_model_version = c->model_version;
+  c->E_model_version = c->tol_active ? 0 : c->model_version;   // tolerance mode: no exact emission matrix to look up
+  c->tol_model_version = c->tol_active ? c->model_version : 0;
   c->E_max_approx = c->max_approx;
   return 0;
 }
@@ -233,7 +235,10 @@ static int rescore_common(sgmm_ctx* c, bool first_pass) {
   // (the resident emission matrix must hold min scores + argmins: not after an alignment with sum scores)
   const bool cached = !first_pass && c->ali_has_cols && c->E_model_version == c->model_version && c->use_cache &&
                       c->E_max_approx;
-  if (cached ? sgmm_launch_rescore_cached(c) : sgmm_launch_rescore(c, first_pass)) return 1;
+  // tolerance mode: the filter's verdicts of the alignment pass name the winner of (almost) every aligned cell
+  const bool by_verdict = !first_pass && c->tol_active && c->ali_has_cols && c->tol_model_version == c->model_version;
+  if (by_verdict ? sgmm_launch_rescore_verdict(c)
+                 : (cached ? sgmm_launch_rescore_cached(c) : sgmm_launch_rescore(c, first_pass))) return 1;
   if (sgmm_launch_score_sum(c)) return 1;
   return 0;
 }
@@ -319,6 +324,7 @@ int sgmm_align_accumulate(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment,
   SGMM_CHECK(c, c->d_fcol.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_ali.reserve(c->n_frames));
   SGMM_CHECK(c, c->d_costs.reserve(c->n_utts));
+  c->tol_active = false;
   {
     StageTimer st(c, SGMM_T_SCORE);
     if (launch_emission_any(c, false, 0, 0, nullptr, nullptr)) return 1;
@@ -329,7 +335,8 @@ int sgmm_align_accumulate(sgmm_ctx* c, int conv, sgmm_alignment_item* alignment,
   }
   c->have_alignment = true;
   c->ali_has_cols = true;
-  c->E_model_version = c->model_version;
+  c->E_model_version = c->tol_active ? 0 : c->model_version;   // tolerance mode: no exact emission matrix to look up
+  c->tol_model_version = c->tol_active ? c->model_version : 0;
   c->E_max_approx = c->max_approx;
   // alignment + costs go home on the copy stream, behind the Viterbi launches, beside the E-step
   SGMM_CHECK(c, cudaEventRecord(c->ev_fork, c->stream));
