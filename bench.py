@@ -453,6 +453,49 @@ def run_other_workloads(args, capi, torch, dist, local, rank, world, which):
     return res
 
 
+def tolerance_experiment(args, capi, local, tables, corp, lex, x_pin):
+    """the tolerance mode (option "tolerance", default OFF, NOT bit-identical) beside the exact mode on the
+    bench shard, in a context of its own: ms per alignment pass + E-step of both, and how the results differ.  A reported
+    experiment — the headline `value` above is the exact mode."""
+    ctx = capi.Context(local)
+    try:
+        ctx.set_option("vit_mw", 0)              # the mode has no multi-warp Viterbi form; both arms run without it
+        ctx.set_model_tables(args.dim, tables)
+        ctx.set_features(x_pin)
+        ctx.set_tdp(3.0, 0.0, 30.0, lex.silence_state)
+        ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"])
+        fo = corp["frame_off"]
+        res = {}
+        for mode in (0, 1):
+            ctx.set_option("tolerance", mode)
+            for _ in range(2):
+                ctx.align(want_alignment=False, want_costs=False)
+                ctx.accumulate(first_pass=False, want=False)
+            ctx.timer_start()
+            for _ in range(3):
+                ctx.align(want_alignment=False, want_costs=False)
+                ctx.accumulate(first_pass=False, want=False)
+            ms = ctx.timer_stop() / 3
+            ali, costs = ctx.align()
+            cnt, sx, _, ssum = ctx.accumulate(first_pass=False)
+            res[mode] = (ms, ali["state"].copy(), costs.copy(), cnt.copy(), sx.copy(), ssum)
+        a, b = res[0], res[1]
+        diff = a[1] != b[1]
+        rel = np.abs(b[2] - a[2]) / np.maximum(np.abs(a[2]), 1e-300)
+        return {"default": "off", "ms_per_pass_exact": a[0], "ms_per_pass_tolerance": b[0],
+                "utterances": int(len(fo) - 1), "frames": int(fo[-1]),
+                "utterances_with_different_alignment": int(sum(bool(diff[fo[u]:fo[u + 1]].any()) for u in range(len(fo) - 1))),
+                "frames_with_different_state": int(diff.sum()),
+                "path_cost_rel_diff_max": float(rel.max()),
+                "densities_with_different_count": int((a[3] != b[3]).sum()),
+                "sum_x_rel_diff_max": float(np.max(np.abs(a[4] - b[4]) / np.maximum(np.abs(a[4]), 1e-300))),
+                "am_score_sum_rel_diff": float(abs(a[5] - b[5]) / abs(a[5])),
+                "note": "pass = sgmm_align + sgmm_accumulate, features resident, no M-step; both arms with option vit_mw = 0; "
+                        "exact mode = the oracle's results (parity_check)"}
+    finally:
+        ctx.close()
+
+
 def config_dict(args, frames_per_gpu, extra=None):
     c = {"workload": "BASELINE configs[1] shape (106 states x %d densities, d=%d, per-state pooled diag cov) "
                      "run as configs[2]'s full EM iteration: score + Viterbi-align + accumulate + M-step (finalize and the model "
@@ -648,6 +691,12 @@ def run_ours(args):
     others = {}
     if not args.no_other_workloads:
         others = run_other_workloads(args, capi, torch, dist, local, rank, world, ("recognize", "stress"))
+    tol = None
+    if world == 1 and not args.no_other_workloads:
+        try:
+            tol = tolerance_experiment(args, capi, local, tables, corp, lex, x_pin)
+        except Exception as e:   # an experiment must not take the bench line down
+            tol = {"error": str(e)[:300]}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -768,6 +817,8 @@ def run_ours(args):
         line["allreduce_check"] = ar_check
     if others:
         line["other_workloads"] = others
+    if tol is not None:
+        line["tolerance_mode"] = tol
     emit(line)
     if world > 1:
         dist.destroy_process_group()

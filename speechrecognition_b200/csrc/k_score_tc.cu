@@ -1476,7 +1476,11 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
                                                    p.pooled ? iv_all + j * p.m.dimP : nullptr);
         if (sc < best) { best = sc; bk = i1; }
       } else {
-        const unsigned long long slot = atomicAdd(p.rescan, 1ull);
+        // one atomic per group of lanes that arrive here together (same-address atomics serialise at the L2)
+        const uint32_t am = __activemask(), ln = threadIdx.x & 31u;
+        unsigned long long slot = 0ull;
+        if (ln == (uint32_t)__ffs(am) - 1u) slot = atomicAdd(p.rescan, (unsigned long long)__popc(am));
+        slot = __shfl_sync(am, slot, __ffs(am) - 1) + __popc(am & ((1u << ln) - 1u));
         if (slot < p.cap) { rq_put(p.rescan, slot, e, frame, s); continue; }
         const float* xf = p.x + frame * p.m.dim;   // list full: rescan here
         for (uint32_t k = k0; k < k1; k++) {
