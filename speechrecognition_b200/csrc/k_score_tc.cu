@@ -52,6 +52,8 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+constexpr uint32_t kUncertain = 0x80000000u;   // verdict: no certified winner -> rescan
+constexpr uint32_t kPair = 0x40000000u;        // verdict: kPair | column a | column b << 15 — the argmin is one of the two
 // suspend-time hint: a waiting warp sleeps in hardware until the phase completes instead of re-polling (polling loops
 // were ~23 % of all issued instructions and compete with the MMA-issuing warp for its scheduler)
 constexpr uint32_t kWaitHintNs = 20000;
@@ -245,9 +247,9 @@ __device__ __forceinline__ void tc_ld_pin(uint32_t (&r)[16]) {
 //   a[b] += c * 2^e                      column e of block b sets bit e of an exact integer < 2^16,
 // so the candidates of the sub-part end up as a bit mask: count = popc, column = ffs.  (The packed FFMA2 form this
 // replaces kept the FMA pipe as busy as the tensor pipe: the epilogue, not the MMAs, set the kernel's pace.)
-template <int NB>
+template <int NB, bool PAIR = false>   // PAIR: also the packed candidate code of TcBest
 __device__ __forceinline__ void tc_subpart(const uint32_t (&v)[NB][16], float Gs, float& ms, float& Gsub, float& a_s,
-                                           float& i_s) {
+                                           float& i_s, uint32_t* packed = nullptr) {
   float mm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
 #pragma unroll
   for (int b = 0; b < NB; b++) {
@@ -278,7 +280,74 @@ __device__ __forceinline__ void tc_subpart(const uint32_t (&v)[NB][16], float Gs
   const int pos = lo ? __ffs(lo) - 1 : 31 + __ffs(hi);
   a_s = thr_ok ? (float)n : 2.f;
   i_s = (float)pos;
+  if (PAIR) {   // packed for TcBest: count code << 30 | (last - first candidate column) << 16 | first candidate column
+    uint32_t code = (thr_ok && n == 1) ? (1u << 30) | (uint32_t)pos : (3u << 30) | (uint32_t)pos;
+    if (__any_sync(0xffffffffu, thr_ok && n == 2)) {   // rare, warp-uniform branch: the second candidate's column
+      const int last = hi ? 63 - __clz(hi) : 31 - __clz(lo | 1u);
+      if (thr_ok && n == 2) code = (2u << 30) | ((uint32_t)(last - pos) << 16) | (uint32_t)pos;
+    }
+    *packed = code;
+  }
 }
+
+// ---- candidates of a (frame, state) cell across sub-parts, column parts and tiles (default epilogue of k_tc_gemm256).
+// Every sub-result is {minimum m, bound G = Gs + 4e-6 |m|, acc = columns below m + G, their first (idx) and last (idxP)
+// column}.  A column of ANOTHER sub-result S can lie below the best one's threshold a + G_a only if it is in S's own
+// count (a <= m_S and |G_a - G_S| <= 4e-6 |a - m_S| give a + G_a <= m_S + G_S), so the cell's candidate set is the union
+// of the counts of the sub-results whose minimum is <= a + G_a.  Kept: the best sub-result, the runner-up (with its
+// count and column) and the third-smallest minimum.  Verdict:
+//   certified      runner-up > a + G_a and acc == 1
+//   pair           runner-up > a + G_a and acc == 2 (both in one sub-result), or
+//                  third > a + G_a >= runner-up and both counts are 1 (one candidate each)       [round 2]
+//   uncertain      otherwise
+// A pair verdict names the ONLY two columns that can be the f64 argmin: the refinement evaluates both exactly (first
+// minimum wins), and the cell never reaches the rescan queue.
+struct TcBest {
+  // 5 registers (as many as the certified-only bookkeeping it replaces; anything more spills inside the column loops and
+  // costs the filter 50 %, measured): three minima and two packed candidate codes
+  //   code = count << 30 | (last - first candidate column) << 16 | first candidate column      count: 1, 2, 3 = more / unknown
+  float m, m2, m3;
+  uint32_t c1, c2;
+  __device__ __forceinline__ void init() { m = m2 = m3 = INFINITY; c1 = c2 = 0xc0000000u; }
+  // (selects only: a data-dependent branch here diverges the 32 rows of an epilogue warp — measured +0.5 ms on the filter)
+  __device__ __forceinline__ void ins(float nm, uint32_t nc) {
+    const bool b1 = nm < m, b2 = nm < m2;                     // m <= m2, so b1 implies b2
+    const float om = m, om2 = m2;
+    const uint32_t oc1 = c1;
+    m3 = b2 ? om2 : fminf(m3, nm);
+    m2 = b1 ? om : (b2 ? nm : om2);
+    c2 = b1 ? oc1 : (b2 ? nc : c2);
+    m = b1 ? nm : om;
+    c1 = b1 ? nc : oc1;
+  }
+  // all of another TcBest whose columns start at column off (off + column < 65536): both triples are sorted, so the
+  // merged one is  winner's m | min(winner's m2, loser's m) | min(max(those two), winner's m3, loser's m2)
+  __device__ __forceinline__ void merge(const TcBest& o, uint32_t off) {
+    const bool ob = o.m < m;
+    const float wm2 = ob ? o.m2 : m2, wm3 = ob ? o.m3 : m3, lm = ob ? m : o.m, lm2 = ob ? m2 : o.m2;
+    const uint32_t wc1 = ob ? o.c1 + off : c1, wc2 = ob ? o.c2 + off : c2, lc1 = ob ? c1 : o.c1 + off;
+    const bool s2 = lm < wm2;
+    m = ob ? o.m : m;
+    c1 = wc1;
+    m2 = s2 ? lm : wm2;
+    c2 = s2 ? lc1 : wc2;
+    m3 = fminf(fminf(s2 ? wm2 : lm, wm3), lm2);
+  }
+  // called by a CONVERGED warp: the pair logic sits behind a warp-uniform vote (all 32 cells certified: the common case)
+  __device__ __forceinline__ uint32_t verdict(float Gs) const {
+    const float thr = m + (Gs + 4e-6f * fabsf(m));          // the best sub-result's own bound (tc_subpart)
+    const uint32_t n1 = c1 >> 30, a = c1 & 0xffffu;
+    const bool alone = m2 > thr, cert = alone && n1 == 1u;
+    uint32_t vd = cert ? a : kUncertain;
+    if (!__all_sync(0xffffffffu, cert)) {
+      const bool pa = alone && n1 == 2u, pb = !alone && m3 > thr && n1 == 1u && (c2 >> 30) == 1u;
+      const uint32_t b = pa ? a + ((c1 >> 16) & 0x3fffu) : (c2 & 0xffffu);
+      const bool okp = (pa || pb) && a != b && a < 32768u && b < 32768u;
+      vd = cert ? a : (okp ? (kPair | min(a, b) | (max(a, b) << 15)) : kUncertain);
+    }
+    return vd;
+  }
+};
 
 template <int NB, bool SINGLE = false>   // SINGLE: the caller guarantees c_hi - c_lo <= 16 * NB (one sub-part, no loop)
 __device__ __forceinline__ void tc_scan_onepass(uint32_t tcol, uint32_t c_lo, uint32_t c_hi, float Gs, uint64_t* release_bar,
@@ -323,6 +392,52 @@ __device__ __forceinline__ void tc_scan_onepass(uint32_t tcol, uint32_t c_lo, ui
         acc = a_s + ((s_lo != c_lo && m <= ms + Gsub) ? 1.f : 0.f);
         idx = i_s; G = Gsub; m = ms;
       } else if (ms <= m + G) acc += 1.f;
+    }
+  }
+  if (!released) {
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(release_bar);
+  }
+}
+
+// tc_scan_onepass with the candidate bookkeeping of TcBest (columns relative to the tile)
+template <int NB>
+__device__ __forceinline__ void tc_scan_onepass2(uint32_t tcol, uint32_t c_lo, uint32_t c_hi, float Gs, uint64_t* release_bar,
+                                                 int lane, uint32_t dbg, TcBest& st) {
+  st.init();
+  bool released = false;
+  if (!(dbg & 1)) {
+    for (uint32_t s_lo = c_lo; s_lo < c_hi; s_lo += 16 * NB) {
+      uint32_t v[NB][16];
+      const bool last = s_lo + 16 * NB >= c_hi;                     // this warp's last read of the accumulator
+      if (s_lo + 16 * NB <= c_hi) {                                 // full sub-part (the common case): no padding
+#pragma unroll
+        for (int b = 0; b < NB; b++) tc_ld16_nowait(tcol + s_lo + 16 * b, v[b]);
+      } else {
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+          if (s_lo + 16 * b < c_hi) tc_ld16_nowait(tcol + s_lo + 16 * b, v[b]);
+          else {
+#pragma unroll
+            for (int e = 0; e < 16; e++) v[b][e] = 0x7f800000u;   // +inf: never the minimum, indicator 0
+          }
+        }
+      }
+      tc_ld_wait(v[0]);
+#pragma unroll
+      for (int b = 1; b < NB; b++) tc_ld_pin(v[b]);
+      if (last) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(release_bar);
+        released = true;
+      }
+      float ms, Gsub, a_s, i_s;
+      uint32_t code;
+      tc_subpart<NB, true>(v, Gs, ms, Gsub, a_s, i_s, &code);
+      if (s_lo == c_lo) { st.m = ms; st.c1 = code + s_lo; }      // (st.init() left the rest empty)
+      else st.ins(ms, code + s_lo);
     }
   }
   if (!released) {
@@ -532,10 +647,10 @@ struct TcParams {
   // column of the certified minimum within the state's (padded) density list, or kUncertain
   uint32_t* cand;
   unsigned long long* prof;   // cycle profile (debug & 32), else NULL
+  int pairs;                  // default epilogue of k_tc_gemm256: emit pair verdicts (option tc_pairs; 0: such cells are uncertain)
   int tol;                    // tolerance mode (fp16 form, k_tc_gemm256): besides the verdict, e32[cell] = min accumulator / (s_f t_s)
   float* e32;                 // = the state's best score minus the frame's x^2 term (k_tol_finish adds it)
 };
-constexpr uint32_t kUncertain = 0x80000000u;
 constexpr uint32_t kAccCol = 128;    // TMEM: columns [0, 128) hold Ahi of both halves, then three 128-column accumulators
 constexpr uint32_t kNumAcc = 3;
 
@@ -1199,7 +1314,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
       const float2 xn = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
       const uint64_t my_cell = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, !p.dense);
       const uint16_t* my_map = prow ? p.pack_colmap + prow[row].colmap : nullptr;
-      float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
+      float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]: a part's TcBest
       uint32_t it = 0;
       long long e_wait = 0;
       const long long e_start = p.prof ? clock64() : 0;
@@ -1208,7 +1323,8 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
         const float4 g = mt.g;
         // certified bound on |f32 score - exact score| differences between two candidates (+0.1 %)
         const float Gs = 2.002f * p.eps * (xn.x * g.x + xn.y * g.y + g.z);
-        float Bbest = INFINITY, Bsecond = INFINITY, Bacc = 0.f, Bidx = 0.f, BG = 0.f;
+        TcBest B;                                                   // candidates of this (row, state) cell so far
+        B.init();
         uint32_t n0 = 0;
         for (uint32_t t = mt.tf; t < mt.tf + mt.nt; t++, it++) {
           const uint32_t N = t == mt.tf ? mt.N0 : p.tile_info[t].y;
@@ -1223,7 +1339,10 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           float m = INFINITY, acc = 0.f, idx = 0.f, G = 0.f;
           if (!(p.debug & 128)) {
             // one pass over tensor memory (default); tc_debug & 128 keeps the two-pass scan below as the A/B reference
-            tc_scan_onepass<4>(tcol, c_lo, c_hi, Gs, &tempty[buf], lane, p.debug, m, acc, idx, G);
+            TcBest st;
+            tc_scan_onepass2<4>(tcol, c_lo, c_hi, Gs, &tempty[buf], lane, p.debug, st);
+            if (t == mt.tf) B = st;                               // first tile of the state (n0 = 0): the common case
+            else B.merge(st, n0);
           } else {
           if (!(p.debug & 1) && c_lo < c_hi) {
             uint32_t ra[16], rb[16];
@@ -1269,27 +1388,29 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[buf]);
+          // (two-pass reference: a count other than 1 carries no columns)
+          B.ins(m, ((acc == 1.0f ? 1u : 3u) << 30) | (n0 + (uint32_t)idx));
           }
-          // merge with the state's earlier tiles
-          if (m < Bbest) { Bsecond = Bbest; Bbest = m; Bacc = acc; Bidx = (float)n0 + idx; BG = G; }
-          else Bsecond = fminf(Bsecond, m);
           n0 += N;
         }
         // the two column parts of a (half, quarter) meet through shared memory once per state
         float* slot = my_x + (j & 1) * (2 * BM * 5);
-        if (part == 1) { slot[0] = Bbest; slot[1] = Bsecond; slot[2] = Bacc; slot[3] = Bidx; slot[4] = BG; }
+        if (part == 1) {
+          slot[0] = B.m; slot[1] = B.m2; slot[2] = B.m3; slot[3] = __uint_as_float(B.c1); slot[4] = __uint_as_float(B.c2);
+        }
         asm volatile("bar.sync %0, 64;" ::"r"(1 + group * 4 + quarter) : "memory");
         if (part == 0) {
-          const float ob = slot[0], os = slot[1];
-          if (ob < Bbest) { Bsecond = fminf(Bbest, os); Bbest = ob; Bacc = slot[2]; Bidx = slot[3]; BG = slot[4]; }
-          else Bsecond = fminf(Bsecond, ob);
+          TcBest o;
+          o.m = slot[0]; o.m2 = slot[1]; o.m3 = slot[2]; o.c1 = __float_as_uint(slot[3]); o.c2 = __float_as_uint(slot[4]);
+          B.merge(o, 0u);                                             // (its columns are already relative to the state)
+          uint32_t vd = B.verdict(Gs);                                // (warp vote inside: before the rows diverge)
           if (row < nvalid) {
-            const bool certain = Bacc == 1.0f && Bsecond > Bbest + BG;
             const uint32_t col = my_map ? (uint32_t)my_map[j] : j;     // packed: this frame's utterance may not use state j
             if (col != 0xFFFFu || !my_map) {
               const uint64_t cell = tc_cell(my_cell, col, !p.dense);
-              p.cand[cell] = certain ? (uint32_t)Bidx : kUncertain;
-              if (F16 && p.tol) p.e32[cell] = Bbest * (g.w / xn.y);
+              if (!p.pairs && (vd & kPair) && !(vd & kUncertain)) vd = kUncertain;
+              p.cand[cell] = vd;
+              if (F16 && p.tol) p.e32[cell] = B.m * (g.w / xn.y);
             }
           }
         }
@@ -1710,7 +1831,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     const bool valid = lane < cur.nvalid;
     uint32_t src;
     {
-      const uint32_t key = (valid && i1 < nd) ? (i1 & 7u) : (lane & 7u);
+      const uint32_t key = (valid && (i1 & ~kPair) < (i1 & kPair ? 0x40000000u : nd)) ? (i1 & 7u) : (lane & 7u);   // (a pair: its first column)
       uint32_t lt = 0u, eq = 0xffffffffu;
 #pragma unroll
       for (int bit = 2; bit >= 0; bit--) {
@@ -1729,15 +1850,24 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     phases ^= 1u << b;
     // the winner's exact score, evaluated by EVERY lane (lanes without a certified winner take row 0 and drop the
     // result): the warp stays converged, so the uniform datapath can feed the constant-bank operands
-    const bool act = src < cur.nvalid, cert = act && my_i1 < nd;
-    const uint32_t ki = cert ? my_i1 : 0u;
-    const double sc = sm_exact<DIM, !kOdd, CIV>(tbl + (size_t)ki * RW, lw[ki], my_xr, iv, ivoff);
+    // A pair verdict (kPair | a | b << 15, a < b) names the only two columns that can be the argmin: both are evaluated —
+    // the second one in a divergent pass that ~8 % of the warps take — and the first minimum wins, as in the reference's scan.
+    const bool act = src < cur.nvalid;
+    const bool pair = act && (my_i1 & kPair) && !(my_i1 & kUncertain) && (my_i1 & 0x7fffu) < nd && ((my_i1 >> 15) & 0x7fffu) < nd;
+    const bool cert = act && (my_i1 < nd || pair);
+    uint32_t ki = cert ? (pair ? (my_i1 & 0x7fffu) : my_i1) : 0u;
+    double sc = sm_exact<DIM, !kOdd, CIV>(tbl + (size_t)ki * RW, lw[ki], my_xr, iv, ivoff);
+    if (pair) {
+      const uint32_t kb = (my_i1 >> 15) & 0x7fffu;
+      const double sb = sm_exact<DIM, !kOdd, false>(tbl + (size_t)kb * RW, lw[kb], my_xr, iv, 0u);
+      if (sb < sc) { sc = sb; ki = kb; }               // kb > ki: on equal scores the lower column stays
+    }
     if (act) {
       double best = 1e10;                              // min_score's own start, Mixtures.cpp:699
       uint32_t bk = 0;
       bool queued = false;
       if (cert) {
-        if (sc < best) { best = sc; bk = my_i1; }
+        if (sc < best) { best = sc; bk = ki; }
       } else if (nd) {
         // near-ties are queued for k_tc_rescan (a rescan inside this kernel was measured: one warp walking 256
         // densities holds its CTA back for ~10k cycles, +0.5 ms per 13 M cells)
@@ -2263,6 +2393,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.pack_colmap = c->d_pack_colmap.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
+  p.pairs = (c->tc_pairs && !dense) ? 1 : 0;   // (the dense pass is refined by the frame-major kernel, which rescans pairs)
   if (c->tol && !dense) {
     if (!(f16 && !epi16 && !c->tc_full)) SGMM_FAIL(c, "tolerance mode: needs the fp16 tensor form (pooled model, 256-column tiles, tc_epi16 = 0)");
     SGMM_CHECK(c, c->d_e32.reserve(n_cells + 2));

@@ -477,6 +477,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_rescan")) { c->tc_rescan = (int)value; return 0; }
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
   if (!strcmp(key, "tc_civ")) { c->tc_civ = value != 0; return 0; }
+  if (!strcmp(key, "tc_pairs")) { c->tc_pairs = value != 0; return 0; }
   if (!strcmp(key, "tolerance")) { c->tol = value != 0; return 0; }
   if (!strcmp(key, "tc_lq")) { c->tc_lq = (int)value; return 0; }   // 0 none, 1 default size, n > 1 entries
   if (!strcmp(key, "host_tables")) { c->host_tables = value != 0; return 0; }   // read by sgmm_set_model

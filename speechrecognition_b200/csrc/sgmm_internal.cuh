@@ -199,6 +199,7 @@ struct sgmm_ctx : SgmmModel {
   int tol = 0;                     // option "tolerance" (experiment, default off): Viterbi consumes the tensor filter's f32 scores; no
                                    // refinement; only the aligned cells are re-scored in f64 (K3).  NOT bit-identical to the reference.
   bool tol_active = false;         // the last alignment pass ran in tolerance mode (its emission matrix is f32: d_e32)
+  int tc_pairs = 1;                // option "tc_pairs": the filter names the TWO candidate columns of a near-tie (refined in place) instead of "uncertain"
   int tc_civ = 1;                  // option "tc_civ": state-major refinement reads the inverse variances from the constant bank (0: shared memory)
   int tc_lq = 1;                   // option "tc_lq": state-major refinement queues an item's near-ties as one run (0: cell by cell)
   int tc_rem = 1;                  // option "tc_rem" (read by sgmm_set_model): pack the K remainder of the fp16 form
