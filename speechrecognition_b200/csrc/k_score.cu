@@ -323,12 +323,20 @@ __global__ void __launch_bounds__(256) k_rescore_verdict(VerdictParams p) {
     k0 = p.c.state_off[s]; k1 = p.c.state_off[s + 1];
     v = p.cand[e];
   }
-  const bool unc = valid && k1 > k0 && !(v < k1 - k0);
+  // a pair verdict (sgmm_tc::kPair | a | b << 15): the argmin is one of two columns
+  const bool pair = valid && k1 > k0 && (v & 0xc0000000u) == 0x40000000u && (v & 0x7fffu) < k1 - k0 && ((v >> 15) & 0x7fffu) < k1 - k0;
+  const bool unc = valid && k1 > k0 && !(v < k1 - k0) && !pair;
   double best = 1e10;                            // min_score's start value, Mixtures.cpp:699
   uint32_t bk = 0;
   if (valid && k1 > k0 && !unc) {
-    const double sc = sgmm_exact_score_rm(p.m, p.x + f * p.m.dim, k0 + v);
-    if (sc < best) { best = sc; bk = v; }
+    const uint32_t ka = pair ? (v & 0x7fffu) : v;
+    const double sc = sgmm_exact_score_rm(p.m, p.x + f * p.m.dim, k0 + ka);
+    if (sc < best) { best = sc; bk = ka; }
+    if (pair) {
+      const uint32_t kb = (v >> 15) & 0x7fffu;     // kb > ka: on equal scores the lower column stays
+      const double sb = sgmm_exact_score_rm(p.m, p.x + f * p.m.dim, k0 + kb);
+      if (sb < best) { best = sb; bk = kb; }
+    }
   }
   uint32_t todo = __ballot_sync(0xffffffffu, unc);
   while (todo) {

@@ -1596,6 +1596,13 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
         const double sc = exact_score_unrolled<NP>(p.m, p.x + frame * p.m.dim, k0 + i1, xs_all + r * XS,
                                                    p.pooled ? iv_all + j * p.m.dimP : nullptr);
         if (sc < best) { best = sc; bk = i1; }
+      } else if ((i1 & kPair) && !(i1 & kUncertain) && (i1 & 0x7fffu) < k1 - k0 && ((i1 >> 15) & 0x7fffu) < k1 - k0) {
+        // pair verdict: the argmin is one of two columns (a < b) — both evaluated, the first minimum wins
+        const uint32_t ka = i1 & 0x7fffu, kb = (i1 >> 15) & 0x7fffu;
+        const double sa = sgmm_exact_score_rm(p.m, p.x + frame * p.m.dim, k0 + ka);
+        const double sb = sgmm_exact_score_rm(p.m, p.x + frame * p.m.dim, k0 + kb);
+        if (sa < best) { best = sa; bk = ka; }
+        if (sb < best) { best = sb; bk = kb; }
       } else {
         // one atomic per group of lanes that arrive here together (same-address atomics serialise at the L2)
         const uint32_t am = __activemask(), ln = threadIdx.x & 31u;
@@ -1632,7 +1639,8 @@ __device__ __forceinline__ double sm_exact(const double* row, double logw, const
   constexpr int NP = DIM / 2;
   static_assert(NP % 4 == 0, "dimension pairs are walked in blocks of four");
   double l0 = 0.0, l1 = 0.0;
-#pragma unroll
+  // (d >= 40: unrolled by two blocks only — fully unrolled, the compiler hoists every load of the 24 pairs and spills 400 B)
+#pragma unroll(NP > 20 ? 2 : 6)
   for (int g = 0; g < NP; g += 4) {          // four 16-byte units of the mean row in flight
     double2 mu[4];
     float xv[8];
@@ -1664,6 +1672,13 @@ __device__ __forceinline__ double sm_exact(const double* row, double logw, const
     dist = __dadd_rn(dist, __dmul_rn(__dmul_rn(c, c), CIV ? c_iv[ivoff + DIM - 1] : iv[DIM - 1]));
   }
   return __dsub_rn(__dadd_rn(row[DIM], __dmul_rn(dist, 0.5)), logw);
+}
+
+// one more density of the same cell, out of line (the second column of a pair verdict: ~8 % of the warps; inlined it
+// doubles the evaluation's register footprint on the main path)
+template <uint32_t DIM, bool VEC>
+__device__ __noinline__ double sm_exact_again(const double* row, double logw, const float* xr, const double* iv) {
+  return sm_exact<DIM, VEC, false>(row, logw, xr, iv, 0u);
 }
 
 // whole-state rescan of one cell, densities first, first + step, ... (out of line: only taken when the rescan list is full)
@@ -1859,7 +1874,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     double sc = sm_exact<DIM, !kOdd, CIV>(tbl + (size_t)ki * RW, lw[ki], my_xr, iv, ivoff);
     if (pair) {
       const uint32_t kb = (my_i1 >> 15) & 0x7fffu;
-      const double sb = sm_exact<DIM, !kOdd, false>(tbl + (size_t)kb * RW, lw[kb], my_xr, iv, 0u);
+      const double sb = sm_exact_again<DIM, !kOdd>(tbl + (size_t)kb * RW, lw[kb], my_xr, iv);
       if (sb < sc) { sc = sb; ki = kb; }               // kb > ki: on equal scores the lower column stays
     }
     if (act) {
@@ -2393,7 +2408,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.pack_colmap = c->d_pack_colmap.p;
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
-  p.pairs = (c->tc_pairs && !dense) ? 1 : 0;   // (the dense pass is refined by the frame-major kernel, which rescans pairs)
+  p.pairs = c->tc_pairs ? 1 : 0;
   if (c->tol && !dense) {
     if (!(f16 && !epi16 && !c->tc_full)) SGMM_FAIL(c, "tolerance mode: needs the fp16 tensor form (pooled model, 256-column tiles, tc_epi16 = 0)");
     SGMM_CHECK(c, c->d_e32.reserve(n_cells + 2));
