@@ -350,9 +350,12 @@ def test_fp16_operand_form_matches_tf32_and_oracle(scale):
     ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"]); ctx.set_tdp(*tdp, lex.silence_state)
     ctx.set_option("scorer", 3)
     fbs = []
-    for f16, epi16 in ((1, 0), (0, 0), (1, 0), (1, 1)):      # last: sixteen epilogue warps per unit (option tc_epi16)
+    # fourth: sixteen epilogue warps per unit (option tc_epi16; certified-only verdicts); fifth: the default epilogue
+    # without pair verdicts (option tc_pairs = 0)
+    for f16, epi16, pairs in ((1, 0, 1), (0, 0, 1), (1, 0, 1), (1, 1, 1), (1, 0, 0)):
         ctx.set_option("tc_f16", f16)
         ctx.set_option("tc_epi16", epi16)
+        ctx.set_option("tc_pairs", pairs)
         ctx.get_counter("fallbacks")
         got_s, got_a = ctx.score_all(0, n)
         fbs.append(ctx.get_counter("fallbacks"))
@@ -362,7 +365,8 @@ def test_fp16_operand_form_matches_tf32_and_oracle(scale):
         assert np.array_equal(got["state"].astype(np.uint32), want_states), f16
         assert np.array_equal(costs, want_costs), f16
     assert fbs[0] == fbs[2] and fbs[0] < 0.1 * want_s.size, fbs      # the fp16 form certifies nearly everything, too
-    assert fbs[3] <= 1.2 * fbs[0] + 16, fbs                          # finer column parts: at most a few more uncertain cells
+    assert fbs[3] <= 1.2 * fbs[4] + 16, fbs                          # finer column parts: at most a few more uncertain cells
+    assert fbs[0] <= fbs[4], fbs                                     # pair verdicts only ever take cells OUT of the rescan queue
     ctx.close()
 
 
@@ -630,3 +634,62 @@ def test_multiwarp_viterbi_long_utterances(beam):
         c, st, _ = O.align_pruned(corp["x"][f0:f1], aut, thr)
         assert c == res[1][3][u], (u, f1 - f0, len(aut))
         assert np.array_equal(res[1][2][f0:f1].astype(np.uint32), st), (u, f1 - f0, len(aut))
+
+
+def test_pair_verdicts_planted_near_ties():
+    """Pair verdicts of the tensor filter (option tc_pairs): near-duplicate densities planted so that the two candidates
+    of a cell sit in the same 64-column sub-part, in different sub-parts of one column part, in different column parts and
+    in different tiles; exact duplicates (the LOWER index must win, as in the reference's scan) and a triple (more than
+    two candidates: rescanned).  Dense scores / argmins (frame-major refinement) and alignments (state-major refinement)
+    equal the oracle's with and without the option, and the option takes cells out of the rescan queue."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(77)
+    dim, nd = 33, 300                                  # 300 densities: two tiles (256 + 44 columns) per state
+    lex = synth.Lexicon()
+    t = synth.random_model(rng, dim, lex.num_states, nd, "mixture")
+    means = t["means"].reshape(-1, dim)
+    off = t["mix_offsets"]
+    plant = {0: ((0, 1, 1e-9),),                       # same sub-part
+             1: ((3, 100, 1e-9),),                     # sub-parts 0 and 1 of column part 0
+             2: ((5, 200, 0.0),),                      # column parts 0 and 1, EXACT duplicate: index 5 wins
+             3: ((7, 280, 1e-10),),                    # tiles 0 and 1
+             4: ((2, 70, 0.0), (2, 140, 0.0)),         # a triple of exact duplicates: uncertain, rescanned, index 2 wins
+             5: ((63, 64, 1e-9),)}                     # across the sub-part boundary
+    for s, pairs in plant.items():
+        for a, b, rel in pairs:
+            means[off[s] + b] = means[off[s] + a] * (1.0 + rel)
+            t["mean_wlog"][off[s] + b] = t["mean_wlog"][off[s] + a]
+            t["mean_w"][off[s] + b] = t["mean_w"][off[s] + a]
+    # frames sitting ON the planted densities, so that those are the winners
+    corp = synth.make_corpus(rng, lex, t, dim, 8)
+    x = corp["x"].copy()
+    for i, (s, pairs) in enumerate(plant.items()):
+        for r in range(6):
+            x[40 * i + r] = (means[off[s] + pairs[0][0]] + 1e-3 * rng.standard_normal(dim)).astype(np.float32)
+    O = Oracle(dim, lex.num_states, "mixture", True, helpers.TDP, lex.silence_state)
+    O.load_tables(t)
+    n = 400
+    want_s, want_a = O.min_score(x[:n])
+    want_states, want_costs = O.align_batch(x, corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, t); ctx.set_features(x)
+    ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"]); ctx.set_tdp(*helpers.TDP, lex.silence_state)
+    ctx.set_option("scorer", 3)
+    assert ctx.get_counter("tc_form") == 1
+    fb = {}
+    for pairs in (1, 0):
+        ctx.set_option("tc_pairs", pairs)
+        ctx.get_counter("fallbacks")
+        got_s, got_a = ctx.score_all(0, n)
+        assert np.array_equal(got_a, want_a) and np.array_equal(got_s, want_s), pairs
+        got, costs = ctx.align()
+        fb[pairs] = ctx.get_counter("fallbacks")
+        assert np.array_equal(got["state"].astype(np.uint32), want_states) and np.array_equal(costs, want_costs), pairs
+    # the planted winners really are ties the filter cannot certify ...
+    assert fb[0] >= 30, fb
+    # ... and pair verdicts resolve most of them in place (the triple and the NaN-free leftovers stay)
+    assert fb[1] < fb[0], fb
+    for i, (s, pairs) in enumerate(plant.items()):
+        assert (want_a[40 * i:40 * i + 6, s] == min(p[0] for p in pairs)).all() or pairs[0][2] != 0.0
+    ctx.close()
