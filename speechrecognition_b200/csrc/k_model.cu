@@ -607,7 +607,7 @@ struct MstepParams {
 };
 
 // one block per state: means, weights, and the variances of NO / MIXTURE pooling
-__global__ void __launch_bounds__(128) k_mstep_state(MstepParams p) {
+__global__ void __launch_bounds__(512) k_mstep_state(MstepParams p) {
   extern __shared__ double shm[];     // [dim] pooled mean / variance scratch, [1] total
   const uint32_t s = blockIdx.x, d = p.dim;
   const uint32_t j0 = p.state_off[s], j1 = p.state_off[s + 1];
@@ -617,7 +617,15 @@ __global__ void __launch_bounds__(128) k_mstep_state(MstepParams p) {
   double* total = shm + d;
   if (threadIdx.x == 0) {             // total_mixture_observations: in-order sum from 0.0 (:381-386)
     double t = 0.0;
-    for (uint32_t j = j0; j < j1; j++) t = __dadd_rn(t, cnt[j]);
+    uint32_t j = j0;
+    for (; j + 8 <= j1; j += 8) {     // (eight loads in flight, added in order: the chain is the additions, not the L2)
+      double v[8];
+#pragma unroll
+      for (int q = 0; q < 8; q++) v[q] = cnt[j + q];
+#pragma unroll
+      for (int q = 0; q < 8; q++) t = __dadd_rn(t, v[q]);
+    }
+    for (; j < j1; j++) t = __dadd_rn(t, cnt[j]);
     *total = t;
     p.state_total[s] = t;
   }
@@ -654,7 +662,15 @@ __global__ void __launch_bounds__(128) k_mstep_state(MstepParams p) {
     // variance of the mixture around its pooled mean (:408-427): sums over the densities in order
     for (uint32_t i = threadIdx.x; i < d; i += blockDim.x) {
       double va = p.seed, pm = 0.0;
-      for (uint32_t j = j0; j < j1; j++) {
+      uint32_t j = j0;
+      for (; j + 8 <= j1; j += 8) {   // same in-order sums, eight densities' loads in flight
+        double a[8], b[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) { a[q] = sxx[(size_t)(j + q) * d + i]; b[q] = sx[(size_t)(j + q) * d + i]; }
+#pragma unroll
+        for (int q = 0; q < 8; q++) { va = __dadd_rn(va, a[q]); pm = __dadd_rn(pm, b[q]); }
+      }
+      for (; j < j1; j++) {
         va = __dadd_rn(va, sxx[(size_t)j * d + i]);
         pm = __dadd_rn(pm, sx[(size_t)j * d + i]);
       }
@@ -807,7 +823,7 @@ int sgmm_mstep(sgmm_ctx* c, int pooling, double var_seed) {
   p.pooling = pooling; p.seed = var_seed; p.dlog2pi = (double)dim * std::log(2 * M_PI);
   p.mean = m.d_mean_src.p; p.inv = m.d_inv_src.p; p.norm = m.d_norm.p; p.logw = m.d_logw.p;
   p.var = c->d_mstep_tmp.p; p.weight = p.var + (size_t)D * dim; p.state_total = p.weight + D; p.gvar = p.state_total + N;
-  k_mstep_state<<<N, 128, (dim + 2) * sizeof(double), c->stream>>>(p);
+  k_mstep_state<<<N, 512, (dim + 2) * sizeof(double), c->stream>>>(p);   // one block per state: 106 blocks at the bench shape, so wide ones
   SGMM_LAUNCH_CHECK(c);
   if (pooling == 2) {
     k_mstep_global<<<1, 128, 0, c->stream>>>(p);
