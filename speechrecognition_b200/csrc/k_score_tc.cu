@@ -401,6 +401,80 @@ __device__ __forceinline__ void tc_scan_onepass(uint32_t tcol, uint32_t c_lo, ui
   }
 }
 
+// ---- sum scores on the tensor path (option sum_tc): instead of a verdict, the epilogue writes for every
+// 64-column sub-part of a cell {candidate mask (64 bits), the sub-part's minimum ms, the width W}: bit e is set iff
+// accumulator column e lies below ms + W + 4e-6 |ms|, W = 45 (in accumulator units) + twice the certified error bound.
+// The local minimum is >= the state's minimum, so the mask is a SUPERSET of the densities within 45 of the best score —
+// the ones whose exp(-score) can change the f64 sum (k_sum_pruned's criterion); k_tc_refine_sm<.., SUM> evaluates them.
+// A threshold outside the exact-indicator range (NaN / inf rows) selects every column.
+template <int NB>
+__device__ __forceinline__ void tc_subpart_mask(const uint32_t (&v)[NB][16], float W, float& ms, uint32_t& lo, uint32_t& hi) {
+  float mm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+#pragma unroll
+  for (int b = 0; b < NB; b++) {
+#pragma unroll
+    for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(v[b][e]));
+  }
+  ms = fminf(fminf(mm[0], mm[1]), fminf(mm[2], mm[3]));
+  const float thr = ms + (W + 4e-6f * fabsf(ms)), nbig = -0x1p100f, T = thr * 0x1p100f;
+  const bool thr_ok = fabsf(thr) > 1e-20f && fabsf(thr) < 1e8f;
+  float a[NB];
+#pragma unroll
+  for (int b = 0; b < NB; b++) a[b] = 0.f;
+#pragma unroll
+  for (int e = 0; e < 16; e++) {
+#pragma unroll
+    for (int b = 0; b < NB; b++) {
+      const float c = __saturatef(fmaf(__uint_as_float(v[b][e]), nbig, T));
+      a[b] = fmaf(c, (float)(1u << e), a[b]);
+    }
+  }
+  uint32_t mk[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+  for (int b = 0; b < NB; b++) mk[b] = __float_as_uint(a[b] + 8388608.f);
+  lo = __byte_perm(mk[0], mk[1], 0x5410);
+  hi = NB > 2 ? __byte_perm(mk[2], mk[3], 0x5410) : 0u;
+  if (!thr_ok) { lo = 0xffffffffu; hi = 0xffffffffu; }
+}
+
+// the one-pass scan in mask mode: columns [c_lo, c_hi) of the state's ONLY tile; out = the cell's four entries
+// (sub-part = columns / 64), or NULL for rows / columns that are not stored
+template <int NB>
+__device__ __forceinline__ void tc_scan_masks(uint32_t tcol, uint32_t c_lo, uint32_t c_hi, float W, uint64_t* release_bar,
+                                              int lane, uint4* out) {
+  bool released = false;
+  for (uint32_t s_lo = c_lo; s_lo < c_hi; s_lo += 16 * NB) {
+    uint32_t v[NB][16];
+    const bool last = s_lo + 16 * NB >= c_hi;
+#pragma unroll
+    for (int b = 0; b < NB; b++) {
+      if (s_lo + 16 * b < c_hi) tc_ld16_nowait(tcol + s_lo + 16 * b, v[b]);
+      else {
+#pragma unroll
+        for (int e = 0; e < 16; e++) v[b][e] = 0x7f800000u;   // +inf: never below a threshold
+      }
+    }
+    tc_ld_wait(v[0]);
+#pragma unroll
+    for (int b = 1; b < NB; b++) tc_ld_pin(v[b]);
+    if (last) {
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(release_bar);
+      released = true;
+    }
+    float ms;
+    uint32_t lo, hi;
+    tc_subpart_mask<NB>(v, W, ms, lo, hi);
+    if (out) out[s_lo / (16 * NB)] = make_uint4(lo, hi, __float_as_uint(ms), __float_as_uint(W));
+  }
+  if (!released) {
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(release_bar);
+  }
+}
+
 // tc_scan_onepass with the candidate bookkeeping of TcBest (columns relative to the tile)
 template <int NB>
 __device__ __forceinline__ void tc_scan_onepass2(uint32_t tcol, uint32_t c_lo, uint32_t c_hi, float Gs, uint64_t* release_bar,
@@ -647,6 +721,7 @@ struct TcParams {
   // column of the certified minimum within the state's (padded) density list, or kUncertain
   uint32_t* cand;
   unsigned long long* prof;   // cycle profile (debug & 32), else NULL
+  uint4* summask;             // mask mode (sum scores on the tensor path): [cell][4] entries, see tc_subpart_mask; else NULL
   int pairs;                  // default epilogue of k_tc_gemm256: emit pair verdicts (option tc_pairs; 0: such cells are uncertain)
   int tol;                    // tolerance mode (fp16 form, k_tc_gemm256): besides the verdict, e32[cell] = min accumulator / (s_f t_s)
   float* e32;                 // = the state's best score minus the frame's x^2 term (k_tol_finish adds it)
@@ -1337,7 +1412,12 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           const uint32_t tcol = tlane + buf * 256;
           const uint32_t c_lo = part * 128, c_hi = min(N, c_lo + 128);
           float m = INFINITY, acc = 0.f, idx = 0.f, G = 0.f;
-          if (!(p.debug & 128)) {
+          if (F16 && p.summask) {
+            // mask mode: 45 in accumulator units (s_f t_s = xn.y / g.w) + twice the certified bound; single-tile states
+            const uint32_t col = my_map ? (uint32_t)my_map[j] : j;
+            uint4* out = (row < nvalid && (col != 0xFFFFu || !my_map)) ? p.summask + 4 * tc_cell(my_cell, col, true) : nullptr;
+            tc_scan_masks<4>(tcol, c_lo, c_hi, 45.f * (xn.y / g.w) + 2.f * Gs, &tempty[buf], lane, out);
+          } else if (!(p.debug & 128)) {
             // one pass over tensor memory (default); tc_debug & 128 keeps the two-pass scan below as the A/B reference
             TcBest st;
             tc_scan_onepass2<4>(tcol, c_lo, c_hi, Gs, &tempty[buf], lane, p.debug, st);
@@ -1409,7 +1489,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
             if (col != 0xFFFFu || !my_map) {
               const uint64_t cell = tc_cell(my_cell, col, !p.dense);
               if (!p.pairs && (vd & kPair) && !(vd & kUncertain)) vd = kUncertain;
-              p.cand[cell] = vd;
+              if (!(F16 && p.summask)) p.cand[cell] = vd;
               if (F16 && p.tol) p.e32[cell] = B.m * (g.w / xn.y);
             }
           }
@@ -1465,6 +1545,7 @@ struct RefineParams {
   uint32_t sm_rw;              // doubles per table row: mean row, norm, padding (2 * odd: bank spread for LDS.128)
   uint32_t sm_maxnd;           // most densities in one state
   const uint32_t* sm_ivoff;    // per item: first double of its state's inverse-variance row in invU / c_iv (k_sm_ivoff)
+  const uint4* summask;        // SUM: the filter's candidate masks, [cell][4] (tc_subpart_mask)
   uint32_t sm_lq;              // entries of the CTA-local near-tie list (0: none, every near-tie goes straight to the global queue)
   // two-stage rescan: f32 tables of the FFMA scorer ([D][4 * dv4] mean and h = 1 / (2 var), c = norm - log w) and
   // the per-state constants of its certified error bound {cmin, |c| max, M max}
@@ -1719,7 +1800,10 @@ __global__ void k_sm_ivoff(const uint4* __restrict__ items, uint32_t n, const ui
 //     cells first so that the 8 lanes of a quarter-warp (one LDS.128 wavefront group) gather table rows from different
 //     16-byte bank groups (a row's group is (winner + unit) mod 8).
 // Near-tie cells are queued for k_tc_rescan as in the frame-major kernel.
-template <uint32_t DIM, bool CIV>   // CIV: the model's inverse-variance rows are in the constant bank (c_iv)
+// SUM (sum scores on the tensor path): the cell's input is not a verdict but the filter's candidate masks
+// (tc_subpart_mask); every candidate density is evaluated exactly and  -log sum_k exp(-score_k)  is accumulated in density
+// order (Mixtures.cpp:719-728) — k_sum_pruned's result with the f32 stage replaced by the tensor filter.
+template <uint32_t DIM, bool CIV, bool SUM = false>   // CIV: the model's inverse-variance rows are in the constant bank (c_iv)
 __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
   constexpr uint32_t kMaxEnt = kSmMaxEntries, kMaxChunks = kSmMaxChunks;
@@ -1802,7 +1886,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     // first cell of the chunk's first 16-frame tile, in the state's column; lane l is frame t0 + l:
     //   cell = tile0 + (l >> 4) * 16 ncol + ((l ^ col) & 15)
     ck.tile0 = (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)(t0 >> 4) * (16u * ncol) + (ck.col << 4);
-    if (lane < ck.nvalid) {
+    if (!SUM && lane < ck.nvalid) {
       const uint64_t cell = ck.tile0 + (uint64_t)(lane >> 4) * (16u * ncol) + ((lane ^ ck.col) & 15u);
       asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(verdict + b * 32 + lane)), "l"(p.cand + cell) : "memory");
     }
@@ -1837,6 +1921,45 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     if (more) nxt = issue(j + nwarp, b ^ 1u);
     const uint32_t ncol = (uint32_t)(cur.tile0 >> 48);
     const uint64_t tile0 = cur.tile0 & 0xffffffffffffull;
+    if (SUM) {
+      // ---- sum scores: lane = frame (no lane swap: every lane walks its own candidate list)
+      const bool act = lane < cur.nvalid;
+      const uint64_t my_cell = tile0 + (uint64_t)(lane >> 4) * (16u * ncol) + ((lane ^ cur.col) & 15u);
+      const float* my_xr = reinterpret_cast<const float*>(tiles + b * kTileB + (kOdd ? cur.al + lane * kRowB : lane * kRowS));
+      uint4 ent[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) ent[q] = act ? __ldg(p.summask + 4 * my_cell + q) : make_uint4(0u, 0u, 0x7f800000u, 0u);
+      mbar_wait(bar + b, (phases >> b) & 1u);
+      phases ^= 1u << b;
+      // sub-parts whose minimum is more than W above the cell's minimum hold nothing within 45 of it
+      float gmin = INFINITY;
+#pragma unroll
+      for (int q = 0; q < 4; q++)
+        if (64u * q < nd) gmin = fminf(gmin, __uint_as_float(ent[q].z));
+      double acc = 0.0;                                       // Mixtures.cpp:721
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        if (64u * q >= nd) break;                             // (warp-uniform)
+        const float msq = __uint_as_float(ent[q].z), Wq = __uint_as_float(ent[q].w);
+        const bool keep = act && !(msq > gmin + Wq + 8e-6f * fabsf(gmin));    // NaN: kept
+        unsigned long long bits = keep ? ((unsigned long long)ent[q].y << 32) | ent[q].x : 0ull;
+        while (__any_sync(0xffffffffu, bits != 0ull)) {       // the densities in index order
+          const bool has = bits != 0ull;
+          const uint32_t k = 64u * q + (has ? (uint32_t)__ffsll((long long)bits) - 1u : 0u);
+          bits &= bits - 1ull;
+          const bool ok = has && k < nd;                      // (padding columns of the tile carry no density)
+          const uint32_t ki = ok ? k : 0u;
+          const double sck = sm_exact<DIM, !kOdd, CIV>(tbl + (size_t)ki * RW, lw[ki], my_xr, iv, ivoff);
+          if (ok) acc = __dadd_rn(acc, exp(-sck));
+        }
+      }
+      if (act) {
+        p.out[my_cell] = -log(acc);                           // :727
+        if (p.amin16) p.amin16[my_cell] = 0;
+      }
+      cur = nxt;
+      continue;
+    }
     // this chunk's verdicts have landed (the next chunk's group may still be in flight); each lane reads its own slot
     if (more) asm volatile("cp.async.wait_group 1;" ::: "memory");
     else asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -2409,7 +2532,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   p.dense = dense ? 1 : 0; p.f0 = dense_f0; p.nframes = dense_nframes; p.n_states = c->n_states;
   p.cand = c->d_ci1.p;
   p.pairs = c->tc_pairs ? 1 : 0;
-  if (c->tol && !dense) {
+  if (c->tol && !dense && !c->tc_sum_pass) {
     if (!(f16 && !epi16 && !c->tc_full)) SGMM_FAIL(c, "tolerance mode: needs the fp16 tensor form (pooled model, 256-column tiles, tc_epi16 = 0)");
     SGMM_CHECK(c, c->d_e32.reserve(n_cells + 2));
     p.tol = 1; p.e32 = c->d_e32.p;
@@ -2454,6 +2577,14 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   const bool sm_can = !dense && !c->tc_full && sm_dim && sm_warps >= 8 && c->n_sm_items > 0 && c->n_frames < 0xffffffffull &&
                       c->max_uniq < 0xffffu;
   const bool use_sm = sm_can && c->tc_refine != 1;
+  if (c->tc_sum_pass && !(f16 && !epi16 && nhalf == 2 && sm_can && sm_maxnd <= 256)) {
+    c->tc_sum_pass = false;   // not this shape: the caller falls back to k_sum_pruned (nothing has been launched yet)
+    return 0;
+  }
+  if (c->tc_sum_pass) {       // 64 B per cell: four {mask, minimum, width} entries
+    SGMM_CHECK(c, c->d_summask.reserve(4 * (n_cells + 2)));
+    p.summask = c->d_summask.p;
+  }
   r.sm_items = c->d_sm_items.p; r.sm_ent_a = c->d_sm_ent_a.p; r.sm_ent_b = c->d_sm_ent_b.p;
   r.sm_rw = sm_rw; r.sm_maxnd = sm_maxnd; r.sm_lq = sm_lq;
   const bool one = ranges.size() == 1;
@@ -2520,6 +2651,37 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   if (!one)
     for (size_t ri = 0; ri < ranges.size(); ri++) SGMM_CHECK(c, cudaStreamWaitEvent(c->stream, c->ev_join[ri], 0));
   sgmm_stage_end(c, SGMM_T_SCORE_FILTER);
+  if (c->tc_sum_pass) {
+    // every candidate of every cell evaluated exactly, summed in density order: the state-major kernel in SUM form
+    sgmm_stage_begin(c, SGMM_T_SCORE_REFINE);
+    const unsigned sgrid = (unsigned)c->n_sm_items;
+    SGMM_CHECK(c, c->d_sm_ivoff.reserve(sgrid));
+    k_sm_ivoff<<<(sgrid + 255) / 256, 256, 0, c->stream>>>(c->d_sm_items.p, sgrid, c->d_state_off.p, c->d_var_of.p, c->dimP, c->d_sm_ivoff.p);
+    SGMM_LAUNCH_CHECK(c);
+    r.sm_ivoff = c->d_sm_ivoff.p; r.summask = c->d_summask.p; r.sm_lq = 0;
+    const size_t sum_smem = sm_tiles;
+    bool civ = false;
+    if (refine_civ_bind(c, &civ)) return 1;
+#define SGMM_SUM_CASE(D)                                                                                                  \
+  case D:                                                                                                                 \
+    if (civ) {                                                                                                            \
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sum_smem));  \
+      k_tc_refine_sm<D, true, true><<<sgrid, 32 * sm_warps, sum_smem, c->stream>>>(r);                                    \
+    } else {                                                                                                              \
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sum_smem)); \
+      k_tc_refine_sm<D, false, true><<<sgrid, 32 * sm_warps, sum_smem, c->stream>>>(r);                                   \
+    }                                                                                                                     \
+    break;
+    switch (c->dim) {
+      SGMM_SUM_CASE(24) SGMM_SUM_CASE(25) SGMM_SUM_CASE(32) SGMM_SUM_CASE(33) SGMM_SUM_CASE(48) SGMM_SUM_CASE(49)
+      default: if (civ) refine_civ_release(c); SGMM_FAIL(c, "sum scores on the tensor path: unsupported dimension");
+    }
+#undef SGMM_SUM_CASE
+    SGMM_LAUNCH_CHECK(c);
+    if (civ && refine_civ_release(c)) return 1;
+    sgmm_stage_end(c, SGMM_T_SCORE_REFINE);
+    return 0;
+  }
   if (p.tol) {
     // tolerance mode: e32 holds f32 scores minus the x^2 term; add it, and that is the emission matrix Viterbi reads
     // (the verdicts stay in d_ci1: the E-step looks the aligned cells' winners up there, k_rescore_verdict)
@@ -2608,6 +2770,15 @@ int sgmm_launch_emission_sum_pruned(sgmm_ctx* c, bool dense, uint64_t dense_f0, 
   using namespace sgmm_tc;
   *handled = false;
   if (!c->sum_prune || !(c->dv4 == 7 || c->dv4 == 9 || c->dv4 == 12 || c->dv4 == 16) || !c->d_mu32T.p) return 0;
+  if (!dense && c->sum_tc && c->tc_ok && sgmm_effective_scorer(c) == 3) {
+    // the tensor filter names the densities within 45 of each cell's best score, the state-major kernel sums them
+    c->tc_sum_pass = true;
+    const int rc = sgmm_launch_emission_tc(c, false, 0, 0, nullptr, nullptr);
+    const bool done = c->tc_sum_pass;
+    c->tc_sum_pass = false;
+    if (rc) return rc;
+    if (done) { *handled = true; return 0; }
+  }
   RefineParams r{};
   r.m.meanT = c->d_meanT.p; r.m.invT = c->d_invT.p; r.m.mean_tail = c->d_mean_tail.p; r.m.inv_tail = c->d_inv_tail.p;
   r.m.norm = c->d_norm.p; r.m.logw = c->d_logw.p; r.m.dim = c->dim; r.m.npair = c->npair; r.m.Dtot = c->Dtot;

@@ -151,6 +151,7 @@ struct sgmm_ctx : SgmmModel {
   DevBuf<float> d_Ahi, d_Alo;
   DevBuf<float2> d_xnorm;
   DevBuf<uint32_t> d_ci1;
+  DevBuf<uint4> d_summask;         // sum scores on the tensor path: [cell][4] {mask lo, mask hi, sub-part minimum, width}
   DevBuf<float> d_e32;             // tolerance mode: the f32 emission matrix (cell-indexed like d_E)
   DevBuf<unsigned long long> d_rescan;   // [0] = count, [1..] = cell ids
   size_t rescan_cap = 0;
@@ -199,6 +200,8 @@ struct sgmm_ctx : SgmmModel {
   int tol = 0;                     // option "tolerance" (experiment, default off): Viterbi consumes the tensor filter's f32 scores; no
                                    // refinement; only the aligned cells are re-scored in f64 (K3).  NOT bit-identical to the reference.
   bool tol_active = false;         // the last alignment pass ran in tolerance mode (its emission matrix is f32: d_e32)
+  int sum_tc = 1;                  // option "sum_tc": sum scores of the gathered pass through the tensor filter's candidate masks (0: k_sum_pruned)
+  bool tc_sum_pass = false;        // set around sgmm_launch_emission_tc by the sum-score launcher
   int tc_pairs = 1;                // option "tc_pairs": the filter names the TWO candidate columns of a near-tie (refined in place) instead of "uncertain"
   int tc_civ = 1;                  // option "tc_civ": state-major refinement reads the inverse variances from the constant bank (0: shared memory)
   int tc_lq = 1;                   // option "tc_lq": state-major refinement queues an item's near-ties as one run (0: cell by cell)
