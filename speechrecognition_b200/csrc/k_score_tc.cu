@@ -402,20 +402,14 @@ __device__ __forceinline__ void tc_scan_onepass(uint32_t tcol, uint32_t c_lo, ui
 }
 
 // ---- sum scores on the tensor path (option sum_tc): instead of a verdict, the epilogue writes for every
-// 64-column sub-part of a cell {candidate mask (64 bits), the sub-part's minimum ms, the width W}: bit e is set iff
-// accumulator column e lies below ms + W + 4e-6 |ms|, W = 45 (in accumulator units) + twice the certified error bound.
-// The local minimum is >= the state's minimum, so the mask is a SUPERSET of the densities within 45 of the best score —
+// 64-column sub-part of a cell {candidate mask (64 bits), the state's minimum gm, the width W}: bit e is set iff
+// accumulator column e lies below gm + W + 4e-6 |gm|, W = 45 (in accumulator units) + twice the certified error bound.
+// By the bound the mask is a SUPERSET of the densities within 45 of the best exact score —
 // the ones whose exp(-score) can change the f64 sum (k_sum_pruned's criterion); k_tc_refine_sm<.., SUM> evaluates them.
 // A threshold outside the exact-indicator range (NaN / inf rows) selects every column.
 template <int NB>
-__device__ __forceinline__ void tc_subpart_mask(const uint32_t (&v)[NB][16], float W, float& ms, uint32_t& lo, uint32_t& hi) {
-  float mm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
-#pragma unroll
-  for (int b = 0; b < NB; b++) {
-#pragma unroll
-    for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(v[b][e]));
-  }
-  ms = fminf(fminf(mm[0], mm[1]), fminf(mm[2], mm[3]));
+__device__ __forceinline__ void tc_subpart_mask(const uint32_t (&v)[NB][16], float W, float ms, uint32_t& lo, uint32_t& hi) {
+  // ms: the minimum the threshold hangs on (the whole state's, exchanged between the column parts before this pass)
   const float thr = ms + (W + 4e-6f * fabsf(ms)), nbig = -0x1p100f, T = thr * 0x1p100f;
   const bool thr_ok = fabsf(thr) > 1e-20f && fabsf(thr) < 1e8f;
   float a[NB];
@@ -437,11 +431,37 @@ __device__ __forceinline__ void tc_subpart_mask(const uint32_t (&v)[NB][16], flo
   if (!thr_ok) { lo = 0xffffffffu; hi = 0xffffffffu; }
 }
 
-// the one-pass scan in mask mode: columns [c_lo, c_hi) of the state's ONLY tile; out = the cell's four entries
-// (sub-part = columns / 64), or NULL for rows / columns that are not stored
+// mask mode, pass 1: the minimum of accumulator columns [c_lo, c_hi) of this thread's row
 template <int NB>
-__device__ __forceinline__ void tc_scan_masks(uint32_t tcol, uint32_t c_lo, uint32_t c_hi, float W, uint64_t* release_bar,
-                                              int lane, uint4* out) {
+__device__ __forceinline__ float tc_part_min(uint32_t tcol, uint32_t c_lo, uint32_t c_hi) {
+  float mm[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+  for (uint32_t s_lo = c_lo; s_lo < c_hi; s_lo += 16 * NB) {
+    uint32_t v[NB][16];
+#pragma unroll
+    for (int b = 0; b < NB; b++) {
+      if (s_lo + 16 * b < c_hi) tc_ld16_nowait(tcol + s_lo + 16 * b, v[b]);
+      else {
+#pragma unroll
+        for (int e = 0; e < 16; e++) v[b][e] = 0x7f800000u;
+      }
+    }
+    tc_ld_wait(v[0]);
+#pragma unroll
+    for (int b = 1; b < NB; b++) tc_ld_pin(v[b]);
+#pragma unroll
+    for (int b = 0; b < NB; b++) {
+#pragma unroll
+      for (int e = 0; e < 16; e++) mm[e & 3] = fminf(mm[e & 3], __uint_as_float(v[b][e]));
+    }
+  }
+  return fminf(fminf(mm[0], mm[1]), fminf(mm[2], mm[3]));
+}
+
+// mask mode, pass 2: columns [c_lo, c_hi) of the state's ONLY tile against the state's minimum gm; out = the cell's four
+// entries (sub-part = columns / 64), or NULL for rows / columns that are not stored
+template <int NB>
+__device__ __forceinline__ void tc_scan_masks(uint32_t tcol, uint32_t c_lo, uint32_t c_hi, float W, float gm,
+                                              uint64_t* release_bar, int lane, uint4* out) {
   bool released = false;
   for (uint32_t s_lo = c_lo; s_lo < c_hi; s_lo += 16 * NB) {
     uint32_t v[NB][16];
@@ -463,10 +483,9 @@ __device__ __forceinline__ void tc_scan_masks(uint32_t tcol, uint32_t c_lo, uint
       if (lane == 0) mbar_arrive(release_bar);
       released = true;
     }
-    float ms;
     uint32_t lo, hi;
-    tc_subpart_mask<NB>(v, W, ms, lo, hi);
-    if (out) out[s_lo / (16 * NB)] = make_uint4(lo, hi, __float_as_uint(ms), __float_as_uint(W));
+    tc_subpart_mask<NB>(v, W, gm, lo, hi);
+    if (out) out[s_lo / (16 * NB)] = make_uint4(lo, hi, __float_as_uint(gm), __float_as_uint(W));
   }
   if (!released) {
     tc_fence_before();
@@ -1416,7 +1435,14 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
             // mask mode: 45 in accumulator units (s_f t_s = xn.y / g.w) + twice the certified bound; single-tile states
             const uint32_t col = my_map ? (uint32_t)my_map[j] : j;
             uint4* out = (row < nvalid && (col != 0xFFFFu || !my_map)) ? p.summask + 4 * tc_cell(my_cell, col, true) : nullptr;
-            tc_scan_masks<4>(tcol, c_lo, c_hi, 45.f * (xn.y / g.w) + 2.f * Gs, &tempty[buf], lane, out);
+            // pass 1: this part's minimum; the two column parts of a (half, quarter) swap theirs through the exchange
+            // slots, so that pass 2's threshold hangs on the STATE's minimum (masks relative to a sub-part's own
+            // minimum held 3x the candidates: measured 10.4 ms of summation per 13 M cells)
+            float* mslot = my_x + (j & 1) * (2 * BM * 5);
+            mslot[part] = tc_part_min<4>(tcol, c_lo, c_hi);
+            asm volatile("bar.sync %0, 64;" ::"r"(1 + group * 4 + quarter) : "memory");
+            const float gm = fminf(mslot[0], mslot[1]);
+            tc_scan_masks<4>(tcol, c_lo, c_hi, 45.f * (xn.y / g.w) + 2.f * Gs, gm, &tempty[buf], lane, out);
           } else if (!(p.debug & 128)) {
             // one pass over tensor memory (default); tc_debug & 128 keeps the two-pass scan below as the A/B reference
             TcBest st;
@@ -1838,7 +1864,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
   unsigned long long* lq = reinterpret_cast<unsigned long long*>(tail + 304 * nwarp + (size_t)nwarp * 2 * kTileB);   // [sm_lq] {cell, frame}
   uint32_t* lq_n = reinterpret_cast<uint32_t*>(lq + 2 * p.sm_lq);            // {entries, -, first slot of the run lo, hi}
   uint32_t n_rescans = 0;
-  if (threadIdx.x == 0) lq_n[0] = 0u;
+  if (p.sm_lq && threadIdx.x == 0) lq_n[0] = 0u;   // (no list: nothing is allocated behind the tiles)
 
   if (lane == 0) { mbar_init(bar, 1); mbar_init(bar + 1, 1); }
   for (uint32_t i = threadIdx.x; i < nd * dimP; i += nthr) {
@@ -1931,27 +1957,25 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
       for (int q = 0; q < 4; q++) ent[q] = act ? __ldg(p.summask + 4 * my_cell + q) : make_uint4(0u, 0u, 0x7f800000u, 0u);
       mbar_wait(bar + b, (phases >> b) & 1u);
       phases ^= 1u << b;
-      // sub-parts whose minimum is more than W above the cell's minimum hold nothing within 45 of it
-      float gmin = INFINITY;
+      // the lane's candidates: the four sub-parts' masks, walked in density order; a warp iteration evaluates every
+      // lane's NEXT candidate (so a chunk takes as many iterations as its busiest cell has candidates)
+      unsigned long long bits[4];
 #pragma unroll
       for (int q = 0; q < 4; q++)
-        if (64u * q < nd) gmin = fminf(gmin, __uint_as_float(ent[q].z));
+        bits[q] = (act && 64u * q < nd) ? (((unsigned long long)ent[q].y << 32) | ent[q].x) : 0ull;
       double acc = 0.0;                                       // Mixtures.cpp:721
-#pragma unroll
-      for (int q = 0; q < 4; q++) {
-        if (64u * q >= nd) break;                             // (warp-uniform)
-        const float msq = __uint_as_float(ent[q].z), Wq = __uint_as_float(ent[q].w);
-        const bool keep = act && !(msq > gmin + Wq + 8e-6f * fabsf(gmin));    // NaN: kept
-        unsigned long long bits = keep ? ((unsigned long long)ent[q].y << 32) | ent[q].x : 0ull;
-        while (__any_sync(0xffffffffu, bits != 0ull)) {       // the densities in index order
-          const bool has = bits != 0ull;
-          const uint32_t k = 64u * q + (has ? (uint32_t)__ffsll((long long)bits) - 1u : 0u);
-          bits &= bits - 1ull;
-          const bool ok = has && k < nd;                      // (padding columns of the tile carry no density)
-          const uint32_t ki = ok ? k : 0u;
-          const double sck = sm_exact<DIM, !kOdd, CIV>(tbl + (size_t)ki * RW, lw[ki], my_xr, iv, ivoff);
-          if (ok) acc = __dadd_rn(acc, exp(-sck));
-        }
+      while (__any_sync(0xffffffffu, (bits[0] | bits[1] | bits[2] | bits[3]) != 0ull)) {
+        const uint32_t q = bits[0] ? 0u : (bits[1] ? 1u : (bits[2] ? 2u : 3u));
+        const unsigned long long cur_bits = q == 0u ? bits[0] : (q == 1u ? bits[1] : (q == 2u ? bits[2] : bits[3]));
+        const bool has = cur_bits != 0ull;
+        const uint32_t k = 64u * q + (has ? (uint32_t)__ffsll((long long)cur_bits) - 1u : 0u);
+        const unsigned long long rest = cur_bits & (cur_bits - 1ull);
+        bits[0] = q == 0u ? rest : bits[0]; bits[1] = q == 1u ? rest : bits[1];
+        bits[2] = q == 2u ? rest : bits[2]; bits[3] = q == 3u ? rest : bits[3];
+        const bool ok = has && k < nd;                        // (padding columns of the tile carry no density)
+        const uint32_t ki = ok ? k : 0u;
+        const double sck = sm_exact<DIM, !kOdd, CIV>(tbl + (size_t)ki * RW, lw[ki], my_xr, iv, ivoff);
+        if (ok) acc = __dadd_rn(acc, exp(-sck));
       }
       if (act) {
         p.out[my_cell] = -log(acc);                           // :727

@@ -174,3 +174,49 @@ def test_soft_accumulation_many_states():
     assert np.array_equal(np.isnan(cnt2), np.isnan(want2)) and np.isnan(cnt2).sum() == nd
     assert np.isinf(ssum2)
     ctx.close()
+
+
+@pytest.mark.parametrize("dim,nd", [(33, 200), (32, 256), (25, 70)])
+def test_sum_scores_on_the_tensor_path(dim, nd):
+    """Option sum_tc (default on): the gathered alignment pass with sum scores takes the tensor filter's candidate masks
+    (densities within 45 of a cell's best score, a certified superset) and the state-major kernel in SUM form instead of
+    k_sum_pruned's f32 stage.  Same criterion, same f64 evaluation, same summation order: the two paths must agree to the
+    last bit on alignments and to 1e-15 on path costs, and both with the oracle (1e-12).  Includes a frame with a huge
+    feature (its row of the filter is NaN: every density is a candidate) and planted duplicate densities."""
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(100 + dim)
+    lex = synth.Lexicon()
+    t = synth.random_model(rng, dim, lex.num_states, nd, "mixture")
+    means = t["means"].reshape(-1, dim)
+    off = t["mix_offsets"]
+    means[off[2] + 9] = means[off[2] + 1]                 # duplicates: both within 45 of each other, always
+    means[off[3] + nd - 1] = means[off[3]] * (1 + 1e-7)
+    corp = synth.make_corpus(rng, lex, t, dim, 20)
+    x = corp["x"].copy()
+    x[11, 3] = 3.0e6                                       # beyond the fp16 row scaling
+    P = Oracle(dim, lex.num_states, "mixture", False, helpers.TDP, lex.silence_state)
+    P.load_tables(t)
+    want_states, want_costs = P.align_batch(x, corp["frame_off"], corp["automata"], corp["aut_off"], threads=8)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, t); ctx.set_features(x)
+    ctx.set_corpus(corp["frame_off"], corp["automata"], corp["aut_off"]); ctx.set_tdp(*helpers.TDP, lex.silence_state)
+    ctx.set_option("scorer", 3)
+    ctx.set_option("max_approx", 0)
+    got = {}
+    for tc in (1, 0):
+        ctx.set_option("sum_tc", tc)
+        ali, costs = ctx.align()
+        st = ctx.stage_ms()
+        got[tc] = (ali["state"].copy(), costs.copy(), st["score_filter"])
+        fin = np.isfinite(want_costs)
+        assert np.array_equal(ali["state"].astype(np.uint32), want_states), tc
+        np.testing.assert_allclose(costs[fin], want_costs[fin], rtol=RTOL)
+        am = P.am_score(want_states, x)
+        assert abs(ctx.am_score_sum() / len(want_states) - am) <= RTOL * abs(am) or not np.isfinite(am)
+    # the tensor filter ran in the first pass only — and not at all for the narrow model (70 densities per state take
+    # the 128-column tiles, which have no mask mode: the option falls back to k_sum_pruned by itself)
+    assert (got[1][2] > 0.0) == (nd > 128) and got[0][2] == 0.0
+    assert np.array_equal(got[1][0], got[0][0])
+    fin = np.isfinite(got[0][1])
+    np.testing.assert_allclose(got[1][1][fin], got[0][1][fin], rtol=1e-15)
+    ctx.close()
