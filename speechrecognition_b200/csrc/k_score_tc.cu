@@ -1096,7 +1096,9 @@ __device__ __forceinline__ TcMeta tc_meta_load(const TcParams& p, const uint32_t
 // E16: all sixteen epilogue warps work on every unit — warp = (lane quarter, one of four 64-column parts), each thread
 // owning the same row of BOTH halves — so that an accumulator is handed back in about half the time; the parts of a
 // (half, quarter) meet through shared memory once per state (three writers, one reader, 128-thread named barrier).
-template <int KS, bool F16, bool E16 = false>
+// MASK: the mask mode of the sum scores (tc_subpart_mask) — an instantiation of its own: compiled into the default kernel,
+// the extra path cost the max-approx filter 0.45 ms (3.95 -> 4.41), measured.
+template <int KS, bool F16, bool E16 = false, bool MASK = false>
 __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -1431,7 +1433,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           const uint32_t tcol = tlane + buf * 256;
           const uint32_t c_lo = part * 128, c_hi = min(N, c_lo + 128);
           float m = INFINITY, acc = 0.f, idx = 0.f, G = 0.f;
-          if (F16 && p.summask) {
+          if (MASK) {
             // mask mode: 45 in accumulator units (s_f t_s = xn.y / g.w) + twice the certified bound; single-tile states
             const uint32_t col = my_map ? (uint32_t)my_map[j] : j;
             uint4* out = (row < nvalid && (col != 0xFFFFu || !my_map)) ? p.summask + 4 * tc_cell(my_cell, col, true) : nullptr;
@@ -1515,7 +1517,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
             if (col != 0xFFFFu || !my_map) {
               const uint64_t cell = tc_cell(my_cell, col, !p.dense);
               if (!p.pairs && (vd & kPair) && !(vd & kUncertain)) vd = kUncertain;
-              if (!(F16 && p.summask)) p.cand[cell] = vd;
+              if (!MASK) p.cand[cell] = vd;
               if (F16 && p.tol) p.e32[cell] = B.m * (g.w / xn.y);
             }
           }
@@ -2646,11 +2648,21 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
         SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<3, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_tc_gemm256<3, true, true><<<grid, 576, smem, st>>>(p);
       } else if (f16 && ks == 3) {   // d = 32..46 pooled, fp16 operands
-        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_tc_gemm256<3, true><<<grid, 576, smem, st>>>(p);
+        if (p.summask) {
+          SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<3, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+          k_tc_gemm256<3, true, false, true><<<grid, 576, smem, st>>>(p);
+        } else {
+          SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+          k_tc_gemm256<3, true><<<grid, 576, smem, st>>>(p);
+        }
       } else if (f16) {
-        SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_tc_gemm256<0, true><<<grid, 576, smem, st>>>(p);
+        if (p.summask) {
+          SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<0, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+          k_tc_gemm256<0, true, false, true><<<grid, 576, smem, st>>>(p);
+        } else {
+          SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+          k_tc_gemm256<0, true><<<grid, 576, smem, st>>>(p);
+        }
       } else if (wide && ks == 5) {
         SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<5, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_tc_gemm256<5, false><<<grid, 576, smem, st>>>(p);
