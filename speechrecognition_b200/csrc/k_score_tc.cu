@@ -52,6 +52,15 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+#ifndef SGMM_TC_TWOPASS_REF
+#define SGMM_TC_TWOPASS_REF 0
+#endif
+constexpr bool kTwoPassRef = SGMM_TC_TWOPASS_REF != 0;   // keep the round-1 two-pass epilogue as an A/B reference (tc_debug & 128)
+#ifndef SGMM_TC_PROF
+#define SGMM_TC_PROF 0
+#endif
+constexpr bool kProf = SGMM_TC_PROF != 0;   // k_tc_gemm256: in-kernel cycle counters (tc_debug & 32) and the timing experiments (tc_debug & 1);
+                                            // build with -DSGMM_TC_PROF=1 for tools/tc_prof.py — off by default for the same reason
 constexpr uint32_t kUncertain = 0x80000000u;   // verdict: no certified winner -> rescan
 constexpr uint32_t kPair = 0x40000000u;        // verdict: kPair | column a | column b << 15 — the argmin is one of the two
 // suspend-time hint: a waiting warp sleeps in hardware until the phase completes instead of re-polling (polling loops
@@ -1198,7 +1207,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
     }
   } else if (warp == kMmaWarp) {
     // ===== MMA issuer: the whole warp walks the loop, one elected lane issues a unit's MMAs =====
-    const bool prof = p.prof != nullptr;
+    const bool prof = kProf && p.prof != nullptr;
     long long w_a = 0, w_full = 0, w_tempty = 0, c0 = 0, c1 = 0;
     unsigned long long g0 = 0;
     if (prof) { c0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0)); }
@@ -1329,7 +1338,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
             mbar_wait(&tfull[buf], use & 1);
             tc_fence_after();
             float m = INFINITY, acc = 0.f, idx = 0.f, G = 0.f;
-            if (p.debug & 128) {   // A/B reference: the two-pass scan, accumulator handed back after the arithmetic
+            if (kTwoPassRef && (p.debug & 128)) {   // A/B reference: the two-pass scan, accumulator handed back after the arithmetic
               if (!(p.debug & 1) && c_lo < c_hi) tc_scan_columns(tlane + buf * 256, c_lo, c_hi, Gs[g], m, acc, idx, G);
               tc_fence_before();
               __syncwarp();
@@ -1413,7 +1422,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
       float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]: a part's TcBest
       uint32_t it = 0;
       long long e_wait = 0;
-      const long long e_start = p.prof ? clock64() : 0;
+      const long long e_start = (kProf && p.prof) ? clock64() : 0;
       for (uint32_t j = 0; j < nu; j++) {
         const TcMeta mt = meta_of(j);
         const float4 g = mt.g;
@@ -1426,9 +1435,9 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           const uint32_t N = t == mt.tf ? mt.N0 : p.tile_info[t].y;
           const uint32_t unit = it * nh + group, buf = unit & 1u, use = unit >> 1;
           long long e0 = 0;
-          if (p.prof) e0 = clock64();
+          if (kProf && p.prof) e0 = clock64();
           mbar_wait(&tfull[buf], use & 1);
-          if (p.prof) e_wait += clock64() - e0;
+          if (kProf && p.prof) e_wait += clock64() - e0;
           tc_fence_after();
           const uint32_t tcol = tlane + buf * 256;
           const uint32_t c_lo = part * 128, c_hi = min(N, c_lo + 128);
@@ -1445,10 +1454,11 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
             asm volatile("bar.sync %0, 64;" ::"r"(1 + group * 4 + quarter) : "memory");
             const float gm = fminf(mslot[0], mslot[1]);
             tc_scan_masks<4>(tcol, c_lo, c_hi, 45.f * (xn.y / g.w) + 2.f * Gs, gm, &tempty[buf], lane, out);
-          } else if (!(p.debug & 128)) {
-            // one pass over tensor memory (default); tc_debug & 128 keeps the two-pass scan below as the A/B reference
+          } else if (!kTwoPassRef || !(p.debug & 128)) {
+            // one pass over tensor memory (default); built with -DSGMM_TC_TWOPASS_REF=1, tc_debug & 128 selects the two-pass
+            // scan below as the A/B reference (compiled out by default: dead code in this kernel is not free, see MASK)
             TcBest st;
-            tc_scan_onepass2<4>(tcol, c_lo, c_hi, Gs, &tempty[buf], lane, p.debug, st);
+            tc_scan_onepass2<4>(tcol, c_lo, c_hi, Gs, &tempty[buf], lane, kProf ? p.debug : 0u, st);
             if (t == mt.tf) B = st;                               // first tile of the state (n0 = 0): the common case
             else B.merge(st, n0);
           } else {
@@ -1523,7 +1533,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
           }
         }
       }
-      if (p.prof && lane == 0 && quarter == 0) {   // one lane per (half, part) warp group
+      if (kProf && p.prof && lane == 0 && quarter == 0) {   // one lane per (half, part) warp group
         atomicAdd(p.prof + 8 + part, (unsigned long long)e_wait);                  // epilogue waiting for the tensor pipe
         atomicAdd(p.prof + 10 + part, (unsigned long long)(clock64() - e_start));  // epilogue loop lifetime
         atomicAdd(p.prof + 12, 1ull);

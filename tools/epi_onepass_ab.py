@@ -1,4 +1,6 @@
-"""A/B of the GEMM epilogue's TMEM traffic at the bench shape: tc_debug 0 = one pass, 64-column sub-parts (default),
+"""(Needs a library built with the measurement paths: make -C speechrecognition_b200/csrc clean all EXTRA_NVFLAGS="-DSGMM_TC_TWOPASS_REF=1 -DSGMM_TC_PROF=1";
+they are compiled out by default because dead code in the filter kernel costs it 3 %.)
+A/B of the GEMM epilogue's TMEM traffic at the bench shape: tc_debug 0 = one pass, 64-column sub-parts (default),
 256 = one pass, 32-column sub-parts, 128 = the two-pass scan.  Filter time, uncertain cells, identical results.
 usage: python tools/epi_onepass_ab.py [utts] [modes...]"""
 import sys

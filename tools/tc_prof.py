@@ -1,4 +1,6 @@
-"""Cycle profile of k_tc_gemm (option tc_debug & 32): where the MMA-issuing warp and the epilogue warps wait.
+"""(Needs a library built with the measurement paths: make -C speechrecognition_b200/csrc clean all EXTRA_NVFLAGS="-DSGMM_TC_PROF=1";
+they are compiled out by default because dead code in the filter kernel costs it 3 %.)
+Cycle profile of k_tc_gemm (option tc_debug & 32): where the MMA-issuing warp and the epilogue warps wait.
 usage: python tools/tc_prof.py [utts]"""
 import sys
 import numpy as np
