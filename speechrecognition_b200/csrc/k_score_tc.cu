@@ -773,6 +773,7 @@ __device__ __forceinline__ uint64_t tc_cell(uint64_t row_cell, uint32_t col, boo
 // accumulators alternate by tile.
 template <int KS>   // KS > 0: k-steps known at compile time (fully unrolled MMA issue); 0: p.ksteps
 __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
+  const uint32_t dbg = kProf ? p.debug : 0u;   // timing experiments (tc_debug): compiled out by default
   extern __shared__ unsigned char smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* sAlo = smem_raw + (base - smem_u32(smem_raw));    // [half][kstep][128 rows][32 B], 32-byte swizzle
@@ -849,7 +850,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
         const uint32_t s = ulist ? ulist[j] : j;
         for (uint32_t t = p.tile_first[s]; t < p.tile_first[s + 1]; t++, it++) {
           const uint32_t stage = it % nstage, bytes = p.stage_bytes;
-          if (p.debug & 16) continue;
+          if (dbg & 16) continue;
           mbar_wait(&empty[stage], ((it / nstage) & 1) ^ 1);
           mbar_expect_tx(&full[stage], bytes);
           bulk_load(sB + stage * p.stage_bytes, p.Bimg + (size_t)t * (p.stage_bytes / 4), bytes, &full[stage]);
@@ -858,7 +859,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
     }
   } else if (warp == 1) {
     // ===== MMA issuer: the whole warp walks the loop, one elected lane issues =====
-    const bool prof = p.prof != nullptr;
+    const bool prof = kProf && p.prof != nullptr;
     long long w_a = 0, w_full = 0, w_tempty = 0, c0 = 0, c1 = 0;
     unsigned long long g0 = 0;
     if (prof) { c0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0)); }
@@ -872,7 +873,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
         const uint32_t N = p.tile_info[t].y;
         const uint32_t stage = it % nstage;
         if (prof) c1 = clock64();
-        if (!(p.debug & 16)) mbar_wait(&full[stage], (it / nstage) & 1);
+        if (!(dbg & 16)) mbar_wait(&full[stage], (it / nstage) & 1);
         if (prof) w_full += clock64() - c1;
         const uint32_t idesc = make_idesc_tf32(BM, N);
         const uint64_t bhi = make_desc_sw32(smem_u32(sB + stage * p.stage_bytes));
@@ -882,7 +883,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           // epilogue that drains the previous unit of the same half
           const uint32_t unit = it * nh + h, buf = unit % kNumAcc, use = unit / kNumAcc;
           if (prof) c1 = clock64();
-          if (!(p.debug & 8)) mbar_wait(&tempty[buf], (use & 1) ^ 1);
+          if (!(dbg & 8)) mbar_wait(&tempty[buf], (use & 1) ^ 1);
           if (prof) w_tempty += clock64() - c1;
           tc_fence_after();
           const uint32_t d = tmem_base + kAccCol + buf * BN;
@@ -894,7 +895,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           const bool hi_t = p.a_smem == 0, lo_t = p.a_smem == 2;
           const uint64_t hi_s = p.a_smem == 1 ? a_s1 : a_s0, lo_s = a_s0;
           if (tc_elect_one()) {
-            if (!(p.debug & 2)) {
+            if (!(dbg & 2)) {
               const uint32_t nk = KS > 0 ? (uint32_t)KS : ks;
               if (hi_t) {
 #pragma unroll
@@ -980,7 +981,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
       float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
       uint32_t it = 0;
       long long e_wait = 0;
-      const long long e_start = p.prof ? clock64() : 0;
+      const long long e_start = (kProf && p.prof) ? clock64() : 0;
       for (uint32_t j = 0; j < nu; j++) {
         const uint32_t s = ulist ? ulist[j] : j;
         const float4 g = __ldg(p.sguard + s);
@@ -992,14 +993,14 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           const uint32_t N = p.tile_info[t].y;
           const uint32_t unit = it * nh + group, buf = unit % kNumAcc, use = unit / kNumAcc;
           long long e0 = 0;
-          if (p.prof) e0 = clock64();
+          if (kProf && p.prof) e0 = clock64();
           mbar_wait(&tfull[buf], use & 1);
-          if (p.prof) e_wait += clock64() - e0;
+          if (kProf && p.prof) e_wait += clock64() - e0;
           tc_fence_after();
           const uint32_t tcol = tlane + kAccCol + buf * BN;
           const uint32_t c_lo = part * 64, c_hi = min(N, c_lo + 64);
           float m = INFINITY, acc = 0.f, idx = 0.f, G = 0.f;
-          if (!(p.debug & 1) && c_lo < c_hi) {
+          if (!(dbg & 1) && c_lo < c_hi) {
             uint32_t ra[16], rb[16];
 #pragma unroll
             for (int e = 0; e < 16; e++) rb[e] = 0;
@@ -1063,7 +1064,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           }
         }
       }
-      if (p.prof && lane == 0 && quarter == 0) {   // one lane per (half, part) warp group
+      if (kProf && p.prof && lane == 0 && quarter == 0) {   // one lane per (half, part) warp group
         atomicAdd(p.prof + 8 + part, (unsigned long long)e_wait);                  // epilogue waiting for the tensor pipe
         atomicAdd(p.prof + 10 + part, (unsigned long long)(clock64() - e_start));  // epilogue loop lifetime
         atomicAdd(p.prof + 12, 1ull);
@@ -1108,7 +1109,7 @@ __device__ __forceinline__ TcMeta tc_meta_load(const TcParams& p, const uint32_t
 // MASK: the mask mode of the sum scores (tc_subpart_mask) — an instantiation of its own: compiled into the default kernel,
 // the extra path cost the max-approx filter 0.45 ms (3.95 -> 4.41), measured.
 template <int KS, bool F16, bool E16 = false, bool MASK = false>
-__global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {
+__global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {   // 96 registers: 18 warps = 5 on two of the four sub-partitions (16 K registers each)
   extern __shared__ unsigned char smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* sA = smem_raw + (base - smem_u32(smem_raw));      // [half][hi, lo][kstep][128 rows][32 B], 32-byte swizzle
