@@ -628,8 +628,10 @@ def run_ours(args):
         # host buffers in, host buffers out: the upload is queued in chunks (option async_upload) and the scorer
         # starts on the first chunk while the rest is still crossing PCIe
         # realign + estimate in one call (sgmm_align_accumulate): the alignment copy overlaps the E-step
+        # the statistics stay on the device, as in the host Trainer (MixtureModel::accumulate passes NULL and finalize runs
+        # sgmm_mstep on the resident block): what comes home every iteration is the alignment, the path costs and the score sum
         ctx.set_features(x_pin)
-        out = ctx.align_accumulate(ali_pin, cost_pin, stat_pin)
+        out = ctx.align_accumulate(ali_pin, cost_pin, (None, None, None))
         ctx.mstep("mixture")
         return out
 
@@ -670,7 +672,7 @@ def run_ours(args):
     ms_e2e = max_over_ranks(ctx.timer_stop())
     barrier()
     h2d = x_pin.nbytes
-    d2h = ali_pin.nbytes + U * 8 + sum(a.nbytes for a in out[:3]) + 8
+    d2h = ali_pin.nbytes + U * 8 + 8
 
     # what the box can move: every rank copies its pinned feature block H2D at the same time, nothing else running
     # (plain cudaMemcpyAsync through torch) -> aggregate GB/s, the ceiling of the streaming end-to-end number
@@ -794,8 +796,10 @@ def run_ours(args):
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / args.steps,
                 "h2d_ceiling_gbs": h2d * world / (h2d_ms / 1e3) / 1e9, "h2d_copy_alone_ms": h2d_ms,
                 "note": "every step re-uploads the features (a corpus larger than HBM streams like this; training proper "
-                        "keeps them resident = `value`); h2d_ceiling_gbs = all ranks copying their block at once, nothing "
-                        "else running; h2d_copy_alone_ms of the step is pure transfer time the GEMM overlaps only partly"},
+                        "keeps them resident = `value`); D2H per step = alignment + path costs + score sum (the E-step statistics "
+                        "stay on the device for the M-step, as in the host Trainer); h2d_ceiling_gbs = all ranks copying "
+                        "their block at once, nothing else running; h2d_copy_alone_ms of the step is pure transfer time the "
+                        "GEMM overlaps only partly"},
         "gpu_launches": int(launches),
         "stage_ms_per_step": stage,
         "roofline": roof,
