@@ -226,8 +226,19 @@ int sgmm_score_sum_static(sgmm_ctx* ctx, const double* d_values, uint64_t n, dou
  * "host_tables" (default 0; read by sgmm_set_model): 1 = derive the model tables on the host (the previous builder, kept
  *   as the checker of the device builder: same tables, same bits).
  * "allreduce" (default 1): 0 = sgmm_accumulate* skip the ncclAllReduce and return this rank's partial sums (checks).
+ * "tc_pairs" (default 1): the tensor filter names the TWO candidate densities of a near-tie (both refined exactly in place)
+ *   instead of declaring the cell uncertain.  "tc_civ" (default 1): the state-major refinement reads the inverse variances
+ *   from the constant bank.  "tc_lq" (0 none, 1 default, n entries): per-item list of near-ties.  All three: same results.
+ * "vit_mw" (read by sgmm_set_corpus; 0 never, 1 default = 1000, n frames): utterances at least this long are aligned by the
+ *   four-warp Viterbi kernel.  Same results.
+ * "sum_tc" (default 1): with max_approx = 0, the gathered alignment pass takes its sum scores from the tensor filter's
+ *   candidate masks where the model shape allows (pooled, 129..256 densities per state); 0 = k_sum_pruned everywhere.
+ * "tolerance" (default 0; an EXPERIMENT, NOT bit-identical to the reference): sgmm_align runs
+ *   Viterbi on the filter's f32 scores without refinement (needs "vit_mw" = 0 before sgmm_set_corpus, a pooled model on the
+ *   fp16 tensor form); path costs then agree to ~2e-6 relative, the E-step stays exact for the alignment it is given.
  * "tc_debug": timing experiments for the tensor-core kernel — any bit other than 32 (cycle profile, read with the
- *   "tc_prof1".."tc_prof12" counters) makes results INVALID; never set in production. */
+ *   "tc_prof1".."tc_prof12" counters) makes results INVALID; never set in production.  The experiments and the counters
+ *   exist only in libraries built with EXTRA_NVFLAGS="-DSGMM_TC_PROF=1 -DSGMM_TC_TWOPASS_REF=1" (csrc/Makefile). */
 int sgmm_set_option(sgmm_ctx* ctx, const char* key, int64_t value);
 /* "fallbacks": (frame, state) cells whose f32 top-2 gap was inside the error bound and were re-scanned in
  * f64 since the counter was last read; "scorer": the scorer the automatic choice resolves to; "tc_form": 1 when the wide
