@@ -1585,6 +1585,7 @@ struct RefineParams {
   uint32_t sm_maxnd;           // most densities in one state
   const uint32_t* sm_ivoff;    // per item: first double of its state's inverse-variance row in invU / c_iv (k_sm_ivoff)
   const uint4* summask;        // SUM: the filter's candidate masks, [cell][4] (tc_subpart_mask)
+  uint32_t sm_dense_stride;    // 0: tiled cells (gathered pass); else the dense pass: cell = base + frame * stride + state (row-major)
   uint32_t sm_lq;              // entries of the CTA-local near-tie list (0: none, every near-tie goes straight to the global queue)
   // two-stage rescan: f32 tables of the FFMA scorer ([D][4 * dv4] mean and h = 1 / (2 var), c = norm - log w) and
   // the per-state constants of its certified error bound {cmin, |c| max, M max}
@@ -1842,7 +1843,9 @@ __global__ void k_sm_ivoff(const uint4* __restrict__ items, uint32_t n, const ui
 // SUM (sum scores on the tensor path): the cell's input is not a verdict but the filter's candidate masks
 // (tc_subpart_mask); every candidate density is evaluated exactly and  -log sum_k exp(-score_k)  is accumulated in density
 // order (Mixtures.cpp:719-728) — k_sum_pruned's result with the f32 stage replaced by the tensor filter.
-template <uint32_t DIM, bool CIV, bool SUM = false>   // CIV: the model's inverse-variance rows are in the constant bank (c_iv)
+// DENSE: the dense pass (row-major cells, p.sm_dense_stride) — a template parameter because the option costs the
+// gathered instantiation 0.1 ms when it is a run-time one.
+template <uint32_t DIM, bool CIV, bool SUM = false, bool DENSE = false>   // CIV: the model's inverse-variance rows are in the constant bank (c_iv)
 __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
   constexpr uint32_t kMaxEnt = kSmMaxEntries, kMaxChunks = kSmMaxChunks;
@@ -1908,6 +1911,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
   __syncthreads();
 
   const unsigned char* xbytes = reinterpret_cast<const unsigned char*>(p.x);
+  const uint32_t dstride = DENSE ? p.sm_dense_stride : 0u;
   // A chunk in flight: where its cells are, how many are valid, its first frame and the alignment of its first row.
   // Its verdicts travel by cp.async into the warp's own shared-memory slots: a register destination would have to stay
   // live across the evaluation of the previous chunk, and the compiler spilled it straight away (measured: every chunk
@@ -1924,9 +1928,12 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     ck.f0 = eb.x + t0;                                       // (the launcher takes this kernel below 2^32 frames only)
     // first cell of the chunk's first 16-frame tile, in the state's column; lane l is frame t0 + l:
     //   cell = tile0 + (l >> 4) * 16 ncol + ((l ^ col) & 15)
-    ck.tile0 = (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)(t0 >> 4) * (16u * ncol) + (ck.col << 4);
+    // (dense pass: row-major cells, cell = tile0 + l * stride with tile0 = block base + t0 * stride + state)
+    ck.tile0 = dstride ? (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)t0 * dstride + ck.col
+                       : (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)(t0 >> 4) * (16u * ncol) + (ck.col << 4);
     if (!SUM && lane < ck.nvalid) {
-      const uint64_t cell = ck.tile0 + (uint64_t)(lane >> 4) * (16u * ncol) + ((lane ^ ck.col) & 15u);
+      const uint64_t cell = dstride ? ck.tile0 + (uint64_t)lane * dstride
+                                    : ck.tile0 + (uint64_t)(lane >> 4) * (16u * ncol) + ((lane ^ ck.col) & 15u);
       asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(verdict + b * 32 + lane)), "l"(p.cand + cell) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -2019,7 +2026,8 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
       src = perm[lane];
     }
     const uint32_t my_i1 = __shfl_sync(0xffffffffu, i1, src);
-    const uint64_t my_cell = tile0 + (uint64_t)(src >> 4) * (16u * ncol) + ((src ^ cur.col) & 15u);
+    const uint64_t my_cell = dstride ? tile0 + (uint64_t)src * dstride
+                                     : tile0 + (uint64_t)(src >> 4) * (16u * ncol) + ((src ^ cur.col) & 15u);
     const float* my_xr = reinterpret_cast<const float*>(tiles + b * kTileB + (kOdd ? cur.al + src * kRowB : src * kRowS));
     mbar_wait(bar + b, (phases >> b) & 1u);
     phases ^= 1u << b;
@@ -2064,6 +2072,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
       if (!queued) {
         p.out[my_cell] = best;
         if (p.amin16) p.amin16[my_cell] = (uint16_t)bk;
+        if (p.argmin) p.argmin[my_cell] = bk;
       }
     }
     cur = nxt;
@@ -2087,6 +2096,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
       sm_rescan<DIM, !kOdd>(tbl, lw, p.x + frame * dim, iv, nd, RW, 0u, 1u, rb, rk);
       p.out[cell] = rb;
       if (p.amin16) p.amin16[cell] = rk == 0xffffffffu ? (uint16_t)0 : (uint16_t)rk;
+      if (p.argmin) p.argmin[cell] = rk == 0xffffffffu ? 0u : rk;
       n_rescans++;
     }
   }
@@ -2613,7 +2623,11 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   const bool sm_dim = c->dim == 24 || c->dim == 25 || c->dim == 32 || c->dim == 33 || c->dim == 48 || c->dim == 49;
   const bool sm_can = !dense && !c->tc_full && sm_dim && sm_warps >= 8 && c->n_sm_items > 0 && c->n_frames < 0xffffffffull &&
                       c->max_uniq < 0xffffu;
-  const bool use_sm = sm_can && c->tc_refine != 1;
+  // dense pass (sgmm_score_all, recognition): the same kernel over items built here — (block of <= 64 k frames, state),
+  // one entry each, row-major cells — instead of the frame-major gather (272 B of L2 traffic per cell)
+  const bool sm_dense = dense && !c->tc_full && sm_dim && sm_warps >= 8 && c->tc_refine != 1 && c->tc_dense_sm &&
+                        dense_f0 + dense_nframes < 0xffffffffull && c->n_states < 0xffffu;
+  const bool use_sm = (sm_can && c->tc_refine != 1) || sm_dense;
   if (c->tc_sum_pass && !(f16 && !epi16 && nhalf == 2 && sm_can && sm_maxnd <= 256)) {
     c->tc_sum_pass = false;   // not this shape: the caller falls back to k_sum_pruned (nothing has been launched yet)
     return 0;
@@ -2756,16 +2770,48 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   // refinement of every cell in one launch (alternating GEMM and refinement launches per range wastes the SMs at
   // every switch: a GEMM CTA needs the whole shared memory of an SM, so it waits for all refinement CTAs there)
   if (use_sm) {
-    const unsigned sgrid = (unsigned)c->n_sm_items;
+    unsigned sgrid = (unsigned)c->n_sm_items;
+    const uint4* d_items = c->d_sm_items.p;
+    if (sm_dense) {
+      const uint64_t nblk = (dense_nframes + kSmBlockFrames - 1) / kSmBlockFrames;
+      std::vector<uint4> items, ea;
+      std::vector<uint2> eb;
+      for (uint64_t bk = 0; bk < nblk; bk++) {
+        const uint64_t t0 = bk * kSmBlockFrames, T = std::min<uint64_t>(kSmBlockFrames, dense_nframes - t0);
+        const uint64_t base = t0 * c->n_states;                       // first cell of the block's first row
+        for (uint32_t st = 0; st < c->n_states; st++) {
+          items.push_back(make_uint4(st, (uint32_t)ea.size(), 1u, (uint32_t)((T + 31) / 32)));
+          ea.push_back(make_uint4((uint32_t)base, (uint32_t)(base >> 32), st << 16, 0u));
+          eb.push_back(make_uint2((uint32_t)(dense_f0 + t0), (uint32_t)T));
+        }
+      }
+      sgrid = (unsigned)items.size();
+      SGMM_CHECK(c, c->d_dsm_items.reserve(items.size()));
+      SGMM_CHECK(c, c->d_dsm_ent_a.reserve(ea.size()));
+      SGMM_CHECK(c, c->d_dsm_ent_b.reserve(eb.size()));
+      // (pageable sources: the copies are staged before the calls return, the vectors may go)
+      SGMM_CHECK(c, cudaMemcpyAsync(c->d_dsm_items.p, items.data(), items.size() * sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
+      SGMM_CHECK(c, cudaMemcpyAsync(c->d_dsm_ent_a.p, ea.data(), ea.size() * sizeof(uint4), cudaMemcpyHostToDevice, c->stream));
+      SGMM_CHECK(c, cudaMemcpyAsync(c->d_dsm_ent_b.p, eb.data(), eb.size() * sizeof(uint2), cudaMemcpyHostToDevice, c->stream));
+      d_items = c->d_dsm_items.p;
+      r.sm_items = d_items; r.sm_ent_a = c->d_dsm_ent_a.p; r.sm_ent_b = c->d_dsm_ent_b.p;
+      r.sm_dense_stride = c->n_states;
+    }
     SGMM_CHECK(c, c->d_sm_ivoff.reserve(sgrid));
-    k_sm_ivoff<<<(sgrid + 255) / 256, 256, 0, c->stream>>>(c->d_sm_items.p, sgrid, c->d_state_off.p, c->d_var_of.p, c->dimP, c->d_sm_ivoff.p);
+    k_sm_ivoff<<<(sgrid + 255) / 256, 256, 0, c->stream>>>(d_items, sgrid, c->d_state_off.p, c->d_var_of.p, c->dimP, c->d_sm_ivoff.p);
     SGMM_LAUNCH_CHECK(c);
     r.sm_ivoff = c->d_sm_ivoff.p;
     bool civ = false;
     if (refine_civ_bind(c, &civ)) return 1;
 #define SGMM_SM_CASE(D)                                                                                              \
   case D:                                                                                                            \
-    if (civ) {                                                                                                       \
+    if (sm_dense && civ) {                                                                                           \
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_smem)); \
+      k_tc_refine_sm<D, true, false, true><<<sgrid, 32 * sm_warps, sm_smem, c->stream>>>(r);                          \
+    } else if (sm_dense) {                                                                                           \
+      SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_smem)); \
+      k_tc_refine_sm<D, false, false, true><<<sgrid, 32 * sm_warps, sm_smem, c->stream>>>(r);                         \
+    } else if (civ) {                                                                                                \
       SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_refine_sm<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_smem)); \
       k_tc_refine_sm<D, true><<<sgrid, 32 * sm_warps, sm_smem, c->stream>>>(r);                                      \
     } else {                                                                                                         \

@@ -93,7 +93,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_fallbacks.release(); c->d_Amin.release(); c->d_fcol.release(); c->d_Ahi.release(); c->d_Alo.release();
   c->d_xnorm.release(); c->d_ci1.release(); c->d_e32.release(); c->d_summask.release(); c->d_rescan.release(); c->d_E.release(); c->d_all_states.release(); c->d_ali.release();
   c->d_costs.release(); c->d_fdens.release(); c->d_fscore.release();
-  c->d_sm_items.release(); c->d_sm_ent_a.release(); c->d_sm_ent_b.release(); c->d_sm_ivoff.release();
+  c->d_sm_items.release(); c->d_sm_ent_a.release(); c->d_sm_ent_b.release(); c->d_sm_ivoff.release(); c->d_dsm_items.release(); c->d_dsm_ent_a.release(); c->d_dsm_ent_b.release();
   c->d_pack_desc.release(); c->d_pack_uniq.release(); c->d_pack_rows.release(); c->d_pack_colmap.release();
   for (int i = 0; i < 2; i++) { c->d_keys[i].release(); c->d_vals[i].release(); }
   c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release(); c->d_soft_keys.release();
@@ -478,6 +478,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_refine")) { c->tc_refine = (int)value; return 0; }
   if (!strcmp(key, "tc_civ")) { c->tc_civ = value != 0; return 0; }
   if (!strcmp(key, "tc_pairs")) { c->tc_pairs = value != 0; return 0; }
+  if (!strcmp(key, "tc_dense_sm")) { c->tc_dense_sm = value != 0; return 0; }
   if (!strcmp(key, "sum_tc")) { c->sum_tc = value != 0; return 0; }
   if (!strcmp(key, "tolerance")) { c->tol = value != 0; return 0; }
   if (!strcmp(key, "tc_lq")) { c->tc_lq = (int)value; return 0; }   // 0 none, 1 default size, n > 1 entries

@@ -202,6 +202,7 @@ struct sgmm_ctx : SgmmModel {
   bool tol_active = false;         // the last alignment pass ran in tolerance mode (its emission matrix is f32: d_e32)
   int sum_tc = 1;                  // option "sum_tc": sum scores of the gathered pass through the tensor filter's candidate masks (0: k_sum_pruned)
   bool tc_sum_pass = false;        // set around sgmm_launch_emission_tc by the sum-score launcher
+  int tc_dense_sm = 1;             // option "tc_dense_sm": the dense pass is refined by the state-major kernel (0: frame-major gather)
   int tc_pairs = 1;                // option "tc_pairs": the filter names the TWO candidate columns of a near-tie (refined in place) instead of "uncertain"
   int tc_civ = 1;                  // option "tc_civ": state-major refinement reads the inverse variances from the constant bank (0: shared memory)
   int tc_lq = 1;                   // option "tc_lq": state-major refinement queues an item's near-ties as one run (0: cell by cell)
@@ -216,6 +217,8 @@ struct sgmm_ctx : SgmmModel {
   DevBuf<uint4> d_sm_ent_a;        // {E_off[u] lo, hi, ncol | column << 16, chunks before}
   DevBuf<uint2> d_sm_ent_b;        // {first frame (< 2^32: the launcher checks), frames}
   DevBuf<uint32_t> d_sm_ivoff;     // per item: offset of its state's inverse-variance row (k_sm_ivoff, every refinement launch)
+  DevBuf<uint4> d_dsm_items, d_dsm_ent_a;   // the dense pass's items of the state-major refinement (built per launch)
+  DevBuf<uint2> d_dsm_ent_b;
   DevBuf<uint4> d_pack_desc;
   DevBuf<uint32_t> d_pack_uniq;
   DevBuf<sgmm_pack_row> d_pack_rows;
