@@ -99,8 +99,8 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release(); c->d_soft_keys.release();
   c->d_partial.release(); c->d_acc.release(); c->d_score_part.release();
   c->d_dense_scores.release(); c->d_dense_argmin.release(); c->d_model_flags.release(); c->d_mstep_tmp.release();
-  c->d_lex_info.release(); c->d_lex_state.release(); c->d_lex_base.release(); c->d_lex_len.release(); c->d_lex_first.release();
-  c->d_lex_order.release(); c->d_rec_frame_off.release(); c->d_rec_tb_off.release(); c->d_rec_tb.release();
+  c->d_lex_info.release(); c->d_lex_state.release(); c->d_lex_base.release(); c->d_rec_perm.release();
+  c->d_rec_frame_off.release(); c->d_rec_tb_off.release(); c->d_rec_tb.release();
   c->d_rec_words.release(); c->d_rec_nwords.release(); c->d_rec_score.release();
   for (auto& vc : c->vclasses) vc.d_utts.release();
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -470,6 +470,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_epi16")) { c->tc_epi16 = (int)value; return 0; }
   if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
   if (!strcmp(key, "tc_rem")) { c->tc_rem = (int)value; return 0; }   // read by sgmm_set_model
+  if (!strcmp(key, "rec_reg")) { c->rec_reg = value != 0; return 0; }
   if (!strcmp(key, "vit_mw")) {   // read by sgmm_set_corpus: 0 = never, 1 = default threshold, n > 1 = utterances of >= n frames
     c->vit_mw = value <= 0 ? 0 : (value == 1 ? SGMM_VIT_MW_MIN_FRAMES : (int)value);
     return 0;

@@ -238,6 +238,7 @@ struct sgmm_ctx : SgmmModel {
   bool sum_prune = true;          // option "sum_prune": sum scores through the f32-pruned kernel (k_sum_pruned)
   bool ali_has_cols = false;      // resident alignment came from sgmm_align (d_fcol valid)
   std::vector<ViterbiClass> vclasses;
+  int rec_reg = 0;                       // option "rec_reg": small lexicons (<= 256 slots, <= 32 words) are searched by k_recognize_reg
   int vit_mw = SGMM_VIT_MW_MIN_FRAMES;   // option "vit_mw" (read by sgmm_set_corpus): utterances of at least this many frames take k_viterbi_mw; 0 = never
   DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)
 
@@ -262,9 +263,9 @@ struct sgmm_ctx : SgmmModel {
 
   // ---- recognition (k_recognize.cu): lexicon tables + per-call buffers
   uint32_t lex_words = 0, lex_live = 0, lex_silence = 0, lex_max_state = 0;
-  DevBuf<uint32_t> d_lex_info, d_lex_state, d_lex_base, d_lex_len, d_lex_first, d_lex_order;
+  DevBuf<uint32_t> d_lex_info, d_lex_state, d_lex_base;   // slot table in processing order (uint4), in table order (uint4), word-end slots
   DevBuf<uint64_t> d_rec_frame_off, d_rec_tb_off;
-  DevBuf<uint32_t> d_rec_tb, d_rec_words, d_rec_nwords;
+  DevBuf<uint32_t> d_rec_tb, d_rec_words, d_rec_nwords, d_rec_perm;
   DevBuf<double> d_rec_score;
 
   // ---- NCCL (dlopen'ed lazily)

@@ -167,9 +167,25 @@ int sgmm_recognize(sgmm_ctx* c, uint32_t n_utts, const uint64_t* frame_off, doub
   // utterance and latency-bound, so a run should hold thousands of utterances), then one warp per utterance
   const uint32_t N = c->n_states;
   const uint64_t budget = std::max<uint64_t>(65536, (4096ull << 20) / (N * sizeof(double)));
+  // runs of utterances, and within each run the launch order: longest first (the search is one warp per utterance, so
+  // the longest one should start with the launch, not in its last wave)
+  std::vector<uint32_t> run_end, perm(n_utts);
   for (uint32_t u0 = 0; u0 < n_utts;) {
     uint32_t u1 = u0 + 1;
     while (u1 < n_utts && frame_off[u1 + 1] - frame_off[u0] <= budget) u1++;
+    for (uint32_t u = u0; u < u1; u++) perm[u] = u;
+    std::stable_sort(perm.begin() + u0, perm.begin() + u1, [&](uint32_t a, uint32_t b) {
+      return frame_off[a + 1] - frame_off[a] > frame_off[b + 1] - frame_off[b];
+    });
+    run_end.push_back(u1);
+    u0 = u1;
+  }
+  SGMM_CHECK(c, c->d_rec_perm.reserve(n_utts));
+  SGMM_CHECK(c, cudaMemcpyAsync(c->d_rec_perm.p, perm.data(), n_utts * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+  SGMM_CHECK(c, cudaStreamSynchronize(c->stream));   // perm and tb_off are stack vectors
+  uint32_t run = 0;
+  for (uint32_t u0 = 0; u0 < n_utts;) {
+    const uint32_t u1 = run_end[run++];
     const uint64_t f0 = frame_off[u0], nf = frame_off[u1] - f0;
     SGMM_CHECK(c, c->d_dense_scores.reserve((size_t)nf * N));
     {

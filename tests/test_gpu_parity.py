@@ -517,6 +517,61 @@ def test_recognize_matches_oracle(scale, word_penalty, am_threshold, scorer):
     ctx.close()
 
 
+@pytest.mark.parametrize("case", ["k2", "k5_sil_last", "k8_words32", "general_300"])
+@pytest.mark.parametrize("negative", [False, True])
+def test_recognize_register_kernel_random_lexicons(case, negative):
+    """k_recognize_reg (lexicons of <= 256 table slots and <= 32 words, every slots-per-lane count) against the general
+    kernel (option rec_reg = 0) and the oracle: random word lengths, one-state words, silence anywhere in the table,
+    emission scores of both signs (the per-slot exact walk next to the collapsed word entries)."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng({"k2": 1, "k5_sil_last": 2, "k8_words32": 3, "general_300": 4}[case] + 10 * negative)
+    if case == "k2":
+        words, sil = [(1, 1)] + [(int(rng.integers(1, 5)), 2) for _ in range(6)], 0
+    elif case == "k5_sil_last":
+        words = [(int(rng.integers(2, 9)), int(rng.integers(1, 4))) for _ in range(9)] + [(1, 1)]
+        sil = len(words) - 1
+    elif case == "k8_words32":
+        words, sil = [(1, 1)] + [(int(rng.integers(1, 5)), 2) for _ in range(31)], 0
+    else:
+        words, sil = [(1, 1)] + [(int(rng.integers(8, 14)), 2) for _ in range(14)], 0
+    lex = synth.Lexicon(words, sil)
+    slots = sum(max(n * r, 2) for n, r in words)
+    assert (slots > 256) == (case == "general_300")
+    dim = 12
+    tables = synth.random_model(rng, dim, lex.num_states, 2, "none")
+    if negative:                           # tiny variances: most emission scores below zero
+        tables["vars"] = tables["vars"] * 0.004
+        tables["vars_inv"] = 1.0 / tables["vars"]
+        tables["norm"] = (dim * np.log(2 * np.pi) + np.log(tables["vars"].reshape(-1, dim)).sum(1)) / 2
+    corp = synth.make_corpus(rng, lex, tables, dim, 40, t_choices=([60, 150, 400], [0.6, 0.3, 0.1]), words_per_utt=(1, 3))
+    O = Oracle(dim, lex.num_states, "none", True, (3.0, 0.0, 30.0), lex.silence_state)
+    O.load_tables(tables)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, tables)
+    ctx.set_features(corp["x"])
+    ctx.set_tdp(3.0, 0.0, 30.0, lex.silence_state)
+    ctx.set_lexicon(lex.automata, lex.silence)
+    s, _ = ctx.score_all(0, 64)
+    assert ((s < 0).mean() > 0.5) == negative
+    word_off = np.concatenate([[0], np.cumsum([len(a) for a in lex.automata])]).astype(np.uint32)
+    word_states = np.concatenate(lex.automata).astype(np.uint32)
+    for wp, thr in ((10.0, 25.0), (0.0, 1e30), (4.0, 3.0)):
+        ctx.set_option("rec_reg", 1)
+        got, scores = ctx.recognize(corp["frame_off"], wp, thr)
+        ctx.set_option("rec_reg", 0)
+        got0, scores0 = ctx.recognize(corp["frame_off"], wp, thr)
+        assert np.array_equal(scores, scores0)
+        for u in range(40):
+            assert np.array_equal(got[u], got0[u]), (u, wp, thr)
+        for u in range(0, 40, 4):
+            f0, f1 = int(corp["frame_off"][u]), int(corp["frame_off"][u + 1])
+            want, want_score = O.recognize(corp["x"][f0:f1], word_off, word_states, lex.silence, wp, thr)
+            assert np.array_equal(got[u], want), (u, wp, thr, got[u], want)
+            assert scores[u] == want_score or (np.isinf(scores[u]) and np.isinf(want_score))
+    ctx.close()
+
+
 def test_recognize_golden():
     """Committed outputs of the unmodified reference Recognizer (tests/golden/recognize.npz)."""
     import os
