@@ -23,11 +23,11 @@ namespace {
 constexpr int kRecWarps = 4;       // utterances per CTA
 constexpr int kMaxSlotsPerLane = 16;
 #ifndef SGMM_REC_LEAN
-#define SGMM_REC_LEAN 0
+#define SGMM_REC_LEAN 1
 #endif
 constexpr bool kLeanBody = SGMM_REC_LEAN != 0;
 #ifndef SGMM_REC_MINB
-#define SGMM_REC_MINB 4
+#define SGMM_REC_MINB 3
 #endif
 
 struct RecParams {

@@ -16,6 +16,7 @@ for name, U, tc in (("all279", 4096, ([279], [1.0])), ("all1399_592", 592, ([139
     ctx.set_features(corp["x"])
     ctx.set_tdp(3.0, 0.0, 30.0, lex.silence_state)
     ctx.set_lexicon(lex.automata, lex.silence)
+    ctx.set_option("rec_reg", int(os.environ.get("REC_REG", "1")))
     for _ in range(2):
         ctx.recognize(corp["frame_off"], 10.0, 20.0)
     v = []
