@@ -329,7 +329,7 @@ def workload_recognize(args, capi, local, rank, world, sync, steps, warmup):
     ms_e2e = ctx.timer_stop()
     stage = {k: float(np.mean([s[k] for s in stages])) for k in ("score", "score_filter", "score_refine", "viterbi", "d2h")}
     out = {"frames": F, "utterances": U, "ms": ms / steps, "ms_e2e": ms_e2e / steps, "stage_ms": stage,
-           "h2d_bytes_per_step": int(x_pin.nbytes), "d2h_bytes_per_step": int(4 * F + 12 * U)}
+           "h2d_bytes_per_step": int(x_pin.nbytes), "d2h_bytes_per_step": int(4 * (U + 1) + 8 * U + 4 * len(hyp.words))}   # word offsets, scores, the words
     D = int(tables["mix_offsets"][-1])
     out["roofline"] = _tc_roofline(ctx, 2.0 * (args.dim + 1) * D * F, stage["score_filter"], _peaks())
     if rank == 0:   # parity: the first utterances through the oracle port's Recognizer restatement

@@ -58,6 +58,28 @@ class SgmmError(RuntimeError):
     pass
 
 
+class WordLists:
+    """The recognised word sequences of a batch: ``hyp[u]`` is utterance u's word-id array (a view into one buffer)."""
+
+    def __init__(self, words, off):
+        self.words, self.off = words, off
+
+    def __len__(self):
+        return len(self.off) - 1
+
+    def __getitem__(self, u):
+        if isinstance(u, slice):
+            return [self[i] for i in range(*u.indices(len(self)))]
+        if u < 0:
+            u += len(self)
+        if not 0 <= u < len(self):
+            raise IndexError(u)
+        return self.words[int(self.off[u]):int(self.off[u + 1])]
+
+    def __iter__(self):
+        return (self[u] for u in range(len(self)))
+
+
 class Context:
     """One sgmm_ctx (one GPU).  All arrays are numpy host arrays, as the C-ABI takes host buffers."""
 
@@ -202,13 +224,13 @@ class Context:
         """Word-loop recognition of every utterance of the resident features -> (list of word-id arrays, scores)."""
         frame_off = np.ascontiguousarray(frame_off, np.uint64)
         U = len(frame_off) - 1
-        words = np.zeros(int(frame_off[-1]), np.uint32)
+        words = np.empty(int(frame_off[-1]), np.uint32)      # upper bound (one word end per frame); only the words are written
         off = np.zeros(U + 1, np.uint32)
         scores = np.zeros(U, np.float64)
         self._ck(self.L.sgmm_recognize(self.h, C.c_uint32(U), _ptr(frame_off, C.c_uint64), C.c_double(word_penalty),
                                        C.c_double(am_threshold), _ptr(words, C.c_uint32), C.c_uint64(len(words)),
                                        _ptr(off, C.c_uint32), _ptr(scores, C.c_double)))
-        return [words[off[u]:off[u + 1]].copy() for u in range(U)], scores
+        return WordLists(words[:int(off[U])], off), scores
 
     def set_alignment(self, states):
         if states.dtype != ALI_DTYPE:

@@ -416,6 +416,34 @@ int launch_reg(sgmm_ctx* c, const RegParams& q, uint32_t n) {
   return 0;
 }
 
+// word lists of all utterances back to back: word_off[u] = words before utterance u (one block: scan of the counts,
+// then every thread moves its utterances' words), so the host reads ~5 words per utterance instead of a frame-sized array
+__global__ void __launch_bounds__(1024) k_rec_compact(const uint32_t* __restrict__ counts, const uint64_t* __restrict__ frame_off,
+                                                      const uint32_t* __restrict__ raw, uint32_t n_utts,
+                                                      uint32_t* __restrict__ word_off, uint32_t* __restrict__ out) {
+  __shared__ uint32_t part[1024];
+  const uint32_t per = (n_utts + 1023u) / 1024u, u0 = threadIdx.x * per, u1 = min(n_utts, u0 + per);
+  uint32_t sum = 0;
+  for (uint32_t u = u0; u < u1; u++) sum += counts[u];
+  part[threadIdx.x] = sum;
+  __syncthreads();
+  for (uint32_t o = 1; o < 1024; o <<= 1) {
+    const uint32_t v = threadIdx.x >= o ? part[threadIdx.x - o] : 0u;
+    __syncthreads();
+    part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  uint32_t at = part[threadIdx.x] - sum;
+  for (uint32_t u = u0; u < u1; u++) {
+    word_off[u] = at;
+    const uint32_t n = counts[u];
+    const uint32_t* src = raw + frame_off[u];
+    for (uint32_t i = 0; i < n; i++) out[at + i] = src[i];
+    at += n;
+  }
+  if (threadIdx.x == 1023) word_off[n_utts] = part[1023];
+}
+
 }  // namespace
 
 // Tables of sgmm_set_lexicon: live slots are positions 0 .. max(len, 2) - 1 of every word (position 1 of a one-state
@@ -512,6 +540,16 @@ int sgmm_launch_recognize(sgmm_ctx* c, uint32_t u0, uint32_t n, uint64_t chunk_f
   if (smem > 200 * 1024) SGMM_FAIL(c, "recognize: lexicon too large for shared memory");
   SGMM_CHECK(c, cudaFuncSetAttribute(k_recognize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   k_recognize<<<(n + kRecWarps - 1) / kRecWarps, kRecWarps * 32, smem, c->stream>>>(p);
+  SGMM_LAUNCH_CHECK(c);
+  return 0;
+}
+
+// after the last search launch: d_rec_woff[n_utts + 1], d_rec_compact[total words]
+int sgmm_launch_rec_compact(sgmm_ctx* c, uint32_t n_utts) {
+  SGMM_CHECK(c, c->d_rec_woff.reserve((size_t)n_utts + 1));
+  SGMM_CHECK(c, c->d_rec_compact.reserve(c->n_frames));     // a word ends at a frame of its own: at most one per frame
+  k_rec_compact<<<1, 1024, 0, c->stream>>>(c->d_rec_nwords.p, c->d_rec_frame_off.p, c->d_rec_words.p, n_utts,
+                                           c->d_rec_woff.p, c->d_rec_compact.p);
   SGMM_LAUNCH_CHECK(c);
   return 0;
 }

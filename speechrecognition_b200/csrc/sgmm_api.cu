@@ -99,7 +99,7 @@ void sgmm_destroy(sgmm_ctx* c) {
   c->d_hist.release(); c->d_cnt_u32.release(); c->d_seg_off.release(); c->d_item_off.release(); c->d_soft_keys.release();
   c->d_partial.release(); c->d_acc.release(); c->d_score_part.release();
   c->d_dense_scores.release(); c->d_dense_argmin.release(); c->d_model_flags.release(); c->d_mstep_tmp.release();
-  c->d_lex_info.release(); c->d_lex_state.release(); c->d_lex_base.release(); c->d_rec_perm.release();
+  c->d_lex_info.release(); c->d_lex_state.release(); c->d_lex_base.release(); c->d_rec_perm.release(); c->d_rec_woff.release(); c->d_rec_compact.release();
   c->d_rec_frame_off.release(); c->d_rec_tb_off.release(); c->d_rec_tb.release();
   c->d_rec_words.release(); c->d_rec_nwords.release(); c->d_rec_score.release();
   for (auto& vc : c->vclasses) vc.d_utts.release();

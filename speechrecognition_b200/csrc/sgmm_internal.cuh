@@ -265,7 +265,7 @@ struct sgmm_ctx : SgmmModel {
   uint32_t lex_words = 0, lex_live = 0, lex_silence = 0, lex_max_state = 0;
   DevBuf<uint32_t> d_lex_info, d_lex_state, d_lex_base;   // slot table in processing order (uint4), in table order (uint4), word-end slots
   DevBuf<uint64_t> d_rec_frame_off, d_rec_tb_off;
-  DevBuf<uint32_t> d_rec_tb, d_rec_words, d_rec_nwords, d_rec_perm;
+  DevBuf<uint32_t> d_rec_tb, d_rec_words, d_rec_nwords, d_rec_perm, d_rec_woff, d_rec_compact;
   DevBuf<double> d_rec_score;
 
   // ---- NCCL (dlopen'ed lazily)
@@ -327,6 +327,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
                            uint32_t* d_argmin);
 int sgmm_effective_scorer(const sgmm_ctx* c);
 int sgmm_launch_viterbi(sgmm_ctx* c, int tdp_convention);
+int sgmm_launch_rec_compact(sgmm_ctx* c, uint32_t n_utts);
 int sgmm_build_lexicon(sgmm_ctx* c, uint32_t n_words, const uint32_t* word_off, const uint32_t* word_states,
                        uint32_t silence_word);
 int sgmm_launch_recognize(sgmm_ctx* c, uint32_t u0, uint32_t n, uint64_t chunk_f0, double word_penalty,

@@ -198,22 +198,20 @@ int sgmm_recognize(sgmm_ctx* c, uint32_t n_utts, const uint64_t* frame_off, doub
     }
     u0 = u1;
   }
-  std::vector<uint32_t> counts(n_utts), raw(c->n_frames);
+  {
+    StageTimer st(c, SGMM_T_VITERBI);
+    if (sgmm_launch_rec_compact(c, n_utts)) return 1;
+  }
   {
     StageTimer st(c, SGMM_T_D2H);
-    SGMM_CHECK(c, cudaMemcpyAsync(counts.data(), c->d_rec_nwords.p, n_utts * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-    SGMM_CHECK(c, cudaMemcpyAsync(raw.data(), c->d_rec_words.p, c->n_frames * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    SGMM_CHECK(c, cudaMemcpyAsync(word_off_out, c->d_rec_woff.p, ((size_t)n_utts + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
     if (scores) SGMM_CHECK(c, cudaMemcpyAsync(scores, c->d_rec_score.p, n_utts * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
+    const uint64_t total = word_off_out[n_utts];
+    if (total > max_words) SGMM_FAIL(c, "recognize: word buffer too small");
+    if (total) SGMM_CHECK(c, cudaMemcpyAsync(words, c->d_rec_compact.p, total * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
   }
   SGMM_CHECK(c, cudaStreamSynchronize(c->stream));
-  uint64_t total = 0;
-  word_off_out[0] = 0;
-  for (uint32_t u = 0; u < n_utts; u++) {
-    if (total + counts[u] > max_words) SGMM_FAIL(c, "recognize: word buffer too small");
-    for (uint32_t i = 0; i < counts[u]; i++) words[total + i] = raw[frame_off[u] + i];
-    total += counts[u];
-    word_off_out[u + 1] = (uint32_t)total;
-  }
   return 0;
 }
 
