@@ -5,14 +5,14 @@ import numpy as np
 from speechrecognition_b200 import capi, synth
 
 lex = synth.Lexicon()
-tables = synth.random_model(np.random.default_rng(synth.SEED), 39, lex.num_states, 128, "mixture")
+tables = synth.random_model(np.random.default_rng(synth.SEED), 33, lex.num_states, 256, "mixture")
 for name, U, tc in (("all279", 4096, ([279], [1.0])), ("all1399_592", 592, ([1399], [1.0])), ("all1399_148", 148, ([1399], [1.0])),
                     ("bench", 4096, synth.SIETILL_T)):
     if len(sys.argv) > 1 and name not in sys.argv[1:]:
         continue
-    corp = synth.make_corpus(np.random.default_rng(synth.SEED + 101), lex, tables, 39, U, t_choices=tc)
+    corp = synth.make_corpus(np.random.default_rng(synth.SEED + 101), lex, tables, 33, U, t_choices=tc)
     ctx = capi.Context(0)
-    ctx.set_model_tables(39, tables)
+    ctx.set_model_tables(33, tables)
     ctx.set_features(corp["x"])
     ctx.set_tdp(3.0, 0.0, 30.0, lex.silence_state)
     ctx.set_lexicon(lex.automata, lex.silence)
