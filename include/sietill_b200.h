@@ -229,6 +229,8 @@ int sgmm_score_sum_static(sgmm_ctx* ctx, const double* d_values, uint64_t n, dou
  * "tc_pairs" (default 1): the tensor filter names the TWO candidate densities of a near-tie (both refined exactly in place)
  *   instead of declaring the cell uncertain.  "tc_civ" (default 1): the state-major refinement reads the inverse variances
  *   from the constant bank.  "tc_lq" (0 none, 1 default, n entries): per-item list of near-ties.  All three: same results.
+ * "rec_run_frames" (default 0 = about 4 GB of scores): sgmm_recognize scores and searches runs of whole utterances of at
+ *   most this many frames at a time (a single longer utterance is a run of its own).
  * "rec_reg" (default 1): sgmm_recognize searches lexicons of at most 256 table slots and 32 words with the
  *   register-resident kernel (same results; 0 = always the general shared-memory kernel).
  * "vit_mw" (read by sgmm_set_corpus; 0 never, 1 default = 1000, n frames): utterances at least this long are aligned by the

@@ -470,6 +470,7 @@ int sgmm_set_option(sgmm_ctx* c, const char* key, int64_t value) {
   if (!strcmp(key, "tc_epi16")) { c->tc_epi16 = (int)value; return 0; }
   if (!strcmp(key, "tc_f16")) { c->tc_f16 = (int)value; return 0; }   // read by sgmm_set_model and at every launch
   if (!strcmp(key, "tc_rem")) { c->tc_rem = (int)value; return 0; }   // read by sgmm_set_model
+  if (!strcmp(key, "rec_run_frames")) { c->rec_run_frames = value < 0 ? 0 : value; return 0; }
   if (!strcmp(key, "rec_reg")) { c->rec_reg = value != 0; return 0; }
   if (!strcmp(key, "vit_mw")) {   // read by sgmm_set_corpus: 0 = never, 1 = default threshold, n > 1 = utterances of >= n frames
     c->vit_mw = value <= 0 ? 0 : (value == 1 ? SGMM_VIT_MW_MIN_FRAMES : (int)value);

@@ -238,6 +238,7 @@ struct sgmm_ctx : SgmmModel {
   bool sum_prune = true;          // option "sum_prune": sum scores through the f32-pruned kernel (k_sum_pruned)
   bool ali_has_cols = false;      // resident alignment came from sgmm_align (d_fcol valid)
   std::vector<ViterbiClass> vclasses;
+  long long rec_run_frames = 0;          // option "rec_run_frames": frames of dense scores per search launch (0 = ~4 GB of scores)
   int rec_reg = 1;                       // option "rec_reg": small lexicons (<= 256 slots, <= 32 words) are searched by k_recognize_reg
   int vit_mw = SGMM_VIT_MW_MIN_FRAMES;   // option "vit_mw" (read by sgmm_set_corpus): utterances of at least this many frames take k_viterbi_mw; 0 = never
   DevBuf<uint32_t> d_all_states;  // 0..n_states-1 (dense scoring)

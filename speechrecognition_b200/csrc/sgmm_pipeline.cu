@@ -166,7 +166,8 @@ int sgmm_recognize(sgmm_ctx* c, uint32_t n_utts, const uint64_t* frame_off, doub
   // dense emission scores for runs of whole utterances (<= ~4 GB of scores per run: the search is one warp per
   // utterance and latency-bound, so a run should hold thousands of utterances), then one warp per utterance
   const uint32_t N = c->n_states;
-  const uint64_t budget = std::max<uint64_t>(65536, (4096ull << 20) / (N * sizeof(double)));
+  const uint64_t budget = c->rec_run_frames > 0 ? (uint64_t)c->rec_run_frames
+                                                : std::max<uint64_t>(65536, (4096ull << 20) / (N * sizeof(double)));
   // runs of utterances, and within each run the launch order: longest first (the search is one warp per utterance, so
   // the longest one should start with the launch, not in its last wave)
   std::vector<uint32_t> run_end, perm(n_utts);

@@ -572,6 +572,29 @@ def test_recognize_register_kernel_random_lexicons(case, negative):
     ctx.close()
 
 
+def test_recognize_in_several_runs():
+    """sgmm_recognize cuts the batch into runs of whole utterances (dense scores of one run at a time, the longest
+    utterance of a run launched first): the same hypotheses and scores whatever the run length."""
+    from speechrecognition_b200 import capi, synth
+    O, corp, _ = helpers.trained_oracle(dim=25, n_utts=24, splits=1)
+    lex = synth.Lexicon()
+    ctx = capi.Context(0)
+    ctx.set_model_tables(25, O.tables())
+    ctx.set_features(corp["x"])
+    ctx.set_tdp(*O.tdp, O.silence)
+    ctx.set_lexicon(lex.automata, lex.silence)
+    want, want_scores = ctx.recognize(corp["frame_off"], 10.0, 20.0)
+    assert sum(len(w) for w in want) > 0
+    for run in (1, 700, 2500):
+        for reg in (1, 0):
+            ctx.set_option("rec_run_frames", run)
+            ctx.set_option("rec_reg", reg)
+            got, scores = ctx.recognize(corp["frame_off"], 10.0, 20.0)
+            assert np.array_equal(scores, want_scores), (run, reg)
+            assert len(got) == len(want) and all(np.array_equal(a, b) for a, b in zip(got, want)), (run, reg)
+    ctx.close()
+
+
 def test_recognize_golden():
     """Committed outputs of the unmodified reference Recognizer (tests/golden/recognize.npz)."""
     import os
