@@ -290,24 +290,42 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
     }
     close_pack();
   }
-  // ---- state-major refinement items.  Utterances are cut into blocks of about kSmBlockFrames frames (at most
-  // kSmMaxEntries utterances); an item is one state of one block and lists the block's utterances that visit it.
+  // ---- state-major refinement items.  Utterances are cut into blocks; an item is one state of one block and lists the
+  // block's utterances that visit it (at most kSmMaxEntries of them, at most kSmMaxChunks chunks of 32 frames).  A block
+  // ends at about kSmBlockFrames frames once its busiest state has kSmTargetChunks chunks: where every utterance visits
+  // a quarter of the states (the digits) that is reached long before, and the frame bound keeps the items small enough to
+  // balance over the SMs; where an utterance visits 150 of 4501 states (config 5) a 64 k-frame block would leave ~70
+  // chunks per item, and the item's prologue (the state's table into shared memory, 1 CTA / SM) would cost more than
+  // its chunks — measured 11.3 ms for 4.7 M chunks in 69 738 items.
   // Items are ordered block-major so that the CTAs in flight write into a few MB of the emission matrix.
   std::vector<uint4> sm_items, sm_ent_a;
   std::vector<uint2> sm_ent_b;
   {
     std::vector<std::vector<std::pair<uint32_t, uint32_t>>> by_state(max_state + 1);   // state -> (utt, column)
+    std::vector<uint32_t> state_chunks(max_state + 1, 0u);
     std::vector<uint32_t> touched;
     uint32_t u0 = 0;
     while (u0 < U) {
-      uint32_t u1 = u0;
-      while (u1 < U && u1 - u0 < kSmMaxEntries && (u1 == u0 || frame_off[u1 + 1] - frame_off[u0] <= kSmBlockFrames)) u1++;
+      uint32_t u1 = u0, busiest = 0;
       touched.clear();
-      for (uint32_t u = u0; u < u1; u++)
-        for (uint32_t j = uniq_off[u]; j < uniq_off[u + 1]; j++) {
-          if (by_state[uniq[j]].empty()) touched.push_back(uniq[j]);
-          by_state[uniq[j]].push_back({u, j - uniq_off[u]});
+      while (u1 < U) {
+        const uint32_t T = (uint32_t)(frame_off[u1 + 1] - frame_off[u1]), ch = (T + 31u) / 32u;
+        if (u1 > u0) {
+          if (frame_off[u1 + 1] - frame_off[u0] > kSmBlockFrames && busiest >= kSmTargetChunks) break;
+          bool fits = true;
+          for (uint32_t j = uniq_off[u1]; j < uniq_off[u1 + 1] && fits; j++)
+            fits = by_state[uniq[j]].size() < kSmMaxEntries && state_chunks[uniq[j]] + ch <= kSmMaxChunks;
+          if (!fits) break;
         }
+        for (uint32_t j = uniq_off[u1]; j < uniq_off[u1 + 1]; j++) {
+          const uint32_t st = uniq[j];
+          if (by_state[st].empty()) touched.push_back(st);
+          by_state[st].push_back({u1, j - uniq_off[u1]});
+          state_chunks[st] += ch;
+          busiest = std::max(busiest, state_chunks[st]);
+        }
+        u1++;
+      }
       std::sort(touched.begin(), touched.end());
       for (uint32_t s : touched) {
         uint32_t chunks = 0;
@@ -321,6 +339,7 @@ int sgmm_set_corpus(sgmm_ctx* c, uint32_t U, const uint64_t* frame_off, const ui
         }
         sm_items.push_back(make_uint4(s, first, (uint32_t)by_state[s].size(), chunks));
         by_state[s].clear();
+        state_chunks[s] = 0;
       }
       u0 = u1;
     }

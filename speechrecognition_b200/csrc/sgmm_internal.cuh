@@ -48,11 +48,13 @@ struct DevBuf {
   void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
-// state-major refinement: a block of utterances holds at most this many utterances / frames; an item's chunks (32
-// consecutive frames of ONE utterance, the last chunk of an utterance may be short) are therefore at most kSmMaxChunks
+// state-major refinement: an item (one state of one block of utterances) lists at most kSmMaxEntries utterances and at
+// most kSmMaxChunks chunks (32 consecutive frames of ONE utterance, the last chunk of an utterance may be short);
+// sgmm_set_corpus ends a block where one more utterance would break either bound (see there)
 constexpr uint32_t kSmMaxEntries = 256;
 constexpr uint32_t kSmBlockFrames = 65536;
 constexpr uint32_t kSmMaxChunks = kSmBlockFrames / 32 + kSmMaxEntries;
+constexpr uint32_t kSmTargetChunks = 2048;   // a block keeps growing past kSmBlockFrames until its busiest state has this many chunks
 
 struct sgmm_pack_row {   // one row of a packed GEMM task (sgmm_set_corpus)
   uint64_t cell;     // first cell of this frame's 16-frame tile in the ragged emission matrix + (t & 15)  (sgmm_cell_rel)
