@@ -215,6 +215,7 @@ int sgmm_score_sum_static(sgmm_ctx* ctx, const double* d_values, uint64_t n, dou
  * "rescore_cache" (default 1): sgmm_accumulate after sgmm_align with an unchanged model looks the aligned cells' scores up.
  * "async_upload" (default 0): sgmm_set_features queues chunked copies ("upload_chunks", 1..16, default 16) and returns;
  *   the host buffer must stay untouched until the next compute call returns (use sgmm_host_alloc memory).
+ *   The tensor-core filter of the next sgmm_align* / sgmm_score_all / sgmm_recognize call starts behind the first chunk.
  * "tc_halves" (0 auto, 1, 2): 128-frame halves per tensor-core CTA.  "tc_pack" (default 1; read by sgmm_set_corpus):
  *   pack short utterance tails into shared 128-row halves.
  * "tc_refine" (0 auto, 1, 2): refinement kernel of the tensor-core scorer — 1 frame-major (winner's mean row gathered

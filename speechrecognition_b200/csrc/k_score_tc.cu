@@ -2525,7 +2525,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   // GEMM of the first chunks runs under the copies of the later ones.
   struct Range { uint64_t f_end; int ev; };
   std::vector<Range> ranges;
-  if (!dense && c->feat_pending && !c->tc_A_valid) {
+  if (c->feat_pending && !c->tc_A_valid) {   // (dense pass too: recognition right behind an upload)
     for (int i = 0; i < c->feat_pending; i++) ranges.push_back({c->feat_chunk_end[i], i});
   } else {
     if (sgmm_wait_features(c)) return 1;
@@ -2665,10 +2665,18 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
     }
     f_prev = rg.f_end;
     // tasks whose frames have all arrived
-    const uint64_t g_end = dense ? n_tasks : std::upper_bound(gemm_end.begin(), gemm_end.end(), rg.f_end) - gemm_end.begin();
+    // (dense: task i is frames dense_f0 + [i * rows, + rows); a range takes the whole tasks below its last frame)
+    const uint64_t g_end = !dense ? std::upper_bound(gemm_end.begin(), gemm_end.end(), rg.f_end) - gemm_end.begin()
+                           : (one || rg.f_end >= dense_f0 + dense_nframes) ? n_tasks
+                           : (rg.f_end <= dense_f0 ? 0 : (rg.f_end - dense_f0) / rows_per_task);
     if (g_end > g_prev) {
       const unsigned grid = (unsigned)(g_end - g_prev);
       p.tasks = dense ? nullptr : gemm_tasks + g_prev;
+      if (dense) {   // the kernel counts dense tasks from blockIdx.x = 0: shift its origin instead
+        p.f0 = dense_f0 + g_prev * rows_per_task;
+        p.nframes = dense_nframes - g_prev * rows_per_task;
+        p.cand = c->d_ci1.p + g_prev * rows_per_task * c->n_states;
+      }
       if (epi16) {   // d = 32..46 pooled, fp16 operands, sixteen epilogue warps per unit
         SGMM_CHECK(c, cudaFuncSetAttribute(k_tc_gemm256<3, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_tc_gemm256<3, true, true><<<grid, 576, smem, st>>>(p);

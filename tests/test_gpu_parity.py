@@ -592,6 +592,16 @@ def test_recognize_in_several_runs():
             got, scores = ctx.recognize(corp["frame_off"], 10.0, 20.0)
             assert np.array_equal(scores, want_scores), (run, reg)
             assert len(got) == len(want) and all(np.array_equal(a, b) for a, b in zip(got, want)), (run, reg)
+    # right behind a chunked upload the dense filter is launched per chunk (whole 256-frame tasks below the chunk's end)
+    ctx.set_option("rec_reg", 1)
+    ctx.set_option("async_upload", 1)
+    for run, chunks in ((0, 16), (2500, 5), (0, 3)):
+        ctx.set_option("rec_run_frames", run)
+        ctx.set_option("upload_chunks", chunks)
+        ctx.set_features(corp["x"])
+        got, scores = ctx.recognize(corp["frame_off"], 10.0, 20.0)
+        assert np.array_equal(scores, want_scores), (run, chunks)
+        assert all(np.array_equal(a, b) for a, b in zip(got, want)), (run, chunks)
     ctx.close()
 
 
