@@ -1854,6 +1854,12 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
   constexpr uint32_t dim = DIM, kRowB = DIM * 4;
   constexpr uint32_t kRowS = kOdd ? kRowB : kRowB + 16;      // tile row stride: odd word count / odd 16-byte count
   constexpr uint32_t kTileB = 32 * kRowS + (kOdd ? 32 : 0);  // odd: + the alignment slack of the one bulk copy
+  // Even dimensions: rows travel in groups of kGrp rows per bulk copy, 16 bytes of padding behind every group.  A row of
+  // d = 48 is twelve 16-byte units: with the padding behind every PAIR of rows the eight rows of a quarter-warp start in
+  // eight different bank groups (12 r + (r >> 1) mod 8 = 0 4 1 5 2 6 3 7) and a tile takes 16 copies instead of 32 —
+  // the copy-issue loop (one elected lane per copy) was a tenth of the kernel's samples at the stress shape.
+  constexpr uint32_t kGrp = (!kOdd && (DIM / 4) % 8 == 4) ? 2u : 1u;
+  auto row_off = [](uint32_t r) -> uint32_t { return (r / kGrp) * (kGrp * kRowB + 16u) + (r % kGrp) * kRowB; };
   // The constant-bank reads of the chunk loop must come out as LDCU (uniform datapath, immediate offsets): per-thread
   // LDC measured SLOWER than the shared-memory broadcast.  The compiler emits LDCU only inside warp-uniform control flow
   // and from an offset it can prove uniform — a value loaded from a uniform address (sm_ivoff[blockIdx.x]; the chain
@@ -1951,7 +1957,8 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     } else {
       if (lane == 0) mbar_expect_tx(bar + b, ck.nvalid * kRowB);
       __syncwarp();
-      if (lane < ck.nvalid) bulk_load(tile + lane * kRowS, xbytes + src + (size_t)lane * kRowB, kRowB, bar + b);
+      if (lane * kGrp < ck.nvalid)
+        bulk_load(tile + row_off(lane * kGrp), xbytes + src + (size_t)lane * kGrp * kRowB, min(kGrp, ck.nvalid - lane * kGrp) * kRowB, bar + b);
     }
     return ck;
   };
@@ -1971,7 +1978,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
       // ---- sum scores: lane = frame (no lane swap: every lane walks its own candidate list)
       const bool act = lane < cur.nvalid;
       const uint64_t my_cell = tile0 + (uint64_t)(lane >> 4) * (16u * ncol) + ((lane ^ cur.col) & 15u);
-      const float* my_xr = reinterpret_cast<const float*>(tiles + b * kTileB + (kOdd ? cur.al + lane * kRowB : lane * kRowS));
+      const float* my_xr = reinterpret_cast<const float*>(tiles + b * kTileB + (kOdd ? cur.al + lane * kRowB : row_off(lane)));
       uint4 ent[4];
 #pragma unroll
       for (int q = 0; q < 4; q++) ent[q] = act ? __ldg(p.summask + 4 * my_cell + q) : make_uint4(0u, 0u, 0x7f800000u, 0u);
@@ -2028,7 +2035,7 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     const uint32_t my_i1 = __shfl_sync(0xffffffffu, i1, src);
     const uint64_t my_cell = dstride ? tile0 + (uint64_t)src * dstride
                                      : tile0 + (uint64_t)(src >> 4) * (16u * ncol) + ((src ^ cur.col) & 15u);
-    const float* my_xr = reinterpret_cast<const float*>(tiles + b * kTileB + (kOdd ? cur.al + src * kRowB : src * kRowS));
+    const float* my_xr = reinterpret_cast<const float*>(tiles + b * kTileB + (kOdd ? cur.al + src * kRowB : row_off(src)));
     mbar_wait(bar + b, (phases >> b) & 1u);
     phases ^= 1u << b;
     // the winner's exact score, evaluated by EVERY lane (lanes without a certified winner take row 0 and drop the
