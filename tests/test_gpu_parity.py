@@ -572,6 +572,45 @@ def test_recognize_register_kernel_random_lexicons(case, negative):
     ctx.close()
 
 
+@pytest.mark.parametrize("words,sil", [([(1, 1)], 0), ([(1, 1), (1, 1)], 1), ([(2, 1), (1, 2), (3, 3)], 0xffffffff),
+                                       ([(1, 1), (5, 2), (4, 2)], 0)])
+def test_recognize_edge_cases(words, sil):
+    """Utterances of 1 .. 5 frames (shorter than any word), a lexicon of one word, one without silence, a zero and a
+    tiny beam: both search kernels against the oracle (hypotheses and final scores, +inf included)."""
+    from oracle.binding import Oracle
+    from speechrecognition_b200 import capi, synth
+    rng = np.random.default_rng(len(words) * 7 + 1)
+    lex = synth.Lexicon(words, 0 if sil == 0xffffffff else sil)
+    dim = 8
+    tables = synth.random_model(rng, dim, lex.num_states, 2, "none")
+    lens = [1, 2, 3, 4, 5, 17, 40, 1, 33, 2]
+    x = rng.normal(0.0, 1.5, size=(sum(lens), dim)).astype(np.float32)
+    frame_off = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    sil_state = lex.silence_state if sil != 0xffffffff else 0
+    O = Oracle(dim, lex.num_states, "none", True, (3.0, 0.0, 30.0), sil_state)
+    O.load_tables(tables)
+    ctx = capi.Context(0)
+    ctx.set_model_tables(dim, tables)
+    ctx.set_features(x)
+    ctx.set_tdp(3.0, 0.0, 30.0, sil_state)
+    ctx.set_lexicon(lex.automata, sil)
+    word_off = np.concatenate([[0], np.cumsum([len(a) for a in lex.automata])]).astype(np.uint32)
+    word_states = np.concatenate(lex.automata).astype(np.uint32)
+    for wp, thr in ((10.0, 20.0), (0.0, 0.0), (2.5, 1e-3), (1.0, 1e30)):
+        res = {}
+        for reg in (1, 0):
+            ctx.set_option("rec_reg", reg)
+            res[reg] = ctx.recognize(frame_off, wp, thr)
+        assert np.array_equal(res[1][1], res[0][1]), (wp, thr, res[1][1], res[0][1])
+        for u in range(len(lens)):
+            assert np.array_equal(res[1][0][u], res[0][0][u]), (u, wp, thr)
+            f0, f1 = int(frame_off[u]), int(frame_off[u + 1])
+            want, want_score = O.recognize(x[f0:f1], word_off, word_states, sil, wp, thr)
+            assert np.array_equal(res[1][0][u], want), (u, wp, thr, res[1][0][u], want)
+            assert res[1][1][u] == want_score, (u, wp, thr, res[1][1][u], want_score)
+    ctx.close()
+
+
 def test_recognize_in_several_runs():
     """sgmm_recognize cuts the batch into runs of whole utterances (dense scores of one run at a time, the longest
     utterance of a run launched first): the same hypotheses and scores whatever the run length."""
