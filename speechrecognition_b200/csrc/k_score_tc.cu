@@ -1848,17 +1848,17 @@ __global__ void k_sm_ivoff(const uint4* __restrict__ items, uint32_t n, const ui
 template <uint32_t DIM, bool CIV, bool SUM = false, bool DENSE = false>   // CIV: the model's inverse-variance rows are in the constant bank (c_iv)
 __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
-  constexpr uint32_t kMaxEnt = kSmMaxEntries, kMaxChunks = kSmMaxChunks;
+  constexpr uint32_t kMaxEnt = kSmMaxEntries, kMaxChunks = kSmMaxChunks;   // (run-time caps cost the d = 33 instantiation 0.09 ms, measured)
   constexpr bool kOdd = (DIM & 1u) != 0;
   static_assert(kOdd || DIM % 4 == 0, "even dimensions take one 16-byte-aligned bulk copy per row");
   constexpr uint32_t dim = DIM, kRowB = DIM * 4;
-  constexpr uint32_t kRowS = kOdd ? kRowB : kRowB + 16;      // tile row stride: odd word count / odd 16-byte count
-  constexpr uint32_t kTileB = 32 * kRowS + (kOdd ? 32 : 0);  // odd: + the alignment slack of the one bulk copy
   // Even dimensions: rows travel in groups of kGrp rows per bulk copy, 16 bytes of padding behind every group.  A row of
   // d = 48 is twelve 16-byte units: with the padding behind every PAIR of rows the eight rows of a quarter-warp start in
   // eight different bank groups (12 r + (r >> 1) mod 8 = 0 4 1 5 2 6 3 7) and a tile takes 16 copies instead of 32 —
   // the copy-issue loop (one elected lane per copy) was a tenth of the kernel's samples at the stress shape.
   constexpr uint32_t kGrp = (!kOdd && (DIM / 4) % 8 == 4) ? 2u : 1u;
+  // tile bytes (the launcher's sm_tile): odd — rows at their own stride + the alignment slack of the one bulk copy
+  constexpr uint32_t kTileB = kOdd ? 32 * kRowB + 32 : (32 / kGrp) * (kGrp * kRowB + 16);
   auto row_off = [](uint32_t r) -> uint32_t { return (r / kGrp) * (kGrp * kRowB + 16u) + (r % kGrp) * kRowB; };
   // The constant-bank reads of the chunk loop must come out as LDCU (uniform datapath, immediate offsets): per-thread
   // LDC measured SLOWER than the shared-memory broadcast.  The compiler emits LDCU only inside warp-uniform control flow
@@ -2620,7 +2620,9 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   // fit next to the table — the carve-up of k_tc_refine_sm
   const size_t sm_fixed = ((size_t)sm_maxnd * sm_rw + ((sm_maxnd + 1u) & ~1u) + c->dimP) * sizeof(double) +
                           kSmMaxEntries * (sizeof(uint4) + sizeof(uint2)) + kSmMaxChunks * sizeof(uint16_t);
-  const size_t sm_tile = (c->dim & 1u) ? 32 * (size_t)c->dim * sizeof(float) + 32 : 32 * ((size_t)c->dim * sizeof(float) + 16);
+  const uint32_t sm_grp = (!(c->dim & 3u) && (c->dim / 4) % 8 == 4) ? 2u : 1u;   // rows per bulk copy (kGrp of k_tc_refine_sm)
+  const size_t sm_tile = (c->dim & 1u) ? 32 * (size_t)c->dim * sizeof(float) + 32
+                                       : (32 / sm_grp) * (sm_grp * (size_t)c->dim * sizeof(float) + 16);
   const size_t sm_warp = 304 + 2 * sm_tile;
   int sm_warps = sm_fixed + 8 * sm_warp <= kSmemLimit ? (int)std::min<size_t>(16, (kSmemLimit - sm_fixed) / sm_warp) : 0;
   const size_t sm_tiles = sm_fixed + (size_t)sm_warps * sm_warp;
