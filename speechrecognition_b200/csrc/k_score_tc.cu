@@ -757,9 +757,10 @@ struct TcParams {
 constexpr uint32_t kAccCol = 128;    // TMEM: columns [0, 128) hold Ahi of both halves, then three 128-column accumulators
 constexpr uint32_t kNumAcc = 3;
 
-// Verdict cell of (row, column).  Dense: row-major, row_cell = first cell of the row.  Gathered: the tiled layout of
-// sgmm_cell_rel — row_cell = first cell of the row's 16-frame tile + (t & 15), so that the 32 rows of a TMEM lane quarter
-// (consecutive frames) store two full 64-byte runs per column instead of 32 sectors.
+// Verdict cell of (row, column): the tiled layout of sgmm_cell_rel — row_cell = first cell of the row's 16-frame tile +
+// (t & 15), so that the 32 rows of a TMEM lane quarter (consecutive frames) store two full 64-byte runs per column instead
+// of 32 sectors.  The dense pass uses it for its verdicts too (stride = all states, tiles counted from the pass's first
+// frame); only its SCORES are row-major, as sgmm_score_all returns them.
 __device__ __forceinline__ uint64_t tc_row_cell(uint64_t out_base, uint32_t row, uint32_t out_stride, bool tiled) {
   return tiled ? out_base + (uint64_t)(row >> 4) * (16u * out_stride) + (row & 15u) : out_base + (uint64_t)row * out_stride;
 }
@@ -976,7 +977,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
         if (lane == 0) mbar_arrive(a_full);
       }
       const float2 xn = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
-      const uint64_t my_cell = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, !p.dense);
+      const uint64_t my_cell = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, true);
       const uint16_t* my_map = prow ? p.pack_colmap + prow[row].colmap : nullptr;
       float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]
       uint32_t it = 0;
@@ -1060,7 +1061,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm(TcParams p) {
           if (row < nvalid) {
             const bool certain = Bacc == 1.0f && Bsecond > Bbest + BG;
             const uint32_t col = my_map ? (uint32_t)my_map[j] : j;     // packed: this frame's utterance may not use state j
-            if (col != 0xFFFFu || !my_map) p.cand[tc_cell(my_cell, col, !p.dense)] = certain ? (uint32_t)Bidx : kUncertain;
+            if (col != 0xFFFFu || !my_map) p.cand[tc_cell(my_cell, col, true)] = certain ? (uint32_t)Bidx : kUncertain;
           }
         }
       }
@@ -1315,7 +1316,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {   // 96 reg
     for (int g = 0; g < 2; g++) {
       const uint32_t row = min((uint32_t)g, nh - 1) * BM + lrow;
       xn[g] = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
-      my_cell[g] = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, !p.dense);
+      my_cell[g] = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, true);
       my_map[g] = prow ? p.pack_colmap + prow[row].colmap : nullptr;
     }
     uint32_t it = 0;
@@ -1382,7 +1383,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {   // 96 reg
             if (row < nvalid) {
               const bool certain = Bacc[g] == 1.0f && Bsecond[g] > Bbest[g] + BG[g];
               const uint32_t col = my_map[g] ? (uint32_t)my_map[g][j] : j;
-              if (col != 0xFFFFu || !my_map[g]) p.cand[tc_cell(my_cell[g], col, !p.dense)] = certain ? (uint32_t)Bidx[g] : kUncertain;
+              if (col != 0xFFFFu || !my_map[g]) p.cand[tc_cell(my_cell[g], col, true)] = certain ? (uint32_t)Bidx[g] : kUncertain;
             }
           }
         }
@@ -1418,7 +1419,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {   // 96 reg
         if (lane == 0) mbar_arrive(a_full);
       }
       const float2 xn = p.xnorm[prow ? (uint64_t)prow[row].frame : min(row0 + row, p.n_frames - 1)];
-      const uint64_t my_cell = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, !p.dense);
+      const uint64_t my_cell = prow ? prow[row].cell : tc_row_cell(out_base, row, out_stride, true);
       const uint16_t* my_map = prow ? p.pack_colmap + prow[row].colmap : nullptr;
       float* my_x = xchg + (group * BM + lrow) * 5;               // [slot][half][row][5]: a part's TcBest
       uint32_t it = 0;
@@ -1526,7 +1527,7 @@ __global__ void __launch_bounds__(576, 1) k_tc_gemm256(TcParams p) {   // 96 reg
           if (row < nvalid) {
             const uint32_t col = my_map ? (uint32_t)my_map[j] : j;     // packed: this frame's utterance may not use state j
             if (col != 0xFFFFu || !my_map) {
-              const uint64_t cell = tc_cell(my_cell, col, !p.dense);
+              const uint64_t cell = tc_cell(my_cell, col, true);
               if (!p.pairs && (vd & kPair) && !(vd & kUncertain)) vd = kUncertain;
               if (!MASK) p.cand[cell] = vd;
               if (F16 && p.tol) p.e32[cell] = B.m * (g.w / xn.y);
@@ -1586,6 +1587,7 @@ struct RefineParams {
   const uint32_t* sm_ivoff;    // per item: first double of its state's inverse-variance row in invU / c_iv (k_sm_ivoff)
   const uint4* summask;        // SUM: the filter's candidate masks, [cell][4] (tc_subpart_mask)
   uint32_t sm_dense_stride;    // 0: tiled cells (gathered pass); else the dense pass: cell = base + frame * stride + state (row-major)
+  uint32_t sm_dense_f0;        // dense pass: its first frame (the verdict tiles are counted from there)
   uint32_t sm_lq;              // entries of the CTA-local near-tie list (0: none, every near-tie goes straight to the global queue)
   // two-stage rescan: f32 tables of the FFMA scorer ([D][4 * dv4] mean and h = 1 / (2 var), c = norm - log w) and
   // the per-state constants of its certified error bound {cmin, |c| max, M max}
@@ -1712,7 +1714,7 @@ __global__ void __launch_bounds__(256) k_tc_refine(RefineParams p) {
     double best = 1e10;
     uint32_t bk = 0;
     if (k1 > k0) {
-      const uint32_t i1 = p.cand[e];
+      const uint32_t i1 = p.cand[tiled ? e : cell0 + (uint64_t)(r >> 4) * (16u * ncol) + (j << 4) + ((r ^ j) & 15u)];   // verdicts are tiled in both passes
       if (i1 < k1 - k0) {                        // certified (kUncertain and padding columns fail this)
         const double sc = exact_score_unrolled<NP>(p.m, p.x + frame * p.m.dim, k0 + i1, xs_all + r * XS,
                                                    p.pooled ? iv_all + j * p.m.dimP : nullptr);
@@ -1938,7 +1940,8 @@ __global__ void __launch_bounds__(512, 1) k_tc_refine_sm(RefineParams p) {
     ck.tile0 = dstride ? (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)t0 * dstride + ck.col
                        : (((uint64_t)ea.y << 32) | ea.x) + (uint64_t)(t0 >> 4) * (16u * ncol) + (ck.col << 4);
     if (!SUM && lane < ck.nvalid) {
-      const uint64_t cell = dstride ? ck.tile0 + (uint64_t)lane * dstride
+      // (dense: the verdicts are tiled over all states, tiles counted from the pass's first frame)
+      const uint64_t cell = dstride ? (uint64_t)(((ck.f0 - p.sm_dense_f0) >> 4) + (lane >> 4)) * (16u * dstride) + (ck.col << 4) + ((lane ^ ck.col) & 15u)
                                     : ck.tile0 + (uint64_t)(lane >> 4) * (16u * ncol) + ((lane ^ ck.col) & 15u);
       asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(verdict + b * 32 + lane)), "l"(p.cand + cell) : "memory");
     }
@@ -2559,7 +2562,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
   const uint64_t n_tasks = dense ? (dense_nframes + rows_per_task - 1) / rows_per_task
                                  : (nhalf == 2 ? c->n_tasks256 : c->n_tasks128);
   if (n_tasks == 0) return 0;
-  SGMM_CHECK(c, c->d_ci1.reserve(n_cells));
+  SGMM_CHECK(c, c->d_ci1.reserve(dense ? (dense_nframes + 15) / 16 * 16 * c->n_states : n_cells));   // (verdicts: whole 16-frame tiles)
   const size_t cap = (size_t)std::max<uint64_t>(1024, n_cells / 8);
   SGMM_CHECK(c, c->d_rescan.reserve(2 * cap + 2));   // [0] entries, [1] -, then {cell, frame | state << 40} per entry
   c->rescan_cap = cap;
@@ -2812,7 +2815,7 @@ int sgmm_launch_emission_tc(sgmm_ctx* c, bool dense, uint64_t dense_f0, uint64_t
       SGMM_CHECK(c, cudaMemcpyAsync(c->d_dsm_ent_b.p, eb.data(), eb.size() * sizeof(uint2), cudaMemcpyHostToDevice, c->stream));
       d_items = c->d_dsm_items.p;
       r.sm_items = d_items; r.sm_ent_a = c->d_dsm_ent_a.p; r.sm_ent_b = c->d_dsm_ent_b.p;
-      r.sm_dense_stride = c->n_states;
+      r.sm_dense_stride = c->n_states; r.sm_dense_f0 = (uint32_t)dense_f0;
     }
     SGMM_CHECK(c, c->d_sm_ivoff.reserve(sgrid));
     k_sm_ivoff<<<(sgrid + 255) / 256, 256, 0, c->stream>>>(d_items, sgrid, c->d_state_off.p, c->d_var_of.p, c->dimP, c->d_sm_ivoff.p);
