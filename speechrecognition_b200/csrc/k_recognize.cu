@@ -12,6 +12,9 @@
 //   - per frame: prune against best + am_threshold (:193-198), best word end with strict '>' (:201-207);
 //   - backtrace over word ends, silence not emitted (:222-231).
 // Emission scores come from the dense K1 pass ([frames][states] f64, exactly min_score().first).
+// Two kernels: k_recognize (any lexicon up to 4096 table slots: hypothesis tables in shared memory) and k_recognize_reg
+// (<= 256 slots, <= 32 words: the table in registers, see there); both launch the longest utterances first, and
+// k_rec_compact packs the word lists so that the host reads words, not a frame-sized array.
 #include <algorithm>
 #include <type_traits>
 #include <vector>
