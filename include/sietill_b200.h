@@ -223,6 +223,11 @@ int sgmm_score_sum_static(sgmm_ctx* ctx, const double* d_values, uint64_t n, dou
  *   "tc_rescan" (0, 1): 0 two-stage rescan of near-tie cells (f32 prefilter, f64 candidates), 1 full f64 scan.
  * "tc_wide" (-1 auto, 0, 1; read by sgmm_set_model): 256-density GEMM tiles (the N = 256 kernel) instead of 128;
  *   auto picks them when some state has more than 128 densities and the tile ring fits shared memory.
+ * "tc_f16" (-1 auto = on when the model allows it, 0, 1; read by sgmm_set_model and at every launch): fp16 hi / lo operands for the 256-wide tiles of pooled
+ *   models (kind::f16 MMAs, 16 terms per k-step); 0 = the 3 x TF32 form.  "tc_rem" (default 1; read by sgmm_set_model): pack
+ *   the K remainder of the fp16 form into one MMA (7 instead of 9 MMAs per tile and 128-frame half).
+ * "tc_dense_sm" (default 1): the dense pass (sgmm_score_all, sgmm_recognize) is refined by the state-major kernel; 0 = the
+ *   frame-major one.
  * "tc_epi16" (default 0): sixteen instead of eight epilogue warps per GEMM unit (measured slower; kept as an A/B switch).
  * "host_tables" (default 0; read by sgmm_set_model): 1 = derive the model tables on the host (the previous builder, kept
  *   as the checker of the device builder: same tables, same bits).

@@ -28,6 +28,19 @@ def test_library_exports_every_declared_symbol():
     assert b"sm_100a" in lib.sgmm_version()
 
 
+def test_every_option_is_documented_in_the_header():
+    """Every key sgmm_set_option accepts is described in include/sietill_b200.h."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = open(os.path.join(root, "speechrecognition_b200", "csrc", "sgmm_api.cu")).read()
+    body = src[src.index("int sgmm_set_option"):src.index("int sgmm_get_counter")]
+    keys = re.findall(r'!strcmp\(key, "([a-z0-9_]+)"\)', body)
+    header = open(os.path.join(root, "include", "sietill_b200.h")).read()
+    assert len(keys) > 20
+    missing = [k for k in keys if '"%s"' % k not in header]
+    assert not missing, missing
+
+
 def test_no_gpu_is_a_loud_error():
     import torch
     if torch.cuda.is_available():
